@@ -1,0 +1,26 @@
+"""Hot ops of cloud_b200, backed by hand-written sm_100a kernels.
+
+CUDA tensors always go through ``libcloud_b200_kernels.so`` (tcgen05/TMEM GEMM fed by TMA, fused
+cross-entropy, fused optimizers, peer-memory collectives); there is no silent PyTorch fallback on a
+GPU.  CPU tensors use a plain PyTorch implementation of the same maths so that the strategy /
+Keras / tuner layers are testable (and usable: OneDeviceStrategy on the CPU preset) without a GPU.
+
+Reference parity: these are the ops the reference makes TensorFlow execute on the accelerator
+(SURVEY.md section 2.5, K1-K12); the reference itself contains no kernels.
+"""
+from ._lib import KernelsUnavailable, kernels, runtime, check  # noqa: F401
+from .dense import gemm, dense, dense_reference  # noqa: F401
+from .loss import softmax_cross_entropy, softmax_cross_entropy_reference  # noqa: F401
+from .elementwise import dropout, relu_bwd_bias_grad, normalize_u8_images  # noqa: F401
+from .optim import FlatOptimizerState, optim_flat, optim_tick, OPT_CODES, make_hyper  # noqa: F401
+
+KERNEL_LAUNCHES = {"count": 0}
+
+
+def native_available() -> bool:
+    """True when the kernel library can be loaded (says nothing about a GPU being present)."""
+    try:
+        kernels()
+        return True
+    except KernelsUnavailable:
+        return False

@@ -1,0 +1,208 @@
+"""Dense layer ops on the tcgen05 GEMM (``csrc/kernels/gemm_tcgen05.cu``).
+
+``dense(x, w, b, activation)`` is an autograd function whose forward and both backward GEMMs run on
+the hand-written kernel: forward with a fused bias(+ReLU | softmax) epilogue, dgrad with a fused
+ReLU-mask epilogue available through ``gemm(..., relu_mask=)``, wgrad from MN-major operands (no
+transposes), bias gradient fused with the ReLU backward in one memory pass.
+
+Reference workload: ``Dense(512, activation='relu')`` / ``Dense(10, activation='softmax')`` in
+README.md:71-75 (ops K1, K2, K3 of SURVEY.md section 2.5).
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+
+from . import _lib
+
+GEMM_RELU = 1
+GEMM_OUT_F32 = 2
+GEMM_ACCUM = 4
+GEMM_SOFTMAX = 8
+
+_launches = 0
+
+
+def launches() -> int:
+    return _launches
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False,
+         bias: torch.Tensor | None = None, relu: bool = False, softmax: bool = False,
+         relu_mask: torch.Tensor | None = None, out: torch.Tensor | None = None,
+         out_dtype: torch.dtype = torch.bfloat16, accumulate: bool = False,
+         block_n: int = 0) -> torch.Tensor:
+    """C[M,N] = op(A) @ op(B)^T with fused epilogue, bf16 operands, fp32 accumulation in TMEM.
+
+    ``a`` is stored ``[M,K]`` (``a_mn=False``) or ``[K,M]`` (``a_mn=True``); ``b`` is stored
+    ``[N,K]`` (``b_mn=False``) or ``[K,N]`` (``b_mn=True``).  Row pitches must be multiples of 8.
+    """
+    global _launches
+    if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16:
+        raise TypeError("gemm operands must be bfloat16")
+    if a.dim() != 2 or b.dim() != 2 or a.stride(1) != 1 or b.stride(1) != 1:
+        raise ValueError("gemm operands must be 2-D with unit inner stride")
+    if a_mn:
+        K, M = a.shape
+    else:
+        M, K = a.shape
+    if b_mn:
+        Kb, N = b.shape
+    else:
+        N, Kb = b.shape
+    if K != Kb:
+        raise ValueError(f"reduction dims differ: {K} vs {Kb}")
+    if not a.is_cuda:
+        return _gemm_reference(a, b, a_mn, b_mn, bias, relu, softmax, relu_mask, out, out_dtype,
+                               accumulate)
+    if out is None:
+        if accumulate:
+            raise ValueError("accumulate=True needs out=")
+        out = torch.empty((M, N), dtype=out_dtype, device=a.device)
+    flags = 0
+    if relu:
+        flags |= GEMM_RELU
+    if softmax:
+        flags |= GEMM_SOFTMAX
+    if out.dtype == torch.float32:
+        flags |= GEMM_OUT_F32
+    elif out.dtype != torch.bfloat16:
+        raise TypeError("gemm output must be bfloat16 or float32")
+    if accumulate:
+        flags |= GEMM_ACCUM
+    if bias is not None and bias.dtype != torch.float32:
+        bias = bias.float()
+    lib = _lib.kernels()
+    rc = lib.cb2_gemm_bf16(_ptr(a), _ptr(b), _ptr(out), _ptr(bias), _ptr(relu_mask), M, N, K,
+                           a.stride(0), b.stride(0), out.stride(0),
+                           relu_mask.stride(0) if relu_mask is not None else 0,
+                           int(a_mn), int(b_mn), flags, block_n, _stream())
+    _lib.check(rc, "gemm_bf16")
+    _launches += 1
+    return out
+
+
+def _gemm_reference(a, b, a_mn, b_mn, bias, relu, softmax, relu_mask, out, out_dtype, accumulate):
+    af = a.float().t() if a_mn else a.float()
+    bf = b.float() if b_mn else b.float().t()
+    c = af @ bf
+    if bias is not None:
+        c = c + bias.float()
+    if relu:
+        c = torch.relu(c)
+    if softmax:
+        c = torch.softmax(c, dim=-1)
+    if relu_mask is not None:
+        c = torch.where(relu_mask.float() > 0, c, torch.zeros_like(c))
+    if out is not None:
+        if accumulate:
+            out += c.to(out.dtype)
+        else:
+            out.copy_(c.to(out.dtype))
+        return out
+    return c.to(out_dtype)
+
+
+def dense_reference(x, w, b=None, activation=None):
+    """fp32 PyTorch oracle for ``dense``."""
+    y = x.float() @ w.float().t()
+    if b is not None:
+        y = y + b.float()
+    if activation == "relu":
+        y = torch.relu(y)
+    elif activation == "softmax":
+        y = torch.softmax(y, dim=-1)
+    return y
+
+
+def _pad_cols(t: torch.Tensor, mult: int = 8) -> torch.Tensor:
+    r = (-t.shape[-1]) % mult
+    if r == 0:
+        return t if t.is_contiguous() else t.contiguous()
+    return F.pad(t, (0, r))
+
+
+class _DenseFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, b, activation):
+        from .elementwise import relu_bwd_bias_grad  # noqa: F401  (backward dependency)
+        x2 = x.reshape(-1, x.shape[-1])
+        if x2.dtype != torch.bfloat16:
+            x2 = x2.to(torch.bfloat16)
+        x2 = _pad_cols(x2)
+        wk = w if w.dtype == torch.bfloat16 else w.to(torch.bfloat16)
+        wk = _pad_cols(wk)
+        y = gemm(x2, wk, bias=b, relu=(activation == "relu"), softmax=(activation == "softmax"))
+        ctx.activation = activation
+        ctx.x_shape = x.shape
+        ctx.in_features = w.shape[1]
+        ctx.has_bias = b is not None
+        ctx.w_dtype = w.dtype
+        ctx.b_dtype = b.dtype if b is not None else None
+        ctx.x_dtype = x.dtype
+        ctx.save_for_backward(x2, wk, y if activation in ("relu", "softmax") else None)
+        return y.reshape(*x.shape[:-1], w.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        from .elementwise import relu_bwd_bias_grad
+        x2, wk, y = ctx.saved_tensors
+        N = wk.shape[0]
+        dy2 = dy.reshape(-1, N)
+        if dy2.dtype != torch.bfloat16:
+            dy2 = dy2.to(torch.bfloat16)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        if ctx.activation == "softmax":
+            yf = y.float()
+            dz = (yf * (dy2.float() - (dy2.float() * yf).sum(-1, keepdim=True))).to(torch.bfloat16)
+            db = dz.float().sum(0) if ctx.has_bias else None
+        else:
+            need_db = ctx.has_bias and ctx.needs_input_grad[2]
+            dz, db = relu_bwd_bias_grad(dy2, y if ctx.activation == "relu" else None,
+                                        want_db=need_db)
+        # pitch padded to a multiple of 8 for TMA; the logical width stays N (OOB rows/cols read 0)
+        dz = _pad_cols(dz)[:, :N]
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            # dX[M,K] = dZ[M,N] @ W[N,K] : B is stored [reduce=N, K] -> MN-major
+            dx = gemm(dz, wk, b_mn=True)
+            dx = dx[:, :ctx.in_features].reshape(ctx.x_shape).to(ctx.x_dtype)
+        if ctx.needs_input_grad[1]:
+            # dW[N,K] = dZ^T[N,M] @ X[M,K] : both stored [reduce=M, *] -> MN-major
+            dw = gemm(dz, x2, a_mn=True, b_mn=True,
+                      out_dtype=torch.float32 if ctx.w_dtype == torch.float32 else torch.bfloat16)
+            dw = dw[:N, :ctx.in_features]
+            if dw.dtype != ctx.w_dtype:
+                dw = dw.to(ctx.w_dtype)
+        if db is not None and ctx.b_dtype is not None and db.dtype != ctx.b_dtype:
+            db = db.to(ctx.b_dtype)
+        return dx, dw, db, None
+
+
+def dense(x: torch.Tensor, w: torch.Tensor, b: torch.Tensor | None = None,
+          activation: str | None = None) -> torch.Tensor:
+    """``activation(x @ w.T + b)`` with ``w`` in torch layout ``[out, in]``.
+
+    CUDA: bf16 tcgen05 GEMM with fused epilogue (output bf16).  CPU: PyTorch in the input dtype.
+    """
+    if activation not in (None, "linear", "relu", "softmax"):
+        raise ValueError(f"unsupported fused activation: {activation}")
+    if activation == "linear":
+        activation = None
+    if x.is_cuda:
+        return _DenseFn.apply(x, w, b, activation)
+    y = F.linear(x, w.to(x.dtype), None if b is None else b.to(x.dtype))
+    if activation == "relu":
+        y = torch.relu(y)
+    elif activation == "softmax":
+        y = torch.softmax(y, dim=-1)
+    return y

@@ -1,0 +1,127 @@
+"""Memory-bound helper ops: ReLU-backward + bias gradient, Philox dropout, input normalisation.
+
+Kernels: ``csrc/kernels/elementwise.cu``.  Reference workloads: ``Dropout(0.2)`` README.md:73 (K5),
+bias gradients of every Dense layer (K3), the ``tf.data`` map that scales images to floats
+(core/tests/testdata/mnist_example_using_fit.py:49-51, K12).
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from . import _lib
+
+_launches = 0
+
+
+def launches() -> int:
+    return _launches
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def relu_bwd_bias_grad(dy: torch.Tensor, y: torch.Tensor | None, want_db: bool = True,
+                       db_dtype: torch.dtype = torch.float32):
+    """Returns ``(dz, db)`` with ``dz = dy * (y > 0)`` (``dz = dy`` if ``y`` is None) and
+    ``db = dz.sum(0)``; one pass over ``dy``."""
+    global _launches
+    M, N = dy.shape
+    if not dy.is_cuda:
+        dz = dy if y is None else torch.where(y > 0, dy, torch.zeros_like(dy))
+        return dz, (dz.float().sum(0).to(db_dtype) if want_db else None)
+    if y is None and not want_db:
+        return dy, None
+    if dy.dtype != torch.bfloat16:
+        raise TypeError("relu_bwd_bias_grad expects bfloat16 gradients")
+    dz = torch.empty_like(dy) if y is not None else dy
+    db = torch.empty(N, dtype=db_dtype, device=dy.device) if want_db else None
+    rc = _lib.kernels().cb2_relu_bwd_bias_grad(
+        dy.data_ptr(), None if y is None else y.data_ptr(),
+        dz.data_ptr() if y is not None else None, None if db is None else db.data_ptr(),
+        0 if db_dtype == torch.float32 else 1, M, N, dy.stride(0), 0, _stream())
+    _lib.check(rc, "relu_bwd_bias_grad")
+    _launches += 1
+    return dz, db
+
+
+class _DropoutFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, p, seed, offset):
+        ctx.p, ctx.seed, ctx.offset = p, seed, offset
+        return _dropout_apply(x, p, seed, offset)
+
+    @staticmethod
+    def backward(ctx, dy):
+        # same (seed, offset) => same mask: nothing saved between forward and backward
+        return _dropout_apply(dy.contiguous(), ctx.p, ctx.seed, ctx.offset), None, None, None
+
+
+def _dropout_apply(x, p, seed, offset):
+    global _launches
+    xc = x if x.is_contiguous() else x.contiguous()
+    y = torch.empty_like(xc)
+    if xc.dtype == torch.float32:
+        dt = 0
+    elif xc.dtype == torch.bfloat16:
+        dt = 1
+    else:
+        raise TypeError("dropout supports float32 and bfloat16")
+    rc = _lib.kernels().cb2_dropout(xc.data_ptr(), y.data_ptr(), xc.numel(), float(p),
+                                    ctypes.c_uint64(seed), ctypes.c_uint64(offset), dt, _stream())
+    _lib.check(rc, "dropout")
+    _launches += 1
+    return y
+
+
+_dropout_counter = {"offset": 0}
+
+
+def dropout(x: torch.Tensor, p: float, training: bool = True, seed: int | None = None,
+            offset: int | None = None) -> torch.Tensor:
+    """Inverted dropout.  CUDA: Philox mask recomputed in backward (no mask tensor)."""
+    if not training or p <= 0.0:
+        return x
+    if not x.is_cuda:
+        return torch.nn.functional.dropout(x, p, training=True)
+    if seed is None:
+        seed = torch.initial_seed() & 0xFFFFFFFFFFFFFFFF
+    if offset is None:
+        offset = _dropout_counter["offset"]
+        _dropout_counter["offset"] += (x.numel() + 3) // 4
+    return _DropoutFn.apply(x, float(p), int(seed), int(offset))
+
+
+_IMAGENET_MEAN = (0.485, 0.456, 0.406)
+_IMAGENET_STD = (0.229, 0.224, 0.225)
+
+
+def normalize_u8_images(images: torch.Tensor, mean=_IMAGENET_MEAN, std=_IMAGENET_STD,
+                        out: torch.Tensor | None = None) -> torch.Tensor:
+    """uint8 NHWC ``[N,H,W,C]`` -> bf16 NHWC ``(x/255 - mean) / std`` (channels_last memory)."""
+    global _launches
+    if images.dtype != torch.uint8:
+        raise TypeError("normalize_u8_images expects uint8")
+    C = images.shape[-1]
+    if not images.is_cuda:
+        m = torch.tensor(mean, dtype=torch.float32)[:C] if C <= 3 else torch.tensor(mean).repeat(C)[:C]
+        s = torch.tensor(std, dtype=torch.float32)[:C] if C <= 3 else torch.tensor(std).repeat(C)[:C]
+        r = ((images.float() / 255.0 - m) / s).to(torch.bfloat16)
+        if out is not None:
+            out.copy_(r)
+            return out
+        return r
+    images = images.contiguous()
+    if out is None:
+        out = torch.empty(images.shape, dtype=torch.bfloat16, device=images.device)
+    arr = ctypes.c_float * 3
+    m = arr(*[float(v) for v in mean])
+    s = arr(*[1.0 / float(v) for v in std])
+    n_pixels = images.numel() // C
+    rc = _lib.kernels().cb2_u8_to_bf16_normalize(images.data_ptr(), out.data_ptr(), n_pixels, C, m, s,
+                                                 _stream())
+    _lib.check(rc, "u8_to_bf16_normalize")
+    _launches += 1
+    return out

@@ -1,0 +1,480 @@
+// Dense-layer GEMM for B200 (sm_100a): C[M,N] = op(A)[M,K] * op(B)[N,K]^T with a fused epilogue.
+//
+//   * operands: bf16, staged global->shared by TMA (cp.async.bulk.tensor, 128B swizzle),
+//   * math: tcgen05.mma (kind::f16, cta_group::1, 128 x BN x 16) issued by one thread,
+//   * accumulators: fp32 in TMEM, double buffered (2 x BN columns) so the epilogue of tile i
+//     overlaps the main loop of tile i+1,
+//   * persistent: one CTA per SM, static round-robin tile schedule,
+//   * warp roles: warp0 = TMA producer, warp1 = TMEM owner + MMA issuer, warps2-5 = epilogue
+//     (tcgen05.ld -> bias / ReLU / ReLU-mask / row-softmax -> bf16|fp32 store or accumulate).
+//
+// Both operands may be K-major (reduction dim contiguous) or MN-major, which covers the three
+// GEMMs of a Dense layer without any transpose kernel:
+//   forward  Y  = X  W^T        A=X  [M,K]  K-major,  B=W  [N,K] K-major
+//   dgrad    dX = dY W          A=dY [M,N'] K-major,  B=W  stored [N',K'] -> MN-major
+//   wgrad    dW = dY^T X        A=dY stored [Mb,N] -> MN-major, B=X stored [Mb,K] -> MN-major
+//
+// Reference parity: this is op K1/K2/K3 of SURVEY.md section 2.5 (the Dense layers the reference's
+// workloads run through TensorFlow, e.g. README.md:71-75); the reference itself has no kernel.
+#include <cuda.h>
+
+#include <mutex>
+
+#include "common.cuh"
+#include "../../include/cloud_b200_kernels.h"
+
+namespace cb2 {
+
+constexpr int BM = 128;
+constexpr int BK = 64;          // 64 bf16 = one 128-byte swizzle span
+constexpr int UMMA_K = 16;
+constexpr int kGemmThreads = 192;
+constexpr int kAStageBytes = BM * BK * 2;
+
+struct GemmArgs {
+  int M, N, K;
+  int ldc, ldmask;
+  void* C;
+  const float* bias;
+  const __nv_bfloat16* mask;
+  uint32_t flags;
+  int m_tiles, n_tiles, k_blocks;
+  uint32_t a_lbo, a_sbo, b_lbo, b_sbo;  // descriptor fields, 16-byte units
+  uint32_t a_kadv, b_kadv;              // start-address advance per UMMA_K step, 16-byte units
+};
+
+template <int BN>
+struct GemmCfg {
+  static constexpr int kStages = BN == 64 ? 8 : (BN == 128 ? 6 : 4);
+  static constexpr int kBStageBytes = BN * BK * 2;
+  static constexpr int kStageBytes = kAStageBytes + kBStageBytes;
+  static constexpr int kTmemCols = 2 * BN;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((saddr >> 4) & 0x3FFFu);
+  d |= static_cast<uint64_t>(lbo & 0x3FFFu) << 16;
+  d |= static_cast<uint64_t>(sbo & 0x3FFFu) << 32;
+  d |= 1ull << 46;  // descriptor version: Blackwell
+  d |= 2ull << 61;  // SWIZZLE_128B
+  return d;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const GemmArgs p) {
+  using Cfg = GemmCfg<BN>;
+  constexpr int kStages = Cfg::kStages;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + kStages * kAStageBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+  uint64_t* full_bar = bars;                    // [kStages] TMA -> MMA
+  uint64_t* empty_bar = bars + kStages;         // [kStages] MMA -> TMA
+  uint64_t* tfull_bar = bars + 2 * kStages;     // [2] MMA -> epilogue
+  uint64_t* tempty_bar = bars + 2 * kStages + 2;  // [2] epilogue -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull_bar[a], 1);
+      mbar_init(&tempty_bar[a], 4);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, Cfg::kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int num_tiles = p.m_tiles * p.n_tiles;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m0 = (tile / p.n_tiles) * BM;
+        const int n0 = (tile % p.n_tiles) * BN;
+        for (int kb = 0; kb < p.k_blocks; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          uint8_t* sa = smem_a + stage * kAStageBytes;
+          uint8_t* sb = smem_b + stage * Cfg::kBStageBytes;
+          const int k0 = kb * BK;
+          if (!A_MN) {
+            tma_load_2d(&tmA, &full_bar[stage], sa, k0, m0);  // box {64 k, 128 rows}
+          } else {
+#pragma unroll
+            for (int c = 0; c < BM / 64; ++c)  // box {64 m, 64 k}
+              tma_load_2d(&tmA, &full_bar[stage], sa + c * (BK * 128), m0 + c * 64, k0);
+          }
+          if (!B_MN) {
+            tma_load_2d(&tmB, &full_bar[stage], sb, k0, n0);  // box {64 k, BN rows}
+          } else {
+#pragma unroll
+            for (int c = 0; c < BN / 64; ++c)  // box {64 n, 64 k}
+              tma_load_2d(&tmB, &full_bar[stage], sb + c * (BK * 128), n0 + c * 64, k0);
+          }
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      const uint32_t idesc = (1u << 4) /*D=f32*/ | (1u << 7) /*A=bf16*/ | (1u << 10) /*B=bf16*/ |
+                             ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
+                             (static_cast<uint32_t>(BN >> 3) << 17) |
+                             (static_cast<uint32_t>(BM >> 4) << 24);
+      int stage = 0;
+      uint32_t phase = 0;
+      int t = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
+        const int acc = t & 1;
+        const uint32_t acc_phase = (t >> 1) & 1;
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * BN;
+        for (int kb = 0; kb < p.k_blocks; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint64_t adesc =
+              make_smem_desc(smem_u32(smem_a + stage * kAStageBytes), p.a_lbo, p.a_sbo);
+          const uint64_t bdesc =
+              make_smem_desc(smem_u32(smem_b + stage * Cfg::kBStageBytes), p.b_lbo, p.b_sbo);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            umma_bf16(tmem_d, adesc + static_cast<uint64_t>(k * p.a_kadv),
+                      bdesc + static_cast<uint64_t>(k * p.b_kadv), idesc, (kb | k) != 0);
+          }
+          umma_commit(&empty_bar[stage]);  // smem slot reusable once these MMAs retire
+          if (kb == p.k_blocks - 1) umma_commit(&tfull_bar[acc]);
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ===================== epilogue (4 warps, TMEM lane quarter = warp % 4) =====================
+    const int q = warp & 3;
+    const bool out_f32 = (p.flags & CB2_GEMM_OUT_F32) != 0;
+    const bool accum = (p.flags & CB2_GEMM_ACCUM) != 0;
+    const bool relu = (p.flags & CB2_GEMM_RELU) != 0;
+    const bool softmax = (p.flags & CB2_GEMM_SOFTMAX) != 0;
+    const bool has_bias = p.bias != nullptr;
+    const bool has_mask = p.mask != nullptr;
+    const bool vec_ok =
+        out_f32 ? ((p.ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(p.C) & 15) == 0)
+                : ((p.ldc & 7) == 0 && (reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
+    int t = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
+      const int acc = t & 1;
+      const uint32_t acc_phase = (t >> 1) & 1;
+      const int m0 = (tile / p.n_tiles) * BM;
+      const int n0 = (tile % p.n_tiles) * BN;
+      const int row = m0 + q * 32 + lane;
+      const bool row_ok = row < p.M;
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+
+      float row_max = -INFINITY, row_sum = 0.f;
+      if (softmax) {
+        // N <= BN (checked on the host): the whole row lives in this thread's TMEM lane.
+        for (int c0 = 0; c0 < BN && n0 + c0 < p.N; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32(taddr + c0, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const int n = n0 + c0 + i;
+            if (n < p.N) {
+              float f = __uint_as_float(v[i]) + (has_bias ? __ldg(p.bias + n) : 0.f);
+              row_max = fmaxf(row_max, f);
+            }
+          }
+        }
+        for (int c0 = 0; c0 < BN && n0 + c0 < p.N; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32(taddr + c0, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const int n = n0 + c0 + i;
+            if (n < p.N) {
+              float f = __uint_as_float(v[i]) + (has_bias ? __ldg(p.bias + n) : 0.f);
+              row_sum += exp2f((f - row_max) * 1.4426950408889634f);
+            }
+          }
+        }
+        row_sum = 1.f / row_sum;
+      }
+
+      for (int c0 = 0; c0 < BN && n0 + c0 < p.N; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32(taddr + c0, v);
+        tmem_ld_wait();
+        float f[32];
+        const int nb = n0 + c0;
+        const bool full = nb + 32 <= p.N;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          f[i] = __uint_as_float(v[i]);
+          if (has_bias && (full || nb + i < p.N)) f[i] += __ldg(p.bias + nb + i);
+          if (relu) f[i] = fmaxf(f[i], 0.f);
+          if (softmax) f[i] = exp2f((f[i] - row_max) * 1.4426950408889634f) * row_sum;
+        }
+        if (row_ok) {
+        if (has_mask) {
+          const __nv_bfloat16* mrow = p.mask + static_cast<size_t>(row) * p.ldmask + nb;
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if ((full || nb + i < p.N) && !(__bfloat162float(mrow[i]) > 0.f)) f[i] = 0.f;
+        }
+        if (out_f32) {
+          float* crow = reinterpret_cast<float*>(p.C) + static_cast<size_t>(row) * p.ldc + nb;
+          if (full && vec_ok) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) {
+              float4 o = make_float4(f[i], f[i + 1], f[i + 2], f[i + 3]);
+              if (accum) {
+                const float4 old = *reinterpret_cast<const float4*>(crow + i);
+                o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
+              }
+              *reinterpret_cast<float4*>(crow + i) = o;
+            }
+          } else {
+            for (int i = 0; i < 32; ++i)
+              if (nb + i < p.N) crow[i] = accum ? crow[i] + f[i] : f[i];
+          }
+        } else {
+          __nv_bfloat16* crow =
+              reinterpret_cast<__nv_bfloat16*>(p.C) + static_cast<size_t>(row) * p.ldc + nb;
+          if (full && vec_ok) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 8) {
+              uint4 o;
+              o.x = pack_bf16(f[i], f[i + 1]);
+              o.y = pack_bf16(f[i + 2], f[i + 3]);
+              o.z = pack_bf16(f[i + 4], f[i + 5]);
+              o.w = pack_bf16(f[i + 6], f[i + 7]);
+              *reinterpret_cast<uint4*>(crow + i) = o;
+            }
+          } else {
+            for (int i = 0; i < 32; ++i)
+              if (nb + i < p.N) crow[i] = __float2bfloat16(f[i]);
+          }
+        }
+        }  // row_ok
+        __syncwarp();  // reconverge before the next warp-collective tcgen05.ld
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, Cfg::kTmemCols);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Host side
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) ==
+            cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(sym);
+  });
+  return fn;
+}
+
+// 2-D bf16 tensor map over a row-major [outer, inner] view with row pitch `ld` elements.
+static int make_tmap(CUtensorMap* tm, const void* base, uint64_t inner, uint64_t outer, uint64_t ld,
+                     uint32_t box_inner, uint32_t box_outer) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) {
+    set_last_error("cuTensorMapEncodeTiled entry point not available");
+    return CB2_ERR_CUDA;
+  }
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {ld * 2};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides,
+                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_last_error("cuTensorMapEncodeTiled failed (%d): inner=%llu outer=%llu ld=%llu box=%ux%u",
+                   static_cast<int>(r), (unsigned long long)inner, (unsigned long long)outer,
+                   (unsigned long long)ld, box_inner, box_outer);
+    return CB2_ERR_CUDA;
+  }
+  return 0;
+}
+
+struct DescOverride {
+  bool on = false;
+  uint32_t a_lbo, a_sbo, b_lbo, b_sbo, a_kadv, b_kadv;
+};
+static DescOverride g_desc_override;
+
+static int num_sms() {
+  static int cached[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (!cached[dev]) cudaDeviceGetAttribute(&cached[dev], cudaDevAttrMultiProcessorCount, dev);
+  return cached[dev];
+}
+
+template <int BN, bool A_MN, bool B_MN>
+static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& args,
+                       cudaStream_t stream) {
+  using Cfg = GemmCfg<BN>;
+  auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN>;
+  static bool configured = false;
+  if (!configured) {
+    CB2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     Cfg::kSmemBytes));
+    configured = true;
+  }
+  const int tiles = args.m_tiles * args.n_tiles;
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(tmA, tmB, args);
+  return check_cuda(cudaGetLastError(), "gemm_tcgen05 launch");
+}
+
+}  // namespace cb2
+
+using namespace cb2;
+
+extern "C" int cb2_gemm_debug_descriptors(int enable, unsigned a_lbo, unsigned a_sbo, unsigned b_lbo,
+                                          unsigned b_sbo, unsigned a_kadv, unsigned b_kadv) {
+  g_desc_override.on = enable != 0;
+  g_desc_override.a_lbo = a_lbo;
+  g_desc_override.a_sbo = a_sbo;
+  g_desc_override.b_lbo = b_lbo;
+  g_desc_override.b_sbo = b_sbo;
+  g_desc_override.a_kadv = a_kadv;
+  g_desc_override.b_kadv = b_kadv;
+  return 0;
+}
+
+extern "C" int cb2_gemm_bf16(const void* A, const void* B, void* C, const float* bias,
+                             const void* relu_mask, int M, int N, int K, int lda, int ldb, int ldc,
+                             int ldmask, int a_mn, int b_mn, unsigned flags, int block_n,
+                             void* stream) {
+  if (M <= 0 || N <= 0 || K <= 0) {
+    set_last_error("gemm: empty problem M=%d N=%d K=%d", M, N, K);
+    return CB2_ERR_ARG;
+  }
+  if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15) || (lda & 7) ||
+      (ldb & 7)) {
+    set_last_error("gemm: TMA needs 16-byte aligned operand bases and row pitches (lda=%d ldb=%d)",
+                   lda, ldb);
+    return CB2_ERR_ARG;
+  }
+  if ((flags & CB2_GEMM_ACCUM) && !(flags & CB2_GEMM_OUT_F32)) {
+    set_last_error("gemm: ACCUM requires OUT_F32");
+    return CB2_ERR_ARG;
+  }
+  const bool softmax = (flags & CB2_GEMM_SOFTMAX) != 0;
+  int bn = block_n;
+  if (bn == 0) {
+    if (N <= 64) bn = 64;
+    else if (N <= 128) bn = 128;
+    else {
+      const int mt = (M + BM - 1) / BM;
+      const int sms = num_sms();
+      if (mt * ((N + 255) / 256) >= sms) bn = 256;
+      else if (mt * ((N + 127) / 128) >= sms / 2) bn = 128;
+      else bn = 64;
+      if (softmax) bn = 256;
+    }
+  }
+  if (bn != 64 && bn != 128 && bn != 256) {
+    set_last_error("gemm: block_n must be 64, 128 or 256 (got %d)", bn);
+    return CB2_ERR_ARG;
+  }
+  if (softmax && N > bn) {
+    set_last_error("gemm: softmax epilogue needs N <= block_n (N=%d)", N);
+    return CB2_ERR_ARG;
+  }
+
+  CUtensorMap tmA, tmB;
+  int rc;
+  if (!a_mn) rc = make_tmap(&tmA, A, K, M, lda, BK, BM);
+  else       rc = make_tmap(&tmA, A, M, K, lda, 64, BK);
+  if (rc) return rc;
+  if (!b_mn) rc = make_tmap(&tmB, B, K, N, ldb, BK, bn);
+  else       rc = make_tmap(&tmB, B, N, K, ldb, 64, BK);
+  if (rc) return rc;
+
+  GemmArgs args;
+  args.M = M; args.N = N; args.K = K;
+  args.ldc = ldc; args.ldmask = ldmask;
+  args.C = C; args.bias = bias;
+  args.mask = reinterpret_cast<const __nv_bfloat16*>(relu_mask);
+  args.flags = flags;
+  args.m_tiles = (M + BM - 1) / BM;
+  args.n_tiles = (N + bn - 1) / bn;
+  args.k_blocks = (K + BK - 1) / BK;
+  // K-major, 128B swizzle: 8-row groups are 1024 B apart (SBO); LBO unused (=1);
+  //                        one UMMA_K step = 16 elements = 32 B inside the swizzle span.
+  // MN-major, 128B swizzle: 64-element MN chunks are BK*128 B apart (LBO); 8-k-row groups are
+  //                        1024 B apart (SBO); one UMMA_K step = 16 k-rows = 2048 B.
+  args.a_lbo = a_mn ? (BK * 128) >> 4 : 1;
+  args.a_sbo = 1024 >> 4;
+  args.a_kadv = a_mn ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
+  args.b_lbo = b_mn ? (BK * 128) >> 4 : 1;
+  args.b_sbo = 1024 >> 4;
+  args.b_kadv = b_mn ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
+  if (g_desc_override.on) {
+    args.a_lbo = g_desc_override.a_lbo; args.a_sbo = g_desc_override.a_sbo;
+    args.b_lbo = g_desc_override.b_lbo; args.b_sbo = g_desc_override.b_sbo;
+    args.a_kadv = g_desc_override.a_kadv; args.b_kadv = g_desc_override.b_kadv;
+  }
+
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+#define CB2_DISPATCH(BNV)                                                            \
+  if (!a_mn && !b_mn) return launch_gemm<BNV, false, false>(tmA, tmB, args, s);      \
+  if (!a_mn && b_mn) return launch_gemm<BNV, false, true>(tmA, tmB, args, s);        \
+  if (a_mn && b_mn) return launch_gemm<BNV, true, true>(tmA, tmB, args, s);          \
+  return launch_gemm<BNV, true, false>(tmA, tmB, args, s);
+  if (bn == 64) { CB2_DISPATCH(64) }
+  if (bn == 128) { CB2_DISPATCH(128) }
+  CB2_DISPATCH(256)
+#undef CB2_DISPATCH
+}

@@ -1,0 +1,137 @@
+/* cloud_b200 kernel library - C ABI (libcloud_b200_kernels.so, sm_100a only).
+ *
+ * Every function returns 0 on success or a CB2_ERR_* code; cb2_last_error() gives the message of
+ * the calling thread's last failure.  Pointers are device pointers unless noted; `stream` is a
+ * cudaStream_t passed as void*.  Nothing here synchronises the device.
+ *
+ * The reference (marvinx97/cloud, TensorFlow Cloud) has no kernels of its own: each entry cites
+ * the reference workload that makes TensorFlow run the equivalent op.
+ */
+#ifndef CLOUD_B200_KERNELS_H_
+#define CLOUD_B200_KERNELS_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CB2_OK 0
+#define CB2_ERR_ARG 1
+#define CB2_ERR_CUDA 2
+#define CB2_ERR_UNSUPPORTED 3
+
+#define CB2_DTYPE_F32 0
+#define CB2_DTYPE_BF16 1
+
+const char* cb2_last_error(void);
+int cb2_version(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Dense GEMM on tcgen05/TMEM fed by TMA.  C[M,N] = op(A)[M,K] * op(B)[N,K]^T (+ epilogue).
+ *   a_mn = 0: A stored row-major [M, lda>=K]  (K-major);  a_mn = 1: stored [K, lda>=M] (MN-major)
+ *   b_mn = 0: B stored row-major [N, ldb>=K]  (K-major);  b_mn = 1: stored [K, ldb>=N] (MN-major)
+ * A/B are bf16, 16-byte aligned, pitches multiples of 8 elements.  C is bf16 or fp32.
+ * Reference workload: Dense layers of README.md:71-75 (K1/K2/K3).
+ * ------------------------------------------------------------------------------------------ */
+#define CB2_GEMM_RELU 1u      /* max(x, 0) after bias */
+#define CB2_GEMM_OUT_F32 2u   /* C is fp32 (default bf16) */
+#define CB2_GEMM_ACCUM 4u     /* C += result (fp32 C only) - wgrad straight into a grad arena */
+#define CB2_GEMM_SOFTMAX 8u   /* row softmax after bias; needs N <= block_n */
+int cb2_gemm_bf16(const void* A, const void* B, void* C, const float* bias /*nullable, [N]*/,
+                  const void* relu_mask /*nullable bf16 [M,ldmask]: C=0 where mask<=0*/, int M,
+                  int N, int K, int lda, int ldb, int ldc, int ldmask, int a_mn, int b_mn,
+                  unsigned flags, int block_n /*0 = auto, else 64|128|256*/, void* stream);
+/* Test hook: override the shared-memory matrix-descriptor fields (16-byte units). */
+int cb2_gemm_debug_descriptors(int enable, unsigned a_lbo, unsigned a_sbo, unsigned b_lbo,
+                               unsigned b_sbo, unsigned a_kadv, unsigned b_kadv);
+
+/* ------------------------------------------------------------------------------------------
+ * Fused sparse softmax cross-entropy, forward + backward in one pass (K4, K11).
+ *   dlogits = (softmax(logits) - onehot(label)) * grad_scale        (same dtype as logits)
+ *   stats[0] += sum_b loss_b ; stats[1] += #(argmax == label) ; row_loss[b] = loss_b (nullable)
+ * Reference workload: loss='sparse_categorical_crossentropy' README.md:77.
+ * ------------------------------------------------------------------------------------------ */
+int cb2_softmax_xent(const void* logits, int dtype, const int64_t* labels, void* dlogits,
+                     float* row_loss, float* stats, int B, int C, int ld, float grad_scale,
+                     void* stream);
+
+/* dz = dy * (y > 0) (nullable y => dz = dy), db[n] (+)= sum_m dz[m,n].  bf16 tensors. (K3) */
+int cb2_relu_bwd_bias_grad(const void* dy, const void* y, void* dz, void* db, int db_dtype, int M,
+                           int N, int ld, int accumulate, void* stream);
+
+/* Philox dropout, mask recomputed from (seed, offset) in backward: y = x * keep / (1-p). (K5) */
+int cb2_dropout(const void* x, void* y, size_t n, float p, uint64_t seed, uint64_t offset,
+                int dtype, void* stream);
+
+/* uint8 NHWC image -> bf16 NHWC, (x/255 - mean[c]) / std[c].  Input pipeline tail (K12). */
+int cb2_u8_to_bf16_normalize(const uint8_t* in, void* out, size_t n_pixels, int channels,
+                             const float* mean3, const float* inv_std3, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Optimizers over flat arenas (K6, K7).  `hyper` is a device float[16]:
+ *   [0] lr [1] beta1 [2] beta2 [3] eps [4] weight_decay [5] step [6] 1-beta1^t [7] 1-beta2^t
+ *   [8] grad_scale [9] momentum / rho [10] nesterov(0/1) [11] rmsprop momentum
+ * cb2_optim_tick advances [5..7] on the device so the whole step can live in a CUDA graph.
+ * Reference workload: optimizer=Adam README.md:78; SGD cloud_fit/tests/unit/client_test.py:87-89;
+ * RMSprop testdata/keras_tuner_cifar_example.py:76.
+ * ------------------------------------------------------------------------------------------ */
+#define CB2_OPT_NONE 0        /* plain reduction: out = grad_scale * sum */
+#define CB2_OPT_ADAM_KERAS 1  /* p -= lr*sqrt(bc2)/bc1 * m / (sqrt(v) + eps) */
+#define CB2_OPT_ADAM_TORCH 2  /* p -= lr/bc1 * m / (sqrt(v/bc2) + eps) */
+#define CB2_OPT_ADAMW 3       /* ADAM_TORCH with decoupled weight decay */
+#define CB2_OPT_SGD 4         /* buf = mu*buf + g ; p -= lr*(nesterov ? g + mu*buf : buf) */
+#define CB2_OPT_RMSPROP 5     /* ms = rho*ms+(1-rho)g^2 ; mom = mu*mom + lr*g/sqrt(ms+eps) ; p -= mom */
+#define CB2_HYPER_LEN 16
+int cb2_optim_tick(float* hyper, void* stream);
+/* master fp32 [n] (nullable => param_out is the fp32 master), s1/s2 fp32 state (m,v | buf | ms,mom) */
+int cb2_optim_flat(int opt, float* master, const void* grad, int grad_dtype, float* s1, float* s2,
+                   void* param_out, int param_dtype, size_t n, const float* hyper, int zero_grad,
+                   void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Peer-memory collectives over NVLink/NVSwitch (K9, K10, K11), fused with the optimizer.
+ * All ranks launch the same call with the same sizes, in the same order, on one stream each.
+ * Reference: implied by MirroredStrategy()/MultiWorkerMirroredStrategy() core/preprocess.py:139-143.
+ * ------------------------------------------------------------------------------------------ */
+#define CB2_MAX_RANKS 8
+#define CB2_COMM_MAX_BLOCKS 128
+#define CB2_COMM_AUX_FLOATS 256
+/* signal pad bytes each rank must provide (zero-initialised, symmetric): flags then aux floats */
+#define CB2_COMM_PAD_BYTES (CB2_COMM_MAX_BLOCKS * CB2_MAX_RANKS * 4 + CB2_COMM_AUX_FLOATS * 4)
+
+#define CB2_ALGO_ONESHOT 0  /* every rank reduces everything (replicated state); latency bound */
+#define CB2_ALGO_TWOSHOT 1  /* reduce-scatter by peer loads -> update shard -> all-gather by peer stores */
+#define CB2_ALGO_NVLS 2     /* multimem.ld_reduce (in-switch sum) -> update shard -> multimem.st */
+
+typedef struct {
+  int rank, world;
+  void* grad_ptrs[CB2_MAX_RANKS];   /* this rank's mapping of every rank's gradient arena */
+  void* param_ptrs[CB2_MAX_RANKS];  /* ... parameter / output arena */
+  void* pad_ptrs[CB2_MAX_RANKS];    /* ... signal pad (CB2_COMM_PAD_BYTES) */
+  void* mc_grad;                    /* multicast mapping of the gradient arena (NVLS) or NULL */
+  void* mc_param;                   /* multicast mapping of the parameter arena or NULL */
+  uint32_t* epochs;                 /* local uint32[CB2_COMM_MAX_BLOCKS], zero-initialised */
+} cb2_comm_ctx;
+
+/* Reduce grad[off, off+len) over ranks, apply `opt` to the owned part, publish parameters.
+ *   ONESHOT: state arrays cover the whole range, indexed [state_off + i].
+ *   TWOSHOT/NVLS: this rank owns [off + rank*len/world, +len/world); state indexed
+ *                 [state_off + i] for i in the owned shard.
+ * len must be a multiple of 8*world, off a multiple of 8.  aux_len fp32 scalars living in the
+ * signal pad are sum-reduced one-shot into aux_out (loss / accuracy counters) by block 0. */
+int cb2_comm_fused(const cb2_comm_ctx* ctx, int algo, int opt, int grad_dtype, int param_dtype,
+                   size_t off, size_t len, float* master, float* s1, float* s2, size_t state_off,
+                   const float* hyper, int zero_grads, int aux_len, float* aux_out, int blocks,
+                   void* stream);
+/* Copy param[off, off+len) of `root` into every rank's parameter arena (initial variable sync). */
+int cb2_comm_broadcast(const cb2_comm_ctx* ctx, int root, int dtype, size_t off, size_t len,
+                       int use_multicast, int blocks, void* stream);
+/* Device-side barrier across ranks (one block). */
+int cb2_comm_barrier(const cb2_comm_ctx* ctx, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CLOUD_B200_KERNELS_H_ */

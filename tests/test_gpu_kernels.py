@@ -1,0 +1,223 @@
+"""GPU numerics tests: every hand-written kernel against a plain PyTorch fp32 oracle of the same op.
+
+Run on a B200 with ``python -m pytest tests -m gpu``.  (The reference has no GPU tests at all -
+SURVEY.md section 4 - so this tier is new.)
+"""
+import math
+
+import pytest
+import torch
+
+from cloud_b200 import ops
+from cloud_b200.ops import dense as dense_ops
+from cloud_b200.ops.optim import _reference_update
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev():
+    return torch.device("cuda:0")
+
+
+def _rand_bf16(*shape, scale=1.0):
+    return (torch.randn(*shape, device=_dev()) * scale).to(torch.bfloat16)
+
+
+def _check_close(got, want, rtol, atol, what=""):
+    got = got.float()
+    want = want.float()
+    err = (got - want).abs()
+    tol = atol + rtol * want.abs()
+    bad = (err > tol).sum().item()
+    assert bad == 0, f"{what}: {bad}/{err.numel()} mismatches, max err {err.max().item():.4g}"
+
+
+GEMM_SHAPES = [
+    # M, N, K
+    (128, 128, 64),
+    (128, 512, 784),     # README MLP layer 1 (README.md:72)
+    (128, 10, 512),      # README MLP layer 2, N not a multiple of 8
+    (256, 256, 4096),
+    (1000, 136, 520),    # ragged tiles in every dimension
+    (4096, 2048, 1024),
+    (64, 120, 2048),     # ResNet head (call_run_within_script_with_keras_fit.py:83-85)
+]
+
+
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+@pytest.mark.parametrize("block_n", [0, 64, 128, 256])
+def test_gemm_kmajor_forward(M, N, K, block_n):
+    torch.manual_seed(0)
+    a = _rand_bf16(M, K)
+    b = _rand_bf16(N, K)
+    bias = torch.randn(N, device=_dev())
+    got = ops.gemm(a, b, bias=bias, relu=True, block_n=block_n)
+    want = torch.relu(a.float() @ b.float().t() + bias)
+    _check_close(got, want, rtol=1e-2, atol=1e-2 * math.sqrt(K), what=f"fwd {M}x{N}x{K}")
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (256, 512, 128), (1000, 136, 520), (512, 784, 512)])
+def test_gemm_b_mn_major_dgrad(M, N, K):
+    # C[M,N] = A[M,K] @ Bst[K,N]   (B stored [K,N] -> MN-major)
+    torch.manual_seed(1)
+    a = _rand_bf16(M, K)
+    bst = _rand_bf16(K, N)
+    got = ops.gemm(a, bst, b_mn=True)
+    want = a.float() @ bst.float()
+    _check_close(got, want, rtol=1e-2, atol=1e-2 * math.sqrt(K), what="dgrad")
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (512, 784, 128), (136, 520, 1000), (64, 2048, 4096)])
+def test_gemm_both_mn_major_wgrad(M, N, K):
+    # C[M,N] = Ast[K,M]^T @ Bst[K,N]
+    torch.manual_seed(2)
+    ast = _rand_bf16(K, M)
+    bst = _rand_bf16(K, N)
+    got = ops.gemm(ast, bst, a_mn=True, b_mn=True, out_dtype=torch.float32)
+    want = ast.float().t() @ bst.float()
+    _check_close(got, want, rtol=1e-2, atol=1e-2 * math.sqrt(K), what="wgrad")
+
+
+def test_gemm_accumulate_and_mask():
+    torch.manual_seed(3)
+    M, N, K = 256, 192, 320
+    a, b = _rand_bf16(M, K), _rand_bf16(N, K)
+    out = torch.randn(M, N, device=_dev())
+    base = out.clone()
+    ops.gemm(a, b, out=out, accumulate=True)
+    _check_close(out, base + a.float() @ b.float().t(), 1e-2, 0.3, "accumulate")
+    mask = _rand_bf16(M, N)
+    got = ops.gemm(a, b, relu_mask=mask)
+    want = torch.where(mask.float() > 0, a.float() @ b.float().t(), torch.zeros(M, N, device=_dev()))
+    _check_close(got, want, 1e-2, 0.3, "mask")
+
+
+def test_gemm_softmax_epilogue():
+    torch.manual_seed(4)
+    M, N, K = 300, 10, 512
+    a, b = _rand_bf16(M, K, scale=0.1), _rand_bf16(N, K, scale=0.1)
+    bias = torch.randn(N, device=_dev())
+    got = ops.gemm(a, b, bias=bias, softmax=True, out_dtype=torch.float32)
+    want = torch.softmax(a.float() @ b.float().t() + bias, dim=-1)
+    _check_close(got, want, 1e-2, 1e-3, "softmax")
+    assert torch.allclose(got.sum(-1), torch.ones(M, device=_dev()), atol=1e-3)
+
+
+@pytest.mark.parametrize("activation", [None, "relu", "softmax"])
+@pytest.mark.parametrize("M,K,N", [(128, 784, 512), (96, 512, 10), (64, 2048, 120)])
+def test_dense_autograd(activation, M, K, N):
+    torch.manual_seed(5)
+    x = (torch.randn(M, K, device=_dev()) * 0.5).to(torch.bfloat16).requires_grad_(True)
+    w = (torch.randn(N, K, device=_dev()) / math.sqrt(K)).to(torch.bfloat16).requires_grad_(True)
+    b = (torch.randn(N, device=_dev()) * 0.1).requires_grad_(True)
+    y = ops.dense(x, w, b, activation)
+    gy = torch.randn_like(y.float()).to(torch.bfloat16)
+    y.backward(gy)
+    xr = x.detach().float().requires_grad_(True)
+    wr = w.detach().float().requires_grad_(True)
+    br = b.detach().clone().requires_grad_(True)
+    yr = ops.dense_reference(xr, wr, br, activation)
+    yr.backward(gy.float())
+    _check_close(y, yr, 2e-2, 2e-2, "dense fwd")
+    _check_close(x.grad, xr.grad, 3e-2, 3e-2 * math.sqrt(N / 64 + 1), "dense dX")
+    _check_close(w.grad, wr.grad, 3e-2, 3e-2 * math.sqrt(M / 64 + 1), "dense dW")
+    _check_close(b.grad, br.grad, 3e-2, 3e-2 * math.sqrt(M / 64 + 1), "dense db")
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("B,C", [(128, 10), (64, 120), (257, 1000), (8, 33)])
+def test_softmax_xent(dtype, B, C):
+    torch.manual_seed(6)
+    logits = (torch.randn(B, C, device=_dev()) * 3).to(dtype).requires_grad_(True)
+    labels = torch.randint(0, C, (B,), device=_dev())
+    stats = torch.zeros(4, device=_dev())
+    loss = ops.softmax_cross_entropy(logits, labels, stats=stats)
+    loss.backward()
+    ls, d, correct = ops.softmax_cross_entropy_reference(logits.detach(), labels)
+    tol = 1e-5 if dtype == torch.float32 else 2e-2
+    assert abs(loss.item() - ls.item() / B) < 1e-3 * max(1.0, abs(ls.item() / B))
+    _check_close(logits.grad, d, tol, tol / B, "dlogits")
+    assert stats[1].item() == correct.item()
+    assert abs(stats[0].item() - ls.item()) < 1e-3 * max(1.0, abs(ls.item()))
+
+
+def test_relu_bwd_bias_grad():
+    torch.manual_seed(7)
+    for M, N in [(128, 512), (1000, 136), (64, 10), (5000, 64)]:
+        dy, y = _rand_bf16(M, N), _rand_bf16(M, N)
+        dz, db = ops.relu_bwd_bias_grad(dy, y)
+        want = torch.where(y.float() > 0, dy.float(), torch.zeros_like(dy.float()))
+        assert torch.equal(dz.float(), want)
+        _check_close(db, want.sum(0), 1e-3, 1e-2, "db")
+        _, db2 = ops.relu_bwd_bias_grad(dy, None)
+        _check_close(db2, dy.float().sum(0), 1e-3, 1e-2, "db no mask")
+
+
+def test_dropout_mask_replay():
+    torch.manual_seed(8)
+    x = torch.randn(1 << 20, device=_dev(), requires_grad=True)
+    y = ops.dropout(x, 0.2, seed=123, offset=77)
+    keep = (y != 0).float().mean().item()
+    assert abs(keep - 0.8) < 5e-3
+    nz = y != 0
+    assert torch.allclose(y[nz], x[nz] / 0.8)
+    y.sum().backward()
+    assert torch.equal(x.grad != 0, nz)           # backward regenerates the same mask
+    y2 = ops.dropout(x.detach().to(torch.bfloat16), 0.5, seed=123, offset=0)
+    assert abs((y2 != 0).float().mean().item() - 0.5) < 5e-3
+
+
+def test_normalize_u8_images():
+    img = torch.randint(0, 256, (8, 32, 32, 3), dtype=torch.uint8, device=_dev())
+    got = ops.normalize_u8_images(img)
+    want = ops.normalize_u8_images(img.cpu()).to(_dev())
+    _check_close(got, want, 1e-2, 1e-2, "normalize")
+
+
+@pytest.mark.parametrize("opt", ["adam_keras", "adam_torch", "adamw", "sgd", "rmsprop"])
+@pytest.mark.parametrize("gdt,pdt", [(torch.float32, torch.float32), (torch.bfloat16, torch.bfloat16)])
+def test_optim_flat_vs_reference(opt, gdt, pdt):
+    torch.manual_seed(9)
+    n = 100_003
+    code = ops.OPT_CODES[opt]
+    hyper = ops.make_hyper(_dev(), lr=1e-2, weight_decay=0.01, grad_scale=0.5, momentum=0.9,
+                           nesterov=True, rms_momentum=0.5)
+    master = torch.randn(n, device=_dev())
+    s1 = torch.zeros(n, device=_dev())
+    s2 = torch.zeros(n, device=_dev())
+    pout = master.to(pdt).clone()
+    r_master, r_s1, r_s2 = master.cpu().clone(), s1.cpu().clone(), s2.cpu().clone()
+    for _ in range(3):
+        g = torch.randn(n, device=_dev()).to(gdt)
+        ops.optim_tick(hyper)
+        ops.optim_flat(code, master=master, grad=g.clone(), s1=s1, s2=s2, param_out=pout,
+                       hyper=hyper, zero_grad=False)
+        r_master = _reference_update(code, r_master, g.cpu(), r_s1, r_s2, hyper.cpu())
+    _check_close(master, r_master.to(_dev()), 1e-4, 1e-5, f"{opt} master")
+    _check_close(pout, master, 1e-2 if pdt == torch.bfloat16 else 0, 1e-6, f"{opt} param_out")
+    assert hyper[5].item() == 3.0
+
+
+def test_adam_torch_matches_torch_optim():
+    torch.manual_seed(10)
+    n = 4096
+    p = torch.randn(n, device=_dev())
+    ref = p.clone().requires_grad_(True)
+    opt = torch.optim.Adam([ref], lr=1e-3, eps=1e-8)
+    hyper = ops.make_hyper(_dev(), lr=1e-3, eps=1e-8)
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    for _ in range(5):
+        g = torch.randn(n, device=_dev())
+        ref.grad = g.clone()
+        opt.step()
+        ops.optim_tick(hyper)
+        ops.optim_flat(ops.OPT_CODES["adam_torch"], master=None, grad=g, s1=m, s2=v, param_out=p,
+                       hyper=hyper, zero_grad=True)
+        assert g.abs().sum().item() == 0.0
+    _check_close(p, ref.detach(), 1e-5, 1e-6, "adam vs torch")
+
+
+def test_kernel_launch_counters_move():
+    before = dense_ops.launches()
+    ops.gemm(_rand_bf16(128, 64), _rand_bf16(64, 64))
+    assert dense_ops.launches() == before + 1
