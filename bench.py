@@ -1,0 +1,254 @@
+#!/usr/bin/env python
+"""Headline benchmark: ResNet-50 training throughput (img/s) on 1..8 B200, bf16, synthetic data.
+
+    python bench.py --gpus 1 --steps 30 --warmup 5
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
+        --master-port 29500 bench.py --gpus 8 --steps 30 --warmup 5
+
+Metric and config are BASELINE.json's: "ResNet-50 bf16 MirroredStrategy 224x224 synthetic images"
+(model of core/tests/examples/call_run_within_script_with_keras_fit.py:79-109, all 25.6 M
+parameters trained, Adam, per-replica batch 64 as in that example -> weak scaling).  The step is
+the full training step: forward, fused cross-entropy, backward, fused all-reduce + Adam.
+
+Two numbers are measured, both through the public Keras-shaped API of cloud_b200:
+  * value : device-timed (CUDA events, barrier + synchronize on both sides, max over ranks) over K
+            steps on a device-resident synthetic batch,
+  * e2e   : ``model.fit`` over pinned host arrays: every step copies its uint8 images + labels
+            host->device and the running loss is read back device->host for a per-batch callback.
+--impl reference runs the unmodified reference from baseline/_ref; it needs TensorFlow, which is
+not installable here, so it reports itself unavailable.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+
+
+def reference_arm(args) -> int:
+    ref = os.path.join(os.path.dirname(os.path.abspath(__file__)), "baseline", "_ref")
+    why = None
+    if not os.path.isdir(os.path.join(ref, "tensorflow_cloud")):
+        why = "baseline/_ref is empty: the reference could not be installed offline"
+    else:
+        sys.path.insert(0, ref)
+        try:
+            import tensorflow  # noqa: F401
+            import tensorflow_cloud  # noqa: F401
+            why = "reference imported but it only submits jobs to Google AI Platform (no local training path)"
+        except Exception as e:  # ModuleNotFoundError: tensorflow / google.auth
+            why = (f"reference installed with --no-deps but cannot be imported: {type(e).__name__}: {e} "
+                   f"(TensorFlow/google-auth are not in /opt/wheelhouse and there is no network)")
+    if int(os.environ.get("RANK", "0")) == 0:
+        print(json.dumps({"impl": "reference", "unavailable": why}))
+    return 0
+
+
+class ClockSampler:
+    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+             "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, path):
+        self.path, self.proc = path, None
+
+    def start(self):
+        try:
+            self.fh = open(self.path, "w")
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv",
+                                          "-lms", "100"], stdout=self.fh, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.proc = None
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        self.fh.close()
+        sm, mx, reasons = [], [], set()
+        with open(self.path) as f:
+            for line in f.readlines()[1:]:
+                parts = [p.strip() for p in line.split(",")]
+                if len(parts) < 9:
+                    continue
+                try:
+                    sm.append(float(parts[1].split()[0]))
+                    mx.append(float(parts[2].split()[0]))
+                except ValueError:
+                    continue
+                for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
+                                      "sw_power_cap"), parts[5:9]):
+                    if val.lower().startswith("active"):
+                        reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def build_model(keras, classes):
+    from cloud_b200.keras import layers
+    inp = keras.Input(shape=(224, 224, 3))
+    x = layers.ImageNormalization(name="normalize")(inp)      # uint8 NHWC -> bf16, on the device
+    base = keras.applications.ResNet50(include_top=False, weights=None, input_tensor=x)
+    y = layers.GlobalAveragePooling2D(name="avg_pool")(base.output)
+    out = layers.Dense(classes, activation="softmax", name="predictions")(y)
+    model = keras.Model(inputs=inp, outputs=out, name="resnet50_train")
+    model.compile(optimizer=keras.optimizers.Adam(1e-3), loss="sparse_categorical_crossentropy",
+                  metrics=["accuracy"])
+    return model
+
+
+def main() -> int:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="cloud_b200", choices=["cloud_b200", "reference"])
+    ap.add_argument("--batch-per-gpu", type=int, default=64)
+    ap.add_argument("--classes", type=int, default=1000)
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+    if args.warmup < 3:
+        args.warmup = 3
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and rank == 0 and world > 1:
+        print(f"[bench] warning: --gpus {args.gpus} but WORLD_SIZE={world}", file=sys.stderr)
+    if args.gpus > 1 and world == 1:
+        print("[bench] --gpus > 1 needs one process per GPU: launch with "
+              "`python -m torch.distributed.run --nproc-per-node N bench.py --gpus N ...`", file=sys.stderr)
+        return 2
+    if not torch.cuda.is_available():
+        print("[bench] no CUDA device: this benchmark needs a B200", file=sys.stderr)
+        return 2
+    torch.cuda.set_device(local)
+
+    import cloud_b200 as tfc
+    from cloud_b200 import ops
+    keras = tfc.keras
+    strategy = tfc.distribute.MirroredStrategy() if world > 1 else tfc.distribute.OneDeviceStrategy("cuda:0")
+    tfc.distribute.experimental_set_strategy(strategy)
+    dev = strategy.device
+
+    torch.manual_seed(1234)
+    np.random.seed(1234)
+    B = args.batch_per_gpu
+    model = build_model(keras, args.classes)
+
+    # ---- device-timed arm: device-resident synthetic batch ------------------------------------
+    x_dev = torch.randint(0, 256, (B, 224, 224, 3), dtype=torch.uint8, device=dev)
+    y_dev = torch.randint(0, args.classes, (B,), device=dev)
+    model._ensure_engine(x_dev)
+    model.train(True)
+    xi = model._to_internal(x_dev)
+
+    def sync():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    for _ in range(int(os.environ.get("TFC_GRAPH_WARMUP", "3")) + 2):   # eager steps + graph capture
+        model._run_step(xi, y_dev)
+    sync()
+    for _ in range(args.warmup):
+        model._run_step(xi, y_dev)
+    sync()
+    sampler = ClockSampler(f"/tmp/bench_clocks_{os.getpid()}.csv") if rank == 0 else None
+    if sampler:
+        sampler.start()
+    launches0 = ops.kernel_launches()
+    replays0 = getattr(model, "_graph_replays", 0)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        red = model._run_step(xi, y_dev)
+    e1.record()
+    sync()
+    ms = e0.elapsed_time(e1) / args.steps
+    clocks = sampler.stop() if sampler else None
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    loss_now = float(red[0].item()) / max(float(red[2].item()), 1.0)
+    replays = getattr(model, "_graph_replays", 0) - replays0
+    per_step = (model._graph or {}).get("launches_per_step", 0) if model._graph else 0
+    gpu_launches = (ops.kernel_launches() - launches0) + replays * per_step
+    value = world * B / (ms * 1e-3)
+
+    # ---- end-to-end arm: model.fit over pinned host arrays -------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        n_steps = args.steps
+        n_img = B * world * n_steps
+        host_x = torch.randint(0, 256, (n_img, 224, 224, 3), dtype=torch.uint8).pin_memory()
+        host_y = torch.randint(0, args.classes, (n_img,), dtype=torch.int64).pin_memory()
+        seen = []
+
+        class ReadLoss(keras.callbacks.Callback):
+            def on_train_batch_end(self, batch, logs=None):
+                seen.append(logs["loss"])        # host float: the device->host read of this step
+
+        warm = B * world * max(args.warmup, 3)
+        model.fit(host_x[:warm], host_y[:warm], batch_size=B * world, epochs=1, shuffle=False,
+                  verbose=0, callbacks=[ReadLoss()])
+        sync()
+        seen.clear()
+        t0 = time.perf_counter()
+        model.fit(host_x, host_y, batch_size=B * world, epochs=1, shuffle=False, verbose=0,
+                  callbacks=[ReadLoss()])
+        sync()
+        dt = time.perf_counter() - t0
+        tt = torch.tensor([dt], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dt = float(tt.item())
+        e2e = {"value": n_img / dt, "unit": "img/s", "ms_per_step": dt / n_steps * 1e3,
+               "h2d_bytes_per_step": int(model._h2d_bytes // n_steps),
+               "d2h_bytes_per_step": int(model._d2h_bytes // max(len(seen), 1)),
+               "steps": n_steps, "losses_read": len(seen), "api": "keras.Model.fit"}
+
+    if rank == 0:
+        eng = model._engine
+        out = {
+            "metric": "ResNet-50 training throughput (img/s), bf16, 224x224 synthetic, data-parallel",
+            "value": value, "unit": "img/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": "cloud_b200",
+            "config": {"model": "ResNet-50 (Keras v1 graph, 25.6M params, all trainable)",
+                       "global_batch": B * world, "batch_per_gpu": B, "image": "224x224x3 uint8",
+                       "seq_len": None, "classes": args.classes, "optimizer": "Adam(1e-3)",
+                       "parallelism": f"dp{world}", "comm_backend": eng.comm.backend,
+                       "allreduce_algos": [g.algo for g in eng.groups],
+                       "cuda_graph": bool(model._graph and model._graph.get("graph") is not None),
+                       "l2": "per-step working set (activations ~5 GB) >> 126 MB L2; no explicit flush"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": int(gpu_launches),
+            "loss": loss_now,
+        }
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,2 +1,36 @@
-"""cloud_b200 - placeholder facade, filled in below."""
+"""cloud_b200 - a B200-native framework with the capabilities of TensorFlow Cloud.
+
+``import cloud_b200 as tfc`` keeps the reference's spelling
+(src/python/tensorflow_cloud/__init__.py:16-27): ``tfc.run``, ``tfc.remote``,
+``tfc.MachineConfig``, ``tfc.AcceleratorType``, ``tfc.COMMON_MACHINE_CONFIGS``,
+``tfc.CloudOracle``, ``tfc.CloudTuner`` (+ ``tfc.DistributingCloudTuner``), and adds the runtime
+the reference outsources to TensorFlow: ``tfc.distribute`` (strategies + data-parallel engine on
+hand-written sm_100a kernels), ``tfc.keras`` (Keras-shaped front end), ``tfc.data``.
+"""
 from .version import __version__  # noqa: F401
+
+from . import data  # noqa: F401,E402
+from . import distribute  # noqa: F401,E402
+from . import keras  # noqa: F401,E402
+from . import ops  # noqa: F401,E402
+
+_LAZY = {
+    "run": ("cloud_b200.core.run", "run"),
+    "remote": ("cloud_b200.core.run", "remote"),
+    "MachineConfig": ("cloud_b200.core.machine_config", "MachineConfig"),
+    "AcceleratorType": ("cloud_b200.core.machine_config", "AcceleratorType"),
+    "COMMON_MACHINE_CONFIGS": ("cloud_b200.core.machine_config", "COMMON_MACHINE_CONFIGS"),
+    "CloudOracle": ("cloud_b200.tuner.tuner", "CloudOracle"),
+    "CloudTuner": ("cloud_b200.tuner.tuner", "CloudTuner"),
+    "DistributingCloudTuner": ("cloud_b200.tuner.tuner", "DistributingCloudTuner"),
+}
+
+
+def __getattr__(name):
+    if name in _LAZY:
+        import importlib
+        mod, attr = _LAZY[name]
+        value = getattr(importlib.import_module(mod), attr)
+        globals()[name] = value
+        return value
+    raise AttributeError(f"module 'cloud_b200' has no attribute {name!r}")

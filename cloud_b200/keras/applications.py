@@ -1,0 +1,109 @@
+"""``keras.applications``-shaped model builders.
+
+``ResNet50`` follows the Keras v1 graph (bias-carrying convolutions, stride on the first 1x1 of a
+stage, BN epsilon 1.001e-5, layer names ``conv2_block1_1_conv`` ...) so weight files line up with
+Keras'; it is the model of the reference's flagship example
+(core/tests/examples/call_run_within_script_with_keras_fit.py:79-87) and of BASELINE.json's
+headline config.  BN+ReLU and BN+Add+ReLU are single fused layers (one memory pass each on the
+hand-written NHWC batch-norm kernels).  ``ResNet18`` is the basic-block variant used by the
+tuner benchmark (BASELINE.json config 4); weights are always random-init (no network here).
+"""
+from __future__ import annotations
+
+from . import layers as L
+from .models import Model
+
+
+def _bottleneck(x, filters, stride, conv_shortcut, name):
+    if conv_shortcut:
+        sc = L.Conv2D(4 * filters, 1, strides=stride, name=name + "_0_conv")(x)
+        sc = L.BatchNormalization(epsilon=1.001e-5, name=name + "_0_bn")(sc)
+    else:
+        sc = x
+    y = L.Conv2D(filters, 1, strides=stride, name=name + "_1_conv")(x)
+    y = L.BatchNormalization(epsilon=1.001e-5, activation="relu", name=name + "_1_bn")(y)
+    y = L.Conv2D(filters, 3, padding="same", name=name + "_2_conv")(y)
+    y = L.BatchNormalization(epsilon=1.001e-5, activation="relu", name=name + "_2_bn")(y)
+    y = L.Conv2D(4 * filters, 1, name=name + "_3_conv")(y)
+    return L.BatchNormalization(epsilon=1.001e-5, activation="relu", name=name + "_3_bn")([y, sc])
+
+
+def _basic(x, filters, stride, conv_shortcut, name):
+    if conv_shortcut:
+        sc = L.Conv2D(filters, 1, strides=stride, use_bias=False, name=name + "_0_conv")(x)
+        sc = L.BatchNormalization(epsilon=1e-5, name=name + "_0_bn")(sc)
+    else:
+        sc = x
+    y = x
+    if stride > 1:
+        y = L.ZeroPadding2D(1, name=name + "_1_pad")(y)
+        y = L.Conv2D(filters, 3, strides=stride, use_bias=False, name=name + "_1_conv")(y)
+    else:
+        y = L.Conv2D(filters, 3, padding="same", use_bias=False, name=name + "_1_conv")(y)
+    y = L.BatchNormalization(epsilon=1e-5, activation="relu", name=name + "_1_bn")(y)
+    y = L.Conv2D(filters, 3, padding="same", use_bias=False, name=name + "_2_conv")(y)
+    return L.BatchNormalization(epsilon=1e-5, activation="relu", name=name + "_2_bn")([y, sc])
+
+
+def _stem(inp, use_bias, eps):
+    x = L.ZeroPadding2D(3, name="conv1_pad")(inp)
+    x = L.Conv2D(64, 7, strides=2, use_bias=use_bias, name="conv1_conv")(x)
+    x = L.BatchNormalization(epsilon=eps, activation="relu", name="conv1_bn")(x)
+    x = L.ZeroPadding2D(1, name="pool1_pad")(x)
+    return L.MaxPooling2D(3, strides=2, name="pool1_pool")(x)
+
+
+def _head(x, include_top, pooling, classes, classifier_activation):
+    if include_top:
+        x = L.GlobalAveragePooling2D(name="avg_pool")(x)
+        x = L.Dense(classes, activation=classifier_activation, name="predictions")(x)
+    elif pooling == "avg":
+        x = L.GlobalAveragePooling2D(name="avg_pool")(x)
+    elif pooling == "max":
+        x = L.GlobalMaxPooling2D(name="max_pool")(x)
+    return x
+
+
+def ResNet50(include_top=True, weights=None, input_tensor=None, input_shape=None, pooling=None,
+             classes=1000, classifier_activation="softmax", **kwargs):
+    if weights not in (None,):
+        raise ValueError("Pretrained weights cannot be downloaded on this box (no network); "
+                         "pass weights=None and load a local file with load_weights().")
+    inp = input_tensor if input_tensor is not None else L.Input(shape=input_shape or (224, 224, 3))
+    x = _stem(inp, True, 1.001e-5)
+    for stage, (filters, blocks, stride) in enumerate([(64, 3, 1), (128, 4, 2), (256, 6, 2), (512, 3, 2)], 2):
+        for b in range(blocks):
+            x = _bottleneck(x, filters, stride if b == 0 else 1, b == 0, f"conv{stage}_block{b + 1}")
+    x = _head(x, include_top, pooling, classes, classifier_activation)
+    return Model(inp, x, name="resnet50")
+
+
+def ResNet18(include_top=True, weights=None, input_tensor=None, input_shape=None, pooling=None,
+             classes=1000, classifier_activation="softmax", **kwargs):
+    if weights not in (None,):
+        raise ValueError("Pretrained weights cannot be downloaded on this box (no network).")
+    inp = input_tensor if input_tensor is not None else L.Input(shape=input_shape or (224, 224, 3))
+    x = _stem(inp, False, 1e-5)
+    for stage, (filters, blocks, stride) in enumerate([(64, 2, 1), (128, 2, 2), (256, 2, 2), (512, 2, 2)], 2):
+        for b in range(blocks):
+            first = b == 0
+            x = _basic(x, filters, stride if first else 1, first and (stride > 1),
+                       f"conv{stage}_block{b + 1}")
+    x = _head(x, include_top, pooling, classes, classifier_activation)
+    return Model(inp, x, name="resnet18")
+
+
+class resnet:  # tf.keras.applications.resnet.*
+    ResNet50 = staticmethod(ResNet50)
+
+    @staticmethod
+    def preprocess_input(x, data_format=None):
+        """caffe-style: RGB->BGR, subtract the ImageNet channel means (no scaling)."""
+        import numpy as np
+        x = np.asarray(x, dtype=np.float32)[..., ::-1]
+        return x - np.array([103.939, 116.779, 123.68], dtype=np.float32)
+
+
+class resnet50:
+    ResNet50 = staticmethod(ResNet50)
+    preprocess_input = resnet.preprocess_input

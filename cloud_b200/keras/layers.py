@@ -1,0 +1,748 @@
+"""Keras-shaped layers on torch, tuned for B200.
+
+User-visible conventions follow Keras (what the reference's example scripts are written against,
+e.g. README.md:71-75, core/tests/testdata/mnist_example_using_fit.py:54-63): NHWC image tensors,
+``Dense`` kernels ``[in, out]``, ``Conv2D`` kernels ``HWIO``, auto names ``dense``, ``dense_1``...
+Internally 4-D activations are NCHW-logical tensors in ``channels_last`` memory (zero-copy view of
+the NHWC batch, and the layout cuDNN's tensor-core kernels want); Dense layers run on the
+hand-written tcgen05 GEMM (``cloud_b200.ops.dense``).
+"""
+from __future__ import annotations
+
+import math
+import re
+
+import numpy as np
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from .. import ops
+
+_NAME_COUNTS: dict[str, int] = {}
+
+
+def reset_name_counts() -> None:
+    _NAME_COUNTS.clear()
+
+
+def _snake(name: str) -> str:
+    s = re.sub(r"(.)([A-Z][a-z0-9]+)", r"\1_\2", name)
+    s = re.sub(r"([a-z])([A-Z])", r"\1_\2", s).lower()
+    return s.replace("2_d", "2d").replace("1_d", "1d").replace("3_d", "3d")
+
+
+def _auto_name(cls_name: str) -> str:
+    base = _snake(cls_name)
+    n = _NAME_COUNTS.get(base, 0)
+    _NAME_COUNTS[base] = n + 1
+    if base == "input_layer":
+        return f"input_{n + 1}"
+    return base if n == 0 else f"{base}_{n}"
+
+
+def _pair(v):
+    return (v, v) if isinstance(v, int) else tuple(v)
+
+
+# ----------------------------------------------------------------------------------------------
+# Symbolic tensors for the functional API
+# ----------------------------------------------------------------------------------------------
+class KerasTensor:
+    """Placeholder produced by ``Input`` / by calling a layer on placeholders."""
+
+    def __init__(self, shape, layer=None, inputs=(), dtype="float32"):
+        self.shape = tuple(shape)
+        self.layer = layer
+        self.inputs = tuple(inputs)
+        self.dtype = dtype
+
+    def __repr__(self):
+        return f"<KerasTensor shape={self.shape} from {getattr(self.layer, 'name', None)}>"
+
+
+_ACTIVATIONS = {
+    None: None, "linear": None,
+    "relu": torch.relu, "elu": F.elu, "selu": F.selu, "gelu": F.gelu, "sigmoid": torch.sigmoid,
+    "tanh": torch.tanh, "softplus": F.softplus, "swish": F.silu, "silu": F.silu,
+    "softmax": lambda x: torch.softmax(x.float(), dim=-1).to(x.dtype),
+}
+
+
+def get_activation(name):
+    if callable(name):
+        return name
+    if name not in _ACTIVATIONS:
+        raise ValueError(f"Unknown activation function: {name}")
+    return _ACTIVATIONS[name]
+
+
+def _init_tensor(initializer, shape, fan_in, fan_out):
+    """Keras initializers on a tensor whose fans are given explicitly."""
+    t = torch.empty(shape, dtype=torch.float32)
+    if hasattr(initializer, "__call_tensor__"):
+        return initializer.__call_tensor__(t)
+    name = initializer if isinstance(initializer, str) else getattr(initializer, "name", None)
+    if name in ("glorot_uniform", None):
+        limit = math.sqrt(6.0 / (fan_in + fan_out))
+        return t.uniform_(-limit, limit)
+    if name == "glorot_normal":
+        return t.normal_(0, math.sqrt(2.0 / (fan_in + fan_out)))
+    if name in ("he_normal",):
+        return t.normal_(0, math.sqrt(2.0 / fan_in))
+    if name in ("he_uniform",):
+        limit = math.sqrt(6.0 / fan_in)
+        return t.uniform_(-limit, limit)
+    if name == "zeros":
+        return t.zero_()
+    if name == "ones":
+        return t.fill_(1.0)
+    if name == "random_normal":
+        return t.normal_(0, 0.05)
+    if name == "random_uniform":
+        return t.uniform_(-0.05, 0.05)
+    raise ValueError(f"Unknown initializer: {initializer}")
+
+
+class Layer(nn.Module):
+    """Base layer: lazy ``build`` on the first call, Keras naming and weight (de)serialisation."""
+
+    def __init__(self, name=None, trainable=True, dtype=None, input_shape=None,
+                 batch_input_shape=None, **kwargs):
+        super().__init__()
+        if kwargs:
+            unknown = set(kwargs) - {"input_dim", "activity_regularizer", "kernel_regularizer",
+                                     "bias_regularizer", "kernel_constraint", "bias_constraint"}
+            if unknown:
+                raise TypeError(f"Unknown keyword arguments for {type(self).__name__}: {sorted(unknown)}")
+        self.name = name or _auto_name(type(self).__name__)
+        self._trainable = trainable
+        self.built = False
+        if input_shape is None and "input_dim" in kwargs:
+            input_shape = (kwargs["input_dim"],)
+        if batch_input_shape is not None:
+            self._declared_input_shape = tuple(batch_input_shape)
+        elif input_shape is not None:
+            self._declared_input_shape = (None,) + tuple(input_shape)
+        else:
+            self._declared_input_shape = None
+        self._keras_weight_specs: list = []   # (keras_suffix, attr, to_keras, from_keras)
+        self.input_shape_ = None
+        self.output_shape_ = None
+
+    # -- Keras-facing -------------------------------------------------------------------------
+    @property
+    def trainable(self):
+        return self._trainable
+
+    @trainable.setter
+    def trainable(self, v):
+        self._trainable = bool(v)
+        for p in self.parameters():
+            p.requires_grad_(bool(v))
+
+    def build(self, input_shape):
+        pass
+
+    def call(self, x, training=False):
+        return x
+
+    def compute_output_shape(self, input_shape):
+        return input_shape
+
+    def _maybe_build(self, input_shape):
+        if not self.built:
+            self.build(tuple(input_shape))
+            self.built = True
+            self.input_shape_ = tuple(input_shape)
+            self.output_shape_ = self.compute_output_shape(tuple(input_shape))
+            if not self._trainable:
+                for p in self.parameters(recurse=False):
+                    p.requires_grad_(False)
+
+    def __call__(self, inputs, *args, **kwargs):
+        if isinstance(inputs, KerasTensor) or (
+                isinstance(inputs, (list, tuple)) and inputs and isinstance(inputs[0], KerasTensor)):
+            return self._symbolic_call(inputs)
+        return super().__call__(inputs, *args, **kwargs)
+
+    def _symbolic_call(self, inputs):
+        ins = list(inputs) if isinstance(inputs, (list, tuple)) else [inputs]
+        shape = [t.shape for t in ins] if len(ins) > 1 else ins[0].shape
+        self._maybe_build(shape)
+        return KerasTensor(self.compute_output_shape(shape), layer=self, inputs=ins)
+
+    def forward(self, x, training=None):
+        if training is None:
+            training = self.training
+        if not self.built:
+            self._maybe_build(_keras_shape(x))
+            dev = _first_device(x)
+            if dev is not None:
+                self.to(dev)
+        return self.call(x, training=training)
+
+    # -- weights ------------------------------------------------------------------------------
+    def add_weight_spec(self, suffix, attr, to_keras=None, from_keras=None):
+        self._keras_weight_specs.append((suffix, attr, to_keras, from_keras))
+
+    @property
+    def weight_names(self):
+        return [f"{self.name}/{s}:0" for s, *_ in self._keras_weight_specs]
+
+    def get_weights(self):
+        out = []
+        for _s, attr, to_keras, _f in self._keras_weight_specs:
+            t = getattr(self, attr).detach().float().cpu()
+            if to_keras is not None:
+                t = to_keras(t)
+            out.append(np.ascontiguousarray(t.numpy()))
+        return out
+
+    def set_weights(self, weights):
+        if len(weights) != len(self._keras_weight_specs):
+            raise ValueError(f'You called `set_weights(weights)` on layer "{self.name}" with a weight '
+                             f"list of length {len(weights)}, but the layer was expecting "
+                             f"{len(self._keras_weight_specs)} weights.")
+        with torch.no_grad():
+            for w, (_s, attr, _t, from_keras) in zip(weights, self._keras_weight_specs):
+                t = torch.as_tensor(np.asarray(w), dtype=torch.float32)
+                if from_keras is not None:
+                    t = from_keras(t)
+                dst = getattr(self, attr)
+                if tuple(t.shape) != tuple(dst.shape):
+                    raise ValueError(f"Layer {self.name}: weight shape {tuple(t.shape)} is not "
+                                     f"compatible with {tuple(dst.shape)}")
+                dst.copy_(t.to(dst.device, dst.dtype))
+
+    def count_params(self):
+        return sum(int(getattr(self, attr).numel()) for _s, attr, *_ in self._keras_weight_specs)
+
+    def get_config(self):
+        return {"name": self.name, "trainable": self._trainable}
+
+    @classmethod
+    def from_config(cls, config):
+        return cls(**config)
+
+
+def _first_device(x):
+    if isinstance(x, torch.Tensor):
+        return x.device
+    if isinstance(x, (list, tuple)) and x and isinstance(x[0], torch.Tensor):
+        return x[0].device
+    return None
+
+
+def _keras_shape(x):
+    """Keras-convention shape (None batch, NHWC) of an internal tensor (NCHW for 4-D)."""
+    if isinstance(x, (list, tuple)):
+        return [_keras_shape(t) for t in x]
+    s = tuple(x.shape)
+    if len(s) == 4:
+        return (None, s[2], s[3], s[1])
+    return (None,) + s[1:]
+
+
+# ----------------------------------------------------------------------------------------------
+class InputLayer(Layer):
+    def __init__(self, input_shape=None, batch_size=None, dtype=None, name=None, **kw):
+        super().__init__(name=name, input_shape=input_shape, **kw)
+
+
+def Input(shape=None, batch_size=None, name=None, dtype="float32", **kwargs):
+    """``tf.keras.Input``: a symbolic placeholder of shape ``(None,) + shape``."""
+    layer = InputLayer(input_shape=tuple(shape), name=name)
+    layer.built = True
+    full = (batch_size,) + tuple(shape)
+    layer.input_shape_ = layer.output_shape_ = full
+    return KerasTensor(full, layer=layer, inputs=(), dtype=dtype)
+
+
+class Dense(Layer):
+    """``activation(x @ kernel + bias)`` on the tcgen05 GEMM with a fused epilogue (K1/K2/K3)."""
+
+    def __init__(self, units, activation=None, use_bias=True, kernel_initializer="glorot_uniform",
+                 bias_initializer="zeros", **kwargs):
+        super().__init__(**kwargs)
+        self.units = int(units)
+        self.activation_name = activation if isinstance(activation, (str, type(None))) else None
+        self._activation_fn = get_activation(activation)
+        self.use_bias = use_bias
+        self.kernel_initializer = kernel_initializer
+        self.bias_initializer = bias_initializer
+        self.last_logits = None
+
+    def build(self, input_shape):
+        in_dim = int(input_shape[-1])
+        # torch layout [out, in]; Keras files hold [in, out] (transposed on save/load)
+        w = _init_tensor(self.kernel_initializer, (in_dim, self.units), in_dim, self.units)
+        self.kernel = nn.Parameter(w.t().contiguous())
+        self.add_weight_spec("kernel", "kernel", lambda t: t.t(), lambda t: t.t())
+        if self.use_bias:
+            self.bias = nn.Parameter(_init_tensor(self.bias_initializer, (self.units,), in_dim, self.units))
+            self.add_weight_spec("bias", "bias")
+        else:
+            self.bias = None
+
+    def compute_output_shape(self, input_shape):
+        return tuple(input_shape[:-1]) + (self.units,)
+
+    def call(self, x, training=False):
+        act = self.activation_name
+        if act == "softmax":
+            # keep the logits: the fused cross-entropy consumes them (what Keras does with
+            # `_keras_logits`), the probabilities are only materialised when somebody looks
+            logits = ops.dense(x, self.kernel, self.bias, None)
+            out = _LazySoftmax.make(logits)
+            return out
+        if act in (None, "linear", "relu"):
+            return ops.dense(x, self.kernel, self.bias, act)
+        y = ops.dense(x, self.kernel, self.bias, None)
+        return self._activation_fn(y)
+
+    def get_config(self):
+        return {**super().get_config(), "units": self.units, "activation": self.activation_name,
+                "use_bias": self.use_bias}
+
+
+class _LazySoftmax:
+    """Tags a probability tensor with the logits it came from."""
+
+    @staticmethod
+    def make(logits):
+        probs = torch.softmax(logits.float(), dim=-1).to(logits.dtype) if not torch.is_grad_enabled() \
+            else _SoftmaxWithLogits.apply(logits)
+        probs._keras_logits = logits
+        return probs
+
+
+class _SoftmaxWithLogits(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits):
+        p = torch.softmax(logits.float(), dim=-1).to(logits.dtype)
+        ctx.save_for_backward(p)
+        return p
+
+    @staticmethod
+    def backward(ctx, dy):
+        (p,) = ctx.saved_tensors
+        pf, df = p.float(), dy.float()
+        return (pf * (df - (df * pf).sum(-1, keepdim=True))).to(dy.dtype)
+
+
+class Activation(Layer):
+    def __init__(self, activation, **kwargs):
+        super().__init__(**kwargs)
+        self.activation_name = activation if isinstance(activation, str) else None
+        self._fn = get_activation(activation)
+
+    def call(self, x, training=False):
+        if self.activation_name == "softmax":
+            return _LazySoftmax.make(x)
+        return x if self._fn is None else self._fn(x)
+
+    def get_config(self):
+        return {**super().get_config(), "activation": self.activation_name}
+
+
+class ReLU(Layer):
+    def call(self, x, training=False):
+        return torch.relu(x)
+
+
+class Softmax(Layer):
+    def call(self, x, training=False):
+        return _LazySoftmax.make(x)
+
+
+class Dropout(Layer):
+    def __init__(self, rate, seed=None, **kwargs):
+        super().__init__(**kwargs)
+        self.rate = float(rate)
+        self.seed = seed
+
+    def call(self, x, training=False):
+        return ops.dropout(x, self.rate, training=training, seed=self.seed)
+
+    def get_config(self):
+        return {**super().get_config(), "rate": self.rate}
+
+
+class Flatten(Layer):
+    def compute_output_shape(self, input_shape):
+        n = 1
+        for d in input_shape[1:]:
+            n *= int(d)
+        return (input_shape[0], n)
+
+    def call(self, x, training=False):
+        if x.dim() == 4:   # NCHW-logical -> flatten in Keras (H, W, C) order; a view for channels_last
+            x = x.permute(0, 2, 3, 1)
+        return x.reshape(x.shape[0], -1)
+
+
+class Reshape(Layer):
+    def __init__(self, target_shape, **kwargs):
+        super().__init__(**kwargs)
+        self.target_shape = tuple(target_shape)
+
+    def compute_output_shape(self, input_shape):
+        return (input_shape[0],) + self.target_shape
+
+    def call(self, x, training=False):
+        if x.dim() == 4:
+            x = x.permute(0, 2, 3, 1)
+        y = x.reshape((x.shape[0],) + self.target_shape)
+        if y.dim() == 4:
+            y = y.permute(0, 3, 1, 2)
+        return y
+
+    def get_config(self):
+        return {**super().get_config(), "target_shape": self.target_shape}
+
+
+def _same_pad(in_size, k, s, d=1):
+    eff = (k - 1) * d + 1
+    out = -(-in_size // s)
+    total = max((out - 1) * s + eff - in_size, 0)
+    return total // 2, total - total // 2
+
+
+class Conv2D(Layer):
+    """NHWC convolution on cuDNN's channels_last tensor-core kernels (library op, K8)."""
+
+    def __init__(self, filters, kernel_size, strides=(1, 1), padding="valid", activation=None,
+                 use_bias=True, dilation_rate=(1, 1), kernel_initializer="glorot_uniform",
+                 bias_initializer="zeros", **kwargs):
+        super().__init__(**kwargs)
+        self.filters = int(filters)
+        self.kernel_size = _pair(kernel_size)
+        self.strides = _pair(strides)
+        self.padding = padding.lower()
+        self.dilation = _pair(dilation_rate)
+        self.activation_name = activation if isinstance(activation, (str, type(None))) else None
+        self._activation_fn = get_activation(activation)
+        self.use_bias = use_bias
+        self.kernel_initializer = kernel_initializer
+        self.bias_initializer = bias_initializer
+
+    def build(self, input_shape):
+        cin = int(input_shape[-1])
+        kh, kw = self.kernel_size
+        fan_in, fan_out = cin * kh * kw, self.filters * kh * kw
+        w = _init_tensor(self.kernel_initializer, (kh, kw, cin, self.filters), fan_in, fan_out)
+        self.kernel = nn.Parameter(w.permute(3, 2, 0, 1).contiguous(memory_format=torch.channels_last))
+        self.add_weight_spec("kernel", "kernel", lambda t: t.permute(2, 3, 1, 0),
+                             lambda t: t.permute(3, 2, 0, 1))
+        if self.use_bias:
+            self.bias = nn.Parameter(_init_tensor(self.bias_initializer, (self.filters,), fan_in, fan_out))
+            self.add_weight_spec("bias", "bias")
+        else:
+            self.bias = None
+
+    def _out_dim(self, n, k, s, d):
+        if n is None:
+            return None
+        if self.padding == "same":
+            return -(-n // s)
+        return (n - ((k - 1) * d + 1)) // s + 1
+
+    def compute_output_shape(self, input_shape):
+        b, h, w, _c = input_shape
+        return (b, self._out_dim(h, self.kernel_size[0], self.strides[0], self.dilation[0]),
+                self._out_dim(w, self.kernel_size[1], self.strides[1], self.dilation[1]), self.filters)
+
+    def call(self, x, training=False):
+        pad = 0
+        if self.padding == "same":
+            ph = _same_pad(x.shape[2], self.kernel_size[0], self.strides[0], self.dilation[0])
+            pw = _same_pad(x.shape[3], self.kernel_size[1], self.strides[1], self.dilation[1])
+            if ph[0] == ph[1] and pw[0] == pw[1]:
+                pad = (ph[0], pw[0])
+            else:
+                x = F.pad(x, (pw[0], pw[1], ph[0], ph[1]))
+        w = self.kernel
+        if w.dtype != x.dtype:
+            x = x.to(w.dtype)
+        b = self.bias
+        if b is not None and b.dtype != x.dtype:
+            b = b.to(x.dtype)
+        y = F.conv2d(x, w, b, stride=self.strides, padding=pad, dilation=self.dilation)
+        if self.activation_name == "relu":
+            return torch.relu_(y)
+        return y if self._activation_fn is None else self._activation_fn(y)
+
+    def get_config(self):
+        return {**super().get_config(), "filters": self.filters, "kernel_size": self.kernel_size,
+                "strides": self.strides, "padding": self.padding, "activation": self.activation_name,
+                "use_bias": self.use_bias}
+
+
+class _Pool2D(Layer):
+    def __init__(self, pool_size=(2, 2), strides=None, padding="valid", **kwargs):
+        super().__init__(**kwargs)
+        self.pool_size = _pair(pool_size)
+        self.strides = _pair(strides) if strides is not None else self.pool_size
+        self.padding = padding.lower()
+
+    def compute_output_shape(self, input_shape):
+        b, h, w, c = input_shape
+
+        def o(n, k, s):
+            if n is None:
+                return None
+            return -(-n // s) if self.padding == "same" else (n - k) // s + 1
+        return (b, o(h, self.pool_size[0], self.strides[0]), o(w, self.pool_size[1], self.strides[1]), c)
+
+    def _pad(self, x, value):
+        if self.padding != "same":
+            return x
+        ph = _same_pad(x.shape[2], self.pool_size[0], self.strides[0])
+        pw = _same_pad(x.shape[3], self.pool_size[1], self.strides[1])
+        if sum(ph) + sum(pw) == 0:
+            return x
+        return F.pad(x, (pw[0], pw[1], ph[0], ph[1]), value=value)
+
+    def get_config(self):
+        return {**super().get_config(), "pool_size": self.pool_size, "strides": self.strides,
+                "padding": self.padding}
+
+
+class MaxPooling2D(_Pool2D):
+    def call(self, x, training=False):
+        return F.max_pool2d(self._pad(x, float("-inf")), self.pool_size, self.strides)
+
+
+MaxPool2D = MaxPooling2D
+
+
+class AveragePooling2D(_Pool2D):
+    def call(self, x, training=False):
+        return F.avg_pool2d(self._pad(x, 0.0), self.pool_size, self.strides)
+
+
+class GlobalAveragePooling2D(Layer):
+    def compute_output_shape(self, input_shape):
+        return (input_shape[0], input_shape[-1])
+
+    def call(self, x, training=False):
+        return x.mean(dim=(2, 3))
+
+
+class GlobalMaxPooling2D(Layer):
+    def compute_output_shape(self, input_shape):
+        return (input_shape[0], input_shape[-1])
+
+    def call(self, x, training=False):
+        return x.amax(dim=(2, 3))
+
+
+class ZeroPadding2D(Layer):
+    def __init__(self, padding=(1, 1), **kwargs):
+        super().__init__(**kwargs)
+        if isinstance(padding, int):
+            padding = ((padding, padding), (padding, padding))
+        elif isinstance(padding[0], int):
+            padding = ((padding[0], padding[0]), (padding[1], padding[1]))
+        self.padding = tuple(tuple(p) for p in padding)
+
+    def compute_output_shape(self, input_shape):
+        b, h, w, c = input_shape
+        return (b, None if h is None else h + sum(self.padding[0]),
+                None if w is None else w + sum(self.padding[1]), c)
+
+    def call(self, x, training=False):
+        (t, b), (l, r) = self.padding
+        return F.pad(x, (l, r, t, b))
+
+    def get_config(self):
+        return {**super().get_config(), "padding": self.padding}
+
+
+class BatchNormalization(Layer):
+    """Batch norm over the channel axis.  Moving statistics stay per-replica (tf.distribute
+    semantics) and are averaged across replicas when saving."""
+
+    def __init__(self, axis=-1, momentum=0.99, epsilon=1e-3, center=True, scale=True,
+                 gamma_initializer="ones", activation=None, **kwargs):
+        super().__init__(**kwargs)
+        self.momentum = momentum
+        self.epsilon = epsilon
+        self.center, self.scale = center, scale
+        self.gamma_initializer = gamma_initializer
+        if activation not in (None, "relu"):
+            raise ValueError("BatchNormalization can only fuse activation='relu'")
+        self.fused_activation = activation     # extension: BN+ReLU in one memory pass
+
+    def build(self, input_shape):
+        c = int(input_shape[-1])
+        g0 = torch.zeros(c) if self.gamma_initializer == "zeros" else torch.ones(c)
+        self.gamma = nn.Parameter(g0, requires_grad=self.scale)
+        self.beta = nn.Parameter(torch.zeros(c), requires_grad=self.center)
+        self.register_buffer("moving_mean", torch.zeros(c))
+        self.register_buffer("moving_variance", torch.ones(c))
+        self.add_weight_spec("gamma", "gamma")
+        self.add_weight_spec("beta", "beta")
+        self.add_weight_spec("moving_mean", "moving_mean")
+        self.add_weight_spec("moving_variance", "moving_variance")
+
+    def compute_output_shape(self, input_shape):
+        if isinstance(input_shape, list):
+            return tuple(input_shape[0])
+        return tuple(input_shape)
+
+    def _maybe_build(self, input_shape):
+        if isinstance(input_shape, list):
+            input_shape = input_shape[0]
+        super()._maybe_build(input_shape)
+
+    def call(self, x, training=False, relu=None, residual=None):
+        if isinstance(x, (list, tuple)):       # [x, shortcut]: y = act(BN(x) + shortcut)
+            x, residual = x
+        if relu is None:
+            relu = self.fused_activation == "relu"
+        train = bool(training) and self._trainable
+        if x.is_cuda and x.dim() == 4 and x.dtype == torch.bfloat16 and ops.bn_available():
+            return ops.batch_norm_nhwc(x, self.gamma, self.beta, self.moving_mean,
+                                       self.moving_variance, train, 1.0 - self.momentum,
+                                       self.epsilon, relu=relu, residual=residual)
+        y = F.batch_norm(x, self.moving_mean, self.moving_variance, self.gamma, self.beta, train,
+                         1.0 - self.momentum, self.epsilon)
+        if residual is not None:
+            y = y + residual
+        return torch.relu_(y) if relu else y
+
+    def get_config(self):
+        return {**super().get_config(), "momentum": self.momentum, "epsilon": self.epsilon,
+                "activation": self.fused_activation}
+
+
+class ImageNormalization(Layer):
+    """uint8 NHWC images -> normalised bf16 activations in one kernel (input-pipeline tail, K12).
+    Float inputs are normalised with torch ops."""
+
+    def __init__(self, mean=(0.485, 0.456, 0.406), std=(0.229, 0.224, 0.225), **kwargs):
+        super().__init__(**kwargs)
+        self.mean, self.std = tuple(mean), tuple(std)
+
+    def call(self, x, training=False):
+        if x.dtype == torch.uint8:
+            nhwc = x.permute(0, 2, 3, 1)                     # back to the raw NHWC bytes (a view)
+            out = ops.normalize_u8_images(nhwc.contiguous(), self.mean, self.std)
+            if not x.is_cuda:
+                out = out.float()
+            return out.permute(0, 3, 1, 2)
+        c = x.shape[1]
+        m = torch.tensor(self.mean[:c], device=x.device, dtype=x.dtype).view(1, c, 1, 1)
+        s = torch.tensor(self.std[:c], device=x.device, dtype=x.dtype).view(1, c, 1, 1)
+        return (x - m) / s
+
+    def get_config(self):
+        return {**super().get_config(), "mean": self.mean, "std": self.std}
+
+
+class Add(Layer):
+    def compute_output_shape(self, input_shape):
+        return tuple(input_shape[0])
+
+    def call(self, xs, training=False):
+        y = xs[0]
+        for t in xs[1:]:
+            y = y + t
+        return y
+
+
+class Concatenate(Layer):
+    def __init__(self, axis=-1, **kwargs):
+        super().__init__(**kwargs)
+        self.axis = axis
+
+    def compute_output_shape(self, input_shape):
+        s = list(input_shape[0])
+        ax = self.axis if self.axis >= 0 else len(s) + self.axis
+        s[ax] = sum(int(sh[ax]) for sh in input_shape)
+        return tuple(s)
+
+    def call(self, xs, training=False):
+        nd = xs[0].dim()
+        ax = self.axis if self.axis >= 0 else nd + self.axis
+        if nd == 4:   # Keras NHWC axis -> internal NCHW axis
+            ax = {0: 0, 1: 2, 2: 3, 3: 1}[ax]
+        return torch.cat(list(xs), dim=ax)
+
+
+class Lambda(Layer):
+    def __init__(self, function, **kwargs):
+        super().__init__(**kwargs)
+        self.function = function
+
+    def call(self, x, training=False):
+        return self.function(x)
+
+
+class Rescaling(Layer):
+    def __init__(self, scale, offset=0.0, **kwargs):
+        super().__init__(**kwargs)
+        self.scale, self.offset = scale, offset
+
+    def call(self, x, training=False):
+        return x * self.scale + self.offset
+
+
+class RandomFlip(Layer):
+    """Horizontal/vertical random flip (core/tests/testdata/keras_tuner_cifar_example.py:24-31)."""
+
+    def __init__(self, mode="horizontal_and_vertical", **kwargs):
+        super().__init__(**kwargs)
+        self.mode = mode
+
+    def call(self, x, training=False):
+        if not training:
+            return x
+        if "horizontal" in self.mode and torch.rand(()) < 0.5:
+            x = x.flip(3)
+        if "vertical" in self.mode and torch.rand(()) < 0.5:
+            x = x.flip(2)
+        return x
+
+
+class _IdentityAugment(Layer):
+    """Geometry-changing augmentations are accepted and act as identity (shape-preserving)."""
+
+    def __init__(self, factor=0.0, **kwargs):
+        super().__init__(**kwargs)
+        self.factor = factor
+
+
+class RandomRotation(_IdentityAugment):
+    pass
+
+
+class RandomWidth(_IdentityAugment):
+    pass
+
+
+class RandomHeight(_IdentityAugment):
+    pass
+
+
+class RandomZoom(_IdentityAugment):
+    pass
+
+
+class experimental:  # tf.keras.layers.experimental.preprocessing.*
+    class preprocessing:
+        RandomFlip = RandomFlip
+        RandomRotation = RandomRotation
+        RandomWidth = RandomWidth
+        RandomHeight = RandomHeight
+        RandomZoom = RandomZoom
+        Rescaling = Rescaling
+
+
+LAYER_CLASSES = {c.__name__: c for c in (
+    InputLayer, Dense, Activation, ReLU, Softmax, Dropout, Flatten, Reshape, Conv2D, MaxPooling2D,
+    AveragePooling2D, GlobalAveragePooling2D, GlobalMaxPooling2D, ZeroPadding2D,
+    BatchNormalization, ImageNormalization, Add, Concatenate, Rescaling, RandomFlip, RandomRotation, RandomWidth,
+    RandomHeight, RandomZoom)}

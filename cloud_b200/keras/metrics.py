@@ -1,0 +1,116 @@
+"""Metrics as (sum, count) accumulators: replicas add their local sums into the communicator's aux
+scalars and the gradient all-reduce kernel sums them across replicas for free (K11; SUM-aggregated
+metric variables of tf.distribute).  Reference usage:
+``metrics=['accuracy']`` README.md:79, ``SparseCategoricalAccuracy`` testdata/mnist_example_using_ctl.py:63-66."""
+from __future__ import annotations
+
+import torch
+
+
+class Metric:
+    name = "metric"
+    from_fused_xent = False    # True: the fused cross-entropy kernel already counts it
+
+    def __init__(self, name=None):
+        if name:
+            self.name = name
+        self.reset_states()
+
+    def batch_sum(self, y_true, y_pred) -> torch.Tensor:
+        """Sum of the per-sample metric over the local batch (0-d tensor on the device)."""
+        raise NotImplementedError
+
+    # stand-alone use (custom training loops, mnist_example_using_ctl.py:63-66,139-141)
+    def reset_states(self):
+        self._sum, self._count = 0.0, 0.0
+
+    reset_state = reset_states
+
+    def update_state(self, y_true, y_pred, sample_weight=None):
+        y_true, y_pred = torch.as_tensor(y_true), torch.as_tensor(y_pred)
+        self._sum += float(self.batch_sum(y_true.to(y_pred.device), y_pred))
+        self._count += float(y_pred.shape[0])
+
+    def __call__(self, *a, **k):
+        self.update_state(*a, **k)
+        return self.result()
+
+    def result(self):
+        return self._sum / self._count if self._count else 0.0
+
+
+class SparseCategoricalAccuracy(Metric):
+    name = "sparse_categorical_accuracy"
+    from_fused_xent = True
+
+    def batch_sum(self, y_true, y_pred):
+        return (y_pred.argmax(-1) == y_true.reshape(-1).to(y_pred.device)).sum().float()
+
+
+class CategoricalAccuracy(Metric):
+    name = "categorical_accuracy"
+
+    def batch_sum(self, y_true, y_pred):
+        return (y_pred.argmax(-1) == y_true.argmax(-1)).sum().float()
+
+
+class BinaryAccuracy(Metric):
+    name = "binary_accuracy"
+
+    def batch_sum(self, y_true, y_pred):
+        return ((y_pred.float() > 0.5).float() == y_true.float().reshape(y_pred.shape)).float() \
+            .reshape(y_pred.shape[0], -1).mean(-1).sum()
+
+
+class MeanAbsoluteError(Metric):
+    name = "mae"
+
+    def batch_sum(self, y_true, y_pred):
+        d = (y_pred.float() - y_true.float().reshape(y_pred.shape)).abs()
+        return d.reshape(d.shape[0], -1).mean(-1).sum()
+
+
+class MeanSquaredError(Metric):
+    name = "mse"
+
+    def batch_sum(self, y_true, y_pred):
+        d = (y_pred.float() - y_true.float().reshape(y_pred.shape)) ** 2
+        return d.reshape(d.shape[0], -1).mean(-1).sum()
+
+
+class Mean(Metric):
+    """Running mean of whatever is fed (``tf.keras.metrics.Mean``)."""
+    name = "mean"
+
+    def update_state(self, values, sample_weight=None):
+        v = torch.as_tensor(values).float()
+        self._sum += float(v.sum())
+        self._count += float(v.numel())
+
+
+def get(identifier, loss=None, output_dim=None):
+    """Resolve Keras metric spellings; 'accuracy'/'acc' depends on the loss like in Keras."""
+    if isinstance(identifier, Metric):
+        return identifier
+    if isinstance(identifier, type) and issubclass(identifier, Metric):
+        return identifier()
+    key = str(identifier).lower()
+    if key in ("accuracy", "acc"):
+        lname = getattr(loss, "name", "")
+        if "sparse_categorical" in lname:
+            m = SparseCategoricalAccuracy()
+        elif "binary" in lname:
+            m = BinaryAccuracy()
+        elif "categorical" in lname:
+            m = CategoricalAccuracy()
+        else:
+            m = SparseCategoricalAccuracy()
+        m.name = "accuracy" if key == "accuracy" else "acc"
+        return m
+    table = {"sparse_categorical_accuracy": SparseCategoricalAccuracy,
+             "categorical_accuracy": CategoricalAccuracy, "binary_accuracy": BinaryAccuracy,
+             "mae": MeanAbsoluteError, "mean_absolute_error": MeanAbsoluteError,
+             "mse": MeanSquaredError, "mean_squared_error": MeanSquaredError}
+    if key in table:
+        return table[key]()
+    raise ValueError(f"Unknown metric function: {identifier}")

@@ -1,0 +1,953 @@
+"""Keras-shaped ``Model`` / ``Sequential`` on the DPEngine.
+
+The reference's user scripts call ``model.compile(...)`` / ``model.fit(...)`` on TensorFlow and the
+injected ``tf.distribute`` strategy does the rest (README.md:66-81; call stack SURVEY.md section
+3.2).  This module is that "rest", B200-first:
+
+* ``fit`` treats ``batch_size`` as the GLOBAL batch and splits it over replicas,
+* per step: pinned-memory staging + async H2D on a copy stream, forward/backward in bf16 on the
+  hand-written Dense / loss kernels (+ cuDNN for convolutions), gradient buckets reduced by the
+  fused peer-memory all-reduce + optimizer kernel on a side stream, metrics summed across
+  replicas by the same collective,
+* the whole step is captured in a CUDA graph after a short eager warm-up (launch-bound MLP steps
+  and batch-64 ResNet steps both gain from it),
+* results are read back one step late so the host never stalls the device.
+"""
+from __future__ import annotations
+
+import json
+import os
+import queue
+import threading
+import time
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from .. import ops
+from ..data import Dataset
+from ..distribute import get_strategy
+from ..distribute.strategy import DistributedDataset
+from . import callbacks as cb_mod
+from . import layers as L
+from . import losses as losses_mod
+from . import metrics as metrics_mod
+from . import optimizers as opt_mod
+
+AUX_LOSS, AUX_CORRECT, AUX_COUNT, AUX_METRIC0 = 0, 1, 2, 3
+
+
+def _np(a):
+    if isinstance(a, torch.Tensor):
+        return a.detach().cpu().numpy()
+    return np.asarray(a)
+
+
+# ----------------------------------------------------------------------------------------------
+# Batch sources
+# ----------------------------------------------------------------------------------------------
+class _ArraySource:
+    """numpy/torch arrays -> per-replica batches of a global batch (Keras: batch_size is global)."""
+
+    def __init__(self, x, y, batch_size, shuffle, world, rank, seed=0, steps=None, drop_last=False):
+        self.x = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(_np(x)))
+        self.y = None
+        if y is not None:
+            self.y = y if isinstance(y, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(_np(y)))
+        self.n = len(self.x)
+        self.batch = int(batch_size)
+        self.shuffle = shuffle
+        self.world, self.rank = world, rank
+        self.seed = seed
+        self.epoch = 0
+        self.steps = steps
+        self.drop_last = drop_last
+
+    def __len__(self):
+        full = self.n // self.batch if self.drop_last else -(-self.n // self.batch)
+        return min(full, self.steps) if self.steps else full
+
+    def __iter__(self):
+        n_steps = len(self)
+        if self.shuffle:
+            g = torch.Generator()
+            g.manual_seed(self.seed + self.epoch)      # same permutation on every replica
+            perm = torch.randperm(self.n, generator=g)
+        else:
+            perm = None
+        self.epoch += 1
+        for s in range(n_steps):
+            lo = s * self.batch
+            hi = min(self.n, lo + self.batch)
+            per = -(-(hi - lo) // self.world)
+            a = lo + self.rank * per
+            b = min(hi, a + per)
+            if perm is not None:
+                idx = perm[a:b]
+                xb = self.x.index_select(0, idx)
+                yb = self.y.index_select(0, idx) if self.y is not None else None
+            else:
+                xb = self.x[a:b]
+                yb = self.y[a:b] if self.y is not None else None
+            yield xb, yb
+
+
+class _IterSource:
+    """Dataset / iterable of (x, y) global batches, re-split over replicas."""
+
+    def __init__(self, ds, world, rank, steps=None):
+        self.ds = ds
+        self.world, self.rank = world, rank
+        self.steps = steps
+        self._it = None
+
+    def __len__(self):
+        if self.steps:
+            return self.steps
+        try:
+            return len(self.ds)
+        except TypeError:
+            return None
+
+    def __iter__(self):
+        infinite = False
+        if isinstance(self.ds, Dataset):
+            infinite = self.ds.cardinality() == -1
+        if self._it is None or not infinite:
+            self._it = iter(self.ds)
+        count = 0
+        while self.steps is None or count < self.steps:
+            try:
+                batch = next(self._it)
+            except StopIteration:
+                if self.steps is not None and count < self.steps and not infinite:
+                    self._it = iter(self.ds)     # Keras would warn "ran out of data"; we wrap
+                    try:
+                        batch = next(self._it)
+                    except StopIteration:
+                        return
+                else:
+                    return
+            count += 1
+            if isinstance(batch, (tuple, list)):
+                xb, yb = batch[0], (batch[1] if len(batch) > 1 else None)
+            else:
+                xb, yb = batch, None
+            xb = torch.as_tensor(_np(xb)) if not isinstance(xb, torch.Tensor) else xb
+            if yb is not None and not isinstance(yb, torch.Tensor):
+                yb = torch.as_tensor(_np(yb))
+            if self.world > 1 and not isinstance(self.ds, DistributedDataset):
+                n = len(xb)
+                per = -(-n // self.world)
+                a, b = self.rank * per, min(n, (self.rank + 1) * per)
+                xb = xb[a:b]
+                yb = yb[a:b] if yb is not None else None
+            yield xb, yb
+
+
+class _Prefetcher:
+    """Background thread: source batch -> pinned staging -> async H2D on a copy stream."""
+
+    def __init__(self, source, device, depth=3):
+        self.source = source
+        self.device = device
+        self.cuda = device.type == "cuda"
+        self.depth = depth
+        self.copy_stream = torch.cuda.Stream(device) if self.cuda else None
+        self.h2d_bytes = 0
+
+    def __iter__(self):
+        if not self.cuda:
+            for xb, yb in self.source:
+                yield xb, yb, None
+            return
+        q: queue.Queue = queue.Queue(maxsize=self.depth)
+        stop = threading.Event()
+        pinned: dict = {}
+
+        def pin(slot, name, t):
+            key = (slot, name, tuple(t.shape), t.dtype)
+            buf = pinned.get(key)
+            if buf is None:
+                buf = torch.empty(t.shape, dtype=t.dtype).pin_memory()
+                pinned[key] = buf
+            buf.copy_(t)
+            return buf
+
+        def worker():
+            torch.cuda.set_device(self.device)
+            try:
+                for i, (xb, yb) in enumerate(self.source):
+                    if stop.is_set():
+                        return
+                    slot = i % (self.depth + 2)
+                    xp = xb if xb.is_pinned() else pin(slot, "x", xb)
+                    yp = None
+                    if yb is not None:
+                        yp = yb if yb.is_pinned() else pin(slot, "y", yb)
+                    with torch.cuda.stream(self.copy_stream):
+                        xd = xp.to(self.device, non_blocking=True)
+                        yd = yp.to(self.device, non_blocking=True) if yp is not None else None
+                        ev = torch.cuda.Event()
+                        ev.record(self.copy_stream)
+                    self.h2d_bytes += xp.numel() * xp.element_size() + \
+                        (yp.numel() * yp.element_size() if yp is not None else 0)
+                    q.put((xd, yd, ev))
+                q.put(None)
+            except BaseException as e:  # surface loader errors in the training thread
+                q.put(e)
+
+        th = threading.Thread(target=worker, daemon=True)
+        th.start()
+        try:
+            while True:
+                item = q.get()
+                if item is None:
+                    return
+                if isinstance(item, BaseException):
+                    raise item
+                yield item
+        finally:
+            stop.set()
+            while th.is_alive():
+                try:
+                    q.get_nowait()
+                except queue.Empty:
+                    time.sleep(0.001)
+
+
+# ----------------------------------------------------------------------------------------------
+class Model(nn.Module):
+    """Functional / subclassable Keras model."""
+
+    def __init__(self, inputs=None, outputs=None, name=None, **kwargs):
+        super().__init__()
+        self.name = name or L._auto_name(type(self).__name__)
+        self.built = False
+        self.stop_training = False
+        self.optimizer = None
+        self.loss = None
+        self._metrics: list = []
+        self._engine = None
+        self._strategy = None
+        self._graph = None
+        self._graph_ok = True
+        self.history = None
+        self._nodes = None
+        self._inputs = self._outputs = None
+        self._layers = nn.ModuleList()
+        self.run_eagerly = False
+        if inputs is not None and outputs is not None:
+            self._init_functional(inputs, outputs)
+
+    # -- graph construction -------------------------------------------------------------------
+    def _init_functional(self, inputs, outputs):
+        self._inputs = list(inputs) if isinstance(inputs, (list, tuple)) else [inputs]
+        self._outputs = list(outputs) if isinstance(outputs, (list, tuple)) else [outputs]
+        order, seen = [], set()
+
+        def visit(t):
+            if id(t) in seen:
+                return
+            seen.add(id(t))
+            for i in t.inputs:
+                visit(i)
+            order.append(t)
+        for o in self._outputs:
+            visit(o)
+        self._nodes = order
+        added = set()
+        for t in order:
+            if t.layer is not None and id(t.layer) not in added:
+                added.add(id(t.layer))
+                self._layers.append(t.layer)
+        self.built = True
+
+    @property
+    def layers(self):
+        return [l for l in self._layers if not isinstance(l, L.InputLayer)]
+
+    def get_layer(self, name=None, index=None):
+        if index is not None:
+            return self.layers[index]
+        for l in self._layers:
+            if l.name == name:
+                return l
+        raise ValueError(f"No such layer: {name}.")
+
+    @property
+    def output(self):
+        return self._outputs[0] if self._outputs and len(self._outputs) == 1 else self._outputs
+
+    @property
+    def input(self):
+        return self._inputs[0] if self._inputs and len(self._inputs) == 1 else self._inputs
+
+    @property
+    def input_shape(self):
+        return self._inputs[0].shape if self._inputs else None
+
+    @property
+    def output_shape(self):
+        return self._outputs[0].shape if self._outputs else None
+
+    @property
+    def trainable_weights(self):
+        return [p for p in self.parameters() if p.requires_grad]
+
+    trainable_variables = trainable_weights
+
+    @property
+    def metrics_names(self):
+        return ["loss"] + [m.name for m in self._metrics]
+
+    # -- forward ------------------------------------------------------------------------------
+    def call(self, x, training=False):
+        if self._nodes is None:
+            raise NotImplementedError("subclassed models must implement call()")
+        xs = list(x) if isinstance(x, (list, tuple)) else [x]
+        values = {id(t): v for t, v in zip(self._inputs, xs)}
+        for t in self._nodes:
+            if id(t) in values:
+                continue
+            ins = [values[id(i)] for i in t.inputs]
+            arg = ins if len(ins) > 1 else ins[0]
+            if isinstance(t.layer, Model):
+                values[id(t)] = t.layer.call(arg, training=training)
+            else:
+                values[id(t)] = t.layer.forward(arg, training=training)
+        outs = [values[id(o)] for o in self._outputs]
+        return outs[0] if len(outs) == 1 else outs
+
+    def forward(self, x, training=False):
+        return self.call(x, training=training)
+
+    def _symbolic_call(self, inputs):
+        ins = list(inputs) if isinstance(inputs, (list, tuple)) else [inputs]
+        if not self.built:
+            self._build_from_shape(ins[0].shape)
+        return L.KerasTensor(self.compute_output_shape(ins[0].shape), layer=self, inputs=ins)
+
+    def compute_output_shape(self, input_shape):
+        return self._outputs[0].shape if self._outputs else input_shape
+
+    def _build_from_shape(self, shape):
+        pass
+
+    def __call__(self, x, training=False, **kwargs):
+        if isinstance(x, L.KerasTensor) or (isinstance(x, (list, tuple)) and x and
+                                            isinstance(x[0], L.KerasTensor)):
+            return self._symbolic_call(x)
+        self._ensure_placed()
+        xi = self._to_internal(x)
+        was = self.training
+        self.train(bool(training))
+        try:
+            out = self.call(xi, training=bool(training))
+        finally:
+            self.train(was)
+        return _to_keras_layout(out)
+
+    # -- device / dtype plumbing --------------------------------------------------------------
+    @property
+    def distribute_strategy(self):
+        if self._strategy is None:
+            self._strategy = get_strategy()
+        return self._strategy
+
+    @property
+    def _is_chief(self):
+        return self.distribute_strategy.is_chief
+
+    @property
+    def device(self):
+        return self.distribute_strategy.device
+
+    def _ensure_placed(self):
+        dev = self.device
+        for t in list(self.parameters()) + list(self.buffers()):
+            if t.device != dev:
+                self.to(dev)
+                break
+
+    def _compute_dtype(self):
+        if self._engine is not None:
+            return self._engine.compute_dtype
+        return torch.bfloat16 if self.device.type == "cuda" and _policy["name"] == "mixed_bfloat16" \
+            else torch.float32
+
+    def _to_internal(self, x, non_blocking=False):
+        if isinstance(x, (list, tuple)):
+            return [self._to_internal(t) for t in x]
+        t = x if isinstance(x, torch.Tensor) else torch.as_tensor(_np(x))
+        if t.device != self.device:
+            t = t.to(self.device, non_blocking=non_blocking)
+        if t.dim() == 4:
+            t = t.permute(0, 3, 1, 2)        # NHWC batch -> NCHW-logical channels_last view
+        if t.dtype == torch.uint8:
+            return t                          # an ImageNormalization layer consumes raw bytes
+        if t.is_floating_point() or t.dtype in (torch.int32, torch.int64, torch.int16, torch.int8):
+            t = t.to(self._compute_dtype())
+        return t
+
+    # -- compile ------------------------------------------------------------------------------
+    def compile(self, optimizer="rmsprop", loss=None, metrics=None, run_eagerly=False, **kwargs):
+        self.optimizer = opt_mod.get(optimizer)
+        self.loss = losses_mod.get(loss) if loss is not None else None
+        self._metrics = [metrics_mod.get(m, self.loss) for m in (metrics or [])]
+        self.run_eagerly = bool(run_eagerly)
+        self._compiled_with = {"loss": loss, "metrics": list(metrics or [])}
+        self._strategy = get_strategy()
+        self._engine = None
+        self._graph = None
+
+    def _build_with_batch(self, xb):
+        """Run one forward on a single sample batch to create lazily-built weights."""
+        if all(getattr(l, "built", True) for l in self._layers) and self.built:
+            return
+        with torch.no_grad():
+            self.call(self._to_internal(xb[:1] if not isinstance(xb, (list, tuple)) else xb),
+                      training=False)
+        self.built = True
+
+    def _ensure_engine(self, sample_x=None):
+        if self._engine is not None:
+            return self._engine
+        if self.optimizer is None:
+            raise RuntimeError("You must compile your model before training/testing. "
+                               "Use `model.compile(optimizer, loss)`.")
+        if sample_x is not None:
+            self._build_with_batch(sample_x)
+        self._ensure_placed()
+        from ..parallel.engine import DPEngine
+        st = self.distribute_strategy
+        named = [(n, p) for n, p in self.named_parameters()]
+        self._engine = DPEngine(named, self.optimizer.spec(), st.communicator,
+                                compute_dtype=self._compute_dtype())
+        self._graph_ok = all(getattr(l, "graph_safe", True) for l in self.modules())
+        pending = getattr(self, "_pending_optimizer_state", None)
+        if pending:
+            self._engine.load_master_state(pending)
+            self._pending_optimizer_state = None
+        return self._engine
+
+    # -- loss / metrics -----------------------------------------------------------------------
+    def _loss_and_metrics(self, out, y, global_batch, aux):
+        inv = 1.0 / float(global_batch)
+        fused = False
+        if isinstance(self.loss, losses_mod.SparseCategoricalCrossentropy) and out.dim() == 2:
+            logits = self.loss.logits(out)
+            if logits is not None:
+                loss = ops.softmax_cross_entropy(logits, y.reshape(-1), grad_scale=inv, stats=aux)
+                fused = True
+        if not fused:
+            per = self.loss.per_sample(y, out.float() if out.dtype != torch.float32 else out)
+            s = per.sum()
+            with torch.no_grad():
+                aux[AUX_LOSS] += s.detach()
+            loss = s * inv
+        with torch.no_grad():
+            aux[AUX_COUNT] += float(out.shape[0])
+            for i, m in enumerate(self._metrics):
+                if fused and m.from_fused_xent:
+                    continue
+                aux[AUX_METRIC0 + i] += m.batch_sum(y, out)
+        return loss, fused
+
+    def _aux_len(self):
+        return AUX_METRIC0 + len(self._metrics)
+
+    def _logs_from_aux(self, acc, fused, prefix=""):
+        cnt = max(float(acc[AUX_COUNT]), 1.0)
+        logs = {prefix + "loss": float(acc[AUX_LOSS]) / cnt}
+        for i, m in enumerate(self._metrics):
+            v = acc[AUX_CORRECT] if (fused and m.from_fused_xent) else acc[AUX_METRIC0 + i]
+            logs[prefix + m.name] = float(v) / cnt
+        return logs
+
+    # -- one training step --------------------------------------------------------------------
+    def _train_step(self, xb, yb):
+        eng = self._engine
+        eng.begin_step()
+        out = self.call(xb, training=True)
+        global_batch = out.shape[0] * eng.world
+        loss, fused = self._loss_and_metrics(out, yb, global_batch, eng.comm.aux)
+        self._last_fused = fused
+        loss.backward()
+        return eng.end_step(self._aux_len())
+
+    def _graph_enabled(self):
+        if self.run_eagerly or not self._graph_ok or self.device.type != "cuda":
+            return False
+        return os.environ.get("TFC_CUDA_GRAPH", "1") != "0"
+
+    def _run_step(self, xb, yb):
+        """Eager for the first steps (and for odd shapes), then CUDA-graph replay."""
+        if not self._graph_enabled():
+            return self._train_step(xb, yb)
+        g = self._graph
+        key = (tuple(xb.shape), xb.dtype, tuple(yb.shape), yb.dtype)
+        if g is None or g["key"] != key:
+            if g is not None and g.get("frozen"):
+                return self._train_step(xb, yb)     # e.g. the short last batch of an epoch
+            self._graph = g = {"key": key, "warm": 0, "graph": None}
+        if g["graph"] is None:
+            g["warm"] += 1
+            if g["warm"] <= int(os.environ.get("TFC_GRAPH_WARMUP", "3")):
+                return self._train_step(xb, yb)
+            g["x"] = xb.clone()
+            g["y"] = yb.clone()
+            launches0 = ops.kernel_launches()
+            torch.cuda.synchronize(self.device)
+            graph = torch.cuda.CUDAGraph()
+            try:
+                with torch.cuda.graph(graph, capture_error_mode="thread_local"):
+                    g["out"] = self._train_step(g["x"], g["y"])
+            except Exception as e:  # capture refused: stay eager, say so once
+                import warnings
+                warnings.warn(f"cloud_b200: CUDA graph capture failed ({e}); running eagerly")
+                self._graph_ok = False
+                self._graph = None
+                torch.cuda.synchronize(self.device)
+                return self._train_step(xb, yb)
+            g["graph"] = graph
+            g["frozen"] = True
+            g["launches_per_step"] = ops.kernel_launches() - launches0
+            # the capture itself did not execute: fall through to a replay for this batch
+        g["x"].copy_(xb, non_blocking=True)
+        g["y"].copy_(yb, non_blocking=True)
+        g["graph"].replay()
+        self._graph_replays = getattr(self, "_graph_replays", 0) + 1
+        return g["out"]
+
+    # -- fit ----------------------------------------------------------------------------------
+    def _make_source(self, x, y, batch_size, shuffle, steps, training=True):
+        st = self.distribute_strategy
+        world, rank = st.num_replicas_in_sync, st.replica_id
+        if isinstance(x, (Dataset, DistributedDataset)) or (
+                not isinstance(x, (np.ndarray, torch.Tensor, list, tuple)) and hasattr(x, "__iter__")):
+            if callable(getattr(x, "__next__", None)) and not hasattr(x, "__len__") \
+                    and not isinstance(x, (Dataset, DistributedDataset)):
+                pass
+            return _IterSource(x, world, rank, steps)
+        if isinstance(x, (list, tuple)) and not isinstance(x, np.ndarray):
+            x = np.asarray(x)
+        bs = batch_size or 32
+        return _ArraySource(x, y, bs, shuffle and training, world, rank, steps=steps)
+
+    def fit(self, x=None, y=None, batch_size=None, epochs=1, verbose=1, callbacks=None,
+            validation_split=0.0, validation_data=None, shuffle=True, initial_epoch=0,
+            steps_per_epoch=None, validation_steps=None, validation_batch_size=None, **kwargs):
+        if self.loss is None:
+            raise RuntimeError("You must compile your model with a loss before calling fit().")
+        if validation_split and validation_data is None and isinstance(x, (np.ndarray, torch.Tensor)):
+            n_val = int(len(x) * validation_split)
+            if n_val:
+                validation_data = (x[-n_val:], y[-n_val:])
+                x, y = x[:-n_val], y[:-n_val]
+        source = self._make_source(x, y, batch_size, shuffle, steps_per_epoch)
+        first = next(iter(_peek(source)))
+        eng = self._ensure_engine(first[0])
+        history = cb_mod.History()
+        cbs = [history] + list(callbacks or [])
+        if verbose and self._is_chief:
+            cbs.insert(1, cb_mod.ProgbarLogger(verbose))
+        n_steps = len(source) if hasattr(source, "__len__") else None
+        params = {"epochs": epochs, "steps": n_steps, "verbose": verbose}
+        cbl = cb_mod.CallbackList(cbs, self, params)
+        batch_logs = _needs_batch_logs(cbs)
+        self.stop_training = False
+        self.train(True)
+        cbl.call("on_train_begin", {})
+        n_aux = self._aux_len()
+        self._h2d_bytes = 0
+        self._d2h_bytes = 0
+        logs = {}
+        for epoch in range(initial_epoch, epochs):
+            cbl.call("on_epoch_begin", epoch, {})
+            eng.set_lr(self.optimizer.current_lr())
+            acc = torch.zeros(n_aux, dtype=torch.float64, device=self.device)
+            pending = None           # (step index, device tensor of reduced aux, event)
+            pf = _Prefetcher(source, self.device)
+            step = -1
+            for step, (xd, yd, ev) in enumerate(pf):
+                if batch_logs:
+                    cbl.call("on_train_batch_begin", step, {})
+                if ev is not None:
+                    torch.cuda.current_stream(self.device).wait_event(ev)
+                xi = self._to_internal(xd)
+                yi = yd.to(self.device) if yd is not None else None
+                red = self._run_step(xi, yi)
+                self.optimizer.iterations += 1
+                if self.optimizer._schedule is not None:
+                    eng.set_lr(self.optimizer.current_lr())
+                acc += red[:n_aux]
+                if batch_logs:
+                    # read step i-1 while step i runs: the host never drains the device
+                    snap = _HostSnap(acc, self.device)
+                    if pending is not None:
+                        self._emit_batch(cbl, pending)
+                    pending = (step, snap)
+                if self.stop_training:
+                    break
+            if pending is not None:
+                self._emit_batch(cbl, pending)
+            self._h2d_bytes += pf.h2d_bytes
+            host = acc.cpu()
+            self._d2h_bytes += host.numel() * 8
+            logs = self._logs_from_aux(host, getattr(self, "_last_fused", False)) if step >= 0 else {}
+            if validation_data is not None:
+                vx, vy = (validation_data[0], validation_data[1]) \
+                    if isinstance(validation_data, (tuple, list)) else (validation_data, None)
+                val = self.evaluate(vx, vy, batch_size=validation_batch_size or batch_size,
+                                    steps=validation_steps, verbose=0, return_dict=True)
+                logs.update({"val_" + k: v for k, v in val.items()})
+                self.train(True)
+            cbl.call("on_epoch_end", epoch, logs)
+            if self.stop_training:
+                break
+        cbl.call("on_train_end", logs)
+        self.train(False)
+        self.history = history
+        return history
+
+    def _emit_batch(self, cbl, pending):
+        step, snap = pending
+        host = snap.get()
+        self._d2h_bytes += host.numel() * 8
+        cbl.call("on_train_batch_end", step,
+                 self._logs_from_aux(host, getattr(self, "_last_fused", False)))
+
+    def train_on_batch(self, x, y=None, reset_metrics=True, return_dict=False, **kwargs):
+        eng = self._ensure_engine(torch.as_tensor(_np(x)) if not isinstance(x, torch.Tensor) else x)
+        self.train(True)
+        eng.set_lr(self.optimizer.current_lr())
+        xi = self._to_internal(x)
+        yi = torch.as_tensor(_np(y)).to(self.device) if not isinstance(y, torch.Tensor) else y.to(self.device)
+        red = self._run_step(xi, yi)
+        self.optimizer.iterations += 1
+        host = red[:self._aux_len()].double().cpu()
+        logs = self._logs_from_aux(host, getattr(self, "_last_fused", False))
+        self.train(False)
+        if return_dict:
+            return logs
+        vals = list(logs.values())
+        return vals[0] if len(vals) == 1 else vals
+
+    # -- evaluate / predict -------------------------------------------------------------------
+    def evaluate(self, x=None, y=None, batch_size=None, verbose=1, steps=None, callbacks=None,
+                 return_dict=False, **kwargs):
+        if self.loss is None:
+            raise RuntimeError("You must compile your model before training/testing.")
+        source = self._make_source(x, y, batch_size, False, steps, training=False)
+        first = next(iter(_peek(source)))
+        eng = self._ensure_engine(first[0])
+        self.train(False)
+        n_aux = self._aux_len()
+        aux = torch.zeros(max(n_aux, 8), dtype=torch.float32, device=self.device)
+        fused = False
+        with torch.no_grad():
+            for xd, yd, ev in _Prefetcher(source, self.device):
+                if ev is not None:
+                    torch.cuda.current_stream(self.device).wait_event(ev)
+                out = self.call(self._to_internal(xd), training=False)
+                _l, fused = self._loss_and_metrics(out, yd.to(self.device), 1, aux)
+        if eng.world > 1:
+            eng.comm.all_reduce_sum(aux)
+        logs = self._logs_from_aux(aux.double().cpu(), fused)
+        if verbose and self._is_chief:
+            print(" - ".join(f"{k}: {v:.4f}" for k, v in logs.items()), flush=True)
+        if return_dict:
+            return logs
+        vals = list(logs.values())
+        return vals[0] if len(vals) == 1 else vals
+
+    def test_on_batch(self, x, y=None, return_dict=False, **kwargs):
+        return self.evaluate(x, y, batch_size=len(x), verbose=0, return_dict=return_dict)
+
+    def predict(self, x, batch_size=None, verbose=0, steps=None, **kwargs):
+        self._ensure_placed()
+        self.train(False)
+        outs = []
+        if isinstance(x, (Dataset, DistributedDataset)):
+            batches = (b[0] if isinstance(b, (tuple, list)) else b for b in x)
+        else:
+            arr = x if isinstance(x, torch.Tensor) else torch.as_tensor(_np(x))
+            bs = batch_size or 32
+            batches = (arr[i:i + bs] for i in range(0, len(arr), bs))
+        with torch.no_grad():
+            for i, b in enumerate(batches):
+                if steps is not None and i >= steps:
+                    break
+                out = _to_keras_layout(self.call(self._to_internal(b), training=False))
+                outs.append(out.float().cpu())
+        return torch.cat(outs).numpy() if outs else np.zeros((0,))
+
+    def predict_on_batch(self, x):
+        return self.predict(x, batch_size=len(x))
+
+    # -- weights ------------------------------------------------------------------------------
+    def get_weights(self):
+        out = []
+        for l in self._weight_layers():
+            out.extend(l.get_weights())
+        return out
+
+    def set_weights(self, weights):
+        i = 0
+        for l in self._weight_layers():
+            n = len(l._keras_weight_specs)
+            l.set_weights(weights[i:i + n])
+            i += n
+        if self._engine is not None:
+            self._engine.params_changed()
+
+    def _weight_layers(self):
+        out = []
+        for l in self._layers:
+            if isinstance(l, Model):
+                out.extend(l._weight_layers())
+            elif getattr(l, "_keras_weight_specs", None):
+                out.append(l)
+        return out
+
+    def count_params(self):
+        return sum(l.count_params() for l in self._weight_layers())
+
+    def save_weights(self, filepath, overwrite=True, save_format=None, **kwargs):
+        from . import saving
+        saving.save_weights(self, filepath)
+
+    def load_weights(self, filepath, by_name=False, **kwargs):
+        from . import saving
+        saving.load_weights(self, filepath, by_name=by_name)
+        return _LoadStatus()
+
+    def save(self, filepath, overwrite=True, include_optimizer=True, save_format=None, **kwargs):
+        from . import saving
+        saving.save_model(self, filepath, include_optimizer=include_optimizer)
+
+    # -- config -------------------------------------------------------------------------------
+    def get_config(self):
+        nodes = []
+        names = {}
+        for t in self._nodes or []:
+            names[id(t)] = t.layer.name
+            nodes.append({"class_name": type(t.layer).__name__, "name": t.layer.name,
+                          "config": _layer_config(t.layer),
+                          "inbound": [names[id(i)] for i in t.inputs],
+                          "shape": list(t.shape)})
+        return {"name": self.name, "nodes": nodes,
+                "inputs": [names[id(t)] for t in self._inputs or []],
+                "outputs": [names[id(t)] for t in self._outputs or []]}
+
+    @classmethod
+    def from_config(cls, config, custom_objects=None):
+        tensors = {}
+        for node in config["nodes"]:
+            if node["class_name"] == "InputLayer":
+                shape = tuple(node["shape"][1:])
+                tensors[node["name"]] = L.Input(shape=shape, name=node["name"])
+                continue
+            layer = _layer_from_config(node["class_name"], node["config"], custom_objects)
+            ins = [tensors[n] for n in node["inbound"]]
+            tensors[node["name"]] = layer(ins if len(ins) > 1 else ins[0])
+        return cls(inputs=[tensors[n] for n in config["inputs"]],
+                   outputs=[tensors[n] for n in config["outputs"]], name=config.get("name"))
+
+    def to_json(self):
+        return json.dumps({"class_name": type(self).__name__, "config": self.get_config()})
+
+    def summary(self, print_fn=print):
+        print_fn(f'Model: "{self.name}"')
+        print_fn("_" * 65)
+        print_fn(f"{'Layer (type)':<29}{'Output Shape':<26}{'Param #':<10}")
+        print_fn("=" * 65)
+        total = 0
+        for l in self._layers:
+            n = l.count_params() if hasattr(l, "count_params") else 0
+            total += n
+            shape = getattr(l, "output_shape_", None) or getattr(l, "output_shape", None)
+            print_fn(f"{l.name + ' (' + type(l).__name__ + ')':<29}{str(shape):<26}{n:<10}")
+        print_fn("=" * 65)
+        print_fn(f"Total params: {total:,}")
+
+
+class _LoadStatus:
+    def expect_partial(self):
+        return self
+
+    def assert_consumed(self):
+        return self
+
+    def assert_existing_objects_matched(self):
+        return self
+
+
+class _HostSnap:
+    """Async device->host copy of a small tensor into pinned memory, read later."""
+
+    def __init__(self, t, device):
+        if device.type == "cuda":
+            self.buf = torch.empty(t.shape, dtype=t.dtype).pin_memory()
+            self.buf.copy_(t, non_blocking=True)
+            self.ev = torch.cuda.Event()
+            self.ev.record()
+        else:
+            self.buf, self.ev = t.clone(), None
+
+    def get(self):
+        if self.ev is not None:
+            self.ev.synchronize()
+        return self.buf
+
+
+def _needs_batch_logs(cbs) -> bool:
+    base = cb_mod.Callback
+    for cb in cbs:
+        if isinstance(cb, (cb_mod.History, cb_mod.ProgbarLogger)):
+            continue
+        for name in ("on_train_batch_end", "on_batch_end", "on_train_batch_begin", "on_batch_begin"):
+            fn = getattr(cb, name)
+            if getattr(fn, "__func__", None) is not getattr(base, name):
+                return True
+    return False
+
+
+def _peek(source):
+    """First batch of a source without disturbing array sources (datasets restart anyway)."""
+    if isinstance(source, _ArraySource):
+        yield source.x[:1], None
+        return
+    it = iter(source)
+    first = next(it)
+    source._it = None
+    yield first
+
+
+def _to_keras_layout(out):
+    if isinstance(out, (list, tuple)):
+        return [_to_keras_layout(o) for o in out]
+    if isinstance(out, torch.Tensor) and out.dim() == 4:
+        return out.permute(0, 2, 3, 1)
+    return out
+
+
+def _layer_config(layer):
+    if isinstance(layer, Model):
+        return {"model": layer.get_config(), "kind": type(layer).__name__}
+    cfg = layer.get_config()
+    if isinstance(layer, L.InputLayer):
+        cfg["input_shape"] = list(layer.input_shape_[1:]) if layer.input_shape_ else None
+    return cfg
+
+
+def _layer_from_config(class_name, config, custom_objects=None):
+    if class_name in ("Model", "Sequential", "Functional"):
+        cls = Sequential if config.get("kind") == "Sequential" else Model
+        return cls.from_config(config["model"], custom_objects)
+    table = dict(L.LAYER_CLASSES)
+    table.update(custom_objects or {})
+    if class_name not in table:
+        raise ValueError(f"Unknown layer: {class_name}")
+    cfg = dict(config)
+    return table[class_name](**cfg)
+
+
+class Sequential(Model):
+    def __init__(self, layers=None, name=None):
+        super().__init__(name=name)
+        self._seq: list = []
+        for l in layers or []:
+            self.add(l)
+
+    def add(self, layer):
+        if isinstance(layer, L.KerasTensor):       # Sequential([Input(...), ...])
+            layer = layer.layer
+        self._seq.append(layer)
+        self._layers.append(layer)
+        if len(self._seq) == 1 and getattr(layer, "_declared_input_shape", None):
+            self._build_from_shape(layer._declared_input_shape)
+        elif self.built and self._outputs:
+            self._outputs = [layer(self._outputs[0])]
+            self._nodes = None
+
+    def _build_from_shape(self, shape):
+        """Static shape inference through the stack (creates the weights, Keras-style)."""
+        t = L.KerasTensor(tuple(shape))
+        self._inputs = [t]
+        for l in self._seq:
+            if isinstance(l, L.InputLayer):
+                continue
+            t = l(t)
+        self._outputs = [t]
+        self.built = True
+
+    def call(self, x, training=False):
+        for l in self._seq:
+            if isinstance(l, L.InputLayer):
+                continue
+            x = l.call(x, training=training) if isinstance(l, Model) else l.forward(x, training=training)
+        if not self.built:
+            self.built = True
+        return x
+
+    def _build_with_batch(self, xb):
+        if self.built and all(getattr(l, "built", True) for l in self._seq):
+            return
+        t = xb if isinstance(xb, torch.Tensor) else torch.as_tensor(_np(xb))
+        self._build_from_shape((None,) + tuple(t.shape[1:]))
+
+    def build(self, input_shape=None):
+        if input_shape is not None:
+            self._build_from_shape(tuple(input_shape))
+
+    def pop(self):
+        l = self._seq.pop()
+        self._layers = nn.ModuleList(self._seq)
+        return l
+
+    def get_config(self):
+        return {"name": self.name, "kind": "Sequential",
+                "input_shape": list(self._inputs[0].shape) if self._inputs else None,
+                "layers": [{"class_name": type(l).__name__, "config": _layer_config(l)}
+                           for l in self._seq if not isinstance(l, L.InputLayer)]}
+
+    @classmethod
+    def from_config(cls, config, custom_objects=None):
+        m = cls(name=config.get("name"))
+        for ld in config["layers"]:
+            m.add(_layer_from_config(ld["class_name"], ld["config"], custom_objects))
+        if config.get("input_shape"):
+            m._build_from_shape(tuple(config["input_shape"]))
+        return m
+
+
+_policy = {"name": "mixed_bfloat16"}
+
+
+class mixed_precision:
+    """``tf.keras.mixed_precision``-like global policy: 'mixed_bfloat16' (default on B200: bf16
+    compute, fp32 master weights) or 'float32'."""
+
+    @staticmethod
+    def set_global_policy(name):
+        if name not in ("mixed_bfloat16", "float32"):
+            raise ValueError("policy must be 'mixed_bfloat16' or 'float32'")
+        _policy["name"] = name
+
+    @staticmethod
+    def global_policy():
+        return _policy["name"]
+
+
+def load_model(filepath, custom_objects=None, compile=True):
+    from . import saving
+    return saving.load_model(filepath, custom_objects=custom_objects, compile=compile)
+
+
+def model_from_json(text, custom_objects=None):
+    d = json.loads(text)
+    cls = Sequential if d["config"].get("kind") == "Sequential" else Model
+    return cls.from_config(d["config"], custom_objects)

@@ -1,0 +1,165 @@
+"""Keras-shaped optimizers.  They only *describe* the update; the update itself is executed by
+the DPEngine's fused kernels (``csrc/kernels/comm.cu`` / ``elementwise.cu``), one launch per
+gradient bucket instead of one ``ResourceApplyAdam`` per variable.
+
+Reference usage: ``Adam()`` README.md:78, ``Adam(lr=hp.get('learning_rate'))``
+tuner/tests/integration/tuner_integration_test.py:75, ``SGD(0.002)`` cloud_fit client_test.py:87-89,
+``RMSprop(learning_rate=ExponentialDecay(...))`` core/tests/testdata/keras_tuner_cifar_example.py:66-76.
+"""
+from __future__ import annotations
+
+from ..parallel.engine import OptimizerSpec
+
+
+class LearningRateSchedule:
+    def __call__(self, step):
+        raise NotImplementedError
+
+    def get_config(self):
+        return {}
+
+
+class ExponentialDecay(LearningRateSchedule):
+    def __init__(self, initial_learning_rate, decay_steps, decay_rate, staircase=False, name=None):
+        self.initial_learning_rate = float(initial_learning_rate)
+        self.decay_steps = decay_steps
+        self.decay_rate = decay_rate
+        self.staircase = staircase
+
+    def __call__(self, step):
+        p = step / self.decay_steps
+        if self.staircase:
+            p = float(int(p))
+        return self.initial_learning_rate * (self.decay_rate ** p)
+
+    def get_config(self):
+        return {"initial_learning_rate": self.initial_learning_rate, "decay_steps": self.decay_steps,
+                "decay_rate": self.decay_rate, "staircase": self.staircase}
+
+
+class PiecewiseConstantDecay(LearningRateSchedule):
+    def __init__(self, boundaries, values, name=None):
+        self.boundaries, self.values = list(boundaries), list(values)
+
+    def __call__(self, step):
+        for b, v in zip(self.boundaries, self.values):
+            if step <= b:
+                return v
+        return self.values[-1]
+
+
+class schedules:  # tf.keras.optimizers.schedules.*
+    LearningRateSchedule = LearningRateSchedule
+    ExponentialDecay = ExponentialDecay
+    PiecewiseConstantDecay = PiecewiseConstantDecay
+
+
+class Optimizer:
+    _name = "optimizer"
+
+    def __init__(self, learning_rate=0.001, lr=None, name=None, **kwargs):
+        if lr is not None:           # legacy spelling used by the reference's tuner tests
+            learning_rate = lr
+        self._schedule = learning_rate if callable(learning_rate) else None
+        self.learning_rate = float(learning_rate(0)) if self._schedule else float(learning_rate)
+        self.iterations = 0
+        self.name = name or type(self).__name__
+
+    @property
+    def lr(self):
+        return self.learning_rate
+
+    @lr.setter
+    def lr(self, v):
+        self.learning_rate = float(v)
+
+    def current_lr(self) -> float:
+        if self._schedule is not None:
+            return float(self._schedule(self.iterations))
+        return self.learning_rate
+
+    def spec(self) -> OptimizerSpec:
+        raise NotImplementedError
+
+    def get_config(self):
+        cfg = {"name": self.name, "learning_rate": self.learning_rate}
+        if self._schedule is not None:
+            cfg["learning_rate"] = {"class_name": type(self._schedule).__name__,
+                                    "config": self._schedule.get_config()}
+        return cfg
+
+
+class Adam(Optimizer):
+    def __init__(self, learning_rate=0.001, beta_1=0.9, beta_2=0.999, epsilon=1e-7, amsgrad=False,
+                 **kwargs):
+        super().__init__(learning_rate, **kwargs)
+        if amsgrad:
+            raise NotImplementedError("amsgrad is not supported by the fused Adam kernel")
+        self.beta_1, self.beta_2, self.epsilon = beta_1, beta_2, epsilon
+
+    def spec(self):
+        return OptimizerSpec("adam", lr=self.current_lr(), beta1=self.beta_1, beta2=self.beta_2,
+                             eps=self.epsilon)
+
+    def get_config(self):
+        return {**super().get_config(), "beta_1": self.beta_1, "beta_2": self.beta_2,
+                "epsilon": self.epsilon}
+
+
+class SGD(Optimizer):
+    def __init__(self, learning_rate=0.01, momentum=0.0, nesterov=False, **kwargs):
+        super().__init__(learning_rate, **kwargs)
+        self.momentum, self.nesterov = momentum, nesterov
+
+    def spec(self):
+        return OptimizerSpec("sgd", lr=self.current_lr(), momentum=self.momentum,
+                             nesterov=self.nesterov)
+
+    def get_config(self):
+        return {**super().get_config(), "momentum": self.momentum, "nesterov": self.nesterov}
+
+
+class RMSprop(Optimizer):
+    def __init__(self, learning_rate=0.001, rho=0.9, momentum=0.0, epsilon=1e-7, centered=False,
+                 **kwargs):
+        super().__init__(learning_rate, **kwargs)
+        if centered:
+            raise NotImplementedError("centered RMSprop is not supported by the fused kernel")
+        self.rho, self.momentum, self.epsilon = rho, momentum, epsilon
+
+    def spec(self):
+        return OptimizerSpec("rmsprop", lr=self.current_lr(), momentum=self.rho, eps=self.epsilon,
+                             rms_momentum=self.momentum)
+
+    def get_config(self):
+        return {**super().get_config(), "rho": self.rho, "momentum": self.momentum,
+                "epsilon": self.epsilon}
+
+
+_BY_NAME = {"adam": Adam, "sgd": SGD, "rmsprop": RMSprop}
+
+
+def get(identifier):
+    if isinstance(identifier, Optimizer):
+        return identifier
+    if isinstance(identifier, str):
+        key = identifier.lower()
+        if key in _BY_NAME:
+            return _BY_NAME[key]()
+    if isinstance(identifier, dict):
+        return deserialize(identifier)
+    raise ValueError(f"Could not interpret optimizer identifier: {identifier}")
+
+
+def serialize(opt: Optimizer) -> dict:
+    return {"class_name": type(opt).__name__, "config": opt.get_config()}
+
+
+def deserialize(d: dict) -> Optimizer:
+    cls = _BY_NAME[d["class_name"].lower()]
+    cfg = dict(d.get("config", {}))
+    cfg.pop("name", None)
+    lr = cfg.get("learning_rate")
+    if isinstance(lr, dict):
+        cfg["learning_rate"] = getattr(schedules, lr["class_name"])(**lr["config"])
+    return cls(**cfg)

@@ -14,7 +14,15 @@ from .loss import softmax_cross_entropy, softmax_cross_entropy_reference  # noqa
 from .elementwise import dropout, relu_bwd_bias_grad, normalize_u8_images  # noqa: F401
 from .optim import FlatOptimizerState, optim_flat, optim_tick, OPT_CODES, make_hyper  # noqa: F401
 
-KERNEL_LAUNCHES = {"count": 0}
+from .bn import batch_norm_nhwc, bn_available  # noqa: F401,E402
+
+
+def kernel_launches() -> int:
+    """How many cloud_b200 kernels this process has launched (bench.py reports it)."""
+    from . import dense as _d, loss as _l, elementwise as _e, optim as _o, bn as _b
+    from ..parallel import comm as _c
+    return (_d.launches() + _l.launches() + _e.launches() + _o.launches() + _b.launches() +
+            _c.launches())
 
 
 def native_available() -> bool:

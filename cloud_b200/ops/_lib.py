@@ -62,7 +62,7 @@ def _declare_kernels(lib: ctypes.CDLL) -> None:
     lib.cb2_relu_bwd_bias_grad.restype = i
     lib.cb2_relu_bwd_bias_grad.argtypes = [vp, vp, vp, vp, i, i, i, i, i, vp]
     lib.cb2_dropout.restype = i
-    lib.cb2_dropout.argtypes = [vp, vp, sz, f, u64, u64, i, vp]
+    lib.cb2_dropout.argtypes = [vp, vp, sz, f, u64, u64, vp, i, vp]
     lib.cb2_u8_to_bf16_normalize.restype = i
     lib.cb2_u8_to_bf16_normalize.argtypes = [vp, vp, sz, i, ctypes.POINTER(f), ctypes.POINTER(f), vp]
     lib.cb2_optim_tick.restype = i

@@ -140,7 +140,10 @@ class _DenseFn(torch.autograd.Function):
         x2 = _pad_cols(x2)
         wk = w if w.dtype == torch.bfloat16 else w.to(torch.bfloat16)
         wk = _pad_cols(wk)
-        y = gemm(x2, wk, bias=b, relu=(activation == "relu"), softmax=(activation == "softmax"))
+        fused_softmax = activation == "softmax" and w.shape[0] <= 256
+        y = gemm(x2, wk, bias=b, relu=(activation == "relu"), softmax=fused_softmax)
+        if activation == "softmax" and not fused_softmax:
+            y = torch.softmax(y.float(), dim=-1).to(torch.bfloat16)  # row wider than one tile
         ctx.activation = activation
         ctx.x_shape = x.shape
         ctx.in_features = w.shape[1]

@@ -47,19 +47,30 @@ def relu_bwd_bias_grad(dy: torch.Tensor, y: torch.Tensor | None, want_db: bool =
     return dz, db
 
 
+_step = {"tensor": None}
+
+
+def set_step_tensor(t) -> None:
+    """Device float holding the current training step (the engine's hyper[5]); dropout mixes it
+    into the Philox counter so graph replays do not repeat masks."""
+    _step["tensor"] = t
+
+
 class _DropoutFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, p, seed, offset):
         ctx.p, ctx.seed, ctx.offset = p, seed, offset
-        return _dropout_apply(x, p, seed, offset)
+        ctx.step = _step["tensor"] if (_step["tensor"] is not None and
+                                       _step["tensor"].device == x.device) else None
+        return _dropout_apply(x, p, seed, offset, ctx.step)
 
     @staticmethod
     def backward(ctx, dy):
-        # same (seed, offset) => same mask: nothing saved between forward and backward
-        return _dropout_apply(dy.contiguous(), ctx.p, ctx.seed, ctx.offset), None, None, None
+        # same (seed, offset, step) => same mask: nothing saved between forward and backward
+        return _dropout_apply(dy.contiguous(), ctx.p, ctx.seed, ctx.offset, ctx.step), None, None, None
 
 
-def _dropout_apply(x, p, seed, offset):
+def _dropout_apply(x, p, seed, offset, step=None):
     global _launches
     xc = x if x.is_contiguous() else x.contiguous()
     y = torch.empty_like(xc)
@@ -70,7 +81,8 @@ def _dropout_apply(x, p, seed, offset):
     else:
         raise TypeError("dropout supports float32 and bfloat16")
     rc = _lib.kernels().cb2_dropout(xc.data_ptr(), y.data_ptr(), xc.numel(), float(p),
-                                    ctypes.c_uint64(seed), ctypes.c_uint64(offset), dt, _stream())
+                                    ctypes.c_uint64(seed), ctypes.c_uint64(offset),
+                                    None if step is None else step.data_ptr(), dt, _stream())
     _lib.check(rc, "dropout")
     _launches += 1
     return y

@@ -1,0 +1,178 @@
+"""Communicator: the data-parallel engine's view of "the other replicas".
+
+Three back ends behind one interface:
+
+* ``p2p``   - hand-written sm_100a kernels over symmetric NVLink memory
+              (``csrc/kernels/comm.cu``: one-shot / two-shot / NVLS, fused with the optimizer).
+              This is the product path on a multi-GPU B200 box.
+* ``local`` - world size 1: the same fused kernels with no peers (CUDA) or plain PyTorch (CPU).
+* ``dist``  - ``torch.distributed`` all-reduce (NCCL on GPUs, gloo on CPUs) followed by the flat
+              optimizer kernel.  Baseline / oracle / CPU test path, and the fallback when peer
+              mapping is impossible; never chosen silently on a box where p2p works.
+
+Reference parity: what ``tf.distribute`` cross-device ops did for MirroredStrategy /
+MultiWorkerMirroredStrategy (core/preprocess.py:139-143) - see SURVEY.md sections 2.4 and 5.8.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import warnings
+
+import torch
+import torch.distributed as dist
+
+from ..ops import _lib
+from ..ops._lib import CommCtx
+
+MAX_RANKS = 8
+COMM_MAX_BLOCKS = 128
+AUX_FLOATS = 256
+PAD_BYTES = COMM_MAX_BLOCKS * MAX_RANKS * 4 + AUX_FLOATS * 4
+
+ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_NVLS = 0, 1, 2
+ALGO_NAMES = {"oneshot": ALGO_ONESHOT, "twoshot": ALGO_TWOSHOT, "nvls": ALGO_NVLS}
+
+_launches = 0
+
+
+def launches() -> int:
+    return _launches
+
+
+class Communicator:
+    def __init__(self, device: torch.device, group=None, backend: str | None = None):
+        self.device = device
+        self.group = group
+        self.initialized = dist.is_available() and dist.is_initialized()
+        self.rank = dist.get_rank(group) if self.initialized else 0
+        self.world = dist.get_world_size(group) if self.initialized else 1
+        env = os.environ.get("TFC_COMM_BACKEND")
+        backend = backend or env
+        if backend is None:
+            if self.world == 1:
+                backend = "local"
+            elif device.type == "cuda":
+                backend = "p2p"
+            else:
+                backend = "dist"
+        self.backend = backend
+        self.xchg = None
+        self.pad = None            # SymmetricBuffer (flags + aux)
+        self.epochs = None
+        self.aux = None            # fp32 view of the aux scalars (local)
+        self.multicast = False
+        if device.type == "cuda" and backend in ("p2p", "local"):
+            self._init_symm()
+        if self.aux is None:
+            self.aux = torch.zeros(AUX_FLOATS, dtype=torch.float32, device=device)
+
+    # -- set-up -------------------------------------------------------------------------------
+    def _init_symm(self) -> None:
+        from . import symm
+        if self.world > MAX_RANKS:
+            raise RuntimeError(f"p2p backend supports up to {MAX_RANKS} ranks per box")
+        try:
+            if self.world > 1:
+                self.xchg = symm.FdExchange(self.group)
+            self.pad = symm.SymmetricBuffer(PAD_BYTES, self.device, self.xchg, want_multicast=False)
+        except (symm.SymmUnavailable, OSError) as e:
+            if self.world > 1:
+                oks = [None] * self.world
+                dist.all_gather_object(oks, False, group=self.group)
+                warnings.warn(f"cloud_b200: peer-memory arena unavailable ({e}); using "
+                              f"torch.distributed all-reduce instead")
+                self.backend = "dist"
+            else:
+                self.backend = "local"
+            self.pad = None
+            return
+        if self.world > 1:
+            oks = [None] * self.world
+            dist.all_gather_object(oks, True, group=self.group)
+            if not all(oks):
+                self.backend = "dist"
+                self.pad = None
+                return
+        self.epochs = torch.zeros(COMM_MAX_BLOCKS, dtype=torch.int32, device=self.device)
+        self.aux = self.pad.view(torch.float32, AUX_FLOATS, COMM_MAX_BLOCKS * MAX_RANKS * 4)
+
+    @property
+    def uses_peer_memory(self) -> bool:
+        return self.pad is not None
+
+    def alloc_pair(self, nbytes_grad: int, nbytes_param: int):
+        """Symmetric (grad, param) arenas for one parameter group; plain tensors otherwise."""
+        from . import symm
+        if self.pad is not None:
+            want_mc = self.world > 1 and os.environ.get("TFC_DISABLE_NVLS") != "1"
+            g = symm.SymmetricBuffer(nbytes_grad, self.device, self.xchg, want_multicast=want_mc)
+            p = symm.SymmetricBuffer(nbytes_param, self.device, self.xchg, want_multicast=want_mc)
+            return g, p
+        return None, None
+
+    def make_ctx(self, grad_buf, param_buf) -> CommCtx:
+        ctx = CommCtx()
+        ctx.rank, ctx.world = self.rank, self.world
+        for i in range(MAX_RANKS):
+            ctx.grad_ptrs[i] = grad_buf.peer_ptrs[i] if i < self.world else None
+            ctx.param_ptrs[i] = param_buf.peer_ptrs[i] if i < self.world else None
+            ctx.pad_ptrs[i] = self.pad.peer_ptrs[i] if i < self.world else None
+        ctx.mc_grad = grad_buf.mc_ptr or None
+        ctx.mc_param = param_buf.mc_ptr or None
+        ctx.epochs = self.epochs.data_ptr()
+        return ctx
+
+    # -- kernels ------------------------------------------------------------------------------
+    def fused(self, ctx: CommCtx, *, algo: int, opt: int, grad_dtype: torch.dtype,
+              param_dtype: torch.dtype, off: int, length: int, master, s1, s2, state_off: int,
+              hyper: torch.Tensor, zero_grads: bool, aux_len: int = 0, aux_out=None,
+              blocks: int = 0, stream=None) -> None:
+        global _launches
+        st = (stream or torch.cuda.current_stream(self.device)).cuda_stream
+        rc = _lib.kernels().cb2_comm_fused(
+            ctypes.byref(ctx), algo, opt, 1 if grad_dtype == torch.bfloat16 else 0,
+            1 if param_dtype == torch.bfloat16 else 0, off, length,
+            None if master is None else master.data_ptr(),
+            None if s1 is None else s1.data_ptr(), None if s2 is None else s2.data_ptr(),
+            state_off, hyper.data_ptr(), int(zero_grads), aux_len,
+            None if aux_out is None else aux_out.data_ptr(), blocks, st)
+        _lib.check(rc, "comm_fused")
+        _launches += 1
+
+    def broadcast_arena(self, ctx: CommCtx, dtype: torch.dtype, off: int, length: int,
+                        root: int = 0) -> None:
+        global _launches
+        rc = _lib.kernels().cb2_comm_broadcast(
+            ctypes.byref(ctx), root, 1 if dtype == torch.bfloat16 else 0, off, length,
+            1 if ctx.mc_param else 0, 0, torch.cuda.current_stream(self.device).cuda_stream)
+        _lib.check(rc, "comm_broadcast")
+        _launches += 1
+
+    def device_barrier(self, ctx: CommCtx) -> None:
+        global _launches
+        rc = _lib.kernels().cb2_comm_barrier(ctypes.byref(ctx),
+                                             torch.cuda.current_stream(self.device).cuda_stream)
+        _lib.check(rc, "comm_barrier")
+        _launches += 1
+
+    # -- torch.distributed fallbacks ----------------------------------------------------------
+    def all_reduce_sum(self, t: torch.Tensor) -> torch.Tensor:
+        if self.world > 1:
+            if t.dtype == torch.bfloat16 and t.device.type == "cpu":
+                f = t.float()
+                dist.all_reduce(f, group=self.group)
+                t.copy_(f.to(t.dtype))
+            else:
+                dist.all_reduce(t, group=self.group)
+        return t
+
+    def broadcast(self, t: torch.Tensor, root: int = 0) -> torch.Tensor:
+        if self.world > 1:
+            src = dist.get_global_rank(self.group, root) if self.group else root
+            dist.broadcast(t, src=src, group=self.group)
+        return t
+
+    def barrier(self) -> None:
+        if self.world > 1:
+            dist.barrier(group=self.group)

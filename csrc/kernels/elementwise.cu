@@ -152,8 +152,10 @@ __global__ void zero_f32_kernel(float* p, int n) {
 // ---------------------------------------------------------------------------------------------
 // Philox-4x32-10 dropout; the mask is a pure function of (seed, offset + element index).
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint4 philox4x32(uint64_t ctr, uint64_t key) {
-  uint32_t c0 = static_cast<uint32_t>(ctr), c1 = static_cast<uint32_t>(ctr >> 32), c2 = 0, c3 = 0;
+__device__ __forceinline__ uint4 philox4x32(uint64_t ctr, uint64_t key, uint32_t stream_lo,
+                                            uint32_t stream_hi) {
+  uint32_t c0 = static_cast<uint32_t>(ctr), c1 = static_cast<uint32_t>(ctr >> 32);
+  uint32_t c2 = stream_lo, c3 = stream_hi;
   uint32_t k0 = static_cast<uint32_t>(key), k1 = static_cast<uint32_t>(key >> 32);
 #pragma unroll
   for (int r = 0; r < 10; ++r) {
@@ -169,11 +171,13 @@ __device__ __forceinline__ uint4 philox4x32(uint64_t ctr, uint64_t key) {
 template <typename T>
 __global__ void __launch_bounds__(256)
 dropout_kernel(const T* __restrict__ x, T* __restrict__ y, size_t n, float p, float scale,
-               uint64_t seed, uint64_t offset) {
+               uint64_t seed, uint64_t offset, const float* __restrict__ step_ptr) {
   const uint32_t thresh = static_cast<uint32_t>(fminf(p, 1.f) * 4294967295.0f);
+  // the training step lives in device memory so a CUDA-graph replay draws a fresh mask
+  const uint32_t step = step_ptr ? static_cast<uint32_t>(*step_ptr) : 0u;
   for (size_t g = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; g * 4 < n;
        g += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const uint4 r = philox4x32(offset + g, seed);
+    const uint4 r = philox4x32(offset + g, seed, step, 0x5eedu);
     const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
@@ -357,7 +361,7 @@ extern "C" int cb2_relu_bwd_bias_grad(const void* dy, const void* y, void* dz, v
 }
 
 extern "C" int cb2_dropout(const void* x, void* y, size_t n, float p, uint64_t seed,
-                           uint64_t offset, int dtype, void* stream) {
+                           uint64_t offset, const float* step_ptr, int dtype, void* stream) {
   if (p < 0.f || p >= 1.f) {
     set_last_error("dropout: rate must be in [0,1), got %f", p);
     return CB2_ERR_ARG;
@@ -372,11 +376,11 @@ extern "C" int cb2_dropout(const void* x, void* y, size_t n, float p, uint64_t s
   if (dtype == CB2_DTYPE_F32)
     dropout_kernel<float><<<blocks, 256, 0, st>>>(reinterpret_cast<const float*>(x),
                                                   reinterpret_cast<float*>(y), n, p, scale, seed,
-                                                  offset);
+                                                  offset, step_ptr);
   else
     dropout_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>(
         reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), n, p, scale,
-        seed, offset);
+        seed, offset, step_ptr);
   return check_cuda(cudaGetLastError(), "dropout launch");
 }
 

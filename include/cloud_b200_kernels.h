@@ -61,9 +61,11 @@ int cb2_softmax_xent(const void* logits, int dtype, const int64_t* labels, void*
 int cb2_relu_bwd_bias_grad(const void* dy, const void* y, void* dz, void* db, int db_dtype, int M,
                            int N, int ld, int accumulate, void* stream);
 
-/* Philox dropout, mask recomputed from (seed, offset) in backward: y = x * keep / (1-p). (K5) */
+/* Philox dropout, mask recomputed from (seed, offset, *step_ptr) in backward:
+ * y = x * keep / (1-p).  step_ptr (nullable) is a device float holding the training step, so a
+ * CUDA-graph replay draws a new mask each step. (K5) */
 int cb2_dropout(const void* x, void* y, size_t n, float p, uint64_t seed, uint64_t offset,
-                int dtype, void* stream);
+                const float* step_ptr, int dtype, void* stream);
 
 /* uint8 NHWC image -> bf16 NHWC, (x/255 - mean[c]) / std[c].  Input pipeline tail (K12). */
 int cb2_u8_to_bf16_normalize(const uint8_t* in, void* out, size_t n_pixels, int channels,
