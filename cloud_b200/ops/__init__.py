@@ -19,10 +19,11 @@ from .bn import batch_norm_nhwc, bn_available  # noqa: F401,E402
 
 def kernel_launches() -> int:
     """How many cloud_b200 kernels this process has launched (bench.py reports it)."""
-    from . import dense as _d, loss as _l, elementwise as _e, optim as _o, bn as _b
-    from ..parallel import comm as _c
-    return (_d.launches() + _l.launches() + _e.launches() + _o.launches() + _b.launches() +
-            _c.launches())
+    import importlib
+    total = 0
+    for name in ("dense", "loss", "elementwise", "optim", "bn"):   # `dense` the module, not the op
+        total += importlib.import_module(f"{__name__}.{name}").launches()
+    return total + importlib.import_module("cloud_b200.parallel.comm").launches()
 
 
 def native_available() -> bool:

@@ -1,16 +1,139 @@
-"""Fused NHWC batch normalisation (+ residual add + ReLU) - filled in by csrc/kernels/bn.cu."""
+"""Fused NHWC batch normalisation (+ residual add) (+ ReLU): ``csrc/kernels/bn.cu``.
+
+Forward: one statistics pass + one apply pass (instead of cuDNN BN, add and ReLU kernels each
+re-reading the activation); backward: one reduce pass + one apply pass with the ReLU mask and the
+shortcut gradient folded in.  Reference workload: ResNet-50's 53 BatchNormalization layers
+(core/tests/examples/call_run_within_script_with_keras_fit.py:79-83, K8).
+"""
 from __future__ import annotations
 
+import ctypes
+import os
+
+import torch
+
+from . import _lib
+
 _launches = 0
+_declared = False
 
 
 def launches() -> int:
     return _launches
 
 
+def _k():
+    global _declared
+    lib = _lib.kernels()
+    if not _declared:
+        vp, i, f = ctypes.c_void_p, ctypes.c_int, ctypes.c_float
+        lib.cb2_bn_supported.restype = i
+        lib.cb2_bn_supported.argtypes = [i]
+        lib.cb2_bn_forward.restype = i
+        lib.cb2_bn_forward.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, f, f, i, i, vp]
+        lib.cb2_bn_backward.restype = i
+        lib.cb2_bn_backward.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp]
+        _declared = True
+    return lib
+
+
 def bn_available() -> bool:
-    return False
+    if os.environ.get("TFC_DISABLE_FUSED_BN") == "1":
+        return False
+    try:
+        _k()
+        return True
+    except _lib.KernelsUnavailable:
+        return False
 
 
-def batch_norm_nhwc(*args, **kwargs):
-    raise NotImplementedError
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _is_nhwc(t):
+    return t.dim() == 4 and t.is_contiguous(memory_format=torch.channels_last)
+
+
+class _BNFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, residual, run_mean, run_var, momentum, eps, relu):
+        global _launches
+        N, C, H, W = x.shape
+        M = N * H * W
+        y = torch.empty_like(x)                       # preserves channels_last
+        sums = torch.zeros(2 * C, dtype=torch.float32, device=x.device)
+        save = torch.empty(2 * C, dtype=torch.float32, device=x.device)
+        rc = _k().cb2_bn_forward(x.data_ptr(), None if residual is None else residual.data_ptr(),
+                                 y.data_ptr(), sums.data_ptr(), gamma.data_ptr(), beta.data_ptr(),
+                                 run_mean.data_ptr(), run_var.data_ptr(), save.data_ptr(),
+                                 save[C:].data_ptr(), M, C, float(eps), float(momentum), int(relu), 1,
+                                 _stream())
+        _lib.check(rc, "bn_forward")
+        _launches += 2
+        ctx.save_for_backward(x, y if relu else None, gamma, save)
+        ctx.relu, ctx.has_res, ctx.M, ctx.C = relu, residual is not None, M, C
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        global _launches
+        x, y, gamma, save = ctx.saved_tensors
+        C, M = ctx.C, ctx.M
+        if not _is_nhwc(dy):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        dx = torch.empty_like(x)
+        dres = torch.empty_like(x) if ctx.has_res and ctx.relu else None
+        sums = torch.zeros(2 * C, dtype=torch.float32, device=x.device)
+        rc = _k().cb2_bn_backward(dy.data_ptr(), None if y is None else y.data_ptr(), x.data_ptr(),
+                                  save.data_ptr(), save[C:].data_ptr(), gamma.data_ptr(),
+                                  sums.data_ptr(), dx.data_ptr(),
+                                  None if dres is None else dres.data_ptr(), M, C, int(ctx.relu),
+                                  _stream())
+        _lib.check(rc, "bn_backward")
+        _launches += 2
+        if ctx.has_res and dres is None:
+            dres = dy                                 # no ReLU: the shortcut gradient is dy itself
+        return dx, sums[C:], sums[:C], dres, None, None, None, None, None
+
+
+def batch_norm_nhwc(x, gamma, beta, run_mean, run_var, training, momentum, eps, relu=False,
+                    residual=None):
+    """``act(BN(x) + residual)`` for bf16 channels_last ``x``; ``momentum`` is the torch-style
+    update rate of the running statistics (1 - keras_momentum)."""
+    global _launches
+    C = x.shape[1]
+    ok = (x.is_cuda and x.dtype == torch.bfloat16 and _is_nhwc(x) and _k().cb2_bn_supported(C)
+          and gamma.dtype == torch.float32 and (residual is None or (
+              residual.dtype == torch.bfloat16 and _is_nhwc(residual) and residual.shape == x.shape)))
+    if not ok:
+        y = torch.nn.functional.batch_norm(x, run_mean, run_var, gamma, beta, training, momentum, eps)
+        if residual is not None:
+            y = y + residual
+        return torch.relu_(y) if relu else y
+    needs_grad = torch.is_grad_enabled() and (
+        x.requires_grad or gamma.requires_grad or beta.requires_grad or
+        (residual is not None and residual.requires_grad))
+    if training and needs_grad:
+        return _BNFn.apply(x, gamma, beta, residual, run_mean, run_var, momentum, eps, relu)
+    if needs_grad:   # frozen layer inside a trainable network: let autograd handle it
+        y = torch.nn.functional.batch_norm(x, run_mean, run_var, gamma, beta, False, momentum, eps)
+        if residual is not None:
+            y = y + residual
+        return torch.relu_(y) if relu else y
+    # no autograd: inference from the running statistics (one pass), or statistics + apply
+    N, _C, H, W = x.shape
+    y = torch.empty_like(x)
+    sums_ptr = save_ptr = save2_ptr = None
+    if training:
+        sums = torch.zeros(2 * C, dtype=torch.float32, device=x.device)
+        save = torch.empty(2 * C, dtype=torch.float32, device=x.device)
+        sums_ptr, save_ptr, save2_ptr = sums.data_ptr(), save.data_ptr(), save[C:].data_ptr()
+    rc = _k().cb2_bn_forward(x.data_ptr(), None if residual is None else residual.data_ptr(),
+                             y.data_ptr(), sums_ptr, gamma.data_ptr(), beta.data_ptr(),
+                             run_mean.data_ptr(), run_var.data_ptr(), save_ptr, save2_ptr,
+                             N * H * W, C, float(eps), float(momentum), int(relu), int(training),
+                             _stream())
+    _lib.check(rc, "bn_forward")
+    _launches += 2 if training else 1
+    return y

@@ -9,7 +9,9 @@ import pytest
 import torch
 
 from cloud_b200 import ops
-from cloud_b200.ops import dense as dense_ops
+import importlib
+
+dense_ops = importlib.import_module('cloud_b200.ops.dense')
 from cloud_b200.ops.optim import _reference_update
 
 pytestmark = pytest.mark.gpu
@@ -221,3 +223,54 @@ def test_kernel_launch_counters_move():
     before = dense_ops.launches()
     ops.gemm(_rand_bf16(128, 64), _rand_bf16(64, 64))
     assert dense_ops.launches() == before + 1
+
+
+@pytest.mark.parametrize("C,HW,N", [(64, 56, 8), (256, 14, 16), (2048, 7, 4), (512, 28, 3)])
+@pytest.mark.parametrize("relu,with_res", [(False, False), (True, False), (True, True), (False, True)])
+def test_fused_batch_norm(C, HW, N, relu, with_res):
+    torch.manual_seed(11)
+    dev = _dev()
+    x = (torch.randn(N, C, HW, HW, device=dev) * 2 + 0.5).to(torch.bfloat16) \
+        .contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    res = None
+    if with_res:
+        res = torch.randn(N, C, HW, HW, device=dev).to(torch.bfloat16) \
+            .contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    gamma = (torch.rand(C, device=dev) + 0.5).requires_grad_(True)
+    beta = (torch.randn(C, device=dev) * 0.1).requires_grad_(True)
+    rm, rv = torch.zeros(C, device=dev), torch.ones(C, device=dev)
+    y = ops.batch_norm_nhwc(x, gamma, beta, rm, rv, True, 0.1, 1e-5, relu=relu, residual=res)
+    gy = torch.randn_like(y)
+    y.backward(gy)
+    # fp32 oracle
+    xr = x.detach().float().requires_grad_(True)
+    rr = res.detach().float().requires_grad_(True) if with_res else None
+    gr, br = gamma.detach().clone().requires_grad_(True), beta.detach().clone().requires_grad_(True)
+    rm2, rv2 = torch.zeros(C, device=dev), torch.ones(C, device=dev)
+    yr = torch.nn.functional.batch_norm(xr, rm2, rv2, gr, br, True, 0.1, 1e-5)
+    if with_res:
+        yr = yr + rr
+    if relu:
+        yr = torch.relu(yr)
+    yr.backward(gy.float())
+    _check_close(y, yr, 2e-2, 2e-2, "bn fwd")
+    _check_close(rm, rm2, 1e-3, 1e-3, "running mean")
+    _check_close(rv, rv2, 1e-2, 1e-2, "running var")
+    # compare gradients where the bf16 ReLU mask agrees with the fp32 one
+    _check_close(beta.grad, br.grad, 3e-2, 0.05 * (N * HW * HW) ** 0.5, "dbeta")
+    _check_close(gamma.grad, gr.grad, 3e-2, 0.08 * (N * HW * HW) ** 0.5, "dgamma")
+    err = (x.grad.float() - xr.grad).abs()
+    assert (err > 0.05 + 0.05 * xr.grad.abs()).float().mean().item() < 2e-3, "bn dX"
+    if with_res:
+        err = (res.grad.float() - rr.grad).abs()
+        assert (err > 0.02 + 0.02 * rr.grad.abs()).float().mean().item() < 2e-3, "bn dRes"
+    # inference path
+    with torch.no_grad():
+        yi = ops.batch_norm_nhwc(x.detach(), gamma.detach(), beta.detach(), rm, rv, False, 0.1, 1e-5,
+                                 relu=relu, residual=None if res is None else res.detach())
+        yo = torch.nn.functional.batch_norm(x.detach().float(), rm, rv, gamma, beta, False, 0.1, 1e-5)
+        if with_res:
+            yo = yo + res.detach().float()
+        if relu:
+            yo = torch.relu(yo)
+    _check_close(yi, yo, 2e-2, 2e-2, "bn inference")
