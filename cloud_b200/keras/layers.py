@@ -426,6 +426,10 @@ class Conv2D(Layer):
         self.use_bias = use_bias
         self.kernel_initializer = kernel_initializer
         self.bias_initializer = bias_initializer
+        # Set by a directly following BatchNormalization: in training mode batch-norm removes any
+        # per-channel shift, so the bias add (one extra read+write of the activation) and its
+        # gradient reduction (one extra read of dY; the gradient is exactly zero) are skipped.
+        self.bias_absorbed_by_bn = False
 
     def build(self, input_shape):
         cin = int(input_shape[-1])
@@ -466,6 +470,8 @@ class Conv2D(Layer):
         if w.dtype != x.dtype:
             x = x.to(w.dtype)
         b = self.bias
+        if b is not None and self.bias_absorbed_by_bn and training:
+            b = None
         if b is not None and b.dtype != x.dtype:
             b = b.to(x.dtype)
         y = F.conv2d(x, w, b, stride=self.strides, padding=pad, dilation=self.dilation)
@@ -574,6 +580,7 @@ class BatchNormalization(Layer):
         if activation not in (None, "relu"):
             raise ValueError("BatchNormalization can only fuse activation='relu'")
         self.fused_activation = activation     # extension: BN+ReLU in one memory pass
+        self._absorbed_conv = None             # (set in _symbolic_call) conv whose bias we absorb
 
     def build(self, input_shape):
         c = int(input_shape[-1])
@@ -597,18 +604,35 @@ class BatchNormalization(Layer):
             input_shape = input_shape[0]
         super()._maybe_build(input_shape)
 
+    def _symbolic_call(self, inputs):
+        out = super()._symbolic_call(inputs)
+        first = inputs[0] if isinstance(inputs, (list, tuple)) else inputs
+        prev = first.layer
+        if isinstance(prev, Conv2D) and prev.use_bias and prev.activation_name in (None, "linear") \
+                and self._trainable:
+            prev.bias_absorbed_by_bn = True
+            object.__setattr__(self, "_absorbed_conv", prev)   # not a submodule: no double registration
+        return out
+
     def call(self, x, training=False, relu=None, residual=None):
         if isinstance(x, (list, tuple)):       # [x, shortcut]: y = act(BN(x) + shortcut)
             x, residual = x
         if relu is None:
             relu = self.fused_activation == "relu"
         train = bool(training) and self._trainable
+        conv = self._absorbed_conv
+        mean_bias = conv.bias if (conv is not None and train and conv.bias is not None) else None
         if x.is_cuda and x.dim() == 4 and x.dtype == torch.bfloat16 and ops.bn_available():
             return ops.batch_norm_nhwc(x, self.gamma, self.beta, self.moving_mean,
                                        self.moving_variance, train, 1.0 - self.momentum,
-                                       self.epsilon, relu=relu, residual=residual)
+                                       self.epsilon, relu=relu, residual=residual,
+                                       mean_bias=mean_bias)
         y = F.batch_norm(x, self.moving_mean, self.moving_variance, self.gamma, self.beta, train,
                          1.0 - self.momentum, self.epsilon)
+        if mean_bias is not None:
+            with torch.no_grad():    # the skipped conv bias still belongs in the moving mean
+                # .data: batch_norm saved the buffer for backward; this update is not part of the graph
+                self.moving_mean.data.add_((1.0 - self.momentum) * mean_bias.detach().float())
         if residual is not None:
             y = y + residual
         return torch.relu_(y) if relu else y

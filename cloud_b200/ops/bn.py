@@ -30,9 +30,11 @@ def _k():
         lib.cb2_bn_supported.restype = i
         lib.cb2_bn_supported.argtypes = [i]
         lib.cb2_bn_forward.restype = i
-        lib.cb2_bn_forward.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, f, f, i, i, vp]
+        lib.cb2_bn_scratch_floats.restype = i
+        lib.cb2_bn_scratch_floats.argtypes = [i]
+        lib.cb2_bn_forward.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, f, f, i, i, vp]
         lib.cb2_bn_backward.restype = i
-        lib.cb2_bn_backward.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp]
+        lib.cb2_bn_backward.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp]
         _declared = True
     return lib
 
@@ -57,18 +59,19 @@ def _is_nhwc(t):
 
 class _BNFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, residual, run_mean, run_var, momentum, eps, relu):
+    def forward(ctx, x, gamma, beta, residual, run_mean, run_var, momentum, eps, relu, mean_bias):
         global _launches
         N, C, H, W = x.shape
         M = N * H * W
         y = torch.empty_like(x)                       # preserves channels_last
-        sums = torch.zeros(2 * C, dtype=torch.float32, device=x.device)
+        sums = torch.zeros(_k().cb2_bn_scratch_floats(C), dtype=torch.float32, device=x.device)
         save = torch.empty(2 * C, dtype=torch.float32, device=x.device)
         rc = _k().cb2_bn_forward(x.data_ptr(), None if residual is None else residual.data_ptr(),
                                  y.data_ptr(), sums.data_ptr(), gamma.data_ptr(), beta.data_ptr(),
                                  run_mean.data_ptr(), run_var.data_ptr(), save.data_ptr(),
-                                 save[C:].data_ptr(), M, C, float(eps), float(momentum), int(relu), 1,
-                                 _stream())
+                                 save[C:].data_ptr(),
+                                 None if mean_bias is None else mean_bias.data_ptr(), M, C,
+                                 float(eps), float(momentum), int(relu), 1, _stream())
         _lib.check(rc, "bn_forward")
         _launches += 2
         ctx.save_for_backward(x, y if relu else None, gamma, save)
@@ -84,23 +87,26 @@ class _BNFn(torch.autograd.Function):
             dy = dy.contiguous(memory_format=torch.channels_last)
         dx = torch.empty_like(x)
         dres = torch.empty_like(x) if ctx.has_res and ctx.relu else None
-        sums = torch.zeros(2 * C, dtype=torch.float32, device=x.device)
+        sums = torch.zeros(_k().cb2_bn_scratch_floats(C), dtype=torch.float32, device=x.device)
+        grads = torch.empty(2 * C, dtype=torch.float32, device=x.device)
         rc = _k().cb2_bn_backward(dy.data_ptr(), None if y is None else y.data_ptr(), x.data_ptr(),
                                   save.data_ptr(), save[C:].data_ptr(), gamma.data_ptr(),
-                                  sums.data_ptr(), dx.data_ptr(),
+                                  sums.data_ptr(), grads.data_ptr(), dx.data_ptr(),
                                   None if dres is None else dres.data_ptr(), M, C, int(ctx.relu),
                                   _stream())
         _lib.check(rc, "bn_backward")
         _launches += 2
         if ctx.has_res and dres is None:
             dres = dy                                 # no ReLU: the shortcut gradient is dy itself
-        return dx, sums[C:], sums[:C], dres, None, None, None, None, None
+        return dx, grads[C:], grads[:C], dres, None, None, None, None, None, None
 
 
 def batch_norm_nhwc(x, gamma, beta, run_mean, run_var, training, momentum, eps, relu=False,
-                    residual=None):
+                    residual=None, mean_bias=None):
     """``act(BN(x) + residual)`` for bf16 channels_last ``x``; ``momentum`` is the torch-style
-    update rate of the running statistics (1 - keras_momentum)."""
+    update rate of the running statistics (1 - keras_momentum).  ``mean_bias`` (fp32 [C]) is added
+    to the batch mean when the running mean is refreshed: it is the bias of a preceding
+    convolution that was skipped in training because batch-norm cancels it exactly."""
     global _launches
     C = x.shape[1]
     ok = (x.is_cuda and x.dtype == torch.bfloat16 and _is_nhwc(x) and _k().cb2_bn_supported(C)
@@ -115,7 +121,7 @@ def batch_norm_nhwc(x, gamma, beta, run_mean, run_var, training, momentum, eps, 
         x.requires_grad or gamma.requires_grad or beta.requires_grad or
         (residual is not None and residual.requires_grad))
     if training and needs_grad:
-        return _BNFn.apply(x, gamma, beta, residual, run_mean, run_var, momentum, eps, relu)
+        return _BNFn.apply(x, gamma, beta, residual, run_mean, run_var, momentum, eps, relu, mean_bias)
     if needs_grad:   # frozen layer inside a trainable network: let autograd handle it
         y = torch.nn.functional.batch_norm(x, run_mean, run_var, gamma, beta, False, momentum, eps)
         if residual is not None:
@@ -126,12 +132,13 @@ def batch_norm_nhwc(x, gamma, beta, run_mean, run_var, training, momentum, eps, 
     y = torch.empty_like(x)
     sums_ptr = save_ptr = save2_ptr = None
     if training:
-        sums = torch.zeros(2 * C, dtype=torch.float32, device=x.device)
+        sums = torch.zeros(_k().cb2_bn_scratch_floats(C), dtype=torch.float32, device=x.device)
         save = torch.empty(2 * C, dtype=torch.float32, device=x.device)
         sums_ptr, save_ptr, save2_ptr = sums.data_ptr(), save.data_ptr(), save[C:].data_ptr()
     rc = _k().cb2_bn_forward(x.data_ptr(), None if residual is None else residual.data_ptr(),
                              y.data_ptr(), sums_ptr, gamma.data_ptr(), beta.data_ptr(),
                              run_mean.data_ptr(), run_var.data_ptr(), save_ptr, save2_ptr,
+                             None if mean_bias is None else mean_bias.data_ptr(),
                              N * H * W, C, float(eps), float(momentum), int(relu), int(training),
                              _stream())
     _lib.check(rc, "bn_forward")

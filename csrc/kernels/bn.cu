@@ -14,6 +14,10 @@
 namespace cb2 {
 
 constexpr int kBnThreads = 256;
+// Partial sums of different CTAs land in kBnCopies replicas of the [2C] accumulator
+// (replica = blockIdx % kBnCopies): same-address L2 atomics serialise, and with ~600 CTAs on one
+// replica they - not HBM - set the kernel time (measured: 60 us floor per launch).
+constexpr int kBnCopies = 16;
 
 struct BnGeom {
   int tpr;       // threads per row = C / 8
@@ -48,12 +52,39 @@ __device__ __forceinline__ void bn_block_reduce_to_global(float (&a)[8], float (
     }
   }
   if (rlane == 0) {
+    float* dst = out + static_cast<size_t>(blockIdx.x % kBnCopies) * 2 * C;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      atomicAdd(out + c8 + j, a[j]);
-      atomicAdd(out + C + c8 + j, b[j]);
+      atomicAdd(dst + c8 + j, a[j]);
+      atomicAdd(dst + C + c8 + j, b[j]);
     }
   }
+}
+
+// Sum the replicas for this thread's 8 channels; one row-lane does it, the others read smem.
+__device__ __forceinline__ void bn_gather_sums(const float* __restrict__ sums, int C, int c8,
+                                               int rlane, float* s_a, float* s_b,
+                                               float (&a)[8], float (&b)[8]) {
+  if (rlane == 0) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] = b[j] = 0.f;
+    for (int k = 0; k < kBnCopies; ++k) {
+      const float* src = sums + static_cast<size_t>(k) * 2 * C;
+      const float4 a0 = *reinterpret_cast<const float4*>(src + c8);
+      const float4 a1 = *reinterpret_cast<const float4*>(src + c8 + 4);
+      const float4 b0 = *reinterpret_cast<const float4*>(src + C + c8);
+      const float4 b1 = *reinterpret_cast<const float4*>(src + C + c8 + 4);
+      a[0] += a0.x; a[1] += a0.y; a[2] += a0.z; a[3] += a0.w;
+      a[4] += a1.x; a[5] += a1.y; a[6] += a1.z; a[7] += a1.w;
+      b[0] += b0.x; b[1] += b0.y; b[2] += b0.z; b[3] += b0.w;
+      b[4] += b1.x; b[5] += b1.y; b[6] += b1.z; b[7] += b1.w;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { s_a[c8 + j] = a[j]; s_b[c8 + j] = b[j]; }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { a[j] = s_a[c8 + j]; b[j] = s_b[c8 + j]; }
 }
 
 // sums[0:C] += sum_m x ; sums[C:2C] += sum_m x^2
@@ -67,15 +98,17 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ sums, i
   for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
   const int stride = gridDim.x * rows;
   int row = blockIdx.x * rows + rlane;
-  // two rows in flight per thread
-  for (; row + stride < M; row += 2 * stride) {
+  // four rows in flight per thread
+  for (; row + 3 * stride < M; row += 4 * stride) {
     const uint4 w0 = ld_stream_v4(x + static_cast<size_t>(row) * C + c8);
     const uint4 w1 = ld_stream_v4(x + static_cast<size_t>(row + stride) * C + c8);
-    const Vec8 a = unpack8_bf16(w0), b = unpack8_bf16(w1);
+    const uint4 w2 = ld_stream_v4(x + static_cast<size_t>(row + 2 * stride) * C + c8);
+    const uint4 w3 = ld_stream_v4(x + static_cast<size_t>(row + 3 * stride) * C + c8);
+    const Vec8 a = unpack8_bf16(w0), b = unpack8_bf16(w1), c = unpack8_bf16(w2), d = unpack8_bf16(w3);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      s[j] += a.v[j] + b.v[j];
-      q[j] = fmaf(a.v[j], a.v[j], fmaf(b.v[j], b.v[j], q[j]));
+      s[j] += (a.v[j] + b.v[j]) + (c.v[j] + d.v[j]);
+      q[j] = fmaf(a.v[j], a.v[j], fmaf(b.v[j], b.v[j], fmaf(c.v[j], c.v[j], fmaf(d.v[j], d.v[j], q[j]))));
     }
   }
   for (; row < M; row += stride) {
@@ -96,19 +129,22 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
                 __nv_bfloat16* __restrict__ y, const float* __restrict__ sums,
                 const float* __restrict__ gamma, const float* __restrict__ beta,
                 float* __restrict__ run_mean, float* __restrict__ run_var,
-                float* __restrict__ save_mean, float* __restrict__ save_invstd, int M, int C,
-                float eps, float momentum, int relu, int training) {
+                float* __restrict__ save_mean, float* __restrict__ save_invstd,
+                const float* __restrict__ mean_bias, int M, int C, float eps, float momentum,
+                int relu, int training) {
+  __shared__ float s_a[2048], s_b[2048];
   const int tpr = C >> 3, rows = kBnThreads / tpr;
   const int rlane = threadIdx.x / tpr, c8 = (threadIdx.x % tpr) * 8;
-  float sc[8], sh[8];
+  float sc[8], sh[8], tot[8], totsq[8];
   const float invM = 1.f / static_cast<float>(M);
+  if (training) bn_gather_sums(sums, C, c8, rlane, s_a, s_b, tot, totsq);
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     const int c = c8 + j;
     float mean, var;
     if (training) {
-      mean = sums[c] * invM;
-      var = fmaxf(sums[C + c] * invM - mean * mean, 0.f);
+      mean = tot[j] * invM;
+      var = fmaxf(totsq[j] * invM - mean * mean, 0.f);
     } else {
       mean = run_mean[c];
       var = run_var[c];
@@ -120,7 +156,8 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
       save_mean[c] = mean;
       save_invstd[c] = istd;
       const float unbiased = M > 1 ? var * static_cast<float>(M) / static_cast<float>(M - 1) : var;
-      run_mean[c] = (1.f - momentum) * run_mean[c] + momentum * mean;
+      run_mean[c] = (1.f - momentum) * run_mean[c] +
+                    momentum * (mean + (mean_bias ? mean_bias[c] : 0.f));
       run_var[c] = (1.f - momentum) * run_var[c] + momentum * unbiased;
     }
   }
@@ -161,7 +198,33 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     db[j] = dg[j] = 0.f;
   }
   const int stride = gridDim.x * rows;
-  for (int row = blockIdx.x * rows + rlane; row < M; row += stride) {
+  int row = blockIdx.x * rows + rlane;
+  // two rows (up to six 16-byte loads) in flight per thread
+  for (; row + stride < M; row += 2 * stride) {
+    const size_t i0 = static_cast<size_t>(row) * C + c8;
+    const size_t i1 = static_cast<size_t>(row + stride) * C + c8;
+    const uint4 wg0 = ld_stream_v4(dy + i0), wg1 = ld_stream_v4(dy + i1);
+    const uint4 wx0 = ld_stream_v4(x + i0), wx1 = ld_stream_v4(x + i1);
+    uint4 wy0 = make_uint4(0, 0, 0, 0), wy1 = wy0;
+    if (relu) { wy0 = ld_stream_v4(y + i0); wy1 = ld_stream_v4(y + i1); }
+    Vec8 g0 = unpack8_bf16(wg0), g1 = unpack8_bf16(wg1);
+    const Vec8 x0 = unpack8_bf16(wx0), x1 = unpack8_bf16(wx1);
+    if (relu) {
+      const Vec8 y0 = unpack8_bf16(wy0), y1 = unpack8_bf16(wy1);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        g0.v[j] = y0.v[j] > 0.f ? g0.v[j] : 0.f;
+        g1.v[j] = y1.v[j] > 0.f ? g1.v[j] : 0.f;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      db[j] += g0.v[j] + g1.v[j];
+      dg[j] = fmaf(g0.v[j], (x0.v[j] - mean[j]) * istd[j],
+                   fmaf(g1.v[j], (x1.v[j] - mean[j]) * istd[j], dg[j]));
+    }
+  }
+  for (; row < M; row += stride) {
     const size_t idx = static_cast<size_t>(row) * C + c8;
     Vec8 g = unpack8_bf16(ld_stream_v4(dy + idx));
     const Vec8 xv = unpack8_bf16(ld_stream_v4(x + idx));
@@ -184,20 +247,27 @@ __global__ void __launch_bounds__(kBnThreads)
 bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
                     const __nv_bfloat16* __restrict__ x, const float* __restrict__ save_mean,
                     const float* __restrict__ save_invstd, const float* __restrict__ gamma,
-                    const float* __restrict__ sums, __nv_bfloat16* __restrict__ dx,
-                    __nv_bfloat16* __restrict__ dres, int M, int C, int relu) {
+                    const float* __restrict__ sums, float* __restrict__ dgamma_dbeta,
+                    __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres, int M, int C,
+                    int relu) {
+  __shared__ float s_a[2048], s_b[2048];
   const int tpr = C >> 3, rows = kBnThreads / tpr;
   const int rlane = threadIdx.x / tpr, c8 = (threadIdx.x % tpr) * 8;
   const float invM = 1.f / static_cast<float>(M);
-  float mean[8], istd[8], k0[8], k1[8], k2[8];
+  float mean[8], istd[8], k0[8], k1[8], k2[8], db[8], dg[8];
+  bn_gather_sums(sums, C, c8, rlane, s_a, s_b, db, dg);
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     const int c = c8 + j;
     mean[j] = save_mean[c];
     istd[j] = save_invstd[c];
     k0[j] = gamma[c] * istd[j];
-    k1[j] = sums[c] * invM;        // dbeta / M
-    k2[j] = sums[C + c] * invM;    // dgamma / M
+    k1[j] = db[j] * invM;        // dbeta / M
+    k2[j] = dg[j] * invM;        // dgamma / M
+    if (blockIdx.x == 0 && rlane == 0) {
+      dgamma_dbeta[c] = db[j];       // [0:C] dbeta
+      dgamma_dbeta[C + c] = dg[j];   // [C:2C] dgamma
+    }
   }
   const int stride = gridDim.x * rows;
   for (int row = blockIdx.x * rows + rlane; row < M; row += stride) {
@@ -227,7 +297,7 @@ static int bn_grid(int M, int C) {
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   long long want = (static_cast<long long>(M) + rows - 1) / rows;
-  const long long cap = static_cast<long long>(sms) * 8;
+  const long long cap = static_cast<long long>(sms) * 4;
   if (want > cap) want = cap;
   if (want < 1) want = 1;
   return static_cast<int>(want);
@@ -250,10 +320,14 @@ extern "C" int cb2_bn_supported(int C) {
   return (C > 0 && !(C & 7) && C <= 2048 && (kBnThreads % (C >> 3)) == 0) ? 1 : 0;
 }
 
-extern "C" int cb2_bn_forward(const void* x, const void* residual, void* y, float* sums /*[2C], zeroed*/,
+extern "C" int cb2_bn_scratch_floats(int C) { return kBnCopies * 2 * C; }
+
+extern "C" int cb2_bn_forward(const void* x, const void* residual, void* y,
+                              float* sums /*[cb2_bn_scratch_floats(C)], zeroed*/,
                               const float* gamma, const float* beta, float* run_mean, float* run_var,
-                              float* save_mean, float* save_invstd, int M, int C, float eps,
-                              float momentum, int relu, int training, void* stream) {
+                              float* save_mean, float* save_invstd, const float* mean_bias, int M,
+                              int C, float eps, float momentum, int relu, int training,
+                              void* stream) {
   int rc = bn_check(M, C, "bn_forward");
   if (rc) return rc;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
@@ -265,13 +339,14 @@ extern "C" int cb2_bn_forward(const void* x, const void* residual, void* y, floa
   bn_apply_kernel<<<grid, kBnThreads, 0, st>>>(
       reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<const __nv_bfloat16*>(residual),
       reinterpret_cast<__nv_bfloat16*>(y), sums, gamma, beta, run_mean, run_var, save_mean,
-      save_invstd, M, C, eps, momentum, relu, training);
+      save_invstd, mean_bias, M, C, eps, momentum, relu, training);
   return check_cuda(cudaGetLastError(), "bn_forward launch");
 }
 
 extern "C" int cb2_bn_backward(const void* dy, const void* y, const void* x, const float* save_mean,
                                const float* save_invstd, const float* gamma,
-                               float* sums /*[2C], zeroed: out dbeta | dgamma*/, void* dx,
+                               float* sums /*[cb2_bn_scratch_floats(C)], zeroed*/,
+                               float* dbeta_dgamma /*out [2C]: dbeta | dgamma*/, void* dx,
                                void* dres /*nullable*/, int M, int C, int relu, void* stream) {
   int rc = bn_check(M, C, "bn_backward");
   if (rc) return rc;
@@ -284,7 +359,7 @@ extern "C" int cb2_bn_backward(const void* dy, const void* y, const void* x, con
       reinterpret_cast<const __nv_bfloat16*>(x), save_mean, save_invstd, sums, M, C, relu);
   bn_bwd_apply_kernel<<<grid, kBnThreads, 0, st>>>(
       reinterpret_cast<const __nv_bfloat16*>(dy), reinterpret_cast<const __nv_bfloat16*>(y),
-      reinterpret_cast<const __nv_bfloat16*>(x), save_mean, save_invstd, gamma, sums,
+      reinterpret_cast<const __nv_bfloat16*>(x), save_mean, save_invstd, gamma, sums, dbeta_dgamma,
       reinterpret_cast<__nv_bfloat16*>(dx), reinterpret_cast<__nv_bfloat16*>(dres), M, C, relu);
   return check_cuda(cudaGetLastError(), "bn_backward launch");
 }
