@@ -122,7 +122,7 @@ class Strategy:
     def communicator(self):
         if self._communicator is None:
             from ..parallel.comm import Communicator
-            self._communicator = Communicator(self.device, self._group)
+            self._communicator = Communicator(self.device, self._group, single=self._world == 1)
         return self._communicator
 
     # --- scope ---------------------------------------------------------------------------------

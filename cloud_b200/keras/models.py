@@ -90,7 +90,7 @@ class _ArraySource:
             else:
                 xb = self.x[a:b]
                 yb = self.y[a:b] if self.y is not None else None
-            yield xb, yb
+            yield xb, yb, hi - lo
 
 
 class _IterSource:
@@ -137,13 +137,15 @@ class _IterSource:
             xb = torch.as_tensor(_np(xb)) if not isinstance(xb, torch.Tensor) else xb
             if yb is not None and not isinstance(yb, torch.Tensor):
                 yb = torch.as_tensor(_np(yb))
+            n_global = len(xb)
             if self.world > 1 and not isinstance(self.ds, DistributedDataset):
-                n = len(xb)
-                per = -(-n // self.world)
-                a, b = self.rank * per, min(n, (self.rank + 1) * per)
+                per = -(-n_global // self.world)
+                a, b = self.rank * per, min(n_global, (self.rank + 1) * per)
                 xb = xb[a:b]
                 yb = yb[a:b] if yb is not None else None
-            yield xb, yb
+            elif self.world > 1:
+                n_global = None          # already split by the strategy: assume an even split
+            yield xb, yb, n_global
 
 
 class _Prefetcher:
@@ -159,8 +161,8 @@ class _Prefetcher:
 
     def __iter__(self):
         if not self.cuda:
-            for xb, yb in self.source:
-                yield xb, yb, None
+            for xb, yb, ng in self.source:
+                yield xb, yb, None, ng
             return
         q: queue.Queue = queue.Queue(maxsize=self.depth)
         stop = threading.Event()
@@ -178,7 +180,7 @@ class _Prefetcher:
         def worker():
             torch.cuda.set_device(self.device)
             try:
-                for i, (xb, yb) in enumerate(self.source):
+                for i, (xb, yb, ng) in enumerate(self.source):
                     if stop.is_set():
                         return
                     slot = i % (self.depth + 2)
@@ -193,7 +195,7 @@ class _Prefetcher:
                         ev.record(self.copy_stream)
                     self.h2d_bytes += xp.numel() * xp.element_size() + \
                         (yp.numel() * yp.element_size() if yp is not None else 0)
-                    q.put((xd, yd, ev))
+                    q.put((xd, yd, ev, ng))
                 q.put(None)
             except BaseException as e:  # surface loader errors in the training thread
                 q.put(e)
@@ -467,11 +469,12 @@ class Model(nn.Module):
         return logs
 
     # -- one training step --------------------------------------------------------------------
-    def _train_step(self, xb, yb):
+    def _train_step(self, xb, yb, global_batch=None):
         eng = self._engine
         eng.begin_step()
         out = self.call(xb, training=True)
-        global_batch = out.shape[0] * eng.world
+        if global_batch is None:
+            global_batch = out.shape[0] * eng.world
         loss, fused = self._loss_and_metrics(out, yb, global_batch, eng.comm.aux)
         self._last_fused = fused
         loss.backward()
@@ -482,20 +485,20 @@ class Model(nn.Module):
             return False
         return os.environ.get("TFC_CUDA_GRAPH", "1") != "0"
 
-    def _run_step(self, xb, yb):
+    def _run_step(self, xb, yb, global_batch=None):
         """Eager for the first steps (and for odd shapes), then CUDA-graph replay."""
         if not self._graph_enabled():
-            return self._train_step(xb, yb)
+            return self._train_step(xb, yb, global_batch)
         g = self._graph
-        key = (tuple(xb.shape), xb.dtype, tuple(yb.shape), yb.dtype)
+        key = (tuple(xb.shape), xb.dtype, tuple(yb.shape), yb.dtype, global_batch)
         if g is None or g["key"] != key:
             if g is not None and g.get("frozen"):
-                return self._train_step(xb, yb)     # e.g. the short last batch of an epoch
+                return self._train_step(xb, yb, global_batch)   # e.g. the short last batch
             self._graph = g = {"key": key, "warm": 0, "graph": None}
         if g["graph"] is None:
             g["warm"] += 1
             if g["warm"] <= int(os.environ.get("TFC_GRAPH_WARMUP", "3")):
-                return self._train_step(xb, yb)
+                return self._train_step(xb, yb, global_batch)
             g["x"] = xb.clone()
             g["y"] = yb.clone()
             launches0 = ops.kernel_launches()
@@ -503,14 +506,14 @@ class Model(nn.Module):
             graph = torch.cuda.CUDAGraph()
             try:
                 with torch.cuda.graph(graph, capture_error_mode="thread_local"):
-                    g["out"] = self._train_step(g["x"], g["y"])
+                    g["out"] = self._train_step(g["x"], g["y"], global_batch)
             except Exception as e:  # capture refused: stay eager, say so once
                 import warnings
                 warnings.warn(f"cloud_b200: CUDA graph capture failed ({e}); running eagerly")
                 self._graph_ok = False
                 self._graph = None
                 torch.cuda.synchronize(self.device)
-                return self._train_step(xb, yb)
+                return self._train_step(xb, yb, global_batch)
             g["graph"] = graph
             g["frozen"] = True
             g["launches_per_step"] = ops.kernel_launches() - launches0
@@ -571,14 +574,14 @@ class Model(nn.Module):
             pending = None           # (step index, device tensor of reduced aux, event)
             pf = _Prefetcher(source, self.device)
             step = -1
-            for step, (xd, yd, ev) in enumerate(pf):
+            for step, (xd, yd, ev, n_global) in enumerate(pf):
                 if batch_logs:
                     cbl.call("on_train_batch_begin", step, {})
                 if ev is not None:
                     torch.cuda.current_stream(self.device).wait_event(ev)
                 xi = self._to_internal(xd)
                 yi = yd.to(self.device) if yd is not None else None
-                red = self._run_step(xi, yi)
+                red = self._run_step(xi, yi, n_global)
                 self.optimizer.iterations += 1
                 if self.optimizer._schedule is not None:
                     eng.set_lr(self.optimizer.current_lr())
@@ -648,7 +651,7 @@ class Model(nn.Module):
         aux = torch.zeros(max(n_aux, 8), dtype=torch.float32, device=self.device)
         fused = False
         with torch.no_grad():
-            for xd, yd, ev in _Prefetcher(source, self.device):
+            for xd, yd, ev, _ng in _Prefetcher(source, self.device):
                 if ev is not None:
                     torch.cuda.current_stream(self.device).wait_event(ev)
                 out = self.call(self._to_internal(xd), training=False)

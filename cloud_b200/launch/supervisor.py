@@ -1,0 +1,147 @@
+"""Per-job supervisor process: ``python -m cloud_b200.launch.supervisor <job_id>``.
+
+Spawns one rank per planned replica (one process per GPU), each with
+``RANK / WORLD_SIZE / LOCAL_RANK / MASTER_ADDR / MASTER_PORT / TF_CONFIG / TFC_RANK_IN_TASK`` and the
+job's GPU subset in ``CUDA_VISIBLE_DEVICES``; tees every rank's stdout+stderr to
+``logs/rank<r>.log``; kills the whole group as soon as one rank fails and records the failing rank
+with the tail of its log; honours ``TFC_JOB_TIMEOUT``.  This is what AI Platform Training did for
+the reference after ``jobs.create`` (deploy.py:82-88); failure detection is new.
+"""
+from __future__ import annotations
+
+import os
+import signal
+import socket
+import subprocess
+import sys
+import time
+
+from . import registry
+
+
+def _free_port() -> int:
+    with socket.socket(socket.AF_INET, socket.SOCK_STREAM) as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _tail(path: str, n: int = 30) -> str:
+    try:
+        with open(path, "rb") as f:
+            f.seek(0, os.SEEK_END)
+            size = f.tell()
+            f.seek(max(0, size - 8192))
+            return "\n".join(f.read().decode(errors="replace").splitlines()[-n:])
+    except OSError:
+        return ""
+
+
+def run_job(job_id: str) -> int:
+    spec = registry.get(job_id)
+    jdir = registry.job_dir(job_id)
+    plan = spec["plan"]
+    image = spec["image"]
+    workdir = image["workdir"]
+    cmd = [spec.get("python") or sys.executable] + image["entrypoint"][1:] + list(spec.get("args") or [])
+    port = _free_port()
+    procs = []
+    logs = []
+    base_env = dict(os.environ)
+    base_env.update(spec.get("env") or {})
+    base_env["MASTER_ADDR"] = "127.0.0.1"
+    base_env["MASTER_PORT"] = str(port)
+    base_env["WORLD_SIZE"] = str(plan["world_size"])
+    base_env["TF_KERAS_RUNNING_REMOTELY"] = "1"
+    base_env["TFC_JOB_ID"] = job_id
+    base_env["TFC_JOB_DIR"] = jdir
+    base_env["PYTHONUNBUFFERED"] = "1"
+    repo_root = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    base_env["PYTHONPATH"] = os.pathsep.join([repo_root, workdir, base_env.get("PYTHONPATH", "")])
+    if plan["uses_gpu"]:
+        base_env["CUDA_VISIBLE_DEVICES"] = ",".join(str(g) for g in plan["gpu_ids"])
+    else:
+        base_env["CUDA_VISIBLE_DEVICES"] = ""
+    registry.set_status(job_id, "RUNNING", supervisor_pid=os.getpid(), master_port=port)
+    for r in plan["ranks"]:
+        env = dict(base_env)
+        env["RANK"] = str(r["rank"])
+        env["LOCAL_RANK"] = str(r["local_rank"])
+        env["TF_CONFIG"] = r["tf_config"]
+        env["TFC_RANK_IN_TASK"] = str(r["rank_in_task"])
+        env["TFC_TASK_TYPE"] = r["task_type"]
+        log_path = os.path.join(jdir, "logs", "rank{}.log".format(r["rank"]))
+        fh = open(log_path, "ab", buffering=0)
+        logs.append((fh, log_path))
+        procs.append(subprocess.Popen(cmd, cwd=workdir, env=env, stdout=fh, stderr=subprocess.STDOUT,
+                                      start_new_session=True))
+    timeout = float(os.environ.get("TFC_JOB_TIMEOUT", "0") or 0)
+    t0 = time.time()
+    failed = None
+    cancelled = {"flag": False}
+
+    def _on_term(signum, frame):
+        cancelled["flag"] = True
+    signal.signal(signal.SIGTERM, _on_term)
+    signal.signal(signal.SIGINT, _on_term)
+
+    while True:
+        alive = 0
+        for i, p in enumerate(procs):
+            rc = p.poll()
+            if rc is None:
+                alive += 1
+            elif rc != 0 and failed is None:
+                failed = (i, rc)
+        if failed is not None or alive == 0 or cancelled["flag"]:
+            break
+        if timeout and time.time() - t0 > timeout:
+            failed = (-1, "timeout after {}s".format(timeout))
+            break
+        time.sleep(0.1)
+
+    if failed is not None or cancelled["flag"]:
+        for p in procs:
+            if p.poll() is None:
+                try:
+                    os.killpg(p.pid, signal.SIGTERM)
+                except (ProcessLookupError, PermissionError):
+                    pass
+        deadline = time.time() + 5
+        for p in procs:
+            try:
+                p.wait(timeout=max(0.1, deadline - time.time()))
+            except subprocess.TimeoutExpired:
+                try:
+                    os.killpg(p.pid, signal.SIGKILL)
+                except (ProcessLookupError, PermissionError):
+                    pass
+    for fh, _ in logs:
+        fh.close()
+    exit_codes = [p.poll() for p in procs]
+    if cancelled["flag"] and failed is None:
+        registry.set_status(job_id, "CANCELLED", exit_codes=exit_codes, seconds=time.time() - t0)
+        return 130
+    if failed is not None:
+        rank, rc = failed
+        tail = _tail(logs[rank][1]) if rank >= 0 else ""
+        registry.set_status(job_id, "FAILED", failed_rank=rank, exit_code=rc, exit_codes=exit_codes,
+                            error_tail=tail, seconds=time.time() - t0)
+        return 1
+    registry.set_status(job_id, "SUCCEEDED", exit_codes=exit_codes, seconds=time.time() - t0)
+    return 0
+
+
+def main(argv=None) -> int:
+    argv = argv if argv is not None else sys.argv[1:]
+    if len(argv) != 1:
+        print("usage: python -m cloud_b200.launch.supervisor <job_id>", file=sys.stderr)
+        return 2
+    try:
+        return run_job(argv[0])
+    except Exception as e:  # the supervisor itself must never leave a job RUNNING forever
+        registry.set_status(argv[0], "FAILED", error_tail="supervisor error: {!r}".format(e))
+        raise
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -41,10 +41,12 @@ def launches() -> int:
 
 
 class Communicator:
-    def __init__(self, device: torch.device, group=None, backend: str | None = None):
+    def __init__(self, device: torch.device, group=None, backend: str | None = None,
+                 single: bool = False):
         self.device = device
         self.group = group
-        self.initialized = dist.is_available() and dist.is_initialized()
+        # `single`: a one-replica strategy inside a process that also belongs to a process group
+        self.initialized = (not single) and dist.is_available() and dist.is_initialized()
         self.rank = dist.get_rank(group) if self.initialized else 0
         self.world = dist.get_world_size(group) if self.initialized else 1
         env = os.environ.get("TFC_COMM_BACKEND")
