@@ -22,6 +22,8 @@
 // Reference parity: K9/K10/K11 of SURVEY.md section 2.5 - the all-reduce TensorFlow runs for
 // MirroredStrategy()/MultiWorkerMirroredStrategy() (core/preprocess.py:139-143) plus the
 // per-variable ResourceApplyAdam launches that follow it.
+#include <stdlib.h>
+
 #include "optim.cuh"
 
 namespace cb2 {
@@ -97,68 +99,139 @@ struct FusedArgs {
   float* aux_out;
 };
 
-template <int ALGO, int OPT, typename GT, typename PT>
+// Runtime optimizer dispatch (warp-uniform switch) keeps the number of kernel instantiations at
+// schedule x dtypes x world instead of multiplying by six optimizers.
+__device__ __forceinline__ Vec8 update8_dyn(int opt, const Vec8& p, const Vec8& g, float* s1,
+                                            float* s2, size_t si, const Hyper& h) {
+  switch (opt) {
+    case CB2_OPT_ADAM_KERAS: return update8<CB2_OPT_ADAM_KERAS>(p, g, s1, s2, si, h);
+    case CB2_OPT_ADAM_TORCH: return update8<CB2_OPT_ADAM_TORCH>(p, g, s1, s2, si, h);
+    case CB2_OPT_ADAMW: return update8<CB2_OPT_ADAMW>(p, g, s1, s2, si, h);
+    case CB2_OPT_SGD: return update8<CB2_OPT_SGD>(p, g, s1, s2, si, h);
+    case CB2_OPT_RMSPROP: return update8<CB2_OPT_RMSPROP>(p, g, s1, s2, si, h);
+    default: return update8<CB2_OPT_NONE>(p, g, s1, s2, si, h);
+  }
+}
+
+// 8 elements as raw 16-byte chunks: loads are issued back to back and only unpacked afterwards,
+// so a thread keeps U x W requests in flight across the ~2 us NVLink round trip.
+template <typename GT> struct Raw8 { uint4 q[sizeof(GT) == 4 ? 2 : 1]; };
+
+template <typename GT>
+__device__ __forceinline__ Raw8<GT> ld_raw8(const void* base, size_t i) {
+  Raw8<GT> r;
+  const GT* p = reinterpret_cast<const GT*>(base) + i;
+  r.q[0] = ld_stream_v4(p);
+  if (sizeof(GT) == 4) r.q[sizeof(GT) == 4 ? 1 : 0] = ld_stream_v4(reinterpret_cast<const float*>(p) + 4);
+  return r;
+}
+template <typename GT>
+__device__ __forceinline__ Raw8<GT> mc_ld_raw8(const void* mc, size_t i) {
+  Raw8<GT> r;
+  const GT* p = reinterpret_cast<const GT*>(mc) + i;
+  if (sizeof(GT) == 4) {
+    r.q[0] = mc_ld_reduce_f32x4(p);
+    r.q[sizeof(GT) == 4 ? 1 : 0] = mc_ld_reduce_f32x4(reinterpret_cast<const float*>(p) + 4);
+  } else {
+    r.q[0] = mc_ld_reduce_bf16x8(p);
+  }
+  return r;
+}
+template <typename GT>
+__device__ __forceinline__ Vec8 unpack_raw8(const Raw8<GT>& r) {
+  if (sizeof(GT) == 4) {
+    Vec8 v;
+    const uint4 a = r.q[0], b = r.q[sizeof(GT) == 4 ? 1 : 0];
+    v.v[0] = __uint_as_float(a.x); v.v[1] = __uint_as_float(a.y);
+    v.v[2] = __uint_as_float(a.z); v.v[3] = __uint_as_float(a.w);
+    v.v[4] = __uint_as_float(b.x); v.v[5] = __uint_as_float(b.y);
+    v.v[6] = __uint_as_float(b.z); v.v[7] = __uint_as_float(b.w);
+    return v;
+  }
+  return unpack8_bf16(r.q[0]);
+}
+
+// WT = compile-time world size (2, 4, 8) or 0 for "any" (runtime loop, one vector per iteration).
+template <int ALGO, typename GT, typename PT, int WT>
 __global__ void __launch_bounds__(512)
-comm_fused_kernel(const DevCtx c, const FusedArgs a) {
+comm_fused_kernel(const DevCtx c, const FusedArgs a, const int opt) {
   const uint32_t base = c.epochs[blockIdx.x];
   const Hyper h = load_hyper(a.hyper);
-  const int W = c.world, R = c.rank;
+  const int W = WT ? WT : c.world;
+  const int R = c.rank;
   const size_t tid = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
   const size_t nthreads = static_cast<size_t>(gridDim.x) * blockDim.x;
+  constexpr int Q = sizeof(GT) == 4 ? 2 : 1;
+  constexpr int WU = WT ? WT : 1;
+  constexpr int U = ALGO == CB2_ALGO_NVLS ? 8 / Q : (WT ? (16 / (WT * Q) > 0 ? 16 / (WT * Q) : 1) : 1);
 
   // 1. every rank's gradients (and aux scalars) for this bucket are final
   if (W > 1) peer_barrier(c, base + 1);
 
-  if (ALGO == CB2_ALGO_ONESHOT) {
-    const size_t nvec = a.len / 8;
-    for (size_t vi = tid; vi < nvec; vi += nthreads) {
-      const size_t i = a.off + vi * 8;
-      Vec8 g = load8<GT>(reinterpret_cast<const GT*>(c.grad[0]), i);
-      for (int p = 1; p < W; ++p) {
-        const Vec8 o = load8<GT>(reinterpret_cast<const GT*>(c.grad[p]), i);
+  const bool oneshot = ALGO == CB2_ALGO_ONESHOT;
+  const size_t span = oneshot ? a.len : a.len / W;     // elements this rank reduces
+  const size_t nvec = span / 8;
+  const size_t ibase = oneshot ? a.off : a.off + static_cast<size_t>(R) * span;
+
+  for (size_t v0 = tid; v0 < nvec; v0 += nthreads * U) {
+    Raw8<GT> raw[U][WU];
+    // ---- issue every load of this batch ----------------------------------------------------
 #pragma unroll
-        for (int j = 0; j < 8; ++j) g.v[j] += o.v[j];
-      }
-      const size_t si = a.state_off + vi * 8;
-      Vec8 pin;
-      if (OPT != CB2_OPT_NONE) {
-        if (a.master) pin = load8_f32(a.master + si);
-        else pin = load8<PT>(reinterpret_cast<const PT*>(c.param[R]), i);
-      }
-      const Vec8 pn = update8<OPT>(pin, g, a.s1, a.s2, si, h);
-      if (OPT != CB2_OPT_NONE && a.master) store8_f32(a.master + si, pn);
-      store8<PT>(reinterpret_cast<PT*>(c.param[R]), i, pn);
-    }
-  } else {
-    const size_t shard = a.len / W;
-    const size_t nvec = shard / 8;
-    const size_t sbase = a.off + static_cast<size_t>(R) * shard;
-    for (size_t vi = tid; vi < nvec; vi += nthreads) {
-      const size_t i = sbase + vi * 8;
-      Vec8 g;
-      if (ALGO == CB2_ALGO_NVLS) {
-        g = mc_reduce8<GT>(c.mc_grad, i);
-      } else {
-        // start with my own arena, then walk the peers starting at rank+1 so the W readers of a
-        // step hit W different source GPUs
-        g = load8<GT>(reinterpret_cast<const GT*>(c.grad[R]), i);
-        for (int d = 1; d < W; ++d) {
-          int p = R + d;
-          if (p >= W) p -= W;
-          const Vec8 o = load8<GT>(reinterpret_cast<const GT*>(c.grad[p]), i);
+    for (int u = 0; u < U; ++u) {
+      const size_t v = v0 + static_cast<size_t>(u) * nthreads;
+      if (v < nvec) {
+        const size_t i = ibase + v * 8;
+        if (ALGO == CB2_ALGO_NVLS) {
+          raw[u][0] = mc_ld_raw8<GT>(c.mc_grad, i);
+        } else if (WT) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) g.v[j] += o.v[j];
+          for (int d = 0; d < WU; ++d) {
+            // one-shot: fixed rank order => bitwise identical sums on every replica;
+            // two-shot: start at my own arena and walk the ring so W readers hit W sources
+            const int p = oneshot ? d : ((R + d) % WU);
+            raw[u][d] = ld_raw8<GT>(c.grad[p], i);
+          }
+        } else {
+          raw[u][0] = ld_raw8<GT>(c.grad[oneshot ? 0 : R], i);
         }
       }
-      const size_t si = a.state_off + vi * 8;
+    }
+    // ---- reduce, update, publish --------------------------------------------------------------
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t v = v0 + static_cast<size_t>(u) * nthreads;
+      if (v >= nvec) continue;
+      const size_t i = ibase + v * 8;
+      Vec8 g = unpack_raw8<GT>(raw[u][0]);
+      if (ALGO != CB2_ALGO_NVLS) {
+        if (WT) {
+#pragma unroll
+          for (int d = 1; d < WU; ++d) {
+            const Vec8 o = unpack_raw8<GT>(raw[u][d]);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) g.v[j] += o.v[j];
+          }
+        } else {
+          for (int d = 1; d < W; ++d) {
+            int p = oneshot ? d : R + d;
+            if (p >= W) p -= W;
+            const Vec8 o = load8<GT>(reinterpret_cast<const GT*>(c.grad[p]), i);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) g.v[j] += o.v[j];
+          }
+        }
+      }
+      const size_t si = a.state_off + v * 8;
       Vec8 pin;
-      if (OPT != CB2_OPT_NONE) {
+      if (opt != CB2_OPT_NONE) {
         if (a.master) pin = load8_f32(a.master + si);
         else pin = load8<PT>(reinterpret_cast<const PT*>(c.param[R]), i);
       }
-      const Vec8 pn = update8<OPT>(pin, g, a.s1, a.s2, si, h);
-      if (OPT != CB2_OPT_NONE && a.master) store8_f32(a.master + si, pn);
-      if (ALGO == CB2_ALGO_NVLS) {
+      const Vec8 pn = update8_dyn(opt, pin, g, a.s1, a.s2, si, h);
+      if (opt != CB2_OPT_NONE && a.master) store8_f32(a.master + si, pn);
+      if (oneshot) {
+        store8<PT>(reinterpret_cast<PT*>(c.param[R]), i, pn);
+      } else if (ALGO == CB2_ALGO_NVLS) {
         mc_store8<PT>(c.mc_param, i, pn);
       } else {
         for (int d = 0; d < W; ++d) {
@@ -187,16 +260,10 @@ comm_fused_kernel(const DevCtx c, const FusedArgs a) {
     // Block b zeroes exactly what the b-th blocks of all ranks have read, which is what the
     // barrier above covered: the b-th stripe of every shard (or of the whole range, one-shot).
     GT* mine = reinterpret_cast<GT*>(c.grad[R]);
-    if (ALGO == CB2_ALGO_ONESHOT) {
-      const size_t nvec = a.len / 8;
-      for (size_t vi = tid; vi < nvec; vi += nthreads) zero8<GT>(mine, a.off + vi * 8);
-    } else {
-      const size_t shard = a.len / W;
-      const size_t nvec = shard / 8;
-      for (int s = 0; s < W; ++s)
-        for (size_t vi = tid; vi < nvec; vi += nthreads)
-          zero8<GT>(mine, a.off + static_cast<size_t>(s) * shard + vi * 8);
-    }
+    const int shards = oneshot ? 1 : W;
+    for (int sidx = 0; sidx < shards; ++sidx)
+      for (size_t v = tid; v < nvec; v += nthreads)
+        zero8<GT>(mine, a.off + static_cast<size_t>(sidx) * span + v * 8);
   }
   if (blockIdx.x == 0 && a.zero_grads && static_cast<int>(threadIdx.x) < a.aux_len)
     aux_of(c.pad[R])[threadIdx.x] = 0.f;
@@ -254,10 +321,10 @@ static int to_dev_ctx(const cb2_comm_ctx* ctx, DevCtx* d) {
   return 0;
 }
 
-template <int ALGO, int OPT>
-static int launch_fused(const DevCtx& d, const FusedArgs& a, int gdt, int pdt, int blocks,
+template <int ALGO, int WT>
+static int launch_fused(const DevCtx& d, const FusedArgs& a, int opt, int gdt, int pdt, int blocks,
                         cudaStream_t st) {
-#define CB2_LAUNCH(GT, PT) comm_fused_kernel<ALGO, OPT, GT, PT><<<blocks, 512, 0, st>>>(d, a)
+#define CB2_LAUNCH(GT, PT) comm_fused_kernel<ALGO, GT, PT, WT><<<blocks, 512, 0, st>>>(d, a, opt)
   if (gdt == CB2_DTYPE_F32 && pdt == CB2_DTYPE_F32) CB2_LAUNCH(float, float);
   else if (gdt == CB2_DTYPE_BF16 && pdt == CB2_DTYPE_BF16) CB2_LAUNCH(__nv_bfloat16, __nv_bfloat16);
   else if (gdt == CB2_DTYPE_F32 && pdt == CB2_DTYPE_BF16) CB2_LAUNCH(float, __nv_bfloat16);
@@ -267,18 +334,30 @@ static int launch_fused(const DevCtx& d, const FusedArgs& a, int gdt, int pdt, i
 }
 
 template <int ALGO>
-static int dispatch_opt(int opt, const DevCtx& d, const FusedArgs& a, int gdt, int pdt, int blocks,
-                        cudaStream_t st) {
-  switch (opt) {
-    case CB2_OPT_NONE: return launch_fused<ALGO, CB2_OPT_NONE>(d, a, gdt, pdt, blocks, st);
-    case CB2_OPT_ADAM_KERAS: return launch_fused<ALGO, CB2_OPT_ADAM_KERAS>(d, a, gdt, pdt, blocks, st);
-    case CB2_OPT_ADAM_TORCH: return launch_fused<ALGO, CB2_OPT_ADAM_TORCH>(d, a, gdt, pdt, blocks, st);
-    case CB2_OPT_ADAMW: return launch_fused<ALGO, CB2_OPT_ADAMW>(d, a, gdt, pdt, blocks, st);
-    case CB2_OPT_SGD: return launch_fused<ALGO, CB2_OPT_SGD>(d, a, gdt, pdt, blocks, st);
-    case CB2_OPT_RMSPROP: return launch_fused<ALGO, CB2_OPT_RMSPROP>(d, a, gdt, pdt, blocks, st);
+static int dispatch_world(int opt, const DevCtx& d, const FusedArgs& a, int gdt, int pdt, int blocks,
+                          cudaStream_t st) {
+  if (opt < CB2_OPT_NONE || opt > CB2_OPT_RMSPROP) {
+    set_last_error("comm_fused: unknown optimizer %d", opt);
+    return CB2_ERR_ARG;
   }
-  set_last_error("comm_fused: unknown optimizer %d", opt);
-  return CB2_ERR_ARG;
+  if (ALGO == CB2_ALGO_NVLS) return launch_fused<ALGO, 0>(d, a, opt, gdt, pdt, blocks, st);
+  switch (d.world) {
+    case 2: return launch_fused<ALGO, 2>(d, a, opt, gdt, pdt, blocks, st);
+    case 4: return launch_fused<ALGO, 4>(d, a, opt, gdt, pdt, blocks, st);
+    case 8: return launch_fused<ALGO, 8>(d, a, opt, gdt, pdt, blocks, st);
+    default: return launch_fused<ALGO, 0>(d, a, opt, gdt, pdt, blocks, st);
+  }
+}
+
+static int max_blocks_env() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("TFC_COMM_MAX_BLOCKS");
+    v = e ? atoi(e) : 0;
+    if (v < 0) v = 0;
+    if (v > CB2_COMM_MAX_BLOCKS) v = CB2_COMM_MAX_BLOCKS;
+  }
+  return v;
 }
 
 }  // namespace cb2
@@ -315,7 +394,8 @@ extern "C" int cb2_comm_fused(const cb2_comm_ctx* ctx, int algo, int opt, int gr
     // never more than the work: one 8-element vector per thread minimum
     const size_t work = (algo == CB2_ALGO_ONESHOT ? len : len / d.world) / 8;
     size_t want = (work + 511) / 512;
-    const size_t cap = algo == CB2_ALGO_NVLS ? 32 : 64;
+    size_t cap = algo == CB2_ALGO_NVLS ? 32 : 64;
+    if (max_blocks_env()) cap = max_blocks_env();
     if (want > cap) want = cap;
     if (want < 1) want = 1;
     blocks = static_cast<int>(want);
@@ -327,9 +407,9 @@ extern "C" int cb2_comm_fused(const cb2_comm_ctx* ctx, int algo, int opt, int gr
   a.zero_grads = zero_grads; a.aux_len = aux_len; a.aux_out = aux_out;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   switch (algo) {
-    case CB2_ALGO_ONESHOT: return dispatch_opt<CB2_ALGO_ONESHOT>(opt, d, a, grad_dtype, param_dtype, blocks, st);
-    case CB2_ALGO_TWOSHOT: return dispatch_opt<CB2_ALGO_TWOSHOT>(opt, d, a, grad_dtype, param_dtype, blocks, st);
-    case CB2_ALGO_NVLS: return dispatch_opt<CB2_ALGO_NVLS>(opt, d, a, grad_dtype, param_dtype, blocks, st);
+    case CB2_ALGO_ONESHOT: return dispatch_world<CB2_ALGO_ONESHOT>(opt, d, a, grad_dtype, param_dtype, blocks, st);
+    case CB2_ALGO_TWOSHOT: return dispatch_world<CB2_ALGO_TWOSHOT>(opt, d, a, grad_dtype, param_dtype, blocks, st);
+    case CB2_ALGO_NVLS: return dispatch_world<CB2_ALGO_NVLS>(opt, d, a, grad_dtype, param_dtype, blocks, st);
   }
   set_last_error("comm_fused: unknown algorithm %d", algo);
   return CB2_ERR_ARG;
