@@ -99,145 +99,171 @@ struct FusedArgs {
   float* aux_out;
 };
 
+// ---------------------------------------------------------------------------------------------
+// Fused all-reduce + optimizer.  The unit of work is ONE 16-byte chunk (4 fp32 or 8 bf16): every
+// load/store instruction of a warp then covers 512 contiguous bytes.  (A first version moved 8
+// fp32 = two half-used 32-byte sectors per thread; peer memory bypasses the local L2, so each half
+// sector crossed NVLink twice and fp32 bus bandwidth stalled at ~290 GB/s.)
+// ---------------------------------------------------------------------------------------------
+template <int N> struct VecN { float v[N]; };
+
+template <typename T> __device__ __forceinline__ VecN<16 / sizeof(T)> unpack16(const uint4& w);
+template <> __device__ __forceinline__ VecN<4> unpack16<float>(const uint4& w) {
+  VecN<4> r;
+  r.v[0] = __uint_as_float(w.x); r.v[1] = __uint_as_float(w.y);
+  r.v[2] = __uint_as_float(w.z); r.v[3] = __uint_as_float(w.w);
+  return r;
+}
+template <> __device__ __forceinline__ VecN<8> unpack16<__nv_bfloat16>(const uint4& w) {
+  VecN<8> r;
+  r.v[0] = bf16_lo(w.x); r.v[1] = bf16_hi(w.x); r.v[2] = bf16_lo(w.y); r.v[3] = bf16_hi(w.y);
+  r.v[4] = bf16_lo(w.z); r.v[5] = bf16_hi(w.z); r.v[6] = bf16_lo(w.w); r.v[7] = bf16_hi(w.w);
+  return r;
+}
+__device__ __forceinline__ uint4 pack16(const VecN<4>& r) {
+  return make_uint4(__float_as_uint(r.v[0]), __float_as_uint(r.v[1]), __float_as_uint(r.v[2]),
+                    __float_as_uint(r.v[3]));
+}
+__device__ __forceinline__ uint4 pack16(const VecN<8>& r) {
+  return make_uint4(pack_bf16(r.v[0], r.v[1]), pack_bf16(r.v[2], r.v[3]), pack_bf16(r.v[4], r.v[5]),
+                    pack_bf16(r.v[6], r.v[7]));
+}
+template <int N> __device__ __forceinline__ VecN<N> load_state(const float* p) {
+  VecN<N> r;
+#pragma unroll
+  for (int k = 0; k < N; k += 4) {
+    const float4 a = *reinterpret_cast<const float4*>(p + k);
+    r.v[k] = a.x; r.v[k + 1] = a.y; r.v[k + 2] = a.z; r.v[k + 3] = a.w;
+  }
+  return r;
+}
+template <int N> __device__ __forceinline__ void store_state(float* p, const VecN<N>& r) {
+#pragma unroll
+  for (int k = 0; k < N; k += 4)
+    *reinterpret_cast<float4*>(p + k) = make_float4(r.v[k], r.v[k + 1], r.v[k + 2], r.v[k + 3]);
+}
+
+template <int OPT, int N>
+__device__ __forceinline__ VecN<N> updateN(const VecN<N>& p, const VecN<N>& g, float* s1, float* s2,
+                                           size_t si, const Hyper& h) {
+  VecN<N> a, b, out;
+  if (OptTraits<OPT>::kS1) a = load_state<N>(s1 + si);
+  if (OptTraits<OPT>::kS2) b = load_state<N>(s2 + si);
+#pragma unroll
+  for (int j = 0; j < N; ++j) out.v[j] = opt_update<OPT>(p.v[j], g.v[j], a.v[j], b.v[j], h);
+  if (OptTraits<OPT>::kS1) store_state<N>(s1 + si, a);
+  if (OptTraits<OPT>::kS2) store_state<N>(s2 + si, b);
+  return out;
+}
+
 // Runtime optimizer dispatch (warp-uniform switch) keeps the number of kernel instantiations at
-// schedule x dtypes x world instead of multiplying by six optimizers.
-__device__ __forceinline__ Vec8 update8_dyn(int opt, const Vec8& p, const Vec8& g, float* s1,
-                                            float* s2, size_t si, const Hyper& h) {
+// schedule x dtype x world instead of multiplying by six optimizers.
+template <int N>
+__device__ __forceinline__ VecN<N> updateN_dyn(int opt, const VecN<N>& p, const VecN<N>& g,
+                                               float* s1, float* s2, size_t si, const Hyper& h) {
   switch (opt) {
-    case CB2_OPT_ADAM_KERAS: return update8<CB2_OPT_ADAM_KERAS>(p, g, s1, s2, si, h);
-    case CB2_OPT_ADAM_TORCH: return update8<CB2_OPT_ADAM_TORCH>(p, g, s1, s2, si, h);
-    case CB2_OPT_ADAMW: return update8<CB2_OPT_ADAMW>(p, g, s1, s2, si, h);
-    case CB2_OPT_SGD: return update8<CB2_OPT_SGD>(p, g, s1, s2, si, h);
-    case CB2_OPT_RMSPROP: return update8<CB2_OPT_RMSPROP>(p, g, s1, s2, si, h);
-    default: return update8<CB2_OPT_NONE>(p, g, s1, s2, si, h);
+    case CB2_OPT_ADAM_KERAS: return updateN<CB2_OPT_ADAM_KERAS, N>(p, g, s1, s2, si, h);
+    case CB2_OPT_ADAM_TORCH: return updateN<CB2_OPT_ADAM_TORCH, N>(p, g, s1, s2, si, h);
+    case CB2_OPT_ADAMW: return updateN<CB2_OPT_ADAMW, N>(p, g, s1, s2, si, h);
+    case CB2_OPT_SGD: return updateN<CB2_OPT_SGD, N>(p, g, s1, s2, si, h);
+    case CB2_OPT_RMSPROP: return updateN<CB2_OPT_RMSPROP, N>(p, g, s1, s2, si, h);
+    default: return updateN<CB2_OPT_NONE, N>(p, g, s1, s2, si, h);
   }
 }
 
-// 8 elements as raw 16-byte chunks: loads are issued back to back and only unpacked afterwards,
-// so a thread keeps U x W requests in flight across the ~2 us NVLink round trip.
-template <typename GT> struct Raw8 { uint4 q[sizeof(GT) == 4 ? 2 : 1]; };
+template <typename T> __device__ __forceinline__ uint4 mc_ld16(const void* mc);
+template <> __device__ __forceinline__ uint4 mc_ld16<float>(const void* mc) { return mc_ld_reduce_f32x4(mc); }
+template <> __device__ __forceinline__ uint4 mc_ld16<__nv_bfloat16>(const void* mc) { return mc_ld_reduce_bf16x8(mc); }
 
-template <typename GT>
-__device__ __forceinline__ Raw8<GT> ld_raw8(const void* base, size_t i) {
-  Raw8<GT> r;
-  const GT* p = reinterpret_cast<const GT*>(base) + i;
-  r.q[0] = ld_stream_v4(p);
-  if (sizeof(GT) == 4) r.q[sizeof(GT) == 4 ? 1 : 0] = ld_stream_v4(reinterpret_cast<const float*>(p) + 4);
-  return r;
-}
-template <typename GT>
-__device__ __forceinline__ Raw8<GT> mc_ld_raw8(const void* mc, size_t i) {
-  Raw8<GT> r;
-  const GT* p = reinterpret_cast<const GT*>(mc) + i;
-  if (sizeof(GT) == 4) {
-    r.q[0] = mc_ld_reduce_f32x4(p);
-    r.q[sizeof(GT) == 4 ? 1 : 0] = mc_ld_reduce_f32x4(reinterpret_cast<const float*>(p) + 4);
-  } else {
-    r.q[0] = mc_ld_reduce_bf16x8(p);
-  }
-  return r;
-}
-template <typename GT>
-__device__ __forceinline__ Vec8 unpack_raw8(const Raw8<GT>& r) {
-  if (sizeof(GT) == 4) {
-    Vec8 v;
-    const uint4 a = r.q[0], b = r.q[sizeof(GT) == 4 ? 1 : 0];
-    v.v[0] = __uint_as_float(a.x); v.v[1] = __uint_as_float(a.y);
-    v.v[2] = __uint_as_float(a.z); v.v[3] = __uint_as_float(a.w);
-    v.v[4] = __uint_as_float(b.x); v.v[5] = __uint_as_float(b.y);
-    v.v[6] = __uint_as_float(b.z); v.v[7] = __uint_as_float(b.w);
-    return v;
-  }
-  return unpack8_bf16(r.q[0]);
-}
-
-// WT = compile-time world size (2, 4, 8) or 0 for "any" (runtime loop, one vector per iteration).
-template <int ALGO, typename GT, typename PT, int WT>
+// WT = compile-time world size (2, 4, 8) or 0 for "any" (runtime loop, one chunk per iteration).
+// Loads of a batch are all issued before the first use, so a thread keeps U x W 16-byte requests
+// in flight across the ~2 us NVLink round trip.
+template <int ALGO, typename T, int WT>
 __global__ void __launch_bounds__(512)
 comm_fused_kernel(const DevCtx c, const FusedArgs a, const int opt) {
+  constexpr int N = 16 / sizeof(T);
+  constexpr int WU = WT ? WT : 1;
+  constexpr int U = ALGO == CB2_ALGO_NVLS ? 8 : (WT ? (16 / WT > 0 ? 16 / WT : 1) : 1);
   const uint32_t base = c.epochs[blockIdx.x];
   const Hyper h = load_hyper(a.hyper);
   const int W = WT ? WT : c.world;
   const int R = c.rank;
   const size_t tid = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
   const size_t nthreads = static_cast<size_t>(gridDim.x) * blockDim.x;
-  constexpr int Q = sizeof(GT) == 4 ? 2 : 1;
-  constexpr int WU = WT ? WT : 1;
-  constexpr int U = ALGO == CB2_ALGO_NVLS ? 8 / Q : (WT ? (16 / (WT * Q) > 0 ? 16 / (WT * Q) : 1) : 1);
 
   // 1. every rank's gradients (and aux scalars) for this bucket are final
   if (W > 1) peer_barrier(c, base + 1);
 
   const bool oneshot = ALGO == CB2_ALGO_ONESHOT;
   const size_t span = oneshot ? a.len : a.len / W;     // elements this rank reduces
-  const size_t nvec = span / 8;
+  const size_t nvec = span / N;
   const size_t ibase = oneshot ? a.off : a.off + static_cast<size_t>(R) * span;
+  T* const my_param = reinterpret_cast<T*>(c.param[R]);
 
   for (size_t v0 = tid; v0 < nvec; v0 += nthreads * U) {
-    Raw8<GT> raw[U][WU];
-    // ---- issue every load of this batch ----------------------------------------------------
+    uint4 raw[U][WU];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const size_t v = v0 + static_cast<size_t>(u) * nthreads;
       if (v < nvec) {
-        const size_t i = ibase + v * 8;
+        const size_t i = ibase + v * N;
         if (ALGO == CB2_ALGO_NVLS) {
-          raw[u][0] = mc_ld_raw8<GT>(c.mc_grad, i);
+          raw[u][0] = mc_ld16<T>(reinterpret_cast<const T*>(c.mc_grad) + i);
         } else if (WT) {
 #pragma unroll
           for (int d = 0; d < WU; ++d) {
             // one-shot: fixed rank order => bitwise identical sums on every replica;
             // two-shot: start at my own arena and walk the ring so W readers hit W sources
             const int p = oneshot ? d : ((R + d) % WU);
-            raw[u][d] = ld_raw8<GT>(c.grad[p], i);
+            raw[u][d] = ld_stream_v4(reinterpret_cast<const T*>(c.grad[p]) + i);
           }
         } else {
-          raw[u][0] = ld_raw8<GT>(c.grad[oneshot ? 0 : R], i);
+          raw[u][0] = ld_stream_v4(reinterpret_cast<const T*>(c.grad[oneshot ? 0 : R]) + i);
         }
       }
     }
-    // ---- reduce, update, publish --------------------------------------------------------------
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const size_t v = v0 + static_cast<size_t>(u) * nthreads;
       if (v >= nvec) continue;
-      const size_t i = ibase + v * 8;
-      Vec8 g = unpack_raw8<GT>(raw[u][0]);
+      const size_t i = ibase + v * N;
+      VecN<N> g = unpack16<T>(raw[u][0]);
       if (ALGO != CB2_ALGO_NVLS) {
         if (WT) {
 #pragma unroll
           for (int d = 1; d < WU; ++d) {
-            const Vec8 o = unpack_raw8<GT>(raw[u][d]);
+            const VecN<N> o = unpack16<T>(raw[u][d]);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) g.v[j] += o.v[j];
+            for (int j = 0; j < N; ++j) g.v[j] += o.v[j];
           }
         } else {
           for (int d = 1; d < W; ++d) {
             int p = oneshot ? d : R + d;
             if (p >= W) p -= W;
-            const Vec8 o = load8<GT>(reinterpret_cast<const GT*>(c.grad[p]), i);
+            const VecN<N> o = unpack16<T>(ld_stream_v4(reinterpret_cast<const T*>(c.grad[p]) + i));
 #pragma unroll
-            for (int j = 0; j < 8; ++j) g.v[j] += o.v[j];
+            for (int j = 0; j < N; ++j) g.v[j] += o.v[j];
           }
         }
       }
-      const size_t si = a.state_off + v * 8;
-      Vec8 pin;
+      const size_t si = a.state_off + v * N;
+      VecN<N> pin;
       if (opt != CB2_OPT_NONE) {
-        if (a.master) pin = load8_f32(a.master + si);
-        else pin = load8<PT>(reinterpret_cast<const PT*>(c.param[R]), i);
+        if (a.master) pin = load_state<N>(a.master + si);
+        else pin = unpack16<T>(ld_stream_v4(my_param + i));
       }
-      const Vec8 pn = update8_dyn(opt, pin, g, a.s1, a.s2, si, h);
-      if (opt != CB2_OPT_NONE && a.master) store8_f32(a.master + si, pn);
+      const VecN<N> pn = updateN_dyn<N>(opt, pin, g, a.s1, a.s2, si, h);
+      if (opt != CB2_OPT_NONE && a.master) store_state<N>(a.master + si, pn);
+      const uint4 packed = pack16(pn);
       if (oneshot) {
-        store8<PT>(reinterpret_cast<PT*>(c.param[R]), i, pn);
+        st_stream_v4(my_param + i, packed);
       } else if (ALGO == CB2_ALGO_NVLS) {
-        mc_store8<PT>(c.mc_param, i, pn);
+        mc_st_v4(reinterpret_cast<T*>(c.mc_param) + i, packed);
       } else {
         for (int d = 0; d < W; ++d) {
           int p = R + d;
           if (p >= W) p -= W;
-          store8<PT>(reinterpret_cast<PT*>(c.param[p]), i, pn);
+          st_stream_v4(reinterpret_cast<T*>(c.param[p]) + i, packed);
         }
       }
     }
@@ -259,11 +285,12 @@ comm_fused_kernel(const DevCtx c, const FusedArgs a, const int opt) {
   if (a.zero_grads) {
     // Block b zeroes exactly what the b-th blocks of all ranks have read, which is what the
     // barrier above covered: the b-th stripe of every shard (or of the whole range, one-shot).
-    GT* mine = reinterpret_cast<GT*>(c.grad[R]);
+    T* mine = reinterpret_cast<T*>(c.grad[R]);
     const int shards = oneshot ? 1 : W;
+    const uint4 z = make_uint4(0, 0, 0, 0);
     for (int sidx = 0; sidx < shards; ++sidx)
       for (size_t v = tid; v < nvec; v += nthreads)
-        zero8<GT>(mine, a.off + static_cast<size_t>(sidx) * span + v * 8);
+        st_stream_v4(mine + a.off + static_cast<size_t>(sidx) * span + v * N, z);
   }
   if (blockIdx.x == 0 && a.zero_grads && static_cast<int>(threadIdx.x) < a.aux_len)
     aux_of(c.pad[R])[threadIdx.x] = 0.f;
@@ -324,12 +351,12 @@ static int to_dev_ctx(const cb2_comm_ctx* ctx, DevCtx* d) {
 template <int ALGO, int WT>
 static int launch_fused(const DevCtx& d, const FusedArgs& a, int opt, int gdt, int pdt, int blocks,
                         cudaStream_t st) {
-#define CB2_LAUNCH(GT, PT) comm_fused_kernel<ALGO, GT, PT, WT><<<blocks, 512, 0, st>>>(d, a, opt)
-  if (gdt == CB2_DTYPE_F32 && pdt == CB2_DTYPE_F32) CB2_LAUNCH(float, float);
-  else if (gdt == CB2_DTYPE_BF16 && pdt == CB2_DTYPE_BF16) CB2_LAUNCH(__nv_bfloat16, __nv_bfloat16);
-  else if (gdt == CB2_DTYPE_F32 && pdt == CB2_DTYPE_BF16) CB2_LAUNCH(float, __nv_bfloat16);
-  else CB2_LAUNCH(__nv_bfloat16, float);
-#undef CB2_LAUNCH
+  if (gdt != pdt) {
+    set_last_error("comm_fused: gradient and parameter arenas must have the same dtype");
+    return CB2_ERR_UNSUPPORTED;
+  }
+  if (gdt == CB2_DTYPE_F32) comm_fused_kernel<ALGO, float, WT><<<blocks, 512, 0, st>>>(d, a, opt);
+  else comm_fused_kernel<ALGO, __nv_bfloat16, WT><<<blocks, 512, 0, st>>>(d, a, opt);
   return check_cuda(cudaGetLastError(), "comm_fused launch");
 }
 
