@@ -92,6 +92,21 @@ def _create_request_dict(job_id, region, image_uri, chief_config, worker_count, 
     return request
 
 
+def submit_plan(plan, image, args=None, job_id=None, labels=None, env=None, region=None):
+    """Lower-level entry used by cloud_fit and the trial scheduler: launch an explicit rank plan
+    with an explicit image manifest ``{"workdir", "entrypoint"}``.  Returns the job id."""
+    job_id = job_id or _generate_job_id()
+    request = {"jobId": job_id, "trainingInput": {"region": region or gcp.get_region(),
+                                                   "scaleTier": "custom", "args": list(args or [])},
+               "plan": plan, "image": image, "args": list(args or []), "python": sys.executable,
+               "env": dict(env or {}), "client": api_client.user_agent(), "submitted": time.time()}
+    if labels:
+        request["labels"] = labels
+    registry.create(job_id, request)
+    _start_supervisor(job_id)
+    return job_id
+
+
 def _start_supervisor(job_id):
     jdir = registry.job_dir(job_id)
     log = open(os.path.join(jdir, "logs", "supervisor.log"), "ab", buffering=0)

@@ -1,0 +1,1 @@
+"""Experimental APIs (reference: src/python/tensorflow_cloud/experimental)."""

@@ -36,8 +36,7 @@ def _basic(x, filters, stride, conv_shortcut, name):
         sc = x
     y = x
     if stride > 1:
-        y = L.ZeroPadding2D(1, name=name + "_1_pad")(y)
-        y = L.Conv2D(filters, 3, strides=stride, use_bias=False, name=name + "_1_conv")(y)
+        y = L.Conv2D(filters, 3, strides=stride, padding=1, use_bias=False, name=name + "_1_conv")(y)
     else:
         y = L.Conv2D(filters, 3, padding="same", use_bias=False, name=name + "_1_conv")(y)
     y = L.BatchNormalization(epsilon=1e-5, activation="relu", name=name + "_1_bn")(y)
@@ -46,11 +45,11 @@ def _basic(x, filters, stride, conv_shortcut, name):
 
 
 def _stem(inp, use_bias, eps):
-    x = L.ZeroPadding2D(3, name="conv1_pad")(inp)
-    x = L.Conv2D(64, 7, strides=2, use_bias=use_bias, name="conv1_conv")(x)
+    # Keras: conv1_pad (ZeroPadding2D 3) + 'valid' conv, pool1_pad (ZeroPadding2D 1) + 'valid' pool.
+    # The paddings are folded into the conv / pool (same maths, two full activation copies saved).
+    x = L.Conv2D(64, 7, strides=2, padding=3, use_bias=use_bias, name="conv1_conv")(inp)
     x = L.BatchNormalization(epsilon=eps, activation="relu", name="conv1_bn")(x)
-    x = L.ZeroPadding2D(1, name="pool1_pad")(x)
-    return L.MaxPooling2D(3, strides=2, name="pool1_pool")(x)
+    return L.MaxPooling2D(3, strides=2, padding=1, name="pool1_pool")(x)
 
 
 def _head(x, include_top, pooling, classes, classifier_activation):

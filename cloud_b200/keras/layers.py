@@ -419,7 +419,9 @@ class Conv2D(Layer):
         self.filters = int(filters)
         self.kernel_size = _pair(kernel_size)
         self.strides = _pair(strides)
-        self.padding = padding.lower()
+        # 'valid' | 'same' as in Keras, or an explicit symmetric zero padding (int or (ph, pw)):
+        # the fused form of ZeroPadding2D + 'valid' convolution (saves a full copy of the input)
+        self.padding = padding.lower() if isinstance(padding, str) else _pair(padding)
         self.dilation = _pair(dilation_rate)
         self.activation_name = activation if isinstance(activation, (str, type(None))) else None
         self._activation_fn = get_activation(activation)
@@ -445,20 +447,21 @@ class Conv2D(Layer):
         else:
             self.bias = None
 
-    def _out_dim(self, n, k, s, d):
+    def _out_dim(self, n, k, s, d, axis=0):
         if n is None:
             return None
         if self.padding == "same":
             return -(-n // s)
-        return (n - ((k - 1) * d + 1)) // s + 1
+        extra = 2 * self.padding[axis] if isinstance(self.padding, tuple) else 0
+        return (n + extra - ((k - 1) * d + 1)) // s + 1
 
     def compute_output_shape(self, input_shape):
         b, h, w, _c = input_shape
-        return (b, self._out_dim(h, self.kernel_size[0], self.strides[0], self.dilation[0]),
-                self._out_dim(w, self.kernel_size[1], self.strides[1], self.dilation[1]), self.filters)
+        return (b, self._out_dim(h, self.kernel_size[0], self.strides[0], self.dilation[0], 0),
+                self._out_dim(w, self.kernel_size[1], self.strides[1], self.dilation[1], 1), self.filters)
 
     def call(self, x, training=False):
-        pad = 0
+        pad = self.padding if isinstance(self.padding, tuple) else 0
         if self.padding == "same":
             ph = _same_pad(x.shape[2], self.kernel_size[0], self.strides[0], self.dilation[0])
             pw = _same_pad(x.shape[3], self.kernel_size[1], self.strides[1], self.dilation[1])
@@ -490,7 +493,8 @@ class _Pool2D(Layer):
         super().__init__(**kwargs)
         self.pool_size = _pair(pool_size)
         self.strides = _pair(strides) if strides is not None else self.pool_size
-        self.padding = padding.lower()
+        # 'valid' | 'same', or an explicit symmetric ZERO padding (int): fused ZeroPadding2D + pool
+        self.padding = padding.lower() if isinstance(padding, str) else int(padding)
 
     def compute_output_shape(self, input_shape):
         b, h, w, c = input_shape
@@ -498,6 +502,8 @@ class _Pool2D(Layer):
         def o(n, k, s):
             if n is None:
                 return None
+            if isinstance(self.padding, int):
+                return (n + 2 * self.padding - k) // s + 1
             return -(-n // s) if self.padding == "same" else (n - k) // s + 1
         return (b, o(h, self.pool_size[0], self.strides[0]), o(w, self.pool_size[1], self.strides[1]), c)
 
@@ -517,6 +523,13 @@ class _Pool2D(Layer):
 
 class MaxPooling2D(_Pool2D):
     def call(self, x, training=False):
+        square = self.pool_size[0] == self.pool_size[1] and self.strides[0] == self.strides[1]
+        if square and self.padding != "same":
+            pad = self.padding if isinstance(self.padding, int) else 0
+            return ops.max_pool_nhwc(x, self.pool_size[0], self.strides[0], pad)
+        if isinstance(self.padding, int) and self.padding:
+            p = self.padding
+            x = F.pad(x, (p, p, p, p))
         return F.max_pool2d(self._pad(x, float("-inf")), self.pool_size, self.strides)
 
 
@@ -525,6 +538,9 @@ MaxPool2D = MaxPooling2D
 
 class AveragePooling2D(_Pool2D):
     def call(self, x, training=False):
+        if isinstance(self.padding, int) and self.padding:
+            p = self.padding
+            x = F.pad(x, (p, p, p, p))
         return F.avg_pool2d(self._pad(x, 0.0), self.pool_size, self.strides)
 
 

@@ -15,13 +15,14 @@ from .elementwise import dropout, relu_bwd_bias_grad, normalize_u8_images  # noq
 from .optim import FlatOptimizerState, optim_flat, optim_tick, OPT_CODES, make_hyper  # noqa: F401
 
 from .bn import batch_norm_nhwc, bn_available  # noqa: F401,E402
+from .pool import max_pool_nhwc  # noqa: F401,E402
 
 
 def kernel_launches() -> int:
     """How many cloud_b200 kernels this process has launched (bench.py reports it)."""
     import importlib
     total = 0
-    for name in ("dense", "loss", "elementwise", "optim", "bn"):   # `dense` the module, not the op
+    for name in ("dense", "loss", "elementwise", "optim", "bn", "pool"):   # `dense` the module, not the op
         total += importlib.import_module(f"{__name__}.{name}").launches()
     return total + importlib.import_module("cloud_b200.parallel.comm").launches()
 

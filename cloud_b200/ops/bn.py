@@ -34,7 +34,7 @@ def _k():
         lib.cb2_bn_scratch_floats.argtypes = [i]
         lib.cb2_bn_forward.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, f, f, i, i, vp]
         lib.cb2_bn_backward.restype = i
-        lib.cb2_bn_backward.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp]
+        lib.cb2_bn_backward.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp]
         _declared = True
     return lib
 
@@ -53,6 +53,41 @@ def _stream():
     return torch.cuda.current_stream().cuda_stream
 
 
+# One zero-filled scratch arena per device, handed out slice by slice and re-zeroed with a single
+# memset at the start of every training step (DPEngine.begin_step): replaces two torch.zeros
+# launches per BatchNormalization layer per step (106 for ResNet-50).
+_pool = {}
+
+
+def reset_scratch(device) -> None:
+    """Start of a step: zero what the previous step used and rewind."""
+    st = _pool.get(device)
+    if st is None:
+        return
+    if st["used"]:
+        st["buf"][:st["used"]].zero_()
+    st["used"] = 0
+
+
+def _scratch(n: int, device) -> torch.Tensor:
+    st = _pool.get(device)
+    if st is None:
+        st = {"buf": torch.zeros(16 << 20, dtype=torch.float32, device=device), "used": 0,
+              "armed": False}
+        _pool[device] = st
+    if not st["armed"] or st["used"] + n > st["buf"].numel():
+        return torch.zeros(n, dtype=torch.float32, device=device)    # no engine driving the pool
+    out = st["buf"][st["used"]:st["used"] + n]
+    st["used"] += (n + 63) // 64 * 64
+    return out
+
+
+def arm_scratch(device) -> None:
+    """Called by the engine once it promises to call ``reset_scratch`` every step."""
+    _scratch(0, device)
+    _pool[device]["armed"] = True
+
+
 def _is_nhwc(t):
     return t.dim() == 4 and t.is_contiguous(memory_format=torch.channels_last)
 
@@ -64,7 +99,7 @@ class _BNFn(torch.autograd.Function):
         N, C, H, W = x.shape
         M = N * H * W
         y = torch.empty_like(x)                       # preserves channels_last
-        sums = torch.zeros(_k().cb2_bn_scratch_floats(C), dtype=torch.float32, device=x.device)
+        sums = _scratch(_k().cb2_bn_scratch_floats(C), x.device)
         save = torch.empty(2 * C, dtype=torch.float32, device=x.device)
         rc = _k().cb2_bn_forward(x.data_ptr(), None if residual is None else residual.data_ptr(),
                                  y.data_ptr(), sums.data_ptr(), gamma.data_ptr(), beta.data_ptr(),
@@ -72,6 +107,7 @@ class _BNFn(torch.autograd.Function):
                                  save[C:].data_ptr(),
                                  None if mean_bias is None else mean_bias.data_ptr(), M, C,
                                  float(eps), float(momentum), int(relu), 1, _stream())
+        ctx.params = (gamma, beta)
         _lib.check(rc, "bn_forward")
         _launches += 2
         ctx.save_for_backward(x, y if relu else None, gamma, save)
@@ -87,17 +123,30 @@ class _BNFn(torch.autograd.Function):
             dy = dy.contiguous(memory_format=torch.channels_last)
         dx = torch.empty_like(x)
         dres = torch.empty_like(x) if ctx.has_res and ctx.relu else None
-        sums = torch.zeros(_k().cb2_bn_scratch_floats(C), dtype=torch.float32, device=x.device)
-        grads = torch.empty(2 * C, dtype=torch.float32, device=x.device)
+        sums = _scratch(_k().cb2_bn_scratch_floats(C), x.device)
+        # gamma / beta gradients go straight into the engine's gradient arena when it exposes one
+        # (no temporary, no accumulate kernel); the engine is told through `_cb2_grad_written`
+        gparam, bparam = ctx.params
+        direct = (getattr(gparam, "_cb2_direct_grad", False) and getattr(bparam, "_cb2_direct_grad", False)
+                  and gparam.grad is not None and bparam.grad is not None)
+        if direct:
+            dbeta_ptr, dgamma_ptr, grads = bparam.grad.data_ptr(), gparam.grad.data_ptr(), None
+        else:
+            grads = torch.empty(2 * C, dtype=torch.float32, device=x.device)
+            dbeta_ptr, dgamma_ptr = grads.data_ptr(), grads[C:].data_ptr()
         rc = _k().cb2_bn_backward(dy.data_ptr(), None if y is None else y.data_ptr(), x.data_ptr(),
                                   save.data_ptr(), save[C:].data_ptr(), gamma.data_ptr(),
-                                  sums.data_ptr(), grads.data_ptr(), dx.data_ptr(),
+                                  sums.data_ptr(), dbeta_ptr, dgamma_ptr, dx.data_ptr(),
                                   None if dres is None else dres.data_ptr(), M, C, int(ctx.relu),
                                   _stream())
         _lib.check(rc, "bn_backward")
         _launches += 2
         if ctx.has_res and dres is None:
             dres = dy                                 # no ReLU: the shortcut gradient is dy itself
+        if direct:
+            gparam._cb2_grad_written(gparam)
+            bparam._cb2_grad_written(bparam)
+            return dx, None, None, dres, None, None, None, None, None, None
         return dx, grads[C:], grads[:C], dres, None, None, None, None, None, None
 
 
@@ -132,7 +181,7 @@ def batch_norm_nhwc(x, gamma, beta, run_mean, run_var, training, momentum, eps, 
     y = torch.empty_like(x)
     sums_ptr = save_ptr = save2_ptr = None
     if training:
-        sums = torch.zeros(_k().cb2_bn_scratch_floats(C), dtype=torch.float32, device=x.device)
+        sums = _scratch(_k().cb2_bn_scratch_floats(C), x.device)
         save = torch.empty(2 * C, dtype=torch.float32, device=x.device)
         sums_ptr, save_ptr, save2_ptr = sums.data_ptr(), save.data_ptr(), save[C:].data_ptr()
     rc = _k().cb2_bn_forward(x.data_ptr(), None if residual is None else residual.data_ptr(),

@@ -229,11 +229,19 @@ class DPEngine:
 
     # ------------------------------------------------------------------------------------------
     def _install_hooks(self) -> None:
+        if self.is_cuda:
+            from ..ops import bn
+            bn.arm_scratch(self.device)
         for gi, g in enumerate(self.groups):
             bi, seen = 0, 0
             for (_name, p) in g.params:
-                handle = p.register_post_accumulate_grad_hook(self._make_hook(gi, bi))
+                hook = self._make_hook(gi, bi)
+                handle = p.register_post_accumulate_grad_hook(hook)
                 self._hook_handles.append(handle)
+                # kernels that own a parameter's gradient (fused batch-norm) may write it straight
+                # into the arena view `p.grad` and call this instead of returning a gradient
+                p._cb2_direct_grad = self.is_cuda
+                p._cb2_grad_written = hook
                 seen += 1
                 if seen == g.buckets[bi].n_params:
                     bi, seen = bi + 1, 0
@@ -267,8 +275,9 @@ class DPEngine:
                 b.ready, b.launched = 0, False
         optim_tick(self.hyper)
         if self.is_cuda:
-            from ..ops import elementwise
+            from ..ops import bn, elementwise
             elementwise.set_step_tensor(self.hyper[5:6])
+            bn.reset_scratch(self.device)
         self._in_step = True
 
     def _launch_bucket(self, gi: int, bi: int) -> None:

@@ -17,7 +17,7 @@ constexpr int kBnThreads = 256;
 // Partial sums of different CTAs land in kBnCopies replicas of the [2C] accumulator
 // (replica = blockIdx % kBnCopies): same-address L2 atomics serialise, and with ~600 CTAs on one
 // replica they - not HBM - set the kernel time (measured: 60 us floor per launch).
-constexpr int kBnCopies = 16;
+constexpr int kBnCopies = 8;
 
 struct BnGeom {
   int tpr;       // threads per row = C / 8
@@ -68,7 +68,8 @@ __device__ __forceinline__ void bn_gather_sums(const float* __restrict__ sums, i
   if (rlane == 0) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) a[j] = b[j] = 0.f;
-    for (int k = 0; k < kBnCopies; ++k) {
+#pragma unroll
+    for (int k = 0; k < kBnCopies; ++k) {   // unrolled: all replica loads in flight together
       const float* src = sums + static_cast<size_t>(k) * 2 * C;
       const float4 a0 = *reinterpret_cast<const float4*>(src + c8);
       const float4 a1 = *reinterpret_cast<const float4*>(src + c8 + 4);
@@ -247,9 +248,9 @@ __global__ void __launch_bounds__(kBnThreads)
 bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
                     const __nv_bfloat16* __restrict__ x, const float* __restrict__ save_mean,
                     const float* __restrict__ save_invstd, const float* __restrict__ gamma,
-                    const float* __restrict__ sums, float* __restrict__ dgamma_dbeta,
-                    __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres, int M, int C,
-                    int relu) {
+                    const float* __restrict__ sums, float* __restrict__ dbeta_out,
+                    float* __restrict__ dgamma_out, __nv_bfloat16* __restrict__ dx,
+                    __nv_bfloat16* __restrict__ dres, int M, int C, int relu) {
   __shared__ float s_a[2048], s_b[2048];
   const int tpr = C >> 3, rows = kBnThreads / tpr;
   const int rlane = threadIdx.x / tpr, c8 = (threadIdx.x % tpr) * 8;
@@ -265,8 +266,8 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
     k1[j] = db[j] * invM;        // dbeta / M
     k2[j] = dg[j] * invM;        // dgamma / M
     if (blockIdx.x == 0 && rlane == 0) {
-      dgamma_dbeta[c] = db[j];       // [0:C] dbeta
-      dgamma_dbeta[C + c] = dg[j];   // [C:2C] dgamma
+      dbeta_out[c] = db[j];
+      dgamma_out[c] = dg[j];
     }
   }
   const int stride = gridDim.x * rows;
@@ -346,7 +347,7 @@ extern "C" int cb2_bn_forward(const void* x, const void* residual, void* y,
 extern "C" int cb2_bn_backward(const void* dy, const void* y, const void* x, const float* save_mean,
                                const float* save_invstd, const float* gamma,
                                float* sums /*[cb2_bn_scratch_floats(C)], zeroed*/,
-                               float* dbeta_dgamma /*out [2C]: dbeta | dgamma*/, void* dx,
+                               float* dbeta /*out [C]*/, float* dgamma /*out [C]*/, void* dx,
                                void* dres /*nullable*/, int M, int C, int relu, void* stream) {
   int rc = bn_check(M, C, "bn_backward");
   if (rc) return rc;
@@ -359,7 +360,7 @@ extern "C" int cb2_bn_backward(const void* dy, const void* y, const void* x, con
       reinterpret_cast<const __nv_bfloat16*>(x), save_mean, save_invstd, sums, M, C, relu);
   bn_bwd_apply_kernel<<<grid, kBnThreads, 0, st>>>(
       reinterpret_cast<const __nv_bfloat16*>(dy), reinterpret_cast<const __nv_bfloat16*>(y),
-      reinterpret_cast<const __nv_bfloat16*>(x), save_mean, save_invstd, gamma, sums, dbeta_dgamma,
+      reinterpret_cast<const __nv_bfloat16*>(x), save_mean, save_invstd, gamma, sums, dbeta, dgamma,
       reinterpret_cast<__nv_bfloat16*>(dx), reinterpret_cast<__nv_bfloat16*>(dres), M, C, relu);
   return check_cuda(cudaGetLastError(), "bn_backward launch");
 }
