@@ -70,6 +70,10 @@ class Strategy:
         self.device = device
         if device.type == "cuda":
             torch.cuda.set_device(device)
+            # let cuDNN time its algorithms per convolution shape during the eager warm-up steps
+            # (before the step is frozen into a CUDA graph)
+            if os.environ.get("TFC_CUDNN_BENCHMARK", "1") != "0":
+                torch.backends.cudnn.benchmark = True
         self._group = None
         world, rank, _local = _env_world()
         if use_process_group and world > 1:

@@ -126,7 +126,9 @@ def _n_weights(layer) -> int:
 
 def load_weights(model, filepath, by_name=False) -> None:
     path = str(filepath)
-    if not os.path.exists(path):
+    if not _is_h5(path) and os.path.exists(_weights_path(path)):
+        path = _weights_path(path)        # TF-checkpoint style prefix -> "<prefix>.weights.h5"
+    elif not os.path.exists(path) or os.path.isdir(path):
         alt = _weights_path(path)
         if os.path.exists(alt):
             path = alt

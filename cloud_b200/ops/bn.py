@@ -34,7 +34,7 @@ def _k():
         lib.cb2_bn_scratch_floats.argtypes = [i]
         lib.cb2_bn_forward.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, f, f, i, i, vp]
         lib.cb2_bn_backward.restype = i
-        lib.cb2_bn_backward.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp]
+        lib.cb2_bn_backward.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp]
         _declared = True
     return lib
 
@@ -110,14 +110,15 @@ class _BNFn(torch.autograd.Function):
         ctx.params = (gamma, beta)
         _lib.check(rc, "bn_forward")
         _launches += 2
-        ctx.save_for_backward(x, y if relu else None, gamma, save)
+        # the ReLU mask is recomputed from x unless a shortcut was added before the ReLU
+        ctx.save_for_backward(x, y if (relu and residual is not None) else None, gamma, save, beta)
         ctx.relu, ctx.has_res, ctx.M, ctx.C = relu, residual is not None, M, C
         return y
 
     @staticmethod
     def backward(ctx, dy):
         global _launches
-        x, y, gamma, save = ctx.saved_tensors
+        x, y, gamma, save, beta = ctx.saved_tensors
         C, M = ctx.C, ctx.M
         if not _is_nhwc(dy):
             dy = dy.contiguous(memory_format=torch.channels_last)
@@ -136,7 +137,8 @@ class _BNFn(torch.autograd.Function):
             dbeta_ptr, dgamma_ptr = grads.data_ptr(), grads[C:].data_ptr()
         rc = _k().cb2_bn_backward(dy.data_ptr(), None if y is None else y.data_ptr(), x.data_ptr(),
                                   save.data_ptr(), save[C:].data_ptr(), gamma.data_ptr(),
-                                  sums.data_ptr(), dbeta_ptr, dgamma_ptr, dx.data_ptr(),
+                                  beta.data_ptr(), sums.data_ptr(), dbeta_ptr, dgamma_ptr,
+                                  dx.data_ptr(),
                                   None if dres is None else dres.data_ptr(), M, C, int(ctx.relu),
                                   _stream())
         _lib.check(rc, "bn_backward")

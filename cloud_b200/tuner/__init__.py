@@ -1,0 +1,7 @@
+"""Hyper-parameter tuning: ``CloudOracle`` / ``CloudTuner`` / ``DistributingCloudTuner`` backed by
+a local Vizier-compatible optimizer, plus a multi-GPU trial scheduler
+(reference: src/python/tensorflow_cloud/tuner)."""
+from .tuner import CloudOracle, CloudTuner, DistributingCloudTuner  # noqa: F401
+from .scheduler import TrialScheduler  # noqa: F401
+from .engine import HyperParameters, Objective  # noqa: F401
+from .engine.tuner import RandomSearch  # noqa: F401

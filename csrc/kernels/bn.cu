@@ -186,16 +186,23 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
 __global__ void __launch_bounds__(kBnThreads)
 bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
                      const __nv_bfloat16* __restrict__ x, const float* __restrict__ save_mean,
-                     const float* __restrict__ save_invstd, float* __restrict__ sums, int M, int C,
+                     const float* __restrict__ save_invstd, const float* __restrict__ gamma,
+                     const float* __restrict__ beta, float* __restrict__ sums, int M, int C,
                      int relu) {
   extern __shared__ float smem[];
   const int tpr = C >> 3, rows = kBnThreads / tpr;
   const int rlane = threadIdx.x / tpr, c8 = (threadIdx.x % tpr) * 8;
-  float mean[8], istd[8], db[8], dg[8];
+  // relu without a saved output: the mask is recomputed from x (y > 0 <=> x*sc + sh > 0), which
+  // saves reading y - one of three activation-sized reads - for every BN+ReLU without shortcut
+  const bool mask_from_x = relu && y == nullptr;
+  const bool mask_from_y = relu && y != nullptr;
+  float mean[8], istd[8], db[8], dg[8], sc[8], sh[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     mean[j] = save_mean[c8 + j];
     istd[j] = save_invstd[c8 + j];
+    sc[j] = gamma[c8 + j] * istd[j];
+    sh[j] = beta[c8 + j] - mean[j] * sc[j];
     db[j] = dg[j] = 0.f;
   }
   const int stride = gridDim.x * rows;
@@ -207,15 +214,21 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     const uint4 wg0 = ld_stream_v4(dy + i0), wg1 = ld_stream_v4(dy + i1);
     const uint4 wx0 = ld_stream_v4(x + i0), wx1 = ld_stream_v4(x + i1);
     uint4 wy0 = make_uint4(0, 0, 0, 0), wy1 = wy0;
-    if (relu) { wy0 = ld_stream_v4(y + i0); wy1 = ld_stream_v4(y + i1); }
+    if (mask_from_y) { wy0 = ld_stream_v4(y + i0); wy1 = ld_stream_v4(y + i1); }
     Vec8 g0 = unpack8_bf16(wg0), g1 = unpack8_bf16(wg1);
     const Vec8 x0 = unpack8_bf16(wx0), x1 = unpack8_bf16(wx1);
-    if (relu) {
+    if (mask_from_y) {
       const Vec8 y0 = unpack8_bf16(wy0), y1 = unpack8_bf16(wy1);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         g0.v[j] = y0.v[j] > 0.f ? g0.v[j] : 0.f;
         g1.v[j] = y1.v[j] > 0.f ? g1.v[j] : 0.f;
+      }
+    } else if (mask_from_x) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        g0.v[j] = fmaf(x0.v[j], sc[j], sh[j]) > 0.f ? g0.v[j] : 0.f;
+        g1.v[j] = fmaf(x1.v[j], sc[j], sh[j]) > 0.f ? g1.v[j] : 0.f;
       }
     }
 #pragma unroll
@@ -229,10 +242,13 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     const size_t idx = static_cast<size_t>(row) * C + c8;
     Vec8 g = unpack8_bf16(ld_stream_v4(dy + idx));
     const Vec8 xv = unpack8_bf16(ld_stream_v4(x + idx));
-    if (relu) {
+    if (mask_from_y) {
       const Vec8 yv = unpack8_bf16(ld_stream_v4(y + idx));
 #pragma unroll
       for (int j = 0; j < 8; ++j) g.v[j] = yv.v[j] > 0.f ? g.v[j] : 0.f;
+    } else if (mask_from_x) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g.v[j] = fmaf(xv.v[j], sc[j], sh[j]) > 0.f ? g.v[j] : 0.f;
     }
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -248,14 +264,17 @@ __global__ void __launch_bounds__(kBnThreads)
 bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
                     const __nv_bfloat16* __restrict__ x, const float* __restrict__ save_mean,
                     const float* __restrict__ save_invstd, const float* __restrict__ gamma,
-                    const float* __restrict__ sums, float* __restrict__ dbeta_out,
+                    const float* __restrict__ beta, const float* __restrict__ sums,
+                    float* __restrict__ dbeta_out,
                     float* __restrict__ dgamma_out, __nv_bfloat16* __restrict__ dx,
                     __nv_bfloat16* __restrict__ dres, int M, int C, int relu) {
   __shared__ float s_a[2048], s_b[2048];
   const int tpr = C >> 3, rows = kBnThreads / tpr;
   const int rlane = threadIdx.x / tpr, c8 = (threadIdx.x % tpr) * 8;
   const float invM = 1.f / static_cast<float>(M);
-  float mean[8], istd[8], k0[8], k1[8], k2[8], db[8], dg[8];
+  const bool mask_from_x = relu && y == nullptr;
+  const bool mask_from_y = relu && y != nullptr;
+  float mean[8], istd[8], k0[8], k1[8], k2[8], db[8], dg[8], sh[8];
   bn_gather_sums(sums, C, c8, rlane, s_a, s_b, db, dg);
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
@@ -263,6 +282,7 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
     mean[j] = save_mean[c];
     istd[j] = save_invstd[c];
     k0[j] = gamma[c] * istd[j];
+    sh[j] = beta[c] - mean[j] * k0[j];
     k1[j] = db[j] * invM;        // dbeta / M
     k2[j] = dg[j] * invM;        // dgamma / M
     if (blockIdx.x == 0 && rlane == 0) {
@@ -275,10 +295,13 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
     const size_t idx = static_cast<size_t>(row) * C + c8;
     Vec8 g = unpack8_bf16(ld_stream_v4(dy + idx));
     const Vec8 xv = unpack8_bf16(ld_stream_v4(x + idx));
-    if (relu) {
+    if (mask_from_y) {
       const Vec8 yv = unpack8_bf16(ld_stream_v4(y + idx));
 #pragma unroll
       for (int j = 0; j < 8; ++j) g.v[j] = yv.v[j] > 0.f ? g.v[j] : 0.f;
+    } else if (mask_from_x) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g.v[j] = fmaf(xv.v[j], k0[j], sh[j]) > 0.f ? g.v[j] : 0.f;
     }
     if (dres) *reinterpret_cast<uint4*>(dres + idx) = pack8_bf16(g);
     Vec8 o;
@@ -345,7 +368,7 @@ extern "C" int cb2_bn_forward(const void* x, const void* residual, void* y,
 }
 
 extern "C" int cb2_bn_backward(const void* dy, const void* y, const void* x, const float* save_mean,
-                               const float* save_invstd, const float* gamma,
+                               const float* save_invstd, const float* gamma, const float* beta,
                                float* sums /*[cb2_bn_scratch_floats(C)], zeroed*/,
                                float* dbeta /*out [C]*/, float* dgamma /*out [C]*/, void* dx,
                                void* dres /*nullable*/, int M, int C, int relu, void* stream) {
@@ -357,10 +380,12 @@ extern "C" int cb2_bn_backward(const void* dy, const void* y, const void* x, con
   const size_t smem = rows > 1 ? static_cast<size_t>(2) * rows * C * sizeof(float) : 0;
   bn_bwd_reduce_kernel<<<grid, kBnThreads, smem, st>>>(
       reinterpret_cast<const __nv_bfloat16*>(dy), reinterpret_cast<const __nv_bfloat16*>(y),
-      reinterpret_cast<const __nv_bfloat16*>(x), save_mean, save_invstd, sums, M, C, relu);
+      reinterpret_cast<const __nv_bfloat16*>(x), save_mean, save_invstd, gamma, beta, sums, M, C,
+      relu);
   bn_bwd_apply_kernel<<<grid, kBnThreads, 0, st>>>(
       reinterpret_cast<const __nv_bfloat16*>(dy), reinterpret_cast<const __nv_bfloat16*>(y),
-      reinterpret_cast<const __nv_bfloat16*>(x), save_mean, save_invstd, gamma, sums, dbeta, dgamma,
+      reinterpret_cast<const __nv_bfloat16*>(x), save_mean, save_invstd, gamma, beta, sums, dbeta,
+      dgamma,
       reinterpret_cast<__nv_bfloat16*>(dx), reinterpret_cast<__nv_bfloat16*>(dres), M, C, relu);
   return check_cuda(cudaGetLastError(), "bn_backward launch");
 }
