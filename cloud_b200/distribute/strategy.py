@@ -70,9 +70,9 @@ class Strategy:
         self.device = device
         if device.type == "cuda":
             torch.cuda.set_device(device)
-            # let cuDNN time its algorithms per convolution shape during the eager warm-up steps
+            # opt-in (TFC_CUDNN_BENCHMARK=1): let cuDNN time its algorithms during the eager warm-up steps
             # (before the step is frozen into a CUDA graph)
-            if os.environ.get("TFC_CUDNN_BENCHMARK", "1") != "0":
+            if os.environ.get("TFC_CUDNN_BENCHMARK", "0") == "1":
                 torch.backends.cudnn.benchmark = True
         self._group = None
         world, rank, _local = _env_world()
