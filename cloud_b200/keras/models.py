@@ -574,6 +574,7 @@ class Model(nn.Module):
             pending = None           # (step index, device tensor of reduced aux, event)
             pf = _Prefetcher(source, self.device)
             step = -1
+            epoch_t0 = time.perf_counter()
             for step, (xd, yd, ev, n_global) in enumerate(pf):
                 if batch_logs:
                     cbl.call("on_train_batch_begin", step, {})
@@ -599,6 +600,8 @@ class Model(nn.Module):
             self._h2d_bytes += pf.h2d_bytes
             host = acc.cpu()
             self._d2h_bytes += host.numel() * 8
+            self._record_epoch_metrics(eng, step + 1, time.perf_counter() - epoch_t0,
+                                       float(host[AUX_COUNT]))
             logs = self._logs_from_aux(host, getattr(self, "_last_fused", False)) if step >= 0 else {}
             if validation_data is not None:
                 vx, vy = (validation_data[0], validation_data[1]) \
@@ -614,6 +617,26 @@ class Model(nn.Module):
         self.train(False)
         self.history = history
         return history
+
+    def _record_epoch_metrics(self, eng, steps, seconds, samples):
+        """Feeds the C++ metrics registry (cloud_b200.monitoring); exported only if enabled."""
+        if steps <= 0 or seconds <= 0:
+            return
+        try:
+            from .. import monitoring as mon
+            if not getattr(self, "_mon_ready", False):
+                mon.define_defaults()
+                mon.start()
+                self._mon_ready = True
+            mon.observe(mon.STEP_TIME, seconds / steps * 1e6)
+            mon.set_gauge(mon.IMAGES_PER_SEC, int(samples / seconds))
+            n_buckets = sum(len(g.buckets) for g in eng.groups)
+            mon.increment(mon.BUCKET_LAUNCHES, steps * n_buckets)
+            if eng.world > 1:
+                nbytes = sum(g.total * (2 if g.dtype == torch.bfloat16 else 4) for g in eng.groups)
+                mon.increment(mon.BYTES_REDUCED, steps * nbytes)
+        except Exception:      # metrics must never break training
+            pass
 
     def _emit_batch(self, cbl, pending):
         step, snap = pending
@@ -791,11 +814,20 @@ class _LoadStatus:
 class _HostSnap:
     """Async device->host copy of a small tensor into pinned memory, read later."""
 
+    _ring: dict = {}       # (shape, dtype) -> [pinned buffers, events, cursor]; pinning is slow
+
     def __init__(self, t, device):
         if device.type == "cuda":
-            self.buf = torch.empty(t.shape, dtype=t.dtype).pin_memory()
+            key = (tuple(t.shape), t.dtype)
+            ring = _HostSnap._ring.get(key)
+            if ring is None:
+                ring = [[torch.empty(t.shape, dtype=t.dtype).pin_memory() for _ in range(4)],
+                        [torch.cuda.Event() for _ in range(4)], 0]
+                _HostSnap._ring[key] = ring
+            i = ring[2] % 4
+            ring[2] += 1
+            self.buf, self.ev = ring[0][i], ring[1][i]
             self.buf.copy_(t, non_blocking=True)
-            self.ev = torch.cuda.Event()
             self.ev.record()
         else:
             self.buf, self.ev = t.clone(), None
@@ -803,6 +835,7 @@ class _HostSnap:
     def get(self):
         if self.ev is not None:
             self.ev.synchronize()
+            return self.buf.clone()      # the ring slot is reused four snapshots later
         return self.buf
 
 

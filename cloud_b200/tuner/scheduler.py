@@ -56,8 +56,21 @@ class TrialScheduler:
         log_dir = log_dir or tempfile.mkdtemp(prefix="cb2_trials_")
         os.makedirs(log_dir, exist_ok=True)
         blob = os.path.join(log_dir, "target.pkl")
+        # a function living in the user's own script/module travels by value: the worker process
+        # cannot be assumed to be able to import that module
+        mod = sys.modules.get(getattr(target, "__module__", None) or "")
+        by_value = (mod is not None and mod.__name__ not in ("__main__",)
+                    and not mod.__name__.startswith("cloud_b200")
+                    and "site-packages" not in (getattr(mod, "__file__", "") or ""))
+        if by_value:
+            cloudpickle.register_pickle_by_value(mod)
+        try:
+            payload = cloudpickle.dumps((target, tuple(args), dict(kwargs or {})))
+        finally:
+            if by_value:
+                cloudpickle.unregister_pickle_by_value(mod)
         with open(blob, "wb") as f:
-            f.write(cloudpickle.dumps((target, tuple(args), dict(kwargs or {}))))
+            f.write(payload)
         pending = [{"index": i, "tuner_id": "tuner{}".format(i), "restarts": 0} for i in range(num_workers)]
         free = list(range(len(slots)))
         running, done = [], []
@@ -66,7 +79,8 @@ class TrialScheduler:
             while pending and free:
                 job = pending.pop(0)
                 slot = free.pop(0)
-                job.update(slot=slot, proc=self._spawn(job, slots[slot], blob, log_dir, env),
+                job["slot"] = slot
+                job.update(proc=self._spawn(job, slots[slot], blob, log_dir, env),
                            started=time.time())
                 running.append(job)
             time.sleep(self.poll)

@@ -72,6 +72,37 @@ int cb2_u8_to_bf16_normalize(const uint8_t* in, void* out, size_t n_pixels, int 
                              const float* mean3, const float* inv_std3, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Fused NHWC batch normalisation (+ residual add) (+ ReLU), bf16 activations [M = N*H*W, C],
+ * fp32 statistics and parameters (K8).  C must be a power-of-two multiple of 8, <= 2048.
+ * `sums` is caller-provided scratch of cb2_bn_scratch_floats(C) floats that MUST be zero on entry
+ * (the reductions accumulate into it with atomics).
+ *   forward : y = act(gamma * (x - mean) / sqrt(var + eps) + beta (+ residual)); training != 0 uses
+ *             batch statistics, refreshes run_mean/run_var (momentum = update rate; mean_bias,
+ *             nullable, is added to the mean that goes into run_mean) and saves mean / inv-std.
+ *   backward: dx, dbeta, dgamma (and dres = masked dy when a residual was added before the ReLU);
+ *             y nullable: with relu != 0 and y == NULL the ReLU mask is recomputed from x.
+ * Reference workload: the 53 BatchNormalization layers of ResNet-50
+ * (core/tests/examples/call_run_within_script_with_keras_fit.py:79-83).
+ * ------------------------------------------------------------------------------------------ */
+int cb2_bn_supported(int C);
+int cb2_bn_scratch_floats(int C);
+int cb2_bn_forward(const void* x, const void* residual /*nullable*/, void* y, float* sums,
+                   const float* gamma, const float* beta, float* run_mean, float* run_var,
+                   float* save_mean, float* save_invstd, const float* mean_bias /*nullable*/, int M,
+                   int C, float eps, float momentum, int relu, int training, void* stream);
+int cb2_bn_backward(const void* dy, const void* y /*nullable*/, const void* x,
+                    const float* save_mean, const float* save_invstd, const float* gamma,
+                    const float* beta, float* sums, float* dbeta, float* dgamma, void* dx,
+                    void* dres /*nullable*/, int M, int C, int relu, void* stream);
+
+/* NHWC max pooling with implicit zero padding; forward keeps a 1-byte arg-max per output element,
+ * backward gathers (no atomics).  bf16, C multiple of 8 (K8: pool1_pad + pool1_pool of ResNet). */
+int cb2_maxpool_nhwc_forward(const void* x, void* y, void* argmax, int N, int H, int W, int C,
+                             int OH, int OW, int k, int s, int pad, void* stream);
+int cb2_maxpool_nhwc_backward(const void* dy, const void* argmax, void* dx, int N, int H, int W,
+                              int C, int OH, int OW, int k, int s, int pad, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Optimizers over flat arenas (K6, K7).  `hyper` is a device float[16]:
  *   [0] lr [1] beta1 [2] beta2 [3] eps [4] weight_decay [5] step [6] 1-beta1^t [7] 1-beta2^t
  *   [8] grad_scale [9] momentum / rho [10] nesterov(0/1) [11] rmsprop momentum
