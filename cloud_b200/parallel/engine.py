@@ -111,6 +111,14 @@ class DPEngine:
         self.aux_out = torch.zeros(comm_mod.AUX_FLOATS, dtype=torch.float32, device=self.device)
         self._hook_handles = []
         self._in_step = False
+        self._fault = None
+        fault = os.environ.get("TFC_FAULT")
+        if fault:
+            try:
+                r, s = fault.split(":")
+                self._fault = (int(r), int(s))
+            except ValueError:
+                raise ValueError("TFC_FAULT must look like '<rank>:<step>', got {!r}".format(fault))
         self._build(list(named_params))
 
     # ------------------------------------------------------------------------------------------
@@ -273,6 +281,9 @@ class DPEngine:
         for g in self.groups:
             for b in g.buckets:
                 b.ready, b.launched = 0, False
+        if self._fault is not None and self._fault == (self.rank, self.steps):
+            # fault injection for launcher / failure-detection tests: TFC_FAULT="<rank>:<step>"
+            os._exit(17)
         optim_tick(self.hyper)
         if self.is_cuda:
             from ..ops import bn, elementwise
