@@ -151,6 +151,8 @@ class _IterSource:
 class _Prefetcher:
     """Background thread: source batch -> pinned staging -> async H2D on a copy stream."""
 
+    _PIN_CACHE: dict = {}      # staging buffers survive across epochs and fit() calls
+
     def __init__(self, source, device, depth=3):
         self.source = source
         self.device = device
@@ -166,7 +168,7 @@ class _Prefetcher:
             return
         q: queue.Queue = queue.Queue(maxsize=self.depth)
         stop = threading.Event()
-        pinned: dict = {}
+        pinned = _Prefetcher._PIN_CACHE        # pinning (cudaHostAlloc) is slow: do it once
 
         def pin(slot, name, t):
             key = (slot, name, tuple(t.shape), t.dtype)
