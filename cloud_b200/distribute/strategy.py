@@ -106,10 +106,16 @@ class Strategy:
         cfg = os.environ.get("TF_CONFIG")
         if cfg:
             try:
-                task = json.loads(cfg).get("task", {})
+                parsed = json.loads(cfg)
+                task = parsed.get("task", {})
                 if task:
-                    return (task.get("type") == "chief" or int(task.get("index", 0)) == 0) \
-                        and self._rank_in_task() == 0
+                    # a cluster with a dedicated chief: only that task is chief; without one,
+                    # worker 0 plays the role (remote.py:148-156)
+                    if "chief" in parsed.get("cluster", {}):
+                        is_chief_task = task.get("type") == "chief"
+                    else:
+                        is_chief_task = task.get("type") == "chief" or int(task.get("index", 0)) == 0
+                    return is_chief_task and self._rank_in_task() == 0
             except (ValueError, TypeError):
                 pass
         return self._rank == 0

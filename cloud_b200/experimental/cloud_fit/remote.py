@@ -64,7 +64,10 @@ def _is_current_worker_chief():
     """TF_CONFIG task 'chief' or index 0 (remote.py:148-156)."""
     cfg = os.environ.get("TF_CONFIG")
     if cfg:
-        task = json.loads(cfg).get("task", {})
+        parsed = json.loads(cfg)
+        task = parsed.get("task", {})
+        if "chief" in parsed.get("cluster", {}):
+            return task.get("type") == "chief"
         return task.get("type") == "chief" or int(task.get("index", 0)) == 0
     return True
 
