@@ -9,6 +9,8 @@
 // Reference workload: the BatchNormalization layers of ResNet-50 (K8 in SURVEY.md section 2.5;
 // core/tests/examples/call_run_within_script_with_keras_fit.py:79-83) which TensorFlow runs as
 // separate cuDNN batch-norm, add and ReLU kernels.
+#include <mutex>
+
 #include "optim.cuh"
 
 namespace cb2 {
@@ -388,4 +390,99 @@ extern "C" int cb2_bn_backward(const void* dy, const void* y, const void* x, con
       dgamma,
       reinterpret_cast<__nv_bfloat16*>(dx), reinterpret_cast<__nv_bfloat16*>(dres), M, C, relu);
   return check_cuda(cudaGetLastError(), "bn_backward launch");
+}
+
+// ---------------------------------------------------------------------------------------------
+// Batch-norm forward for callers that cannot allocate device memory.
+//
+// cb2_bn_forward needs a zero-filled scratch buffer from its caller.  Some users of this C ABI
+// have nowhere to get one: a plug-in loaded into a serving process that handed the whole HBM to
+// its own pool at start-up (any further cudaMalloc fails), a host written in plain C or another
+// language that links the library without torch's caching allocator, or a steady-state loop that
+// must not pay the device-wide synchronisation cudaMalloc / cudaFree imply.  For them the
+// scratch lives in the library image itself.
+//
+// The array below is per-device storage that every GPU which loads this library keeps until the
+// process exits: kBnStaticScratchFloats * 4 bytes = 128 KiB, sized for the largest supported
+// channel count (C = 2048).  Its name is only a handle in host code - the kernels need the device
+// address, which cudaGetSymbolAddress returns for the CURRENT device, so it is looked up once per
+// device and cached.
+// ---------------------------------------------------------------------------------------------
+constexpr int kBnStaticMaxC = 2048;
+constexpr int kBnStaticScratchFloats = cb2::kBnCopies * 2 * kBnStaticMaxC;
+static __device__ __align__(256) float g_bn_static_scratch[kBnStaticScratchFloats];
+
+namespace cb2 {
+
+__global__ void bn_static_scratch_clear_kernel(float* __restrict__ scratch, int n) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    scratch[i] = 0.f;
+}
+
+constexpr int kBnStaticMaxDevices = 64;
+static float* g_bn_static_ptr[kBnStaticMaxDevices] = {nullptr};
+static std::mutex g_bn_static_mu;
+
+// Device address of the static scratch on the current device (set-up on first use per device).
+static int bn_static_scratch_ptr(float** out) {
+  int dev = -1;
+  CB2_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kBnStaticMaxDevices) {
+    set_last_error("bn_forward_static: device ordinal %d is outside the supported range [0, %d)",
+                   dev, kBnStaticMaxDevices);
+    return CB2_ERR_UNSUPPORTED;
+  }
+  std::lock_guard<std::mutex> lock(g_bn_static_mu);
+  if (g_bn_static_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_bn_static_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      set_last_error("bn_forward_static: cudaGetSymbolAddress failed on device %d: %s", dev,
+                     cudaGetErrorString(e));
+      return CB2_ERR_CUDA;
+    }
+    g_bn_static_ptr[dev] = static_cast<float*>(p);
+  }
+  *out = g_bn_static_ptr[dev];
+  return 0;
+}
+
+}  // namespace cb2
+
+extern "C" int cb2_bn_static_scratch_max_channels(void) { return kBnStaticMaxC; }
+
+extern "C" int cb2_bn_forward_static(const void* x, const void* residual, void* y,
+                                     const float* gamma, const float* beta, float* run_mean,
+                                     float* run_var, float* save_mean, float* save_invstd,
+                                     const float* mean_bias, int M, int C, float eps,
+                                     float momentum, int relu, int training, void* stream) {
+  const long long need_ll = static_cast<long long>(kBnCopies) * 2 * C;
+  const int need = static_cast<int>(need_ll);
+  if (C > kBnStaticMaxC || need_ll > kBnStaticScratchFloats) {
+    set_last_error("bn_forward_static: C=%d needs %d scratch floats but the built-in scratch holds "
+                   "%d (C <= %d); use cb2_bn_forward with caller-provided scratch instead",
+                   C, need, kBnStaticScratchFloats, kBnStaticMaxC);
+    return CB2_ERR_UNSUPPORTED;
+  }
+  int rc = bn_check(M, C, "bn_forward_static");
+  if (rc) return rc;
+  float* scratch = nullptr;
+  rc = bn_static_scratch_ptr(&scratch);
+  if (rc) return rc;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int grid = bn_grid(M, C);
+  const int rows = kBnThreads / (C >> 3);
+  const size_t smem = rows > 1 ? static_cast<size_t>(2) * rows * C * sizeof(float) : 0;
+  if (training) {
+    // the array still holds the previous call's partial sums: the part this call accumulates into
+    // has to start from zero
+    bn_static_scratch_clear_kernel<<<(need + 255) / 256, 256, 0, st>>>(scratch, need);
+    bn_stats_kernel<<<grid, kBnThreads, smem, st>>>(reinterpret_cast<const __nv_bfloat16*>(x),
+                                                    scratch, M, C);
+  }
+  bn_apply_kernel<<<grid, kBnThreads, 0, st>>>(
+      reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<const __nv_bfloat16*>(residual),
+      reinterpret_cast<__nv_bfloat16*>(y), scratch, gamma, beta, run_mean, run_var, save_mean,
+      save_invstd, mean_bias, M, C, eps, momentum, relu, training);
+  return check_cuda(cudaGetLastError(), "bn_forward_static launch");
 }

@@ -95,6 +95,32 @@ int cb2_bn_backward(const void* dy, const void* y /*nullable*/, const void* x,
                     const float* beta, float* sums, float* dbeta, float* dgamma, void* dx,
                     void* dres /*nullable*/, int M, int C, int relu, void* stream);
 
+/* cb2_bn_forward for callers that cannot allocate device memory.  (No counterpart in the
+ * reference: it has no kernels and no C ABI; this entry exists for embedders of this library.)
+ *
+ * Who needs it: a plug-in inside a serving process that gave all of HBM to its own pool at
+ * start-up (a further cudaMalloc fails), a host that links the C ABI without torch and so has no
+ * caching allocator to borrow scratch from, or a steady-state loop that cannot afford the
+ * device-wide synchronisation of cudaMalloc / cudaFree.  Same arguments and results as
+ * cb2_bn_forward minus `sums`: the scratch is a 128 KiB array inside the library image
+ * (8 replicas x 2 x 2048 floats), which every GPU that loads the library keeps until the process
+ * exits.  Limit: C <= cb2_bn_static_scratch_max_channels() (2048); larger C is rejected with
+ * CB2_ERR_UNSUPPORTED and a message naming the limit.
+ *
+ * The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine) and
+ * clears the part of the scratch it accumulates into before use, because the array still holds
+ * the previous call's sums.  All calls on a device share that one array: two calls that may
+ * overlap on the GPU (different streams, or the same stream from racing host threads) corrupt
+ * each other's statistics - serialise them.  The first call on each device looks up the array's
+ * device address (cudaGetSymbolAddress, with that device current) and caches it; make that first
+ * call before starting any stream capture. */
+int cb2_bn_static_scratch_max_channels(void);
+int cb2_bn_forward_static(const void* x, const void* residual /*nullable*/, void* y,
+                          const float* gamma, const float* beta, float* run_mean, float* run_var,
+                          float* save_mean, float* save_invstd, const float* mean_bias /*nullable*/,
+                          int M, int C, float eps, float momentum, int relu, int training,
+                          void* stream);
+
 /* NHWC max pooling with implicit zero padding; forward keeps a 1-byte arg-max per output element,
  * backward gathers (no atomics).  bf16, C multiple of 8 (K8: pool1_pad + pool1_pool of ResNet). */
 int cb2_maxpool_nhwc_forward(const void* x, void* y, void* argmax, int N, int H, int W, int C,
