@@ -1,0 +1,58 @@
+"""A few launches of each hand-written single-GPU kernel on representative shapes, for
+`ncu --set full` captures (one GPU; see /opt/skills/guides/B200_PROFILING.md):
+
+    python bench/ncu_targets.py && ncu --set full --clock-control none --import-source on \
+        -k regex:"gemm_tcgen05|bn_|softmax_xent|optim_flat|maxpool" -c 24 -o gpurun_out/prof \
+        python bench/ncu_targets.py
+"""
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from cloud_b200 import ops  # noqa: E402
+
+dev = torch.device("cuda:0")
+torch.manual_seed(0)
+
+# GEMM: large square (compute bound) and a ResNet 1x1-conv shape (output bound)
+a = torch.randn(8192, 8192, device=dev).to(torch.bfloat16)
+b = torch.randn(8192, 8192, device=dev).to(torch.bfloat16)
+for _ in range(2):
+    ops.gemm(a, b)
+a2 = torch.randn(12544, 512, device=dev).to(torch.bfloat16)
+b2 = torch.randn(2048, 512, device=dev).to(torch.bfloat16)
+for _ in range(2):
+    ops.gemm(a2, b2, bias=torch.zeros(2048, device=dev), relu=True)
+
+# batch norm fwd+bwd on the largest ResNet-50 activation (64 x 56 x 56 x 256) and a small one
+for (n, c, hw) in ((64, 256, 56), (64, 1024, 14)):
+    x = torch.randn(n, c, hw, hw, device=dev).to(torch.bfloat16).contiguous(
+        memory_format=torch.channels_last).requires_grad_(True)
+    g = torch.ones(c, device=dev, requires_grad=True)
+    bt = torch.zeros(c, device=dev, requires_grad=True)
+    rm, rv = torch.zeros(c, device=dev), torch.ones(c, device=dev)
+    y = ops.batch_norm_nhwc(x, g, bt, rm, rv, True, 0.1, 1e-5, relu=True)
+    y.backward(torch.ones_like(y))
+
+# stem max-pool
+xp = torch.rand(64, 64, 112, 112, device=dev).to(torch.bfloat16).contiguous(
+    memory_format=torch.channels_last).requires_grad_(True)
+yp = ops.max_pool_nhwc(xp, 3, 2, 1)
+yp.backward(torch.ones_like(yp))
+
+# loss and optimizer
+logits = torch.randn(4096, 1000, device=dev).to(torch.bfloat16).requires_grad_(True)
+labels = torch.randint(0, 1000, (4096,), device=dev)
+ops.softmax_cross_entropy(logits, labels).backward()
+n = 25_600_000
+master = torch.randn(n, device=dev)
+grad = torch.randn(n, device=dev).to(torch.bfloat16)
+m, v = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+pout = master.to(torch.bfloat16)
+hyper = ops.make_hyper(dev)
+ops.optim_tick(hyper)
+ops.optim_flat(1, master=master, grad=grad, s1=m, s2=v, param_out=pout, hyper=hyper, zero_grad=True)
+torch.cuda.synchronize()
+print("ncu targets done")
