@@ -101,6 +101,44 @@ def main():
                 tf = 2.0 * M * N * K / (ms * 1e-3) / 1e12
                 OUT["perf"].append({"shape": [M, N, K], "impl": label, "ms": ms, "tflops": tf})
                 print(f"{label:8s} {M}x{N}x{K}: {ms:.4f} ms  {tf:.1f} TFLOP/s", flush=True)
+    # ResNet-50 1x1 convolutions (NHWC activations are plain [N*H*W, C] matrices): our GEMM vs
+    # cuDNN through torch.conv2d on channels_last tensors; these are bandwidth-bound shapes
+    if all_ok:
+        OUT["conv1x1"] = []
+        import torch.nn.functional as F
+        for (n, hw, cin, cout) in [(64, 56, 64, 64), (64, 56, 64, 256), (64, 56, 256, 64), (64, 28, 128, 512),
+                                   (64, 28, 512, 128), (64, 14, 256, 1024), (64, 14, 1024, 256),
+                                   (64, 7, 512, 2048), (64, 7, 2048, 512)]:
+            M = n * hw * hw
+            x = torch.randn(n, cin, hw, hw, device=dev).to(torch.bfloat16).contiguous(
+                memory_format=torch.channels_last)
+            w = torch.randn(cout, cin, 1, 1, device=dev).to(torch.bfloat16).contiguous(
+                memory_format=torch.channels_last)
+            xm = x.permute(0, 2, 3, 1).reshape(M, cin)
+            wm = w.reshape(cout, cin)
+            want = F.conv2d(x, w).permute(0, 2, 3, 1).reshape(M, cout).float()
+            got = ops.gemm(xm, wm).float()
+            rel = ((got - want).abs().max() / want.abs().max()).item()
+            row = {"shape": [M, cout, cin], "rel_err": rel}
+            for label, fn in (("tcgen05", lambda: ops.gemm(xm, wm)), ("cudnn", lambda: F.conv2d(x, w))):
+                for _ in range(3):
+                    fn()
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                iters = 20
+                e0.record()
+                for _ in range(iters):
+                    fn()
+                e1.record()
+                torch.cuda.synchronize()
+                ms = e0.elapsed_time(e1) / iters
+                gbs = 2.0 * (M * cin + M * cout + cin * cout) / (ms * 1e-3) / 1e9
+                row[label + "_us"] = ms * 1e3
+                row[label + "_gbs"] = gbs
+            OUT["conv1x1"].append(row)
+            print(f"conv1x1 M={M} cin={cin} cout={cout}: rel {rel:.2e}  tcgen05 {row['tcgen05_us']:.1f} us "
+                  f"({row['tcgen05_gbs']:.0f} GB/s)  cudnn {row['cudnn_us']:.1f} us ({row['cudnn_gbs']:.0f} GB/s)",
+                  flush=True)
     OUT["all_ok"] = all_ok
     os.makedirs("gpurun_out", exist_ok=True)
     with open("gpurun_out/gemm_selftest.json", "w") as f:

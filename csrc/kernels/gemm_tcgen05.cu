@@ -17,6 +17,7 @@
 // Reference parity: this is op K1/K2/K3 of SURVEY.md section 2.5 (the Dense layers the reference's
 // workloads run through TensorFlow, e.g. README.md:71-75); the reference itself has no kernel.
 #include <cuda.h>
+#include <stdlib.h>
 
 #include <mutex>
 
@@ -41,6 +42,7 @@ struct GemmArgs {
   int m_tiles, n_tiles, k_blocks;
   uint32_t a_lbo, a_sbo, b_lbo, b_sbo;  // descriptor fields, 16-byte units
   uint32_t a_kadv, b_kadv;              // start-address advance per UMMA_K step, 16-byte units
+  int tma_store;                        // epilogue through smem staging + TMA store (coalesced)
 };
 
 template <int BN>
@@ -49,7 +51,10 @@ struct GemmCfg {
   static constexpr int kBStageBytes = BN * BK * 2;
   static constexpr int kStageBytes = kAStageBytes + kBStageBytes;
   static constexpr int kTmemCols = 2 * BN;
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  // epilogue staging: 4 warps x 2 buffers x (32 rows x 128 B), 128B-swizzled, feeds TMA stores
+  static constexpr int kStagingBytes = 4 * 2 * 4096;
+  static constexpr int kSmemBytes =
+      kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
 __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
@@ -65,7 +70,7 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo,
 template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                    const GemmArgs p) {
+                    const __grid_constant__ CUtensorMap tmC, const GemmArgs p) {
   using Cfg = GemmCfg<BN>;
   constexpr int kStages = Cfg::kStages;
 
@@ -74,7 +79,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                                              ~static_cast<uintptr_t>(1023));
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + kStages * kAStageBytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+  uint8_t* smem_stage = smem + kStages * Cfg::kStageBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_stage + Cfg::kStagingBytes);
   uint64_t* full_bar = bars;                    // [kStages] TMA -> MMA
   uint64_t* empty_bar = bars + kStages;         // [kStages] MMA -> TMA
   uint64_t* tfull_bar = bars + 2 * kStages;     // [2] MMA -> epilogue
@@ -87,6 +93,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    if (p.tma_store) tma_prefetch_desc(&tmC);
     for (int s = 0; s < kStages; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
@@ -186,6 +193,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         out_f32 ? ((p.ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(p.C) & 15) == 0)
                 : ((p.ldc & 7) == 0 && (reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
     int t = 0;
+    int stage_buf = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
       const int acc = t & 1;
       const uint32_t acc_phase = (t >> 1) & 1;
@@ -196,6 +204,72 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+
+      if (p.tma_store) {
+        // Coalesced epilogue: TMEM -> registers -> 128B-swizzled smem tile (32 rows x 128 B per
+        // warp, double buffered) -> TMA store / reduce-add.  Out-of-range rows and columns are
+        // clipped by the tensor map, so no bounds checks are needed here.
+        uint8_t* stg = smem_stage + (warp - 2) * 8192;
+        const int cols_per_chunk = out_f32 ? 32 : 64;
+        for (int c0 = 0; c0 < BN && n0 + c0 < p.N; c0 += cols_per_chunk) {
+          uint8_t* buf = stg + stage_buf * 4096;
+          if (lane == 0) tma_store_wait_read<1>();     // the store that last used this buffer is done
+          __syncwarp();
+          uint8_t* rowp = buf + lane * 128;
+          const int sw = lane & 7;
+          if (out_f32) {
+            uint32_t v[32];
+            tmem_ld_32x32(taddr + c0, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              float f[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const int n = n0 + c0 + j * 4 + e;
+                f[e] = __uint_as_float(v[j * 4 + e]);
+                if (has_bias && n < p.N) f[e] += __ldg(p.bias + n);
+                if (relu) f[e] = fmaxf(f[e], 0.f);
+              }
+              *reinterpret_cast<float4*>(rowp + ((j ^ sw) << 4)) = make_float4(f[0], f[1], f[2], f[3]);
+            }
+          } else {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              uint32_t v[32];
+              tmem_ld_32x32(taddr + c0 + h * 32, v);
+              tmem_ld_wait();
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                float f[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                  const int n = n0 + c0 + h * 32 + j * 8 + e;
+                  f[e] = __uint_as_float(v[j * 8 + e]);
+                  if (has_bias && n < p.N) f[e] += __ldg(p.bias + n);
+                  if (relu) f[e] = fmaxf(f[e], 0.f);
+                }
+                uint4 o;
+                o.x = pack_bf16(f[0], f[1]); o.y = pack_bf16(f[2], f[3]);
+                o.z = pack_bf16(f[4], f[5]); o.w = pack_bf16(f[6], f[7]);
+                *reinterpret_cast<uint4*>(rowp + (((h * 4 + j) ^ sw) << 4)) = o;
+              }
+            }
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            if (accum) tma_reduce_add_2d(&tmC, buf, n0 + c0, m0 + q * 32);
+            else tma_store_2d(&tmC, buf, n0 + c0, m0 + q * 32);
+            tma_store_commit();
+          }
+          stage_buf ^= 1;
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+        continue;
+      }
 
       float row_max = -INFINITY, row_sum = 0.f;
       if (softmax) {
@@ -291,6 +365,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty_bar[acc]);
     }
+    if (p.tma_store && lane == 0) tma_store_wait<0>();   // staging smem must outlive its stores
   }
 
   tc_fence_before();
@@ -320,19 +395,20 @@ static EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-// 2-D bf16 tensor map over a row-major [outer, inner] view with row pitch `ld` elements.
+// 2-D tensor map over a row-major [outer, inner] view with row pitch `ld` elements.
 static int make_tmap(CUtensorMap* tm, const void* base, uint64_t inner, uint64_t outer, uint64_t ld,
-                     uint32_t box_inner, uint32_t box_outer) {
+                     uint32_t box_inner, uint32_t box_outer, bool f32 = false) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) {
     set_last_error("cuTensorMapEncodeTiled entry point not available");
     return CB2_ERR_CUDA;
   }
   cuuint64_t dims[2] = {inner, outer};
-  cuuint64_t strides[1] = {ld * 2};
+  cuuint64_t strides[1] = {ld * (f32 ? 4 : 2)};
   cuuint32_t box[2] = {box_inner, box_outer};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides,
+  CUresult r = fn(tm, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                  const_cast<void*>(base), dims, strides,
                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -360,8 +436,8 @@ static int num_sms() {
 }
 
 template <int BN, bool A_MN, bool B_MN>
-static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& args,
-                       cudaStream_t stream) {
+static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
+                       const GemmArgs& args, cudaStream_t stream) {
   using Cfg = GemmCfg<BN>;
   auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN>;
   static bool configured = false;
@@ -372,7 +448,7 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
   }
   const int tiles = args.m_tiles * args.n_tiles;
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(tmA, tmB, args);
+  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(tmA, tmB, tmC, args);
   return check_cuda(cudaGetLastError(), "gemm_tcgen05 launch");
 }
 
@@ -442,7 +518,22 @@ extern "C" int cb2_gemm_bf16(const void* A, const void* B, void* C, const float*
   else       rc = make_tmap(&tmB, B, N, K, ldb, 64, BK);
   if (rc) return rc;
 
+  // Epilogue through TMA stores whenever the output is TMA-addressable and no per-element side
+  // input (ReLU mask) or row-wide operation (softmax) is requested.
+  const bool out_f32 = (flags & CB2_GEMM_OUT_F32) != 0;
+  const int esize = out_f32 ? 4 : 2;
+  static const bool tma_store_disabled = getenv("TFC_GEMM_NO_TMA_STORE") != nullptr;
+  const bool tma_store = !tma_store_disabled && !softmax && relu_mask == nullptr &&
+                         (reinterpret_cast<uintptr_t>(C) & 15) == 0 &&
+                         ((static_cast<long long>(ldc) * esize) & 15) == 0;
+  CUtensorMap tmC = tmA;
+  if (tma_store) {
+    rc = make_tmap(&tmC, C, N, M, ldc, out_f32 ? 32 : 64, 32, out_f32);
+    if (rc) return rc;
+  }
+
   GemmArgs args;
+  args.tma_store = tma_store ? 1 : 0;
   args.M = M; args.N = N; args.K = K;
   args.ldc = ldc; args.ldmask = ldmask;
   args.C = C; args.bias = bias;
@@ -469,10 +560,10 @@ extern "C" int cb2_gemm_bf16(const void* A, const void* B, void* C, const float*
 
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
 #define CB2_DISPATCH(BNV)                                                            \
-  if (!a_mn && !b_mn) return launch_gemm<BNV, false, false>(tmA, tmB, args, s);      \
-  if (!a_mn && b_mn) return launch_gemm<BNV, false, true>(tmA, tmB, args, s);        \
-  if (a_mn && b_mn) return launch_gemm<BNV, true, true>(tmA, tmB, args, s);          \
-  return launch_gemm<BNV, true, false>(tmA, tmB, args, s);
+  if (!a_mn && !b_mn) return launch_gemm<BNV, false, false>(tmA, tmB, tmC, args, s); \
+  if (!a_mn && b_mn) return launch_gemm<BNV, false, true>(tmA, tmB, tmC, args, s);   \
+  if (a_mn && b_mn) return launch_gemm<BNV, true, true>(tmA, tmB, tmC, args, s);     \
+  return launch_gemm<BNV, true, false>(tmA, tmB, tmC, args, s);
   if (bn == 64) { CB2_DISPATCH(64) }
   if (bn == 128) { CB2_DISPATCH(128) }
   CB2_DISPATCH(256)
