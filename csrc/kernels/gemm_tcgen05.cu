@@ -43,6 +43,7 @@ struct GemmArgs {
   uint32_t a_lbo, a_sbo, b_lbo, b_sbo;  // descriptor fields, 16-byte units
   uint32_t a_kadv, b_kadv;              // start-address advance per UMMA_K step, 16-byte units
   int tma_store;                        // epilogue through smem staging + TMA store (coalesced)
+  int debug;                            // bench/gemm_epilogue_probe.py: skip parts of the epilogue
 };
 
 template <int BN>
@@ -52,7 +53,8 @@ struct GemmCfg {
   static constexpr int kStageBytes = kAStageBytes + kBStageBytes;
   static constexpr int kTmemCols = 2 * BN;
   // epilogue staging: 4 warps x 2 buffers x (32 rows x 128 B), 128B-swizzled, feeds TMA stores
-  static constexpr int kStagingBytes = 4 * 2 * 4096;
+  static constexpr int kStagingBytes = 4 * 2 * 4096 + BN * 4;   // + bias copy
+  static_assert(kStages * kStageBytes + kStagingBytes + 1024 + 256 <= 232448, "smem budget");
   static constexpr int kSmemBytes =
       kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
@@ -65,6 +67,90 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo,
   d |= 1ull << 46;  // descriptor version: Blackwell
   d |= 2ull << 61;  // SWIZZLE_128B
   return d;
+}
+
+// Coalesced epilogue of one 32-row slice of an accumulator tile: TMEM -> registers -> 128B-swizzled
+// smem tile (32 rows x 128 B, double buffered per warp) -> TMA store / reduce-add.  Rows and
+// columns outside the matrix are clipped by the tensor map.  Each scheduler runs a single
+// epilogue warp, so every latency in here is exposed: the TMEM load of chunk i+1 is issued before
+// chunk i is converted, the element loop is straight-line code (bias from a smem copy, ReLU as a
+// max with 0 or -inf, or neither when `plain`), and all addresses are explicit shared addresses.
+template <int BN, bool F32>
+__device__ __forceinline__ void epilogue_tma(const CUtensorMap* tmC, uint32_t taddr, uint32_t stg,
+                                             uint32_t sbias, int& stage_buf, int n0, int row0, int N,
+                                             float lo, bool plain, bool accum, int lane) {
+  constexpr int COLS = F32 ? 32 : 64;
+  constexpr int NCH = BN / COLS;
+  constexpr int NLD = F32 ? 1 : 2;
+  uint32_t v[2][NLD][32];
+  const uint32_t sw = lane & 7;
+  const int rem = N - n0;
+  const int nch = rem >= BN ? NCH : (rem + COLS - 1) / COLS;
+#pragma unroll
+  for (int l = 0; l < NLD; ++l) tmem_ld_32x32(taddr + l * 32, v[0][l]);
+#pragma unroll
+  for (int ci = 0; ci < NCH; ++ci) {
+    if (ci < nch) {
+      uint32_t(&cur)[NLD][32] = v[ci & 1];
+      tmem_ld_wait_for(cur[0]);
+      if (NLD > 1) reg_fence(cur[NLD - 1]);
+      if (ci + 1 < NCH && ci + 1 < nch) {
+#pragma unroll
+        for (int l = 0; l < NLD; ++l) tmem_ld_32x32(taddr + (ci + 1) * COLS + l * 32, v[(ci + 1) & 1][l]);
+      }
+      const uint32_t buf = stg + stage_buf * 4096;
+      const uint32_t rowp = buf + lane * 128;
+      if (lane == 0) tma_store_wait_read<1>();   // the store that last read this buffer is done
+      __syncwarp();
+      if (F32) {
+        if (plain) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            st_shared_v4(rowp + ((j ^ sw) << 4), cur[0][j * 4], cur[0][j * 4 + 1], cur[0][j * 4 + 2],
+                         cur[0][j * 4 + 3]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 bb = ld_shared_f4(sbias + (ci * COLS + j * 4) * 4);
+            const float f0 = fmaxf(__uint_as_float(cur[0][j * 4 + 0]) + bb.x, lo);
+            const float f1 = fmaxf(__uint_as_float(cur[0][j * 4 + 1]) + bb.y, lo);
+            const float f2 = fmaxf(__uint_as_float(cur[0][j * 4 + 2]) + bb.z, lo);
+            const float f3 = fmaxf(__uint_as_float(cur[0][j * 4 + 3]) + bb.w, lo);
+            st_shared_v4(rowp + ((j ^ sw) << 4), __float_as_uint(f0), __float_as_uint(f1),
+                         __float_as_uint(f2), __float_as_uint(f3));
+          }
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint32_t* w = &cur[NLD - 1 < j / 4 ? NLD - 1 : j / 4][(j & 3) * 8];
+          uint32_t o0, o1, o2, o3;
+          if (plain) {
+            o0 = pack_bf16(__uint_as_float(w[0]), __uint_as_float(w[1]));
+            o1 = pack_bf16(__uint_as_float(w[2]), __uint_as_float(w[3]));
+            o2 = pack_bf16(__uint_as_float(w[4]), __uint_as_float(w[5]));
+            o3 = pack_bf16(__uint_as_float(w[6]), __uint_as_float(w[7]));
+          } else {
+            const float4 b0 = ld_shared_f4(sbias + (ci * COLS + j * 8) * 4);
+            const float4 b1 = ld_shared_f4(sbias + (ci * COLS + j * 8 + 4) * 4);
+            o0 = pack_bf16(fmaxf(__uint_as_float(w[0]) + b0.x, lo), fmaxf(__uint_as_float(w[1]) + b0.y, lo));
+            o1 = pack_bf16(fmaxf(__uint_as_float(w[2]) + b0.z, lo), fmaxf(__uint_as_float(w[3]) + b0.w, lo));
+            o2 = pack_bf16(fmaxf(__uint_as_float(w[4]) + b1.x, lo), fmaxf(__uint_as_float(w[5]) + b1.y, lo));
+            o3 = pack_bf16(fmaxf(__uint_as_float(w[6]) + b1.z, lo), fmaxf(__uint_as_float(w[7]) + b1.w, lo));
+          }
+          st_shared_v4(rowp + ((j ^ sw) << 4), o0, o1, o2, o3);
+        }
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        if (accum) tma_reduce_add_2d(tmC, buf, n0 + ci * COLS, row0);
+        else tma_store_2d(tmC, buf, n0 + ci * COLS, row0);
+        tma_store_commit();
+      }
+      stage_buf ^= 1;
+    }
+  }
 }
 
 template <int BN, bool A_MN, bool B_MN>
@@ -206,64 +292,28 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
 
       if (p.tma_store) {
-        // Coalesced epilogue: TMEM -> registers -> 128B-swizzled smem tile (32 rows x 128 B per
-        // warp, double buffered) -> TMA store / reduce-add.  Out-of-range rows and columns are
-        // clipped by the tensor map, so no bounds checks are needed here.
-        uint8_t* stg = smem_stage + (warp - 2) * 8192;
-        const int cols_per_chunk = out_f32 ? 32 : 64;
-        for (int c0 = 0; c0 < BN && n0 + c0 < p.N; c0 += cols_per_chunk) {
-          uint8_t* buf = stg + stage_buf * 4096;
-          if (lane == 0) tma_store_wait_read<1>();     // the store that last used this buffer is done
-          __syncwarp();
-          uint8_t* rowp = buf + lane * 128;
-          const int sw = lane & 7;
-          if (out_f32) {
-            uint32_t v[32];
-            tmem_ld_32x32(taddr + c0, v);
-            tmem_ld_wait();
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              float f[4];
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const int n = n0 + c0 + j * 4 + e;
-                f[e] = __uint_as_float(v[j * 4 + e]);
-                if (has_bias && n < p.N) f[e] += __ldg(p.bias + n);
-                if (relu) f[e] = fmaxf(f[e], 0.f);
-              }
-              *reinterpret_cast<float4*>(rowp + ((j ^ sw) << 4)) = make_float4(f[0], f[1], f[2], f[3]);
-            }
-          } else {
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-              uint32_t v[32];
-              tmem_ld_32x32(taddr + c0 + h * 32, v);
-              tmem_ld_wait();
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                float f[8];
-#pragma unroll
-                for (int e = 0; e < 8; ++e) {
-                  const int n = n0 + c0 + h * 32 + j * 8 + e;
-                  f[e] = __uint_as_float(v[j * 8 + e]);
-                  if (has_bias && n < p.N) f[e] += __ldg(p.bias + n);
-                  if (relu) f[e] = fmaxf(f[e], 0.f);
-                }
-                uint4 o;
-                o.x = pack_bf16(f[0], f[1]); o.y = pack_bf16(f[2], f[3]);
-                o.z = pack_bf16(f[4], f[5]); o.w = pack_bf16(f[6], f[7]);
-                *reinterpret_cast<uint4*>(rowp + (((h * 4 + j) ^ sw) << 4)) = o;
-              }
-            }
+        // one bias copy for the four epilogue warps (they are at most one tile apart, hence the
+        // named barrier before it is overwritten and after it is filled)
+        const uint32_t sbias = smem_u32(smem_stage) + 4 * 8192;
+        if (has_bias || t == 0) {
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          for (int i = threadIdx.x - 64; i < BN; i += 128) {
+            const int n = n0 + i;
+            const float bv = (has_bias && n < p.N) ? __ldg(p.bias + n) : 0.f;
+            asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbias + i * 4), "f"(bv) : "memory");
           }
-          fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) {
-            if (accum) tma_reduce_add_2d(&tmC, buf, n0 + c0, m0 + q * 32);
-            else tma_store_2d(&tmC, buf, n0 + c0, m0 + q * 32);
-            tma_store_commit();
-          }
-          stage_buf ^= 1;
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+        }
+        const float lo = relu ? 0.f : -INFINITY;
+        const bool plain = !has_bias && !relu;
+        const uint32_t stg = smem_u32(smem_stage) + (warp - 2) * 8192;
+        if (!(p.debug & 16)) {
+          if (out_f32)
+            epilogue_tma<BN, true>(&tmC, taddr, stg, sbias, stage_buf, n0, m0 + q * 32, p.N, lo, plain,
+                                   accum, lane);
+          else
+            epilogue_tma<BN, false>(&tmC, taddr, stg, sbias, stage_buf, n0, m0 + q * 32, p.N, lo, plain,
+                                    accum, lane);
         }
         tc_fence_before();
         __syncwarp();
@@ -456,6 +506,12 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUt
 
 using namespace cb2;
 
+static int g_epilogue_debug = 0;
+extern "C" int cb2_gemm_debug_epilogue(int bits) {
+  g_epilogue_debug = bits;
+  return 0;
+}
+
 extern "C" int cb2_gemm_debug_descriptors(int enable, unsigned a_lbo, unsigned a_sbo, unsigned b_lbo,
                                           unsigned b_sbo, unsigned a_kadv, unsigned b_kadv) {
   g_desc_override.on = enable != 0;
@@ -534,6 +590,7 @@ extern "C" int cb2_gemm_bf16(const void* A, const void* B, void* C, const float*
 
   GemmArgs args;
   args.tma_store = tma_store ? 1 : 0;
+  args.debug = g_epilogue_debug;
   args.M = M; args.N = N; args.K = K;
   args.ldc = ldc; args.ldmask = ldmask;
   args.C = C; args.bias = bias;

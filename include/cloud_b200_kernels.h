@@ -44,6 +44,8 @@ int cb2_gemm_bf16(const void* A, const void* B, void* C, const float* bias /*nul
                   int N, int K, int lda, int ldb, int ldc, int ldmask, int a_mn, int b_mn,
                   unsigned flags, int block_n /*0 = auto, else 64|128|256*/, void* stream);
 /* Test hook: override the shared-memory matrix-descriptor fields (16-byte units). */
+/* Diagnostics only (bench/gemm_epilogue_probe.py): bit mask of epilogue phases to skip. */
+int cb2_gemm_debug_epilogue(int bits);
 int cb2_gemm_debug_descriptors(int enable, unsigned a_lbo, unsigned a_sbo, unsigned b_lbo,
                                unsigned b_sbo, unsigned a_kadv, unsigned b_kadv);
 
