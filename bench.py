@@ -116,6 +116,7 @@ def main() -> int:
     ap.add_argument("--batch-per-gpu", type=int, default=64)
     ap.add_argument("--classes", type=int, default=1000)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--profile-e2e", action="store_true", help="cProfile of the timed fit() to stderr")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
@@ -212,11 +213,23 @@ def main() -> int:
                   verbose=0, callbacks=[ReadLoss()])
         sync()
         seen.clear()
+        prof = None
+        if args.profile_e2e:
+            import cProfile
+            prof = cProfile.Profile()
+            prof.enable()
         t0 = time.perf_counter()
         model.fit(host_x, host_y, batch_size=B * world, epochs=1, shuffle=False, verbose=0,
                   callbacks=[ReadLoss()])
         sync()
         dt = time.perf_counter() - t0
+        if prof is not None:
+            import io
+            import pstats
+            prof.disable()
+            buf = io.StringIO()
+            pstats.Stats(prof, stream=buf).sort_stats("cumulative").print_stats(35)
+            print(buf.getvalue()[:8000], file=sys.stderr)
         tt = torch.tensor([dt], device=dev, dtype=torch.float64)
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)

@@ -2,9 +2,9 @@
 // a one-pass statistics reduction; backward in two passes (reduce, apply) with the ReLU mask and
 // the residual gradient folded in.  bf16 activations, fp32 statistics / parameters.
 //
-// Layout: x is [M, C] row-major (M = N*H*W, channels_last), C a multiple of 8 and <= 2048.  A CTA
-// of 256 threads covers 256/(C/8) rows per iteration; each thread owns 8 consecutive channels and
-// moves them with one 16-byte access, so every warp reads/writes whole 128-byte lines.
+// Layout: x is [M, C] row-major (M = N*H*W, channels_last), C = 8, 16, 32 or a multiple of 64, at
+// most 2048.  Each thread owns 8 consecutive channels and moves them with one 16-byte access; a
+// CTA of 256 threads owns a 64-channel slab of a group of rows (see BnMap).
 //
 // Reference workload: the BatchNormalization layers of ResNet-50 (K8 in SURVEY.md section 2.5;
 // core/tests/examples/call_run_within_script_with_keras_fit.py:79-83) which TensorFlow runs as
@@ -21,92 +21,111 @@ constexpr int kBnThreads = 256;
 // replica they - not HBM - set the kernel time (measured: 60 us floor per launch).
 constexpr int kBnCopies = 8;
 
-struct BnGeom {
-  int tpr;       // threads per row = C / 8
-  int rows;      // rows per CTA iteration = 256 / tpr
+// Work split.  The [M, C] matrix is cut into channel slabs of W = min(C, 64) channels (128 bytes
+// of every row) and row groups; CTA b owns slab b % slabs and row group b / slabs, so CTAs that run
+// at the same time still sweep contiguous memory.  Inside a CTA a thread keeps 8 fixed channels
+// (one 16-byte access per row) and W/8 threads share a row, i.e. a warp touches whole 128-byte
+// lines.  Because a CTA only ever sees W channels, the end-of-kernel reduction costs 2*W atomics per
+// CTA whatever C is (a CTA that spans all of C needs 2*C: 1.2 M atomics for C = 1024, which - not
+// the 25 MB of data - set the time of the 14x14 and 7x7 layers).
+struct BnMap {
+  int tpr;     // threads per row = W / 8  (1, 2, 4 or 8)
+  int rows;    // rows per CTA iteration = 256 / tpr
+  int w;       // slab width in channels
+  int cbase;   // first channel of the slab
+  int c8;      // first of this thread's 8 channels
+  int rlane;   // this thread's row inside an iteration
+  int row0;    // first row of this CTA
+  int stride;  // row step between iterations
+  int rg;      // row group
 };
 
-__device__ __forceinline__ void bn_block_reduce_to_global(float (&a)[8], float (&b)[8], int tpr,
-                                                          int rows, int rlane, int c8, int C,
-                                                          float* __restrict__ out, float* smem) {
-  // smem: [rows][tpr*8] x 2
-  if (rows > 1) {
-    float* sa = smem;
-    float* sb = smem + rows * tpr * 8;
-    const int col = (threadIdx.x % tpr) * 8;
+__device__ __forceinline__ BnMap bn_map(int C) {
+  BnMap m;
+  m.w = C < 64 ? C : 64;
+  m.tpr = m.w >> 3;
+  m.rows = kBnThreads / m.tpr;
+  const int slabs = C / m.w;
+  const int slab = blockIdx.x % slabs;
+  m.rg = blockIdx.x / slabs;
+  const int nrg = gridDim.x / slabs;
+  m.cbase = slab * m.w;
+  m.c8 = m.cbase + (threadIdx.x % m.tpr) * 8;
+  m.rlane = threadIdx.x / m.tpr;
+  m.row0 = m.rg * m.rows + m.rlane;
+  m.stride = nrg * m.rows;
+  return m;
+}
+
+// CTA-wide sum of (a, b) over rows, then one atomic per channel and quantity into replica
+// rg % kBnCopies of the [2C] accumulator.
+__device__ __forceinline__ void bn_block_reduce_to_global(float (&a)[8], float (&b)[8],
+                                                          const BnMap& m, int C,
+                                                          float* __restrict__ out) {
+  __shared__ float s_part[kBnThreads / 32][2][64];
+  // lanes that differ in bits >= log2(tpr) hold other rows of the same channels
+  for (int off = 16; off >= m.tpr; off >>= 1) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      sa[rlane * tpr * 8 + col + j] = a[j];
-      sb[rlane * tpr * 8 + col + j] = b[j];
-    }
-    __syncthreads();
-    if (rlane == 0) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float s = 0.f, q = 0.f;
-        for (int r = 0; r < rows; ++r) {
-          s += sa[r * tpr * 8 + col + j];
-          q += sb[r * tpr * 8 + col + j];
-        }
-        a[j] = s;
-        b[j] = q;
-      }
+      a[j] += __shfl_xor_sync(0xffffffffu, a[j], off);
+      b[j] += __shfl_xor_sync(0xffffffffu, b[j], off);
     }
   }
-  if (rlane == 0) {
-    float* dst = out + static_cast<size_t>(blockIdx.x % kBnCopies) * 2 * C;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane < m.tpr) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      atomicAdd(dst + c8 + j, a[j]);
-      atomicAdd(dst + C + c8 + j, b[j]);
+      s_part[warp][0][lane * 8 + j] = a[j];
+      s_part[warp][1][lane * 8 + j] = b[j];
     }
+  }
+  __syncthreads();
+  if (threadIdx.x < 2 * m.w) {
+    const int which = threadIdx.x / m.w, c = threadIdx.x % m.w;
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < kBnThreads / 32; ++w) t += s_part[w][which][c];
+    atomicAdd(out + static_cast<size_t>(m.rg % kBnCopies) * 2 * C + which * C + m.cbase + c, t);
   }
 }
 
-// Sum the replicas for this thread's 8 channels; one row-lane does it, the others read smem.
-__device__ __forceinline__ void bn_gather_sums(const float* __restrict__ sums, int C, int c8,
-                                               int rlane, float* s_a, float* s_b,
-                                               float (&a)[8], float (&b)[8]) {
-  if (rlane == 0) {
+// Totals of this thread's 8 channels: 2*W threads add up the replicas, the rest read smem.
+__device__ __forceinline__ void bn_gather_sums(const float* __restrict__ sums, int C,
+                                               const BnMap& m, float (&a)[8], float (&b)[8]) {
+  __shared__ float s_tot[2][64];
+  if (threadIdx.x < 2 * m.w) {
+    const int which = threadIdx.x / m.w, c = threadIdx.x % m.w;
+    float v[kBnCopies];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) a[j] = b[j] = 0.f;
+    for (int k = 0; k < kBnCopies; ++k)      // unrolled: all replica loads in flight together
+      v[k] = sums[static_cast<size_t>(k) * 2 * C + which * C + m.cbase + c];
+    float t = 0.f;
 #pragma unroll
-    for (int k = 0; k < kBnCopies; ++k) {   // unrolled: all replica loads in flight together
-      const float* src = sums + static_cast<size_t>(k) * 2 * C;
-      const float4 a0 = *reinterpret_cast<const float4*>(src + c8);
-      const float4 a1 = *reinterpret_cast<const float4*>(src + c8 + 4);
-      const float4 b0 = *reinterpret_cast<const float4*>(src + C + c8);
-      const float4 b1 = *reinterpret_cast<const float4*>(src + C + c8 + 4);
-      a[0] += a0.x; a[1] += a0.y; a[2] += a0.z; a[3] += a0.w;
-      a[4] += a1.x; a[5] += a1.y; a[6] += a1.z; a[7] += a1.w;
-      b[0] += b0.x; b[1] += b0.y; b[2] += b0.z; b[3] += b0.w;
-      b[4] += b1.x; b[5] += b1.y; b[6] += b1.z; b[7] += b1.w;
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) { s_a[c8 + j] = a[j]; s_b[c8 + j] = b[j]; }
+    for (int k = 0; k < kBnCopies; ++k) t += v[k];
+    s_tot[which][c] = t;
   }
   __syncthreads();
+  const int cl = (threadIdx.x % m.tpr) * 8;
 #pragma unroll
-  for (int j = 0; j < 8; ++j) { a[j] = s_a[c8 + j]; b[j] = s_b[c8 + j]; }
+  for (int j = 0; j < 8; ++j) { a[j] = s_tot[0][cl + j]; b[j] = s_tot[1][cl + j]; }
 }
 
 // sums[0:C] += sum_m x ; sums[C:2C] += sum_m x^2
 __global__ void __launch_bounds__(kBnThreads)
 bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ sums, int M, int C) {
-  extern __shared__ float smem[];
-  const int tpr = C >> 3, rows = kBnThreads / tpr;
-  const int rlane = threadIdx.x / tpr, c8 = (threadIdx.x % tpr) * 8;
+  const BnMap m = bn_map(C);
   float s[8], q[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
-  const int stride = gridDim.x * rows;
-  int row = blockIdx.x * rows + rlane;
+  const int stride = m.stride;
+  const __nv_bfloat16* xp = x + m.c8;
+  int row = m.row0;
   // four rows in flight per thread
   for (; row + 3 * stride < M; row += 4 * stride) {
-    const uint4 w0 = ld_stream_v4(x + static_cast<size_t>(row) * C + c8);
-    const uint4 w1 = ld_stream_v4(x + static_cast<size_t>(row + stride) * C + c8);
-    const uint4 w2 = ld_stream_v4(x + static_cast<size_t>(row + 2 * stride) * C + c8);
-    const uint4 w3 = ld_stream_v4(x + static_cast<size_t>(row + 3 * stride) * C + c8);
+    const uint4 w0 = ld_stream_v4(xp + static_cast<size_t>(row) * C);
+    const uint4 w1 = ld_stream_v4(xp + static_cast<size_t>(row + stride) * C);
+    const uint4 w2 = ld_stream_v4(xp + static_cast<size_t>(row + 2 * stride) * C);
+    const uint4 w3 = ld_stream_v4(xp + static_cast<size_t>(row + 3 * stride) * C);
     const Vec8 a = unpack8_bf16(w0), b = unpack8_bf16(w1), c = unpack8_bf16(w2), d = unpack8_bf16(w3);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -115,18 +134,26 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ sums, i
     }
   }
   for (; row < M; row += stride) {
-    const Vec8 a = unpack8_bf16(ld_stream_v4(x + static_cast<size_t>(row) * C + c8));
+    const Vec8 a = unpack8_bf16(ld_stream_v4(xp + static_cast<size_t>(row) * C));
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       s[j] += a.v[j];
       q[j] = fmaf(a.v[j], a.v[j], q[j]);
     }
   }
-  bn_block_reduce_to_global(s, q, tpr, rows, rlane, c8, C, sums, smem);
+  bn_block_reduce_to_global(s, q, m, C, sums);
 }
 
-// y = act(x * scale + shift (+ residual)); training: scale/shift from the batch sums (and block 0
-// refreshes the running statistics and the saved mean / inv-std); inference: from running stats.
+__device__ __forceinline__ Vec8 bn_affine(const Vec8& v, const float (&sc)[8], const float (&sh)[8]) {
+  Vec8 o;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) o.v[j] = fmaf(v.v[j], sc[j], sh[j]);
+  return o;
+}
+
+// y = act(x * scale + shift (+ residual)); training: scale/shift from the batch sums (and row
+// group 0 refreshes the running statistics and the saved mean / inv-std); inference: from the
+// running statistics.
 __global__ void __launch_bounds__(kBnThreads)
 bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res,
                 __nv_bfloat16* __restrict__ y, const float* __restrict__ sums,
@@ -135,15 +162,13 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
                 float* __restrict__ save_mean, float* __restrict__ save_invstd,
                 const float* __restrict__ mean_bias, int M, int C, float eps, float momentum,
                 int relu, int training) {
-  __shared__ float s_a[2048], s_b[2048];
-  const int tpr = C >> 3, rows = kBnThreads / tpr;
-  const int rlane = threadIdx.x / tpr, c8 = (threadIdx.x % tpr) * 8;
+  const BnMap m = bn_map(C);
   float sc[8], sh[8], tot[8], totsq[8];
   const float invM = 1.f / static_cast<float>(M);
-  if (training) bn_gather_sums(sums, C, c8, rlane, s_a, s_b, tot, totsq);
+  if (training) bn_gather_sums(sums, C, m, tot, totsq);
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
-    const int c = c8 + j;
+    const int c = m.c8 + j;
     float mean, var;
     if (training) {
       mean = tot[j] * invM;
@@ -155,7 +180,7 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
     const float istd = rsqrtf(var + eps);
     sc[j] = gamma[c] * istd;
     sh[j] = beta[c] - mean * sc[j];
-    if (training && blockIdx.x == 0 && rlane == 0) {
+    if (training && m.rg == 0 && m.rlane == 0) {
       save_mean[c] = mean;
       save_invstd[c] = istd;
       const float unbiased = M > 1 ? var * static_cast<float>(M) / static_cast<float>(M - 1) : var;
@@ -164,174 +189,211 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
       run_var[c] = (1.f - momentum) * run_var[c] + momentum * unbiased;
     }
   }
-  const int stride = gridDim.x * rows;
-  for (int row = blockIdx.x * rows + rlane; row < M; row += stride) {
-    const size_t idx = static_cast<size_t>(row) * C + c8;
-    Vec8 v = unpack8_bf16(ld_stream_v4(x + idx));
+  const float lo = relu ? 0.f : -INFINITY;
+  const int stride = m.stride;
+  int row = m.row0;
+  // two rows (up to four 16-byte loads) in flight per thread; y is re-read by the next conv, so
+  // it is written with default caching (stays in L2)
+  for (; row + stride < M; row += 2 * stride) {
+    const size_t i0 = static_cast<size_t>(row) * C + m.c8;
+    const size_t i1 = static_cast<size_t>(row + stride) * C + m.c8;
+    const uint4 wx0 = ld_stream_v4(x + i0), wx1 = ld_stream_v4(x + i1);
+    Vec8 v0 = bn_affine(unpack8_bf16(wx0), sc, sh), v1 = bn_affine(unpack8_bf16(wx1), sc, sh);
+    if (res) {
+      const Vec8 r0 = unpack8_bf16(ld_stream_v4(res + i0)), r1 = unpack8_bf16(ld_stream_v4(res + i1));
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { v0.v[j] += r0.v[j]; v1.v[j] += r1.v[j]; }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { v0.v[j] = fmaxf(v0.v[j], lo); v1.v[j] = fmaxf(v1.v[j], lo); }
+    *reinterpret_cast<uint4*>(y + i0) = pack8_bf16(v0);
+    *reinterpret_cast<uint4*>(y + i1) = pack8_bf16(v1);
+  }
+  for (; row < M; row += stride) {
+    const size_t idx = static_cast<size_t>(row) * C + m.c8;
+    Vec8 v = bn_affine(unpack8_bf16(ld_stream_v4(x + idx)), sc, sh);
     if (res) {
       const Vec8 r = unpack8_bf16(ld_stream_v4(res + idx));
 #pragma unroll
-      for (int j = 0; j < 8; ++j) v.v[j] = fmaf(v.v[j], sc[j], sh[j]) + r.v[j];
-    } else {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v.v[j] = fmaf(v.v[j], sc[j], sh[j]);
+      for (int j = 0; j < 8; ++j) v.v[j] += r.v[j];
     }
-    if (relu) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) v.v[j] = fmaxf(v.v[j], 0.f);
-    }
-    *reinterpret_cast<uint4*>(y + idx) = pack8_bf16(v);   // y is re-read by the next conv: keep in L2
+    for (int j = 0; j < 8; ++j) v.v[j] = fmaxf(v.v[j], lo);
+    *reinterpret_cast<uint4*>(y + idx) = pack8_bf16(v);
   }
 }
 
-// sums[0:C] += sum dz ; sums[C:2C] += sum dz * xhat,  dz = dy * (y > 0 if relu)
+// dz = dy * (y > 0) when a ReLU follows the BN.  Without a saved output the mask is recomputed
+// from x (y > 0 <=> x*sc + sh > 0), which saves reading y - one of three activation-sized reads -
+// for every BN+ReLU without shortcut.
+template <int MODE /*0 none, 1 from y, 2 from x*/>
+__device__ __forceinline__ void bn_mask(Vec8& g, const Vec8& xv, const uint4& wy, const float (&sc)[8],
+                                        const float (&sh)[8]) {
+  if (MODE == 1) {
+    const Vec8 yv = unpack8_bf16(wy);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g.v[j] = yv.v[j] > 0.f ? g.v[j] : 0.f;
+  } else if (MODE == 2) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g.v[j] = fmaf(xv.v[j], sc[j], sh[j]) > 0.f ? g.v[j] : 0.f;
+  }
+}
+
+// sums[0:C] += sum dz ; sums[C:2C] += sum dz * xhat
+template <int MODE>
 __global__ void __launch_bounds__(kBnThreads)
 bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
                      const __nv_bfloat16* __restrict__ x, const float* __restrict__ save_mean,
                      const float* __restrict__ save_invstd, const float* __restrict__ gamma,
-                     const float* __restrict__ beta, float* __restrict__ sums, int M, int C,
-                     int relu) {
-  extern __shared__ float smem[];
-  const int tpr = C >> 3, rows = kBnThreads / tpr;
-  const int rlane = threadIdx.x / tpr, c8 = (threadIdx.x % tpr) * 8;
-  // relu without a saved output: the mask is recomputed from x (y > 0 <=> x*sc + sh > 0), which
-  // saves reading y - one of three activation-sized reads - for every BN+ReLU without shortcut
-  const bool mask_from_x = relu && y == nullptr;
-  const bool mask_from_y = relu && y != nullptr;
-  float mean[8], istd[8], db[8], dg[8], sc[8], sh[8];
+                     const float* __restrict__ beta, float* __restrict__ sums, int M, int C) {
+  const BnMap m = bn_map(C);
+  // xhat = x * istd + nm  (nm = -mean * istd)
+  float istd[8], nm[8], db[8], dg[8], sc[8], sh[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
-    mean[j] = save_mean[c8 + j];
-    istd[j] = save_invstd[c8 + j];
-    sc[j] = gamma[c8 + j] * istd[j];
-    sh[j] = beta[c8 + j] - mean[j] * sc[j];
+    const int c = m.c8 + j;
+    istd[j] = save_invstd[c];
+    nm[j] = -save_mean[c] * istd[j];
+    sc[j] = gamma[c] * istd[j];
+    sh[j] = fmaf(gamma[c], nm[j], beta[c]);
     db[j] = dg[j] = 0.f;
   }
-  const int stride = gridDim.x * rows;
-  int row = blockIdx.x * rows + rlane;
+  const int stride = m.stride;
+  int row = m.row0;
   // two rows (up to six 16-byte loads) in flight per thread
   for (; row + stride < M; row += 2 * stride) {
-    const size_t i0 = static_cast<size_t>(row) * C + c8;
-    const size_t i1 = static_cast<size_t>(row + stride) * C + c8;
+    const size_t i0 = static_cast<size_t>(row) * C + m.c8;
+    const size_t i1 = static_cast<size_t>(row + stride) * C + m.c8;
     const uint4 wg0 = ld_stream_v4(dy + i0), wg1 = ld_stream_v4(dy + i1);
     const uint4 wx0 = ld_stream_v4(x + i0), wx1 = ld_stream_v4(x + i1);
     uint4 wy0 = make_uint4(0, 0, 0, 0), wy1 = wy0;
-    if (mask_from_y) { wy0 = ld_stream_v4(y + i0); wy1 = ld_stream_v4(y + i1); }
+    if (MODE == 1) { wy0 = ld_stream_v4(y + i0); wy1 = ld_stream_v4(y + i1); }
     Vec8 g0 = unpack8_bf16(wg0), g1 = unpack8_bf16(wg1);
     const Vec8 x0 = unpack8_bf16(wx0), x1 = unpack8_bf16(wx1);
-    if (mask_from_y) {
-      const Vec8 y0 = unpack8_bf16(wy0), y1 = unpack8_bf16(wy1);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        g0.v[j] = y0.v[j] > 0.f ? g0.v[j] : 0.f;
-        g1.v[j] = y1.v[j] > 0.f ? g1.v[j] : 0.f;
-      }
-    } else if (mask_from_x) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        g0.v[j] = fmaf(x0.v[j], sc[j], sh[j]) > 0.f ? g0.v[j] : 0.f;
-        g1.v[j] = fmaf(x1.v[j], sc[j], sh[j]) > 0.f ? g1.v[j] : 0.f;
-      }
-    }
+    bn_mask<MODE>(g0, x0, wy0, sc, sh);
+    bn_mask<MODE>(g1, x1, wy1, sc, sh);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       db[j] += g0.v[j] + g1.v[j];
-      dg[j] = fmaf(g0.v[j], (x0.v[j] - mean[j]) * istd[j],
-                   fmaf(g1.v[j], (x1.v[j] - mean[j]) * istd[j], dg[j]));
+      dg[j] = fmaf(g0.v[j], fmaf(x0.v[j], istd[j], nm[j]),
+                   fmaf(g1.v[j], fmaf(x1.v[j], istd[j], nm[j]), dg[j]));
     }
   }
   for (; row < M; row += stride) {
-    const size_t idx = static_cast<size_t>(row) * C + c8;
+    const size_t idx = static_cast<size_t>(row) * C + m.c8;
     Vec8 g = unpack8_bf16(ld_stream_v4(dy + idx));
     const Vec8 xv = unpack8_bf16(ld_stream_v4(x + idx));
-    if (mask_from_y) {
-      const Vec8 yv = unpack8_bf16(ld_stream_v4(y + idx));
-#pragma unroll
-      for (int j = 0; j < 8; ++j) g.v[j] = yv.v[j] > 0.f ? g.v[j] : 0.f;
-    } else if (mask_from_x) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) g.v[j] = fmaf(xv.v[j], sc[j], sh[j]) > 0.f ? g.v[j] : 0.f;
-    }
+    uint4 wy = make_uint4(0, 0, 0, 0);
+    if (MODE == 1) wy = ld_stream_v4(y + idx);
+    bn_mask<MODE>(g, xv, wy, sc, sh);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       db[j] += g.v[j];
-      dg[j] = fmaf(g.v[j], (xv.v[j] - mean[j]) * istd[j], dg[j]);
+      dg[j] = fmaf(g.v[j], fmaf(xv.v[j], istd[j], nm[j]), dg[j]);
     }
   }
-  bn_block_reduce_to_global(db, dg, tpr, rows, rlane, c8, C, sums, smem);
+  bn_block_reduce_to_global(db, dg, m, C, sums);
 }
 
 // dx = gamma * istd * (dz - dbeta/M - xhat * dgamma/M) ; optionally dres = dz
+template <int MODE>
 __global__ void __launch_bounds__(kBnThreads)
 bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
                     const __nv_bfloat16* __restrict__ x, const float* __restrict__ save_mean,
                     const float* __restrict__ save_invstd, const float* __restrict__ gamma,
                     const float* __restrict__ beta, const float* __restrict__ sums,
-                    float* __restrict__ dbeta_out,
-                    float* __restrict__ dgamma_out, __nv_bfloat16* __restrict__ dx,
-                    __nv_bfloat16* __restrict__ dres, int M, int C, int relu) {
-  __shared__ float s_a[2048], s_b[2048];
-  const int tpr = C >> 3, rows = kBnThreads / tpr;
-  const int rlane = threadIdx.x / tpr, c8 = (threadIdx.x % tpr) * 8;
+                    float* __restrict__ dbeta_out, float* __restrict__ dgamma_out,
+                    __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres, int M, int C) {
+  const BnMap m = bn_map(C);
   const float invM = 1.f / static_cast<float>(M);
-  const bool mask_from_x = relu && y == nullptr;
-  const bool mask_from_y = relu && y != nullptr;
-  float mean[8], istd[8], k0[8], k1[8], k2[8], db[8], dg[8], sh[8];
-  bn_gather_sums(sums, C, c8, rlane, s_a, s_b, db, dg);
+  // dx = k0*dz - kx*x - kc   with kx = k0*k2*istd, kc = k0*(k1 + k2*nm)
+  float k0[8], kx[8], kc[8], sc[8], sh[8], db[8], dg[8];
+  bn_gather_sums(sums, C, m, db, dg);
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
-    const int c = c8 + j;
-    mean[j] = save_mean[c];
-    istd[j] = save_invstd[c];
-    k0[j] = gamma[c] * istd[j];
-    sh[j] = beta[c] - mean[j] * k0[j];
-    k1[j] = db[j] * invM;        // dbeta / M
-    k2[j] = dg[j] * invM;        // dgamma / M
-    if (blockIdx.x == 0 && rlane == 0) {
+    const int c = m.c8 + j;
+    const float istd = save_invstd[c];
+    const float nm = -save_mean[c] * istd;
+    const float g = gamma[c];
+    k0[j] = g * istd;
+    sc[j] = k0[j];
+    sh[j] = fmaf(g, nm, beta[c]);
+    const float k1 = db[j] * invM;        // dbeta / M
+    const float k2 = dg[j] * invM;        // dgamma / M
+    kx[j] = k0[j] * k2 * istd;
+    kc[j] = k0[j] * fmaf(k2, nm, k1);
+    if (m.rg == 0 && m.rlane == 0) {
       dbeta_out[c] = db[j];
       dgamma_out[c] = dg[j];
     }
   }
-  const int stride = gridDim.x * rows;
-  for (int row = blockIdx.x * rows + rlane; row < M; row += stride) {
-    const size_t idx = static_cast<size_t>(row) * C + c8;
+  const int stride = m.stride;
+  int row = m.row0;
+  for (; row + stride < M; row += 2 * stride) {
+    const size_t i0 = static_cast<size_t>(row) * C + m.c8;
+    const size_t i1 = static_cast<size_t>(row + stride) * C + m.c8;
+    const uint4 wg0 = ld_stream_v4(dy + i0), wg1 = ld_stream_v4(dy + i1);
+    const uint4 wx0 = ld_stream_v4(x + i0), wx1 = ld_stream_v4(x + i1);
+    uint4 wy0 = make_uint4(0, 0, 0, 0), wy1 = wy0;
+    if (MODE == 1) { wy0 = ld_stream_v4(y + i0); wy1 = ld_stream_v4(y + i1); }
+    Vec8 g0 = unpack8_bf16(wg0), g1 = unpack8_bf16(wg1);
+    const Vec8 x0 = unpack8_bf16(wx0), x1 = unpack8_bf16(wx1);
+    bn_mask<MODE>(g0, x0, wy0, sc, sh);
+    bn_mask<MODE>(g1, x1, wy1, sc, sh);
+    if (dres) {
+      *reinterpret_cast<uint4*>(dres + i0) = pack8_bf16(g0);
+      *reinterpret_cast<uint4*>(dres + i1) = pack8_bf16(g1);
+    }
+    Vec8 o0, o1;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      o0.v[j] = fmaf(k0[j], g0.v[j], -fmaf(kx[j], x0.v[j], kc[j]));
+      o1.v[j] = fmaf(k0[j], g1.v[j], -fmaf(kx[j], x1.v[j], kc[j]));
+    }
+    *reinterpret_cast<uint4*>(dx + i0) = pack8_bf16(o0);
+    *reinterpret_cast<uint4*>(dx + i1) = pack8_bf16(o1);
+  }
+  for (; row < M; row += stride) {
+    const size_t idx = static_cast<size_t>(row) * C + m.c8;
     Vec8 g = unpack8_bf16(ld_stream_v4(dy + idx));
     const Vec8 xv = unpack8_bf16(ld_stream_v4(x + idx));
-    if (mask_from_y) {
-      const Vec8 yv = unpack8_bf16(ld_stream_v4(y + idx));
-#pragma unroll
-      for (int j = 0; j < 8; ++j) g.v[j] = yv.v[j] > 0.f ? g.v[j] : 0.f;
-    } else if (mask_from_x) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) g.v[j] = fmaf(xv.v[j], k0[j], sh[j]) > 0.f ? g.v[j] : 0.f;
-    }
+    uint4 wy = make_uint4(0, 0, 0, 0);
+    if (MODE == 1) wy = ld_stream_v4(y + idx);
+    bn_mask<MODE>(g, xv, wy, sc, sh);
     if (dres) *reinterpret_cast<uint4*>(dres + idx) = pack8_bf16(g);
     Vec8 o;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float xh = (xv.v[j] - mean[j]) * istd[j];
-      o.v[j] = k0[j] * (g.v[j] - k1[j] - xh * k2[j]);
-    }
+    for (int j = 0; j < 8; ++j) o.v[j] = fmaf(k0[j], g.v[j], -fmaf(kx[j], xv.v[j], kc[j]));
     *reinterpret_cast<uint4*>(dx + idx) = pack8_bf16(o);
   }
 }
 
+// Grid: a multiple of the slab count, about four CTAs per SM, never more row groups than there
+// are CTA-iterations of rows.
 static int bn_grid(int M, int C) {
-  const int rows = kBnThreads / (C >> 3);
+  const int w = C < 64 ? C : 64;
+  const int slabs = C / w;
+  const int rows = kBnThreads / (w >> 3);
   int sms = 148;
   int dev = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  long long want = (static_cast<long long>(M) + rows - 1) / rows;
-  const long long cap = static_cast<long long>(sms) * 4;
-  if (want > cap) want = cap;
-  if (want < 1) want = 1;
-  return static_cast<int>(want);
+  long long nrg = (static_cast<long long>(M) + rows - 1) / rows;
+  long long cap = (static_cast<long long>(sms) * 4) / slabs;
+  if (cap < 1) cap = 1;
+  if (nrg > cap) nrg = cap;
+  if (nrg < 1) nrg = 1;
+  return static_cast<int>(nrg * slabs);
+}
+
+static bool bn_shape_ok(int C) {
+  if (C <= 0 || (C & 7) || C > 2048) return false;
+  return C % 64 == 0 || C == 8 || C == 16 || C == 32;
 }
 
 static int bn_check(int M, int C, const char* what) {
-  if (M <= 0 || C <= 0 || (C & 7) || C > 2048 || (kBnThreads % (C >> 3)) != 0) {
-    set_last_error("%s: unsupported shape M=%d C=%d (C must be a power-of-two multiple of 8, <= 2048)",
+  if (M <= 0 || !bn_shape_ok(C)) {
+    set_last_error("%s: unsupported shape M=%d C=%d (C must be 8, 16, 32 or a multiple of 64, <= 2048)",
                    what, M, C);
     return CB2_ERR_UNSUPPORTED;
   }
@@ -342,9 +404,7 @@ static int bn_check(int M, int C, const char* what) {
 
 using namespace cb2;
 
-extern "C" int cb2_bn_supported(int C) {
-  return (C > 0 && !(C & 7) && C <= 2048 && (kBnThreads % (C >> 3)) == 0) ? 1 : 0;
-}
+extern "C" int cb2_bn_supported(int C) { return bn_shape_ok(C) ? 1 : 0; }
 
 extern "C" int cb2_bn_scratch_floats(int C) { return kBnCopies * 2 * C; }
 
@@ -358,10 +418,8 @@ extern "C" int cb2_bn_forward(const void* x, const void* residual, void* y,
   if (rc) return rc;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int grid = bn_grid(M, C);
-  const int rows = kBnThreads / (C >> 3);
-  const size_t smem = rows > 1 ? static_cast<size_t>(2) * rows * C * sizeof(float) : 0;
   if (training)
-    bn_stats_kernel<<<grid, kBnThreads, smem, st>>>(reinterpret_cast<const __nv_bfloat16*>(x), sums, M, C);
+    bn_stats_kernel<<<grid, kBnThreads, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(x), sums, M, C);
   bn_apply_kernel<<<grid, kBnThreads, 0, st>>>(
       reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<const __nv_bfloat16*>(residual),
       reinterpret_cast<__nv_bfloat16*>(y), sums, gamma, beta, run_mean, run_var, save_mean,
@@ -378,17 +436,22 @@ extern "C" int cb2_bn_backward(const void* dy, const void* y, const void* x, con
   if (rc) return rc;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int grid = bn_grid(M, C);
-  const int rows = kBnThreads / (C >> 3);
-  const size_t smem = rows > 1 ? static_cast<size_t>(2) * rows * C * sizeof(float) : 0;
-  bn_bwd_reduce_kernel<<<grid, kBnThreads, smem, st>>>(
-      reinterpret_cast<const __nv_bfloat16*>(dy), reinterpret_cast<const __nv_bfloat16*>(y),
-      reinterpret_cast<const __nv_bfloat16*>(x), save_mean, save_invstd, gamma, beta, sums, M, C,
-      relu);
-  bn_bwd_apply_kernel<<<grid, kBnThreads, 0, st>>>(
-      reinterpret_cast<const __nv_bfloat16*>(dy), reinterpret_cast<const __nv_bfloat16*>(y),
-      reinterpret_cast<const __nv_bfloat16*>(x), save_mean, save_invstd, gamma, beta, sums, dbeta,
-      dgamma,
-      reinterpret_cast<__nv_bfloat16*>(dx), reinterpret_cast<__nv_bfloat16*>(dres), M, C, relu);
+  const __nv_bfloat16* dyp = reinterpret_cast<const __nv_bfloat16*>(dy);
+  const __nv_bfloat16* yp = reinterpret_cast<const __nv_bfloat16*>(y);
+  const __nv_bfloat16* xp = reinterpret_cast<const __nv_bfloat16*>(x);
+  __nv_bfloat16* dxp = reinterpret_cast<__nv_bfloat16*>(dx);
+  __nv_bfloat16* drp = reinterpret_cast<__nv_bfloat16*>(dres);
+  const int mode = !relu ? 0 : (y != nullptr ? 1 : 2);
+#define CB2_BN_BWD(MODE)                                                                          \
+  bn_bwd_reduce_kernel<MODE><<<grid, kBnThreads, 0, st>>>(dyp, yp, xp, save_mean, save_invstd,    \
+                                                          gamma, beta, sums, M, C);               \
+  bn_bwd_apply_kernel<MODE><<<grid, kBnThreads, 0, st>>>(dyp, yp, xp, save_mean, save_invstd,     \
+                                                         gamma, beta, sums, dbeta, dgamma, dxp,   \
+                                                         drp, M, C);
+  if (mode == 0) { CB2_BN_BWD(0) }
+  else if (mode == 1) { CB2_BN_BWD(1) }
+  else { CB2_BN_BWD(2) }
+#undef CB2_BN_BWD
   return check_cuda(cudaGetLastError(), "bn_backward launch");
 }
 
@@ -471,14 +534,12 @@ extern "C" int cb2_bn_forward_static(const void* x, const void* residual, void* 
   if (rc) return rc;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int grid = bn_grid(M, C);
-  const int rows = kBnThreads / (C >> 3);
-  const size_t smem = rows > 1 ? static_cast<size_t>(2) * rows * C * sizeof(float) : 0;
   if (training) {
     // the array still holds the previous call's partial sums: the part this call accumulates into
     // has to start from zero
     bn_static_scratch_clear_kernel<<<(need + 255) / 256, 256, 0, st>>>(scratch, need);
-    bn_stats_kernel<<<grid, kBnThreads, smem, st>>>(reinterpret_cast<const __nv_bfloat16*>(x),
-                                                    scratch, M, C);
+    bn_stats_kernel<<<grid, kBnThreads, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(x),
+                                                 scratch, M, C);
   }
   bn_apply_kernel<<<grid, kBnThreads, 0, st>>>(
       reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<const __nv_bfloat16*>(residual),

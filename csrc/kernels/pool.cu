@@ -15,15 +15,19 @@ struct PoolGeom {
   int N, H, W, C, OH, OW, k, s, pad;
 };
 
+// KS = k*16 + s for the compile-time specialisations (0: read k and s from the geometry).  All
+// index arithmetic is 32-bit (the host rejects tensors with 2^31 or more 16-byte groups): 64-bit
+// divisions made the first version of these kernels instruction-bound.
+template <int KS>
 __global__ void __launch_bounds__(256)
 maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
                    uint8_t* __restrict__ idx, const PoolGeom g) {
-  const int c8n = g.C >> 3;
-  const size_t total = static_cast<size_t>(g.N) * g.OH * g.OW * c8n;
-  for (size_t t = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; t < total;
-       t += static_cast<size_t>(gridDim.x) * blockDim.x) {
+  const int K = KS ? (KS >> 4) : g.k, S = KS ? (KS & 15) : g.s;
+  const unsigned c8n = g.C >> 3;
+  const unsigned total = static_cast<unsigned>(g.N) * g.OH * g.OW * c8n;
+  for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
     const int c8 = static_cast<int>(t % c8n) * 8;
-    size_t r = t / c8n;
+    unsigned r = t / c8n;
     const int ow = static_cast<int>(r % g.OW); r /= g.OW;
     const int oh = static_cast<int>(r % g.OH);
     const int n = static_cast<int>(r / g.OH);
@@ -31,10 +35,12 @@ maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restric
     int arg[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) { best[j] = -INFINITY; arg[j] = 0; }
-    for (int kh = 0; kh < g.k; ++kh) {
-      const int h = oh * g.s - g.pad + kh;
-      for (int kw = 0; kw < g.k; ++kw) {
-        const int w = ow * g.s - g.pad + kw;
+#pragma unroll
+    for (int kh = 0; kh < K; ++kh) {
+      const int h = oh * S - g.pad + kh;
+#pragma unroll
+      for (int kw = 0; kw < K; ++kw) {
+        const int w = ow * S - g.pad + kw;
         Vec8 v;
         if (h >= 0 && h < g.H && w >= 0 && w < g.W) {
           v = unpack8_bf16(*reinterpret_cast<const uint4*>(
@@ -43,7 +49,7 @@ maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restric
 #pragma unroll
           for (int j = 0; j < 8; ++j) v.v[j] = 0.f;     // zero padding
         }
-        const int code = kh * g.k + kw;
+        const int code = kh * K + kw;
 #pragma unroll
         for (int j = 0; j < 8; ++j)
           if (v.v[j] > best[j]) { best[j] = v.v[j]; arg[j] = code; }
@@ -61,15 +67,16 @@ maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restric
   }
 }
 
+template <int KS>
 __global__ void __launch_bounds__(256)
 maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __restrict__ idx,
                    __nv_bfloat16* __restrict__ dx, const PoolGeom g) {
-  const int c8n = g.C >> 3;
-  const size_t total = static_cast<size_t>(g.N) * g.H * g.W * c8n;
-  for (size_t t = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; t < total;
-       t += static_cast<size_t>(gridDim.x) * blockDim.x) {
+  const int K = KS ? (KS >> 4) : g.k, S = KS ? (KS & 15) : g.s;
+  const unsigned c8n = g.C >> 3;
+  const unsigned total = static_cast<unsigned>(g.N) * g.H * g.W * c8n;
+  for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
     const int c8 = static_cast<int>(t % c8n) * 8;
-    size_t r = t / c8n;
+    unsigned r = t / c8n;
     const int w = static_cast<int>(r % g.W); r /= g.W;
     const int h = static_cast<int>(r % g.H);
     const int n = static_cast<int>(r / g.H);
@@ -78,23 +85,25 @@ maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __restri
     for (int j = 0; j < 8; ++j) acc[j] = 0.f;
     // windows (oh, ow) with oh*s - pad <= h <= oh*s - pad + k - 1
     const int hp = h + g.pad, wp = w + g.pad;
-    int oh0 = (hp - g.k + g.s) / g.s;          // ceil((hp - k + 1) / s)
-    if (hp - g.k + 1 <= 0) oh0 = 0;
-    int ow0 = (wp - g.k + g.s) / g.s;
-    if (wp - g.k + 1 <= 0) ow0 = 0;
-    const int oh1 = min(hp / g.s, g.OH - 1), ow1 = min(wp / g.s, g.OW - 1);
+    int oh0 = (hp - K + S) / S;          // ceil((hp - k + 1) / s)
+    if (hp - K + 1 <= 0) oh0 = 0;
+    int ow0 = (wp - K + S) / S;
+    if (wp - K + 1 <= 0) ow0 = 0;
+    const int oh1 = min(hp / S, g.OH - 1), ow1 = min(wp / S, g.OW - 1);
     for (int oh = oh0; oh <= oh1; ++oh) {
-      const int kh = hp - oh * g.s;
+      const int kh = hp - oh * S;
       for (int ow = ow0; ow <= ow1; ++ow) {
-        const int code = kh * g.k + (wp - ow * g.s);
+        const int code = kh * K + (wp - ow * S);
         const size_t oi = ((static_cast<size_t>(n) * g.OH + oh) * g.OW + ow) * g.C + c8;
         const uint2 pk = *reinterpret_cast<const uint2*>(idx + oi);
         const Vec8 gy = unpack8_bf16(*reinterpret_cast<const uint4*>(dy + oi));
+        // byte-wise compare of four arg-max codes at once: 0xff where the window's max is here
+        const uint32_t code4 = static_cast<uint32_t>(code) * 0x01010101u;
+        const uint32_t m0 = __vcmpeq4(pk.x, code4), m1 = __vcmpeq4(pk.y, code4);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          const uint32_t word = j < 4 ? pk.x : pk.y;
-          const int a = (word >> ((j & 3) * 8)) & 0xff;
-          if (a == code) acc[j] += gy.v[j];
+          const uint32_t mk = j < 4 ? m0 : m1;
+          if (mk & (0x80u << ((j & 3) * 8))) acc[j] += gy.v[j];
         }
       }
     }
@@ -117,6 +126,10 @@ static int pool_grid(size_t total) {
 }
 
 static int pool_check(const PoolGeom& g) {
+  if (static_cast<long long>(g.N) * g.H * g.W * (g.C >> 3) >= (1LL << 31)) {
+    set_last_error("maxpool: tensor too large for 32-bit indexing");
+    return CB2_ERR_UNSUPPORTED;
+  }
   if (g.N <= 0 || g.H <= 0 || g.W <= 0 || g.C <= 0 || (g.C & 7) || g.k <= 0 || g.k > 15 ||
       g.s <= 0 || g.pad < 0 || g.pad >= g.k || g.OH != (g.H + 2 * g.pad - g.k) / g.s + 1 ||
       g.OW != (g.W + 2 * g.pad - g.k) / g.s + 1) {
@@ -137,7 +150,9 @@ extern "C" int cb2_maxpool_nhwc_forward(const void* x, void* y, void* argmax, in
   int rc = pool_check(g);
   if (rc) return rc;
   const size_t total = static_cast<size_t>(N) * OH * OW * (C >> 3);
-  maxpool_fwd_kernel<<<pool_grid(total), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+  auto kern = (k == 3 && s == 2) ? maxpool_fwd_kernel<3 * 16 + 2>
+              : (k == 2 && s == 2) ? maxpool_fwd_kernel<2 * 16 + 2> : maxpool_fwd_kernel<0>;
+  kern<<<pool_grid(total), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y),
       reinterpret_cast<uint8_t*>(argmax), g);
   return check_cuda(cudaGetLastError(), "maxpool_fwd launch");
@@ -150,7 +165,9 @@ extern "C" int cb2_maxpool_nhwc_backward(const void* dy, const void* argmax, voi
   int rc = pool_check(g);
   if (rc) return rc;
   const size_t total = static_cast<size_t>(N) * H * W * (C >> 3);
-  maxpool_bwd_kernel<<<pool_grid(total), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+  auto kern = (k == 3 && s == 2) ? maxpool_bwd_kernel<3 * 16 + 2>
+              : (k == 2 && s == 2) ? maxpool_bwd_kernel<2 * 16 + 2> : maxpool_bwd_kernel<0>;
+  kern<<<pool_grid(total), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const __nv_bfloat16*>(dy), reinterpret_cast<const uint8_t*>(argmax),
       reinterpret_cast<__nv_bfloat16*>(dx), g);
   return check_cuda(cudaGetLastError(), "maxpool_bwd launch");

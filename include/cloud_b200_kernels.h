@@ -75,7 +75,7 @@ int cb2_u8_to_bf16_normalize(const uint8_t* in, void* out, size_t n_pixels, int 
 
 /* ------------------------------------------------------------------------------------------
  * Fused NHWC batch normalisation (+ residual add) (+ ReLU), bf16 activations [M = N*H*W, C],
- * fp32 statistics and parameters (K8).  C must be a power-of-two multiple of 8, <= 2048.
+ * fp32 statistics and parameters (K8).  C must be 8, 16, 32 or a multiple of 64, <= 2048.
  * `sums` is caller-provided scratch of cb2_bn_scratch_floats(C) floats that MUST be zero on entry
  * (the reductions accumulate into it with atomics).
  *   forward : y = act(gamma * (x - mean) / sqrt(var + eps) + beta (+ residual)); training != 0 uses
