@@ -10,6 +10,7 @@ hand-written tcgen05 GEMM (``cloud_b200.ops.dense``).
 from __future__ import annotations
 
 import math
+import os
 import re
 
 import numpy as np
@@ -18,6 +19,10 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from .. import ops
+
+# 1x1 / stride-1 convolutions run on the tcgen05 GEMM (ops/conv.py); TFC_CONV1X1_GEMM=0 sends them
+# to cuDNN like every other convolution
+_CONV1X1_GEMM = os.environ.get("TFC_CONV1X1_GEMM", "1") != "0"
 
 _NAME_COUNTS: dict[str, int] = {}
 
@@ -432,6 +437,9 @@ class Conv2D(Layer):
         # per-channel shift, so the bias add (one extra read+write of the activation) and its
         # gradient reduction (one extra read of dY; the gradient is exactly zero) are skipped.
         self.bias_absorbed_by_bn = False
+        # Set by a directly following trainable BatchNormalization: a 1x1 convolution on the
+        # tcgen05 GEMM then reduces the batch statistics in its epilogue (ops/conv.py).
+        self.feeds_bn = False
 
     def build(self, input_shape):
         cin = int(input_shape[-1])
@@ -477,7 +485,11 @@ class Conv2D(Layer):
             b = None
         if b is not None and b.dtype != x.dtype:
             b = b.to(x.dtype)
-        y = F.conv2d(x, w, b, stride=self.strides, padding=pad, dilation=self.dilation)
+        if _CONV1X1_GEMM and ops.conv1x1_supported(x, w, self.strides, pad, self.dilation):
+            y = ops.conv1x1(x, w, b, bn_stats=bool(training) and self.feeds_bn and
+                            self.activation_name in (None, "linear"))
+        else:
+            y = F.conv2d(x, w, b, stride=self.strides, padding=pad, dilation=self.dilation)
         if self.activation_name == "relu":
             return torch.relu_(y)
         return y if self._activation_fn is None else self._activation_fn(y)
@@ -624,10 +636,11 @@ class BatchNormalization(Layer):
         out = super()._symbolic_call(inputs)
         first = inputs[0] if isinstance(inputs, (list, tuple)) else inputs
         prev = first.layer
-        if isinstance(prev, Conv2D) and prev.use_bias and prev.activation_name in (None, "linear") \
-                and self._trainable:
-            prev.bias_absorbed_by_bn = True
-            object.__setattr__(self, "_absorbed_conv", prev)   # not a submodule: no double registration
+        if isinstance(prev, Conv2D) and prev.activation_name in (None, "linear") and self._trainable:
+            prev.feeds_bn = True
+            if prev.use_bias:
+                prev.bias_absorbed_by_bn = True
+                object.__setattr__(self, "_absorbed_conv", prev)   # not a submodule: no double registration
         return out
 
     def call(self, x, training=False, relu=None, residual=None):
@@ -642,7 +655,8 @@ class BatchNormalization(Layer):
             return ops.batch_norm_nhwc(x, self.gamma, self.beta, self.moving_mean,
                                        self.moving_variance, train, 1.0 - self.momentum,
                                        self.epsilon, relu=relu, residual=residual,
-                                       mean_bias=mean_bias)
+                                       mean_bias=mean_bias,
+                                       sums=getattr(x, "_cb2_bn_sums", None) if train else None)
         y = F.batch_norm(x, self.moving_mean, self.moving_variance, self.gamma, self.beta, train,
                          1.0 - self.momentum, self.epsilon)
         if mean_bias is not None:

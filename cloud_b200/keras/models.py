@@ -492,7 +492,9 @@ class Model(nn.Module):
         if not self._graph_enabled():
             return self._train_step(xb, yb, global_batch)
         g = self._graph
-        key = (tuple(xb.shape), xb.dtype, tuple(yb.shape), yb.dtype, global_batch)
+        if global_batch is None:        # same key whether or not the caller spelled it out
+            global_batch = int(xb.shape[0]) * self._engine.world
+        key = (tuple(xb.shape), xb.dtype, tuple(yb.shape), yb.dtype, int(global_batch))
         if g is None or g["key"] != key:
             if g is not None and g.get("frozen"):
                 return self._train_step(xb, yb, global_batch)   # e.g. the short last batch

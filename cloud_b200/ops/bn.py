@@ -72,7 +72,7 @@ def reset_scratch(device) -> None:
 def _scratch(n: int, device) -> torch.Tensor:
     st = _pool.get(device)
     if st is None:
-        st = {"buf": torch.zeros(16 << 20, dtype=torch.float32, device=device), "used": 0,
+        st = {"buf": torch.zeros(32 << 20, dtype=torch.float32, device=device), "used": 0,
               "armed": False}
         _pool[device] = st
     if not st["armed"] or st["used"] + n > st["buf"].numel():
@@ -94,22 +94,27 @@ def _is_nhwc(t):
 
 class _BNFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, residual, run_mean, run_var, momentum, eps, relu, mean_bias):
+    def forward(ctx, x, gamma, beta, residual, run_mean, run_var, momentum, eps, relu, mean_bias,
+                sums=None):
         global _launches
         N, C, H, W = x.shape
         M = N * H * W
         y = torch.empty_like(x)                       # preserves channels_last
-        sums = _scratch(_k().cb2_bn_scratch_floats(C), x.device)
+        # `sums`: batch statistics already reduced by the producer of x (ops/conv.py: the GEMM
+        # epilogue of a 1x1 convolution) - the statistics pass over x is skipped (training = 2)
+        mode = 1 if sums is None else 2
+        if sums is None:
+            sums = _scratch(_k().cb2_bn_scratch_floats(C), x.device)
         save = torch.empty(2 * C, dtype=torch.float32, device=x.device)
         rc = _k().cb2_bn_forward(x.data_ptr(), None if residual is None else residual.data_ptr(),
                                  y.data_ptr(), sums.data_ptr(), gamma.data_ptr(), beta.data_ptr(),
                                  run_mean.data_ptr(), run_var.data_ptr(), save.data_ptr(),
                                  save[C:].data_ptr(),
                                  None if mean_bias is None else mean_bias.data_ptr(), M, C,
-                                 float(eps), float(momentum), int(relu), 1, _stream())
+                                 float(eps), float(momentum), int(relu), mode, _stream())
         ctx.params = (gamma, beta)
         _lib.check(rc, "bn_forward")
-        _launches += 2
+        _launches += 3 - mode
         # the ReLU mask is recomputed from x unless a shortcut was added before the ReLU
         ctx.save_for_backward(x, y if (relu and residual is not None) else None, gamma, save, beta)
         ctx.relu, ctx.has_res, ctx.M, ctx.C = relu, residual is not None, M, C
@@ -148,16 +153,17 @@ class _BNFn(torch.autograd.Function):
         if direct:
             gparam._cb2_grad_written(gparam)
             bparam._cb2_grad_written(bparam)
-            return dx, None, None, dres, None, None, None, None, None, None
-        return dx, grads[C:], grads[:C], dres, None, None, None, None, None, None
+            return dx, None, None, dres, None, None, None, None, None, None, None
+        return dx, grads[C:], grads[:C], dres, None, None, None, None, None, None, None
 
 
 def batch_norm_nhwc(x, gamma, beta, run_mean, run_var, training, momentum, eps, relu=False,
-                    residual=None, mean_bias=None):
+                    residual=None, mean_bias=None, sums=None):
     """``act(BN(x) + residual)`` for bf16 channels_last ``x``; ``momentum`` is the torch-style
     update rate of the running statistics (1 - keras_momentum).  ``mean_bias`` (fp32 [C]) is added
     to the batch mean when the running mean is refreshed: it is the bias of a preceding
-    convolution that was skipped in training because batch-norm cancels it exactly."""
+    convolution that was skipped in training because batch-norm cancels it exactly.  ``sums``
+    (fp32 ``[8, 2, C]``): batch statistics the producer of ``x`` has already reduced."""
     global _launches
     C = x.shape[1]
     ok = (x.is_cuda and x.dtype == torch.bfloat16 and _is_nhwc(x) and _k().cb2_bn_supported(C)
@@ -172,7 +178,8 @@ def batch_norm_nhwc(x, gamma, beta, run_mean, run_var, training, momentum, eps, 
         x.requires_grad or gamma.requires_grad or beta.requires_grad or
         (residual is not None and residual.requires_grad))
     if training and needs_grad:
-        return _BNFn.apply(x, gamma, beta, residual, run_mean, run_var, momentum, eps, relu, mean_bias)
+        return _BNFn.apply(x, gamma, beta, residual, run_mean, run_var, momentum, eps, relu, mean_bias,
+                           sums)
     if needs_grad:   # frozen layer inside a trainable network: let autograd handle it
         y = torch.nn.functional.batch_norm(x, run_mean, run_var, gamma, beta, False, momentum, eps)
         if residual is not None:

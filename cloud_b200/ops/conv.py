@@ -1,0 +1,98 @@
+"""1x1 convolutions on the tcgen05 GEMM (``csrc/kernels/gemm_tcgen05.cu``).
+
+With channels_last activations a 1x1 / stride-1 convolution IS a matrix product:
+``Y[N*H*W, Cout] = X[N*H*W, Cin] @ W[Cout, Cin]^T`` - no im2col, no layout change.  36 of the 53
+convolutions of ResNet-50 (and more than half of its FLOPs) have this form, so they run on the
+hand-written kernel instead of cuDNN:
+
+* forward: K-major x K-major GEMM; when a BatchNormalization follows, the epilogue also reduces
+  the per-channel sum / sum of squares of the tile it is about to store (``colstats``), which makes
+  the separate statistics pass over the activation (one full read) unnecessary;
+* input gradient: ``dX = dY @ W`` (B operand MN-major, no transpose);
+* weight gradient: ``dW = dY^T @ X`` (both operands MN-major) with split-K - the reduction runs over
+  N*H*W, up to 200 704 here, while dW has one to a few dozen tiles - summed by TMA reduce-adds
+  into an fp32 workspace.
+
+Reference workload: ResNet-50 through ``tf.keras.applications`` in
+core/tests/examples/call_run_within_script_with_keras_fit.py (K8 of SURVEY.md section 2.5); the
+reference leaves these to cuDNN / cuBLAS inside TensorFlow.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+
+from . import bn as _bn
+from . import dense as _dense
+
+def supported(x: torch.Tensor, w: torch.Tensor, stride, padding, dilation) -> bool:
+    """True when ``conv2d(x, w)`` can run as one GEMM on the tcgen05 kernel."""
+    return (x.is_cuda and x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and x.dim() == 4
+            and tuple(w.shape[2:]) == (1, 1) and tuple(stride) == (1, 1) and tuple(dilation) == (1, 1)
+            and padding in (0, (0, 0), "valid") and x.shape[1] % 8 == 0 and w.shape[0] % 8 == 0
+            and x.is_contiguous(memory_format=torch.channels_last))
+
+
+def _as_matrix(t: torch.Tensor) -> torch.Tensor:
+    """[N, C, H, W] channels_last -> its [N*H*W, C] row-major matrix (a view)."""
+    n, c, h, w = t.shape
+    return t.permute(0, 2, 3, 1).reshape(n * h * w, c)
+
+
+class _Conv1x1Fn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, bias, colstats):
+        n, cin, h, wd = x.shape
+        cout = w.shape[0]
+        w2 = w.reshape(cout, cin)
+        y = torch.empty((n, h, wd, cout), dtype=torch.bfloat16, device=x.device)
+        _dense.gemm(_as_matrix(x), w2, bias=bias, out=y.view(n * h * wd, cout), colstats=colstats)
+        ctx.save_for_backward(x, w)
+        ctx.has_bias = bias is not None
+        return y.permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        n, cin, h, wd = x.shape
+        cout = w.shape[0]
+        m = n * h * wd
+        if not dy.is_contiguous(memory_format=torch.channels_last):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        dy2 = _as_matrix(dy)
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dxm = torch.empty((n, h, wd, cin), dtype=torch.bfloat16, device=x.device)
+            _dense.gemm(dy2, w.reshape(cout, cin), b_mn=True, out=dxm.view(m, cin))
+            dx = dxm.permute(0, 3, 1, 2)
+        if ctx.needs_input_grad[1]:
+            # split-K partial sums meet in an fp32 workspace that the engine zeroes once per step
+            ws = _bn._scratch(cout * cin, x.device).view(cout, cin)
+            _dense.gemm(dy2, _as_matrix(x), a_mn=True, b_mn=True, out=ws, accumulate=True, split_k=0)
+            if getattr(w, "_cb2_direct_grad", False) and w.grad is not None:
+                # straight into the engine's gradient arena (bf16) - no temporary, no autograd add
+                w.grad.view(cout, cin).add_(ws)
+                w._cb2_grad_written(w)
+            else:
+                dw = ws.to(torch.bfloat16).view(cout, cin, 1, 1)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            db = dy2.float().sum(0)
+        return dx, dw, db, None
+
+
+def conv1x1(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None,
+            bn_stats: bool = False) -> torch.Tensor:
+    """1x1 / stride-1 convolution of a channels_last bf16 tensor.  With ``bn_stats`` the result
+    carries ``_cb2_bn_sums``: the batch statistics a following fused batch-norm can use as is."""
+    if not x.is_cuda:
+        return F.conv2d(x, w, bias)
+    sums = None
+    if bn_stats and bias is None:
+        cout = w.shape[0]
+        sums = _bn._scratch(16 * cout, x.device)
+    if bias is not None and bias.dtype != torch.float32:
+        bias = bias.float()
+    y = _Conv1x1Fn.apply(x, w, bias, sums)
+    if sums is not None:
+        y._cb2_bn_sums = sums
+    return y

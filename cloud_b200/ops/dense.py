@@ -39,11 +39,14 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
          bias: torch.Tensor | None = None, relu: bool = False, softmax: bool = False,
          relu_mask: torch.Tensor | None = None, out: torch.Tensor | None = None,
          out_dtype: torch.dtype = torch.bfloat16, accumulate: bool = False,
-         block_n: int = 0) -> torch.Tensor:
+         block_n: int = 0, split_k: int = 1, colstats: torch.Tensor | None = None) -> torch.Tensor:
     """C[M,N] = op(A) @ op(B)^T with fused epilogue, bf16 operands, fp32 accumulation in TMEM.
 
     ``a`` is stored ``[M,K]`` (``a_mn=False``) or ``[K,M]`` (``a_mn=True``); ``b`` is stored
     ``[N,K]`` (``b_mn=False``) or ``[K,N]`` (``b_mn=True``).  Row pitches must be multiples of 8.
+    ``split_k`` (0 = choose) cuts K into slices summed by TMA reduce-adds; it needs
+    ``accumulate=True`` into an fp32 ``out``.  ``colstats`` (fp32 ``[8, 2, N]``) receives the
+    per-column sum / sum of squares of the bf16 result (batch-norm statistics).
     """
     global _launches
     if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16:
@@ -61,8 +64,13 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     if K != Kb:
         raise ValueError(f"reduction dims differ: {K} vs {Kb}")
     if not a.is_cuda:
-        return _gemm_reference(a, b, a_mn, b_mn, bias, relu, softmax, relu_mask, out, out_dtype,
-                               accumulate)
+        c = _gemm_reference(a, b, a_mn, b_mn, bias, relu, softmax, relu_mask, out, out_dtype,
+                            accumulate)
+        if colstats is not None:
+            cf = c.float()
+            colstats[0, 0] += cf.sum(0)
+            colstats[0, 1] += (cf * cf).sum(0)
+        return c
     if out is None:
         if accumulate:
             raise ValueError("accumulate=True needs out=")
@@ -81,10 +89,14 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     if bias is not None and bias.dtype != torch.float32:
         bias = bias.float()
     lib = _lib.kernels()
-    rc = lib.cb2_gemm_bf16(_ptr(a), _ptr(b), _ptr(out), _ptr(bias), _ptr(relu_mask), M, N, K,
-                           a.stride(0), b.stride(0), out.stride(0),
-                           relu_mask.stride(0) if relu_mask is not None else 0,
-                           int(a_mn), int(b_mn), flags, block_n, _stream())
+    if colstats is not None and (colstats.dtype != torch.float32 or colstats.numel() != 16 * N
+                                 or not colstats.is_contiguous()):
+        raise ValueError("colstats must be a contiguous fp32 [8, 2, N] tensor")
+    rc = lib.cb2_gemm_bf16_ex(_ptr(a), _ptr(b), _ptr(out), _ptr(bias), _ptr(relu_mask), M, N, K,
+                              a.stride(0), b.stride(0), out.stride(0),
+                              relu_mask.stride(0) if relu_mask is not None else 0,
+                              int(a_mn), int(b_mn), flags, block_n, int(split_k), _ptr(colstats),
+                              _stream())
     _lib.check(rc, "gemm_bf16")
     _launches += 1
     return out

@@ -418,7 +418,7 @@ extern "C" int cb2_bn_forward(const void* x, const void* residual, void* y,
   if (rc) return rc;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int grid = bn_grid(M, C);
-  if (training)
+  if (training == 1)     // training == 2: `sums` already holds the statistics (GEMM epilogue)
     bn_stats_kernel<<<grid, kBnThreads, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(x), sums, M, C);
   bn_apply_kernel<<<grid, kBnThreads, 0, st>>>(
       reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<const __nv_bfloat16*>(residual),

@@ -44,6 +44,9 @@ struct GemmArgs {
   uint32_t a_kadv, b_kadv;              // start-address advance per UMMA_K step, 16-byte units
   int tma_store;                        // epilogue through smem staging + TMA store (coalesced)
   int debug;                            // bench/gemm_epilogue_probe.py: skip parts of the epilogue
+  int splits, kb_per_split;             // split-K: work item = (m tile, n tile, k slice)
+  int m_fast;                           // work order: m tile index fastest (else n fastest)
+  float* colstats;                      // [kColStatCopies][2][N] += column sums / sums of squares
 };
 
 template <int BN>
@@ -69,61 +72,82 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo,
   return d;
 }
 
+// Work item -> (m tile, n tile, k-block range).  Consecutive items differ in n (default: CTAs that
+// run together share the A tile) or in m (m_fast: they share the B tile, and one CTA keeps the same
+// n for long runs - what the column-statistics epilogue wants).
+struct WorkItem { int m0, n0, kb0, kb1; };
+template <int BN>
+__device__ __forceinline__ WorkItem decode_work(const GemmArgs& p, int w) {
+  int mi, ni, si;
+  if (p.m_fast) {
+    mi = w % p.m_tiles; w /= p.m_tiles;
+    ni = w % p.n_tiles; si = w / p.n_tiles;
+  } else {
+    ni = w % p.n_tiles; w /= p.n_tiles;
+    mi = w % p.m_tiles; si = w / p.m_tiles;
+  }
+  WorkItem it;
+  it.m0 = mi * BM;
+  it.n0 = ni * BN;
+  it.kb0 = si * p.kb_per_split;
+  it.kb1 = min(p.k_blocks, it.kb0 + p.kb_per_split);
+  return it;
+}
+
+constexpr int kColStatCopies = 8;   // same replica count as the batch-norm scratch (bn.cu)
+
 // Coalesced epilogue of one 32-row slice of an accumulator tile: TMEM -> registers -> 128B-swizzled
 // smem tile (32 rows x 128 B, double buffered per warp) -> TMA store / reduce-add.  Rows and
 // columns outside the matrix are clipped by the tensor map.  Each scheduler runs a single
 // epilogue warp, so every latency in here is exposed: the TMEM load of chunk i+1 is issued before
 // chunk i is converted, the element loop is straight-line code (bias from a smem copy, ReLU as a
 // max with 0 or -inf, or neither when `plain`), and all addresses are explicit shared addresses.
-template <int BN, bool F32>
+template <int BN, bool F32, bool STATS>
 __device__ __forceinline__ void epilogue_tma(const CUtensorMap* tmC, uint32_t taddr, uint32_t stg,
                                              uint32_t sbias, int& stage_buf, int n0, int row0, int N,
-                                             float lo, bool plain, bool accum, int lane) {
-  constexpr int COLS = F32 ? 32 : 64;
-  constexpr int NCH = BN / COLS;
-  constexpr int NLD = F32 ? 1 : 2;
-  uint32_t v[2][NLD][32];
+                                             float lo, bool plain, bool accum, int lane,
+                                             float (&cs)[F32 ? 1 : BN / 64][4]) {
+  // unit = 32 accumulator columns = one tcgen05.ld; a staged chunk (128-byte rows) is one unit of
+  // fp32 or two units of bf16
+  constexpr int NU = BN / 32;
+  constexpr int UPC = F32 ? 1 : 2;
+  uint32_t v[2][32];
   const uint32_t sw = lane & 7;
   const int rem = N - n0;
-  const int nch = rem >= BN ? NCH : (rem + COLS - 1) / COLS;
+  const int nu = rem >= BN ? NU : (((rem + 32 * UPC - 1) / (32 * UPC)) * UPC);
+  tmem_ld_32x32(taddr, v[0]);
 #pragma unroll
-  for (int l = 0; l < NLD; ++l) tmem_ld_32x32(taddr + l * 32, v[0][l]);
-#pragma unroll
-  for (int ci = 0; ci < NCH; ++ci) {
-    if (ci < nch) {
-      uint32_t(&cur)[NLD][32] = v[ci & 1];
-      tmem_ld_wait_for(cur[0]);
-      if (NLD > 1) reg_fence(cur[NLD - 1]);
-      if (ci + 1 < NCH && ci + 1 < nch) {
-#pragma unroll
-        for (int l = 0; l < NLD; ++l) tmem_ld_32x32(taddr + (ci + 1) * COLS + l * 32, v[(ci + 1) & 1][l]);
-      }
+  for (int u = 0; u < NU; ++u) {
+    if (u < nu) {
+      uint32_t(&cur)[32] = v[u & 1];
+      tmem_ld_wait_for(cur);
+      if (u + 1 < NU && u + 1 < nu) tmem_ld_32x32(taddr + (u + 1) * 32, v[(u + 1) & 1]);
+      const int ci = u / UPC, h = u % UPC;
       const uint32_t buf = stg + stage_buf * 4096;
       const uint32_t rowp = buf + lane * 128;
-      if (lane == 0) tma_store_wait_read<1>();   // the store that last read this buffer is done
-      __syncwarp();
+      if (h == 0) {
+        if (lane == 0) tma_store_wait_read<1>();   // the store that last read this buffer is done
+        __syncwarp();
+      }
       if (F32) {
-        if (plain) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j)
-            st_shared_v4(rowp + ((j ^ sw) << 4), cur[0][j * 4], cur[0][j * 4 + 1], cur[0][j * 4 + 2],
-                         cur[0][j * 4 + 3]);
-        } else {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 bb = ld_shared_f4(sbias + (ci * COLS + j * 4) * 4);
-            const float f0 = fmaxf(__uint_as_float(cur[0][j * 4 + 0]) + bb.x, lo);
-            const float f1 = fmaxf(__uint_as_float(cur[0][j * 4 + 1]) + bb.y, lo);
-            const float f2 = fmaxf(__uint_as_float(cur[0][j * 4 + 2]) + bb.z, lo);
-            const float f3 = fmaxf(__uint_as_float(cur[0][j * 4 + 3]) + bb.w, lo);
+        for (int j = 0; j < 8; ++j) {
+          if (plain) {
+            st_shared_v4(rowp + ((j ^ sw) << 4), cur[j * 4], cur[j * 4 + 1], cur[j * 4 + 2], cur[j * 4 + 3]);
+          } else {
+            const float4 bb = ld_shared_f4(sbias + (u * 32 + j * 4) * 4);
+            const float f0 = fmaxf(__uint_as_float(cur[j * 4 + 0]) + bb.x, lo);
+            const float f1 = fmaxf(__uint_as_float(cur[j * 4 + 1]) + bb.y, lo);
+            const float f2 = fmaxf(__uint_as_float(cur[j * 4 + 2]) + bb.z, lo);
+            const float f3 = fmaxf(__uint_as_float(cur[j * 4 + 3]) + bb.w, lo);
             st_shared_v4(rowp + ((j ^ sw) << 4), __float_as_uint(f0), __float_as_uint(f1),
                          __float_as_uint(f2), __float_as_uint(f3));
           }
         }
       } else {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const uint32_t* w = &cur[NLD - 1 < j / 4 ? NLD - 1 : j / 4][(j & 3) * 8];
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t* w = &cur[j * 8];
           uint32_t o0, o1, o2, o3;
           if (plain) {
             o0 = pack_bf16(__uint_as_float(w[0]), __uint_as_float(w[1]));
@@ -131,25 +155,64 @@ __device__ __forceinline__ void epilogue_tma(const CUtensorMap* tmC, uint32_t ta
             o2 = pack_bf16(__uint_as_float(w[4]), __uint_as_float(w[5]));
             o3 = pack_bf16(__uint_as_float(w[6]), __uint_as_float(w[7]));
           } else {
-            const float4 b0 = ld_shared_f4(sbias + (ci * COLS + j * 8) * 4);
-            const float4 b1 = ld_shared_f4(sbias + (ci * COLS + j * 8 + 4) * 4);
+            const float4 b0 = ld_shared_f4(sbias + (u * 32 + j * 8) * 4);
+            const float4 b1 = ld_shared_f4(sbias + (u * 32 + j * 8 + 4) * 4);
             o0 = pack_bf16(fmaxf(__uint_as_float(w[0]) + b0.x, lo), fmaxf(__uint_as_float(w[1]) + b0.y, lo));
             o1 = pack_bf16(fmaxf(__uint_as_float(w[2]) + b0.z, lo), fmaxf(__uint_as_float(w[3]) + b0.w, lo));
             o2 = pack_bf16(fmaxf(__uint_as_float(w[4]) + b1.x, lo), fmaxf(__uint_as_float(w[5]) + b1.y, lo));
             o3 = pack_bf16(fmaxf(__uint_as_float(w[6]) + b1.z, lo), fmaxf(__uint_as_float(w[7]) + b1.w, lo));
           }
-          st_shared_v4(rowp + ((j ^ sw) << 4), o0, o1, o2, o3);
+          st_shared_v4(rowp + (((h * 4 + j) ^ sw) << 4), o0, o1, o2, o3);
         }
       }
-      fence_proxy_async_smem();
-      __syncwarp();
-      if (lane == 0) {
-        if (accum) tma_reduce_add_2d(tmC, buf, n0 + ci * COLS, row0);
-        else tma_store_2d(tmC, buf, n0 + ci * COLS, row0);
-        tma_store_commit();
+      if (h == UPC - 1) {
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          if (accum) tma_reduce_add_2d(tmC, buf, n0 + ci * (32 * UPC), row0);
+          else tma_store_2d(tmC, buf, n0 + ci * (32 * UPC), row0);
+          tma_store_commit();
+        }
+        if (STATS && !F32) {
+          // Column sums of what was just staged (the bf16-rounded values the next kernel will
+          // read): lane l owns columns 2l, 2l+1 of the chunk and walks down the 32 rows; with
+          // the 128B swizzle the 32 lanes of one row read hit 32 different banks.
+          const uint32_t colp = buf + ((lane & 3) << 2);
+          const uint32_t j = lane >> 2;
+#pragma unroll
+          for (int r = 0; r < 32; ++r) {
+            uint32_t w;
+            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(colp + r * 128 + ((j ^ (r & 7)) << 4)));
+            const float a = __uint_as_float(w << 16), b = __uint_as_float(w & 0xffff0000u);
+            cs[ci][0] += a;
+            cs[ci][1] += b;
+            cs[ci][2] = fmaf(a, a, cs[ci][2]);
+            cs[ci][3] = fmaf(b, b, cs[ci][3]);
+          }
+        }
+        stage_buf ^= 1;
       }
-      stage_buf ^= 1;
     }
+  }
+}
+
+// Add a warp's column statistics of tile column block n0 to the global accumulator and clear them.
+template <int BN>
+__device__ __forceinline__ void flush_colstats(float (&cs)[BN / 64][4], float* __restrict__ out,
+                                               int n0, int N, int replica, int lane) {
+  float* dst = out + static_cast<size_t>(replica) * 2 * N;
+#pragma unroll
+  for (int ci = 0; ci < BN / 64; ++ci) {
+    const int n = n0 + ci * 64 + 2 * lane;
+    if (n < N) {
+      atomicAdd(dst + n, cs[ci][0]);
+      atomicAdd(dst + N + n, cs[ci][2]);
+    }
+    if (n + 1 < N) {
+      atomicAdd(dst + n + 1, cs[ci][1]);
+      atomicAdd(dst + N + n + 1, cs[ci][3]);
+    }
+    cs[ci][0] = cs[ci][1] = cs[ci][2] = cs[ci][3] = 0.f;
   }
 }
 
@@ -196,7 +259,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int num_tiles = p.m_tiles * p.n_tiles;
+  const int num_tiles = p.m_tiles * p.n_tiles * p.splits;
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -204,9 +267,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m0 = (tile / p.n_tiles) * BM;
-        const int n0 = (tile % p.n_tiles) * BN;
-        for (int kb = 0; kb < p.k_blocks; ++kb) {
+        const WorkItem it = decode_work<BN>(p, tile);
+        const int m0 = it.m0, n0 = it.n0;
+        for (int kb = it.kb0; kb < it.kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
           uint8_t* sa = smem_a + stage * kAStageBytes;
@@ -247,7 +310,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BN;
-        for (int kb = 0; kb < p.k_blocks; ++kb) {
+        const WorkItem it = decode_work<BN>(p, tile);
+        for (int kb = it.kb0; kb < it.kb1; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           const uint64_t adesc =
@@ -257,10 +321,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k) {
             umma_bf16(tmem_d, adesc + static_cast<uint64_t>(k * p.a_kadv),
-                      bdesc + static_cast<uint64_t>(k * p.b_kadv), idesc, (kb | k) != 0);
+                      bdesc + static_cast<uint64_t>(k * p.b_kadv), idesc, ((kb - it.kb0) | k) != 0);
           }
           umma_commit(&empty_bar[stage]);  // smem slot reusable once these MMAs retire
-          if (kb == p.k_blocks - 1) umma_commit(&tfull_bar[acc]);
+          if (kb == it.kb1 - 1) umma_commit(&tfull_bar[acc]);
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       }
@@ -280,11 +344,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 : ((p.ldc & 7) == 0 && (reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
     int t = 0;
     int stage_buf = 0;
+    float cs[BN / 64][4];            // column statistics carried across tiles with the same n0
+    int cs_n0 = -1;
+#pragma unroll
+    for (int ci = 0; ci < BN / 64; ++ci) cs[ci][0] = cs[ci][1] = cs[ci][2] = cs[ci][3] = 0.f;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
       const int acc = t & 1;
       const uint32_t acc_phase = (t >> 1) & 1;
-      const int m0 = (tile / p.n_tiles) * BM;
-      const int n0 = (tile % p.n_tiles) * BN;
+      const WorkItem it = decode_work<BN>(p, tile);
+      const int m0 = it.m0, n0 = it.n0;
       const int row = m0 + q * 32 + lane;
       const bool row_ok = row < p.M;
       mbar_wait(&tfull_bar[acc], acc_phase);
@@ -308,12 +376,22 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const bool plain = !has_bias && !relu;
         const uint32_t stg = smem_u32(smem_stage) + (warp - 2) * 8192;
         if (!(p.debug & 16)) {
-          if (out_f32)
-            epilogue_tma<BN, true>(&tmC, taddr, stg, sbias, stage_buf, n0, m0 + q * 32, p.N, lo, plain,
-                                   accum, lane);
-          else
-            epilogue_tma<BN, false>(&tmC, taddr, stg, sbias, stage_buf, n0, m0 + q * 32, p.N, lo, plain,
-                                    accum, lane);
+          if (out_f32) {
+            float none[1][4];
+            epilogue_tma<BN, true, false>(&tmC, taddr, stg, sbias, stage_buf, n0, m0 + q * 32, p.N, lo,
+                                          plain, accum, lane, none);
+          } else if (p.colstats != nullptr) {
+            if (n0 != cs_n0) {
+              if (cs_n0 >= 0)
+                flush_colstats<BN>(cs, p.colstats, cs_n0, p.N, (blockIdx.x * 4 + q) % kColStatCopies, lane);
+              cs_n0 = n0;
+            }
+            epilogue_tma<BN, false, true>(&tmC, taddr, stg, sbias, stage_buf, n0, m0 + q * 32, p.N, lo,
+                                          plain, accum, lane, cs);
+          } else {
+            epilogue_tma<BN, false, false>(&tmC, taddr, stg, sbias, stage_buf, n0, m0 + q * 32, p.N, lo,
+                                           plain, accum, lane, cs);
+          }
         }
         tc_fence_before();
         __syncwarp();
@@ -415,6 +493,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty_bar[acc]);
     }
+    if (p.colstats != nullptr && cs_n0 >= 0)
+      flush_colstats<BN>(cs, p.colstats, cs_n0, p.N, (blockIdx.x * 4 + q) % kColStatCopies, lane);
     if (p.tma_store && lane == 0) tma_store_wait<0>();   // staging smem must outlive its stores
   }
 
@@ -496,7 +576,7 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUt
                                      Cfg::kSmemBytes));
     configured = true;
   }
-  const int tiles = args.m_tiles * args.n_tiles;
+  const int tiles = args.m_tiles * args.n_tiles * args.splits;
   const int grid = tiles < num_sms() ? tiles : num_sms();
   kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(tmA, tmB, tmC, args);
   return check_cuda(cudaGetLastError(), "gemm_tcgen05 launch");
@@ -524,10 +604,25 @@ extern "C" int cb2_gemm_debug_descriptors(int enable, unsigned a_lbo, unsigned a
   return 0;
 }
 
+extern "C" int cb2_gemm_bf16_ex(const void* A, const void* B, void* C, const float* bias,
+                                const void* relu_mask, int M, int N, int K, int lda, int ldb,
+                                int ldc, int ldmask, int a_mn, int b_mn, unsigned flags, int block_n,
+                                int split_k, float* colstats, void* stream);
+
 extern "C" int cb2_gemm_bf16(const void* A, const void* B, void* C, const float* bias,
                              const void* relu_mask, int M, int N, int K, int lda, int ldb, int ldc,
                              int ldmask, int a_mn, int b_mn, unsigned flags, int block_n,
                              void* stream) {
+  return cb2_gemm_bf16_ex(A, B, C, bias, relu_mask, M, N, K, lda, ldb, ldc, ldmask, a_mn, b_mn, flags,
+                          block_n, 1, nullptr, stream);
+}
+
+extern "C" int cb2_gemm_colstat_copies(void) { return kColStatCopies; }
+
+extern "C" int cb2_gemm_bf16_ex(const void* A, const void* B, void* C, const float* bias,
+                                const void* relu_mask, int M, int N, int K, int lda, int ldb,
+                                int ldc, int ldmask, int a_mn, int b_mn, unsigned flags, int block_n,
+                                int split_k, float* colstats, void* stream) {
   if (M <= 0 || N <= 0 || K <= 0) {
     set_last_error("gemm: empty problem M=%d N=%d K=%d", M, N, K);
     return CB2_ERR_ARG;
@@ -599,6 +694,34 @@ extern "C" int cb2_gemm_bf16(const void* A, const void* B, void* C, const float*
   args.m_tiles = (M + BM - 1) / BM;
   args.n_tiles = (N + bn - 1) / bn;
   args.k_blocks = (K + BK - 1) / BK;
+  // Split-K: partial products of K slices are summed by the TMA reduce-add epilogue, so it needs
+  // an fp32 output in ACCUM mode (C holds zeros or a running sum).  0 = pick: enough slices to
+  // give every SM a work item, at least four k-blocks each.
+  const bool can_split = tma_store && out_f32 && (flags & CB2_GEMM_ACCUM) && bias == nullptr &&
+                         !(flags & CB2_GEMM_RELU);
+  int splits = split_k;
+  if (splits == 0) {
+    splits = 1;
+    const int tiles = args.m_tiles * args.n_tiles;
+    if (can_split && tiles * 2 <= num_sms()) {
+      splits = num_sms() / tiles;
+      if (splits > args.k_blocks / 4) splits = args.k_blocks / 4;
+      if (splits < 1) splits = 1;
+    }
+  }
+  if (splits > 1 && !can_split) {
+    set_last_error("gemm: split_k=%d needs OUT_F32|ACCUM, a TMA-storable C and no bias/ReLU", splits);
+    return CB2_ERR_ARG;
+  }
+  if (splits > args.k_blocks) splits = args.k_blocks;
+  args.kb_per_split = (args.k_blocks + splits - 1) / splits;
+  args.splits = (args.k_blocks + args.kb_per_split - 1) / args.kb_per_split;   // no empty slices
+  args.colstats = colstats;
+  args.m_fast = colstats != nullptr ? 1 : 0;
+  if (colstats != nullptr && (!tma_store || out_f32 || bias != nullptr)) {
+    set_last_error("gemm: column statistics need a bf16, TMA-storable C and no bias");
+    return CB2_ERR_ARG;
+  }
   // K-major, 128B swizzle: 8-row groups are 1024 B apart (SBO); LBO unused (=1);
   //                        one UMMA_K step = 16 elements = 32 B inside the swizzle span.
   // MN-major, 128B swizzle: 64-element MN chunks are BK*128 B apart (LBO); 8-k-row groups are

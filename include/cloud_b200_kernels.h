@@ -44,6 +44,15 @@ int cb2_gemm_bf16(const void* A, const void* B, void* C, const float* bias /*nul
                   int N, int K, int lda, int ldb, int ldc, int ldmask, int a_mn, int b_mn,
                   unsigned flags, int block_n /*0 = auto, else 64|128|256*/, void* stream);
 /* Test hook: override the shared-memory matrix-descriptor fields (16-byte units). */
+/* cb2_gemm_bf16 plus: split_k (1 = off, 0 = choose; > 1 needs OUT_F32|ACCUM: K slices are summed
+ * into C by TMA reduce-adds, so C must hold zeros or a running sum) and colstats (nullable):
+ * [cb2_gemm_colstat_copies()][2][N] fp32 accumulators that receive, per output column, the sum and
+ * the sum of squares of the bf16-rounded results - the batch statistics of a following batch
+ * normalisation, for free while the tile is still on chip (bf16 C, no bias). */
+int cb2_gemm_bf16_ex(const void* A, const void* B, void* C, const float* bias, const void* relu_mask,
+                     int M, int N, int K, int lda, int ldb, int ldc, int ldmask, int a_mn, int b_mn,
+                     unsigned flags, int block_n, int split_k, float* colstats, void* stream);
+int cb2_gemm_colstat_copies(void);
 /* Diagnostics only (bench/gemm_epilogue_probe.py): bit mask of epilogue phases to skip. */
 int cb2_gemm_debug_epilogue(int bits);
 int cb2_gemm_debug_descriptors(int enable, unsigned a_lbo, unsigned a_sbo, unsigned b_lbo,
@@ -81,6 +90,8 @@ int cb2_u8_to_bf16_normalize(const uint8_t* in, void* out, size_t n_pixels, int 
  *   forward : y = act(gamma * (x - mean) / sqrt(var + eps) + beta (+ residual)); training != 0 uses
  *             batch statistics, refreshes run_mean/run_var (momentum = update rate; mean_bias,
  *             nullable, is added to the mean that goes into run_mean) and saves mean / inv-std.
+ *             training == 2: `sums` already holds the batch sums (written by the colstats
+ *             epilogue of cb2_gemm_bf16_ex) and the statistics pass is skipped.
  *   backward: dx, dbeta, dgamma (and dres = masked dy when a residual was added before the ReLU);
  *             y nullable: with relu != 0 and y == NULL the ReLU mask is recomputed from x.
  * Reference workload: the 53 BatchNormalization layers of ResNet-50

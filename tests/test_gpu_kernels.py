@@ -274,3 +274,90 @@ def test_fused_batch_norm(C, HW, N, relu, with_res):
         if relu:
             yo = torch.relu(yo)
     _check_close(yi, yo, 2e-2, 2e-2, "bn inference")
+
+
+@pytest.mark.parametrize("M,N,K,split", [(256, 64, 8192, 0), (64, 256, 200704 // 8, 0), (512, 2048, 3136, 4),
+                                         (136, 520, 1000, 3), (128, 128, 256, 8)])
+def test_gemm_split_k_wgrad(M, N, K, split):
+    """dW = dY^T @ X with the reduction cut into K slices summed by TMA reduce-adds."""
+    torch.manual_seed(5)
+    a = _rand_bf16(K, M, scale=0.5)          # stored [K, M]  (A MN-major)
+    b = _rand_bf16(K, N, scale=0.5)          # stored [K, N]  (B MN-major)
+    out = torch.zeros(M, N, device=_dev())
+    ops.gemm(a, b, a_mn=True, b_mn=True, out=out, accumulate=True, split_k=split)
+    want = a.float().t() @ b.float()
+    _check_close(out, want, 1e-3, 1e-3 * math.sqrt(K), "split-K wgrad")
+    # a second call accumulates on top
+    ops.gemm(a, b, a_mn=True, b_mn=True, out=out, accumulate=True, split_k=split)
+    _check_close(out, 2 * want, 1e-3, 2e-3 * math.sqrt(K), "split-K wgrad, second accumulate")
+
+
+@pytest.mark.parametrize("M,N,K", [(200704 // 16, 256, 64), (3136, 2048, 512), (1000, 520, 136), (128, 64, 64),
+                                   (50176 // 4, 128, 512)])
+def test_gemm_column_statistics(M, N, K):
+    """The colstats epilogue returns sum / sum of squares of the bf16 output per column."""
+    torch.manual_seed(6)
+    a, b = _rand_bf16(M, K), _rand_bf16(N, K, scale=0.2)
+    stats = torch.zeros(8, 2, N, device=_dev())
+    c = ops.gemm(a, b, colstats=stats)
+    want_c = a.float() @ b.float().t()
+    _check_close(c, want_c, 2e-2, 2e-2, "gemm with colstats")
+    cf = c.float()
+    tot = stats.sum(0)
+    _check_close(tot[0], cf.sum(0), 1e-3, 1e-3 * math.sqrt(M) * cf.abs().max().item(), "column sums")
+    _check_close(tot[1], (cf * cf).sum(0), 1e-3, 1e-2, "column sums of squares")
+
+
+@pytest.mark.parametrize("N,H,Cin,Cout,bias", [(8, 56, 64, 256, False), (4, 14, 1024, 256, False),
+                                               (2, 7, 512, 2048, True), (3, 28, 128, 512, False)])
+def test_conv1x1_on_gemm_matches_conv2d(N, H, Cin, Cout, bias):
+    torch.manual_seed(7)
+    dev = _dev()
+    x = torch.randn(N, Cin, H, H, device=dev).to(torch.bfloat16) \
+        .contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    w = (torch.randn(Cout, Cin, 1, 1, device=dev) / math.sqrt(Cin)).to(torch.bfloat16) \
+        .contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    b = (torch.randn(Cout, device=dev) * 0.1).requires_grad_(True) if bias else None
+    assert ops.conv1x1_supported(x, w, (1, 1), 0, (1, 1))
+    y = ops.conv1x1(x, w, b, bn_stats=not bias)
+    assert y.shape == (N, Cout, H, H) and y.is_contiguous(memory_format=torch.channels_last)
+    gy = torch.randn_like(y)
+    y.backward(gy)
+    xr = x.detach().float().requires_grad_(True)
+    wr = w.detach().float().requires_grad_(True)
+    br = b.detach().clone().requires_grad_(True) if bias else None
+    yr = torch.nn.functional.conv2d(xr, wr, br)
+    yr.backward(gy.float())
+    _check_close(y, yr, 2e-2, 2e-2, "conv1x1 fwd")
+    _check_close(x.grad, xr.grad, 2e-2, 2e-2 * math.sqrt(Cout / 64), "conv1x1 dX")
+    _check_close(w.grad, wr.grad, 2e-2, 2e-2 * math.sqrt(N * H * H), "conv1x1 dW")
+    if bias:
+        _check_close(b.grad, br.grad, 1e-2, 1e-2 * math.sqrt(N * H * H), "conv1x1 db")
+    else:
+        sums = y._cb2_bn_sums.view(8, 2, Cout).sum(0)
+        yf = y.detach().float()
+        _check_close(sums[0], yf.sum((0, 2, 3)), 1e-3, 1e-2 * math.sqrt(N * H * H), "conv1x1 channel sums")
+        _check_close(sums[1], (yf * yf).sum((0, 2, 3)), 1e-3, 1e-1, "conv1x1 channel sums of squares")
+
+
+def test_batch_norm_with_statistics_from_the_conv_epilogue():
+    """conv1x1(bn_stats) -> fused BN must equal conv -> BN with its own statistics pass."""
+    torch.manual_seed(8)
+    dev = _dev()
+    N, H, Cin, Cout = 8, 28, 128, 256
+    x = torch.randn(N, Cin, H, H, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(Cout, Cin, 1, 1, device=dev) / math.sqrt(Cin)).to(torch.bfloat16) \
+        .contiguous(memory_format=torch.channels_last)
+    gamma = (torch.rand(Cout, device=dev) + 0.5).requires_grad_(True)
+    beta = (torch.randn(Cout, device=dev) * 0.1).requires_grad_(True)
+    outs = []
+    for fused in (True, False):
+        rm, rv = torch.zeros(Cout, device=dev), torch.ones(Cout, device=dev)
+        y = ops.conv1x1(x, w, None, bn_stats=fused)
+        sums = getattr(y, "_cb2_bn_sums", None)
+        assert (sums is not None) == fused
+        z = ops.batch_norm_nhwc(y, gamma, beta, rm, rv, True, 0.1, 1e-5, relu=True, sums=sums)
+        outs.append((z.detach().float(), rm, rv))
+    _check_close(outs[0][0], outs[1][0], 1e-2, 1e-2, "BN output")
+    _check_close(outs[0][1], outs[1][1], 1e-4, 1e-4, "running mean")
+    _check_close(outs[0][2], outs[1][2], 1e-3, 1e-4, "running var")
