@@ -22,8 +22,10 @@ from __future__ import annotations
 import torch
 import torch.nn.functional as F
 
-from . import bn as _bn
-from . import dense as _dense
+import importlib
+
+_bn = importlib.import_module(__package__ + ".bn")
+_dense = importlib.import_module(__package__ + ".dense")     # the module (ops.dense is also an op)
 
 def supported(x: torch.Tensor, w: torch.Tensor, stride, padding, dilation) -> bool:
     """True when ``conv2d(x, w)`` can run as one GEMM on the tcgen05 kernel."""

@@ -9,6 +9,8 @@
 // Reference workload: the BatchNormalization layers of ResNet-50 (K8 in SURVEY.md section 2.5;
 // core/tests/examples/call_run_within_script_with_keras_fit.py:79-83) which TensorFlow runs as
 // separate cuDNN batch-norm, add and ReLU kernels.
+#include <stdlib.h>
+
 #include <mutex>
 
 #include "optim.cuh"
@@ -370,7 +372,7 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
 
 // Grid: a multiple of the slab count, about four CTAs per SM, never more row groups than there
 // are CTA-iterations of rows.
-static int bn_grid(int M, int C) {
+static int bn_grid(int M, int C, bool backward = false) {
   const int w = C < 64 ? C : 64;
   const int slabs = C / w;
   const int rows = kBnThreads / (w >> 3);
@@ -379,7 +381,14 @@ static int bn_grid(int M, int C) {
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   long long nrg = (static_cast<long long>(M) + rows - 1) / rows;
-  long long cap = (static_cast<long long>(sms) * 4) / slabs;
+  // CTAs per SM: measured on B200 over the ResNet-50 shapes (bench/bn_probe.py) - the one- and
+  // two-stream forward kernels peak at 4 (6.0 TB/s on 411 MB), the backward kernels at 6 (6.1)
+  static const int env_per_sm = [] {
+    const char* e = getenv("TFC_BN_CTAS_PER_SM");
+    return e ? atoi(e) : 0;
+  }();
+  const int per_sm = env_per_sm > 0 ? env_per_sm : (backward ? 6 : 4);
+  long long cap = (static_cast<long long>(sms) * per_sm) / slabs;
   if (cap < 1) cap = 1;
   if (nrg > cap) nrg = cap;
   if (nrg < 1) nrg = 1;
@@ -435,7 +444,7 @@ extern "C" int cb2_bn_backward(const void* dy, const void* y, const void* x, con
   int rc = bn_check(M, C, "bn_backward");
   if (rc) return rc;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  const int grid = bn_grid(M, C);
+  const int grid = bn_grid(M, C, true);
   const __nv_bfloat16* dyp = reinterpret_cast<const __nv_bfloat16*>(dy);
   const __nv_bfloat16* yp = reinterpret_cast<const __nv_bfloat16*>(y);
   const __nv_bfloat16* xp = reinterpret_cast<const __nv_bfloat16*>(x);

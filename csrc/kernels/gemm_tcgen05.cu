@@ -179,15 +179,34 @@ __device__ __forceinline__ void epilogue_tma(const CUtensorMap* tmC, uint32_t ta
           // the 128B swizzle the 32 lanes of one row read hit 32 different banks.
           const uint32_t colp = buf + ((lane & 3) << 2);
           const uint32_t j = lane >> 2;
+          // loads in batches of 16 ahead of the arithmetic: with one warp per scheduler nothing
+          // else hides the shared-memory latency
 #pragma unroll
-          for (int r = 0; r < 32; ++r) {
-            uint32_t w;
-            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(colp + r * 128 + ((j ^ (r & 7)) << 4)));
-            const float a = __uint_as_float(w << 16), b = __uint_as_float(w & 0xffff0000u);
-            cs[ci][0] += a;
-            cs[ci][1] += b;
-            cs[ci][2] = fmaf(a, a, cs[ci][2]);
-            cs[ci][3] = fmaf(b, b, cs[ci][3]);
+          for (int r0 = 0; r0 < 32; r0 += 16) {
+            uint32_t wv[16];
+#pragma unroll
+            for (int r = 0; r < 16; ++r)
+              asm volatile("ld.shared.b32 %0, [%1];"
+                           : "=r"(wv[r])
+                           : "r"(colp + (r0 + r) * 128 + ((j ^ ((r0 + r) & 7)) << 4)));
+            float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;      // second set of chains: more ILP
+#pragma unroll
+            for (int r = 0; r < 16; r += 2) {
+              const float a = __uint_as_float(wv[r] << 16), b = __uint_as_float(wv[r] & 0xffff0000u);
+              const float c = __uint_as_float(wv[r + 1] << 16), d = __uint_as_float(wv[r + 1] & 0xffff0000u);
+              cs[ci][0] += a;
+              cs[ci][1] += b;
+              cs[ci][2] = fmaf(a, a, cs[ci][2]);
+              cs[ci][3] = fmaf(b, b, cs[ci][3]);
+              s0 += c;
+              s1 += d;
+              q0 = fmaf(c, c, q0);
+              q1 = fmaf(d, d, q1);
+            }
+            cs[ci][0] += s0;
+            cs[ci][1] += s1;
+            cs[ci][2] += q0;
+            cs[ci][3] += q1;
           }
         }
         stage_buf ^= 1;
@@ -639,6 +658,12 @@ extern "C" int cb2_gemm_bf16_ex(const void* A, const void* B, void* C, const flo
   }
   const bool softmax = (flags & CB2_GEMM_SOFTMAX) != 0;
   int bn = block_n;
+  const bool want_split = split_k != 1 && (flags & CB2_GEMM_OUT_F32) && (flags & CB2_GEMM_ACCUM);
+  if (bn == 0 && want_split) {
+    // split-K fills the machine whatever the tile count is: take the widest tile (best MMA shape,
+    // least operand traffic); measured on the ResNet-50 wgrad shapes (bench/wgrad_probe.py)
+    bn = N >= 256 ? 256 : (N >= 128 ? 128 : 64);
+  }
   if (bn == 0) {
     if (N <= 64) bn = 64;
     else if (N <= 128) bn = 128;
@@ -704,8 +729,8 @@ extern "C" int cb2_gemm_bf16_ex(const void* A, const void* B, void* C, const flo
     splits = 1;
     const int tiles = args.m_tiles * args.n_tiles;
     if (can_split && tiles * 2 <= num_sms()) {
-      splits = num_sms() / tiles;
-      if (splits > args.k_blocks / 4) splits = args.k_blocks / 4;
+      splits = num_sms() / tiles;                 // one wave of work items
+      if (splits > args.k_blocks / 2) splits = args.k_blocks / 2;
       if (splits < 1) splits = 1;
     }
   }
