@@ -113,7 +113,8 @@ def main() -> int:
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="cloud_b200", choices=["cloud_b200", "reference"])
-    ap.add_argument("--batch-per-gpu", type=int, default=64)
+    ap.add_argument("--batch-per-gpu", type=int, default=256,
+                    help="per-GPU batch (weak scaling); 256 fills a B200: ~20 GB of activations")
     ap.add_argument("--classes", type=int, default=1000)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--profile-e2e", action="store_true", help="cProfile of the timed fit() to stderr")
@@ -252,7 +253,7 @@ def main() -> int:
                        "parallelism": f"dp{world}", "comm_backend": eng.comm.backend,
                        "allreduce_algos": [g.algo for g in eng.groups],
                        "cuda_graph": bool(model._graph and model._graph.get("graph") is not None),
-                       "l2": "per-step working set (activations ~5 GB) >> 126 MB L2; no explicit flush"},
+                       "l2": f"per-step working set (activations ~{B * 0.08:.0f} GB) >> 126 MB L2; no explicit flush"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(gpu_launches),
             "loss": loss_now,
         }

@@ -20,9 +20,9 @@ import torch.nn.functional as F
 
 from .. import ops
 
-# 1x1 / stride-1 convolutions run on the tcgen05 GEMM (ops/conv.py); TFC_CONV1X1_GEMM=0 sends them
-# to cuDNN like every other convolution
-_CONV1X1_GEMM = os.environ.get("TFC_CONV1X1_GEMM", "1") != "0"
+# 1x1 / stride-1 convolutions go through ops/conv.py, which puts their weight gradient (default) or
+# all three GEMMs (TFC_CONV1X1_GEMM=all) on the tcgen05 kernel; TFC_CONV1X1_GEMM=0: plain cuDNN
+_CONV1X1_GEMM = ops.conv1x1_mode() != "0"
 
 _NAME_COUNTS: dict[str, int] = {}
 

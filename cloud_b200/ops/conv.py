@@ -23,6 +23,7 @@ import torch
 import torch.nn.functional as F
 
 import importlib
+import os
 
 _bn = importlib.import_module(__package__ + ".bn")
 _dense = importlib.import_module(__package__ + ".dense")     # the module (ops.dense is also an op)
@@ -41,16 +42,29 @@ def _as_matrix(t: torch.Tensor) -> torch.Tensor:
     return t.permute(0, 2, 3, 1).reshape(n * h * w, c)
 
 
+def mode() -> str:
+    """Which of the three GEMMs of a 1x1 convolution run on the tcgen05 kernel
+    (``TFC_CONV1X1_GEMM``): ``wgrad`` (default) - only the weight gradient, where the split-K
+    kernel beats cuBLAS + its split-K reduction on the ResNet-50 shapes (bench/wgrad_probe.py),
+    forward and input gradient stay on cuDNN; ``all`` - all three plus batch-norm statistics from
+    the forward epilogue; ``0`` - none."""
+    v = os.environ.get("TFC_CONV1X1_GEMM", "wgrad").lower()
+    return {"1": "all", "true": "all", "off": "0", "false": "0"}.get(v, v)
+
+
 class _Conv1x1Fn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, w, bias, colstats):
+    def forward(ctx, x, w, bias, colstats, all_gemm):
         n, cin, h, wd = x.shape
         cout = w.shape[0]
+        ctx.save_for_backward(x, w)
+        ctx.has_bias = bias is not None
+        ctx.all_gemm = all_gemm
+        if not all_gemm:
+            return F.conv2d(x, w, None if bias is None else bias.to(x.dtype))
         w2 = w.reshape(cout, cin)
         y = torch.empty((n, h, wd, cout), dtype=torch.bfloat16, device=x.device)
         _dense.gemm(_as_matrix(x), w2, bias=bias, out=y.view(n * h * wd, cout), colstats=colstats)
-        ctx.save_for_backward(x, w)
-        ctx.has_bias = bias is not None
         return y.permute(0, 3, 1, 2)
 
     @staticmethod
@@ -63,7 +77,10 @@ class _Conv1x1Fn(torch.autograd.Function):
             dy = dy.contiguous(memory_format=torch.channels_last)
         dy2 = _as_matrix(dy)
         dx = dw = db = None
-        if ctx.needs_input_grad[0]:
+        if ctx.needs_input_grad[0] and not ctx.all_gemm:
+            dx = torch.ops.aten.convolution_backward(
+                dy, x, w, None, (1, 1), (0, 0), (1, 1), False, (0, 0), 1, (True, False, False))[0]
+        elif ctx.needs_input_grad[0]:
             dxm = torch.empty((n, h, wd, cin), dtype=torch.bfloat16, device=x.device)
             _dense.gemm(dy2, w.reshape(cout, cin), b_mn=True, out=dxm.view(m, cin))
             dx = dxm.permute(0, 3, 1, 2)
@@ -79,7 +96,7 @@ class _Conv1x1Fn(torch.autograd.Function):
                 dw = ws.to(torch.bfloat16).view(cout, cin, 1, 1)
         if ctx.has_bias and ctx.needs_input_grad[2]:
             db = dy2.float().sum(0)
-        return dx, dw, db, None
+        return dx, dw, db, None, None
 
 
 def conv1x1(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None,
@@ -88,13 +105,14 @@ def conv1x1(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None,
     carries ``_cb2_bn_sums``: the batch statistics a following fused batch-norm can use as is."""
     if not x.is_cuda:
         return F.conv2d(x, w, bias)
+    all_gemm = mode() == "all"
     sums = None
-    if bn_stats and bias is None:
+    if all_gemm and bn_stats and bias is None:
         cout = w.shape[0]
         sums = _bn._scratch(16 * cout, x.device)
     if bias is not None and bias.dtype != torch.float32:
         bias = bias.float()
-    y = _Conv1x1Fn.apply(x, w, bias, sums)
+    y = _Conv1x1Fn.apply(x, w, bias, sums, all_gemm)
     if sums is not None:
         y._cb2_bn_sums = sums
     return y

@@ -308,9 +308,11 @@ def test_gemm_column_statistics(M, N, K):
     _check_close(tot[1], (cf * cf).sum(0), 1e-3, 1e-2, "column sums of squares")
 
 
+@pytest.mark.parametrize("gemm_mode", ["all", "wgrad"])
 @pytest.mark.parametrize("N,H,Cin,Cout,bias", [(8, 56, 64, 256, False), (4, 14, 1024, 256, False),
                                                (2, 7, 512, 2048, True), (3, 28, 128, 512, False)])
-def test_conv1x1_on_gemm_matches_conv2d(N, H, Cin, Cout, bias):
+def test_conv1x1_on_gemm_matches_conv2d(N, H, Cin, Cout, bias, gemm_mode, monkeypatch):
+    monkeypatch.setenv("TFC_CONV1X1_GEMM", gemm_mode)
     torch.manual_seed(7)
     dev = _dev()
     x = torch.randn(N, Cin, H, H, device=dev).to(torch.bfloat16) \
@@ -333,15 +335,16 @@ def test_conv1x1_on_gemm_matches_conv2d(N, H, Cin, Cout, bias):
     _check_close(w.grad, wr.grad, 2e-2, 2e-2 * math.sqrt(N * H * H), "conv1x1 dW")
     if bias:
         _check_close(b.grad, br.grad, 1e-2, 1e-2 * math.sqrt(N * H * H), "conv1x1 db")
-    else:
+    elif gemm_mode == "all":
         sums = y._cb2_bn_sums.view(8, 2, Cout).sum(0)
         yf = y.detach().float()
         _check_close(sums[0], yf.sum((0, 2, 3)), 1e-3, 1e-2 * math.sqrt(N * H * H), "conv1x1 channel sums")
         _check_close(sums[1], (yf * yf).sum((0, 2, 3)), 1e-3, 1e-1, "conv1x1 channel sums of squares")
 
 
-def test_batch_norm_with_statistics_from_the_conv_epilogue():
+def test_batch_norm_with_statistics_from_the_conv_epilogue(monkeypatch):
     """conv1x1(bn_stats) -> fused BN must equal conv -> BN with its own statistics pass."""
+    monkeypatch.setenv("TFC_CONV1X1_GEMM", "all")
     torch.manual_seed(8)
     dev = _dev()
     N, H, Cin, Cout = 8, 28, 128, 256
