@@ -58,6 +58,8 @@ def _declare_kernels(lib: ctypes.CDLL) -> None:
     lib.cb2_gemm_bf16_ex.restype = i
     lib.cb2_gemm_bf16_ex.argtypes = [vp, vp, vp, vp, vp, i, i, i, i, i, i, i, i, i, u, i, i, vp, vp]
     lib.cb2_gemm_colstat_copies.restype = i
+    lib.cb2_gemm_splitk_bf16.restype = i
+    lib.cb2_gemm_splitk_bf16.argtypes = [vp, vp, vp, vp, vp, i, i, i, i, i, i, i, i, i, i, i, i, vp]
     lib.cb2_gemm_debug_epilogue.restype = i
     lib.cb2_gemm_debug_epilogue.argtypes = [i]
     lib.cb2_gemm_debug_descriptors.restype = i

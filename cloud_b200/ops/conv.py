@@ -11,7 +11,8 @@ hand-written kernel instead of cuDNN:
 * input gradient: ``dX = dY @ W`` (B operand MN-major, no transpose);
 * weight gradient: ``dW = dY^T @ X`` (both operands MN-major) with split-K - the reduction runs over
   N*H*W, up to 200 704 here, while dW has one to a few dozen tiles - summed by TMA reduce-adds
-  into an fp32 workspace.
+  into an fp32 workspace and rounded into the bf16 gradient arena by the last-arriving warp of
+  the same kernel.
 
 Reference workload: ResNet-50 through ``tf.keras.applications`` in
 core/tests/examples/call_run_within_script_with_keras_fit.py (K8 of SURVEY.md section 2.5); the
@@ -27,6 +28,9 @@ import os
 
 _bn = importlib.import_module(__package__ + ".bn")
 _dense = importlib.import_module(__package__ + ".dense")     # the module (ops.dense is also an op)
+
+_FINALIZE_IN_KERNEL = os.environ.get("TFC_WGRAD_FINALIZE", "0") == "1"
+
 
 def supported(x: torch.Tensor, w: torch.Tensor, stride, padding, dilation) -> bool:
     """True when ``conv2d(x, w)`` can run as one GEMM on the tcgen05 kernel."""
@@ -85,15 +89,26 @@ class _Conv1x1Fn(torch.autograd.Function):
             _dense.gemm(dy2, w.reshape(cout, cin), b_mn=True, out=dxm.view(m, cin))
             dx = dxm.permute(0, 3, 1, 2)
         if ctx.needs_input_grad[1]:
-            # split-K partial sums meet in an fp32 workspace that the engine zeroes once per step
-            ws = _bn._scratch(cout * cin, x.device).view(cout, cin)
-            _dense.gemm(dy2, _as_matrix(x), a_mn=True, b_mn=True, out=ws, accumulate=True, split_k=0)
-            if getattr(w, "_cb2_direct_grad", False) and w.grad is not None:
-                # straight into the engine's gradient arena (bf16) - no temporary, no autograd add
-                w.grad.view(cout, cin).add_(ws)
-                w._cb2_grad_written(w)
+            direct = getattr(w, "_cb2_direct_grad", False) and w.grad is not None
+            if _FINALIZE_IN_KERNEL:
+                # the kernel itself rounds the finished split-K sum into the bf16 destination
+                dst = w.grad.view(cout, cin) if direct else torch.zeros(
+                    (cout, cin), dtype=torch.bfloat16, device=x.device)
+                _dense.gemm_splitk_bf16(dy2, _as_matrix(x), dst)
+                if not direct:
+                    dw = dst.view(cout, cin, 1, 1)
             else:
-                dw = ws.to(torch.bfloat16).view(cout, cin, 1, 1)
+                # split-K slices meet in an fp32 workspace that the engine zeroes once per step;
+                # one add rounds it into the gradient arena (measured 1% faster end to end than
+                # the in-kernel finalize, whose serial tail costs more than the extra launch)
+                ws = _bn._scratch(cout * cin, x.device).view(cout, cin)
+                _dense.gemm(dy2, _as_matrix(x), a_mn=True, b_mn=True, out=ws, accumulate=True, split_k=0)
+                if direct:
+                    w.grad.view(cout, cin).add_(ws)
+                else:
+                    dw = ws.to(torch.bfloat16).view(cout, cin, 1, 1)
+            if direct:
+                w._cb2_grad_written(w)      # straight into the engine's arena: no autograd add
         if ctx.has_bias and ctx.needs_input_grad[2]:
             db = dy2.float().sum(0)
         return dx, dw, db, None, None

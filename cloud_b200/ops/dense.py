@@ -102,6 +102,41 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     return out
 
 
+_splitk_state: dict = {}      # device -> (fp32 workspace, counters); shared by stream-ordered calls
+
+
+def gemm_splitk_bf16(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn: bool = True,
+                     b_mn: bool = True, block_n: int = 0, split_k: int = 0) -> torch.Tensor:
+    """``out[M,N] += bf16(op(A) @ op(B)^T)`` with split-K and the final rounding done inside the
+    kernel (``cb2_gemm_splitk_bf16``): the weight-gradient GEMM of a 1x1 convolution, written
+    straight into a bf16 gradient buffer.  Default operand layout: both stored ``[K, M]`` / ``[K, N]``."""
+    global _launches
+    if a_mn:
+        K, M = a.shape
+    else:
+        M, K = a.shape
+    N = b.shape[1] if b_mn else b.shape[0]
+    if out.dtype != torch.bfloat16 or out.shape != (M, N) or out.stride(1) != 1:
+        raise ValueError("out must be a bf16 [M, N] matrix with unit inner stride")
+    if not a.is_cuda:
+        af = a.float().t() if a_mn else a.float()
+        bf = b.float() if b_mn else b.float().t()
+        out += (af @ bf).to(torch.bfloat16)
+        return out
+    st = _splitk_state.get(a.device)
+    if st is None or st[0].numel() < M * N:
+        ws = torch.zeros(max(M * N, 1 << 20), dtype=torch.float32, device=a.device)
+        counters = torch.zeros(4096, dtype=torch.int32, device=a.device)
+        st = _splitk_state[a.device] = (ws, counters)
+    ws, counters = st
+    rc = _lib.kernels().cb2_gemm_splitk_bf16(
+        _ptr(a), _ptr(b), _ptr(ws), _ptr(out), _ptr(counters), counters.numel(), M, N, K,
+        a.stride(0), b.stride(0), N, out.stride(0), int(a_mn), int(b_mn), block_n, int(split_k), _stream())
+    _lib.check(rc, "gemm_splitk_bf16")
+    _launches += 1
+    return out
+
+
 def _gemm_reference(a, b, a_mn, b_mn, bias, relu, softmax, relu_mask, out, out_dtype, accumulate):
     af = a.float().t() if a_mn else a.float()
     bf = b.float() if b_mn else b.float().t()

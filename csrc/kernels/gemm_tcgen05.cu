@@ -47,6 +47,9 @@ struct GemmArgs {
   int splits, kb_per_split;             // split-K: work item = (m tile, n tile, k slice)
   int m_fast;                           // work order: m tile index fastest (else n fastest)
   float* colstats;                      // [kColStatCopies][2][N] += column sums / sums of squares
+  __nv_bfloat16* fin_out;               // split-K finalize: fin_out += bf16(C) by the last slice
+  int fin_ld;                           //   row pitch of fin_out (elements)
+  unsigned* fin_counters;               //   [m_tiles * n_tiles * 4], zero between calls
 };
 
 template <int BN>
@@ -235,6 +238,87 @@ __device__ __forceinline__ void flush_colstats(float (&cs)[BN / 64][4], float* _
   }
 }
 
+// Split-K finalize, done by the kernel itself.  Every epilogue warp that has added its K slice of
+// a 32-row output slice into the fp32 workspace C bumps that slice's counter; the warp that
+// arrives last (counter == splits - 1) owns the complete sum: it adds it, rounded to bf16, into
+// fin_out (the gradient arena), puts the workspace slice back to zero and resets the counter, so
+// neither a reduction kernel nor a per-step memset of the workspace is needed.
+template <int BN>
+__device__ __forceinline__ void splitk_finalize(const GemmArgs& p, int row0, int n0, int slot,
+                                                int lane) {
+  unsigned old = 0;
+  if (lane == 0) {
+    tma_store_wait<0>();          // this warp's reduce-adds have been performed at L2
+    __threadfence();
+    old = atomicAdd(p.fin_counters + slot, 1u);
+  }
+  old = __shfl_sync(0xffffffffu, old, 0);
+  if (old != static_cast<unsigned>(p.splits - 1)) return;
+  __threadfence();
+  constexpr int CPL = BN / 32;                 // columns per lane: 2, 4 or 8
+  constexpr int RB = 8;                        // rows per batch: all their loads are issued first
+  const int c = n0 + lane * CPL;
+  float* ws = reinterpret_cast<float*>(p.C);
+  if (c < p.N) {
+#pragma unroll 1
+    for (int r0 = 0; r0 < 32; r0 += RB) {
+      float v[RB][CPL];
+      uint32_t o[RB][CPL / 2];
+#pragma unroll
+      for (int r = 0; r < RB; ++r) {
+        const int row = min(row0 + r0 + r, p.M - 1);          // clamped: loads stay in bounds
+        const float* wp = ws + static_cast<size_t>(row) * p.ldc + c;
+        const __nv_bfloat16* op = p.fin_out + static_cast<size_t>(row) * p.fin_ld + c;
+        if (CPL == 2) {
+          const float2 t = __ldcg(reinterpret_cast<const float2*>(wp));
+          v[r][0] = t.x; v[r][1] = t.y;
+          o[r][0] = *reinterpret_cast<const uint32_t*>(op);
+        } else if (CPL == 4) {
+          const float4 t = __ldcg(reinterpret_cast<const float4*>(wp));
+          v[r][0] = t.x; v[r][1] = t.y; v[r][2] = t.z; v[r][3] = t.w;
+          const uint2 u = *reinterpret_cast<const uint2*>(op);
+          o[r][0] = u.x; o[r][CPL / 2 - 1] = u.y;
+        } else {
+          const float4 t0 = __ldcg(reinterpret_cast<const float4*>(wp));
+          const float4 t1 = __ldcg(reinterpret_cast<const float4*>(wp + 4));
+          v[r][0] = t0.x; v[r][1] = t0.y; v[r][2] = t0.z; v[r][3] = t0.w;
+          v[r][CPL - 4] = t1.x; v[r][CPL - 3] = t1.y; v[r][CPL - 2] = t1.z; v[r][CPL - 1] = t1.w;
+          const uint4 u = *reinterpret_cast<const uint4*>(op);
+          o[r][0] = u.x; o[r][1 % (CPL / 2)] = u.y; o[r][CPL / 2 - 2 < 0 ? 0 : CPL / 2 - 2] = u.z;
+          o[r][CPL / 2 - 1] = u.w;
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < RB; ++r) {
+        const int row = row0 + r0 + r;
+        if (row < p.M) {
+          float* wp = ws + static_cast<size_t>(row) * p.ldc + c;
+          __nv_bfloat16* op = p.fin_out + static_cast<size_t>(row) * p.fin_ld + c;
+#pragma unroll
+          for (int k = 0; k < CPL / 2; ++k)
+            o[r][k] = pack_bf16(__uint_as_float(o[r][k] << 16) + v[r][2 * k],
+                                __uint_as_float(o[r][k] & 0xffff0000u) + v[r][2 * k + 1]);
+          if (CPL == 2) {
+            *reinterpret_cast<float2*>(wp) = make_float2(0.f, 0.f);
+            *reinterpret_cast<uint32_t*>(op) = o[r][0];
+          } else if (CPL == 4) {
+            *reinterpret_cast<float4*>(wp) = make_float4(0.f, 0.f, 0.f, 0.f);
+            *reinterpret_cast<uint2*>(op) = make_uint2(o[r][0], o[r][CPL / 2 - 1]);
+          } else {
+            *reinterpret_cast<float4*>(wp) = make_float4(0.f, 0.f, 0.f, 0.f);
+            *reinterpret_cast<float4*>(wp + 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+            *reinterpret_cast<uint4*>(op) = make_uint4(o[r][0], o[r][1 % (CPL / 2)],
+                                                       o[r][CPL / 2 - 2 < 0 ? 0 : CPL / 2 - 2],
+                                                       o[r][CPL / 2 - 1]);
+          }
+        }
+      }
+    }
+  }
+  __syncwarp();
+  if (lane == 0) p.fin_counters[slot] = 0;
+}
+
 template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -415,6 +499,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+        if (p.fin_out != nullptr)
+          splitk_finalize<BN>(p, m0 + q * 32, n0, ((m0 / BM) * p.n_tiles + n0 / BN) * 4 + q, lane);
         continue;
       }
 
@@ -628,6 +714,35 @@ extern "C" int cb2_gemm_bf16_ex(const void* A, const void* B, void* C, const flo
                                 int ldc, int ldmask, int a_mn, int b_mn, unsigned flags, int block_n,
                                 int split_k, float* colstats, void* stream);
 
+namespace {
+struct FinalizeArgs {
+  void* out = nullptr;
+  int ld = 0;
+  unsigned* counters = nullptr;
+  int n_counters = 0;
+};
+thread_local FinalizeArgs g_finalize;
+}  // namespace
+
+extern "C" int cb2_gemm_splitk_bf16(const void* A, const void* B, float* workspace, void* out_bf16,
+                                    unsigned* counters, int n_counters, int M, int N, int K, int lda,
+                                    int ldb, int ld_ws, int ld_out, int a_mn, int b_mn, int block_n,
+                                    int split_k, void* stream) {
+  if ((reinterpret_cast<uintptr_t>(out_bf16) & 15) || (ld_out & 7) || (ld_ws & 3) || counters == nullptr) {
+    set_last_error("gemm_splitk: out must be 16-byte aligned with a row pitch that is a multiple of 8");
+    return CB2_ERR_ARG;
+  }
+  g_finalize.out = out_bf16;
+  g_finalize.ld = ld_out;
+  g_finalize.counters = counters;
+  g_finalize.n_counters = n_counters;
+  const int rc = cb2_gemm_bf16_ex(A, B, workspace, nullptr, nullptr, M, N, K, lda, ldb, ld_ws, 0, a_mn,
+                                  b_mn, CB2_GEMM_OUT_F32 | CB2_GEMM_ACCUM, block_n, split_k, nullptr,
+                                  stream);
+  g_finalize = FinalizeArgs();
+  return rc;
+}
+
 extern "C" int cb2_gemm_bf16(const void* A, const void* B, void* C, const float* bias,
                              const void* relu_mask, int M, int N, int K, int lda, int ldb, int ldc,
                              int ldmask, int a_mn, int b_mn, unsigned flags, int block_n,
@@ -743,6 +858,20 @@ extern "C" int cb2_gemm_bf16_ex(const void* A, const void* B, void* C, const flo
   args.splits = (args.k_blocks + args.kb_per_split - 1) / args.kb_per_split;   // no empty slices
   args.colstats = colstats;
   args.m_fast = colstats != nullptr ? 1 : 0;
+  args.fin_out = reinterpret_cast<__nv_bfloat16*>(g_finalize.out);
+  args.fin_ld = g_finalize.ld;
+  args.fin_counters = g_finalize.counters;
+  if (args.fin_out != nullptr) {
+    if (!can_split) {
+      set_last_error("gemm_splitk: workspace must be TMA-storable fp32");
+      return CB2_ERR_ARG;
+    }
+    if (args.m_tiles * args.n_tiles * 4 > g_finalize.n_counters) {
+      set_last_error("gemm_splitk: %d counters needed, %d given", args.m_tiles * args.n_tiles * 4,
+                     g_finalize.n_counters);
+      return CB2_ERR_ARG;
+    }
+  }
   if (colstats != nullptr && (!tma_store || out_f32 || bias != nullptr)) {
     set_last_error("gemm: column statistics need a bf16, TMA-storable C and no bias");
     return CB2_ERR_ARG;

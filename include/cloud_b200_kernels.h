@@ -53,6 +53,17 @@ int cb2_gemm_bf16_ex(const void* A, const void* B, void* C, const float* bias, c
                      int M, int N, int K, int lda, int ldb, int ldc, int ldmask, int a_mn, int b_mn,
                      unsigned flags, int block_n, int split_k, float* colstats, void* stream);
 int cb2_gemm_colstat_copies(void);
+/* out_bf16[M,N] += bf16(op(A) @ op(B)^T) with the reduction cut into split_k slices (0 = choose).
+ * The slices meet in `workspace` (fp32 [M, ld_ws], all zero on entry) through TMA reduce-adds; the
+ * epilogue warp that completes a 32-row slice rounds it into out_bf16, re-zeroes that part of the
+ * workspace and resets its counter (`counters`: >= 4 * ceil(M/128) * ceil(N/block_n) unsigned, all
+ * zero on entry), so both are ready for the next call without a memset.  Calls that share a
+ * workspace / counters must be ordered on one stream.  Workload: 1x1-convolution weight gradients,
+ * dW[Cout,Cin] = dY^T X over N*H*W rows, written straight into the bf16 gradient arena. */
+int cb2_gemm_splitk_bf16(const void* A, const void* B, float* workspace, void* out_bf16,
+                         unsigned* counters, int n_counters, int M, int N, int K, int lda, int ldb,
+                         int ld_ws, int ld_out, int a_mn, int b_mn, int block_n, int split_k,
+                         void* stream);
 /* Diagnostics only (bench/gemm_epilogue_probe.py): bit mask of epilogue phases to skip. */
 int cb2_gemm_debug_epilogue(int bits);
 int cb2_gemm_debug_descriptors(int enable, unsigned a_lbo, unsigned a_sbo, unsigned b_lbo,

@@ -364,3 +364,23 @@ def test_batch_norm_with_statistics_from_the_conv_epilogue(monkeypatch):
     _check_close(outs[0][0], outs[1][0], 1e-2, 1e-2, "BN output")
     _check_close(outs[0][1], outs[1][1], 1e-4, 1e-4, "running mean")
     _check_close(outs[0][2], outs[1][2], 1e-3, 1e-4, "running var")
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 64, 8192), (64, 256, 25088), (512, 2048, 3136), (136, 520, 1000),
+                                   (1024, 256, 12544), (64, 64, 200704)])
+def test_gemm_split_k_finalized_in_kernel(M, N, K):
+    """cb2_gemm_splitk_bf16: bf16 out += A^T B, workspace and counters left clean for the next call."""
+    torch.manual_seed(9)
+    a = _rand_bf16(K, M, scale=0.5)
+    b = _rand_bf16(K, N, scale=0.5)
+    want = a.float().t() @ b.float()
+    out = torch.zeros(M, N, device=_dev(), dtype=torch.bfloat16)
+    for rep in (1, 2, 3):           # repeated calls reuse the shared workspace: it must come back zeroed
+        dense_ops.gemm_splitk_bf16(a, b, out)
+        if rep == 1:
+            _check_close(out, want, 1e-2, 1e-2 * math.sqrt(K), "split-K finalize")
+    # three accumulations, each rounded to bf16 on the way in
+    _check_close(out, 3 * want, 2e-2, 3e-2 * math.sqrt(K), "split-K finalize, accumulated")
+    ws, counters = dense_ops._splitk_state[_dev()]
+    assert int(counters.abs().sum().item()) == 0
+    assert float(ws.abs().max().item()) == 0.0
