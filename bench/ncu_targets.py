@@ -26,8 +26,20 @@ b2 = torch.randn(2048, 512, device=dev).to(torch.bfloat16)
 for _ in range(2):
     ops.gemm(a2, b2, bias=torch.zeros(2048, device=dev), relu=True)
 
-# batch norm fwd+bwd on the largest ResNet-50 activation (64 x 56 x 56 x 256) and a small one
-for (n, c, hw) in ((64, 256, 56), (64, 1024, 14)):
+# 1x1-convolution shapes: forward with the column-statistics epilogue, split-K weight gradient
+a3 = torch.randn(200704, 64, device=dev).to(torch.bfloat16)
+b3 = torch.randn(256, 64, device=dev).to(torch.bfloat16)
+stats = torch.zeros(8, 2, 256, device=dev)
+for _ in range(2):
+    ops.gemm(a3, b3, colstats=stats)
+dy4 = torch.randn(12544 * 4, 1024, device=dev).to(torch.bfloat16)
+x4 = torch.randn(12544 * 4, 256, device=dev).to(torch.bfloat16)
+ws4 = torch.zeros(1024, 256, device=dev)
+for _ in range(2):
+    ops.gemm(dy4, x4, a_mn=True, b_mn=True, out=ws4, accumulate=True, split_k=0)
+
+# batch norm fwd+bwd on the largest ResNet-50 activation (256 x 56 x 56 x 256) and a small one
+for (n, c, hw) in ((256, 256, 56), (64, 1024, 14)):
     x = torch.randn(n, c, hw, hw, device=dev).to(torch.bfloat16).contiguous(
         memory_format=torch.channels_last).requires_grad_(True)
     g = torch.ones(c, device=dev, requires_grad=True)
@@ -37,7 +49,7 @@ for (n, c, hw) in ((64, 256, 56), (64, 1024, 14)):
     y.backward(torch.ones_like(y))
 
 # stem max-pool
-xp = torch.rand(64, 64, 112, 112, device=dev).to(torch.bfloat16).contiguous(
+xp = torch.rand(256, 64, 112, 112, device=dev).to(torch.bfloat16).contiguous(
     memory_format=torch.channels_last).requires_grad_(True)
 yp = ops.max_pool_nhwc(xp, 3, 2, 1)
 yp.backward(torch.ones_like(yp))
