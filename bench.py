@@ -238,7 +238,9 @@ def main() -> int:
         e2e = {"value": n_img / dt, "unit": "img/s", "ms_per_step": dt / n_steps * 1e3,
                "h2d_bytes_per_step": int(model._h2d_bytes // n_steps),
                "d2h_bytes_per_step": int(model._d2h_bytes // max(len(seen), 1)),
-               "steps": n_steps, "losses_read": len(seen), "api": "keras.Model.fit"}
+               "steps": n_steps, "losses_read": len(seen), "api": "keras.Model.fit",
+               "host_ms_per_step": {k: round(v / n_steps * 1e3, 3) for k, v in
+                                    getattr(model, "_fit_profile", {}).items() if k.endswith("_s")}}
 
     if rank == 0:
         eng = model._engine

@@ -579,11 +579,20 @@ class Model(nn.Module):
             pf = _Prefetcher(source, self.device)
             step = -1
             epoch_t0 = time.perf_counter()
+            # where the host thread spends the epoch (bench.py reports it next to the e2e number)
+            prof = self._fit_profile = {"wait_data_s": 0.0, "launch_s": 0.0, "read_back_s": 0.0, "steps": 0}
+            t_mark = epoch_t0
             for step, (xd, yd, ev, n_global) in enumerate(pf):
+                now = time.perf_counter()
+                prof["wait_data_s"] += now - t_mark
                 if batch_logs:
                     cbl.call("on_train_batch_begin", step, {})
                 if ev is not None:
-                    torch.cuda.current_stream(self.device).wait_event(ev)
+                    cur = torch.cuda.current_stream(self.device)
+                    cur.wait_event(ev)
+                    xd.record_stream(cur)          # allocated on the loader's copy stream
+                    if yd is not None:
+                        yd.record_stream(cur)
                 xi = self._to_internal(xd)
                 yi = yd.to(self.device) if yd is not None else None
                 red = self._run_step(xi, yi, n_global)
@@ -591,12 +600,17 @@ class Model(nn.Module):
                 if self.optimizer._schedule is not None:
                     eng.set_lr(self.optimizer.current_lr())
                 acc += red[:n_aux]
+                t_launched = time.perf_counter()
+                prof["launch_s"] += t_launched - now
                 if batch_logs:
                     # read step i-1 while step i runs: the host never drains the device
                     snap = _HostSnap(acc, self.device)
                     if pending is not None:
                         self._emit_batch(cbl, pending)
                     pending = (step, snap)
+                t_mark = time.perf_counter()
+                prof["read_back_s"] += t_mark - t_launched
+                prof["steps"] = step + 1
                 if self.stop_training:
                     break
             if pending is not None:

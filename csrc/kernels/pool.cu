@@ -17,7 +17,16 @@ struct PoolGeom {
 
 // KS = k*16 + s for the compile-time specialisations (0: read k and s from the geometry).  All
 // index arithmetic is 32-bit (the host rejects tensors with 2^31 or more 16-byte groups): 64-bit
-// divisions made the first version of these kernels instruction-bound.
+// divisions made the first version of these kernels instruction-bound.  The arithmetic is packed
+// bf16x2 (max / compare-mask / masked add on two channels per instruction): max is exact in bf16,
+// and a gradient element is the sum of at most ceil(k/s)^2 bf16 values, nearly always one.
+__device__ __forceinline__ __nv_bfloat162 as_bf162(uint32_t w) {
+  return *reinterpret_cast<__nv_bfloat162*>(&w);
+}
+__device__ __forceinline__ uint32_t as_u32(__nv_bfloat162 v) {
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
 template <int KS>
 __global__ void __launch_bounds__(256)
 maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
@@ -31,38 +40,34 @@ maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restric
     const int ow = static_cast<int>(r % g.OW); r /= g.OW;
     const int oh = static_cast<int>(r % g.OH);
     const int n = static_cast<int>(r / g.OH);
-    float best[8];
-    int arg[8];
+    uint32_t best[4], arg[4];          // two channels per word: bf16 values / 16-bit tap codes
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { best[j] = -INFINITY; arg[j] = 0; }
+    for (int j = 0; j < 4; ++j) { best[j] = 0xff80ff80u; arg[j] = 0; }     // -inf, -inf
+    const __nv_bfloat16* xn = x + static_cast<size_t>(n) * g.H * g.W * g.C + c8;
 #pragma unroll
     for (int kh = 0; kh < K; ++kh) {
       const int h = oh * S - g.pad + kh;
 #pragma unroll
       for (int kw = 0; kw < K; ++kw) {
         const int w = ow * S - g.pad + kw;
-        Vec8 v;
-        if (h >= 0 && h < g.H && w >= 0 && w < g.W) {
-          v = unpack8_bf16(*reinterpret_cast<const uint4*>(
-              x + ((static_cast<size_t>(n) * g.H + h) * g.W + w) * g.C + c8));
-        } else {
+        uint4 v = make_uint4(0, 0, 0, 0);             // zero padding
+        if (h >= 0 && h < g.H && w >= 0 && w < g.W)
+          v = *reinterpret_cast<const uint4*>(xn + (static_cast<size_t>(h) * g.W + w) * g.C);
+        const uint32_t code2 = static_cast<uint32_t>(kh * K + kw) * 0x00010001u;
+        const uint32_t vv[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-          for (int j = 0; j < 8; ++j) v.v[j] = 0.f;     // zero padding
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t m = __hgt2_mask(as_bf162(vv[j]), as_bf162(best[j]));   // strict: first max wins
+          best[j] = (vv[j] & m) | (best[j] & ~m);
+          arg[j] = (code2 & m) | (arg[j] & ~m);
         }
-        const int code = kh * K + kw;
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (v.v[j] > best[j]) { best[j] = v.v[j]; arg[j] = code; }
       }
     }
-    Vec8 o;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) o.v[j] = best[j];
     const size_t oi = ((static_cast<size_t>(n) * g.OH + oh) * g.OW + ow) * g.C + c8;
-    *reinterpret_cast<uint4*>(y + oi) = pack8_bf16(o);
-    uint2 packed;
-    packed.x = arg[0] | (arg[1] << 8) | (arg[2] << 16) | (arg[3] << 24);
-    packed.y = arg[4] | (arg[5] << 8) | (arg[6] << 16) | (arg[7] << 24);
+    *reinterpret_cast<uint4*>(y + oi) = make_uint4(best[0], best[1], best[2], best[3]);
+    uint2 packed;                                      // one byte per channel
+    packed.x = __byte_perm(arg[0], arg[1], 0x6420);
+    packed.y = __byte_perm(arg[2], arg[3], 0x6420);
     *reinterpret_cast<uint2*>(idx + oi) = packed;
   }
 }
@@ -80,9 +85,14 @@ maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __restri
     const int w = static_cast<int>(r % g.W); r /= g.W;
     const int h = static_cast<int>(r % g.H);
     const int n = static_cast<int>(r / g.H);
-    float acc[8];
+    // specialised (k, s): at most four windows contain a pixel - packed bf16 accumulation;
+    // generic: up to k*k contributions, accumulated in fp32
+    __nv_bfloat162 acc[4];
+    float accf[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    for (int j = 0; j < 4; ++j) acc[j] = as_bf162(0u);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) accf[j] = 0.f;
     // windows (oh, ow) with oh*s - pad <= h <= oh*s - pad + k - 1
     const int hp = h + g.pad, wp = w + g.pad;
     int oh0 = (hp - K + S) / S;          // ceil((hp - k + 1) / s)
@@ -93,24 +103,38 @@ maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __restri
     for (int oh = oh0; oh <= oh1; ++oh) {
       const int kh = hp - oh * S;
       for (int ow = ow0; ow <= ow1; ++ow) {
-        const int code = kh * K + (wp - ow * S);
+        const uint32_t code4 = static_cast<uint32_t>(kh * K + (wp - ow * S)) * 0x01010101u;
         const size_t oi = ((static_cast<size_t>(n) * g.OH + oh) * g.OW + ow) * g.C + c8;
         const uint2 pk = *reinterpret_cast<const uint2*>(idx + oi);
-        const Vec8 gy = unpack8_bf16(*reinterpret_cast<const uint4*>(dy + oi));
-        // byte-wise compare of four arg-max codes at once: 0xff where the window's max is here
-        const uint32_t code4 = static_cast<uint32_t>(code) * 0x01010101u;
+        const uint4 gy = *reinterpret_cast<const uint4*>(dy + oi);
+        // byte-wise compare of four arg-max codes at once (0xff where this pixel was the max),
+        // widened to 16-bit lane masks
         const uint32_t m0 = __vcmpeq4(pk.x, code4), m1 = __vcmpeq4(pk.y, code4);
+        const uint32_t g0 = gy.x & __byte_perm(m0, 0, 0x1100), g1 = gy.y & __byte_perm(m0, 0, 0x3322);
+        const uint32_t g2 = gy.z & __byte_perm(m1, 0, 0x1100), g3 = gy.w & __byte_perm(m1, 0, 0x3322);
+        if (KS != 0) {
+          acc[0] = __hadd2(acc[0], as_bf162(g0));
+          acc[1] = __hadd2(acc[1], as_bf162(g1));
+          acc[2] = __hadd2(acc[2], as_bf162(g2));
+          acc[3] = __hadd2(acc[3], as_bf162(g3));
+        } else {
+          const uint32_t gg[4] = {g0, g1, g2, g3};
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const uint32_t mk = j < 4 ? m0 : m1;
-          if (mk & (0x80u << ((j & 3) * 8))) acc[j] += gy.v[j];
+          for (int j = 0; j < 4; ++j) {
+            accf[2 * j] += __uint_as_float(gg[j] << 16);
+            accf[2 * j + 1] += __uint_as_float(gg[j] & 0xffff0000u);
+          }
         }
       }
     }
-    Vec8 o;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) o.v[j] = acc[j];
-    st_stream_v4(dx + ((static_cast<size_t>(n) * g.H + h) * g.W + w) * g.C + c8, pack8_bf16(o));
+    uint4 o;
+    if (KS != 0) {
+      o = make_uint4(as_u32(acc[0]), as_u32(acc[1]), as_u32(acc[2]), as_u32(acc[3]));
+    } else {
+      o = make_uint4(pack_bf16(accf[0], accf[1]), pack_bf16(accf[2], accf[3]),
+                     pack_bf16(accf[4], accf[5]), pack_bf16(accf[6], accf[7]));
+    }
+    st_stream_v4(dx + ((static_cast<size_t>(n) * g.H + h) * g.W + w) * g.C + c8, o);
   }
 }
 
