@@ -23,8 +23,8 @@ def worker(tuner_id, directory, study_id, max_trials, model_kind, epochs):
     tfc.distribute.experimental_set_strategy(tfc.distribute.OneDeviceStrategy("/gpu:0"))
     rng = np.random.RandomState(0)
     if model_kind == "mlp":
-        x = rng.rand(10000, 28, 28).astype("float32")
-        y = rng.randint(0, 10, 10000)
+        x = rng.rand(60000, 28, 28).astype("float32")      # MNIST-sized
+        y = rng.randint(0, 10, 60000)
 
         def build(hp):
             m = keras.Sequential()
@@ -60,7 +60,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--trials", type=int, default=8)
     ap.add_argument("--model", default="mlp")
-    ap.add_argument("--epochs", type=int, default=2)
+    ap.add_argument("--epochs", type=int, default=5)
     ap.add_argument("--skip-sequential", action="store_true")
     args = ap.parse_args()
     from cloud_b200.tuner import TrialScheduler

@@ -55,6 +55,11 @@ def run_job(job_id: str) -> int:
     base_env["TFC_JOB_ID"] = job_id
     base_env["TFC_JOB_DIR"] = jdir
     base_env["PYTHONUNBUFFERED"] = "1"
+    # ranks share the host: each gets its share of the cores for OpenMP/MKL (torchrun pins this to
+    # 1; a data loader thread plus the training thread want a little more when cores allow)
+    share = str(max(1, (os.cpu_count() or 1) // max(1, int(plan["world_size"]))))
+    for k in ("OMP_NUM_THREADS", "MKL_NUM_THREADS"):
+        base_env.setdefault(k, share)
     repo_root = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     base_env["PYTHONPATH"] = os.pathsep.join([repo_root, workdir, base_env.get("PYTHONPATH", "")])
     if plan["uses_gpu"]:

@@ -30,6 +30,7 @@ from ..launch import topology
 class TrialScheduler:
     def __init__(self, num_gpus: int | None = None, gpus_per_trial: int = 1,
                  max_restarts: int = 1, poll: float = 0.1):
+        self._concurrent = 1
         topo = topology.discover()
         self.num_gpus = topo.gpu_count if num_gpus is None else int(num_gpus)
         self.gpus_per_trial = max(int(gpus_per_trial), 1)
@@ -53,6 +54,7 @@ class TrialScheduler:
         in the optimizer store.  Returns one record per worker."""
         slots = self.slots(num_workers)
         num_workers = num_workers or len(slots)
+        self._concurrent = min(num_workers, len(slots))
         log_dir = log_dir or tempfile.mkdtemp(prefix="cb2_trials_")
         os.makedirs(log_dir, exist_ok=True)
         blob = os.path.join(log_dir, "target.pkl")
@@ -112,6 +114,13 @@ class TrialScheduler:
         e["KERASTUNER_TUNER_ID"] = job["tuner_id"]
         e["CUDA_VISIBLE_DEVICES"] = ",".join(str(g) for g in gpu_ids)
         e["TFC_TRIAL_SLOT"] = str(job["slot"])
+        # workers share the host: give each its share of the cores instead of letting every
+        # process start one OpenMP/MKL thread per core (8 workers x 8 spinning threads made a
+        # packed search slower than a sequential one)
+        share = str(max(1, (os.cpu_count() or 1) // max(1, self._concurrent)))
+        for k in ("OMP_NUM_THREADS", "MKL_NUM_THREADS"):
+            if k not in os.environ and k not in (env or {}):
+                e[k] = share
         for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):   # a worker is its own one-replica job
             e.pop(k, None)
         repo_root = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
