@@ -124,6 +124,10 @@ def main() -> int:
     if args.warmup < 3:
         args.warmup = 3
 
+    # rank 0 prints ONE JSON line on stdout: keep NCCL's banner ("NCCL version ...") and any
+    # NCCL_DEBUG output out of it
+    os.environ.setdefault("NCCL_DEBUG_FILE", f"/tmp/bench_nccl_{os.getpid()}.log")
+
     import numpy as np
     import torch
     import torch.distributed as dist
