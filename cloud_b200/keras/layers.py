@@ -468,7 +468,26 @@ class Conv2D(Layer):
         return (b, self._out_dim(h, self.kernel_size[0], self.strides[0], self.dilation[0], 0),
                 self._out_dim(w, self.kernel_size[1], self.strides[1], self.dilation[1], 1), self.filters)
 
+    def is_stem_geometry(self) -> bool:
+        return (self.filters == 64 and self.kernel_size == (7, 7) and self.strides == (2, 2)
+                and self.padding == (3, 3) and self.dilation == (1, 1))
+
     def call(self, x, training=False):
+        pending = getattr(x, "_cb2_pending_norm", None)
+        if pending is not None:          # raw uint8 image from a deferring ImageNormalization
+            mean, std = pending
+            nhwc = x.permute(0, 2, 3, 1)
+            w = self.kernel
+            if (self.is_stem_geometry() and w.dtype == torch.bfloat16 and x.shape[1] == 3
+                    and x.shape[2] % 2 == 0 and x.shape[3] % 2 == 0 and x.shape[3] // 2 <= 128):
+                b = self.bias
+                if b is not None and self.bias_absorbed_by_bn and training:
+                    b = None
+                y = ops.stem_conv_s2d(ops.normalize_u8_images_s2d(nhwc.contiguous(), mean, std), w, b)
+                if self.activation_name == "relu":
+                    return torch.relu_(y)
+                return y if self._activation_fn is None else self._activation_fn(y)
+            x = ops.normalize_u8_images(nhwc.contiguous(), mean, std).permute(0, 3, 1, 2)
         pad = self.padding if isinstance(self.padding, tuple) else 0
         if self.padding == "same":
             ph = _same_pad(x.shape[2], self.kernel_size[0], self.strides[0], self.dilation[0])
@@ -485,7 +504,9 @@ class Conv2D(Layer):
             b = None
         if b is not None and b.dtype != x.dtype:
             b = b.to(x.dtype)
-        if _CONV1X1_GEMM and ops.conv1x1_supported(x, w, self.strides, pad, self.dilation):
+        if _CONV1X1_GEMM and ops.stem_supported(x, w, self.strides, pad, self.dilation):
+            y = ops.stem_conv(x, w, b)
+        elif _CONV1X1_GEMM and ops.conv1x1_supported(x, w, self.strides, pad, self.dilation):
             y = ops.conv1x1(x, w, b, bn_stats=bool(training) and self.feeds_bn and
                             self.activation_name in (None, "linear"))
         else:
@@ -679,8 +700,15 @@ class ImageNormalization(Layer):
     def __init__(self, mean=(0.485, 0.456, 0.406), std=(0.229, 0.224, 0.225), **kwargs):
         super().__init__(**kwargs)
         self.mean, self.std = tuple(mean), tuple(std)
+        # Set by Model._init_functional when the only consumer is a ResNet-stem convolution: the
+        # bytes are then normalised straight into the stem kernel's space-to-depth layout by the
+        # convolution (one pass instead of normalise + pad + regroup).
+        self.defer_to_stem = False
 
     def call(self, x, training=False):
+        if x.dtype == torch.uint8 and self.defer_to_stem and x.is_cuda and _CONV1X1_GEMM:
+            x._cb2_pending_norm = (self.mean, self.std)
+            return x
         if x.dtype == torch.uint8:
             nhwc = x.permute(0, 2, 3, 1)                     # back to the raw NHWC bytes (a view)
             out = ops.normalize_u8_images(nhwc.contiguous(), self.mean, self.std)

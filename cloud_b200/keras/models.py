@@ -261,6 +261,18 @@ class Model(nn.Module):
         for o in self._outputs:
             visit(o)
         self._nodes = order
+        # fusion pass: an ImageNormalization whose only consumer is a ResNet-stem convolution
+        # hands the raw bytes on (see ImageNormalization.defer_to_stem)
+        consumers: dict = {}
+        for t in order:
+            for i in t.inputs:
+                consumers.setdefault(id(i), []).append(t)
+        outs = {id(o) for o in self._outputs}
+        for t in order:
+            if isinstance(t.layer, L.ImageNormalization) and id(t) not in outs:
+                cons = consumers.get(id(t), [])
+                if len(cons) == 1 and isinstance(cons[0].layer, L.Conv2D) and cons[0].layer.is_stem_geometry():
+                    t.layer.defer_to_stem = True
         added = set()
         for t in order:
             if t.layer is not None and id(t.layer) not in added:

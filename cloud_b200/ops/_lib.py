@@ -60,6 +60,10 @@ def _declare_kernels(lib: ctypes.CDLL) -> None:
     lib.cb2_gemm_colstat_copies.restype = i
     lib.cb2_gemm_splitk_bf16.restype = i
     lib.cb2_gemm_splitk_bf16.argtypes = [vp, vp, vp, vp, vp, i, i, i, i, i, i, i, i, i, i, i, i, vp]
+    lib.cb2_conv_stem_forward.restype = i
+    lib.cb2_conv_stem_forward.argtypes = [vp, vp, vp, i, i, i, vp]
+    lib.cb2_conv_stem_wgrad.restype = i
+    lib.cb2_conv_stem_wgrad.argtypes = [vp, vp, vp, i, i, i, vp]
     lib.cb2_gemm_debug_epilogue.restype = i
     lib.cb2_gemm_debug_epilogue.argtypes = [i]
     lib.cb2_gemm_debug_descriptors.restype = i
@@ -70,6 +74,8 @@ def _declare_kernels(lib: ctypes.CDLL) -> None:
     lib.cb2_relu_bwd_bias_grad.argtypes = [vp, vp, vp, vp, i, i, i, i, i, vp]
     lib.cb2_dropout.restype = i
     lib.cb2_dropout.argtypes = [vp, vp, sz, f, u64, u64, vp, i, vp]
+    lib.cb2_u8_to_s2d_bf16.restype = i
+    lib.cb2_u8_to_s2d_bf16.argtypes = [vp, vp, i, i, i, ctypes.POINTER(f), ctypes.POINTER(f), vp]
     lib.cb2_u8_to_bf16_normalize.restype = i
     lib.cb2_u8_to_bf16_normalize.argtypes = [vp, vp, sz, i, ctypes.POINTER(f), ctypes.POINTER(f), vp]
     lib.cb2_optim_tick.restype = i

@@ -131,3 +131,79 @@ def conv1x1(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None,
     if sums is not None:
         y._cb2_bn_sums = sums
     return y
+
+
+# ----------------------------------------------------------------------------------------------
+# ResNet stem: 7x7 / stride 2 / pad 3 on a 3-channel image (cb2_conv_stem_* in gemm_tcgen05.cu)
+# ----------------------------------------------------------------------------------------------
+def stem_supported(x: torch.Tensor, w: torch.Tensor, stride, padding, dilation) -> bool:
+    """True for the ImageNet stem geometry on a CUDA bf16 channels_last image that needs no input
+    gradient (cuDNN takes 2.5 ms for this layer at batch 256; the implicit GEMM ~0.3 ms)."""
+    return (mode() != "0" and x.is_cuda and x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16
+            and x.dim() == 4 and tuple(w.shape) == (64, 3, 7, 7) and tuple(stride) == (2, 2)
+            and padding in (3, (3, 3)) and tuple(dilation) == (1, 1) and not x.requires_grad
+            and x.shape[2] % 2 == 0 and x.shape[3] % 2 == 0 and x.shape[3] // 2 <= 128)
+
+
+def space_to_depth_stem(x: torch.Tensor) -> torch.Tensor:
+    """[B, 3, H, W] (channels_last or not) -> [B, H/2+3, W/2+3, 16]: pixel (r, s) holds input pixels
+    (2r-4+a, 2s-4+b) as channels (a*2+b)*3 + c; borders and channels 12..15 are zero."""
+    b, c, h, w = x.shape
+    p = F.pad(x, (4, 2, 4, 2)).permute(0, 2, 3, 1)                  # NHWC view, [B, H+6, W+6, 3]
+    r, s = (h + 6) // 2, (w + 6) // 2
+    p = p.reshape(b, r, 2, s, 2, c).permute(0, 1, 3, 2, 4, 5).reshape(b, r, s, 4 * c)
+    return F.pad(p, (0, 16 - 4 * c)).contiguous()
+
+
+def stem_weight_matrix(w: torch.Tensor) -> torch.Tensor:
+    """Kernel [64, 3, 7, 7] -> [64, 256] in the operand order of ``cb2_conv_stem_forward``:
+    k = i*64 + j*16 + (a*2+b)*3 + c for kernel row 2i+a-1, column 2j+b-1 (differentiable)."""
+    co, c = w.shape[0], w.shape[1]
+    w8 = F.pad(w, (1, 0, 1, 0))                                     # tap -1 (zero) in front: 8 x 8
+    w8 = w8.reshape(co, c, 4, 2, 4, 2).permute(0, 2, 4, 3, 5, 1)    # co, i, j, a, b, c
+    return F.pad(w8.reshape(co, 4, 4, 4 * c), (0, 16 - 4 * c)).reshape(co, 256).contiguous()
+
+
+class _StemFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, xs, wm):
+        b, r, s, _ = xs.shape
+        oh, ow = r - 3, s - 3
+        y = torch.empty((b, oh, ow, 64), dtype=torch.bfloat16, device=xs.device)
+        rc = _dense._lib.kernels().cb2_conv_stem_forward(xs.data_ptr(), wm.data_ptr(), y.data_ptr(),
+                                                         b, oh, ow, _dense._stream())
+        _dense._lib.check(rc, "conv_stem_forward")
+        _dense._launches += 1
+        ctx.save_for_backward(xs)
+        ctx.geom = (b, oh, ow)
+        return y.permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (xs,) = ctx.saved_tensors
+        b, oh, ow = ctx.geom
+        if not dy.is_contiguous(memory_format=torch.channels_last):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        dwt = _bn._scratch(256 * 64, xs.device).view(256, 64)       # zeroed once per step by the engine
+        rc = _dense._lib.kernels().cb2_conv_stem_wgrad(xs.data_ptr(), dy.data_ptr(), dwt.data_ptr(),
+                                                       b, oh, ow, _dense._stream())
+        _dense._lib.check(rc, "conv_stem_wgrad")
+        _dense._launches += 1
+        return None, dwt.t().to(torch.bfloat16)
+
+
+def stem_conv_s2d(xs: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None) -> torch.Tensor:
+    """The stem convolution of an image already in the space-to-depth layout
+    (``ops.normalize_u8_images_s2d``)."""
+    y = _StemFn.apply(xs, stem_weight_matrix(w))
+    if bias is not None:
+        y = y + bias.to(y.dtype).view(1, -1, 1, 1)
+    return y
+
+
+def stem_conv(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None) -> torch.Tensor:
+    """``conv2d(x, w, stride=2, padding=3)`` for the ResNet stem on the tcgen05 implicit GEMM."""
+    y = _StemFn.apply(space_to_depth_stem(x), stem_weight_matrix(w))
+    if bias is not None:
+        y = y + bias.to(y.dtype).view(1, -1, 1, 1)
+    return y

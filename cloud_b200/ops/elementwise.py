@@ -137,3 +137,25 @@ def normalize_u8_images(images: torch.Tensor, mean=_IMAGENET_MEAN, std=_IMAGENET
     _lib.check(rc, "u8_to_bf16_normalize")
     _launches += 1
     return out
+
+
+def normalize_u8_images_s2d(images: torch.Tensor, mean=_IMAGENET_MEAN, std=_IMAGENET_STD) -> torch.Tensor:
+    """uint8 NHWC RGB ``[N,H,W,3]`` -> normalised bf16 ``[N, H/2+3, W/2+3, 16]`` in the space-to-depth
+    layout of the ResNet stem (``ops.stem_conv_s2d``): normalisation, zero padding and the 2x2
+    regrouping in one pass over the bytes."""
+    global _launches
+    if images.dtype != torch.uint8 or images.dim() != 4 or images.shape[-1] != 3:
+        raise TypeError("normalize_u8_images_s2d expects uint8 [N, H, W, 3]")
+    n, h, w, _ = images.shape
+    if not images.is_cuda:
+        from .conv import space_to_depth_stem
+        return space_to_depth_stem(normalize_u8_images(images, mean, std).permute(0, 3, 1, 2))
+    images = images.contiguous()
+    out = torch.empty((n, h // 2 + 3, w // 2 + 3, 16), dtype=torch.bfloat16, device=images.device)
+    arr = ctypes.c_float * 3
+    rc = _lib.kernels().cb2_u8_to_s2d_bf16(images.data_ptr(), out.data_ptr(), n, h, w,
+                                           arr(*[float(v) for v in mean]),
+                                           arr(*[1.0 / float(v) for v in std]), _stream())
+    _lib.check(rc, "u8_to_s2d_bf16")
+    _launches += 1
+    return out

@@ -222,6 +222,48 @@ u8_to_bf16_norm_kernel(const uint8_t* __restrict__ in, __nv_bfloat16* __restrict
   }
 }
 
+// uint8 NHWC RGB image -> normalised bf16 in the space-to-depth layout of the ResNet stem
+// (cb2_conv_stem_forward): out[b, r, s, (a*2+bb)*3 + c] = norm(in[b, 2r-4+a, 2s-4+bb, c]), zero
+// outside the image (the convolution pads the NORMALISED image with zeros) and in channels
+// 12..15.  One thread per output pixel: 2 x 6 input bytes in, 32 bytes out.
+__global__ void __launch_bounds__(256)
+u8_to_s2d_bf16_kernel(const uint8_t* __restrict__ in, __nv_bfloat16* __restrict__ out, int B, int H,
+                      int W, float m0, float m1, float m2, float s0, float s1, float s2) {
+  const int R = H / 2 + 3, S = W / 2 + 3;
+  const unsigned total = static_cast<unsigned>(B) * R * S;
+  const float mean[3] = {m0, m1, m2};
+  const float istd[3] = {s0, s1, s2};
+  for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
+    const int s = static_cast<int>(t % S);
+    unsigned q = t / S;
+    const int r = static_cast<int>(q % R);
+    const int b = static_cast<int>(q / R);
+    float f[12];
+#pragma unroll
+    for (int j = 0; j < 12; ++j) f[j] = 0.f;
+    const int w0 = 2 * s - 4;                       // even; both pixels of the pair in or out together
+    if (w0 >= 0 && w0 < W) {
+#pragma unroll
+      for (int a = 0; a < 2; ++a) {
+        const int h = 2 * r - 4 + a;
+        if (h >= 0 && h < H) {
+          const uint16_t* src = reinterpret_cast<const uint16_t*>(
+              in + (static_cast<size_t>(b) * H * W + static_cast<size_t>(h) * W + w0) * 3);
+          const uint32_t u0 = __ldg(src), u1 = __ldg(src + 1), u2 = __ldg(src + 2);
+          const uint32_t bytes[6] = {u0 & 0xffu, u0 >> 8, u1 & 0xffu, u1 >> 8, u2 & 0xffu, u2 >> 8};
+#pragma unroll
+          for (int k = 0; k < 6; ++k)
+            f[a * 6 + k] = (static_cast<float>(bytes[k]) * (1.f / 255.f) - mean[k % 3]) * istd[k % 3];
+        }
+      }
+    }
+    uint4* dst = reinterpret_cast<uint4*>(out + static_cast<size_t>(t) * 16);
+    dst[0] = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]),
+                        pack_bf16(f[6], f[7]));
+    dst[1] = make_uint4(pack_bf16(f[8], f[9]), pack_bf16(f[10], f[11]), 0u, 0u);
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Optimizers
 // ---------------------------------------------------------------------------------------------
@@ -401,6 +443,23 @@ extern "C" int cb2_u8_to_bf16_normalize(const uint8_t* in, void* out, size_t n_p
                                                  channels, mean3[0], mean3[1], mean3[2],
                                                  inv_std3[0], inv_std3[1], inv_std3[2]);
   return check_cuda(cudaGetLastError(), "u8_to_bf16_normalize launch");
+}
+
+extern "C" int cb2_u8_to_s2d_bf16(const uint8_t* in, void* out, int B, int H, int W,
+                                  const float* mean3, const float* inv_std3, void* stream) {
+  if (B <= 0 || H <= 0 || W <= 0 || (H & 1) || (W & 1) ||
+      static_cast<long long>(B) * (H / 2 + 3) * (W / 2 + 3) >= (1LL << 31)) {
+    set_last_error("u8_to_s2d_bf16: unsupported geometry B=%d H=%d W=%d (even H, W)", B, H, W);
+    return CB2_ERR_UNSUPPORTED;
+  }
+  const long long total = static_cast<long long>(B) * (H / 2 + 3) * (W / 2 + 3);
+  long long blocks = (total + 255) / 256;
+  const long long cap = static_cast<long long>(sm_count()) * 16;
+  if (blocks > cap) blocks = cap;
+  u8_to_s2d_bf16_kernel<<<static_cast<int>(blocks), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      in, reinterpret_cast<__nv_bfloat16*>(out), B, H, W, mean3[0], mean3[1], mean3[2], inv_std3[0],
+      inv_std3[1], inv_std3[2]);
+  return check_cuda(cudaGetLastError(), "u8_to_s2d_bf16 launch");
 }
 
 extern "C" int cb2_optim_tick(float* hyper, void* stream) {

@@ -64,6 +64,14 @@ int cb2_gemm_splitk_bf16(const void* A, const void* B, float* workspace, void* o
                          unsigned* counters, int n_counters, int M, int N, int K, int lda, int ldb,
                          int ld_ws, int ld_out, int a_mn, int b_mn, int block_n, int split_k,
                          void* stream);
+/* ResNet stem (7x7 / stride 2 / pad 3, 3 -> 64 channels) as an implicit GEMM on the tcgen05 kernel.
+ * xs: bf16 [B, OH+3, OW+3, 16] space-to-depth image (pixel (r, s) = input pixels (2r-4+a, 2s-4+b),
+ * channel (a*2+b)*3 + c, zero where the input has none); wm: bf16 [64, 256] kernel with
+ * k = i*64 + j*16 + (a*2+b)*3 + c for kernel row 2i+a-1, column 2j+b-1; y / dy: bf16 [B, OH, OW, 64];
+ * dwt: fp32 [256, 64], the transposed gradient of wm, accumulated (zero or a running sum on entry).
+ * OW <= 128.  No counterpart in the reference (TensorFlow hands this convolution to cuDNN). */
+int cb2_conv_stem_forward(const void* xs, const void* wm, void* y, int B, int OH, int OW, void* stream);
+int cb2_conv_stem_wgrad(const void* xs, const void* dy, float* dwt, int B, int OH, int OW, void* stream);
 /* Diagnostics only (bench/gemm_epilogue_probe.py): bit mask of epilogue phases to skip. */
 int cb2_gemm_debug_epilogue(int bits);
 int cb2_gemm_debug_descriptors(int enable, unsigned a_lbo, unsigned a_sbo, unsigned b_lbo,
@@ -92,6 +100,10 @@ int cb2_dropout(const void* x, void* y, size_t n, float p, uint64_t seed, uint64
 /* uint8 NHWC image -> bf16 NHWC, (x/255 - mean[c]) / std[c].  Input pipeline tail (K12). */
 int cb2_u8_to_bf16_normalize(const uint8_t* in, void* out, size_t n_pixels, int channels,
                              const float* mean3, const float* inv_std3, void* stream);
+/* Same normalisation, written in the space-to-depth layout cb2_conv_stem_forward reads:
+ * out bf16 [B, H/2+3, W/2+3, 16] (see there); in uint8 [B, H, W, 3], H and W even. */
+int cb2_u8_to_s2d_bf16(const uint8_t* in, void* out, int B, int H, int W, const float* mean3,
+                       const float* inv_std3, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Fused NHWC batch normalisation (+ residual add) (+ ReLU), bf16 activations [M = N*H*W, C],

@@ -384,3 +384,52 @@ def test_gemm_split_k_finalized_in_kernel(M, N, K):
     ws, counters = dense_ops._splitk_state[_dev()]
     assert int(counters.abs().sum().item()) == 0
     assert float(ws.abs().max().item()) == 0.0
+
+
+@pytest.mark.parametrize("B,H,W", [(4, 224, 224), (3, 64, 96), (2, 32, 256)])
+def test_stem_conv_implicit_gemm_matches_conv2d(B, H, W):
+    """7x7/2 stem on the tcgen05 implicit GEMM (space-to-depth input, 4-D TMA map) vs conv2d."""
+    torch.manual_seed(10)
+    dev = _dev()
+    x = torch.randn(B, 3, H, W, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(64, 3, 7, 7, device=dev) / math.sqrt(147)).to(torch.bfloat16) \
+        .contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    assert ops.stem_supported(x, w, (2, 2), (3, 3), (1, 1))
+    y = ops.stem_conv(x, w)
+    assert y.shape == (B, 64, H // 2, W // 2) and y.is_contiguous(memory_format=torch.channels_last)
+    gy = torch.randn_like(y)
+    y.backward(gy)
+    wr = w.detach().float().requires_grad_(True)
+    yr = torch.nn.functional.conv2d(x.float(), wr, None, stride=2, padding=3)
+    yr.backward(gy.float())
+    _check_close(y, yr, 2e-2, 2e-2, "stem fwd")
+    _check_close(w.grad, wr.grad, 2e-2, 2e-2 * math.sqrt(B * H * W / 4), "stem dW")
+
+
+def test_u8_images_straight_into_the_stem_layout():
+    """normalize_u8_images_s2d == space_to_depth(normalize_u8_images) and the Keras stem uses it."""
+    from cloud_b200.ops import conv as conv_ops
+    torch.manual_seed(11)
+    dev = _dev()
+    img = torch.randint(0, 256, (3, 64, 96, 3), dtype=torch.uint8, device=dev)
+    got = ops.normalize_u8_images_s2d(img)
+    want = conv_ops.space_to_depth_stem(ops.normalize_u8_images(img).permute(0, 3, 1, 2))
+    assert got.shape == want.shape == (3, 35, 51, 16)
+    assert torch.equal(got, want)
+
+    import cloud_b200 as tfc
+    from cloud_b200.keras import layers
+    keras = tfc.keras
+    tfc.distribute.experimental_set_strategy(tfc.distribute.OneDeviceStrategy("cuda:0"))
+    inp = keras.Input(shape=(64, 96, 3))
+    x = layers.ImageNormalization(name="norm")(inp)
+    x = layers.Conv2D(64, 7, strides=2, padding=3, use_bias=False, name="stem")(x)
+    out = layers.GlobalAveragePooling2D()(x)
+    m = keras.Model(inp, out)
+    assert m.get_layer("norm").defer_to_stem
+    m.compile(optimizer="sgd", loss="mse")
+    y = m.predict(img.cpu().numpy(), batch_size=3)
+    w = torch.tensor(m.get_layer("stem").get_weights()[0], device=dev).permute(3, 2, 0, 1)   # HWIO -> OIHW
+    ref = torch.nn.functional.conv2d(ops.normalize_u8_images(img).permute(0, 3, 1, 2).float(), w.float(),
+                                     stride=2, padding=3).mean((2, 3))
+    _check_close(torch.tensor(y, device=dev), ref, 3e-2, 3e-2, "keras stem on raw bytes")
