@@ -23,6 +23,9 @@ from .. import ops
 # 1x1 / stride-1 convolutions go through ops/conv.py, which puts their weight gradient (default) or
 # all three GEMMs (TFC_CONV1X1_GEMM=all) on the tcgen05 kernel; TFC_CONV1X1_GEMM=0: plain cuDNN
 _CONV1X1_GEMM = ops.conv1x1_mode() != "0"
+# k x k weight gradients on the tcgen05 shifted-box kernel: correct but slower than cuDNN's sm_100
+# kernels on the 3x3 shapes of ResNet-50 (256 vs 110 us at 56x56x64, batch 256), so opt-in
+_CONV_KXK = os.environ.get("TFC_CONV_KXK_WGRAD", "0") == "1"
 
 _NAME_COUNTS: dict[str, int] = {}
 
@@ -506,6 +509,8 @@ class Conv2D(Layer):
             b = b.to(x.dtype)
         if _CONV1X1_GEMM and ops.stem_supported(x, w, self.strides, pad, self.dilation):
             y = ops.stem_conv(x, w, b)
+        elif _CONV1X1_GEMM and _CONV_KXK and ops.kxk_supported(x, w, self.strides, pad, self.dilation):
+            y = ops.conv_kxk(x, w, b)
         elif _CONV1X1_GEMM and ops.conv1x1_supported(x, w, self.strides, pad, self.dilation):
             y = ops.conv1x1(x, w, b, bn_stats=bool(training) and self.feeds_bn and
                             self.activation_name in (None, "linear"))

@@ -60,6 +60,8 @@ def _declare_kernels(lib: ctypes.CDLL) -> None:
     lib.cb2_gemm_colstat_copies.restype = i
     lib.cb2_gemm_splitk_bf16.restype = i
     lib.cb2_gemm_splitk_bf16.argtypes = [vp, vp, vp, vp, vp, i, i, i, i, i, i, i, i, i, i, i, i, vp]
+    lib.cb2_conv_wgrad.restype = i
+    lib.cb2_conv_wgrad.argtypes = [vp, vp, vp, i, i, i, i, i, i, i, i, vp]
     lib.cb2_conv_stem_forward.restype = i
     lib.cb2_conv_stem_forward.argtypes = [vp, vp, vp, i, i, i, vp]
     lib.cb2_conv_stem_wgrad.restype = i

@@ -207,3 +207,58 @@ def stem_conv(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None
     if bias is not None:
         y = y + bias.to(y.dtype).view(1, -1, 1, 1)
     return y
+
+
+# ----------------------------------------------------------------------------------------------
+# k x k / stride-1 / 'same' convolutions: cuDNN forward and input gradient, weight gradient on the
+# tcgen05 kernel (cb2_conv_wgrad: shifted pixel boxes through 4-D TMA maps)
+# ----------------------------------------------------------------------------------------------
+def kxk_supported(x: torch.Tensor, w: torch.Tensor, stride, padding, dilation) -> bool:
+    k = w.shape[2]
+    return (mode() != "0" and x.is_cuda and x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16
+            and x.dim() == 4 and w.shape[2] == w.shape[3] and k in (3, 5, 7) and tuple(stride) == (1, 1)
+            and tuple(dilation) == (1, 1) and padding in (k // 2, (k // 2, k // 2))
+            and x.shape[1] % 64 == 0 and w.shape[0] % 64 == 0 and x.shape[3] <= 64
+            and x.is_contiguous(memory_format=torch.channels_last))
+
+
+class _ConvKxKFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, bias):
+        ctx.save_for_backward(x, w)
+        ctx.has_bias = bias is not None
+        k = w.shape[2]
+        return F.conv2d(x, w, None if bias is None else bias.to(x.dtype), padding=k // 2)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        n, cin, h, wd = x.shape
+        cout, k = w.shape[0], w.shape[2]
+        if not dy.is_contiguous(memory_format=torch.channels_last):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.ops.aten.convolution_backward(
+                dy, x, w, None, (1, 1), (k // 2, k // 2), (1, 1), False, (0, 0), 1, (True, False, False))[0]
+        if ctx.needs_input_grad[1]:
+            ws = _bn._scratch(k * k * cin * cout, x.device).view(k * k * cin, cout)   # zeroed per step
+            rc = _dense._lib.kernels().cb2_conv_wgrad(x.data_ptr(), dy.data_ptr(), ws.data_ptr(), n, h, wd,
+                                                      cin, cout, k, k // 2, 1, _dense._stream())
+            _dense._lib.check(rc, "conv_wgrad")
+            _dense._launches += 1
+            # [(i, j, ci), co] -> the parameter's [co, ci, i, j] (channels_last memory = [co, i, j, ci])
+            g = ws.view(k, k, cin, cout).permute(3, 2, 0, 1)
+            if getattr(w, "_cb2_direct_grad", False) and w.grad is not None:
+                w.grad.add_(g)
+                w._cb2_grad_written(w)
+            else:
+                dw = g.to(torch.bfloat16)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            db = dy.float().sum((0, 2, 3))
+        return dx, dw, db
+
+
+def conv_kxk(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None) -> torch.Tensor:
+    """k x k / stride-1 / 'same' convolution of a channels_last bf16 tensor."""
+    return _ConvKxKFn.apply(x, w, bias)

@@ -72,6 +72,14 @@ int cb2_gemm_splitk_bf16(const void* A, const void* B, float* workspace, void* o
  * OW <= 128.  No counterpart in the reference (TensorFlow hands this convolution to cuDNN). */
 int cb2_conv_stem_forward(const void* xs, const void* wm, void* y, int B, int OH, int OW, void* stream);
 int cb2_conv_stem_wgrad(const void* xs, const void* dy, float* dwt, int B, int OH, int OW, void* stream);
+/* Weight gradient of a k x k convolution with pad = k/2 and stride 1 or 2, bf16 NHWC
+ * x [B, H*stride, W*stride, Cin] and dy [B, H, W, Cout] read in place through 4-D TMA maps (taps =
+ * shifted pixel boxes, stride = TMA traversal stride, zero padding = TMA out-of-bounds fill):
+ * dwt[(i*k + j)*Cin + ci, co] += sum_pixels x[.., h*stride+i-pad, w*stride+j-pad, ci] * dy[.., h, w, co];
+ * dwt fp32 [k*k*Cin, Cout], zero or a running sum on entry.  W <= 64, Cin and Cout multiples of 64.
+ * No counterpart in the reference (cuDNN inside TensorFlow). */
+int cb2_conv_wgrad(const void* x, const void* dy, float* dwt, int B, int H, int W, int Cin, int Cout,
+                   int ksize, int pad, int stride, void* stream);
 /* Diagnostics only (bench/gemm_epilogue_probe.py): bit mask of epilogue phases to skip. */
 int cb2_gemm_debug_epilogue(int bits);
 int cb2_gemm_debug_descriptors(int enable, unsigned a_lbo, unsigned a_sbo, unsigned b_lbo,

@@ -433,3 +433,26 @@ def test_u8_images_straight_into_the_stem_layout():
     ref = torch.nn.functional.conv2d(ops.normalize_u8_images(img).permute(0, 3, 1, 2).float(), w.float(),
                                      stride=2, padding=3).mean((2, 3))
     _check_close(torch.tensor(y, device=dev), ref, 3e-2, 3e-2, "keras stem on raw bytes")
+
+
+@pytest.mark.parametrize("B,H,W,Cin,Cout,k", [(4, 56, 56, 64, 64, 3), (3, 28, 28, 128, 128, 3),
+                                              (5, 14, 14, 256, 256, 3), (6, 7, 7, 512, 512, 3),
+                                              (2, 20, 12, 64, 128, 5)])
+def test_conv_kxk_weight_gradient_on_shifted_tma_boxes(B, H, W, Cin, Cout, k):
+    torch.manual_seed(12)
+    dev = _dev()
+    x = torch.randn(B, Cin, H, W, device=dev).to(torch.bfloat16) \
+        .contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    w = (torch.randn(Cout, Cin, k, k, device=dev) / math.sqrt(Cin * k * k)).to(torch.bfloat16) \
+        .contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    assert ops.kxk_supported(x, w, (1, 1), k // 2, (1, 1))
+    y = ops.conv_kxk(x, w)
+    gy = torch.randn_like(y)
+    y.backward(gy)
+    xr = x.detach().float().requires_grad_(True)
+    wr = w.detach().float().requires_grad_(True)
+    yr = torch.nn.functional.conv2d(xr, wr, padding=k // 2)
+    yr.backward(gy.float())
+    _check_close(y, yr, 2e-2, 2e-2, "conv fwd")
+    _check_close(x.grad, xr.grad, 3e-2, 3e-2, "conv dX")
+    _check_close(w.grad, wr.grad, 2e-2, 2e-2 * math.sqrt(B * H * W), "conv dW")
