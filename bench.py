@@ -124,9 +124,11 @@ def main() -> int:
     if args.warmup < 3:
         args.warmup = 3
 
-    # rank 0 prints ONE JSON line on stdout: keep NCCL's banner ("NCCL version ...") and any
-    # NCCL_DEBUG output out of it
-    os.environ.setdefault("NCCL_DEBUG_FILE", f"/tmp/bench_nccl_{os.getpid()}.log")
+    # rank 0 prints ONE JSON line on stdout: everything else that lands on fd 1 while the benchmark
+    # runs (NCCL's "NCCL version ..." banner is a C-level printf) is sent to stderr instead
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
 
     import numpy as np
     import torch
@@ -263,7 +265,10 @@ def main() -> int:
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(gpu_launches),
             "loss": loss_now,
         }
-        print(json.dumps(out))
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        print(json.dumps(out), flush=True)
+        os.dup2(2, 1)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
