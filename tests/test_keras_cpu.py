@@ -1,0 +1,185 @@
+"""Keras-shaped front end on the CPU path: training loop, functional graphs, callbacks, optimizers
+against torch.optim, HDF5 weight round trips.  (New tier: the reference leaves all of this to
+tf.keras - SURVEY.md appendix B.)"""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import cloud_b200 as tfc
+from cloud_b200.io import hdf5
+
+keras = tfc.keras
+L = keras.layers
+
+
+@pytest.fixture(autouse=True)
+def _cpu_strategy():
+    tfc.distribute.experimental_set_strategy(tfc.distribute.OneDeviceStrategy("/cpu:0"))
+    torch.manual_seed(0)
+    np.random.seed(0)
+    yield
+
+
+def _blobs(n=512, d=20, classes=4, seed=0):
+    rng = np.random.RandomState(seed)
+    centers = rng.randn(classes, d) * 3
+    y = rng.randint(0, classes, n)
+    x = centers[y] + rng.randn(n, d)
+    return x.astype("float32"), y.astype("int64")
+
+
+def _mlp(d=20, classes=4, dropout=0.1):
+    m = keras.Sequential([L.Dense(32, activation="relu", input_shape=(d,)), L.Dropout(dropout),
+                          L.Dense(classes, activation="softmax")])
+    m.compile(optimizer=keras.optimizers.Adam(1e-2), loss="sparse_categorical_crossentropy",
+              metrics=["accuracy"])
+    return m
+
+
+def test_sequential_fit_learns_and_reports_history():
+    x, y = _blobs()
+    m = _mlp()
+    h = m.fit(x, y, batch_size=64, epochs=6, verbose=0, shuffle=True)
+    assert set(h.history) >= {"loss", "accuracy"}
+    assert len(h.history["loss"]) == 6
+    assert h.history["loss"][-1] < 0.5 * h.history["loss"][0]
+    assert h.history["accuracy"][-1] > 0.9
+    ev = m.evaluate(x, y, batch_size=128, verbose=0, return_dict=True)
+    assert ev["accuracy"] > 0.9 and abs(ev["loss"] - h.history["loss"][-1]) < 0.5
+    p = m.predict(x[:10])
+    assert p.shape == (10, 4) and np.allclose(p.sum(1), 1.0, atol=1e-3)
+
+
+def test_functional_conv_graph_with_residual_and_pooling():
+    inp = keras.Input(shape=(16, 16, 3))
+    x = L.Conv2D(8, 3, padding="same", name="c1")(inp)
+    x = L.BatchNormalization(activation="relu", name="bn1")(x)
+    s = x
+    x = L.Conv2D(8, 3, padding="same", use_bias=False, name="c2")(x)
+    x = L.BatchNormalization(name="bn2")([x, s])                      # fused shortcut input
+    x = L.MaxPooling2D(2)(x)
+    x = L.Concatenate()([L.GlobalAveragePooling2D()(x), L.GlobalMaxPooling2D()(x)])
+    out = L.Dense(3, activation="softmax", name="head")(x)
+    m = keras.Model(inp, out)
+    assert m.get_layer("c1").bias_absorbed_by_bn and m.get_layer("c2").feeds_bn
+    m.compile(optimizer="sgd", loss="sparse_categorical_crossentropy", metrics=["acc"])
+    xs = np.random.rand(24, 16, 16, 3).astype("float32")
+    ys = np.random.randint(0, 3, 24)
+    before = m.evaluate(xs, ys, verbose=0, return_dict=True)["loss"]
+    m.fit(xs, ys, batch_size=8, epochs=5, verbose=0)
+    after = m.evaluate(xs, ys, verbose=0, return_dict=True)["loss"]
+    assert after < before
+    assert m.output_shape == (None, 3) and m.predict(xs[:2]).shape == (2, 3)
+    cfg = m.to_json()
+    m2 = keras.model_from_json(cfg)
+    assert [l.name for l in m2.layers] == [l.name for l in m.layers]
+
+
+def test_callbacks_early_stopping_checkpoint_and_lr_schedule(tmp_path):
+    x, y = _blobs(256)
+    m = _mlp()
+    seen = []
+    ckpt = str(tmp_path / "w-{epoch:02d}.h5")
+    cbs = [keras.callbacks.EarlyStopping(monitor="loss", patience=0, min_delta=10.0),   # stops after epoch 2
+           keras.callbacks.ModelCheckpoint(ckpt, save_weights_only=True),
+           keras.callbacks.LearningRateScheduler(lambda epoch, lr: lr * 0.5),
+           keras.callbacks.LambdaCallback(on_epoch_end=lambda e, logs: seen.append((e, logs["loss"])))]
+    h = m.fit(x, y, batch_size=64, epochs=10, verbose=0, callbacks=cbs)
+    assert len(h.history["loss"]) == 2 and [e for e, _ in seen] == [0, 1]
+    assert os.path.exists(str(tmp_path / "w-01.h5")) and os.path.exists(str(tmp_path / "w-02.h5"))
+    assert abs(m.optimizer.current_lr() - 1e-2 * 0.25) < 1e-9
+
+
+@pytest.mark.parametrize("name,make,ref", [
+    ("adam", lambda: keras.optimizers.Adam(1e-2), lambda p: torch.optim.Adam(p, 1e-2, eps=1e-7)),
+    ("sgd_momentum", lambda: keras.optimizers.SGD(0.05, momentum=0.9),
+     lambda p: torch.optim.SGD(p, 0.05, momentum=0.9)),
+    ("rmsprop", lambda: keras.optimizers.RMSprop(1e-2), None),
+])
+def test_optimizers_follow_their_reference_update_rule(name, make, ref):
+    x, y = _blobs(128, d=6, classes=2)
+    m = keras.Sequential([L.Dense(2, input_shape=(6,), name="d")])
+    m.compile(optimizer=make(), loss=keras.losses.SparseCategoricalCrossentropy(from_logits=True))
+    w0 = [w.copy() for w in m.get_weights()]
+    for _ in range(5):
+        m.train_on_batch(x, y)
+    w1 = m.get_weights()
+    assert not np.allclose(w0[0], w1[0])
+    if ref is None:
+        return
+    k = torch.tensor(w0[0], requires_grad=True)
+    b = torch.tensor(w0[1], requires_grad=True)
+    opt = ref([k, b])
+    xt, yt = torch.tensor(x), torch.tensor(y)
+    for _ in range(5):
+        opt.zero_grad()
+        torch.nn.functional.cross_entropy(xt @ k + b, yt).backward()
+        opt.step()
+    assert np.allclose(w1[0], k.detach().numpy(), atol=2e-4), name
+    assert np.allclose(w1[1], b.detach().numpy(), atol=2e-4), name
+
+
+def test_weights_round_trip_in_keras_hdf5_layout(tmp_path):
+    x, y = _blobs(64)
+    m = _mlp()
+    m.fit(x, y, batch_size=32, epochs=1, verbose=0)
+    path = str(tmp_path / "weights.h5")
+    m.save_weights(path)
+    with hdf5.File(path, "r") as f:
+        names = [n.decode() if isinstance(n, bytes) else n for n in f.attrs["layer_names"]]
+        assert names == [l.name for l in m.layers]
+        dense = names[0]
+        wnames = [n.decode() if isinstance(n, bytes) else n for n in f[dense].attrs["weight_names"]]
+        assert wnames == [f"{dense}/kernel:0", f"{dense}/bias:0"]
+        assert f[dense][wnames[0]].shape == (20, 32)            # Keras Dense layout [in, out]
+    m2 = _mlp()
+    m2.build((None, 20)) if hasattr(m2, "build") else None
+    m2.predict(x[:1])
+    m2.load_weights(path)
+    for a, b in zip(m.get_weights(), m2.get_weights()):
+        assert np.array_equal(a, b)
+    assert np.allclose(m.predict(x[:8]), m2.predict(x[:8]), atol=1e-6)
+
+
+def test_whole_model_save_and_load(tmp_path):
+    x, y = _blobs(64)
+    m = _mlp(dropout=0.0)          # no dropout: the two copies must take identical steps
+    m.fit(x, y, batch_size=32, epochs=1, verbose=0)
+    d = str(tmp_path / "saved")
+    m.save(d)
+    assert os.path.exists(os.path.join(d, "config.json"))
+    json.load(open(os.path.join(d, "config.json")))
+    m2 = keras.load_model(d)
+    assert np.allclose(m.predict(x[:8]), m2.predict(x[:8]), atol=1e-6)
+    # the optimizer state came along: one more identical step gives identical weights
+    m.train_on_batch(x[:32], y[:32])
+    m2.train_on_batch(x[:32], y[:32])
+    for a, b in zip(m.get_weights(), m2.get_weights()):
+        assert np.allclose(a, b, atol=1e-6)
+
+
+def test_fit_on_dataset_and_validation():
+    x, y = _blobs(256)
+    ds = tfc.data.Dataset.from_tensor_slices((x, y)).shuffle(256, seed=1).batch(32)
+    m = _mlp()
+    h = m.fit(ds, epochs=3, verbose=0, validation_data=(x[:64], y[:64]))
+    assert "val_loss" in h.history and "val_accuracy" in h.history
+    assert h.history["val_accuracy"][-1] > 0.8
+
+
+def test_image_normalization_defers_only_to_a_stem_convolution():
+    inp = keras.Input(shape=(32, 32, 3))
+    n = L.ImageNormalization(name="n")(inp)
+    out = L.GlobalAveragePooling2D()(L.Conv2D(64, 7, strides=2, padding=3, name="stem")(n))
+    m = keras.Model(inp, out)
+    assert m.get_layer("n").defer_to_stem
+    inp2 = keras.Input(shape=(32, 32, 3))
+    n2 = L.ImageNormalization(name="n2")(inp2)
+    out2 = L.GlobalAveragePooling2D()(L.Conv2D(8, 3, name="c")(n2))
+    m2 = keras.Model(inp2, out2)
+    assert not m2.get_layer("n2").defer_to_stem
+    img = np.random.randint(0, 256, (2, 32, 32, 3)).astype("uint8")
+    assert m.predict(img).shape == (2, 64) and m2.predict(img).shape == (2, 8)    # CPU: never deferred
