@@ -26,6 +26,7 @@ import torch
 import torch.nn as nn
 
 from .. import ops
+from ..utils.profiling import nvtx_range
 from ..data import Dataset
 from ..distribute import get_strategy
 from ..distribute.strategy import DistributedDataset
@@ -486,13 +487,17 @@ class Model(nn.Module):
     def _train_step(self, xb, yb, global_batch=None):
         eng = self._engine
         eng.begin_step()
-        out = self.call(xb, training=True)
+        with nvtx_range("forward"):
+            out = self.call(xb, training=True)
         if global_batch is None:
             global_batch = out.shape[0] * eng.world
-        loss, fused = self._loss_and_metrics(out, yb, global_batch, eng.comm.aux)
+        with nvtx_range("loss"):
+            loss, fused = self._loss_and_metrics(out, yb, global_batch, eng.comm.aux)
         self._last_fused = fused
-        loss.backward()
-        return eng.end_step(self._aux_len())
+        with nvtx_range("backward+bucketed all-reduce/optimizer"):
+            loss.backward()
+        with nvtx_range("end_step"):
+            return eng.end_step(self._aux_len())
 
     def _graph_enabled(self):
         if self.run_eagerly or not self._graph_ok or self.device.type != "cuda":
