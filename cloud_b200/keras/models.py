@@ -48,6 +48,13 @@ def _np(a):
 # ----------------------------------------------------------------------------------------------
 # Batch sources
 # ----------------------------------------------------------------------------------------------
+class _Forked(list):
+    """The two handles of a forked batch-norm output, handed out to its two consumers."""
+
+
+_FORK_BN = os.environ.get("TFC_BN_FORK", "1") != "0"
+
+
 class _ArraySource:
     """numpy/torch arrays -> per-replica batches of a global batch (Keras: batch_size is global)."""
 
@@ -274,6 +281,11 @@ class Model(nn.Module):
                 cons = consumers.get(id(t), [])
                 if len(cons) == 1 and isinstance(cons[0].layer, L.Conv2D) and cons[0].layer.is_stem_geometry():
                     t.layer.defer_to_stem = True
+        # a batch-norm output with two consumers (the input of a residual block): in training its
+        # two gradients are merged inside the batch-norm backward kernels (ops.bn_fork)
+        self._fork_ids = {id(t) for t in order
+                          if isinstance(t.layer, L.BatchNormalization) and id(t) not in outs
+                          and len(consumers.get(id(t), [])) == 2}
         added = set()
         for t in order:
             if t.layer is not None and id(t.layer) not in added:
@@ -325,15 +337,18 @@ class Model(nn.Module):
             raise NotImplementedError("subclassed models must implement call()")
         xs = list(x) if isinstance(x, (list, tuple)) else [x]
         values = {id(t): v for t, v in zip(self._inputs, xs)}
+        fork_ids = getattr(self, "_fork_ids", ()) if training and _FORK_BN else ()
         for t in self._nodes:
             if id(t) in values:
                 continue
-            ins = [values[id(i)] for i in t.inputs]
+            ins = [v.pop() if isinstance(v, _Forked) else v for v in (values[id(i)] for i in t.inputs)]
             arg = ins if len(ins) > 1 else ins[0]
             if isinstance(t.layer, Model):
                 values[id(t)] = t.layer.call(arg, training=training)
             else:
                 values[id(t)] = t.layer.forward(arg, training=training)
+            if id(t) in fork_ids and isinstance(values[id(t)], torch.Tensor):
+                values[id(t)] = _Forked(ops.bn_fork(values[id(t)]))
         outs = [values[id(o)] for o in self._outputs]
         return outs[0] if len(outs) == 1 else outs
 

@@ -14,7 +14,7 @@ from .loss import softmax_cross_entropy, softmax_cross_entropy_reference  # noqa
 from .elementwise import dropout, relu_bwd_bias_grad, normalize_u8_images, normalize_u8_images_s2d  # noqa: F401
 from .optim import FlatOptimizerState, optim_flat, optim_tick, OPT_CODES, make_hyper  # noqa: F401
 
-from .bn import batch_norm_nhwc, bn_available  # noqa: F401,E402
+from .bn import batch_norm_nhwc, bn_available, fork as bn_fork  # noqa: F401,E402
 from .pool import max_pool_nhwc  # noqa: F401,E402
 from .conv import conv1x1, supported as conv1x1_supported, mode as conv1x1_mode  # noqa: F401,E402
 from .conv import stem_conv, stem_conv_s2d, stem_supported, conv_kxk, kxk_supported  # noqa: F401,E402

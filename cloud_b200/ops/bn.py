@@ -33,6 +33,8 @@ def _k():
         lib.cb2_bn_scratch_floats.restype = i
         lib.cb2_bn_scratch_floats.argtypes = [i]
         lib.cb2_bn_forward.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, f, f, i, i, vp]
+        lib.cb2_bn_backward2.restype = i
+        lib.cb2_bn_backward2.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp]
         lib.cb2_bn_backward.restype = i
         lib.cb2_bn_backward.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp]
         _declared = True
@@ -95,7 +97,10 @@ def _is_nhwc(t):
 class _BNFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, gamma, beta, residual, run_mean, run_var, momentum, eps, relu, mean_bias,
-                sums=None):
+                sums=None, mailbox=None):
+        # `mailbox`: a dict shared with a `fork` of this layer's output (two consumers): the
+        # second consumer's gradient arrives there instead of being added to `dy` by autograd
+        ctx.mailbox = mailbox
         global _launches
         N, C, H, W = x.shape
         M = N * H * W
@@ -140,12 +145,17 @@ class _BNFn(torch.autograd.Function):
         else:
             grads = torch.empty(2 * C, dtype=torch.float32, device=x.device)
             dbeta_ptr, dgamma_ptr = grads.data_ptr(), grads[C:].data_ptr()
-        rc = _k().cb2_bn_backward(dy.data_ptr(), None if y is None else y.data_ptr(), x.data_ptr(),
-                                  save.data_ptr(), save[C:].data_ptr(), gamma.data_ptr(),
-                                  beta.data_ptr(), sums.data_ptr(), dbeta_ptr, dgamma_ptr,
-                                  dx.data_ptr(),
-                                  None if dres is None else dres.data_ptr(), M, C, int(ctx.relu),
-                                  _stream())
+        dy2 = ctx.mailbox.pop("dy2", None) if ctx.mailbox is not None else None
+        if dy2 is not None and not (dy2.shape == dy.shape and dy2.dtype == dy.dtype and _is_nhwc(dy2)):
+            dy = dy + dy2                              # odd layout: fall back to an explicit add
+            dy2 = None
+        rc = _k().cb2_bn_backward2(dy.data_ptr(), None if dy2 is None else dy2.data_ptr(),
+                                   None if y is None else y.data_ptr(), x.data_ptr(),
+                                   save.data_ptr(), save[C:].data_ptr(), gamma.data_ptr(),
+                                   beta.data_ptr(), sums.data_ptr(), dbeta_ptr, dgamma_ptr,
+                                   dx.data_ptr(),
+                                   None if dres is None else dres.data_ptr(), M, C, int(ctx.relu),
+                                   _stream())
         _lib.check(rc, "bn_backward")
         _launches += 2
         if ctx.has_res and dres is None:
@@ -153,8 +163,8 @@ class _BNFn(torch.autograd.Function):
         if direct:
             gparam._cb2_grad_written(gparam)
             bparam._cb2_grad_written(bparam)
-            return dx, None, None, dres, None, None, None, None, None, None, None
-        return dx, grads[C:], grads[:C], dres, None, None, None, None, None, None, None
+            return dx, None, None, dres, None, None, None, None, None, None, None, None
+        return dx, grads[C:], grads[:C], dres, None, None, None, None, None, None, None, None
 
 
 def batch_norm_nhwc(x, gamma, beta, run_mean, run_var, training, momentum, eps, relu=False,
@@ -178,8 +188,11 @@ def batch_norm_nhwc(x, gamma, beta, run_mean, run_var, training, momentum, eps, 
         x.requires_grad or gamma.requires_grad or beta.requires_grad or
         (residual is not None and residual.requires_grad))
     if training and needs_grad:
-        return _BNFn.apply(x, gamma, beta, residual, run_mean, run_var, momentum, eps, relu, mean_bias,
-                           sums)
+        mailbox: dict = {}
+        y = _BNFn.apply(x, gamma, beta, residual, run_mean, run_var, momentum, eps, relu, mean_bias,
+                        sums, mailbox)
+        y._cb2_mailbox = mailbox
+        return y
     if needs_grad:   # frozen layer inside a trainable network: let autograd handle it
         y = torch.nn.functional.batch_norm(x, run_mean, run_var, gamma, beta, False, momentum, eps)
         if residual is not None:
@@ -202,3 +215,32 @@ def batch_norm_nhwc(x, gamma, beta, run_mean, run_var, training, momentum, eps, 
     _lib.check(rc, "bn_forward")
     _launches += 2 if training else 1
     return y
+
+
+class _ForkFn(torch.autograd.Function):
+    """Identity with two outputs for a fused batch-norm output that feeds two consumers.  In
+    backward the second gradient goes into the producer's mailbox (its backward kernels read both
+    gradient streams and sum them in fp32) instead of being added by an elementwise kernel."""
+
+    @staticmethod
+    def forward(ctx, a, mailbox):
+        ctx.mailbox = mailbox
+        return a.view_as(a), a.view_as(a)
+
+    @staticmethod
+    def backward(ctx, g1, g2):
+        if g1 is None or g2 is None:
+            return (g1 if g2 is None else g2), None
+        if not _is_nhwc(g1):
+            g1 = g1.contiguous(memory_format=torch.channels_last)
+        ctx.mailbox["dy2"] = g2
+        return g1, None
+
+
+def fork(a: torch.Tensor):
+    """Two handles on ``a`` whose gradients are merged inside the producing batch-norm's backward
+    kernels; plain ``(a, a)`` when ``a`` did not come from the fused batch-norm with autograd on."""
+    mb = getattr(a, "_cb2_mailbox", None)
+    if mb is None or not a.requires_grad:
+        return a, a
+    return _ForkFn.apply(a, mb)

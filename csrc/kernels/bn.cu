@@ -225,6 +225,14 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
   }
 }
 
+// g += second gradient stream (the output of this BN feeds two consumers: instead of an add
+// kernel in front of the backward pass, both gradients are read here and summed in fp32)
+__device__ __forceinline__ void bn_add8(Vec8& g, const uint4& w) {
+  const Vec8 h = unpack8_bf16(w);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) g.v[j] += h.v[j];
+}
+
 // dz = dy * (y > 0) when a ReLU follows the BN.  Without a saved output the mask is recomputed
 // from x (y > 0 <=> x*sc + sh > 0), which saves reading y - one of three activation-sized reads -
 // for every BN+ReLU without shortcut.
@@ -242,9 +250,10 @@ __device__ __forceinline__ void bn_mask(Vec8& g, const Vec8& xv, const uint4& wy
 }
 
 // sums[0:C] += sum dz ; sums[C:2C] += sum dz * xhat
-template <int MODE>
+template <int MODE, bool DY2>
 __global__ void __launch_bounds__(kBnThreads)
-bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
+bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dy2,
+                     const __nv_bfloat16* __restrict__ y,
                      const __nv_bfloat16* __restrict__ x, const float* __restrict__ save_mean,
                      const float* __restrict__ save_invstd, const float* __restrict__ gamma,
                      const float* __restrict__ beta, float* __restrict__ sums, int M, int C) {
@@ -268,9 +277,11 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     const size_t i1 = static_cast<size_t>(row + stride) * C + m.c8;
     const uint4 wg0 = ld_stream_v4(dy + i0), wg1 = ld_stream_v4(dy + i1);
     const uint4 wx0 = ld_stream_v4(x + i0), wx1 = ld_stream_v4(x + i1);
-    uint4 wy0 = make_uint4(0, 0, 0, 0), wy1 = wy0;
+    uint4 wy0 = make_uint4(0, 0, 0, 0), wy1 = wy0, wh0 = wy0, wh1 = wy0;
     if (MODE == 1) { wy0 = ld_stream_v4(y + i0); wy1 = ld_stream_v4(y + i1); }
+    if (DY2) { wh0 = ld_stream_v4(dy2 + i0); wh1 = ld_stream_v4(dy2 + i1); }
     Vec8 g0 = unpack8_bf16(wg0), g1 = unpack8_bf16(wg1);
+    if (DY2) { bn_add8(g0, wh0); bn_add8(g1, wh1); }
     const Vec8 x0 = unpack8_bf16(wx0), x1 = unpack8_bf16(wx1);
     bn_mask<MODE>(g0, x0, wy0, sc, sh);
     bn_mask<MODE>(g1, x1, wy1, sc, sh);
@@ -284,6 +295,7 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
   for (; row < M; row += stride) {
     const size_t idx = static_cast<size_t>(row) * C + m.c8;
     Vec8 g = unpack8_bf16(ld_stream_v4(dy + idx));
+    if (DY2) bn_add8(g, ld_stream_v4(dy2 + idx));
     const Vec8 xv = unpack8_bf16(ld_stream_v4(x + idx));
     uint4 wy = make_uint4(0, 0, 0, 0);
     if (MODE == 1) wy = ld_stream_v4(y + idx);
@@ -298,9 +310,10 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
 }
 
 // dx = gamma * istd * (dz - dbeta/M - xhat * dgamma/M) ; optionally dres = dz
-template <int MODE>
+template <int MODE, bool DY2>
 __global__ void __launch_bounds__(kBnThreads)
-bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
+bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dy2,
+                    const __nv_bfloat16* __restrict__ y,
                     const __nv_bfloat16* __restrict__ x, const float* __restrict__ save_mean,
                     const float* __restrict__ save_invstd, const float* __restrict__ gamma,
                     const float* __restrict__ beta, const float* __restrict__ sums,
@@ -336,9 +349,11 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
     const size_t i1 = static_cast<size_t>(row + stride) * C + m.c8;
     const uint4 wg0 = ld_stream_v4(dy + i0), wg1 = ld_stream_v4(dy + i1);
     const uint4 wx0 = ld_stream_v4(x + i0), wx1 = ld_stream_v4(x + i1);
-    uint4 wy0 = make_uint4(0, 0, 0, 0), wy1 = wy0;
+    uint4 wy0 = make_uint4(0, 0, 0, 0), wy1 = wy0, wh0 = wy0, wh1 = wy0;
     if (MODE == 1) { wy0 = ld_stream_v4(y + i0); wy1 = ld_stream_v4(y + i1); }
+    if (DY2) { wh0 = ld_stream_v4(dy2 + i0); wh1 = ld_stream_v4(dy2 + i1); }
     Vec8 g0 = unpack8_bf16(wg0), g1 = unpack8_bf16(wg1);
+    if (DY2) { bn_add8(g0, wh0); bn_add8(g1, wh1); }
     const Vec8 x0 = unpack8_bf16(wx0), x1 = unpack8_bf16(wx1);
     bn_mask<MODE>(g0, x0, wy0, sc, sh);
     bn_mask<MODE>(g1, x1, wy1, sc, sh);
@@ -358,6 +373,7 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
   for (; row < M; row += stride) {
     const size_t idx = static_cast<size_t>(row) * C + m.c8;
     Vec8 g = unpack8_bf16(ld_stream_v4(dy + idx));
+    if (DY2) bn_add8(g, ld_stream_v4(dy2 + idx));
     const Vec8 xv = unpack8_bf16(ld_stream_v4(x + idx));
     uint4 wy = make_uint4(0, 0, 0, 0);
     if (MODE == 1) wy = ld_stream_v4(y + idx);
@@ -436,30 +452,51 @@ extern "C" int cb2_bn_forward(const void* x, const void* residual, void* y,
   return check_cuda(cudaGetLastError(), "bn_forward launch");
 }
 
+extern "C" int cb2_bn_backward2(const void* dy, const void* dy2, const void* y, const void* x,
+                                const float* save_mean, const float* save_invstd, const float* gamma,
+                                const float* beta, float* sums, float* dbeta, float* dgamma, void* dx,
+                                void* dres, int M, int C, int relu, void* stream);
+
 extern "C" int cb2_bn_backward(const void* dy, const void* y, const void* x, const float* save_mean,
                                const float* save_invstd, const float* gamma, const float* beta,
                                float* sums /*[cb2_bn_scratch_floats(C)], zeroed*/,
                                float* dbeta /*out [C]*/, float* dgamma /*out [C]*/, void* dx,
                                void* dres /*nullable*/, int M, int C, int relu, void* stream) {
+  return cb2_bn_backward2(dy, nullptr, y, x, save_mean, save_invstd, gamma, beta, sums, dbeta, dgamma,
+                          dx, dres, M, C, relu, stream);
+}
+
+extern "C" int cb2_bn_backward2(const void* dy, const void* dy2 /*nullable: dy += dy2*/, const void* y,
+                                const void* x, const float* save_mean, const float* save_invstd,
+                                const float* gamma, const float* beta, float* sums, float* dbeta,
+                                float* dgamma, void* dx, void* dres, int M, int C, int relu,
+                                void* stream) {
   int rc = bn_check(M, C, "bn_backward");
   if (rc) return rc;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int grid = bn_grid(M, C, true);
   const __nv_bfloat16* dyp = reinterpret_cast<const __nv_bfloat16*>(dy);
+  const __nv_bfloat16* dy2p = reinterpret_cast<const __nv_bfloat16*>(dy2);
   const __nv_bfloat16* yp = reinterpret_cast<const __nv_bfloat16*>(y);
   const __nv_bfloat16* xp = reinterpret_cast<const __nv_bfloat16*>(x);
   __nv_bfloat16* dxp = reinterpret_cast<__nv_bfloat16*>(dx);
   __nv_bfloat16* drp = reinterpret_cast<__nv_bfloat16*>(dres);
   const int mode = !relu ? 0 : (y != nullptr ? 1 : 2);
-#define CB2_BN_BWD(MODE)                                                                          \
-  bn_bwd_reduce_kernel<MODE><<<grid, kBnThreads, 0, st>>>(dyp, yp, xp, save_mean, save_invstd,    \
-                                                          gamma, beta, sums, M, C);               \
-  bn_bwd_apply_kernel<MODE><<<grid, kBnThreads, 0, st>>>(dyp, yp, xp, save_mean, save_invstd,     \
-                                                         gamma, beta, sums, dbeta, dgamma, dxp,   \
-                                                         drp, M, C);
-  if (mode == 0) { CB2_BN_BWD(0) }
-  else if (mode == 1) { CB2_BN_BWD(1) }
-  else { CB2_BN_BWD(2) }
+#define CB2_BN_BWD(MODE, DY2)                                                                      \
+  bn_bwd_reduce_kernel<MODE, DY2><<<grid, kBnThreads, 0, st>>>(dyp, dy2p, yp, xp, save_mean,           \
+                                                               save_invstd, gamma, beta, sums, M, C);  \
+  bn_bwd_apply_kernel<MODE, DY2><<<grid, kBnThreads, 0, st>>>(dyp, dy2p, yp, xp, save_mean,            \
+                                                              save_invstd, gamma, beta, sums, dbeta,   \
+                                                              dgamma, dxp, drp, M, C);
+  if (dy2p == nullptr) {
+    if (mode == 0) { CB2_BN_BWD(0, false) }
+    else if (mode == 1) { CB2_BN_BWD(1, false) }
+    else { CB2_BN_BWD(2, false) }
+  } else {
+    if (mode == 0) { CB2_BN_BWD(0, true) }
+    else if (mode == 1) { CB2_BN_BWD(1, true) }
+    else { CB2_BN_BWD(2, true) }
+  }
 #undef CB2_BN_BWD
   return check_cuda(cudaGetLastError(), "bn_backward launch");
 }

@@ -138,6 +138,13 @@ int cb2_bn_backward(const void* dy, const void* y /*nullable*/, const void* x,
                     const float* save_mean, const float* save_invstd, const float* gamma,
                     const float* beta, float* sums, float* dbeta, float* dgamma, void* dx,
                     void* dres /*nullable*/, int M, int C, int relu, void* stream);
+/* cb2_bn_backward with a second incoming gradient: dy_total = dy + dy2 (dy2 nullable), summed in
+ * fp32 inside both passes - for a batch-norm output that feeds two consumers (a residual block's
+ * input), instead of an elementwise add of two activation-sized tensors in front of it. */
+int cb2_bn_backward2(const void* dy, const void* dy2, const void* y, const void* x,
+                     const float* save_mean, const float* save_invstd, const float* gamma,
+                     const float* beta, float* sums, float* dbeta, float* dgamma, void* dx, void* dres,
+                     int M, int C, int relu, void* stream);
 
 /* cb2_bn_forward for callers that cannot allocate device memory.  (No counterpart in the
  * reference: it has no kernels and no C ABI; this entry exists for embedders of this library.)
