@@ -456,3 +456,29 @@ def test_conv_kxk_weight_gradient_on_shifted_tma_boxes(B, H, W, Cin, Cout, k):
     _check_close(y, yr, 2e-2, 2e-2, "conv fwd")
     _check_close(x.grad, xr.grad, 3e-2, 3e-2, "conv dX")
     _check_close(w.grad, wr.grad, 2e-2, 2e-2 * math.sqrt(B * H * W), "conv dW")
+
+
+def test_forked_batch_norm_output_merges_gradients_in_its_backward():
+    """y = BN(x) feeds two consumers: with ops.bn_fork the two gradients are summed inside the BN
+    backward kernels; the result must equal plain autograd accumulation."""
+    torch.manual_seed(13)
+    dev = _dev()
+    C = 128
+    x0 = (torch.randn(6, C, 14, 14, device=dev) * 2).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    w1 = torch.randn(C, C, 1, 1, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last) / 12
+    res_out = {}
+    for forked in (True, False):
+        x = x0.clone().requires_grad_(True)
+        gamma = (torch.rand(C, device=dev) + 0.5).requires_grad_(True)
+        beta = torch.zeros(C, device=dev, requires_grad=True)
+        rm, rv = torch.zeros(C, device=dev), torch.ones(C, device=dev)
+        a = ops.batch_norm_nhwc(x, gamma, beta, rm, rv, True, 0.1, 1e-5, relu=True)
+        a1, a2 = ops.bn_fork(a) if forked else (a, a)
+        assert (a1 is not a) == forked
+        out = torch.nn.functional.conv2d(a1, w1) * 0.5 + a2 * 2.0
+        torch.manual_seed(14)
+        out.backward(torch.randn_like(out))
+        res_out[forked] = (x.grad.float(), gamma.grad.clone(), beta.grad.clone())
+    for got, want, name in zip(res_out[True], res_out[False], ("dx", "dgamma", "dbeta")):
+        scale = want.abs().max().item()
+        assert (got - want).abs().max().item() <= 2e-2 * scale + 1e-3, name
