@@ -466,18 +466,19 @@ def test_forked_batch_norm_output_merges_gradients_in_its_backward():
     C = 128
     x0 = (torch.randn(6, C, 14, 14, device=dev) * 2).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
     w1 = torch.randn(C, C, 1, 1, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last) / 12
+    gamma0 = torch.rand(C, device=dev) + 0.5
+    grad_out = torch.randn(6, C, 14, 14, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
     res_out = {}
     for forked in (True, False):
         x = x0.clone().requires_grad_(True)
-        gamma = (torch.rand(C, device=dev) + 0.5).requires_grad_(True)
+        gamma = gamma0.clone().requires_grad_(True)
         beta = torch.zeros(C, device=dev, requires_grad=True)
         rm, rv = torch.zeros(C, device=dev), torch.ones(C, device=dev)
         a = ops.batch_norm_nhwc(x, gamma, beta, rm, rv, True, 0.1, 1e-5, relu=True)
         a1, a2 = ops.bn_fork(a) if forked else (a, a)
         assert (a1 is not a) == forked
         out = torch.nn.functional.conv2d(a1, w1) * 0.5 + a2 * 2.0
-        torch.manual_seed(14)
-        out.backward(torch.randn_like(out))
+        out.backward(grad_out)
         res_out[forked] = (x.grad.float(), gamma.grad.clone(), beta.grad.clone())
     for got, want, name in zip(res_out[True], res_out[False], ("dx", "dgamma", "dbeta")):
         scale = want.abs().max().item()
