@@ -2,7 +2,7 @@
 `ncu --set full` captures (one GPU; see /opt/skills/guides/B200_PROFILING.md):
 
     python bench/ncu_targets.py && ncu --set full --clock-control none --import-source on \
-        -k regex:"gemm_tcgen05|bn_|softmax_xent|optim_flat|maxpool" -c 24 -o gpurun_out/prof \
+        -k regex:"gemm_tcgen05|bn_|softmax_xent|optim_flat|maxpool|u8_to" -c 24 -o gpurun_out/prof \
         python bench/ncu_targets.py
 """
 import os
@@ -47,6 +47,15 @@ for (n, c, hw) in ((256, 256, 56), (64, 1024, 14)):
     rm, rv = torch.zeros(c, device=dev), torch.ones(c, device=dev)
     y = ops.batch_norm_nhwc(x, g, bt, rm, rv, True, 0.1, 1e-5, relu=True)
     y.backward(torch.ones_like(y))
+
+# ResNet stem on the implicit GEMM (space-to-depth image through a 4-D tensor map), batch 256
+from cloud_b200.ops import conv as conv_ops  # noqa: E402
+img = torch.randint(0, 256, (256, 224, 224, 3), dtype=torch.uint8, device=dev)
+wst = (torch.randn(64, 3, 7, 7, device=dev) / 12).to(torch.bfloat16).contiguous(
+    memory_format=torch.channels_last).requires_grad_(True)
+for _ in range(2):
+    ys = ops.stem_conv_s2d(ops.normalize_u8_images_s2d(img), wst)
+    ys.backward(torch.ones_like(ys))
 
 # stem max-pool
 xp = torch.rand(256, 64, 112, 112, device=dev).to(torch.bfloat16).contiguous(
