@@ -348,6 +348,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint64_t* tfull_bar = bars + 2 * kStages;     // [2] MMA -> epilogue
   uint64_t* tempty_bar = bars + 2 * kStages + 2;  // [2] epilogue -> MMA
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+  uint64_t* wbar = bars + 2 * kStages + 5;      // conv == 4: resident weights loaded
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -364,6 +365,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       mbar_init(&tfull_bar[a], 1);
       mbar_init(&tempty_bar[a], 4);
     }
+    mbar_init(wbar, 1);
     mbar_fence_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, Cfg::kTmemCols);
@@ -373,13 +375,45 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const uint32_t tmem_base = *tmem_slot;
 
   const int num_tiles = p.m_tiles * p.n_tiles * p.splits;
+  // conv == 4 (stem forward with an input-row ring): every CTA owns a contiguous range of output
+  // rows, so that consecutive tiles share three of their four input rows; otherwise round-robin
+  // (the convolution modes exist only in the instantiations their host entry points launch)
+  constexpr bool kStemFwd = BN == 64 && !A_MN && !B_MN;
+  constexpr bool kConvMN = A_MN && B_MN;
+  int tile_begin = blockIdx.x, tile_end = num_tiles, tile_step = gridDim.x;
+  if (kStemFwd && p.conv == 4) {
+    const int per = (num_tiles + gridDim.x - 1) / gridDim.x;
+    tile_begin = blockIdx.x * per;
+    tile_end = min(num_tiles, tile_begin + per);
+    tile_step = 1;
+  }
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      if (kStemFwd && p.conv == 4) {
+        // resident weights: the four k blocks go into B stages 0..3 once
+        mbar_expect_tx(wbar, 4 * Cfg::kBStageBytes);
+        for (int kb = 0; kb < 4; ++kb)
+          tma_load_2d(&tmB, wbar, smem_b + kb * Cfg::kBStageBytes, kb * BK, 0);
+        // input rows stream through the A stages as a ring: tile (b, oh) needs rows oh..oh+3 and
+        // only row oh+3 is new unless the tile starts an image or this CTA's range
+        int seq = 0;
+        for (int R = tile_begin; R < tile_end; ++R) {
+          const int b = R / p.conv_oh, oh = R - b * p.conv_oh;
+          const bool fresh = R == tile_begin || oh == 0;
+          for (int h = fresh ? oh : oh + 3; h <= oh + 3; ++h, ++seq) {
+            const int slot = seq % kStages;
+            mbar_wait(&empty_bar[slot], (((seq / kStages) & 1) ^ 1));
+            mbar_expect_tx(&full_bar[slot], p.conv_a_bytes);
+            tma_load_4d(&tmA, &full_bar[slot], smem_a + slot * kAStageBytes, 0, 0, h, b);
+          }
+        }
+        tile_begin = tile_end;       // nothing left for the generic loop below
+      }
+      for (int tile = tile_begin; tile < tile_end; tile += tile_step) {
         const WorkItem it = decode_work<BN>(p, tile);
         const int m0 = it.m0, n0 = it.n0;
         for (int kb = it.kb0; kb < it.kb1; ++kb) {
@@ -387,7 +421,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           uint8_t* sa = smem_a + stage * kAStageBytes;
           uint8_t* sb = smem_b + stage * Cfg::kBStageBytes;
           const int k0 = kb * BK;
-          if (p.conv == 1) {
+          if (kStemFwd && p.conv == 1) {
             // stem forward: output row R = (image, oh); k block kb = kernel row: the 112 A rows
             // are the 128-byte windows of input row oh + kb, one per output pixel (32 B apart)
             const int R = m0 / BM;
@@ -398,7 +432,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             continue;
           }
           mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-          if (p.conv == 2) {
+          if (kConvMN && BN == 64 && p.conv == 2) {
             // stem weight gradient: k block = 64 output pixels (half) of output row R; the two
             // 64-wide chunks of the A tile are kernel rows 2*mt and 2*mt + 1
             const int R = kb >> 1, half = kb & 1;
@@ -410,7 +444,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             if (++stage == kStages) { stage = 0; phase ^= 1; }
             continue;
           }
-          if (p.conv == 3) {
+          if (kConvMN && p.conv == 3) {
             const int b = kb / p.conv_hblocks;
             const int h0 = (kb - b * p.conv_hblocks) * p.conv_hbox;
 #pragma unroll
@@ -458,7 +492,41 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       int stage = 0;
       uint32_t phase = 0;
       int t = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
+      if (kStemFwd && p.conv == 4) {
+        mbar_wait(wbar, 0);
+        int base = 0, loaded = 0;    // load-sequence number of row oh of the tile / rows requested so far
+        for (int R = tile_begin; R < tile_end; ++R, ++t) {
+          const int oh = R % p.conv_oh;
+          const bool fresh = R == tile_begin || oh == 0;
+          base = fresh ? loaded : base + 1;
+          loaded += fresh ? 4 : 1;
+          const int acc = t & 1;
+          mbar_wait(&tempty_bar[acc], ((t >> 1) & 1) ^ 1);
+          tc_fence_after();
+          const uint32_t tmem_d = tmem_base + acc * BN;
+          for (int i = 0; i < 4; ++i) {
+            const int sq = base + i, slot = sq % kStages;
+            mbar_wait(&full_bar[slot], (sq / kStages) & 1);     // rows seen by earlier tiles: already complete
+            tc_fence_after();
+            const uint64_t adesc =
+                make_smem_desc(smem_u32(smem_a + slot * kAStageBytes), p.a_lbo, p.a_sbo);
+            const uint64_t bdesc =
+                make_smem_desc(smem_u32(smem_b + i * Cfg::kBStageBytes), p.b_lbo, p.b_sbo);
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k)
+              umma_bf16(tmem_d, adesc + static_cast<uint64_t>(k * p.a_kadv),
+                        bdesc + static_cast<uint64_t>(k * p.b_kadv), idesc, (i | k) != 0);
+          }
+          // this tile is the last user of row oh; the last tile of an image / of the range also
+          // releases the three rows nobody else will read
+          umma_commit(&empty_bar[base % kStages]);
+          if (R + 1 == tile_end || oh == p.conv_oh - 1)
+            for (int i = 1; i < 4; ++i) umma_commit(&empty_bar[(base + i) % kStages]);
+          umma_commit(&tfull_bar[acc]);
+        }
+        tile_begin = tile_end;
+      }
+      for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++t) {
         const int acc = t & 1;
         const uint32_t acc_phase = (t >> 1) & 1;
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
@@ -502,7 +570,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     int cs_n0 = -1;
 #pragma unroll
     for (int ci = 0; ci < BN / 64; ++ci) cs[ci][0] = cs[ci][1] = cs[ci][2] = cs[ci][3] = 0.f;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
+    for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++t) {
       const int acc = t & 1;
       const uint32_t acc_phase = (t >> 1) & 1;
       const WorkItem it = decode_work<BN>(p, tile);
@@ -543,7 +611,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             epilogue_tma<BN, false, true>(&tmC, taddr, stg, sbias, stage_buf, n0, m0 + q * 32, p.N, lo,
                                           plain, accum, lane, cs);
           } else {
-            if (p.conv == 1)
+            if (kStemFwd && (p.conv == 1 || p.conv == 4))
               epilogue_tma<BN, false, false>(&tmC, taddr, stg, sbias, stage_buf, n0, q * 32, p.N, lo,
                                              plain, accum, lane, cs, m0 / BM);
             else
@@ -682,6 +750,14 @@ static EncodeTiledFn get_encode_fn() {
         qres == cudaDriverEntryPointSuccess)
       fn = reinterpret_cast<EncodeTiledFn>(sym);
   });
+  // The driver call wants a current context on the calling thread.  A thread that has only ever
+  // been handed device pointers (autograd's backward thread running the first backward of the
+  // process) has none yet: a runtime call binds the primary context (seen as error 201).
+  static thread_local bool bound = false;
+  if (!bound) {
+    cudaFree(nullptr);
+    bound = true;
+  }
   return fn;
 }
 
@@ -1045,7 +1121,10 @@ extern "C" int cb2_conv_stem_forward(const void* xs, const void* wm, void* y, in
   args.m_tiles = B * OH; args.n_tiles = 1; args.k_blocks = 4;
   args.splits = 1; args.kb_per_split = 4;
   args.tma_store = 1;
-  args.conv = 1; args.conv_oh = OH; args.conv_a_bytes = OW * 128;
+  // 4 = input rows kept in a ring of smem stages (each row fetched once per CTA instead of once per
+  // kernel row) and the weights resident; TFC_STEM_RING=0 selects the plain per-tile loads (1)
+  static const bool ring = [] { const char* e = getenv("TFC_STEM_RING"); return !(e && e[0] == '0'); }();
+  args.conv = ring ? 4 : 1; args.conv_oh = OH; args.conv_a_bytes = OW * 128;
   fill_descriptors(args, false, false);
   return launch_gemm<64, false, false>(tmA, tmB, tmC, args, reinterpret_cast<cudaStream_t>(stream));
 }
