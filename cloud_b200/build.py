@@ -161,6 +161,35 @@ def build_runtime_tests(verbose: bool = False) -> list[Path]:
     return outs
 
 
+def build_runtime_tests_sanitized(sanitizer: str = "thread", verbose: bool = False) -> list[Path]:
+    """The C++ unit tests and the whole runtime library compiled into one binary with
+    ``-fsanitize=<sanitizer>`` (thread | address | undefined): the race / memory checks of
+    SURVEY.md section 5.2 for the exporter thread, the registry locks and the HDF5 code."""
+    cxx = _find("g++", ["/usr/bin/g++"])
+    if cxx is None:
+        raise RuntimeError("g++ not found")
+    lib_srcs = [s for s in sorted((CSRC / "runtime").glob("*.cc")) if not s.name.startswith("test_")]
+    outs = []
+    for src in sorted((CSRC / "runtime").glob("test_*.cc")):
+        out = ROOT / "build" / "bin" / f"{src.stem}_{sanitizer}san"
+        out.parent.mkdir(parents=True, exist_ok=True)
+        newest = max(p.stat().st_mtime_ns for p in lib_srcs + [src])
+        if out.exists() and out.stat().st_mtime_ns > newest:
+            outs.append(out)
+            continue
+        flags = [f for f in CXX_FLAGS if f not in ("-O3", "-O2")] + ["-O1", "-g", f"-fsanitize={sanitizer}",
+                                                                      "-fno-omit-frame-pointer"]
+        cmd = [cxx] + flags + [f"-I{INCLUDE}", f"-I{CSRC / 'runtime'}", f"-I{cuda_home()}/include", str(src)] + \
+            [str(s) for s in lib_srcs] + ["-o", str(out), "-ldl", "-pthread"]
+        if verbose:
+            print("[cloud_b200.build]", " ".join(cmd), flush=True)
+        res = subprocess.run(cmd, capture_output=True, text=True)
+        if res.returncode != 0:
+            raise RuntimeError(f"sanitized test build failed: {src}\n{res.stdout}\n{res.stderr}")
+        outs.append(out)
+    return outs
+
+
 def build_all(verbose: bool = False) -> dict[str, Path]:
     return {"kernels": build_kernels(verbose), "runtime": build_runtime(verbose)}
 

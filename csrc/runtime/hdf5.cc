@@ -359,22 +359,33 @@ struct Reader {
   uint64_t base = 0;
   uint16_t leaf_k = 4, internal_k = 16;
 
-  bool ok(uint64_t a, size_t n) const { return a != UNDEF && a + n <= f.size(); }
+  // Every access of the reader goes through these: a truncated or corrupted file must produce
+  // "no such object" / an error, never an out-of-bounds read (csrc/runtime/test_hdf5.cc feeds it
+  // hundreds of broken files under AddressSanitizer).
+  bool ok(uint64_t a, uint64_t n) const { return a != UNDEF && n <= f.size() && a <= f.size() - n; }
+  uint8_t at(uint64_t a) const { return a < f.size() ? f[a] : 0; }
   uint64_t rd(uint64_t a, int n) const {
+    if (!ok(a, static_cast<uint64_t>(n))) return 0;
     uint64_t v = 0;
     for (int i = 0; i < n; ++i) v |= static_cast<uint64_t>(f[a + i]) << (8 * i);
     return v;
   }
+  // NUL-terminated string at `a`, cut at the end of the file
+  std::string cstr(uint64_t a) const {
+    std::string out;
+    while (a < f.size() && f[a] != 0 && out.size() < 4096) out.push_back(static_cast<char>(f[a++]));
+    return out;
+  }
 };
 
 bool parse_datatype(const Reader& r, uint64_t a, int* dtype, size_t* size) {
-  const uint8_t cv = r.f[a];
+  const uint8_t cv = r.at(a);
   const int cls = cv & 0x0f;
   const uint32_t sz = static_cast<uint32_t>(r.rd(a + 4, 4));
   *size = sz;
   if (cls == 1) { *dtype = sz == 4 ? F32 : (sz == 8 ? F64 : -1); return true; }
   if (cls == 0) {
-    const bool sign = (r.f[a + 1] & 0x08) != 0;
+    const bool sign = (r.at(a + 1) & 0x08) != 0;
     if (sz == 4 && sign) *dtype = I32;
     else if (sz == 8 && sign) *dtype = I64;
     else if (sz == 1) *dtype = U8;
@@ -387,7 +398,7 @@ bool parse_datatype(const Reader& r, uint64_t a, int* dtype, size_t* size) {
 }
 
 size_t datatype_msg_len(const Reader& r, uint64_t a) {
-  const int cls = r.f[a] & 0x0f;
+  const int cls = r.at(a) & 0x0f;
   if (cls == 1) return 20;
   if (cls == 0) return 12;
   if (cls == 3) return 8;
@@ -395,9 +406,10 @@ size_t datatype_msg_len(const Reader& r, uint64_t a) {
 }
 
 bool parse_dataspace(const Reader& r, uint64_t a, std::vector<uint64_t>* dims, size_t* len) {
-  const int ver = r.f[a];
-  const int rank = r.f[a + 1];
-  const int flags = r.f[a + 2];
+  const int ver = r.at(a);
+  const int rank = r.at(a + 1);
+  const int flags = r.at(a + 2);
+  if (rank > 32) return false;
   uint64_t p;
   if (ver == 1) p = a + 8;
   else if (ver == 2) p = a + 4;
@@ -411,7 +423,7 @@ bool parse_dataspace(const Reader& r, uint64_t a, std::vector<uint64_t>* dims, s
 }
 
 void parse_attr(const Reader& r, uint64_t a, size_t msg_size, RObject* obj) {
-  const int ver = r.f[a];
+  const int ver = r.at(a);
   RAttr at;
   uint64_t p;
   const size_t name_sz = r.rd(a + 2, 2), dt_sz = r.rd(a + 4, 2), ds_sz = r.rd(a + 6, 2);
@@ -419,7 +431,7 @@ void parse_attr(const Reader& r, uint64_t a, size_t msg_size, RObject* obj) {
   p = a + 8;
   if (ver == 3) p += 1;  // name character-set encoding
   if (ver < 1 || ver > 3) return;
-  at.name = std::string(reinterpret_cast<const char*>(&r.f[p]));
+  at.name = r.cstr(p);
   p += pad(name_sz);
   size_t esz = 0;
   parse_datatype(r, p, &at.dtype, &esz);
@@ -429,10 +441,10 @@ void parse_attr(const Reader& r, uint64_t a, size_t msg_size, RObject* obj) {
   if (!parse_dataspace(r, p, &at.dims, &dsl)) return;
   p += pad(ds_sz);
   uint64_t n = 1;
-  for (uint64_t d : at.dims) n *= d;
-  const size_t bytes = n * esz;
-  if (p + bytes > a + msg_size + 8 || p + bytes > r.f.size()) { at.dtype = -1; }
-  else at.data.assign(r.f.begin() + p, r.f.begin() + p + bytes);
+  for (uint64_t d : at.dims) n = (d != 0 && n > (1ull << 40) / d) ? (1ull << 40) : n * d;   // no overflow
+  const uint64_t bytes = n * esz;
+  if (bytes > msg_size + 8 || !r.ok(p, bytes) || p + bytes > a + msg_size + 8) { at.dtype = -1; }
+  else at.data.assign(r.f.begin() + static_cast<long>(p), r.f.begin() + static_cast<long>(p + bytes));
   obj->attrs.push_back(std::move(at));
 }
 
@@ -442,7 +454,7 @@ void parse_messages(const Reader& r, uint64_t a, uint64_t end, int* remaining, R
     const uint16_t size = static_cast<uint16_t>(r.rd(a + 2, 2));
     const uint64_t body = a + 8;
     --*remaining;
-    if (body + size > r.f.size()) return;
+    if (!r.ok(body, size)) return;
     switch (type) {
       case 0x0011:
         obj->is_group = true;
@@ -452,13 +464,17 @@ void parse_messages(const Reader& r, uint64_t a, uint64_t end, int* remaining, R
       case 0x0001: { size_t l; parse_dataspace(r, body, &obj->dims, &l); break; }
       case 0x0003: parse_datatype(r, body, &obj->dtype, &obj->elem_size); break;
       case 0x0008: {
-        const int ver = r.f[body];
+        const int ver = r.at(body);
         if (ver == 3) {
-          const int cls = r.f[body + 1];
+          const int cls = r.at(body + 1);
           if (cls == 1) { obj->data_addr = r.rd(body + 2, 8); obj->data_size = r.rd(body + 10, 8);
                           if (obj->data_addr != UNDEF) obj->data_addr += r.base; }
-          else if (cls == 0) { const size_t n = r.rd(body + 2, 2); obj->is_compact = true;
-                               obj->compact.assign(r.f.begin() + body + 4, r.f.begin() + body + 4 + n); }
+          else if (cls == 0) { const size_t n = r.rd(body + 2, 2);
+                               if (r.ok(body + 4, n)) {
+                                 obj->is_compact = true;
+                                 obj->compact.assign(r.f.begin() + static_cast<long>(body + 4),
+                                                     r.f.begin() + static_cast<long>(body + 4 + n));
+                               } }
         }
         break;
       }
@@ -475,7 +491,7 @@ void parse_messages(const Reader& r, uint64_t a, uint64_t end, int* remaining, R
 }
 
 bool read_object(const Reader& r, uint64_t addr, RObject* obj) {
-  if (!r.ok(addr, 16) || r.f[addr] != 1) return false;
+  if (!r.ok(addr, 16) || r.at(addr) != 1) return false;
   int nmsg = static_cast<int>(r.rd(addr + 2, 2));
   const uint64_t size = r.rd(addr + 8, 4);
   parse_messages(r, addr + 16, addr + 16 + size, &nmsg, obj, 0);
@@ -486,7 +502,7 @@ void walk_btree(const Reader& r, uint64_t node, uint64_t heap_data,
                 std::vector<std::pair<std::string, uint64_t>>* out, int depth) {
   if (!r.ok(node, 24) || depth > 8) return;
   if (memcmp(&r.f[node], "TREE", 4) == 0) {
-    const int level = r.f[node + 5];
+    const int level = r.at(node + 5);
     const int used = static_cast<int>(r.rd(node + 6, 2));
     uint64_t p = node + 24 + 8;
     for (int i = 0; i < used; ++i) {
@@ -500,8 +516,8 @@ void walk_btree(const Reader& r, uint64_t node, uint64_t heap_data,
     uint64_t p = node + 8;
     for (int i = 0; i < cnt; ++i) {
       const uint64_t noff = r.rd(p, 8), oh = r.rd(p + 8, 8) + r.base;
-      if (r.ok(heap_data + noff, 1))
-        out->push_back({std::string(reinterpret_cast<const char*>(&r.f[heap_data + noff])), oh});
+      if (r.ok(heap_data, 1) && noff < r.f.size() && r.ok(heap_data + noff, 1) && out->size() < 100000)
+        out->push_back({r.cstr(heap_data + noff), oh});
       p += 40;
     }
   }
@@ -627,8 +643,19 @@ void* cb2h5_reader_open(const char* filename) {
   r->base = r->rd(p, 8);
   if (r->base == UNDEF) r->base = 0;
   r->base += 0;
+  const uint64_t eof = r->rd(p + 16, 8);
+  if (eof != UNDEF && (eof > r->f.size() || r->base > r->f.size() - eof)) {
+    cb2rt::set_error("%s is truncated: the superblock says %llu bytes, the file has %zu", filename,
+                     static_cast<unsigned long long>(eof + r->base), r->f.size());
+    return nullptr;
+  }
   p += 32;  // base, free-space, eof, driver
   r->root_header = r->rd(p + 8, 8) + r->base;
+  RObject root;
+  if (!read_object(*r, r->root_header, &root) || !root.is_group) {
+    cb2rt::set_error("%s: the root group's object header is unreadable", filename);
+    return nullptr;
+  }
   return r.release();
 }
 
@@ -668,7 +695,11 @@ int cb2h5_reader_read_dataset(void* rp, const char* path, void* out, size_t nbyt
   for (uint64_t d : o.dims) n *= d;
   const size_t need = n * o.elem_size;
   if (need != nbytes) { cb2rt::set_error("dataset %s holds %zu bytes, buffer has %zu", path, need, nbytes); return 1; }
-  if (o.is_compact) { memcpy(out, o.compact.data(), std::min(need, o.compact.size())); return 0; }
+  if (o.is_compact) {
+    if (o.compact.size() < need) { cb2rt::set_error("dataset %s: compact data shorter than its shape", path); return 1; }
+    memcpy(out, o.compact.data(), need);
+    return 0;
+  }
   if (need == 0) return 0;
   if (!r->ok(o.data_addr, need)) { cb2rt::set_error("dataset %s is not contiguous (chunked/unallocated data is not supported)", path); return 1; }
   memcpy(out, &r->f[o.data_addr], need);
