@@ -48,6 +48,36 @@ def _np(a):
 # ----------------------------------------------------------------------------------------------
 # Batch sources
 # ----------------------------------------------------------------------------------------------
+_HEARTBEAT = {"path": None, "last": 0.0, "resolved": False}
+
+
+def _heartbeat():
+    """Under the launcher: touch <job_dir>/heartbeat/rank<r> at most once a second.  The host blocks
+    on the device within a step or two (loss read-back, launch queue), so a hung kernel or
+    collective silences it and the supervisor's TFC_HEARTBEAT_TIMEOUT check ends the job."""
+    hb = _HEARTBEAT
+    if not hb["resolved"]:
+        hb["resolved"] = True
+        jdir = os.environ.get("TFC_JOB_DIR")
+        if jdir:
+            d = os.path.join(jdir, "heartbeat")
+            try:
+                os.makedirs(d, exist_ok=True)
+                hb["path"] = os.path.join(d, "rank{}".format(os.environ.get("RANK", "0")))
+            except OSError:
+                hb["path"] = None
+    if hb["path"] is None:
+        return
+    now = time.monotonic()
+    if now - hb["last"] >= 1.0:
+        hb["last"] = now
+        try:
+            with open(hb["path"], "a"):
+                os.utime(hb["path"], None)
+        except OSError:
+            pass
+
+
 class _Forked(list):
     """The two handles of a forked batch-norm output, handed out to its two consumers."""
 
@@ -521,6 +551,7 @@ class Model(nn.Module):
 
     def _run_step(self, xb, yb, global_batch=None):
         """Eager for the first steps (and for odd shapes), then CUDA-graph replay."""
+        _heartbeat()
         if not self._graph_enabled():
             return self._train_step(xb, yb, global_batch)
         g = self._graph

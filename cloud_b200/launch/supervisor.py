@@ -80,6 +80,13 @@ def run_job(job_id: str) -> int:
         procs.append(subprocess.Popen(cmd, cwd=workdir, env=env, stdout=fh, stderr=subprocess.STDOUT,
                                       start_new_session=True))
     timeout = float(os.environ.get("TFC_JOB_TIMEOUT", "0") or 0)
+    # Heartbeats: the training engine touches <job_dir>/heartbeat/rank<r>
+    # after every step.  A rank that has started beating and then stays silent for longer than
+    # TFC_HEARTBEAT_TIMEOUT seconds (0 = off) - a hung collective, a wedged data loader - fails
+    # the job instead of holding the GPUs forever.
+    hb_timeout = float(os.environ.get("TFC_HEARTBEAT_TIMEOUT", "0") or 0)
+    hb_dir = os.path.join(jdir, "heartbeat")
+    os.makedirs(hb_dir, exist_ok=True)
     t0 = time.time()
     failed = None
     cancelled = {"flag": False}
@@ -102,6 +109,15 @@ def run_job(job_id: str) -> int:
         if timeout and time.time() - t0 > timeout:
             failed = (-1, "timeout after {}s".format(timeout))
             break
+        if hb_timeout:
+            now = time.time()
+            for i, p in enumerate(procs):
+                hb = os.path.join(hb_dir, "rank{}".format(i))
+                if p.poll() is None and os.path.exists(hb) and now - os.path.getmtime(hb) > hb_timeout:
+                    failed = (i, "no heartbeat for {:.0f}s (stalled)".format(now - os.path.getmtime(hb)))
+                    break
+            if failed is not None:
+                break
         time.sleep(0.1)
 
     if failed is not None or cancelled["flag"]:

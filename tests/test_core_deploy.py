@@ -101,6 +101,24 @@ def test_failing_rank_fails_job_and_is_reported(tmp_path, capsys):
     assert "Job failed (rank 1, exit code 3)." in capsys.readouterr().out
 
 
+def test_stalled_rank_is_detected_by_its_heartbeat(tmp_path, capsys, monkeypatch):
+    """A rank that beat once and then hangs (a wedged collective) fails the job (section 5.3)."""
+    monkeypatch.setenv("TFC_HEARTBEAT_TIMEOUT", "1.5")
+    script = ("import os, time\n"
+              "hb = os.path.join(os.environ['TFC_JOB_DIR'], 'heartbeat', 'rank' + os.environ['RANK'])\n"
+              "os.makedirs(os.path.dirname(hb), exist_ok=True)\n"
+              "for i in range(100):\n"
+              "    if os.environ['RANK'] == '0' or i == 0:\n"
+              "        open(hb, 'a').close(); os.utime(hb, None)\n"
+              "    time.sleep(0.3)\n")
+    uri = _stage(tmp_path, script)
+    job_id = deploy.deploy_job("us-central1", uri, CFG["CPU"], 1, CFG["CPU"], None, True)
+    st = registry.status(job_id)
+    assert st["state"] == "FAILED" and st["failed_rank"] == 1
+    assert "no heartbeat" in str(st["exit_code"])
+    assert st["seconds"] < 20
+
+
 def test_submission_error_is_reported(tmp_path, capsys):
     uri = _stage(tmp_path)
     with mock.patch.object(deploy, "_start_supervisor", side_effect=OSError("no fork")):

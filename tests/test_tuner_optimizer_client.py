@@ -166,3 +166,48 @@ def test_user_agent_is_stamped(svc):
     path = os.path.join(svc.root, "proj", "us-central1", "study-a", "study.json")
     assert json.load(open(path))["client"].startswith("cloud-b200/")
     assert c.project_id == "proj"
+
+
+# -- the file-backed service under concurrent processes -------------------
+def _hammer(args):
+    root, worker, n_trials = args
+    import os
+    import random
+    import time
+    os.environ["TFC_VIZIER_ROOT"] = root
+    os.environ["TFC_STUDY_RETRY_SECS"] = "0"
+    from cloud_b200.tuner import local_vizier as lv, optimizer_client as oc
+    time.sleep(random.random() * 0.05)                 # start jitter, as in the reference's integration test
+    c = oc.create_or_load_study("proj", "r", "stress", CONFIG, service_client=lv.LocalVizier())
+    mine = []
+    for i in range(n_trials):
+        sug = c.get_suggestions("w{}".format(worker))
+        if not sug.get("trials"):
+            break
+        t = sug["trials"][0]
+        tid = t["name"].split("/")[-1]
+        again = c.get_suggestions("w{}".format(worker))["trials"][0]["name"]     # sticky while ACTIVE
+        assert again == t["name"]
+        c.report_intermediate_objective_value(step=1, elapsed_secs=0.1, metric_list=[{"acc": 0.1 * i}],
+                                              trial_id=tid)
+        c.complete_trial(tid, trial_infeasible=False)
+        mine.append(t["name"])
+    return mine
+
+
+def test_file_locked_store_survives_concurrent_processes(tmp_path):
+    import multiprocessing as mp
+    root = str(tmp_path / "vizier")
+    workers, per = 6, 8
+    ctx = mp.get_context("spawn")
+    with ctx.Pool(workers) as pool:
+        results = pool.map(_hammer, [(root, w, per) for w in range(workers)])
+    names = [n for r in results for n in r]
+    assert len(names) == workers * per
+    assert len(set(names)) == len(names), "two processes were handed the same trial"
+    svc = local_vizier.LocalVizier(root)
+    trials = svc.list_trials("projects/proj/locations/r/studies/stress")["trials"]
+    assert len(trials) == workers * per
+    assert sorted(int(t["name"].split("/")[-1]) for t in trials) == list(range(1, workers * per + 1))
+    assert all(t["state"] == "COMPLETED" and t.get("finalMeasurement") for t in trials)
+    assert {t["clientId"] for t in trials} == {"w{}".format(w) for w in range(workers)}
