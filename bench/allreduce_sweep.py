@@ -114,6 +114,43 @@ def check(comm, dev, world, rank, results):
     return ok_all
 
 
+def stress(comm, dev, world, rank, results, iters=48):
+    """Skewed arrival: back-to-back fused all-reduces with NO host barrier
+    in between, every rank delaying both its host thread and its stream by a different random
+    amount before each call, schedules and lengths alternating.  Exercises the per-(block, source)
+    epoch flags and the closing barrier of the kernels when a fast rank is already two calls ahead
+    of a slow one."""
+    import random
+    import time
+    n_max = 8 * world * 8209
+    gbuf, pbuf = comm.alloc_pair(n_max * 4, n_max * 4)
+    ctx = comm.make_ctx(gbuf, pbuf)
+    g_arena, p_arena = gbuf.view(torch.float32, n_max), pbuf.view(torch.float32, n_max)
+    algos = [C.ALGO_ONESHOT, C.ALGO_TWOSHOT] + ([C.ALGO_NVLS] if gbuf.mc_ptr and pbuf.mc_ptr else [])
+    hyper = make_hyper(dev, lr=1e-2, grad_scale=1.0 / world)
+    rng = random.Random(1234 + 17 * rank)            # different delays on every rank
+    lens = [8 * world * k for k in (1, 33, 1027, 8209)]
+    bad = 0
+    dist.barrier()
+    for it in range(iters):
+        n = lens[it % len(lens)]
+        algo = algos[it % len(algos)]
+        g_arena[:n].fill_(float((rank + 1) * (it + 1)))
+        time.sleep(rng.random() * 0.003)
+        torch.cuda._sleep(int(rng.random() * 3e6))    # up to ~1.5 ms of stream delay
+        comm.fused(ctx, algo=algo, opt=0, grad_dtype=torch.float32, param_dtype=torch.float32, off=0,
+                   length=n, master=None, s1=None, s2=None, state_off=0, hyper=hyper, zero_grads=True)
+        want = (it + 1) * (world + 1) / 2.0           # mean over ranks of (rank+1)*(it+1)
+        got = p_arena[:n]
+        bad += int((got - want).abs().max().item() > 1e-4 * want) + int(g_arena[:n].abs().max().item() != 0.0)
+    torch.cuda.synchronize()
+    t = torch.tensor([bad], device=dev, dtype=torch.float32)
+    dist.all_reduce(t)
+    ok = t.item() == 0
+    results.append({"check": f"stress/skewed_arrival/{iters}_calls", "bad_calls": int(t.item()), "ok": ok})
+    return ok
+
+
 def time_fn(fn, iters, dev):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
@@ -196,6 +233,7 @@ def main():
         out["error"] = "p2p backend unavailable"
     else:
         ok = check(comm, dev, world, rank, out["checks"])
+        ok = stress(comm, dev, world, rank, out["checks"]) and ok
         out["checks_ok"] = bool(ok)
         for c in out["checks"]:
             log(json.dumps(c))
