@@ -33,6 +33,10 @@ def _k():
         lib.cb2_bn_scratch_floats.restype = i
         lib.cb2_bn_scratch_floats.argtypes = [i]
         lib.cb2_bn_forward.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, f, f, i, i, vp]
+        lib.cb2_bn_forward_mask.restype = i
+        lib.cb2_bn_forward_mask.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, f, f, i, i, vp]
+        lib.cb2_bn_backward3.restype = i
+        lib.cb2_bn_backward3.argtypes = [vp, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp]
         lib.cb2_bn_backward2.restype = i
         lib.cb2_bn_backward2.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp]
         lib.cb2_bn_backward.restype = i
@@ -59,6 +63,9 @@ def _stream():
 # memset at the start of every training step (DPEngine.begin_step): replaces two torch.zeros
 # launches per BatchNormalization layer per step (106 for ResNet-50).
 _pool = {}
+
+
+_SIGN_BITS = os.environ.get("TFC_BN_SIGN_BITS", "1") != "0"
 
 
 def reset_scratch(device) -> None:
@@ -111,18 +118,25 @@ class _BNFn(torch.autograd.Function):
         if sums is None:
             sums = _scratch(_k().cb2_bn_scratch_floats(C), x.device)
         save = torch.empty(2 * C, dtype=torch.float32, device=x.device)
-        rc = _k().cb2_bn_forward(x.data_ptr(), None if residual is None else residual.data_ptr(),
-                                 y.data_ptr(), sums.data_ptr(), gamma.data_ptr(), beta.data_ptr(),
-                                 run_mean.data_ptr(), run_var.data_ptr(), save.data_ptr(),
-                                 save[C:].data_ptr(),
-                                 None if mean_bias is None else mean_bias.data_ptr(), M, C,
-                                 float(eps), float(momentum), int(relu), mode, _stream())
+        # shortcut + ReLU: the mask cannot be recomputed from x alone; the forward pass leaves one
+        # sign bit per element so that backward does not have to re-read the whole output
+        mask = torch.empty(M * C // 8, dtype=torch.uint8, device=x.device) \
+            if (relu and residual is not None and _SIGN_BITS) else None
+        rc = _k().cb2_bn_forward_mask(x.data_ptr(), None if residual is None else residual.data_ptr(),
+                                      y.data_ptr(), sums.data_ptr(), gamma.data_ptr(), beta.data_ptr(),
+                                      run_mean.data_ptr(), run_var.data_ptr(), save.data_ptr(),
+                                      save[C:].data_ptr(),
+                                      None if mean_bias is None else mean_bias.data_ptr(),
+                                      None if mask is None else mask.data_ptr(), M, C,
+                                      float(eps), float(momentum), int(relu), mode, _stream())
         ctx.params = (gamma, beta)
         _lib.check(rc, "bn_forward")
         _launches += 3 - mode
         # the ReLU mask is recomputed from x unless a shortcut was added before the ReLU
-        ctx.save_for_backward(x, y if (relu and residual is not None) else None, gamma, save, beta)
+        keep = mask if mask is not None else (y if (relu and residual is not None) else None)
+        ctx.save_for_backward(x, keep, gamma, save, beta)
         ctx.relu, ctx.has_res, ctx.M, ctx.C = relu, residual is not None, M, C
+        ctx.y_is_mask = mask is not None
         return y
 
     @staticmethod
@@ -149,8 +163,8 @@ class _BNFn(torch.autograd.Function):
         if dy2 is not None and not (dy2.shape == dy.shape and dy2.dtype == dy.dtype and _is_nhwc(dy2)):
             dy = dy + dy2                              # odd layout: fall back to an explicit add
             dy2 = None
-        rc = _k().cb2_bn_backward2(dy.data_ptr(), None if dy2 is None else dy2.data_ptr(),
-                                   None if y is None else y.data_ptr(), x.data_ptr(),
+        rc = _k().cb2_bn_backward3(dy.data_ptr(), None if dy2 is None else dy2.data_ptr(),
+                                   None if y is None else y.data_ptr(), int(ctx.y_is_mask), x.data_ptr(),
                                    save.data_ptr(), save[C:].data_ptr(), gamma.data_ptr(),
                                    beta.data_ptr(), sums.data_ptr(), dbeta_ptr, dgamma_ptr,
                                    dx.data_ptr(),

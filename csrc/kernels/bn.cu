@@ -146,6 +146,15 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ sums, i
   bn_block_reduce_to_global(s, q, m, C, sums);
 }
 
+// One bit per channel: output > 0.  Saved by the forward pass of a BN + shortcut + ReLU so that the
+// backward kernels read one byte per 8 channels instead of the 16 bytes of the saved output.
+__device__ __forceinline__ uint8_t bn_sign_bits(const Vec8& v) {
+  uint32_t b = 0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) b |= (v.v[j] > 0.f ? 1u : 0u) << j;
+  return static_cast<uint8_t>(b);
+}
+
 __device__ __forceinline__ Vec8 bn_affine(const Vec8& v, const float (&sc)[8], const float (&sh)[8]) {
   Vec8 o;
 #pragma unroll
@@ -162,8 +171,8 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
                 const float* __restrict__ gamma, const float* __restrict__ beta,
                 float* __restrict__ run_mean, float* __restrict__ run_var,
                 float* __restrict__ save_mean, float* __restrict__ save_invstd,
-                const float* __restrict__ mean_bias, int M, int C, float eps, float momentum,
-                int relu, int training) {
+                const float* __restrict__ mean_bias, uint8_t* __restrict__ mask_out, int M, int C,
+                float eps, float momentum, int relu, int training) {
   const BnMap m = bn_map(C);
   float sc[8], sh[8], tot[8], totsq[8];
   const float invM = 1.f / static_cast<float>(M);
@@ -210,6 +219,10 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
     for (int j = 0; j < 8; ++j) { v0.v[j] = fmaxf(v0.v[j], lo); v1.v[j] = fmaxf(v1.v[j], lo); }
     *reinterpret_cast<uint4*>(y + i0) = pack8_bf16(v0);
     *reinterpret_cast<uint4*>(y + i1) = pack8_bf16(v1);
+    if (mask_out) {
+      mask_out[static_cast<size_t>(row) * (C >> 3) + (m.c8 >> 3)] = bn_sign_bits(v0);
+      mask_out[static_cast<size_t>(row + stride) * (C >> 3) + (m.c8 >> 3)] = bn_sign_bits(v1);
+    }
   }
   for (; row < M; row += stride) {
     const size_t idx = static_cast<size_t>(row) * C + m.c8;
@@ -222,6 +235,7 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
 #pragma unroll
     for (int j = 0; j < 8; ++j) v.v[j] = fmaxf(v.v[j], lo);
     *reinterpret_cast<uint4*>(y + idx) = pack8_bf16(v);
+    if (mask_out) mask_out[static_cast<size_t>(row) * (C >> 3) + (m.c8 >> 3)] = bn_sign_bits(v);
   }
 }
 
@@ -236,7 +250,7 @@ __device__ __forceinline__ void bn_add8(Vec8& g, const uint4& w) {
 // dz = dy * (y > 0) when a ReLU follows the BN.  Without a saved output the mask is recomputed
 // from x (y > 0 <=> x*sc + sh > 0), which saves reading y - one of three activation-sized reads -
 // for every BN+ReLU without shortcut.
-template <int MODE /*0 none, 1 from y, 2 from x*/>
+template <int MODE /*0 none, 1 from y, 2 from x, 3 from the sign bits saved by the forward pass*/>
 __device__ __forceinline__ void bn_mask(Vec8& g, const Vec8& xv, const uint4& wy, const float (&sc)[8],
                                         const float (&sh)[8]) {
   if (MODE == 1) {
@@ -246,6 +260,9 @@ __device__ __forceinline__ void bn_mask(Vec8& g, const Vec8& xv, const uint4& wy
   } else if (MODE == 2) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) g.v[j] = fmaf(xv.v[j], sc[j], sh[j]) > 0.f ? g.v[j] : 0.f;
+  } else if (MODE == 3) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g.v[j] = ((wy.x >> j) & 1u) ? g.v[j] : 0.f;
   }
 }
 
@@ -279,6 +296,11 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     const uint4 wx0 = ld_stream_v4(x + i0), wx1 = ld_stream_v4(x + i1);
     uint4 wy0 = make_uint4(0, 0, 0, 0), wy1 = wy0, wh0 = wy0, wh1 = wy0;
     if (MODE == 1) { wy0 = ld_stream_v4(y + i0); wy1 = ld_stream_v4(y + i1); }
+    if (MODE == 3) {            // `y` carries the saved sign bits: one byte per 8 channels
+      const uint8_t* mk = reinterpret_cast<const uint8_t*>(y);
+      wy0.x = mk[static_cast<size_t>(row) * (C >> 3) + (m.c8 >> 3)];
+      wy1.x = mk[static_cast<size_t>(row + stride) * (C >> 3) + (m.c8 >> 3)];
+    }
     if (DY2) { wh0 = ld_stream_v4(dy2 + i0); wh1 = ld_stream_v4(dy2 + i1); }
     Vec8 g0 = unpack8_bf16(wg0), g1 = unpack8_bf16(wg1);
     if (DY2) { bn_add8(g0, wh0); bn_add8(g1, wh1); }
@@ -299,6 +321,7 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     const Vec8 xv = unpack8_bf16(ld_stream_v4(x + idx));
     uint4 wy = make_uint4(0, 0, 0, 0);
     if (MODE == 1) wy = ld_stream_v4(y + idx);
+    if (MODE == 3) wy.x = reinterpret_cast<const uint8_t*>(y)[static_cast<size_t>(row) * (C >> 3) + (m.c8 >> 3)];
     bn_mask<MODE>(g, xv, wy, sc, sh);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -351,6 +374,11 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
     const uint4 wx0 = ld_stream_v4(x + i0), wx1 = ld_stream_v4(x + i1);
     uint4 wy0 = make_uint4(0, 0, 0, 0), wy1 = wy0, wh0 = wy0, wh1 = wy0;
     if (MODE == 1) { wy0 = ld_stream_v4(y + i0); wy1 = ld_stream_v4(y + i1); }
+    if (MODE == 3) {            // `y` carries the saved sign bits: one byte per 8 channels
+      const uint8_t* mk = reinterpret_cast<const uint8_t*>(y);
+      wy0.x = mk[static_cast<size_t>(row) * (C >> 3) + (m.c8 >> 3)];
+      wy1.x = mk[static_cast<size_t>(row + stride) * (C >> 3) + (m.c8 >> 3)];
+    }
     if (DY2) { wh0 = ld_stream_v4(dy2 + i0); wh1 = ld_stream_v4(dy2 + i1); }
     Vec8 g0 = unpack8_bf16(wg0), g1 = unpack8_bf16(wg1);
     if (DY2) { bn_add8(g0, wh0); bn_add8(g1, wh1); }
@@ -377,6 +405,7 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
     const Vec8 xv = unpack8_bf16(ld_stream_v4(x + idx));
     uint4 wy = make_uint4(0, 0, 0, 0);
     if (MODE == 1) wy = ld_stream_v4(y + idx);
+    if (MODE == 3) wy.x = reinterpret_cast<const uint8_t*>(y)[static_cast<size_t>(row) * (C >> 3) + (m.c8 >> 3)];
     bn_mask<MODE>(g, xv, wy, sc, sh);
     if (dres) *reinterpret_cast<uint4*>(dres + idx) = pack8_bf16(g);
     Vec8 o;
@@ -433,12 +462,28 @@ extern "C" int cb2_bn_supported(int C) { return bn_shape_ok(C) ? 1 : 0; }
 
 extern "C" int cb2_bn_scratch_floats(int C) { return kBnCopies * 2 * C; }
 
+extern "C" int cb2_bn_forward_mask(const void* x, const void* residual, void* y, float* sums,
+                                   const float* gamma, const float* beta, float* run_mean,
+                                   float* run_var, float* save_mean, float* save_invstd,
+                                   const float* mean_bias, void* mask_out, int M, int C, float eps,
+                                   float momentum, int relu, int training, void* stream);
+
 extern "C" int cb2_bn_forward(const void* x, const void* residual, void* y,
                               float* sums /*[cb2_bn_scratch_floats(C)], zeroed*/,
                               const float* gamma, const float* beta, float* run_mean, float* run_var,
                               float* save_mean, float* save_invstd, const float* mean_bias, int M,
                               int C, float eps, float momentum, int relu, int training,
                               void* stream) {
+  return cb2_bn_forward_mask(x, residual, y, sums, gamma, beta, run_mean, run_var, save_mean,
+                             save_invstd, mean_bias, nullptr, M, C, eps, momentum, relu, training, stream);
+}
+
+extern "C" int cb2_bn_forward_mask(const void* x, const void* residual, void* y, float* sums,
+                                   const float* gamma, const float* beta, float* run_mean,
+                                   float* run_var, float* save_mean, float* save_invstd,
+                                   const float* mean_bias, void* mask_out /*nullable: [M*C/8] sign bits of y*/,
+                                   int M, int C, float eps, float momentum, int relu, int training,
+                                   void* stream) {
   int rc = bn_check(M, C, "bn_forward");
   if (rc) return rc;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
@@ -448,7 +493,7 @@ extern "C" int cb2_bn_forward(const void* x, const void* residual, void* y,
   bn_apply_kernel<<<grid, kBnThreads, 0, st>>>(
       reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<const __nv_bfloat16*>(residual),
       reinterpret_cast<__nv_bfloat16*>(y), sums, gamma, beta, run_mean, run_var, save_mean,
-      save_invstd, mean_bias, M, C, eps, momentum, relu, training);
+      save_invstd, mean_bias, reinterpret_cast<uint8_t*>(mask_out), M, C, eps, momentum, relu, training);
   return check_cuda(cudaGetLastError(), "bn_forward launch");
 }
 
@@ -466,7 +511,23 @@ extern "C" int cb2_bn_backward(const void* dy, const void* y, const void* x, con
                           dx, dres, M, C, relu, stream);
 }
 
+extern "C" int cb2_bn_backward3(const void* dy, const void* dy2, const void* y, int y_is_mask,
+                                const void* x, const float* save_mean, const float* save_invstd,
+                                const float* gamma, const float* beta, float* sums, float* dbeta,
+                                float* dgamma, void* dx, void* dres, int M, int C, int relu,
+                                void* stream);
+
 extern "C" int cb2_bn_backward2(const void* dy, const void* dy2 /*nullable: dy += dy2*/, const void* y,
+                                const void* x, const float* save_mean, const float* save_invstd,
+                                const float* gamma, const float* beta, float* sums, float* dbeta,
+                                float* dgamma, void* dx, void* dres, int M, int C, int relu,
+                                void* stream) {
+  return cb2_bn_backward3(dy, dy2, y, 0, x, save_mean, save_invstd, gamma, beta, sums, dbeta, dgamma, dx,
+                          dres, M, C, relu, stream);
+}
+
+extern "C" int cb2_bn_backward3(const void* dy, const void* dy2 /*nullable*/, const void* y /*nullable*/,
+                                int y_is_mask /*y = the sign bits cb2_bn_forward_mask saved*/,
                                 const void* x, const float* save_mean, const float* save_invstd,
                                 const float* gamma, const float* beta, float* sums, float* dbeta,
                                 float* dgamma, void* dx, void* dres, int M, int C, int relu,
@@ -481,7 +542,7 @@ extern "C" int cb2_bn_backward2(const void* dy, const void* dy2 /*nullable: dy +
   const __nv_bfloat16* xp = reinterpret_cast<const __nv_bfloat16*>(x);
   __nv_bfloat16* dxp = reinterpret_cast<__nv_bfloat16*>(dx);
   __nv_bfloat16* drp = reinterpret_cast<__nv_bfloat16*>(dres);
-  const int mode = !relu ? 0 : (y != nullptr ? 1 : 2);
+  const int mode = !relu ? 0 : (y == nullptr ? 2 : (y_is_mask ? 3 : 1));
 #define CB2_BN_BWD(MODE, DY2)                                                                      \
   bn_bwd_reduce_kernel<MODE, DY2><<<grid, kBnThreads, 0, st>>>(dyp, dy2p, yp, xp, save_mean,           \
                                                                save_invstd, gamma, beta, sums, M, C);  \
@@ -491,11 +552,13 @@ extern "C" int cb2_bn_backward2(const void* dy, const void* dy2 /*nullable: dy +
   if (dy2p == nullptr) {
     if (mode == 0) { CB2_BN_BWD(0, false) }
     else if (mode == 1) { CB2_BN_BWD(1, false) }
-    else { CB2_BN_BWD(2, false) }
+    else if (mode == 2) { CB2_BN_BWD(2, false) }
+    else { CB2_BN_BWD(3, false) }
   } else {
     if (mode == 0) { CB2_BN_BWD(0, true) }
     else if (mode == 1) { CB2_BN_BWD(1, true) }
-    else { CB2_BN_BWD(2, true) }
+    else if (mode == 2) { CB2_BN_BWD(2, true) }
+    else { CB2_BN_BWD(3, true) }
   }
 #undef CB2_BN_BWD
   return check_cuda(cudaGetLastError(), "bn_backward launch");
@@ -590,6 +653,6 @@ extern "C" int cb2_bn_forward_static(const void* x, const void* residual, void* 
   bn_apply_kernel<<<grid, kBnThreads, 0, st>>>(
       reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<const __nv_bfloat16*>(residual),
       reinterpret_cast<__nv_bfloat16*>(y), scratch, gamma, beta, run_mean, run_var, save_mean,
-      save_invstd, mean_bias, M, C, eps, momentum, relu, training);
+      save_invstd, mean_bias, nullptr, M, C, eps, momentum, relu, training);
   return check_cuda(cudaGetLastError(), "bn_forward_static launch");
 }

@@ -145,6 +145,18 @@ int cb2_bn_backward2(const void* dy, const void* dy2, const void* y, const void*
                      const float* save_mean, const float* save_invstd, const float* gamma,
                      const float* beta, float* sums, float* dbeta, float* dgamma, void* dx, void* dres,
                      int M, int C, int relu, void* stream);
+/* The shortcut variant (BN + residual + ReLU) without re-reading the output in backward:
+ * cb2_bn_forward_mask also writes mask_out[M * C / 8], one bit per element (output > 0), and
+ * cb2_bn_backward3 with y_is_mask != 0 takes those bytes in place of y - 1/16 of the bytes in each
+ * of the two backward passes. */
+int cb2_bn_forward_mask(const void* x, const void* residual, void* y, float* sums, const float* gamma,
+                        const float* beta, float* run_mean, float* run_var, float* save_mean,
+                        float* save_invstd, const float* mean_bias, void* mask_out, int M, int C,
+                        float eps, float momentum, int relu, int training, void* stream);
+int cb2_bn_backward3(const void* dy, const void* dy2, const void* y, int y_is_mask, const void* x,
+                     const float* save_mean, const float* save_invstd, const float* gamma,
+                     const float* beta, float* sums, float* dbeta, float* dgamma, void* dx, void* dres,
+                     int M, int C, int relu, void* stream);
 
 /* cb2_bn_forward for callers that cannot allocate device memory.  (No counterpart in the
  * reference: it has no kernels and no C ABI; this entry exists for embedders of this library.)
