@@ -5,8 +5,15 @@
 //   * accumulators: fp32 in TMEM, double buffered (2 x BN columns) so the epilogue of tile i
 //     overlaps the main loop of tile i+1,
 //   * persistent: one CTA per SM, static round-robin tile schedule,
-//   * warp roles: warp0 = TMA producer, warp1 = TMEM owner + MMA issuer, warps2-5 = epilogue
-//     (tcgen05.ld -> bias / ReLU / ReLU-mask / row-softmax -> bf16|fp32 store or accumulate).
+//   * warp roles: warp0 = TMA producer, warp1 = TMEM owner + MMA issuer, warps2-5 = epilogue,
+//   * epilogue: tcgen05.ld (next chunk prefetched) -> bias / ReLU -> 128B-swizzled smem tile ->
+//     TMA store, or TMA reduce-add for ACCUM / split-K; optional per-column sum / sum of squares
+//     (batch-norm statistics); a per-row path with direct stores remains for the row-softmax and
+//     ReLU-mask epilogues,
+//   * split-K: work item = (m tile, n tile, K slice); slices meet in an fp32 C through reduce-adds,
+//     optionally rounded into a bf16 matrix by the last-arriving warp (cb2_gemm_splitk_bf16),
+//   * convolutions as implicit GEMMs: the producer can address NHWC activations in place through
+//     3-D / 4-D tensor maps (cb2_conv_stem_forward / _wgrad, cb2_conv_wgrad at the end of the file).
 //
 // Both operands may be K-major (reduction dim contiguous) or MN-major, which covers the three
 // GEMMs of a Dense layer without any transpose kernel:
