@@ -21,6 +21,8 @@ def main():
     ap.add_argument("--epochs", type=int, default=3)
     ap.add_argument("--batch", type=int, default=128, help="global batch")
     ap.add_argument("--samples", type=int, default=60000)
+    ap.add_argument("--steps-per-execution", type=int, default=1,
+                    help="Keras compile(steps_per_execution=K): K steps per CUDA graph")
     args = ap.parse_args()
     if args.cpu:
         os.environ["CUDA_VISIBLE_DEVICES"] = ""
@@ -40,7 +42,7 @@ def main():
                               keras.layers.Dropout(0.2),
                               keras.layers.Dense(10, activation="softmax")])
     model.compile(loss="sparse_categorical_crossentropy", optimizer=keras.optimizers.Adam(),
-                  metrics=["accuracy"])
+                  metrics=["accuracy"], steps_per_execution=args.steps_per_execution)
     if strategy.device.type == "cuda":
         x_t, y_t = torch.from_numpy(x).pin_memory(), torch.from_numpy(y).pin_memory()
     else:
@@ -58,11 +60,13 @@ def main():
     steps = args.epochs * -(-args.samples // args.batch)
     if strategy.replica_id == 0:
         print(json.dumps({"bench": "mnist_mlp", "device": strategy.device.type, "n_replicas": world,
-                          "global_batch": args.batch, "steps_per_s": steps / dt,
+                          "global_batch": args.batch, "steps_per_execution": args.steps_per_execution,
+                          "steps_per_s": steps / dt,
                           "s_per_epoch": dt / args.epochs, "samples_per_s": steps * args.batch / dt,
                           "final_loss": h.history["loss"][-1],
                           "backend": model._engine.comm.backend,
-                          "cuda_graph": bool(model._graph and model._graph.get("graph") is not None)}))
+                          "cuda_graph": bool((model._graph and model._graph.get("graph") is not None) or
+                                             (model._graph_k and model._graph_k.get("graph") is not None))}))
 
 
 if __name__ == "__main__":

@@ -78,6 +78,33 @@ def _heartbeat():
             pass
 
 
+def _grouped(batches, k):
+    """Lists of ``k`` consecutive batches with identical shapes (``steps_per_execution``); whatever
+    does not fill a group - the tail of an epoch, a short last batch - comes out one by one."""
+    if k <= 1:
+        for b in batches:
+            yield [b]
+        return
+    buf = []
+    for b in batches:
+        if b[1] is None:                      # unlabelled: never grouped
+            for old in buf:
+                yield [old]
+            buf = []
+            yield [b]
+            continue
+        if buf and (b[0].shape != buf[0][0].shape or b[3] != buf[0][3]):
+            for old in buf:
+                yield [old]
+            buf = []
+        buf.append(b)
+        if len(buf) == k:
+            yield buf
+            buf = []
+    for old in buf:
+        yield [old]
+
+
 class _Forked(list):
     """The two handles of a forked batch-norm output, handed out to its two consumers."""
 
@@ -274,6 +301,7 @@ class Model(nn.Module):
         self._engine = None
         self._strategy = None
         self._graph = None
+        self._graph_k = None          # graph of steps_per_execution steps
         self._graph_ok = True
         self.history = None
         self._nodes = None
@@ -454,7 +482,12 @@ class Model(nn.Module):
         return t
 
     # -- compile ------------------------------------------------------------------------------
-    def compile(self, optimizer="rmsprop", loss=None, metrics=None, run_eagerly=False, **kwargs):
+    def compile(self, optimizer="rmsprop", loss=None, metrics=None, run_eagerly=False,
+                steps_per_execution=1, **kwargs):
+        # Keras: "the number of batches to run during each call".  Here: that many training steps
+        # are captured in ONE CUDA graph (inputs staged in a [K, batch, ...] buffer), which takes
+        # the Python cost of a step (~0.25 ms) out of launch-bound models such as the README MLP.
+        self.steps_per_execution = max(1, int(steps_per_execution or 1))
         self.optimizer = opt_mod.get(optimizer)
         self.loss = losses_mod.get(loss) if loss is not None else None
         self._metrics = [metrics_mod.get(m, self.loss) for m in (metrics or [])]
@@ -591,6 +624,53 @@ class Model(nn.Module):
         self._graph_replays = getattr(self, "_graph_replays", 0) + 1
         return g["out"]
 
+    def _run_steps(self, xs, ys, global_batch, k):
+        """``k`` training steps on the stacked batches ``xs[k, ...]`` / ``ys[k, ...]`` as one CUDA
+        graph (``steps_per_execution``); returns the metric scalars summed over the k steps."""
+        _heartbeat()
+        n_aux = self._aux_len()
+        if not self._graph_enabled():
+            total = None
+            for i in range(k):
+                red = self._train_step(self._to_internal(xs[i]), ys[i], global_batch)[:n_aux].clone()
+                total = red if total is None else total + red
+            return total
+        g = self._graph_k
+        key = (tuple(xs.shape), xs.dtype, tuple(ys.shape), ys.dtype, int(global_batch), k)
+        if g is None or g["key"] != key:
+            self._graph_k = g = {"key": key, "warm": 0, "graph": None}
+        if g["graph"] is None:
+            g["warm"] += 1
+            if g["warm"] <= 1 and (self._graph is None or self._graph.get("graph") is None):
+                total = None                      # one eager pass (lazy builds, allocator warm-up)
+                for i in range(k):
+                    red = self._train_step(self._to_internal(xs[i]), ys[i], global_batch)[:n_aux].clone()
+                    total = red if total is None else total + red
+                return total
+            g["x"], g["y"] = xs.clone(), ys.clone()
+            g["sum"] = torch.zeros(n_aux, dtype=torch.float32, device=self.device)
+            torch.cuda.synchronize(self.device)
+            graph = torch.cuda.CUDAGraph()
+            try:
+                with torch.cuda.graph(graph, capture_error_mode="thread_local"):
+                    g["sum"].zero_()
+                    for i in range(k):
+                        red = self._train_step(self._to_internal(g["x"][i]), g["y"][i], global_batch)
+                        g["sum"] += red[:n_aux]
+            except Exception as e:
+                import warnings
+                warnings.warn(f"cloud_b200: CUDA graph capture of {k} steps failed ({e}); running eagerly")
+                self._graph_ok = False
+                self._graph_k = None
+                torch.cuda.synchronize(self.device)
+                return self._run_steps(xs, ys, global_batch, k)
+            g["graph"] = graph
+        g["x"].copy_(xs, non_blocking=True)
+        g["y"].copy_(ys, non_blocking=True)
+        g["graph"].replay()
+        self._graph_replays = getattr(self, "_graph_replays", 0) + 1
+        return g["sum"]
+
     # -- fit ----------------------------------------------------------------------------------
     def _make_source(self, x, y, batch_size, shuffle, steps, training=True):
         st = self.distribute_strategy
@@ -645,21 +725,30 @@ class Model(nn.Module):
             # where the host thread spends the epoch (bench.py reports it next to the e2e number)
             prof = self._fit_profile = {"wait_data_s": 0.0, "launch_s": 0.0, "read_back_s": 0.0, "steps": 0}
             t_mark = epoch_t0
-            for step, (xd, yd, ev, n_global) in enumerate(pf):
+            for group in _grouped(pf, getattr(self, "steps_per_execution", 1)):
                 now = time.perf_counter()
                 prof["wait_data_s"] += now - t_mark
+                step += len(group)
                 if batch_logs:
                     cbl.call("on_train_batch_begin", step, {})
-                if ev is not None:
-                    cur = torch.cuda.current_stream(self.device)
-                    cur.wait_event(ev)
-                    xd.record_stream(cur)          # allocated on the loader's copy stream
-                    if yd is not None:
-                        yd.record_stream(cur)
-                xi = self._to_internal(xd)
-                yi = yd.to(self.device) if yd is not None else None
-                red = self._run_step(xi, yi, n_global)
-                self.optimizer.iterations += 1
+                cur = torch.cuda.current_stream(self.device) if self.device.type == "cuda" else None
+                for (xd, yd, ev, _ng) in group:
+                    if ev is not None:
+                        cur.wait_event(ev)
+                        xd.record_stream(cur)          # allocated on the loader's copy stream
+                        if yd is not None:
+                            yd.record_stream(cur)
+                n_global = group[0][3]
+                if len(group) == 1:
+                    xd, yd = group[0][0], group[0][1]
+                    xi = self._to_internal(xd)
+                    yi = yd.to(self.device) if yd is not None else None
+                    red = self._run_step(xi, yi, n_global)
+                else:
+                    xs = torch.stack([b[0].to(self.device) for b in group])
+                    ys = torch.stack([b[1].to(self.device) for b in group])
+                    red = self._run_steps(xs, ys, n_global, len(group))
+                self.optimizer.iterations += len(group)
                 if self.optimizer._schedule is not None:
                     eng.set_lr(self.optimizer.current_lr())
                 acc += red[:n_aux]

@@ -76,3 +76,27 @@ def test_resnet_stem_training_step_matches_torch():
         assert 0.8 < np.linalg.norm(got) / (np.linalg.norm(want) + 1e-12) < 1.25, name
     # the absorbed conv bias gets a zero gradient, exactly
     assert np.array_equal(w0[1], w1[1])
+
+
+def test_steps_per_execution_graph_matches_single_step_training():
+    """K steps captured in one CUDA graph give the weights K single-step replays give."""
+    import cloud_b200 as tfc
+    keras = tfc.keras
+    tfc.distribute.experimental_set_strategy(tfc.distribute.OneDeviceStrategy("cuda:0"))
+    rng = np.random.RandomState(0)
+    x = rng.rand(24 * 64, 48).astype("float32")
+    y = rng.randint(0, 5, 24 * 64)
+    out = {}
+    for spe in (1, 6):
+        torch.manual_seed(0)
+        m = keras.Sequential([keras.layers.Dense(64, activation="relu", input_shape=(48,)),
+                              keras.layers.Dense(5, activation="softmax")])
+        m.compile(optimizer=keras.optimizers.Adam(1e-3), loss="sparse_categorical_crossentropy",
+                  metrics=["accuracy"], steps_per_execution=spe)
+        h = m.fit(x, y, batch_size=64, epochs=3, shuffle=False, verbose=0)
+        out[spe] = (m.get_weights(), h.history["loss"])
+        if spe > 1:
+            assert m._graph_k is not None and m._graph_k.get("graph") is not None
+    for a, b in zip(out[1][0], out[6][0]):
+        assert np.allclose(a, b, atol=2e-2, rtol=2e-2)
+    assert np.allclose(out[1][1], out[6][1], rtol=2e-2)

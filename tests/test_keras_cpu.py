@@ -183,3 +183,27 @@ def test_image_normalization_defers_only_to_a_stem_convolution():
     assert not m2.get_layer("n2").defer_to_stem
     img = np.random.randint(0, 256, (2, 32, 32, 3)).astype("uint8")
     assert m.predict(img).shape == (2, 64) and m2.predict(img).shape == (2, 8)    # CPU: never deferred
+
+
+def test_steps_per_execution_groups_steps_without_changing_the_training():
+    """compile(steps_per_execution=K): K steps per call (one CUDA graph on a GPU); same result."""
+    x, y = _blobs(10 * 32 + 7)          # 11 batches of 32, the last one short
+    results = {}
+    for spe in (1, 4):
+        torch.manual_seed(0)
+        m = keras.Sequential([L.Dense(16, activation="relu", input_shape=(20,)),
+                              L.Dense(4, activation="softmax")])
+        m.compile(optimizer=keras.optimizers.SGD(0.05), loss="sparse_categorical_crossentropy",
+                  metrics=["accuracy"], steps_per_execution=spe)
+        ends = []
+        h = m.fit(x, y, batch_size=32, epochs=2, shuffle=False, verbose=0,
+                  callbacks=[keras.callbacks.LambdaCallback(on_batch_end=lambda b, logs: ends.append(b))])
+        results[spe] = (m.get_weights(), h.history, ends)
+        assert m.optimizer.iterations == 22
+    w1, h1, e1 = results[1]
+    w4, h4, e4 = results[4]
+    for a, b in zip(w1, w4):
+        assert np.allclose(a, b, atol=1e-6)
+    assert np.allclose(h1["loss"], h4["loss"], rtol=1e-5) and np.allclose(h1["accuracy"], h4["accuracy"])
+    assert e1[:11] == list(range(11))
+    assert e4[:5] == [3, 7, 8, 9, 10]      # two full groups, then the leftovers one by one
