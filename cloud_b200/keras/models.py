@@ -87,7 +87,7 @@ def _grouped(batches, k):
         return
     buf = []
     for b in batches:
-        if b[1] is None:                      # unlabelled: never grouped
+        if b[1] is None or getattr(b[3], "k", 1) > 1:     # unlabelled / already stacked by the source
             for old in buf:
                 yield [old]
             buf = []
@@ -112,10 +112,19 @@ class _Forked(list):
 _FORK_BN = os.environ.get("TFC_BN_FORK", "1") != "0"
 
 
-class _ArraySource:
-    """numpy/torch arrays -> per-replica batches of a global batch (Keras: batch_size is global)."""
+class _NG(int):
+    """Global batch size of a source item that carries ``k`` stacked batches ([k, per, ...])."""
+    k = 1
 
-    def __init__(self, x, y, batch_size, shuffle, world, rank, seed=0, steps=None, drop_last=False):
+
+class _ArraySource:
+    """numpy/torch arrays -> per-replica batches of a global batch (Keras: batch_size is global).
+    With ``group=K`` (``steps_per_execution``) K consecutive full batches travel as one
+    ``[K, per_replica, ...]`` item - one host slice/gather and one H2D copy per execution."""
+
+    def __init__(self, x, y, batch_size, shuffle, world, rank, seed=0, steps=None, drop_last=False,
+                 group=1):
+        self.group = max(1, int(group))
         self.x = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(_np(x)))
         self.y = None
         if y is not None:
@@ -142,7 +151,25 @@ class _ArraySource:
         else:
             perm = None
         self.epoch += 1
-        for s in range(n_steps):
+        s = 0
+        K = self.group
+        per_full = -(-self.batch // self.world)
+        while K > 1 and self.y is not None and s + K <= n_steps and (s + K) * self.batch <= self.n \
+                and per_full * self.world == self.batch:
+            # K full global batches: this replica's rows of each, stacked
+            if perm is None and self.world == 1:
+                xb = self.x[s * self.batch:(s + K) * self.batch]
+                yb = self.y[s * self.batch:(s + K) * self.batch]
+            else:
+                base = torch.arange(K).repeat_interleave(per_full) * self.batch + \
+                    torch.arange(per_full).repeat(K) + self.rank * per_full + s * self.batch
+                idx = perm[base] if perm is not None else base
+                xb, yb = self.x.index_select(0, idx), self.y.index_select(0, idx)
+            ng = _NG(self.batch)
+            ng.k = K
+            yield xb.reshape(K, per_full, *self.x.shape[1:]), yb.reshape(K, per_full, *self.y.shape[1:]), ng
+            s += K
+        for s in range(s, n_steps):
             lo = s * self.batch
             hi = min(self.n, lo + self.batch)
             per = -(-(hi - lo) // self.world)
@@ -684,7 +711,8 @@ class Model(nn.Module):
         if isinstance(x, (list, tuple)) and not isinstance(x, np.ndarray):
             x = np.asarray(x)
         bs = batch_size or 32
-        return _ArraySource(x, y, bs, shuffle and training, world, rank, steps=steps)
+        return _ArraySource(x, y, bs, shuffle and training, world, rank, steps=steps,
+                            group=getattr(self, "steps_per_execution", 1) if training else 1)
 
     def fit(self, x=None, y=None, batch_size=None, epochs=1, verbose=1, callbacks=None,
             validation_split=0.0, validation_data=None, shuffle=True, initial_epoch=0,
@@ -739,7 +767,12 @@ class Model(nn.Module):
                         if yd is not None:
                             yd.record_stream(cur)
                 n_global = group[0][3]
-                if len(group) == 1:
+                pre_k = getattr(n_global, "k", 1)
+                if pre_k > 1:                       # the source already stacked k batches
+                    step += pre_k - 1
+                    red = self._run_steps(group[0][0], group[0][1].to(self.device), int(n_global), pre_k)
+                    self.optimizer.iterations += pre_k - 1
+                elif len(group) == 1:
                     xd, yd = group[0][0], group[0][1]
                     xi = self._to_internal(xd)
                     yi = yd.to(self.device) if yd is not None else None

@@ -207,3 +207,25 @@ def test_steps_per_execution_groups_steps_without_changing_the_training():
     assert np.allclose(h1["loss"], h4["loss"], rtol=1e-5) and np.allclose(h1["accuracy"], h4["accuracy"])
     assert e1[:11] == list(range(11))
     assert e4[:5] == [3, 7, 8, 9, 10]      # two full groups, then the leftovers one by one
+
+
+@pytest.mark.parametrize("shuffle", [False, True])
+def test_array_source_groups_partition_each_global_batch_across_replicas(shuffle):
+    from cloud_b200.keras.models import _ArraySource
+    n, B, K, world = 100, 8, 3, 2
+    x = torch.arange(n).float().view(n, 1)
+    y = torch.arange(n)
+    plain = list(_ArraySource(x, y, B, shuffle, 1, 0, seed=5))                 # the global batches
+    per_rank = [list(_ArraySource(x, y, B, shuffle, world, r, seed=5, group=K)) for r in range(world)]
+    assert len(per_rank[0]) == len(per_rank[1])
+    step = 0
+    for items in zip(*per_rank):
+        k = getattr(items[0][2], "k", 1)
+        for i in range(k):
+            rows = torch.cat([(it[1][i] if k > 1 else it[1]) for it in items])
+            want = plain[step][1]
+            assert sorted(rows.tolist()) == sorted(want.tolist())
+            step += 1
+        if k > 1:
+            assert items[0][0].shape == (K, B // world, 1) and int(items[0][2]) == B
+    assert step == len(plain) == 13
