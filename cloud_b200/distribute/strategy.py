@@ -13,6 +13,26 @@ import torch
 import torch.distributed as dist
 
 
+_exit_hook_installed = False
+
+
+def _destroy_group_at_exit():
+    """The strategy created the process group, so it also tears it down (NCCL warns otherwise)."""
+    global _exit_hook_installed
+    if _exit_hook_installed:
+        return
+    _exit_hook_installed = True
+    import atexit
+
+    def _cleanup():
+        try:
+            if dist.is_initialized():
+                dist.destroy_process_group()
+        except Exception:      # interpreter shutdown: nothing useful can be done with an error here
+            pass
+    atexit.register(_cleanup)
+
+
 class ReduceOp(enum.Enum):
     SUM = "SUM"
     MEAN = "MEAN"
@@ -85,6 +105,7 @@ class Strategy:
                 os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
                 os.environ.setdefault("MASTER_PORT", "29512")
                 dist.init_process_group(backend, rank=rank, world_size=world, **kwargs)
+                _destroy_group_at_exit()
             self._world, self._rank = dist.get_world_size(), dist.get_rank()
         else:
             self._world, self._rank = 1, 0
