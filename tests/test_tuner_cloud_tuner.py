@@ -311,3 +311,46 @@ def test_crashed_worker_trial_is_marked_infeasible(tmp_path):
     trials = local_vizier.LocalVizier().list_trials(
         "projects/p/locations/r/studies/CloudTuner_study_crash")["trials"]
     assert trials[0]["state"] == "COMPLETED" and trials[0]["trialInfeasible"] is True
+
+
+def test_distributing_cloud_tuner_trains_every_trial_as_a_launched_job(tmp_path, monkeypatch):
+    """T5: each trial is shipped through cloud_fit to its own job; the tuner replays the job's
+    per-epoch metrics into the oracle and can load the trained model back."""
+    monkeypatch.setenv("TFC_JOB_ROOT", str(tmp_path / "jobs"))
+    monkeypatch.setenv("TFC_VIZIER_ROOT", str(tmp_path / "vizier"))
+    x, y = _data(128)
+    directory = tmp_path / "dist_tuner"
+    t = tfc.DistributingCloudTuner(_build_model, project_id="p", region="r", directory=str(directory),
+                                   objective="acc", hyperparameters=_search_space(), max_trials=2,
+                                   study_id="dct", replica_config=tfc.COMMON_MACHINE_CONFIGS["CPU"],
+                                   replica_count=1)
+    t.search(x=x, y=y, epochs=2, batch_size=32, verbose=0)
+    trials = t.oracle.get_best_trials(5)
+    assert len(trials) == 2
+    for tr in trials:
+        assert tr.status == "COMPLETED" and tr.score is not None
+        tdir = directory / tr.trial_id
+        assert (tdir / "logs" / "train" / "scalars.jsonl").exists()       # TensorBoard callback ran in the job
+        assert (tdir / "output").exists()                                 # cloud_fit wrote the trained model
+    from cloud_b200.tuner import local_vizier
+    stored = local_vizier.LocalVizier().list_trials("projects/p/locations/r/studies/CloudTuner_study_dct")["trials"]
+    assert len(stored) == 2
+    assert all(len(s["measurements"]) == 2 for s in stored)               # one report per epoch of the job
+    model = t.load_model(trials[0])
+    assert model.predict(x[:4]).shape == (4, 4)
+    # the jobs went through the launcher's registry
+    from cloud_b200.launch import registry
+    jobs = [j for j in os.listdir(tmp_path / "jobs" / "jobs")]
+    assert len(jobs) == 2 and all(registry.status(j)["state"] == "SUCCEEDED" for j in jobs)
+
+
+def test_distributing_cloud_tuner_fails_the_trial_when_its_job_fails(tmp_path, monkeypatch):
+    monkeypatch.setenv("TFC_JOB_ROOT", str(tmp_path / "jobs"))
+    monkeypatch.setenv("TFC_VIZIER_ROOT", str(tmp_path / "vizier"))
+    monkeypatch.setenv("TFC_FAULT", "0:1")              # rank 0 dies at step 1 of every job
+    x, y = _data(128)
+    t = tfc.DistributingCloudTuner(_build_model, project_id="p", region="r", directory=str(tmp_path / "d"),
+                                   objective="acc", hyperparameters=_search_space(), max_trials=1,
+                                   study_id="dct_fail", replica_config=tfc.COMMON_MACHINE_CONFIGS["CPU"])
+    with pytest.raises(RuntimeError, match="AIP Training job failed"):
+        t.search(x=x, y=y, epochs=1, batch_size=32, verbose=0)
