@@ -11,7 +11,6 @@ from __future__ import annotations
 import datetime
 import logging
 import os
-import pickle
 import types
 from typing import Any, Dict, Optional, Text
 

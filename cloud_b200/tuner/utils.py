@@ -7,7 +7,7 @@ is tested upstream: tuner/tests/unit/tuner_test.py:60-73), so key names - includ
 """
 from __future__ import annotations
 
-from typing import Any, Dict, List, Optional, Text, Union
+from typing import Any, Dict, List, Optional, Text
 
 from .engine import hyperparameters as hp_module
 from .engine import metrics_tracking
