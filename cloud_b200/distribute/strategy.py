@@ -90,9 +90,9 @@ class Strategy:
         self.device = device
         if device.type == "cuda":
             torch.cuda.set_device(device)
-            # opt-in (TFC_CUDNN_BENCHMARK=1): let cuDNN time its algorithms during the eager warm-up steps
-            # (before the step is frozen into a CUDA graph)
-            if os.environ.get("TFC_CUDNN_BENCHMARK", "0") == "1":
+            # cuDNN times its algorithms during the eager warm-up steps, before the step is frozen into
+            # a CUDA graph: 19.31 -> 19.07 ms/step on ResNet-50 at batch 256 (TFC_CUDNN_BENCHMARK=0: off)
+            if os.environ.get("TFC_CUDNN_BENCHMARK", "1") != "0":
                 torch.backends.cudnn.benchmark = True
         self._group = None
         world, rank, _local = _env_world()
