@@ -229,3 +229,45 @@ def test_array_source_groups_partition_each_global_batch_across_replicas(shuffle
         if k > 1:
             assert items[0][0].shape == (K, B // world, 1) and int(items[0][2]) == B
     assert step == len(plain) == 13
+
+
+def test_tensorboard_jsonl_progbar_and_terminate_on_nan(tmp_path, capsys):
+    x, y = _blobs(128)
+    m = _mlp(dropout=0.0)
+    tb = keras.callbacks.TensorBoard(log_dir=str(tmp_path / "logs"))
+    m.fit(x, y, batch_size=32, epochs=2, verbose=2, validation_data=(x[:32], y[:32]), callbacks=[tb])
+    out = capsys.readouterr().out
+    assert "Epoch 1/2" in out and "Epoch 2/2" in out and "loss:" in out and "val_loss:" in out
+    recs = [json.loads(l) for l in open(tmp_path / "logs" / "train" / "scalars.jsonl")]
+    assert [r["step"] for r in recs] == [0, 1] and {"loss", "accuracy"} <= set(recs[0])
+    vrecs = [json.loads(l) for l in open(tmp_path / "logs" / "validation" / "scalars.jsonl")]
+    assert len(vrecs) == 2 and "loss" in vrecs[0]
+    # a diverging run stops at the first non-finite loss
+    m2 = keras.Sequential([L.Dense(4, input_shape=(20,))])
+    m2.compile(optimizer="sgd", loss=keras.losses.SparseCategoricalCrossentropy(from_logits=True))
+    x_bad = x.copy()
+    x_bad[5, 3] = np.nan
+    h = m2.fit(x_bad, y, batch_size=32, epochs=5, verbose=0, shuffle=False,
+               callbacks=[keras.callbacks.TerminateOnNaN()])
+    assert len(h.history["loss"]) == 1 and m2.stop_training
+
+
+def test_learning_rate_schedules_and_metrics_objects():
+    sched = keras.optimizers.ExponentialDecay(0.1, decay_steps=10, decay_rate=0.5, staircase=True)
+    assert sched(0) == pytest.approx(0.1) and sched(10) == pytest.approx(0.05) and sched(25) == pytest.approx(0.025)
+    pw = keras.optimizers.PiecewiseConstantDecay([5, 10], [1.0, 0.5, 0.1])
+    assert [pw(s) for s in (0, 5, 6, 11)] == [1.0, 1.0, 0.5, 0.1]
+    opt = keras.optimizers.SGD(learning_rate=sched)
+    x, y = _blobs(64)
+    m = keras.Sequential([L.Dense(4, activation="softmax", input_shape=(20,))])
+    m.compile(optimizer=opt, loss="sparse_categorical_crossentropy")
+    m.fit(x, y, batch_size=8, epochs=2, verbose=0)             # 16 steps: the rate has halved once
+    assert m.optimizer.current_lr() == pytest.approx(0.05)
+    acc = keras.metrics.SparseCategoricalAccuracy()
+    acc.update_state(np.array([0, 1, 2]), np.array([[0.9, 0.1, 0], [0.2, 0.7, 0.1], [0.5, 0.4, 0.1]]))
+    assert float(acc.result()) == pytest.approx(2 / 3)
+    mean = keras.metrics.Mean()
+    mean.update_state(2.0)
+    mean.update_state(4.0)
+    assert float(mean.result()) == pytest.approx(3.0)
+    mean.reset_states() if hasattr(mean, "reset_states") else mean.reset_state()
