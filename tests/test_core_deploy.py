@@ -4,6 +4,7 @@ CPU ranks (only sys.exit mocked, like upstream :37,50-137)."""
 import json
 import os
 import textwrap
+import time
 from unittest import mock
 
 import pytest
@@ -185,3 +186,30 @@ def test_run_with_tpu_worker_reports_no_tpu(tmp_path, monkeypatch):
     with pytest.raises(plan_mod.RankPlanError, match=r"no TPU on this box"):
         tfc.run(entry_point="train.py", chief_config=CFG["CPU"], worker_config=CFG["TPU"],
                 worker_count=1, docker_base_image="custom")
+
+
+def test_job_cli_lists_describes_streams_and_cancels(tmp_path, capsys):
+    """`python -m cloud_b200.launch ...`: the local stand-in for `gcloud ai-platform jobs ...`."""
+    from cloud_b200.launch import __main__ as cli
+    uri = _stage(tmp_path, "print('hello from the job')\n")
+    done = deploy.deploy_job("us-central1", uri, CFG["CPU"], 0, CFG["CPU"], None, False)
+    assert registry.wait(done, timeout=60)["state"] == "SUCCEEDED"
+    slow_uri = _stage(tmp_path, "import time\nprint('started', flush=True)\ntime.sleep(120)\n")
+    slow = deploy.deploy_job("us-central1", slow_uri, CFG["CPU"], 0, CFG["CPU"], None, False)
+    t0 = time.time()
+    while registry.status(slow).get("state") != "RUNNING" and time.time() - t0 < 30:
+        time.sleep(0.1)
+    capsys.readouterr()
+    assert cli.main(["list"]) == 0
+    out = capsys.readouterr().out
+    assert done in out and "SUCCEEDED" in out and slow in out and "RUNNING" in out
+    assert cli.main(["describe", done]) == 0
+    desc = json.loads(capsys.readouterr().out)
+    assert desc["status"]["state"] == "SUCCEEDED" and desc["plan"]["world_size"] == 1 and desc["logs"]
+    assert cli.main(["stream-logs", done]) == 0
+    assert "hello from the job" in capsys.readouterr().out
+    assert cli.main(["cancel", slow]) == 0
+    assert registry.status(slow)["state"] == "CANCELLED"
+    assert cli.main(["cancel", slow]) == 0 and "already CANCELLED" in capsys.readouterr().out
+    assert cli.main(["describe", "tf_cloud_train_nope"]) == 2
+    assert cli.main(["topology"]) == 0
