@@ -413,6 +413,27 @@ class Model(nn.Module):
     trainable_variables = trainable_weights
 
     @property
+    def non_trainable_weights(self):
+        """Frozen parameters and layer state that is not trained (batch-norm moving statistics)."""
+        return [p for p in self.parameters() if not p.requires_grad] + list(self.buffers())
+
+    non_trainable_variables = non_trainable_weights
+
+    @property
+    def weights(self):
+        return self.trainable_weights + self.non_trainable_weights
+
+    variables = weights
+
+    def reset_metrics(self):
+        for m in self._metrics:
+            if hasattr(m, "reset_state"):
+                m.reset_state()
+
+    def reset_states(self):
+        """Keras resets the state of stateful (recurrent) layers here; this front end has none."""
+
+    @property
     def metrics_names(self):
         return ["loss"] + [m.name for m in self._metrics]
 
