@@ -18,40 +18,41 @@ keras = tfc.keras
 preprocessing = keras.layers.experimental.preprocessing
 
 
+ACTIVATIONS = ["relu", "elu"]
+
+
+def _augmentation():
+    """Random flip / rotation / width / height, as a nested Sequential used like a layer."""
+    return keras.Sequential([preprocessing.RandomFlip(), preprocessing.RandomRotation(0.1),
+                             preprocessing.RandomWidth(0.1), preprocessing.RandomHeight(0.1)])
+
+
+def _conv(hp, tag, filters):
+    act = hp.Choice("conv_activation_" + tag, values=ACTIVATIONS, default="relu")
+    return keras.layers.Conv2D(filters, (3, 3), padding="same", activation=act)
+
+
 def build_model(hp):
-    """Constructs a model."""
-    data_augmentation = keras.Sequential([
-        preprocessing.RandomFlip(),
-        preprocessing.RandomRotation(0.1),
-        preprocessing.RandomWidth(0.1),
-        preprocessing.RandomHeight(0.1),
-    ])
-    inputs = keras.Input(shape=(32, 32, 3))
-    x = data_augmentation(inputs)
-    x = keras.layers.Conv2D(
-        32, (3, 3), padding="same",
-        activation=hp.Choice("conv_activation_0", values=["relu", "elu"], default="relu"))(x)
-    for i in range(hp.Int("num_blocks", 1, 3)):
-        for j in range(hp.Int("num_conv_{}".format(i), 1, 3)):
-            x = keras.layers.Conv2D(
-                hp.Int("filter_{}_{}".format(i, j), 16, 256, step=16), (3, 3), padding="same",
-                activation=hp.Choice("conv_activation_{}_{}".format(i, j), values=["relu", "elu"],
-                                     default="relu"))(x)
-        x = keras.layers.MaxPooling2D(pool_size=(2, 2))(x)
-    x = keras.layers.Dropout(
-        rate=hp.Float("dropout_1", min_value=0.0, max_value=0.9, default=0.25, step=0.05))(x)
-    x = keras.layers.GlobalMaxPooling2D()(x)
-    x = keras.layers.Dense(512, activation="relu")(x)
-    outputs = keras.layers.Dense(10, activation="softmax")(x)
-    model = keras.Model(inputs, outputs)
-    lr_schedule = keras.optimizers.schedules.ExponentialDecay(
+    """The hypermodel: every hyperparameter is declared here, the deeper ones only when the block
+    they belong to exists (conditional search space)."""
+    image = keras.Input(shape=(32, 32, 3))
+    net = _conv(hp, "0", 32)(_augmentation()(image))
+    n_blocks = hp.Int("num_blocks", 1, 3)
+    for blk in range(n_blocks):
+        for cv in range(hp.Int("num_conv_%d" % blk, 1, 3)):
+            width = hp.Int("filter_%d_%d" % (blk, cv), 16, 256, step=16)
+            net = _conv(hp, "%d_%d" % (blk, cv), width)(net)
+        net = keras.layers.MaxPooling2D(pool_size=(2, 2))(net)
+    drop = hp.Float("dropout_1", min_value=0.0, max_value=0.9, default=0.25, step=0.05)
+    net = keras.layers.GlobalMaxPooling2D()(keras.layers.Dropout(rate=drop)(net))
+    net = keras.layers.Dense(512, activation="relu")(net)
+    model = keras.Model(image, keras.layers.Dense(10, activation="softmax")(net))
+
+    schedule = keras.optimizers.schedules.ExponentialDecay(
         initial_learning_rate=hp.Choice("initial_learning_rate", [1e-1, 1e-2, 1e-3]),
-        decay_steps=100000,
-        decay_rate=hp.Choice("decay_rate", [0.5, 0.75, 0.95]),
-        staircase=True)
-    model.compile(loss="sparse_categorical_crossentropy",
-                  optimizer=keras.optimizers.RMSprop(learning_rate=lr_schedule),
-                  metrics=["sparse_categorical_accuracy"])
+        decay_steps=100000, decay_rate=hp.Choice("decay_rate", [0.5, 0.75, 0.95]), staircase=True)
+    model.compile(optimizer=keras.optimizers.RMSprop(learning_rate=schedule),
+                  loss="sparse_categorical_crossentropy", metrics=["sparse_categorical_accuracy"])
     return model
 
 

@@ -5,26 +5,22 @@ import numpy as np
 
 import cloud_b200 as tfc
 
-from create_model import create_keras_model
+from create_model import create_keras_model      # sibling module: the directory travels with the job
 
 keras = tfc.keras
-(x_train, y_train), (x_test, y_test) = keras.datasets.mnist.load_data()
-x_train, y_train = x_train[:2048, ..., None], y_train[:2048]
-x_test, y_test = x_test[:512, ..., None], y_test[:512]
-
-BUFFER_SIZE = 10000
-BATCH_SIZE = 64
+BATCH, SHUFFLE_BUFFER = 64, 10000
 
 
-def scale(image, label):
-    return np.asarray(image, dtype="float32") / 255, label
+def pipeline(images, labels, training):
+    """uint8 images -> float32 in [0, 1], cached, (shuffled,) batched."""
+    ds = tfc.data.Dataset.from_tensor_slices((images[..., None], labels))
+    ds = ds.map(lambda im, lb: (np.asarray(im, dtype="float32") / 255, lb))
+    if training:
+        ds = ds.cache().shuffle(SHUFFLE_BUFFER)
+    return ds.batch(BATCH)
 
 
-train_dataset = tfc.data.Dataset.from_tensor_slices((x_train, y_train)).map(scale).cache()
-train_dataset = train_dataset.shuffle(BUFFER_SIZE).batch(BATCH_SIZE)
-eval_dataset = tfc.data.Dataset.from_tensor_slices((x_test, y_test)).map(scale).batch(BATCH_SIZE)
-
+(train_x, train_y), (test_x, test_y) = keras.datasets.mnist.load_data()
 model = create_keras_model()
-epochs = 2 if tfc.remote() else 1
-model.fit(train_dataset, epochs=epochs, verbose=2)
-print("eval:", model.evaluate(eval_dataset, verbose=0))
+model.fit(pipeline(train_x[:2048], train_y[:2048], True), epochs=2 if tfc.remote() else 1, verbose=2)
+print("eval:", model.evaluate(pipeline(test_x[:512], test_y[:512], False), verbose=0))
