@@ -38,139 +38,131 @@ class CloudOracle(oracle_module.Oracle):
                  hyperparameters: hp_module.HyperParameters = None,
                  study_config: Optional[Dict[Text, Any]] = None, max_trials: int = None,
                  study_id: Optional[Text] = None):
-        if study_config:
-            if objective or hyperparameters:
-                raise ValueError('Please configure either study_config or '
-                                 '"objective, and hyperparameters".')
-            objective = utils.convert_study_config_to_objective(study_config)
-            hyperparameters = utils.convert_study_config_to_hps(study_config)
-            self.study_config = study_config
-        else:
-            if not (objective and hyperparameters):
-                raise ValueError("If study_config is not set, "
-                                 "objective and hyperparameters must be set.")
-            self.study_config = utils.make_study_config(objective, hyperparameters)
-
+        if not project_id:
+            raise ValueError('"project_id" is not found.')
+        if not region:
+            raise ValueError('"region" is not found.')
+        objective, hyperparameters, self.study_config = self._search_space(
+            objective, hyperparameters, study_config)
         super(CloudOracle, self).__init__(objective=objective, hyperparameters=hyperparameters,
                                           max_trials=max_trials, allow_new_entries=False,
                                           tune_new_entries=False)
-        if not project_id:
-            raise ValueError('"project_id" is not found.')
-        self.project_id = project_id
-        if not region:
-            raise ValueError('"region" is not found.')
-        self.region = region
+        self.project_id, self.region = project_id, region
         self.objective = utils.format_objective(objective)
         self.hyperparameters = hyperparameters
         self.max_trials = max_trials
-        if study_id:
-            self.study_id = "CloudTuner_study_{}".format(study_id)
-        else:
-            self.study_id = "CloudTuner_study_{}".format(
-                datetime.datetime.now().strftime("%Y%m%d_%H%M%S"))
+        suffix = study_id or datetime.datetime.now().strftime("%Y%m%d_%H%M%S")
+        self.study_id = "CloudTuner_study_{}".format(suffix)
         self.service = optimizer_client.create_or_load_study(
             self.project_id, self.region, self.study_id, self.study_config)
         self.trials = {}
         self._start_time = None
 
+    @staticmethod
+    def _search_space(objective, hyperparameters, study_config):
+        """The search space comes either from a ready StudyConfig or from (objective,
+        hyperparameters) - never from both; returns (objective, hyperparameters, study_config)."""
+        if study_config:
+            if objective or hyperparameters:
+                raise ValueError('Please configure either study_config or '
+                                 '"objective, and hyperparameters".')
+            return (utils.convert_study_config_to_objective(study_config),
+                    utils.convert_study_config_to_hps(study_config), study_config)
+        if not (objective and hyperparameters):
+            raise ValueError("If study_config is not set, objective and hyperparameters must be set.")
+        return objective, hyperparameters, utils.make_study_config(objective, hyperparameters)
+
+    # -- service trial <-> engine trial ---------------------------------------------------------
+    def _as_trial(self, optimizer_trial, status) -> trial_module.Trial:
+        """An engine trial for a trial of the optimizer service (same id, suggested values)."""
+        hps = utils.convert_optimizer_trial_to_hps(self.hyperparameters.copy(), optimizer_trial)
+        trial = trial_module.Trial(hyperparameters=hps, trial_id=utils.get_trial_id(optimizer_trial),
+                                   status=status)
+        final = optimizer_trial.get("finalMeasurement")
+        if final:
+            trial.best_step = int(final.get("stepCount", 1))
+            trial.score = final["metrics"][0]["value"]
+        return trial
+
+    def _no_more_trials(self) -> trial_module.Trial:
+        hps = self.hyperparameters.copy()
+        hps.values = None
+        return trial_module.Trial(hyperparameters=hps, trial_id="n", status=trial_module.TrialStatus.STOPPED)
+
     def create_trial(self, tuner_id: Text) -> trial_module.Trial:
-        trial_list = self.service.list_trials()
-        stopping_trials = [t for t in trial_list if t["state"] == "STOPPING"]
-        if (self.max_trials and len(trial_list) >= self.max_trials) or stopping_trials:
-            # same tuner re-asking for its own still-pending trial is the only exception upstream
-            # handles through the service; here we mirror it exactly: no new trials.
-            hyperparameters = self.hyperparameters.copy()
-            hyperparameters.values = None
-            return trial_module.Trial(hyperparameters=hyperparameters, trial_id="n",
-                                      status=trial_module.TrialStatus.STOPPED)
+        """Next trial for ``tuner_id``: none once the study holds ``max_trials`` trials or the
+        service is stopping one; otherwise the service's suggestion for this client."""
+        known = self.service.list_trials()
+        exhausted = bool(self.max_trials) and len(known) >= self.max_trials
+        if exhausted or any(t["state"] == "STOPPING" for t in known):
+            return self._no_more_trials()
         suggestions = self.service.get_suggestions(tuner_id)
         if "trials" not in suggestions:
             return trial_module.Trial(hyperparameters={}, status=trial_module.TrialStatus.STOPPED)
-        optimizer_trial = suggestions["trials"][0]
-        trial_id = utils.get_trial_id(optimizer_trial)
-        kerastuner_trial = trial_module.Trial(
-            hyperparameters=utils.convert_optimizer_trial_to_hps(self.hyperparameters.copy(),
-                                                                 optimizer_trial),
-            trial_id=trial_id, status=trial_module.TrialStatus.RUNNING)
-        logger.info("Hyperparameters requested by tuner (%s): %s ", tuner_id,
-                    kerastuner_trial.hyperparameters.values)
+        trial = self._as_trial(suggestions["trials"][0], trial_module.TrialStatus.RUNNING)
+        logger.info("Hyperparameters requested by tuner (%s): %s ", tuner_id, trial.hyperparameters.values)
         self._start_time = time.time()
-        self.trials[trial_id] = kerastuner_trial
-        self.ongoing_trials[tuner_id] = kerastuner_trial
-        self._save_trial(kerastuner_trial)
+        self.trials[trial.trial_id] = trial
+        self.ongoing_trials[tuner_id] = trial
+        self._save_trial(trial)
         self.save()
-        return kerastuner_trial
+        return trial
 
     def update_trial(self, trial_id: Text, metrics: Mapping[Text, Union[int, float]], step: int = 0):
+        """Reports the objective values of ``metrics`` at ``step`` and asks the service whether
+        the trial should stop early; returns the trial's (possibly STOPPED) status."""
         elapsed_secs = time.time() - self._start_time
         if elapsed_secs < 0 or step < 0:
             raise ValueError("Both elapsed_secs and step must be non-negative.")
         if elapsed_secs == 0 and step == 0:
             raise ValueError("At least one of {elapsed_secs, step} must be positive")
-        metric_list = []
-        for ob in self.objective:
-            if ob.name not in metrics:
-                logger.info('Objective "%s" is not found in metrics.', ob.name)
-                continue
-            metric_list.append({"metric": ob.name, "value": float(metrics.get(ob.name))})
-        self.service.report_intermediate_objective_value(step, elapsed_secs, metric_list, trial_id)
-        kerastuner_trial = self.trials[trial_id]
+        wanted = [ob.name for ob in self.objective]
+        for name in wanted:
+            if name not in metrics:
+                logger.info('Objective "%s" is not found in metrics.', name)
+        reported = [{"metric": n, "value": float(metrics[n])} for n in wanted if n in metrics]
+        self.service.report_intermediate_objective_value(step, elapsed_secs, reported, trial_id)
+        trial = self.trials[trial_id]
         logger.info("UpdateTrial: polls the stop decision.")
         if self.service.should_trial_stop(trial_id):
-            kerastuner_trial.status = trial_module.TrialStatus.STOPPED
-        return kerastuner_trial.status
+            trial.status = trial_module.TrialStatus.STOPPED
+        return trial.status
+
+    # status -> (trial_infeasible, infeasibility_reason) for the service's complete call
+    _COMPLETION = {trial_module.TrialStatus.COMPLETED: (False, None),
+                   trial_module.TrialStatus.INVALID: (True, trial_module.TrialStatus.INVALID)}
 
     def end_trial(self, trial_id: Text, status: Text = "COMPLETED"):
-        kerastuner_trial = None
-        for tuner_id, ongoing_trial in self.ongoing_trials.items():
-            if ongoing_trial.trial_id == trial_id:
-                logger.info("End trial requested by tuner (%s)", tuner_id)
-                kerastuner_trial = self.ongoing_trials.pop(tuner_id)
-                break
-        if not kerastuner_trial:
+        """Completes the ongoing trial ``trial_id`` in the service (as infeasible for INVALID) and
+        records its final score / best step."""
+        owner = next((tid for tid, t in self.ongoing_trials.items() if t.trial_id == trial_id), None)
+        if owner is None:
             raise ValueError("Ongoing trial with id: {} not found.".format(trial_id))
-        kerastuner_trial.status = status
-        if status == trial_module.TrialStatus.COMPLETED:
-            trial_infeasible, infeasibility_reason = False, None
-        elif status == trial_module.TrialStatus.INVALID:
-            trial_infeasible, infeasibility_reason = True, status
-        else:
+        logger.info("End trial requested by tuner (%s)", owner)
+        trial = self.ongoing_trials.pop(owner)
+        trial.status = status
+        if status not in self._COMPLETION:
             raise ValueError('Unexpected status passed. Expected "COMPLETED" or '
                              '"INVALID", found {}'.format(status))
-        optimizer_trial = self.service.complete_trial(trial_id, trial_infeasible,
-                                                      infeasibility_reason)
-        if status == trial_module.TrialStatus.COMPLETED:
-            final_measurement = optimizer_trial["finalMeasurement"]
-            kerastuner_trial.best_step = int(final_measurement.get("stepCount", 1))
-            kerastuner_trial.score = final_measurement["metrics"][0]["value"]
-        self._save_trial(kerastuner_trial)
+        infeasible, reason = self._COMPLETION[status]
+        finished = self.service.complete_trial(trial_id, infeasible, reason)
+        if not infeasible:
+            final = finished["finalMeasurement"]
+            trial.best_step = int(final.get("stepCount", 1))
+            trial.score = final["metrics"][0]["value"]
+        self._save_trial(trial)
         self.save()
 
     def get_best_trials(self, num_trials: int = 1) -> List[trial_module.Trial]:
+        """COMPLETED trials of the study ranked by their final measurement (single objective)."""
         if len(self.objective) > 1:
             raise ValueError("Getting the best trials for multi-objective optimization "
                              "is not supported. ")
-        maximizing = utils.format_goal(self.objective[0].direction) == "MAXIMIZE"
-        trial_list = self.service.list_trials()
-        optimizer_trials = [t for t in trial_list
-                            if t["state"] == "COMPLETED" and "finalMeasurement" in t]
-        if not optimizer_trials:
-            return []
-        sorted_trials = sorted(optimizer_trials,
-                               key=lambda t: t["finalMeasurement"]["metrics"][0]["value"],
-                               reverse=maximizing)
-        best_trials = []
-        for optimizer_trial in sorted_trials[:num_trials]:
-            final_measurement = optimizer_trial["finalMeasurement"]
-            kerastuner_trial = trial_module.Trial(
-                hyperparameters=utils.convert_optimizer_trial_to_hps(self.hyperparameters.copy(),
-                                                                     optimizer_trial),
-                trial_id=utils.get_trial_id(optimizer_trial),
-                status=trial_module.TrialStatus.COMPLETED)
-            kerastuner_trial.best_step = int(final_measurement.get("stepCount", 1))
-            kerastuner_trial.score = final_measurement["metrics"][0]["value"]
-            best_trials.append(kerastuner_trial)
-        return best_trials
+        finished = [t for t in self.service.list_trials()
+                    if t["state"] == "COMPLETED" and "finalMeasurement" in t]
+        finished.sort(key=lambda t: t["finalMeasurement"]["metrics"][0]["value"],
+                      reverse=utils.format_goal(self.objective[0].direction) == "MAXIMIZE")
+        return [self._as_trial(t, trial_module.TrialStatus.COMPLETED) for t in finished[:num_trials]]
 
 
 class CloudTuner(tuner_module.Tuner):
