@@ -13,11 +13,14 @@ polled with ``operations.get``; the same ``client_id`` gets the same trial back 
 ACTIVE; more than ``MAX_TRIALS_PER_STUDY`` trials or an exhausted grid -> 429; ``complete`` without
 a final measurement uses the last reported one; trial names end in a numeric id.
 
-Algorithms: ``ALGORITHM_UNSPECIFIED`` and ``RANDOM_SEARCH`` -> seeded random search honouring
+Algorithms: ``RANDOM_SEARCH`` -> seeded random search honouring
 ``scale_type``; ``GRID_SEARCH`` -> lexicographic grid over DISCRETE / CATEGORICAL / INTEGER;
-``GAUSSIAN_PROCESS_BANDIT`` -> random exploration mixed with Gaussian perturbations of the best
-trials so far (a bandit-flavoured stand-in, not a GP).  Early stopping: median rule at equal step
-for both ``decayCurveStoppingConfig`` and ``medianAutomatedStoppingConfig``.
+``GAUSSIAN_PROCESS_BANDIT`` - and ``ALGORITHM_UNSPECIFIED``, whose meaning is "the service's
+default", unless ``TFC_VIZIER_DEFAULT_ALGORITHM`` says otherwise - -> Gaussian-process regression
+with expected improvement (``gp_bandit.py``) after a few random trials.  Early stopping:
+``medianAutomatedStoppingConfig`` -> median rule at equal progress; ``decayCurveStoppingConfig``
+-> optimistic extrapolation of the learning curve against the best finished trial; progress is
+the step count, or the elapsed time with ``useElapsedTime``.
 """
 from __future__ import annotations
 
@@ -31,7 +34,7 @@ import random
 import time
 import uuid
 
-from . import constants
+from . import constants, gp_bandit
 from ..utils import api_client
 
 
@@ -50,6 +53,13 @@ class HttpError(Exception):
         self.resp = _Resp(status)
         self.status_code = status
         self.content = message.encode()
+
+
+MIN_TRIALS_FOR_STOPPING = 3
+DECAY_CURVE_OPTIMISM = 2.0
+GP_RANDOM_CANDIDATES = 384
+GP_ANCHORS = 4
+GP_PERTURBATIONS_PER_ANCHOR = 32
 
 
 def default_root() -> str:
@@ -217,7 +227,7 @@ class LocalVizier:
                     if out:
                         break
                     raise HttpError(429, "search space exhausted")
-                tid = str(len(trials) + 1)
+                tid = self._next_trial_id(study, trials)
                 trial = {"name": "{}/trials/{}".format(parent, tid), "state": "ACTIVE",
                          "parameters": params, "clientId": client_id, "startTime": _now(),
                          "measurements": []}
@@ -230,8 +240,9 @@ class LocalVizier:
     def create_trial(self, parent: str, body: dict) -> dict:
         d = self._study_dir(parent)
         with self._locked(d):
-            _study, trials = self._load(d)
-            tid = str(len(trials) + 1)
+            study, trials = self._load(d)
+            tid = self._next_trial_id(study, trials)
+            self._write(os.path.join(d, "study.json"), study)
             trial = dict(body)
             trial.update({"name": "{}/trials/{}".format(parent, tid), "startTime": _now()})
             trial.setdefault("state", "REQUESTED")
@@ -239,6 +250,14 @@ class LocalVizier:
             trials.append(trial)
             self._write(os.path.join(d, "trials.json"), trials)
             return trial
+
+    @staticmethod
+    def _next_trial_id(study, trials) -> str:
+        """Trial ids are never reused, also not after ``trials.delete``."""
+        last = max([int(study.get("last_trial_id", 0))] +
+                   [int(t["name"].rpartition("/")[2]) for t in trials if t["name"].rpartition("/")[2].isdigit()])
+        study["last_trial_id"] = last + 1
+        return str(last + 1)
 
     def list_trials(self, parent: str) -> dict:
         d = self._study_dir(parent)
@@ -325,54 +344,146 @@ class LocalVizier:
             cur = next((t for t in trials if t["name"] == name), None)
             if cur is None:
                 raise HttpError(404, "trial not found")
-            should_stop = self._median_rule(study, trials, cur)
+            should_stop = self._should_stop(study, trials, cur)
             return self._new_operation(d, study_name, {"shouldStop": should_stop})
 
-    def _median_rule(self, study, trials, cur) -> bool:
+    # -- automated stopping -----------------------------------------------------------------------------
+    @staticmethod
+    def _progress(measurement, use_elapsed_time: bool) -> float:
+        """Where on its learning curve a measurement sits: step count, or seconds since the trial
+        started when the config says ``useElapsedTime`` (what make_study_config asks for,
+        tuner/utils.py:62-68)."""
+        if use_elapsed_time:
+            elapsed = measurement.get("elapsedTime")
+            if isinstance(elapsed, dict):
+                return float(elapsed.get("seconds", 0))
+            if isinstance(elapsed, str):
+                return float(elapsed.rstrip("s") or 0)
+        return float(measurement.get("stepCount", 0))
+
+    def _curve(self, study, trial, use_elapsed_time):
+        """[(progress, objective value)] of a trial, in the order reported."""
+        metric, _goal = self._goal(study)
+        out = []
+        for m in trial.get("measurements", []):
+            for mv in m.get("metrics", []):
+                if metric is None or mv.get("metric") == metric:
+                    out.append((self._progress(m, use_elapsed_time), float(mv["value"])))
+                    break
+        return out
+
+    @staticmethod
+    def _best_until(curve, progress, maximize):
+        values = [v for p, v in curve if p <= progress]
+        if not values:
+            return None
+        return max(values) if maximize else min(values)
+
+    def _should_stop(self, study, trials, cur) -> bool:
         cfg = study.get("studyConfig", {}).get("automatedStoppingConfig")
         if not cfg or not cur.get("measurements"):
             return False
-        metric, goal = self._goal(study)
-
-        def value_at(t, step):
-            best = None
-            for m in t.get("measurements", []):
-                if int(m.get("stepCount", 0)) > step:
-                    continue
-                for mv in m.get("metrics", []):
-                    if metric is None or mv.get("metric") == metric:
-                        v = float(mv["value"])
-                        if best is None or (v > best if goal == "MAXIMIZE" else v < best):
-                            best = v
-            return best
-        step = int(cur["measurements"][-1].get("stepCount", 0))
-        mine = value_at(cur, step)
-        others = [value_at(t, step) for t in trials
-                  if t["name"] != cur["name"] and t["state"] == "COMPLETED" and not t.get("trialInfeasible")]
-        others = sorted(v for v in others if v is not None)
-        if mine is None or len(others) < 3 or step < 1:
+        decay = cfg.get("decayCurveStoppingConfig")
+        median = cfg.get("medianAutomatedStoppingConfig")
+        rule_cfg = decay if decay is not None else (median or {})
+        use_elapsed = bool(rule_cfg.get("useElapsedTime"))
+        _metric, goal = self._goal(study)
+        maximize = goal == "MAXIMIZE"
+        mine = self._curve(study, cur, use_elapsed)
+        if not mine:
             return False
-        median = others[len(others) // 2]
-        return mine < median if goal == "MAXIMIZE" else mine > median
+        # a trial whose measurements carry no elapsed time falls back to step counts
+        if use_elapsed and all(p == 0 for p, _v in mine):
+            use_elapsed = False
+            mine = self._curve(study, cur, False)
+        now = mine[-1][0]
+        finished = [self._curve(study, t, use_elapsed) for t in trials
+                    if t["name"] != cur["name"] and t["state"] == "COMPLETED"
+                    and not t.get("trialInfeasible")]
+        finished = [c for c in finished if c]
+        if len(finished) < MIN_TRIALS_FOR_STOPPING or len(mine) < 2 and now < 1:
+            return False
+        if decay is not None:
+            return self._decay_curve_rule(mine, finished, now, maximize)
+        return self._median_rule(mine, finished, now, maximize)
+
+    def _median_rule(self, mine, finished, now, maximize) -> bool:
+        """Stop when the trial's best value so far is worse than the median of what the finished
+        trials had reached at the same point."""
+        current = self._best_until(mine, now, maximize)
+        others = sorted(v for v in (self._best_until(c, now, maximize) for c in finished) if v is not None)
+        if current is None or len(others) < MIN_TRIALS_FOR_STOPPING:
+            return False
+        middle = others[len(others) // 2]
+        return current < middle if maximize else current > middle
+
+    def _decay_curve_rule(self, mine, finished, now, maximize) -> bool:
+        """Stop when an optimistic extrapolation of the trial's curve ends below the best finished
+        trial.  The extrapolation adds to the current value ``DECAY_CURVE_OPTIMISM`` times the
+        upper-quartile gain that finished trials still made after the same point of their own
+        curves - learning curves flatten, so late in a trial that gain is small and a hopeless trial
+        is cut, while early on it is large and only trials far behind are stopped."""
+        sign = 1.0 if maximize else -1.0
+        current = self._best_until(mine, now, maximize)
+        gains, finals = [], []
+        for curve in finished:
+            final = self._best_until(curve, float("inf"), maximize)
+            at_now = self._best_until(curve, now, maximize)
+            finals.append(sign * final)
+            if at_now is not None:      # a curve that ended before `now` gained nothing after it
+                gains.append(sign * (final - at_now))
+        if current is None or len(gains) < MIN_TRIALS_FOR_STOPPING:
+            return False
+        gains.sort()
+        optimistic_gain = DECAY_CURVE_OPTIMISM * max(0.0, gains[min(len(gains) - 1, (3 * len(gains)) // 4)])
+        return sign * current + optimistic_gain < max(finals)
 
     # -- suggestion algorithms ----------------------------------------------------------------------------
     def _next_parameters(self, study, trials):
         cfg = study.get("studyConfig", {})
         algo = cfg.get("algorithm", "ALGORITHM_UNSPECIFIED")
+        if algo == "ALGORITHM_UNSPECIFIED":     # the service's default is its GP bandit
+            algo = os.environ.get("TFC_VIZIER_DEFAULT_ALGORITHM", "GAUSSIAN_PROCESS_BANDIT")
         specs = cfg.get("parameters", [])
         rng = random.Random(study["seed"] + 7919 * len(trials))
         if algo == "GRID_SEARCH":
             return self._grid_point(study, specs)
         if algo == "GAUSSIAN_PROCESS_BANDIT":
-            done = [t for t in trials if t["state"] == "COMPLETED" and t.get("finalMeasurement")
-                    and not t.get("trialInfeasible")]
-            if len(done) >= 4 and rng.random() < 0.6:
-                _metric, goal = self._goal(study)
-                done.sort(key=lambda t: t["finalMeasurement"]["metrics"][0]["value"],
-                          reverse=goal == "MAXIMIZE")
-                anchor = rng.choice(done[:max(1, len(done) // 4)])
-                return self._perturb(specs, anchor["parameters"], rng)
+            params = self._gp_bandit_point(study, specs, trials, rng)
+            if params is not None:
+                return params
         return [self._sample(spec, rng) for spec in specs]
+
+    def _objective_of(self, study, trial):
+        metric, _goal = self._goal(study)
+        for mv in (trial.get("finalMeasurement") or {}).get("metrics", []):
+            if metric is None or mv.get("metric") == metric:
+                return float(mv["value"])
+        return None
+
+    def _gp_bandit_point(self, study, specs, trials, rng):
+        """Expected-improvement maximiser over random candidates and perturbations of the best
+        trials (``gp_bandit.choose``); None until enough trials have finished."""
+        _metric, goal = self._goal(study)
+        observed, pending = [], []
+        for t in trials:
+            if t["state"] == "COMPLETED":
+                value = None if t.get("trialInfeasible") else self._objective_of(study, t)
+                if value is not None or t.get("trialInfeasible"):
+                    observed.append((t["parameters"], value))
+            elif t["state"] in ("ACTIVE", "STOPPING", "REQUESTED"):
+                pending.append(t["parameters"])
+        feasible = [(p, v) for p, v in observed if v is not None]
+        feasible.sort(key=lambda pv: pv[1], reverse=goal == "MAXIMIZE")
+        candidates = [[self._sample(spec, rng) for spec in specs] for _ in range(GP_RANDOM_CANDIDATES)]
+        for anchor, _v in feasible[:GP_ANCHORS]:
+            candidates += [self._perturb(specs, anchor, rng) for _ in range(GP_PERTURBATIONS_PER_ANCHOR)]
+        seen = {json.dumps(p, sort_keys=True) for p, _v in observed} | \
+            {json.dumps(p, sort_keys=True) for p in pending}
+        fresh = [c for c in candidates if json.dumps(c, sort_keys=True) not in seen]
+        candidates = fresh or candidates
+        pick = gp_bandit.choose(specs, observed, pending, candidates, goal == "MAXIMIZE")
+        return None if pick is None else candidates[pick]
 
     @staticmethod
     def _value_entry(spec, v):
@@ -405,29 +516,36 @@ class LocalVizier:
         return self._value_entry(spec, rng.choice(vs["values"]))
 
     def _perturb(self, specs, anchor_params, rng):
-        anchor = {}
-        for p in anchor_params:
-            anchor[p["parameter"]] = p.get("floatValue", p.get("intValue", p.get("stringValue")))
+        """A neighbour of ``anchor_params``: numeric coordinates move by a Gaussian step of 10 % of
+        their (scaled) range, discrete ones mostly to an adjacent value, categorical ones mostly stay."""
+        anchor = {p["parameter"]: gp_bandit.param_value(p) for p in anchor_params}
         out = []
         for spec in specs:
             kind = spec["type"]
             a = anchor.get(spec["parameter"])
-            if a is None or kind in ("CATEGORICAL", "DISCRETE"):
-                if a is not None and rng.random() < 0.7:
-                    out.append(self._value_entry(spec, a))
-                else:
-                    out.append(self._sample(spec, rng))
-                continue
-            vs = spec.get("double_value_spec") or spec.get("integer_value_spec") or {}
-            lo, hi = float(vs["min_value"]), float(vs["max_value"])
-            log = (spec.get("scale_type") == "UNIT_LOG_SCALE") and lo > 0
-            x = math.log(float(a)) if log else float(a)
-            l2, h2 = (math.log(lo), math.log(hi)) if log else (lo, hi)
-            x = min(max(rng.gauss(x, 0.15 * (h2 - l2)), l2), h2)
-            v = math.exp(x) if log else x
-            if kind == "INTEGER":
-                v = int(round(v))
-            out.append(self._value_entry(spec, v))
+            if a is None:
+                out.append(self._sample(spec, rng))
+            elif kind == "CATEGORICAL":
+                out.append(self._value_entry(spec, a) if rng.random() < 0.75 else self._sample(spec, rng))
+            elif kind == "DISCRETE":
+                vs = spec.get("discrete_value_spec") or spec.get("discreteValueSpec")
+                values = sorted(vs["values"])
+                near = min(range(len(values)), key=lambda i: abs(float(values[i]) - float(a)))
+                near = min(max(near + rng.choice((-1, 0, 0, 1)), 0), len(values) - 1)
+                out.append(self._value_entry(spec, values[near]))
+            else:
+                vs = spec.get("double_value_spec") or spec.get("doubleValueSpec") or \
+                    spec.get("integer_value_spec") or spec.get("integerValueSpec")
+                lo = float(vs.get("min_value", vs.get("minValue")))
+                hi = float(vs.get("max_value", vs.get("maxValue")))
+                log = (spec.get("scale_type") or spec.get("scaleType")) == "UNIT_LOG_SCALE" and lo > 0
+                x = math.log(float(a)) if log else float(a)
+                l2, h2 = (math.log(lo), math.log(hi)) if log else (lo, hi)
+                x = min(max(rng.gauss(x, 0.1 * (h2 - l2)), l2), h2)
+                v = math.exp(x) if log else x
+                if kind == "INTEGER":
+                    v = int(min(max(round(v), lo), hi))
+                out.append(self._value_entry(spec, v))
         return out
 
     def _grid_point(self, study, specs):

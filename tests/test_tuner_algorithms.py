@@ -1,0 +1,217 @@
+"""Suggestion and early-stopping algorithms of the local optimizer service.
+
+The reference leaves both to Google's Vizier service and only names them in its wire contract
+(tuner/api/ml_public_google_rest_v1.json: ``StudyConfig.algorithm``, ``automatedStoppingConfig``;
+``make_study_config`` asks for ALGORITHM_UNSPECIFIED + decay-curve stopping, tuner/utils.py:58-68),
+so these tests have no upstream counterpart: they check that the local stand-ins behave like the
+algorithms they are named after."""
+import json
+import math
+import os
+import statistics
+
+import numpy as np
+import pytest
+
+from cloud_b200.tuner import gp_bandit, local_vizier
+
+PARENT = "projects/p/locations/r"
+SPACE = [
+    {"parameter": "lr", "type": "DOUBLE", "double_value_spec": {"min_value": 1e-5, "max_value": 1e-1},
+     "scale_type": "UNIT_LOG_SCALE"},
+    {"parameter": "units", "type": "INTEGER", "integer_value_spec": {"min_value": 8, "max_value": 128}},
+    {"parameter": "act", "type": "CATEGORICAL", "categorical_value_spec": {"values": ["relu", "tanh", "elu"]}},
+    {"parameter": "depth", "type": "DISCRETE", "discrete_value_spec": {"values": [1, 2, 4, 8]}},
+]
+
+
+def _values(parameters):
+    return {p["parameter"]: gp_bandit.param_value(p) for p in parameters}
+
+
+def _objective(parameters):
+    v = _values(parameters)
+    return -(math.log10(v["lr"]) + 3) ** 2 - ((v["units"] - 96) / 40) ** 2 \
+        - {"relu": 0.0, "tanh": 0.5, "elu": 0.2}[v["act"]] - 0.05 * abs(math.log2(v["depth"]) - 1)
+
+
+@pytest.fixture
+def svc(tmp_path):
+    return local_vizier.LocalVizier(str(tmp_path / "vizier"))
+
+
+def _study(svc, study_id, algorithm=None, seed=0, stopping=None, goal="MAXIMIZE"):
+    cfg = {"metrics": [{"metric": "score", "goal": goal}], "parameters": SPACE}
+    if algorithm:
+        cfg["algorithm"] = algorithm
+    if stopping:
+        cfg["automatedStoppingConfig"] = stopping
+    svc.create_study(PARENT, study_id, {"study_config": cfg})
+    name = "{}/studies/{}".format(PARENT, study_id)
+    path = os.path.join(svc._study_dir(name), "study.json")
+    study = json.load(open(path))
+    study["seed"] = seed                # the service draws one at random; pin it for the test
+    json.dump(study, open(path, "w"))
+    return name
+
+
+def _suggest(svc, name, client="c"):
+    op = svc.suggest_trials(name, {"client_id": client, "suggestion_count": 1})
+    return svc.get_operation(op["name"])["response"]["trials"][0]
+
+
+def _finish(svc, trial, curve):
+    for step, value in enumerate(curve, 1):
+        svc.add_measurement(trial["name"], {"measurement": {
+            "stepCount": step, "elapsedTime": {"seconds": 10 * step},
+            "metrics": [{"metric": "score", "value": value}]}})
+    svc.complete_trial(trial["name"], {})
+
+
+def _search(svc, name, n):
+    best = -float("inf")
+    for _ in range(n):
+        t = _suggest(svc, name)
+        value = _objective(t["parameters"])
+        best = max(best, value)
+        _finish(svc, t, [value])
+    return best
+
+
+def test_encoder_maps_every_parameter_kind_into_the_unit_cube():
+    enc = gp_bandit.SpaceEncoder(SPACE)
+    assert enc.dims == 1 + 1 + 3 + 1
+    x = enc.encode([{"parameter": "lr", "floatValue": 1e-3}, {"parameter": "units", "intValue": "68"},
+                    {"parameter": "act", "stringValue": "tanh"}, {"parameter": "depth", "floatValue": 8.0}])
+    np.testing.assert_allclose(x, [0.5, 0.5, 0, 1, 0, 1.0], atol=1e-9)
+    rev = gp_bandit.SpaceEncoder([dict(SPACE[0], scale_type="UNIT_REVERSE_LOG_SCALE")])
+    lo, hi = rev.encode([{"parameter": "lr", "floatValue": 1e-5}]), rev.encode([{"parameter": "lr", "floatValue": 1e-1}])
+    assert lo[0] == pytest.approx(0.0) and hi[0] == pytest.approx(1.0)
+
+
+def test_gaussian_process_interpolates_and_is_uncertain_far_away():
+    rng = np.random.default_rng(0)
+    x = rng.random((24, 2))
+    y = np.sin(4 * x[:, 0]) + x[:, 1] ** 2
+    y = (y - y.mean()) / y.std()
+    gp = gp_bandit.GaussianProcess(x, y)
+    mean, std = gp.predict(x)
+    np.testing.assert_allclose(mean, y, atol=0.05)
+    assert std.max() < 0.2
+    _m, far = gp.predict(np.array([[5.0, 5.0]]))
+    assert far[0] > 0.9                                  # back to the prior away from the data
+    ei = gp_bandit.expected_improvement(np.array([0.0, 1.0]), np.array([1.0, 1.0]), incumbent=0.5)
+    assert ei[1] > ei[0] > 0
+
+
+def test_gp_bandit_beats_random_search_on_a_smooth_objective(svc):
+    random_best = [_search(svc, _study(svc, "rnd%d" % s, "RANDOM_SEARCH", seed=s), 24) for s in range(3)]
+    gp_best = [_search(svc, _study(svc, "gp%d" % s, "GAUSSIAN_PROCESS_BANDIT", seed=s), 24) for s in range(3)]
+    assert statistics.mean(gp_best) > statistics.mean(random_best)
+    assert min(gp_best) > -0.2                           # close to the optimum (0) every time
+
+
+def test_unspecified_algorithm_is_the_service_default(svc, monkeypatch):
+    calls = []
+    real = gp_bandit.choose
+    monkeypatch.setattr(gp_bandit, "choose", lambda *a, **k: calls.append(1) or real(*a, **k))
+    _search(svc, _study(svc, "default"), 10)
+    assert calls, "ALGORITHM_UNSPECIFIED never reached the GP bandit"
+    calls.clear()
+    monkeypatch.setenv("TFC_VIZIER_DEFAULT_ALGORITHM", "RANDOM_SEARCH")
+    _search(svc, _study(svc, "forced-random"), 10)
+    assert not calls
+
+
+def test_running_trials_spread_parallel_suggestions(svc):
+    name = _study(svc, "parallel", "GAUSSIAN_PROCESS_BANDIT", seed=3)
+    _search(svc, name, 12)
+    batch = [_suggest(svc, name, client="w%d" % i) for i in range(8)]       # eight workers at once
+    points = {json.dumps(t["parameters"], sort_keys=True) for t in batch}
+    assert len(points) == 8
+    for t in batch:
+        v = _values(t["parameters"])
+        assert 1e-5 <= v["lr"] <= 1e-1 and 8 <= v["units"] <= 128
+        assert v["act"] in ("relu", "tanh", "elu") and v["depth"] in (1, 2, 4, 8)
+
+
+def test_infeasible_trials_are_avoided_not_fatal(svc):
+    name = _study(svc, "infeasible", "GAUSSIAN_PROCESS_BANDIT", seed=1)
+    for i in range(14):
+        t = _suggest(svc, name)
+        if _values(t["parameters"])["act"] == "tanh":
+            svc.complete_trial(t["name"], {"trial_infeasible": True, "infeasible_reason": "diverged"})
+        else:
+            _finish(svc, t, [_objective(t["parameters"])])
+    later = [_values(_suggest(svc, name, client="z%d" % i)["parameters"])["act"] for i in range(6)]
+    assert later.count("tanh") <= 2
+
+
+def test_trial_ids_are_not_reused_after_delete(svc):
+    name = _study(svc, "ids", "RANDOM_SEARCH")
+    a, b = _suggest(svc, name, "a"), _suggest(svc, name, "b")
+    svc.delete_trial(b["name"])
+    c = _suggest(svc, name, "c")
+    assert [t["name"].rpartition("/")[2] for t in (a, b, c)] == ["1", "2", "3"]
+
+
+DECAY = {"decayCurveStoppingConfig": {"useElapsedTime": False}}
+MEDIAN = {"medianAutomatedStoppingConfig": {"useElapsedTime": False}}
+
+
+def _running(svc, name, curve, client):
+    t = _suggest(svc, name, client)
+    for step, value in enumerate(curve, 1):
+        svc.add_measurement(t["name"], {"measurement": {"stepCount": step,
+                                                        "metrics": [{"metric": "score", "value": value}]}})
+    op = svc.check_early_stopping_state(t["name"])
+    return svc.get_operation(op["name"])["response"]["shouldStop"]
+
+
+def test_decay_curve_rule_extrapolates_before_it_stops(svc):
+    name = _study(svc, "decay", "RANDOM_SEARCH", stopping=DECAY)
+    for k in range(4):                  # finished trials climb 0.2 -> ~0.9 over ten steps
+        _finish(svc, _suggest(svc, name, "f%d" % k),
+                [0.9 - 0.7 * math.exp(-0.5 * s) - 0.01 * k for s in range(10)])
+    # early and behind: the finished trials still gained a lot after step 2, so keep going
+    assert _running(svc, name, [0.15, 0.35], "early") is False
+    # late and far behind: even the optimistic gain cannot reach the best finished trial
+    assert _running(svc, name, [0.1, 0.2, 0.25, 0.28, 0.3, 0.31, 0.31, 0.32], "late") is True
+    # late and ahead of everything
+    assert _running(svc, name, [0.3, 0.6, 0.8, 0.9, 0.93, 0.95, 0.95, 0.96], "ahead") is False
+
+
+def test_median_rule_compares_at_equal_progress(svc):
+    name = _study(svc, "median", "RANDOM_SEARCH", stopping=MEDIAN)
+    for k, top in enumerate([0.9, 0.8, 0.7]):
+        _finish(svc, _suggest(svc, name, "f%d" % k), [top * (1 - math.exp(-0.7 * s)) for s in range(1, 9)])
+    assert _running(svc, name, [0.05, 0.1], "slow") is True          # below the median at step 2
+    assert _running(svc, name, [0.5, 0.75], "fast") is False
+    # the decay-curve rule would not have stopped the slow one that early
+    other = _study(svc, "decay2", "RANDOM_SEARCH", stopping=DECAY)
+    for k, top in enumerate([0.9, 0.8, 0.7]):
+        _finish(svc, _suggest(svc, other, "f%d" % k), [top * (1 - math.exp(-0.7 * s)) for s in range(1, 9)])
+    assert _running(svc, other, [0.25, 0.5], "slow") is False
+
+
+def test_stopping_rules_respect_a_minimising_goal_and_elapsed_time(svc):
+    name = _study(svc, "min", "RANDOM_SEARCH", goal="MINIMIZE",
+                  stopping={"decayCurveStoppingConfig": {"useElapsedTime": True}})
+    for k in range(3):
+        _finish(svc, _suggest(svc, name, "f%d" % k), [2.0 * math.exp(-0.4 * s) + 0.1 * k for s in range(8)])
+    t = _suggest(svc, name, "bad")
+    for step, loss in enumerate([3.0, 2.9, 2.9, 2.8, 2.8, 2.8, 2.8], 1):
+        svc.add_measurement(t["name"], {"measurement": {"stepCount": step, "elapsedTime": {"seconds": 10 * step},
+                                                        "metrics": [{"metric": "score", "value": loss}]}})
+    op = svc.check_early_stopping_state(t["name"])
+    assert svc.get_operation(op["name"])["response"]["shouldStop"] is True
+    fresh = _suggest(svc, name, "no-measurements")
+    op = svc.check_early_stopping_state(fresh["name"])
+    assert svc.get_operation(op["name"])["response"]["shouldStop"] is False
+
+
+def test_no_stopping_config_never_stops(svc):
+    name = _study(svc, "plain", "RANDOM_SEARCH")
+    for k in range(4):
+        _finish(svc, _suggest(svc, name, "f%d" % k), [0.9])
+    assert _running(svc, name, [0.0, 0.0, 0.0], "hopeless") is False
