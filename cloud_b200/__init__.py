@@ -5,11 +5,14 @@
 ``tfc.MachineConfig``, ``tfc.AcceleratorType``, ``tfc.COMMON_MACHINE_CONFIGS``,
 ``tfc.CloudOracle``, ``tfc.CloudTuner`` (+ ``tfc.DistributingCloudTuner``), and adds the runtime
 the reference outsources to TensorFlow: ``tfc.distribute`` (strategies + data-parallel engine on
-hand-written sm_100a kernels), ``tfc.keras`` (Keras-shaped front end), ``tfc.data``.
+hand-written sm_100a kernels), ``tfc.keras`` (Keras-shaped front end), ``tfc.data`` (tf.data-shaped
+pipeline), ``tfc.datasets`` (tfds-shaped synthetic catalogue), ``tfc.image``.
 """
 from .version import __version__  # noqa: F401
 
 from . import data  # noqa: F401,E402
+from . import datasets  # noqa: F401,E402
+from . import image  # noqa: F401,E402
 from . import distribute  # noqa: F401,E402
 from . import keras  # noqa: F401,E402
 from . import ops  # noqa: F401,E402

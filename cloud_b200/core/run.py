@@ -98,7 +98,10 @@ def run(entry_point=None, requirements_txt=None, distribution_strategy="auto",
 
 
 def _called_from_notebook():
-    """Detects a Jupyter / Colab kernel (run.py:249-263)."""
+    """Detects a Jupyter / Colab kernel (run.py:249-263), or the headless notebook runner
+    (``cloud_b200.utils.notebook``), which names the running notebook in ``TFC_NOTEBOOK_PATH``."""
+    if os.environ.get("TFC_NOTEBOOK_PATH"):
+        return True
     try:
         import IPython  # noqa: F401
     except ImportError:

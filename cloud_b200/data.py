@@ -273,3 +273,14 @@ class experimental:
 
     class AutoShardPolicy:
         OFF, AUTO, FILE, DATA = 0, 1, 2, 3
+
+    INFINITE_CARDINALITY = -1
+    UNKNOWN_CARDINALITY = -2
+
+    @staticmethod
+    def cardinality(dataset):
+        """``tf.data.experimental.cardinality(ds)`` (dogs_classification.ipynb prints it)."""
+        return dataset.cardinality()
+
+
+AUTOTUNE = -1

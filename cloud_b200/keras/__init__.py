@@ -5,6 +5,7 @@ core/tests/testdata); this package provides that surface on torch + the B200 ker
 scripts run after changing only their import line.
 """
 from . import layers, losses, metrics, optimizers, callbacks, applications, datasets, saving  # noqa: F401
+from . import initializers, regularizers  # noqa: F401
 from .layers import Input  # noqa: F401
 from .models import Model, Sequential, load_model, mixed_precision, model_from_json  # noqa: F401
 from . import models  # noqa: F401
@@ -18,36 +19,6 @@ class backend:
     @staticmethod
     def backend():
         return "cloud_b200"
-
-
-class initializers:
-    class Constant:
-        def __init__(self, value=0.0):
-            self.value = value
-            self.name = "constant"
-
-        def __call_tensor__(self, t):
-            return t.fill_(float(self.value))
-
-    class Zeros(Constant):
-        def __init__(self):
-            super().__init__(0.0)
-
-    class Ones(Constant):
-        def __init__(self):
-            super().__init__(1.0)
-
-
-class regularizers:
-    """Accepted for API compatibility; weight decay is expressed through the optimizer here."""
-
-    @staticmethod
-    def l2(l=0.01):
-        return ("l2", l)
-
-    @staticmethod
-    def l1(l=0.01):
-        return ("l1", l)
 
 
 class utils:

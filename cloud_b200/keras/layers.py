@@ -86,30 +86,9 @@ def get_activation(name):
 
 
 def _init_tensor(initializer, shape, fan_in, fan_out):
-    """Keras initializers on a tensor whose fans are given explicitly."""
-    t = torch.empty(shape, dtype=torch.float32)
-    if hasattr(initializer, "__call_tensor__"):
-        return initializer.__call_tensor__(t)
-    name = initializer if isinstance(initializer, str) else getattr(initializer, "name", None)
-    if name in ("glorot_uniform", None):
-        limit = math.sqrt(6.0 / (fan_in + fan_out))
-        return t.uniform_(-limit, limit)
-    if name == "glorot_normal":
-        return t.normal_(0, math.sqrt(2.0 / (fan_in + fan_out)))
-    if name in ("he_normal",):
-        return t.normal_(0, math.sqrt(2.0 / fan_in))
-    if name in ("he_uniform",):
-        limit = math.sqrt(6.0 / fan_in)
-        return t.uniform_(-limit, limit)
-    if name == "zeros":
-        return t.zero_()
-    if name == "ones":
-        return t.fill_(1.0)
-    if name == "random_normal":
-        return t.normal_(0, 0.05)
-    if name == "random_uniform":
-        return t.uniform_(-0.05, 0.05)
-    raise ValueError(f"Unknown initializer: {initializer}")
+    """A float32 tensor of ``shape`` filled by a Keras initializer (name, config dict or object)."""
+    from . import initializers
+    return initializers.get(initializer).fill(torch.empty(shape, dtype=torch.float32), fan_in, fan_out)
 
 
 class Layer(nn.Module):
@@ -126,6 +105,9 @@ class Layer(nn.Module):
         self.name = name or _auto_name(type(self).__name__)
         self._trainable = trainable
         self.built = False
+        from . import regularizers
+        self.kernel_regularizer = regularizers.get(kwargs.get("kernel_regularizer"))
+        self.bias_regularizer = regularizers.get(kwargs.get("bias_regularizer"))
         if input_shape is None and "input_dim" in kwargs:
             input_shape = (kwargs["input_dim"],)
         if batch_input_shape is not None:
@@ -148,6 +130,10 @@ class Layer(nn.Module):
         self._trainable = bool(v)
         for p in self.parameters():
             p.requires_grad_(bool(v))
+        self._on_trainable_changed()
+
+    def _on_trainable_changed(self):
+        pass
 
     def build(self, input_shape):
         pass
@@ -226,8 +212,23 @@ class Layer(nn.Module):
     def count_params(self):
         return sum(int(getattr(self, attr).numel()) for _s, attr, *_ in self._keras_weight_specs)
 
+    @property
+    def losses(self):
+        """Weight penalties of this layer (``kernel_regularizer`` / ``bias_regularizer``)."""
+        out = []
+        for reg, attr in ((self.kernel_regularizer, "kernel"), (self.bias_regularizer, "bias")):
+            w = getattr(self, attr, None) if reg is not None else None
+            if w is not None and (w.requires_grad or not torch.is_grad_enabled()):
+                out.append(reg(w))
+        return out
+
     def get_config(self):
-        return {"name": self.name, "trainable": self._trainable}
+        from . import regularizers
+        cfg = {"name": self.name, "trainable": self._trainable}
+        for key in ("kernel_regularizer", "bias_regularizer"):
+            if getattr(self, key) is not None:
+                cfg[key] = regularizers.serialize(getattr(self, key))
+        return cfg
 
     @classmethod
     def from_config(cls, config):
@@ -669,6 +670,16 @@ class BatchNormalization(Layer):
                 object.__setattr__(self, "_absorbed_conv", prev)   # not a submodule: no double registration
         return out
 
+    def _on_trainable_changed(self):
+        # A frozen batch-norm runs on its moving statistics (Keras semantics), which do not cancel a
+        # per-channel shift: the convolution in front has to add its bias itself again.
+        conv = self._absorbed_conv
+        if conv is not None:
+            conv.bias_absorbed_by_bn = self._trainable
+        if self.built:
+            self.gamma.requires_grad_(self._trainable and self.scale)
+            self.beta.requires_grad_(self._trainable and self.center)
+
     def call(self, x, training=False, relu=None, residual=None):
         if isinstance(x, (list, tuple)):       # [x, shortcut]: y = act(BN(x) + shortcut)
             x, residual = x
@@ -758,6 +769,9 @@ class Concatenate(Layer):
             ax = {0: 0, 1: 2, 2: 3, 3: 1}[ax]
         return torch.cat(list(xs), dim=ax)
 
+    def get_config(self):
+        return {**super().get_config(), "axis": self.axis}
+
 
 class Lambda(Layer):
     def __init__(self, function, **kwargs):
@@ -776,6 +790,9 @@ class Rescaling(Layer):
     def call(self, x, training=False):
         return x * self.scale + self.offset
 
+    def get_config(self):
+        return {**super().get_config(), "scale": self.scale, "offset": self.offset}
+
 
 class RandomFlip(Layer):
     """Horizontal/vertical random flip (core/tests/testdata/keras_tuner_cifar_example.py:24-31)."""
@@ -793,6 +810,9 @@ class RandomFlip(Layer):
             x = x.flip(2)
         return x
 
+    def get_config(self):
+        return {**super().get_config(), "mode": self.mode}
+
 
 class _IdentityAugment(Layer):
     """Geometry-changing augmentations are accepted and act as identity (shape-preserving)."""
@@ -800,6 +820,9 @@ class _IdentityAugment(Layer):
     def __init__(self, factor=0.0, **kwargs):
         super().__init__(**kwargs)
         self.factor = factor
+
+    def get_config(self):
+        return {**super().get_config(), "factor": self.factor}
 
 
 class RandomRotation(_IdentityAugment):

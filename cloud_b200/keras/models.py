@@ -544,6 +544,7 @@ class Model(nn.Module):
         self._strategy = get_strategy()
         self._engine = None
         self._graph = None
+        self._regularized_layers = None
 
     def _build_with_batch(self, xb):
         """Run one forward on a single sample batch to create lazily-built weights."""
@@ -569,6 +570,15 @@ class Model(nn.Module):
         self._engine = DPEngine(named, self.optimizer.spec(), st.communicator,
                                 compute_dtype=self._compute_dtype())
         self._graph_ok = all(getattr(l, "graph_safe", True) for l in self.modules())
+        cd = self._engine.compute_dtype
+        if cd != torch.float32:
+            # frozen matrices / conv kernels are not in the engine's arenas: give them the compute
+            # dtype (and the channels_last layout the trainable ones have) here
+            with torch.no_grad():
+                for p in self.parameters():
+                    if not p.requires_grad and p.dim() >= 2 and p.dtype != cd:
+                        fmt = torch.channels_last if p.dim() == 4 else torch.preserve_format
+                        p.data = p.data.to(dtype=cd, memory_format=fmt)
         pending = getattr(self, "_pending_optimizer_state", None)
         if pending:
             self._engine.load_master_state(pending)
@@ -590,6 +600,14 @@ class Model(nn.Module):
             with torch.no_grad():
                 aux[AUX_LOSS] += s.detach()
             loss = s * inv
+        penalty = self._regularization_loss()
+        if penalty is not None:
+            # Keras adds the weight penalties to the loss it minimises and reports.  Gradients are
+            # summed over replicas, so each adds its share (local batch / global batch) of one penalty.
+            n = float(out.shape[0])
+            with torch.no_grad():
+                aux[AUX_LOSS] += penalty.detach() * n
+            loss = loss + penalty * (n * inv)
         with torch.no_grad():
             aux[AUX_COUNT] += float(out.shape[0])
             for i, m in enumerate(self._metrics):
@@ -597,6 +615,46 @@ class Model(nn.Module):
                     continue
                 aux[AUX_METRIC0 + i] += m.batch_sum(y, out)
         return loss, fused
+
+    @property
+    def trainable(self):
+        return getattr(self, "_trainable", True)
+
+    @trainable.setter
+    def trainable(self, v):
+        """``model.trainable = False`` freezes every layer (the reference's transfer-learning
+        examples freeze the ResNet-50 base: call_run_within_script_with_keras_fit.py:79-87,
+        dogs_classification.ipynb).  As in Keras, it takes effect at the next ``compile()``."""
+        object.__setattr__(self, "_trainable", bool(v))
+        for m in self.modules():
+            if m is not self and isinstance(m, L.Layer):
+                m.trainable = bool(v)
+
+    @property
+    def losses(self):
+        """``tf.keras.Model.losses``: the weight penalties of all layers (see ``regularizers``)."""
+        out = []
+        for m in self.modules():
+            if m is not self and isinstance(m, L.Layer) and not isinstance(m, Model):
+                out.extend(m.losses)
+        return out
+
+    def _regularization_loss(self):
+        layers = getattr(self, "_regularized_layers", None)
+        if layers is None:              # found once per compile(): this runs every training step
+            layers = self._regularized_layers = [
+                m for m in self.modules() if m is not self and isinstance(m, L.Layer)
+                and not isinstance(m, Model)
+                and (m.kernel_regularizer is not None or m.bias_regularizer is not None)]
+        if not layers:
+            return None
+        terms = [t for m in layers for t in m.losses]
+        if not terms:
+            return None
+        total = terms[0]
+        for t in terms[1:]:
+            total = total + t
+        return total
 
     def _aux_len(self):
         return AUX_METRIC0 + len(self._metrics)

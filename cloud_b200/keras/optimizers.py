@@ -54,6 +54,28 @@ class schedules:  # tf.keras.optimizers.schedules.*
     PiecewiseConstantDecay = PiecewiseConstantDecay
 
 
+class _HyperParameter(float):
+    """What ``optimizer.lr`` / ``optimizer.learning_rate`` read as: a float that also answers the
+    ``tf.Variable`` calls user callbacks make on it (``.numpy()``, ``.assign(v)``) - e.g. the
+    ``PrintLR`` callback of the reference's examples (testdata/mnist_example_using_fit.py:82-88)."""
+
+    def __new__(cls, value, owner=None):
+        self = super().__new__(cls, value)
+        self._owner = owner
+        return self
+
+    def numpy(self):
+        return float(self)
+
+    def assign(self, value):
+        if self._owner is not None:
+            self._owner.learning_rate = value
+        return _HyperParameter(value, self._owner)
+
+    def __reduce__(self):
+        return (float, (float(self),))
+
+
 class Optimizer:
     _name = "optimizer"
 
@@ -61,28 +83,30 @@ class Optimizer:
         if lr is not None:           # legacy spelling used by the reference's tuner tests
             learning_rate = lr
         self._schedule = learning_rate if callable(learning_rate) else None
-        self.learning_rate = float(learning_rate(0)) if self._schedule else float(learning_rate)
+        self._lr = float(learning_rate(0)) if self._schedule else float(learning_rate)
         self.iterations = 0
         self.name = name or type(self).__name__
 
     @property
-    def lr(self):
-        return self.learning_rate
+    def learning_rate(self):
+        return _HyperParameter(self._lr, self)
 
-    @lr.setter
-    def lr(self, v):
-        self.learning_rate = float(v)
+    @learning_rate.setter
+    def learning_rate(self, v):
+        self._lr = float(v)
+
+    lr = learning_rate
 
     def current_lr(self) -> float:
         if self._schedule is not None:
             return float(self._schedule(self.iterations))
-        return self.learning_rate
+        return self._lr
 
     def spec(self) -> OptimizerSpec:
         raise NotImplementedError
 
     def get_config(self):
-        cfg = {"name": self.name, "learning_rate": self.learning_rate}
+        cfg = {"name": self.name, "learning_rate": self._lr}
         if self._schedule is not None:
             cfg["learning_rate"] = {"class_name": type(self._schedule).__name__,
                                     "config": self._schedule.get_config()}

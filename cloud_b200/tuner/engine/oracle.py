@@ -216,7 +216,13 @@ class RandomSearchOracle(Oracle):
     """Plain random search (KerasTuner's RandomSearch oracle) - the fully local tuner path."""
 
     def _populate_space(self, trial_id):
-        return {"status": trial_lib.TrialStatus.RUNNING, "values": self._random_values()}
+        # like KerasTuner, the first trial evaluates the declared defaults: a sensible baseline
+        # that every later random point has to beat
+        if not self.trials:
+            values = {hp.name: hp.default for hp in self.hyperparameters.space}
+        else:
+            values = self._random_values()
+        return {"status": trial_lib.TrialStatus.RUNNING, "values": values}
 
     def _score_trial(self, trial):
         obj = self.objective[0] if isinstance(self.objective, list) else self.objective

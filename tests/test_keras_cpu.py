@@ -271,3 +271,106 @@ def test_learning_rate_schedules_and_metrics_objects():
     mean.update_state(4.0)
     assert float(mean.result()) == pytest.approx(3.0)
     mean.reset_states() if hasattr(mean, "reset_states") else mean.reset_state()
+
+
+# -- regularizers, initializers, frozen layers (the cloud_fit test model of the reference uses all of
+# them: experimental/cloud_fit/tests/unit/client_test.py:69-90) ------------------------------------
+def test_weight_penalty_is_part_of_the_loss_and_of_the_gradient():
+    inp = L.Input(shape=(1,))
+    times_w = L.Dense(1, kernel_initializer=keras.initializers.Constant([[0.5]]),
+                      kernel_regularizer=keras.regularizers.l2(0.01), use_bias=False)
+    plus_1 = L.Dense(1, kernel_initializer=keras.initializers.Constant([[1.0]]),
+                     bias_initializer=keras.initializers.Constant([1.0]), trainable=False)
+    model = keras.Model(inp, plus_1(times_w(inp)))
+    model.compile(keras.optimizers.SGD(0.002), "mean_squared_error", run_eagerly=True)
+    x = np.array([[9.], [10.], [11.]] * 10, dtype="float32")
+    y = x / 2 + 6
+    hist = model.fit(x, y, batch_size=len(x), epochs=1, verbose=0)
+    # loss = mean((0.5 x + 1 - y)^2) + 0.01 * 0.5^2 ; dloss/dw = mean(2 (0.5 x + 1 - y) x) + 0.02 * 0.5
+    assert hist.history["loss"][0] == pytest.approx(25.0 + 0.0025, rel=1e-6)
+    w, frozen_w, frozen_b = model.get_weights()
+    assert w[0, 0] == pytest.approx(0.5 + 0.002 * (100.0 - 0.01), rel=1e-6)
+    assert frozen_w[0, 0] == 1.0 and frozen_b[0] == 1.0
+    assert len(model.losses) == 1 and float(model.losses[0].detach()) == pytest.approx(0.01 * w[0, 0] ** 2, rel=1e-5)
+    assert model.evaluate(x, y, verbose=0) == pytest.approx(
+        float(np.mean((w[0, 0] * x + 1 - y) ** 2)) + 0.01 * w[0, 0] ** 2, rel=1e-5)
+    # the penalty survives a save / load round trip through the layer config
+    clone = keras.Model.from_config(model.get_config())
+    assert clone.layers[0].kernel_regularizer.l2 == pytest.approx(0.01)
+    assert keras.regularizers.get("l1_l2").l1 == 0.01 and keras.regularizers.get(None) is None
+    assert float(keras.regularizers.l1_l2(0.5, 0.25)(torch.tensor([1.0, -2.0]))) == pytest.approx(0.5 * 3 + 0.25 * 5)
+
+
+def test_initializers_have_keras_statistics_and_configs():
+    init = keras.initializers
+    t = init.get("glorot_uniform").fill(torch.empty(400, 600), 400, 600)
+    limit = (6.0 / 1000) ** 0.5
+    assert t.abs().max() <= limit and t.std() == pytest.approx(limit / 3 ** 0.5, rel=0.05)
+    t = init.HeNormal(seed=1).fill(torch.empty(512, 512), 512, 512)
+    assert t.std() == pytest.approx((2.0 / 512) ** 0.5, rel=0.05)
+    assert torch.equal(t, init.HeNormal(seed=1).fill(torch.empty(512, 512), 512, 512))     # seeded
+    assert init.Constant([[1.0, 2.0]]).fill(torch.empty(1, 2), 1, 2).tolist() == [[1.0, 2.0]]
+    assert init.get("zeros").fill(torch.empty(3), 1, 1).sum() == 0
+    cfg = init.serialize(init.RandomNormal(stddev=0.2, seed=3))
+    assert init.get(cfg).stddev == 0.2 and cfg["class_name"] == "RandomNormal"
+    with pytest.raises(ValueError, match="Unknown initializer"):
+        init.get("no_such_init")
+    dense = L.Dense(4, kernel_initializer=init.RandomUniform(-0.01, 0.01), bias_initializer="ones")
+    dense(torch.zeros(2, 8))
+    assert dense.kernel.abs().max() <= 0.01 and dense.bias.tolist() == [1.0] * 4
+
+
+def test_frozen_base_keeps_its_weights_and_runs_batch_norm_on_moving_statistics():
+    inp = L.Input(shape=(8, 8, 3))
+    x = L.Conv2D(4, 3, padding="same", name="c1")(inp)          # its bias is absorbed while BN trains
+    x = L.ReLU()(L.BatchNormalization(name="bn1")(x))
+    base = keras.Model(inp, x)
+    head = L.Dense(3, name="head")
+    model = keras.Model(inp, head(L.GlobalAveragePooling2D()(base.output)))
+    base.trainable = False
+    conv, bn = model.get_layer("c1"), model.get_layer("bn1")
+    assert not base.trainable and not conv.trainable and conv.bias_absorbed_by_bn is False
+    with torch.no_grad():
+        conv.bias.fill_(0.7)
+        bn.moving_mean.fill_(0.1)
+        bn.moving_variance.fill_(2.0)
+    model.compile(keras.optimizers.SGD(0.1), keras.losses.SparseCategoricalCrossentropy(from_logits=True))
+    assert len(model.trainable_weights) == 2
+    rng = np.random.default_rng(0)
+    xs, ys = rng.normal(size=(16, 8, 8, 3)).astype("float32"), rng.integers(0, 3, 16)
+    before = [w.copy() for w in base.get_weights()]
+    head_before = None
+    first = model.train_on_batch(xs, ys)
+    head_before = [w.copy() for w in head.get_weights()]
+    model.fit(xs, ys, batch_size=8, epochs=2, verbose=0)
+    assert all(np.array_equal(a, b) for a, b in zip(before, base.get_weights()))      # incl. moving stats
+    assert not np.array_equal(head_before[0], head.get_weights()[0])
+    ref = torch.nn.functional.conv2d(torch.tensor(xs).permute(0, 3, 1, 2), conv.kernel.float(),
+                                     conv.bias.float(), padding=1)
+    ref = torch.nn.functional.batch_norm(ref, bn.moving_mean, bn.moving_variance, bn.gamma, bn.beta,
+                                         False, 0.0, bn.epsilon).relu().mean((2, 3))
+    ref = ref @ head.kernel.float().t() + head.bias
+    np.testing.assert_allclose(model.predict(xs), ref.detach().numpy(), atol=1e-5)
+    assert np.isfinite(first)
+    base.trainable = True
+    assert conv.bias_absorbed_by_bn is True and bn.gamma.requires_grad
+
+
+def test_optimizer_learning_rate_reads_like_a_variable():
+    opt = keras.optimizers.Adam(learning_rate=3e-4)
+    assert opt.lr.numpy() == pytest.approx(3e-4) and opt.learning_rate == pytest.approx(3e-4)
+    opt.lr = 1e-2
+    assert opt.learning_rate.numpy() == pytest.approx(1e-2) and opt.current_lr() == pytest.approx(1e-2)
+    opt.learning_rate.assign(5e-3)
+    assert float(opt.lr) == pytest.approx(5e-3)
+    assert json.loads(json.dumps(opt.get_config()))["learning_rate"] == pytest.approx(5e-3)
+
+
+def test_layer_configs_round_trip():
+    cases = [L.Rescaling(1 / 255.0, offset=-1), L.RandomFlip("horizontal"), L.RandomRotation(0.1),
+             L.Concatenate(axis=1), L.Reshape((2, 2)), L.ZeroPadding2D(((1, 2), (3, 4))),
+             L.Dense(4, activation="relu", kernel_regularizer=keras.regularizers.l2(0.5))]
+    for layer in cases:
+        cfg = layer.get_config()
+        clone = type(layer).from_config(dict(cfg))
+        assert clone.get_config() == cfg, type(layer).__name__
