@@ -16,8 +16,10 @@ from . import image  # noqa: F401,E402
 from . import distribute  # noqa: F401,E402
 from . import keras  # noqa: F401,E402
 from . import ops  # noqa: F401,E402
+from . import nn  # noqa: F401,E402
 
 _LAZY = {
+    "GradientTape": ("cloud_b200.keras.tape", "GradientTape"),
     "run": ("cloud_b200.core.run", "run"),
     "remote": ("cloud_b200.core.run", "remote"),
     "MachineConfig": ("cloud_b200.core.machine_config", "MachineConfig"),

@@ -7,6 +7,7 @@ scripts run after changing only their import line.
 from . import layers, losses, metrics, optimizers, callbacks, applications, datasets, saving  # noqa: F401
 from . import initializers, regularizers  # noqa: F401
 from .layers import Input  # noqa: F401
+from .tape import GradientTape  # noqa: F401
 from .models import Model, Sequential, load_model, mixed_precision, model_from_json  # noqa: F401
 from . import models  # noqa: F401
 

@@ -20,14 +20,16 @@ class Metric:
         """Sum of the per-sample metric over the local batch (0-d tensor on the device)."""
         raise NotImplementedError
 
-    # stand-alone use (custom training loops, mnist_example_using_ctl.py:63-66,139-141)
+    # stand-alone use (custom training loops, mnist_example_using_ctl.py:63-66,139-141): the
+    # accumulators are per replica - each replica sees its own shard of every batch, so result()
+    # is that replica's estimate; sum (sum, count) pairs with strategy.reduce for a global number
     def reset_states(self):
         self._sum, self._count = 0.0, 0.0
 
     reset_state = reset_states
 
     def update_state(self, y_true, y_pred, sample_weight=None):
-        y_true, y_pred = torch.as_tensor(y_true), torch.as_tensor(y_pred)
+        y_true, y_pred = torch.as_tensor(y_true), torch.as_tensor(y_pred).detach()
         self._sum += float(self.batch_sum(y_true.to(y_pred.device), y_pred))
         self._count += float(y_pred.shape[0])
 
@@ -83,7 +85,7 @@ class Mean(Metric):
     name = "mean"
 
     def update_state(self, values, sample_weight=None):
-        v = torch.as_tensor(values).float()
+        v = torch.as_tensor(values).detach().float()
         self._sum += float(v.sum())
         self._count += float(v.numel())
 

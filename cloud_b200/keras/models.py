@@ -569,6 +569,8 @@ class Model(nn.Module):
         named = [(n, p) for n, p in self.named_parameters()]
         self._engine = DPEngine(named, self.optimizer.spec(), st.communicator,
                                 compute_dtype=self._compute_dtype())
+        self.optimizer._engine = self._engine         # custom loops on a compiled model share it
+        self.optimizer._engine_vars = tuple(id(p) for _n, p in named if p.requires_grad)
         self._graph_ok = all(getattr(l, "graph_safe", True) for l in self.modules())
         cd = self._engine.compute_dtype
         if cd != torch.float32:

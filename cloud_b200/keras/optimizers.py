@@ -97,6 +97,69 @@ class Optimizer:
 
     lr = learning_rate
 
+    # -- custom training loops (testdata/mnist_example_using_ctl.py:128-129) --------------------
+    def _engine_for(self, variables):
+        """The data-parallel engine that owns ``variables``: the one ``Model.compile`` + ``fit``
+        created for this optimizer, else one built here on first use."""
+        eng = getattr(self, "_engine", None)
+        ids = tuple(id(v) for v in variables)
+        if eng is not None and getattr(self, "_engine_vars", ids) == ids:
+            return eng
+        import torch
+        from ..distribute import get_strategy
+        from ..parallel.engine import DPEngine
+        from . import models
+        st = get_strategy()
+        dev = st.device
+        for v in variables:
+            if v.device != dev:
+                v.data = v.data.to(dev)
+        cd = torch.bfloat16 if dev.type == "cuda" and models.mixed_precision.global_policy() == "mixed_bfloat16" \
+            else torch.float32
+        named = [("variable_{}".format(i), v) for i, v in enumerate(variables)]
+        self._engine = DPEngine(named, self.spec(), st.communicator, compute_dtype=cd)
+        self._engine_vars = ids
+        return self._engine
+
+    def apply_gradients(self, grads_and_vars, name=None, **kwargs):
+        """Sums the gradients over replicas and applies the update (one fused kernel per bucket).
+        As in ``tf.distribute``, per-replica losses are expected to be scaled by 1 / global batch."""
+        pairs = [(g, v) for g, v in grads_and_vars]
+        variables = [v for _g, v in pairs if v.requires_grad]
+        eng = self._engine_for(variables)
+        if not eng.in_step:
+            eng.begin_step()
+        eng.set_lr(self.current_lr())
+        import torch
+        with torch.no_grad():
+            for g, v in pairs:
+                if g is not None and v.requires_grad:
+                    v.grad.copy_(g)
+        eng.end_step()
+        self.iterations += 1
+        return self.iterations
+
+    def minimize(self, loss, var_list, grad_loss=None, name=None, tape=None):
+        """Backward pass with the bucketed all-reduce + update overlapped (the path ``fit`` uses).
+        ``loss`` may be a tensor or, as in Keras, a callable returning one."""
+        variables = [v for v in (var_list() if callable(var_list) else var_list) if v.requires_grad]
+        if getattr(self, "_engine", None) is None or \
+                getattr(self, "_engine_vars", None) not in (None, tuple(id(v) for v in variables)):
+            # the engine moves the variables into its arena: not possible between forward and backward
+            from .tape import GradientTape
+            t = tape if tape is not None else GradientTape()
+            value = loss() if callable(loss) else loss
+            return self.apply_gradients(zip(t.gradient(value, variables), variables))
+        eng = self._engine
+        if not eng.in_step:
+            eng.begin_step()
+        eng.set_lr(self.current_lr())
+        value = loss() if callable(loss) else loss
+        value.backward(grad_loss)
+        eng.end_step()
+        self.iterations += 1
+        return self.iterations
+
     def current_lr(self) -> float:
         if self._schedule is not None:
             return float(self._schedule(self.iterations))

@@ -21,6 +21,7 @@ the CPU (gloo) implementation of identical semantics.
 from __future__ import annotations
 
 import os
+import weakref
 from dataclasses import dataclass, field
 
 import torch
@@ -80,6 +81,14 @@ def _round_up(x: int, m: int) -> int:
     return (x + m - 1) // m * m
 
 
+_LIVE: "weakref.WeakSet" = weakref.WeakSet()
+
+
+def live_engines() -> list:
+    """Engines of this process (custom training loops arm them when a GradientTape opens)."""
+    return list(_LIVE)
+
+
 class DPEngine:
     def __init__(self, named_params, optimizer: OptimizerSpec, communicator: Communicator,
                  *, compute_dtype: torch.dtype | None = None, bucket_mb: float | None = None,
@@ -120,6 +129,11 @@ class DPEngine:
             except ValueError:
                 raise ValueError("TFC_FAULT must look like '<rank>:<step>', got {!r}".format(fault))
         self._build(list(named_params))
+        _LIVE.add(self)
+
+    @property
+    def in_step(self) -> bool:
+        return self._in_step
 
     # ------------------------------------------------------------------------------------------
     def _build(self, named_params) -> None:

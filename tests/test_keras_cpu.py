@@ -374,3 +374,73 @@ def test_layer_configs_round_trip():
         cfg = layer.get_config()
         clone = type(layer).from_config(dict(cfg))
         assert clone.get_config() == cfg, type(layer).__name__
+
+
+# -- custom training loops (reference: core/tests/testdata/mnist_example_using_ctl.py:103-131) -----
+def _ctl_model():
+    torch.manual_seed(3)
+    return keras.Sequential([L.Dense(16, activation="relu", input_shape=(20,)), L.Dense(4)])
+
+
+def test_gradient_tape_and_apply_gradients_match_fit():
+    x, y = _blobs(128)
+    loss_object = keras.losses.SparseCategoricalCrossentropy(from_logits=True,
+                                                             reduction=keras.losses.Reduction.NONE)
+    ctl, opt = _ctl_model(), keras.optimizers.Adam(1e-2)
+    for step in range(6):
+        xb, yb = x[step * 16:(step + 1) * 16], y[step * 16:(step + 1) * 16]
+        with tfc.GradientTape() as tape:
+            logits = ctl(xb, training=True)
+            loss = tfc.nn.compute_average_loss(loss_object(yb, logits), global_batch_size=16)
+        grads = tape.gradient(loss, ctl.trainable_variables)
+        assert len(grads) == 4 and all(g is not None for g in grads)
+        opt.apply_gradients(zip(grads, ctl.trainable_variables))
+    assert opt.iterations == 6
+    fitted = _ctl_model()
+    fitted.compile(keras.optimizers.Adam(1e-2), keras.losses.SparseCategoricalCrossentropy(from_logits=True))
+    fitted.fit(x[:96], y[:96], batch_size=16, epochs=1, shuffle=False, verbose=0)
+    for a, b in zip(ctl.get_weights(), fitted.get_weights()):
+        np.testing.assert_allclose(a, b, rtol=1e-5, atol=1e-6)
+
+
+def test_minimize_overlaps_the_update_with_backward_and_matches_apply_gradients():
+    x, y = _blobs(64)
+    xent = keras.losses.SparseCategoricalCrossentropy(from_logits=True)
+    a, opt_a = _ctl_model(), keras.optimizers.SGD(0.1, momentum=0.9)
+    b, opt_b = _ctl_model(), keras.optimizers.SGD(0.1, momentum=0.9)
+    for step in range(4):
+        xb, yb = x[step * 16:(step + 1) * 16], y[step * 16:(step + 1) * 16]
+        with tfc.GradientTape() as tape:
+            loss = xent(yb, a(xb, training=True))
+        opt_a.minimize(loss, a.trainable_variables, tape=tape)          # step 0: engine is created here
+        with tfc.GradientTape() as tape:
+            loss = xent(yb, b(xb, training=True))
+        opt_b.apply_gradients(zip(tape.gradient(loss, b.trainable_variables), b.trainable_variables))
+    for wa, wb in zip(a.get_weights(), b.get_weights()):
+        np.testing.assert_allclose(wa, wb, rtol=1e-5, atol=1e-6)
+    # Keras also accepts a callable loss
+    before = a.get_weights()[0].copy()
+    opt_a.minimize(lambda: xent(y[:16], a(x[:16], training=True)), a.trainable_variables)
+    assert not np.array_equal(before, a.get_weights()[0]) and opt_a.iterations == 5
+
+
+def test_tape_details():
+    w = torch.nn.Parameter(torch.tensor([1.0, 2.0]))
+    unused = torch.nn.Parameter(torch.tensor([5.0]))
+    x = torch.tensor([3.0, 4.0])
+    with tfc.GradientTape(persistent=True) as tape:
+        tape.watch(x)
+        out = (w * x).sum()
+    assert tape.gradient(out, w).tolist() == [3.0, 4.0]
+    assert tape.gradient(out, x).tolist() == [1.0, 2.0]                   # persistent: a second call
+    g = tape.gradient(out, [w, unused])
+    assert g[1] is None
+    assert tape.gradient(out, [w, unused], unconnected_gradients="zero")[1].tolist() == [0.0]
+    with tfc.GradientTape() as once:
+        out = (w * w).sum()
+    once.gradient(out, w)
+    with pytest.raises(RuntimeError, match="non-persistent"):
+        once.gradient(out, w)
+    per_example = torch.tensor([1.0, 2.0, 3.0])
+    assert float(tfc.nn.compute_average_loss(per_example, global_batch_size=6)) == 1.0
+    assert float(tfc.nn.compute_average_loss(per_example)) == 2.0          # one replica: plain mean
