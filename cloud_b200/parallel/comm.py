@@ -1,11 +1,14 @@
 """Communicator: the data-parallel engine's view of "the other replicas".
 
-Three back ends behind one interface:
+Four back ends behind one interface:
 
 * ``p2p``   - hand-written sm_100a kernels over symmetric NVLink memory
               (``csrc/kernels/comm.cu``: one-shot / two-shot / NVLS, fused with the optimizer).
               This is the product path on a multi-GPU B200 box.
 * ``local`` - world size 1: the same fused kernels with no peers (CUDA) or plain PyTorch (CPU).
+* ``shm``   - CPU ranks of one box: the one-shot / two-shot schedules and the epoch-flag protocol of
+              the kernels over a POSIX shared-memory segment (``csrc/runtime/shm_comm.cc``);
+              gradients live in the segment, so the all-reduce is in place.  Default for CPU ranks.
 * ``dist``  - ``torch.distributed`` all-reduce (NCCL on GPUs, gloo on CPUs) followed by the flat
               optimizer kernel.  Baseline / oracle / CPU test path, and the fallback when peer
               mapping is impossible; never chosen silently on a box where p2p works.
@@ -57,8 +60,9 @@ class Communicator:
             elif device.type == "cuda":
                 backend = "p2p"
             else:
-                backend = "dist"
+                backend = "shm"
         self.backend = backend
+        self.shm = None            # ShmArena (CPU ranks)
         self.xchg = None
         self.pad = None            # SymmetricBuffer (flags + aux)
         self.epochs = None
@@ -66,6 +70,8 @@ class Communicator:
         self.multicast = False
         if device.type == "cuda" and backend in ("p2p", "local"):
             self._init_symm()
+        if backend == "shm":
+            self._init_shm()
         if self.aux is None:
             self.aux = torch.zeros(AUX_FLOATS, dtype=torch.float32, device=device)
 
@@ -99,9 +105,36 @@ class Communicator:
         self.epochs = torch.zeros(COMM_MAX_BLOCKS, dtype=torch.int32, device=self.device)
         self.aux = self.pad.view(torch.float32, AUX_FLOATS, COMM_MAX_BLOCKS * MAX_RANKS * 4)
 
+    def _init_shm(self) -> None:
+        from . import shm
+        if self.device.type != "cpu" or self.world == 1:
+            self.backend = "dist" if self.world > 1 else "local"
+            return
+        try:
+            nbytes = int(float(os.environ.get("TFC_SHM_ARENA_MB", "256")) * (1 << 20))
+            self.shm = shm.ShmArena(nbytes, self.group)
+        except (shm.ShmError, _lib.KernelsUnavailable, OSError) as e:
+            warnings.warn(f"cloud_b200: shared-memory arena unavailable ({e}); using "
+                          f"torch.distributed all-reduce instead")
+            self.backend = "dist"
+            self.shm = None
+            return
+        self.aux = self.shm.aux
+
     @property
     def uses_peer_memory(self) -> bool:
         return self.pad is not None
+
+    def alloc_flat(self, numel: int, dtype: torch.dtype) -> torch.Tensor:
+        """A zero-filled flat tensor for gradients: inside the shared segment when this
+        communicator has one (so ``all_reduce_sum`` on it - or on a slice of it - is in place)."""
+        if self.shm is not None:
+            nbytes = numel * torch.empty((), dtype=dtype).element_size()
+            if nbytes + 64 <= self.shm.free_bytes:
+                return self.shm.tensor(numel, dtype)
+            warnings.warn(f"cloud_b200: {nbytes >> 20} MiB of gradients do not fit the shared-memory "
+                          f"arena (TFC_SHM_ARENA_MB); this group goes through torch.distributed")
+        return torch.zeros(numel, dtype=dtype, device=self.device)
 
     def alloc_pair(self, nbytes_grad: int, nbytes_param: int):
         """Symmetric (grad, param) arenas for one parameter group; plain tensors otherwise."""
@@ -160,6 +193,10 @@ class Communicator:
 
     # -- torch.distributed fallbacks ----------------------------------------------------------
     def all_reduce_sum(self, t: torch.Tensor) -> torch.Tensor:
+        if self.world > 1 and self.shm is not None and t.dtype in (torch.float32, torch.bfloat16) \
+                and self.shm.offset_of(t) is not None:
+            self.shm.all_reduce(t)
+            return t
         if self.world > 1:
             if t.dtype == torch.bfloat16 and t.device.type == "cpu":
                 f = t.float()

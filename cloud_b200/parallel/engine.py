@@ -191,7 +191,7 @@ class DPEngine:
             g.algo = self._pick_algo(g, n * itemsize)
             g.sharded = g.algo != comm_mod.ALGO_ONESHOT and self.world > 1
         else:
-            g.grad_arena = torch.zeros(n, dtype=g.dtype, device=self.device)
+            g.grad_arena = self.comm.alloc_flat(n, g.dtype)        # in the shared segment on CPU ranks
             g.param_arena = torch.zeros(n, dtype=g.dtype, device=self.device)
         n_state = n // self.world if g.sharded else n
         code = self.opt.code
@@ -362,6 +362,9 @@ class DPEngine:
                                 s2=None, state_off=0, hyper=self.hyper, zero_grads=True,
                                 aux_len=n, aux_out=self.aux_out, blocks=1,
                                 stream=self.comm_stream)
+            return self.aux_out[:n]
+        if self.world > 1 and getattr(self.comm, "shm", None) is not None:
+            self.aux_out[:n].copy_(self.comm.shm.reduce_aux(n))     # the scalars ride in the signal pad
             return self.aux_out[:n]
         self.aux_out[:n].copy_(self.comm.aux[:n])
         self.comm.aux[:n].zero_()

@@ -24,6 +24,7 @@
 #include <vector>
 
 #include "rt_common.h"
+#include "cloud_b200_runtime.h"   // the public declarations must match the definitions below
 
 namespace {
 

@@ -11,6 +11,7 @@
 #include <thread>
 
 #include "monitoring.h"
+#include "cloud_b200_runtime.h"   // the public declarations must match the definitions below
 #include "rt_common.h"
 
 namespace cb2mon {

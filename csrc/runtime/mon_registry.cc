@@ -8,6 +8,7 @@
 #include <cstring>
 
 #include "monitoring.h"
+#include "cloud_b200_runtime.h"   // the public declarations must match the definitions below
 
 namespace cb2mon {
 

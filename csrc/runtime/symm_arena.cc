@@ -22,6 +22,7 @@
 #include <mutex>
 
 #include "rt_common.h"
+#include "cloud_b200_runtime.h"   // the public declarations must match the definitions below
 
 namespace {
 

@@ -1,5 +1,7 @@
-"""Multi-process CPU tests (gloo, world_size 2): the host-side logic of the data-parallel engine -
-bucketing, hooks, broadcast, metric reduction, chief-only saving - without a GPU.  The reference
+"""Multi-process CPU tests (world_size 2 and 3): the host-side logic of the data-parallel engine -
+bucketing, hooks, broadcast, metric reduction, chief-only saving - without a GPU, over both CPU
+transports: the shared-memory collectives that mirror the GPU kernels' schedules and flag protocol
+(default for CPU ranks) and plain torch.distributed / gloo.  The reference
 never really tests multi-node (mocked, TF_CONFIG-faked or process pools)."""
 import os
 import subprocess
@@ -19,10 +21,26 @@ def _torchrun(script, nproc, env_extra, port, timeout=240):
     return subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=timeout)
 
 
-@pytest.mark.parametrize("nproc", [2, 3])
-def test_mirrored_equals_single_replica_cpu(tmp_path, nproc):
-    res = _torchrun(os.path.join(ROOT, "tests", "dist_train_check.py"), nproc,
-                    {"CHECK_DEVICE": "cpu", "CUDA_VISIBLE_DEVICES": "", "CHECK_OUT": str(tmp_path)},
-                    port=29610 + nproc)
+@pytest.mark.parametrize("nproc,backend", [(2, "shm"), (3, "shm"), (2, "dist"), (3, "dist")])
+def test_mirrored_equals_single_replica_cpu(tmp_path, nproc, backend):
+    env = {"CHECK_DEVICE": "cpu", "CUDA_VISIBLE_DEVICES": "", "CHECK_OUT": str(tmp_path)}
+    if backend != "shm":                       # shm is what CPU ranks pick by themselves
+        env["TFC_COMM_BACKEND"] = backend
+    res = _torchrun(os.path.join(ROOT, "tests", "dist_train_check.py"), nproc, env,
+                    port=29610 + nproc + (10 if backend == "dist" else 0))
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
-    assert "OK world=%d backend=dist" % nproc in res.stdout
+    assert "OK world=%d backend=%s" % (nproc, backend) in res.stdout
+
+
+def test_shared_memory_collectives_across_processes(tmp_path):
+    res = _torchrun(os.path.join(ROOT, "tests", "shm_collectives_check.py"), 4,
+                    {"CUDA_VISIBLE_DEVICES": ""}, port=29631)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    assert "SHM OK world=4" in res.stdout
+
+
+def test_a_rank_that_never_arrives_fails_the_others_instead_of_hanging(tmp_path):
+    res = _torchrun(os.path.join(ROOT, "tests", "shm_collectives_check.py"), 3,
+                    {"CUDA_VISIBLE_DEVICES": "", "SHM_CHECK_ABSENT_RANK": "2"}, port=29632)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    assert res.stdout.count("WATCHDOG OK") == 2 and "for rank 2" in res.stdout
