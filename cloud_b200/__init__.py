@@ -17,6 +17,7 @@ from . import distribute  # noqa: F401,E402
 from . import keras  # noqa: F401,E402
 from . import ops  # noqa: F401,E402
 from . import nn  # noqa: F401,E402
+from . import models  # noqa: F401,E402
 
 _LAZY = {
     "GradientTape": ("cloud_b200.keras.tape", "GradientTape"),

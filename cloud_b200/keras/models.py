@@ -914,6 +914,12 @@ class Model(nn.Module):
                 self._mon_ready = True
             mon.observe(mon.STEP_TIME, seconds / steps * 1e6)
             mon.set_gauge(mon.IMAGES_PER_SEC, int(samples / seconds))
+            prof = getattr(self, "_fit_profile", None)
+            if prof and prof.get("steps"):
+                mon.observe(mon.DATA_WAIT, prof["wait_data_s"] / prof["steps"] * 1e6)
+            for us in eng.allreduce_host_us[-4096:]:
+                mon.observe(mon.ALLREDUCE_TIME, us)
+            del eng.allreduce_host_us[:]
             n_buckets = sum(len(g.buckets) for g in eng.groups)
             mon.increment(mon.BUCKET_LAUNCHES, steps * n_buckets)
             if eng.world > 1:

@@ -21,6 +21,7 @@ the CPU (gloo) implementation of identical semantics.
 from __future__ import annotations
 
 import os
+import time
 import weakref
 from dataclasses import dataclass, field
 
@@ -119,6 +120,7 @@ class DPEngine:
         self.steps = 0
         self.aux_out = torch.zeros(comm_mod.AUX_FLOATS, dtype=torch.float32, device=self.device)
         self._hook_handles = []
+        self.allreduce_host_us: list = []      # drained by the front end into the metrics registry
         self._in_step = False
         self._fault = None
         fault = os.environ.get("TFC_FAULT")
@@ -328,7 +330,10 @@ class DPEngine:
             return
         grad = g.grad_arena[b.off:b.off + b.length]
         if self.world > 1:
+            t0 = time.perf_counter()
             self.comm.all_reduce_sum(grad)
+            if not self.is_cuda:          # host-timed only where the call is synchronous
+                self.allreduce_host_us.append((time.perf_counter() - t0) * 1e6)
         sl = slice(b.off, b.off + b.length)
         optim_flat(code, master=None if g.master is None else g.master[sl], grad=grad,
                    s1=None if g.s1 is None else g.s1[sl], s2=None if g.s2 is None else g.s2[sl],

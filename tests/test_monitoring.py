@@ -72,3 +72,25 @@ print("exports", m.export_count())
     assert res.returncode == 0, res.stderr
     assert "exports" in res.stdout
     assert "my_counter 3" in out.read_text()
+
+
+def test_fit_feeds_the_hot_path_metrics(tmp_path):
+    """The engine's own metrics (step time, data wait, throughput, bucket
+    launches) reach the sink after a fit; the defaults of the allow-list are exactly these."""
+    out = tmp_path / "fit.jsonl"
+    code = """
+import numpy as np
+import cloud_b200 as tfc
+from cloud_b200 import monitoring as m
+tfc.distribute.experimental_set_strategy(tfc.distribute.OneDeviceStrategy("/cpu:0"))
+model = tfc.models.compiled("mnist_mlp")
+model.fit(np.random.rand(256, 784).astype("float32"), np.random.randint(0, 10, 256), batch_size=64, epochs=2, verbose=0)
+m.export_now()
+"""
+    res = _run(code, {"TFC_MONITORING_SINK": "jsonl:%s" % out, "CUDA_VISIBLE_DEVICES": ""})
+    assert res.returncode == 0, res.stderr
+    series = [s for l in out.read_text().splitlines() for s in json.loads(l).get("request", {}).get("time_series", [])]
+    by_type = {s["metric"]["type"].split("cloud_b200/")[1]: s for s in series}
+    assert {"train/step_time_usecs", "data/wait_usecs", "train/images_per_sec", "comm/bucket_launches"} <= set(by_type)
+    assert by_type["data/wait_usecs"]["points"]["value"]["distribution_value"]["count"] == 2       # one per epoch
+    assert int(by_type["comm/bucket_launches"]["points"]["value"]["int64_value"]) == 8             # 4 steps x 2 epochs
