@@ -249,3 +249,82 @@ class TerminateOnNaN(Callback):
         loss = (logs or {}).get("loss")
         if loss is not None and (np.isnan(loss) or np.isinf(loss)):
             self.model.stop_training = True
+
+
+class ReduceLROnPlateau(Callback):
+    """Multiplies the learning rate by ``factor`` when ``monitor`` has not improved for
+    ``patience`` epochs (``tf.keras.callbacks.ReduceLROnPlateau``)."""
+
+    def __init__(self, monitor="val_loss", factor=0.1, patience=10, verbose=0, mode="auto",
+                 min_delta=1e-4, cooldown=0, min_lr=0.0, **kwargs):
+        super().__init__()
+        if factor >= 1.0:
+            raise ValueError("ReduceLROnPlateau does not support a factor >= 1.0.")
+        self.monitor, self.factor, self.patience, self.verbose = monitor, factor, patience, verbose
+        self.mode, self.min_delta, self.cooldown, self.min_lr = mode, abs(min_delta), cooldown, min_lr
+
+    def on_train_begin(self, logs=None):
+        self.best, self.wait, self.cooldown_counter = None, 0, 0
+
+    def on_epoch_end(self, epoch, logs=None):
+        logs = logs if logs is not None else {}
+        logs["lr"] = float(self.model.optimizer.learning_rate)
+        cur = logs.get(self.monitor)
+        if cur is None:
+            return
+        mode = self.mode if self.mode != "auto" else ("max" if "acc" in self.monitor else "min")
+        if self.cooldown_counter > 0:
+            self.cooldown_counter -= 1
+            self.wait = 0
+        better = self.best is None or (cur > self.best + self.min_delta if mode == "max"
+                                       else cur < self.best - self.min_delta)
+        if better:
+            self.best, self.wait = cur, 0
+        elif self.cooldown_counter <= 0:
+            self.wait += 1
+            if self.wait >= self.patience:
+                old = float(self.model.optimizer.learning_rate)
+                if old > self.min_lr:
+                    new = max(old * self.factor, self.min_lr)
+                    self.model.optimizer.learning_rate = new
+                    if self.verbose:
+                        print(f"\nEpoch {epoch + 1}: ReduceLROnPlateau reducing learning rate to {new}.")
+                    self.cooldown_counter, self.wait = self.cooldown, 0
+
+
+class CSVLogger(Callback):
+    """One row of metrics per epoch (``tf.keras.callbacks.CSVLogger``); written by the chief only."""
+
+    def __init__(self, filename, separator=",", append=False):
+        super().__init__()
+        self.filename, self.sep, self.append = str(filename), separator, append
+        self._file, self._keys = None, None
+
+    def _chief(self):
+        return getattr(self.model, "_is_chief", True)
+
+    def on_train_begin(self, logs=None):
+        if not self._chief():
+            return
+        import os
+        os.makedirs(os.path.dirname(os.path.abspath(self.filename)), exist_ok=True)
+        had_rows = self.append and os.path.exists(self.filename) and os.path.getsize(self.filename) > 0
+        self._file = open(self.filename, "a" if self.append else "w")
+        self._write_header = not had_rows
+
+    def on_epoch_end(self, epoch, logs=None):
+        if self._file is None:
+            return
+        logs = logs or {}
+        if self._keys is None:
+            self._keys = sorted(logs)
+            if self._write_header:
+                self._file.write(self.sep.join(["epoch"] + self._keys) + "\n")
+        self._file.write(self.sep.join([str(epoch)] + [repr(float(logs[k])) if k in logs else "NA"
+                                                        for k in self._keys]) + "\n")
+        self._file.flush()
+
+    def on_train_end(self, logs=None):
+        if self._file is not None:
+            self._file.close()
+            self._file = None

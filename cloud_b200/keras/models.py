@@ -809,9 +809,12 @@ class Model(nn.Module):
         first = next(iter(_peek(source)))
         eng = self._ensure_engine(first[0])
         history = cb_mod.History()
-        cbs = [history] + list(callbacks or [])
+        # Keras order: the user's callbacks, then the progress bar, then History - so the history
+        # (and the printed line) include what callbacks add to the logs, e.g. "lr"
+        cbs = list(callbacks or [])
         if verbose and self._is_chief:
-            cbs.insert(1, cb_mod.ProgbarLogger(verbose))
+            cbs.append(cb_mod.ProgbarLogger(verbose))
+        cbs.append(history)
         n_steps = len(source) if hasattr(source, "__len__") else None
         params = {"epochs": epochs, "steps": n_steps, "verbose": verbose}
         cbl = cb_mod.CallbackList(cbs, self, params)

@@ -444,3 +444,24 @@ def test_tape_details():
     per_example = torch.tensor([1.0, 2.0, 3.0])
     assert float(tfc.nn.compute_average_loss(per_example, global_batch_size=6)) == 1.0
     assert float(tfc.nn.compute_average_loss(per_example)) == 2.0          # one replica: plain mean
+
+
+def test_reduce_lr_on_plateau_and_csv_logger(tmp_path):
+    x, y = _blobs(128)
+    m = _mlp()
+    m.compile(optimizer=keras.optimizers.SGD(0.5), loss="sparse_categorical_crossentropy", metrics=["accuracy"])
+    log = tmp_path / "logs" / "train.csv"
+    # min_delta so large that no epoch counts as an improvement: the rate halves every second epoch
+    plateau = keras.callbacks.ReduceLROnPlateau(monitor="loss", factor=0.5, patience=2, min_delta=100.0,
+                                                min_lr=0.1)
+    hist = m.fit(x, y, batch_size=32, epochs=7, verbose=0,
+                 callbacks=[plateau, keras.callbacks.CSVLogger(str(log))])
+    assert hist.history["lr"] == [0.5, 0.5, 0.5, 0.25, 0.25, 0.125, 0.125]
+    assert float(m.optimizer.lr) == 0.1                                   # clipped at min_lr
+    rows = log.read_text().strip().splitlines()
+    assert rows[0] == "epoch,accuracy,loss,lr" and len(rows) == 8
+    assert float(rows[-1].split(",")[2]) == pytest.approx(hist.history["loss"][-1])
+    m.fit(x, y, batch_size=32, epochs=1, verbose=0, callbacks=[keras.callbacks.CSVLogger(str(log), append=True)])
+    assert len(log.read_text().strip().splitlines()) == 9                 # appended, one header
+    with pytest.raises(ValueError):
+        keras.callbacks.ReduceLROnPlateau(factor=1.5)
