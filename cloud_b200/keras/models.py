@@ -478,6 +478,8 @@ class Model(nn.Module):
                                             isinstance(x[0], L.KerasTensor)):
             return self._symbolic_call(x)
         self._ensure_placed()
+        if training and self._engine is None and not getattr(self, "_initial_sync_done", False):
+            self._sync_initial_variables(x)
         xi = self._to_internal(x)
         was = self.training
         self.train(bool(training))
@@ -486,6 +488,21 @@ class Model(nn.Module):
         finally:
             self.train(was)
         return _to_keras_layout(out)
+
+    def _sync_initial_variables(self, sample_x):
+        """Custom training loops call the model before any engine exists (the engine is built by the
+        first ``apply_gradients``).  Mirrored variables start from replica 0's values
+        (tf.distribute semantics), so the first training call broadcasts
+        them; ``fit`` gets the same from the engine's own broadcast."""
+        object.__setattr__(self, "_initial_sync_done", True)
+        st = self.distribute_strategy
+        if st.num_replicas_in_sync <= 1:
+            return
+        self._build_with_batch(sample_x)
+        self._ensure_placed()
+        with torch.no_grad():
+            for t in list(self.parameters()) + list(self.buffers()):
+                st.communicator.broadcast(t.data, root=0)
 
     # -- device / dtype plumbing --------------------------------------------------------------
     @property

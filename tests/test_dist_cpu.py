@@ -44,3 +44,10 @@ def test_a_rank_that_never_arrives_fails_the_others_instead_of_hanging(tmp_path)
                     {"CUDA_VISIBLE_DEVICES": "", "SHM_CHECK_ABSENT_RANK": "2"}, port=29632)
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     assert res.stdout.count("WATCHDOG OK") == 2 and "for rank 2" in res.stdout
+
+
+def test_custom_training_loop_equals_single_replica_cpu(tmp_path):
+    res = _torchrun(os.path.join(ROOT, "tests", "dist_ctl_check.py"), 2,
+                    {"CHECK_DEVICE": "cpu", "CUDA_VISIBLE_DEVICES": ""}, port=29641)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    assert "CTL OK world=2 backend=shm" in res.stdout

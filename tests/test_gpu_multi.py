@@ -41,3 +41,11 @@ def test_mirrored_training_matches_single_gpu(tmp_path, eager):
                     env_extra={"CHECK_OUT": str(tmp_path), "CHECK_EAGER": eager}, port=29702 + int(eager))
     assert res.returncode == 0, res.stdout[-4000:] + res.stderr[-4000:]
     assert "backend=p2p" in res.stdout, res.stdout[-2000:]
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
+def test_custom_training_loop_matches_single_gpu():
+    n = min(_ngpu(), 8)
+    res = _torchrun(os.path.join(ROOT, "tests", "dist_ctl_check.py"), n, port=29706)
+    assert res.returncode == 0, res.stdout[-4000:] + res.stderr[-4000:]
+    assert "CTL OK" in res.stdout and "backend=p2p" in res.stdout, res.stdout[-2000:]
