@@ -113,8 +113,10 @@ def _start_supervisor(job_id):
     env = dict(os.environ)
     repo_root = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     env["PYTHONPATH"] = os.pathsep.join([repo_root, env.get("PYTHONPATH", "")])
-    subprocess.Popen([sys.executable, "-m", "cloud_b200.launch.supervisor", job_id], env=env,
-                     stdout=log, stderr=subprocess.STDOUT, start_new_session=True, cwd=jdir)
+    proc = subprocess.Popen([sys.executable, "-m", "cloud_b200.launch.supervisor", job_id], env=env,
+                            stdout=log, stderr=subprocess.STDOUT, start_new_session=True, cwd=jdir)
+    # known from the first moment: a job can be cancelled while its supervisor is still starting
+    registry.set_status(job_id, "QUEUED", supervisor_pid=proc.pid)
 
 
 def _print_logs_info(job_id, project_id):

@@ -7,6 +7,7 @@ and points users at the cloud console for everything else).
     python -m cloud_b200.launch stream-logs <job_id>
     python -m cloud_b200.launch cancel <job_id>
     python -m cloud_b200.launch topology
+    python -m cloud_b200.launch gpus             # which job holds which GPU, who is waiting
 
 Jobs live under ``$TFC_JOB_ROOT/jobs/<job_id>`` (see ``launch/registry.py``).
 """
@@ -19,7 +20,7 @@ import signal
 import sys
 import time
 
-from . import registry, topology
+from . import leases, registry, topology
 
 
 def _fmt_time(t):
@@ -64,8 +65,22 @@ def cmd_cancel(args) -> int:
     if not pid:
         print("Job {} has no running supervisor.".format(args.job_id), file=sys.stderr)
         return 1
-    os.kill(int(pid), signal.SIGTERM)          # the supervisor kills its ranks and records CANCELLED
-    final = registry.wait(args.job_id, timeout=args.timeout)
+    try:
+        os.kill(int(pid), signal.SIGTERM)      # the supervisor kills its ranks and records CANCELLED
+    except ProcessLookupError:
+        pass
+    deadline = time.time() + args.timeout
+    while True:
+        final = registry.status(args.job_id)
+        if final.get("state") in registry.TERMINAL or time.time() > deadline:
+            break
+        if not leases._alive(pid):
+            # the signal caught the supervisor before it could answer it (still starting up, or
+            # gone without a trace): nothing is running, so the record is written here
+            leases.release(args.job_id)
+            registry.set_status(args.job_id, "CANCELLED", exit_codes=[], seconds=0.0)
+            continue
+        time.sleep(0.1)
     print("Job {}: {}".format(args.job_id, final.get("state")))
     return 0 if final.get("state") == "CANCELLED" else 1
 
@@ -73,6 +88,22 @@ def cmd_cancel(args) -> int:
 def cmd_topology(_args) -> int:
     topo = topology.discover()
     print(json.dumps(topo.to_dict() if hasattr(topo, "to_dict") else topo.__dict__, indent=1, default=str))
+    return 0
+
+
+def cmd_gpus(_args) -> int:
+    total = topology.discover().gpu_count
+    table = leases.snapshot(total)
+    print("{:<5} {:<58} {:>8}  {}".format("GPU", "HELD BY", "PID", "SINCE"))
+    for g in range(total):
+        lease = table["gpus"].get(str(g))
+        if lease:
+            print("{:<5} {:<58} {:>8}  {}".format(g, lease.get("job", "?"), lease.get("pid", "?"),
+                                                  _fmt_time(lease.get("time"))))
+        else:
+            print("{:<5} {:<58}".format(g, "-"))
+    for q in table["queue"]:
+        print("waiting: {} wants {} GPU(s) since {}".format(q["owner"], q["n"], _fmt_time(q.get("time"))))
     return 0
 
 
@@ -89,6 +120,7 @@ def main(argv=None) -> int:
     p.add_argument("--timeout", type=float, default=30.0)
     p.set_defaults(fn=cmd_cancel)
     sub.add_parser("topology").set_defaults(fn=cmd_topology)
+    sub.add_parser("gpus").set_defaults(fn=cmd_gpus)
     args = ap.parse_args(argv)
     try:
         return args.fn(args)

@@ -16,7 +16,7 @@ import subprocess
 import sys
 import time
 
-from . import registry
+from . import leases, registry, topology
 
 
 def _free_port() -> int:
@@ -34,6 +34,27 @@ def _tail(path: str, n: int = 30) -> str:
             return "\n".join(f.read().decode(errors="replace").splitlines()[-n:])
     except OSError:
         return ""
+
+
+def _lease_gpus(job_id: str, n: int, cancelled: dict):
+    """Physical GPU ids for the job, or None after recording why it did not get them."""
+    if os.environ.get("TFC_GPU_LEASES", "1") == "0":
+        return list(range(n))
+    total = topology.discover().gpu_count
+    if n > total:
+        registry.set_status(job_id, "FAILED", error_tail="the job needs {} GPUs, the box has {}".format(n, total))
+        return None
+    wait = float(os.environ.get("TFC_QUEUE_TIMEOUT", "0") or 0) or None
+    try:
+        got = leases.acquire(job_id, n, total, timeout=wait, should_stop=lambda: cancelled["flag"],
+                             on_wait=lambda: registry.set_status(job_id, "QUEUED", supervisor_pid=os.getpid(),
+                                                                 waiting_for_gpus=n))
+    except leases.LeaseTimeout as e:
+        registry.set_status(job_id, "FAILED", error_tail=str(e))
+        return None
+    if got is None:
+        registry.set_status(job_id, "CANCELLED", exit_codes=[], seconds=0.0)
+    return got
 
 
 def run_job(job_id: str) -> int:
@@ -62,11 +83,24 @@ def run_job(job_id: str) -> int:
         base_env.setdefault(k, share)
     repo_root = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     base_env["PYTHONPATH"] = os.pathsep.join([repo_root, workdir, base_env.get("PYTHONPATH", "")])
+    cancelled = {"flag": False}
+
+    def _on_term(signum, frame):
+        cancelled["flag"] = True
+    signal.signal(signal.SIGTERM, _on_term)
+    signal.signal(signal.SIGINT, _on_term)
     if plan["uses_gpu"]:
-        base_env["CUDA_VISIBLE_DEVICES"] = ",".join(str(g) for g in plan["gpu_ids"])
+        # the plan numbers the job's GPUs 0..n-1; which physical GPUs those are is decided here,
+        # under the box-wide lease table, so concurrent jobs never share a GPU.  Until enough GPUs
+        # are free the job stays QUEUED (FIFO); leases die with this process.
+        gpu_ids = _lease_gpus(job_id, len(plan["gpu_ids"]), cancelled)
+        if gpu_ids is None:
+            return 1
+        base_env["CUDA_VISIBLE_DEVICES"] = ",".join(str(g) for g in gpu_ids)
     else:
+        gpu_ids = []
         base_env["CUDA_VISIBLE_DEVICES"] = ""
-    registry.set_status(job_id, "RUNNING", supervisor_pid=os.getpid(), master_port=port)
+    registry.set_status(job_id, "RUNNING", supervisor_pid=os.getpid(), master_port=port, gpus=gpu_ids)
     for r in plan["ranks"]:
         env = dict(base_env)
         env["RANK"] = str(r["rank"])
@@ -89,13 +123,6 @@ def run_job(job_id: str) -> int:
     os.makedirs(hb_dir, exist_ok=True)
     t0 = time.time()
     failed = None
-    cancelled = {"flag": False}
-
-    def _on_term(signum, frame):
-        cancelled["flag"] = True
-    signal.signal(signal.SIGTERM, _on_term)
-    signal.signal(signal.SIGINT, _on_term)
-
     while True:
         alive = 0
         for i, p in enumerate(procs):
@@ -138,17 +165,19 @@ def run_job(job_id: str) -> int:
                     pass
     for fh, _ in logs:
         fh.close()
+    if gpu_ids:
+        leases.release(job_id)
     exit_codes = [p.poll() for p in procs]
     if cancelled["flag"] and failed is None:
-        registry.set_status(job_id, "CANCELLED", exit_codes=exit_codes, seconds=time.time() - t0)
+        registry.set_status(job_id, "CANCELLED", exit_codes=exit_codes, seconds=time.time() - t0, gpus=gpu_ids)
         return 130
     if failed is not None:
         rank, rc = failed
         tail = _tail(logs[rank][1]) if rank >= 0 else ""
         registry.set_status(job_id, "FAILED", failed_rank=rank, exit_code=rc, exit_codes=exit_codes,
-                            error_tail=tail, seconds=time.time() - t0)
+                            error_tail=tail, seconds=time.time() - t0, gpus=gpu_ids)
         return 1
-    registry.set_status(job_id, "SUCCEEDED", exit_codes=exit_codes, seconds=time.time() - t0)
+    registry.set_status(job_id, "SUCCEEDED", exit_codes=exit_codes, seconds=time.time() - t0, gpus=gpu_ids)
     return 0
 
 

@@ -55,6 +55,29 @@ class TrialScheduler:
         slots = self.slots(num_workers)
         num_workers = num_workers or len(slots)
         self._concurrent = min(num_workers, len(slots))
+        # the GPUs of the slots come from the box-wide lease table (launch/leases.py), so a search
+        # and the jobs launched with tfc.run share the box without sharing a GPU
+        lease_owner = None
+        wanted = sum(len(s) for s in slots)
+        if wanted and os.environ.get("TFC_GPU_LEASES", "1") != "0":
+            from ..launch import leases
+            lease_owner = "trial_scheduler_{}_{}".format(os.getpid(), int(time.time() * 1000) % 100000)
+            # take the slots that are free right now (at least one): a search next to a running
+            # job uses the rest of the box instead of waiting for all of it
+            free = len(leases.snapshot(self.num_gpus)["free"])
+            n_slots = min(len(slots), max(1, free // self.gpus_per_trial))
+            got = leases.acquire(lease_owner, n_slots * self.gpus_per_trial, self.num_gpus,
+                                 timeout=float(os.environ.get("TFC_QUEUE_TIMEOUT", "0") or 0) or None)
+            slots = [got[i * self.gpus_per_trial:(i + 1) * self.gpus_per_trial] for i in range(n_slots)]
+            self._concurrent = min(num_workers, len(slots))
+        try:
+            return self._run(target, args, kwargs, num_workers, slots, study, env, timeout, log_dir)
+        finally:
+            if lease_owner:
+                from ..launch import leases
+                leases.release(lease_owner)
+
+    def _run(self, target, args, kwargs, num_workers, slots, study, env, timeout, log_dir) -> list:
         log_dir = log_dir or tempfile.mkdtemp(prefix="cb2_trials_")
         os.makedirs(log_dir, exist_ok=True)
         blob = os.path.join(log_dir, "target.pkl")
