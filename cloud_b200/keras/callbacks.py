@@ -328,3 +328,62 @@ class CSVLogger(Callback):
         if self._file is not None:
             self._file.close()
             self._file = None
+
+
+class BackupAndRestore(Callback):
+    """Fault tolerance for ``fit`` (``tf.keras.callbacks.experimental.BackupAndRestore``): after
+    every epoch the training state (weights, optimizer state, epoch number) is saved under
+    ``backup_dir``; a ``fit`` that finds a backup there - the same script started again after a
+    crash, e.g. by the launcher with ``TFC_JOB_RESTARTS`` - restores it and continues with the next
+    epoch.  The backup is deleted when training ends normally.  All replicas take part in saving
+    (optimizer state may be sharded); only the chief writes."""
+
+    def __init__(self, backup_dir, delete_checkpoint=True):
+        super().__init__()
+        self.backup_dir = str(backup_dir)
+        self.delete_checkpoint = delete_checkpoint
+
+    def _meta(self):
+        import os
+        return os.path.join(self.backup_dir, "backup.json")
+
+    def on_train_begin(self, logs=None):
+        import json
+        import os
+        try:
+            with open(self._meta()) as f:
+                meta = json.load(f)
+        except (OSError, ValueError):
+            return
+        from . import saving
+        ckpt = os.path.join(self.backup_dir, meta["checkpoint"])
+        saving.restore_training_state(self.model, ckpt)
+        self.model._resume_from_epoch = int(meta["epoch"]) + 1
+        if getattr(self.model, "_is_chief", True):
+            print("BackupAndRestore: resuming after epoch {} from {}".format(int(meta["epoch"]) + 1, ckpt), flush=True)
+
+    def on_epoch_end(self, epoch, logs=None):
+        import json
+        import os
+        import shutil
+        name = "ckpt_{}".format(epoch % 2)                 # two slots: the previous one stays valid
+        path = os.path.join(self.backup_dir, name)
+        chief = getattr(self.model, "_is_chief", True)
+        if chief:
+            shutil.rmtree(path, ignore_errors=True)
+        self.model.save(path)                              # collective
+        if chief:
+            tmp = self._meta() + ".tmp"
+            with open(tmp, "w") as f:
+                json.dump({"epoch": epoch, "checkpoint": name}, f)
+            os.replace(tmp, self._meta())                  # the backup exists from this instant
+
+    def on_train_end(self, logs=None):
+        import shutil
+        if self.delete_checkpoint and getattr(self.model, "_is_chief", True) \
+                and not getattr(self.model, "stop_training_failed", False):
+            shutil.rmtree(self.backup_dir, ignore_errors=True)
+
+
+class experimental:  # tf.keras.callbacks.experimental.*
+    BackupAndRestore = BackupAndRestore

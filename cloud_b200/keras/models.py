@@ -838,7 +838,9 @@ class Model(nn.Module):
         batch_logs = _needs_batch_logs(cbs)
         self.stop_training = False
         self.train(True)
+        self._resume_from_epoch = 0
         cbl.call("on_train_begin", {})
+        initial_epoch = max(initial_epoch, int(self._resume_from_epoch))      # set by BackupAndRestore
         n_aux = self._aux_len()
         self._h2d_bytes = 0
         self._d2h_bytes = 0

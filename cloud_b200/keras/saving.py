@@ -244,6 +244,24 @@ def load_model(filepath, custom_objects=None, compile=True):
     return model
 
 
+def restore_training_state(model, filepath) -> None:
+    """Weights and optimizer state of a ``model.save(dir)`` into an existing, compiled model of the
+    same architecture (what ``BackupAndRestore`` does after a restart)."""
+    path = str(filepath)
+    model.load_weights(os.path.join(path, "weights.h5"))
+    opt_path = os.path.join(path, "optimizer.pt")
+    if not os.path.exists(opt_path):
+        return
+    state = torch.load(opt_path, weights_only=False)
+    eng = getattr(model, "_engine", None)
+    if eng is not None:
+        eng.load_master_state(state)
+    else:
+        model._pending_optimizer_state = state
+    if model.optimizer is not None and "__step__" in state:
+        model.optimizer.iterations = int(state["__step__"])
+
+
 def _model_from_config(config, custom_objects, Model, Sequential):
     cfg = config["config"]
     cls = Sequential if (config.get("class_name") == "Sequential" or cfg.get("kind") == "Sequential") \

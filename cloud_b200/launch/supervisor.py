@@ -65,8 +65,6 @@ def run_job(job_id: str) -> int:
     workdir = image["workdir"]
     cmd = [spec.get("python") or sys.executable] + image["entrypoint"][1:] + list(spec.get("args") or [])
     port = _free_port()
-    procs = []
-    logs = []
     base_env = dict(os.environ)
     base_env.update(spec.get("env") or {})
     base_env["MASTER_ADDR"] = "127.0.0.1"
@@ -100,31 +98,77 @@ def run_job(job_id: str) -> int:
     else:
         gpu_ids = []
         base_env["CUDA_VISIBLE_DEVICES"] = ""
-    registry.set_status(job_id, "RUNNING", supervisor_pid=os.getpid(), master_port=port, gpus=gpu_ids)
-    for r in plan["ranks"]:
-        env = dict(base_env)
-        env["RANK"] = str(r["rank"])
-        env["LOCAL_RANK"] = str(r["local_rank"])
-        env["TF_CONFIG"] = r["tf_config"]
-        env["TFC_RANK_IN_TASK"] = str(r["rank_in_task"])
-        env["TFC_TASK_TYPE"] = r["task_type"]
-        log_path = os.path.join(jdir, "logs", "rank{}.log".format(r["rank"]))
-        fh = open(log_path, "ab", buffering=0)
-        logs.append((fh, log_path))
-        procs.append(subprocess.Popen(cmd, cwd=workdir, env=env, stdout=fh, stderr=subprocess.STDOUT,
-                                      start_new_session=True))
-    timeout = float(os.environ.get("TFC_JOB_TIMEOUT", "0") or 0)
+    timeout = float(base_env.get("TFC_JOB_TIMEOUT", "0") or 0)      # own environment or the job's `env`
     # Heartbeats: the training engine touches <job_dir>/heartbeat/rank<r>
     # after every step.  A rank that has started beating and then stays silent for longer than
     # TFC_HEARTBEAT_TIMEOUT seconds (0 = off) - a hung collective, a wedged data loader - fails
     # the job instead of holding the GPUs forever.
-    hb_timeout = float(os.environ.get("TFC_HEARTBEAT_TIMEOUT", "0") or 0)
+    hb_timeout = float(base_env.get("TFC_HEARTBEAT_TIMEOUT", "0") or 0)
     hb_dir = os.path.join(jdir, "heartbeat")
     os.makedirs(hb_dir, exist_ok=True)
+    # Restarts: after a failed rank the whole group is started again, up to TFC_JOB_RESTARTS times
+    # (default 0, like AI Platform).  Training resumes where a `BackupAndRestore` callback left it;
+    # ranks see the attempt number in TFC_RESTART_COUNT.
+    max_restarts = int(base_env.get("TFC_JOB_RESTARTS", "0") or spec.get("max_restarts", 0) or 0)
     t0 = time.time()
-    failed = None
+    attempt = 0
+    failures = []
     while True:
-        alive = 0
+        for name in os.listdir(hb_dir):                  # beats of a previous attempt say nothing
+            os.remove(os.path.join(hb_dir, name))
+        base_env["MASTER_PORT"] = str(port if attempt == 0 else _free_port())
+        base_env["TFC_RESTART_COUNT"] = str(attempt)
+        registry.set_status(job_id, "RUNNING", supervisor_pid=os.getpid(),
+                            master_port=int(base_env["MASTER_PORT"]), gpus=gpu_ids, restarts=attempt,
+                            failures=failures)
+        procs, logs = [], []
+        for r in plan["ranks"]:
+            env = dict(base_env)
+            env["RANK"] = str(r["rank"])
+            env["LOCAL_RANK"] = str(r["local_rank"])
+            env["TF_CONFIG"] = r["tf_config"]
+            env["TFC_RANK_IN_TASK"] = str(r["rank_in_task"])
+            env["TFC_TASK_TYPE"] = r["task_type"]
+            log_path = os.path.join(jdir, "logs", "rank{}.log".format(r["rank"]))
+            fh = open(log_path, "ab", buffering=0)
+            if attempt:
+                fh.write("---- restart {} of {} ----\n".format(attempt, max_restarts).encode())
+            logs.append((fh, log_path))
+            procs.append(subprocess.Popen(cmd, cwd=workdir, env=env, stdout=fh, stderr=subprocess.STDOUT,
+                                          start_new_session=True))
+        failed = _watch(procs, cancelled, timeout, t0, hb_timeout, hb_dir)
+        if failed is not None or cancelled["flag"]:
+            _kill_group(procs)
+        for fh, _ in logs:
+            fh.close()
+        retry = (failed is not None and failed[0] >= 0 and not cancelled["flag"] and attempt < max_restarts)
+        if not retry:
+            break
+        failures.append({"attempt": attempt, "rank": failed[0], "exit_code": failed[1],
+                         "error_tail": _tail(logs[failed[0]][1], 8)})
+        attempt += 1
+    if gpu_ids:
+        leases.release(job_id)
+    exit_codes = [p.poll() for p in procs]
+    common = dict(exit_codes=exit_codes, seconds=time.time() - t0, gpus=gpu_ids, restarts=attempt,
+                  failures=failures)
+    if cancelled["flag"] and failed is None:
+        registry.set_status(job_id, "CANCELLED", **common)
+        return 130
+    if failed is not None:
+        rank, rc = failed
+        tail = _tail(logs[rank][1]) if rank >= 0 else ""
+        registry.set_status(job_id, "FAILED", failed_rank=rank, exit_code=rc, error_tail=tail, **common)
+        return 1
+    registry.set_status(job_id, "SUCCEEDED", **common)
+    return 0
+
+
+def _watch(procs, cancelled, timeout, t0, hb_timeout, hb_dir):
+    """Blocks until every rank has exited, one has failed, the job is cancelled or out of time.
+    Returns None or (rank, exit code or reason); rank -1 = the job as a whole."""
+    while True:
+        alive, failed = 0, None
         for i, p in enumerate(procs):
             rc = p.poll()
             if rc is None:
@@ -132,53 +176,35 @@ def run_job(job_id: str) -> int:
             elif rc != 0 and failed is None:
                 failed = (i, rc)
         if failed is not None or alive == 0 or cancelled["flag"]:
-            break
+            return failed
         if timeout and time.time() - t0 > timeout:
-            failed = (-1, "timeout after {}s".format(timeout))
-            break
+            return (-1, "timeout after {}s".format(timeout))
         if hb_timeout:
             now = time.time()
             for i, p in enumerate(procs):
                 hb = os.path.join(hb_dir, "rank{}".format(i))
                 if p.poll() is None and os.path.exists(hb) and now - os.path.getmtime(hb) > hb_timeout:
-                    failed = (i, "no heartbeat for {:.0f}s (stalled)".format(now - os.path.getmtime(hb)))
-                    break
-            if failed is not None:
-                break
+                    return (i, "no heartbeat for {:.0f}s (stalled)".format(now - os.path.getmtime(hb)))
         time.sleep(0.1)
 
-    if failed is not None or cancelled["flag"]:
-        for p in procs:
-            if p.poll() is None:
-                try:
-                    os.killpg(p.pid, signal.SIGTERM)
-                except (ProcessLookupError, PermissionError):
-                    pass
-        deadline = time.time() + 5
-        for p in procs:
+
+def _kill_group(procs) -> None:
+    for p in procs:
+        if p.poll() is None:
             try:
-                p.wait(timeout=max(0.1, deadline - time.time()))
-            except subprocess.TimeoutExpired:
-                try:
-                    os.killpg(p.pid, signal.SIGKILL)
-                except (ProcessLookupError, PermissionError):
-                    pass
-    for fh, _ in logs:
-        fh.close()
-    if gpu_ids:
-        leases.release(job_id)
-    exit_codes = [p.poll() for p in procs]
-    if cancelled["flag"] and failed is None:
-        registry.set_status(job_id, "CANCELLED", exit_codes=exit_codes, seconds=time.time() - t0, gpus=gpu_ids)
-        return 130
-    if failed is not None:
-        rank, rc = failed
-        tail = _tail(logs[rank][1]) if rank >= 0 else ""
-        registry.set_status(job_id, "FAILED", failed_rank=rank, exit_code=rc, exit_codes=exit_codes,
-                            error_tail=tail, seconds=time.time() - t0, gpus=gpu_ids)
-        return 1
-    registry.set_status(job_id, "SUCCEEDED", exit_codes=exit_codes, seconds=time.time() - t0, gpus=gpu_ids)
-    return 0
+                os.killpg(p.pid, signal.SIGTERM)
+            except (ProcessLookupError, PermissionError):
+                pass
+    deadline = time.time() + 5
+    for p in procs:
+        try:
+            p.wait(timeout=max(0.1, deadline - time.time()))
+        except subprocess.TimeoutExpired:
+            try:
+                os.killpg(p.pid, signal.SIGKILL)
+            except (ProcessLookupError, PermissionError):
+                pass
+            p.wait()
 
 
 def main(argv=None) -> int:

@@ -124,7 +124,7 @@ class DPEngine:
         self._in_step = False
         self._fault = None
         fault = os.environ.get("TFC_FAULT")
-        if fault:
+        if fault and os.environ.get("TFC_RESTART_COUNT", "0") == "0":   # injected once, not again after a restart
             try:
                 r, s = fault.split(":")
                 self._fault = (int(r), int(s))
