@@ -16,7 +16,6 @@ model, so the exported model takes raw pixels / raw features like an AutoKeras e
 """
 from __future__ import annotations
 
-import os
 import tempfile
 
 import numpy as np

@@ -195,24 +195,45 @@ class EarlyStopping(Callback):
 
 
 class TensorBoard(Callback):
+    """Logs for TensorBoard (``tf.keras.callbacks.TensorBoard``): real event files
+    (``<log_dir>/{train,validation}/events.out.tfevents.*``, tags ``epoch_<metric>``, weight
+    histograms every ``histogram_freq`` epochs - see ``cloud_b200/io/tfevents.py``), plus the same
+    scalars as JSON lines (``scalars.jsonl``) for tools without a protobuf reader.  Chief only."""
+
     def __init__(self, log_dir="logs", histogram_freq=0, write_graph=True, update_freq="epoch",
                  **kwargs):
         super().__init__()
         self.log_dir = str(log_dir)
         self.histogram_freq = histogram_freq
+        self._writers = {}
+
+    def _chief(self):
+        return getattr(self.model, "_is_chief", True)
+
+    def _writer(self, split):
+        if split not in self._writers:
+            from ..io import tfevents
+            self._writers[split] = tfevents.EventFileWriter(os.path.join(self.log_dir, split))
+        return self._writers[split]
 
     def _write(self, split, step, scalars):
-        if not getattr(self.model, "_is_chief", True):
+        if not self._chief():
             return
         d = os.path.join(self.log_dir, split)
         os.makedirs(d, exist_ok=True)
+        now = time.time()
+        writer = self._writer(split)
+        for k, v in scalars.items():
+            writer.add_scalar("epoch_" + k, float(v), int(step), now)
+        writer.flush()
         with open(os.path.join(d, "scalars.jsonl"), "a") as f:
-            f.write(json.dumps({"step": int(step), "wall_time": time.time(),
+            f.write(json.dumps({"step": int(step), "wall_time": now,
                                 **{k: float(v) for k, v in scalars.items()}}) + "\n")
 
     def on_train_begin(self, logs=None):
-        if getattr(self.model, "_is_chief", True):
+        if self._chief():
             os.makedirs(os.path.join(self.log_dir, "train"), exist_ok=True)
+            self._writer("train")
 
     def on_epoch_end(self, epoch, logs=None):
         logs = logs or {}
@@ -222,15 +243,27 @@ class TensorBoard(Callback):
             self._write("train", epoch, train)
         if val:
             self._write("validation", epoch, val)
-        if self.histogram_freq and (epoch + 1) % self.histogram_freq == 0 \
-                and getattr(self.model, "_is_chief", True):
+        if self.histogram_freq and (epoch + 1) % self.histogram_freq == 0 and self._chief():
             hist = {}
+            writer = self._writer("train")
             for layer in self.model.layers:
                 for name, w in zip(layer.weight_names, layer.get_weights()):
                     counts, edges = np.histogram(w, bins=30)
                     hist[name] = {"counts": counts.tolist(), "edges": edges.tolist()}
+                    writer.add_histogram(name.replace(":0", "_0"), w, int(epoch))
+            writer.flush()
             with open(os.path.join(self.log_dir, "train", "histograms.jsonl"), "a") as f:
                 f.write(json.dumps({"step": int(epoch), "histograms": hist}) + "\n")
+
+    def on_train_end(self, logs=None):
+        for w in self._writers.values():
+            w.close()
+        self._writers = {}
+
+    def __getstate__(self):                 # cloud_fit pickles callbacks: open files stay behind
+        state = dict(self.__dict__)
+        state["_writers"] = {}
+        return state
 
 
 class LambdaCallback(Callback):

@@ -9,7 +9,6 @@ hand-written tcgen05 GEMM (``cloud_b200.ops.dense``).
 """
 from __future__ import annotations
 
-import math
 import os
 import re
 
