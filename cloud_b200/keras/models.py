@@ -817,6 +817,14 @@ class Model(nn.Module):
             steps_per_epoch=None, validation_steps=None, validation_batch_size=None, **kwargs):
         if self.loss is None:
             raise RuntimeError("You must compile your model with a loss before calling fit().")
+        for name in ("class_weight", "sample_weight"):       # would change the loss: never ignore silently
+            if kwargs.get(name) is not None:
+                raise NotImplementedError("fit({}=...) is not supported; weight the loss in a custom "
+                                          "training loop (tfc.GradientTape) instead.".format(name))
+        unknown = set(kwargs) - {"class_weight", "sample_weight", "workers", "use_multiprocessing",
+                                 "max_queue_size", "validation_freq"}
+        if unknown:
+            raise TypeError("fit() got unexpected keyword arguments: {}".format(sorted(unknown)))
         if validation_split and validation_data is None and isinstance(x, (np.ndarray, torch.Tensor)):
             n_val = int(len(x) * validation_split)
             if n_val:
