@@ -111,14 +111,14 @@ class Communicator:
             self.backend = "dist" if self.world > 1 else "local"
             return
         try:
-            nbytes = int(float(os.environ.get("TFC_SHM_ARENA_MB", "256")) * (1 << 20))
-            self.shm = shm.ShmArena(nbytes, self.group)
+            self.shm = shm.ShmArena(1 << 20, self.group)        # signal pad + scalars + small tensors
         except (shm.ShmError, _lib.KernelsUnavailable, OSError) as e:
             warnings.warn(f"cloud_b200: shared-memory arena unavailable ({e}); using "
                           f"torch.distributed all-reduce instead")
             self.backend = "dist"
             self.shm = None
             return
+        self._shm_arenas = [self.shm]
         self.aux = self.shm.aux
 
     @property
@@ -126,25 +126,32 @@ class Communicator:
         return self.pad is not None
 
     def alloc_flat(self, numel: int, dtype: torch.dtype) -> torch.Tensor:
-        """A zero-filled flat tensor for gradients: inside the shared segment when this
-        communicator has one (so ``all_reduce_sum`` on it - or on a slice of it - is in place)."""
+        """A zero-filled flat tensor for gradients.  CPU ranks with the shared-memory back end get it
+        inside a segment of exactly that size (reserved up front), so ``all_reduce_sum`` on it - or
+        on a slice of it - is in place.  Collective there: every rank calls it in the same order."""
         if self.shm is not None:
+            from . import shm
             nbytes = numel * torch.empty((), dtype=dtype).element_size()
-            if nbytes + 64 <= self.shm.free_bytes:
-                return self.shm.tensor(numel, dtype)
-            warnings.warn(f"cloud_b200: {nbytes >> 20} MiB of gradients do not fit the shared-memory "
-                          f"arena (TFC_SHM_ARENA_MB); this group goes through torch.distributed")
+            cap = int(float(os.environ.get("TFC_SHM_ARENA_MB", "4096")) * (1 << 20))
+            err = None
+            if nbytes <= cap:
+                try:
+                    arena = shm.ShmArena(nbytes + 4096, self.group)
+                    self._shm_arenas.append(arena)
+                    return arena.tensor(numel, dtype)
+                except shm.ShmError as e:          # raised on every rank or on none (see ShmArena)
+                    err = e
+            warnings.warn(f"cloud_b200: {nbytes >> 20} MiB of gradients do not go into shared memory "
+                          f"({err or 'above TFC_SHM_ARENA_MB'}); this group uses torch.distributed")
         return torch.zeros(numel, dtype=dtype, device=self.device)
 
-    def alloc_pair(self, nbytes_grad: int, nbytes_param: int):
-        """Symmetric (grad, param) arenas for one parameter group; plain tensors otherwise."""
-        from . import symm
-        if self.pad is not None:
-            want_mc = self.world > 1 and os.environ.get("TFC_DISABLE_NVLS") != "1"
-            g = symm.SymmetricBuffer(nbytes_grad, self.device, self.xchg, want_multicast=want_mc)
-            p = symm.SymmetricBuffer(nbytes_param, self.device, self.xchg, want_multicast=want_mc)
-            return g, p
-        return None, None
+    def _shm_arena_of(self, t: torch.Tensor):
+        if self.shm is None or t.dtype not in (torch.float32, torch.bfloat16):
+            return None
+        for arena in self._shm_arenas:
+            if arena.offset_of(t) is not None:
+                return arena
+        return None
 
     def make_ctx(self, grad_buf, param_buf) -> CommCtx:
         ctx = CommCtx()
@@ -193,9 +200,9 @@ class Communicator:
 
     # -- torch.distributed fallbacks ----------------------------------------------------------
     def all_reduce_sum(self, t: torch.Tensor) -> torch.Tensor:
-        if self.world > 1 and self.shm is not None and t.dtype in (torch.float32, torch.bfloat16) \
-                and self.shm.offset_of(t) is not None:
-            self.shm.all_reduce(t)
+        arena = self._shm_arena_of(t) if self.world > 1 else None
+        if arena is not None:
+            arena.all_reduce(t)
             return t
         if self.world > 1:
             if t.dtype == torch.bfloat16 and t.device.type == "cpu":

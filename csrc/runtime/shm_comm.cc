@@ -273,6 +273,18 @@ void* cb2rt_shm_open(const char* name, int rank, int world, size_t arena_bytes, 
       shm_unlink(name);
       return nullptr;
     }
+    // Reserve the pages now: a tmpfs that is too small (containers often mount 64 MB at /dev/shm)
+    // must fail here with an error, not later with SIGBUS on the first touch of a missing page.
+    if (fd >= 0) {
+      const int rc = posix_fallocate(fd, 0, static_cast<off_t>(bytes));
+      if (rc != 0) {
+        cb2rt::set_error("shm collective: cannot reserve %zu bytes of shared memory for %s: %s", bytes, name,
+                         strerror(rc));
+        close(fd);
+        shm_unlink(name);
+        return nullptr;
+      }
+    }
   } else {
     fd = shm_open(name, O_RDWR, 0600);
   }
