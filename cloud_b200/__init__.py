@@ -10,14 +10,11 @@ pipeline), ``tfc.datasets`` (tfds-shaped synthetic catalogue), ``tfc.image``.
 """
 from .version import __version__  # noqa: F401
 
-from . import data  # noqa: F401,E402
-from . import datasets  # noqa: F401,E402
-from . import image  # noqa: F401,E402
-from . import distribute  # noqa: F401,E402
-from . import keras  # noqa: F401,E402
-from . import ops  # noqa: F401,E402
-from . import nn  # noqa: F401,E402
-from . import models  # noqa: F401,E402
+# Sub-packages load on first use (``tfc.keras``, ``from cloud_b200 import keras`` and
+# ``import cloud_b200.keras`` all work): the launcher's supervisor, the job CLI and the client side of
+# ``tfc.run`` never pay for importing torch.
+_SUBMODULES = ("data", "datasets", "image", "distribute", "keras", "ops", "nn", "models", "monitoring",
+               "tuner", "automl", "launch", "core", "experimental", "io", "parallel", "utils", "build")
 
 _LAZY = {
     "GradientTape": ("cloud_b200.keras.tape", "GradientTape"),
@@ -32,6 +29,10 @@ _LAZY = {
 }
 
 
+def __dir__():
+    return sorted(list(globals()) + list(_LAZY) + list(_SUBMODULES))
+
+
 def __getattr__(name):
     if name in _LAZY:
         import importlib
@@ -39,4 +40,7 @@ def __getattr__(name):
         value = getattr(importlib.import_module(mod), attr)
         globals()[name] = value
         return value
+    if name in _SUBMODULES:
+        import importlib
+        return importlib.import_module("cloud_b200." + name)
     raise AttributeError(f"module 'cloud_b200' has no attribute {name!r}")

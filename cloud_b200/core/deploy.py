@@ -48,8 +48,7 @@ def _create_request_dict(job_id, region, image_uri, chief_config, worker_count, 
                          entry_point_args, job_labels, gpu_ids=None, env=None):
     """The job spec stored in the registry.  ``trainingInput`` mirrors the CAIP request body
     (deploy.py:98-167) so tools written against it keep working; ``plan`` is what actually runs."""
-    topo = topology.discover()
-    visible = gpu_ids if gpu_ids is not None else list(range(topo.gpu_count))
+    visible = gpu_ids if gpu_ids is not None else list(range(topology.gpu_count()))
     plan = plan_mod.plan_ranks(chief_config, worker_count, worker_config, gpu_ids=visible)
     training_input = {
         "region": region,

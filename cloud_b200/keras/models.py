@@ -917,7 +917,7 @@ class Model(nn.Module):
             self._record_epoch_metrics(eng, step + 1, time.perf_counter() - epoch_t0,
                                        float(host[AUX_COUNT]))
             logs = self._logs_from_aux(host, getattr(self, "_last_fused", False)) if step >= 0 else {}
-            if validation_data is not None:
+            if validation_data is not None and (epoch + 1) % max(1, int(kwargs.get("validation_freq") or 1)) == 0:
                 vx, vy = (validation_data[0], validation_data[1]) \
                     if isinstance(validation_data, (tuple, list)) else (validation_data, None)
                 val = self.evaluate(vx, vy, batch_size=validation_batch_size or batch_size,

@@ -92,7 +92,7 @@ def cmd_topology(_args) -> int:
 
 
 def cmd_gpus(_args) -> int:
-    total = topology.discover().gpu_count
+    total = topology.gpu_count()
     table = leases.snapshot(total)
     print("{:<5} {:<58} {:>8}  {}".format("GPU", "HELD BY", "PID", "SINCE"))
     for g in range(total):

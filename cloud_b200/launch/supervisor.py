@@ -40,7 +40,7 @@ def _lease_gpus(job_id: str, n: int, cancelled: dict):
     """Physical GPU ids for the job, or None after recording why it did not get them."""
     if os.environ.get("TFC_GPU_LEASES", "1") == "0":
         return list(range(n))
-    total = topology.discover().gpu_count
+    total = topology.gpu_count()
     if n > total:
         registry.set_status(job_id, "FAILED", error_tail="the job needs {} GPUs, the box has {}".format(n, total))
         return None

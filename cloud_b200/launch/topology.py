@@ -34,6 +34,37 @@ def _visible_override():
     return int(v) if v else None
 
 
+def gpu_count() -> int:
+    """Number of GPUs this process may use, without importing torch or creating a CUDA context
+    (the launcher asks this for every job): ``TFC_FAKE_GPUS``, else ``CUDA_VISIBLE_DEVICES`` if it
+    is set, else NVML, else torch."""
+    fake = _visible_override()
+    if fake is not None:
+        return fake
+    visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if visible is not None:
+        ids = [v for v in visible.split(",") if v.strip()]
+        if not ids:
+            return 0
+    else:
+        ids = None
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        try:
+            n = int(pynvml.nvmlDeviceGetCount())
+        finally:
+            pynvml.nvmlShutdown()
+        return min(n, len(ids)) if ids is not None else n
+    except Exception:
+        pass
+    try:
+        import torch
+        return torch.cuda.device_count() if torch.cuda.is_available() else 0
+    except Exception:
+        return 0
+
+
 def discover() -> Topology:
     t = Topology(cpu_count=os.cpu_count() or 1)
     fake = _visible_override()

@@ -153,6 +153,16 @@ class Communicator:
                 return arena
         return None
 
+    def alloc_pair(self, nbytes_grad: int, nbytes_param: int):
+        """Symmetric (grad, param) arenas for one parameter group; plain tensors otherwise."""
+        from . import symm
+        if self.pad is not None:
+            want_mc = self.world > 1 and os.environ.get("TFC_DISABLE_NVLS") != "1"
+            g = symm.SymmetricBuffer(nbytes_grad, self.device, self.xchg, want_multicast=want_mc)
+            p = symm.SymmetricBuffer(nbytes_param, self.device, self.xchg, want_multicast=want_mc)
+            return g, p
+        return None, None
+
     def make_ctx(self, grad_buf, param_buf) -> CommCtx:
         ctx = CommCtx()
         ctx.rank, ctx.world = self.rank, self.world

@@ -465,3 +465,15 @@ def test_reduce_lr_on_plateau_and_csv_logger(tmp_path):
     assert len(log.read_text().strip().splitlines()) == 9                 # appended, one header
     with pytest.raises(ValueError):
         keras.callbacks.ReduceLROnPlateau(factor=1.5)
+
+
+def test_fit_keyword_contract():
+    x, y = _blobs(64)
+    m = _mlp()
+    hist = m.fit(x, y, batch_size=32, epochs=4, verbose=0, validation_data=(x, y), validation_freq=2)
+    assert len(hist.history["loss"]) == 4 and len(hist.history["val_loss"]) == 2      # epochs 2 and 4
+    with pytest.raises(NotImplementedError, match="sample_weight"):
+        m.fit(x, y, sample_weight=np.ones(len(x)), verbose=0)
+    with pytest.raises(TypeError, match="unexpected keyword"):
+        m.fit(x, y, epochz=3)
+    m.fit(x, y, batch_size=32, epochs=1, verbose=0, workers=4, use_multiprocessing=False)   # accepted, meaningless here
