@@ -63,8 +63,14 @@ class Dataset:
         return Dataset(self._source, self._ops + [op])
 
     # -- transformations ------------------------------------------------------------------------
-    def map(self, fn, num_parallel_calls=None, **_):
-        return self._with(("map", fn))
+    def map(self, fn, num_parallel_calls=None, deterministic=True, **_):
+        """``num_parallel_calls`` (or AUTOTUNE): the function runs on a pool of threads, results come
+        out in input order; numpy releases the GIL in the heavy calls (resize, casts), so decoding /
+        augmenting scales with cores like tf.data's parallel map."""
+        workers = 0
+        if num_parallel_calls is not None:
+            workers = _autotune_workers() if int(num_parallel_calls) < 0 else int(num_parallel_calls)
+        return self._with(("map", fn, workers if workers > 1 else 0))
 
     def cache(self, filename=""):
         return self._with(("cache",))
@@ -85,7 +91,10 @@ class Dataset:
         return self._with(("skip", int(count)))
 
     def prefetch(self, buffer_size=None):
-        return self
+        """Elements are produced by a background thread, up to ``buffer_size`` ahead of the consumer
+        (AUTOTUNE: 2), overlapping the input pipeline with the training step."""
+        n = 2 if buffer_size is None or int(buffer_size) < 0 else int(buffer_size)
+        return self._with(("prefetch", n)) if n > 0 else self
 
     def with_options(self, options):
         return self
@@ -115,7 +124,7 @@ class Dataset:
                 n = max(n - op[1], 0)
             elif op[0] == "unbatch":
                 return -2
-        return n
+        return n                        # map / cache / shuffle / prefetch keep the count
 
     def __len__(self):
         n = self.cardinality()
@@ -154,16 +163,87 @@ class Dataset:
         return iter(self)
 
 
+def _autotune_workers() -> int:
+    import os
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except (AttributeError, OSError):
+        cores = os.cpu_count() or 1
+    return max(1, min(8, cores))
+
+
 def _apply(it, op, rng, ds, idx):
     kind = op[0]
     if kind == "map":
         fn = op[1]
+        workers = op[2] if len(op) > 2 else 0
+
+        def call(e):
+            out = fn(*e) if isinstance(e, tuple) else fn(e)
+            return _map_structure(_to_numpy, out) if not isinstance(out, tuple) else \
+                tuple(_map_structure(_to_numpy, o) for o in out)
 
         def gen():
             for e in it:
-                out = fn(*e) if isinstance(e, tuple) else fn(e)
-                yield _map_structure(_to_numpy, out) if not isinstance(out, tuple) else \
-                    tuple(_map_structure(_to_numpy, o) for o in out)
+                yield call(e)
+
+        def parallel_gen():
+            import collections
+            from concurrent.futures import ThreadPoolExecutor
+            window = collections.deque()
+            pool = ThreadPoolExecutor(max_workers=workers, thread_name_prefix="tfc-data-map")
+            try:
+                for e in it:
+                    window.append(pool.submit(call, e))
+                    if len(window) >= 2 * workers:
+                        yield window.popleft().result()      # input order is kept
+                while window:
+                    yield window.popleft().result()
+            finally:
+                for f in window:
+                    f.cancel()
+                pool.shutdown(wait=False)
+        return parallel_gen() if workers else gen()
+    if kind == "prefetch":
+        def gen():
+            import queue
+            import threading
+            q = queue.Queue(maxsize=op[1])
+            stop = threading.Event()
+            end = object()
+
+            def produce():
+                try:
+                    for e in it:
+                        while not stop.is_set():
+                            try:
+                                q.put(e, timeout=0.1)
+                                break
+                            except queue.Full:
+                                continue
+                        if stop.is_set():
+                            return
+                    item = end
+                except BaseException as err:             # surfaces in the consumer
+                    item = err
+                while not stop.is_set():
+                    try:
+                        q.put(item, timeout=0.1)
+                        return
+                    except queue.Full:
+                        continue
+            t = threading.Thread(target=produce, name="tfc-data-prefetch", daemon=True)
+            t.start()
+            try:
+                while True:
+                    e = q.get()
+                    if e is end:
+                        return
+                    if isinstance(e, BaseException):
+                        raise e
+                    yield e
+            finally:
+                stop.set()
         return gen()
     if kind == "cache":
         key = ("_cache", idx)

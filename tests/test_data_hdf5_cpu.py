@@ -86,3 +86,64 @@ def test_hdf5_rejects_garbage_and_oversized_attributes(tmp_path):
     with hdf5.File(str(tmp_path / "big.h5"), "w") as f:
         with pytest.raises(hdf5.AttributeTooLarge):
             f.attrs["model_config"] = b"x" * 70000               # > one 64 KB object-header message
+
+
+# -- parallel map and prefetch (tf.data runs these in C++ threads; here: Python threads around numpy) --
+def test_parallel_map_keeps_order_and_uses_several_threads():
+    import threading
+    import time
+    from cloud_b200 import data
+    seen = set()
+
+    def slow_square(v):
+        seen.add(threading.current_thread().name)
+        time.sleep(0.01)
+        return v * v
+    ds = data.Dataset.range(40)
+    t0 = time.perf_counter()
+    serial = [int(v) for v in ds.map(slow_square)]
+    t_serial = time.perf_counter() - t0
+    seen.clear()
+    t0 = time.perf_counter()
+    parallel = [int(v) for v in ds.map(slow_square, num_parallel_calls=4)]
+    t_parallel = time.perf_counter() - t0
+    assert parallel == serial == [i * i for i in range(40)]
+    assert len(seen) >= 2 and all(n.startswith("tfc-data-map") for n in seen)
+    assert t_parallel < 0.6 * t_serial
+    auto = ds.map(slow_square, num_parallel_calls=data.experimental.AUTOTUNE).batch(8)
+    assert [b.tolist() for b in auto][0] == [0, 1, 4, 9, 16, 25, 36, 49] and auto.cardinality() == 5
+    # a consumer that stops early does not leave the pool hanging
+    assert [int(v) for v in ds.map(slow_square, num_parallel_calls=4).take(3)] == [0, 1, 4]
+
+
+def test_prefetch_overlaps_producer_and_consumer_and_forwards_errors():
+    import time
+    from cloud_b200 import data
+
+    def slow(v):
+        time.sleep(0.01)
+        return v
+    ds = data.Dataset.range(30).map(slow)
+    t0 = time.perf_counter()
+    for _ in ds:
+        time.sleep(0.01)                       # the "training step"
+    t_plain = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    got = []
+    for v in ds.prefetch(4):
+        time.sleep(0.01)
+        got.append(int(v))
+    t_prefetch = time.perf_counter() - t0
+    assert got == list(range(30)) and t_prefetch < 0.75 * t_plain
+    assert ds.prefetch(data.AUTOTUNE).cardinality() == 30
+    assert [int(v) for v in ds.prefetch(2).take(2)] == [0, 1]          # early stop: the thread lets go
+
+    def boom(v):
+        if v == 5:
+            raise ValueError("bad element")
+        return v
+    with pytest.raises(ValueError, match="bad element"):
+        list(data.Dataset.range(10).map(boom).prefetch(2))
+    # two epochs over the same dataset object
+    twice = data.Dataset.range(6).shuffle(6, seed=1).batch(2).prefetch(2)
+    assert sorted(sum((b.tolist() for b in twice), [])) == sorted(sum((b.tolist() for b in twice), [])) == list(range(6))
