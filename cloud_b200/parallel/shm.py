@@ -21,7 +21,7 @@ import torch.distributed as dist
 from ..ops import _lib
 
 ALGO_ONESHOT, ALGO_TWOSHOT = 0, 1
-ONESHOT_MAX_BYTES = 256 << 10          # below this the second pass of two-shot costs more than it saves
+ONESHOT_MAX_BYTES = 16 << 10           # measured cross-over (bench/shm_allreduce.py, 2 and 4 ranks)
 
 
 class ShmError(RuntimeError):
