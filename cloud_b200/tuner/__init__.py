@@ -4,4 +4,4 @@ a local Vizier-compatible optimizer, plus a multi-GPU trial scheduler
 from .tuner import CloudOracle, CloudTuner, DistributingCloudTuner  # noqa: F401
 from .scheduler import TrialScheduler  # noqa: F401
 from .engine import HyperParameters, Objective  # noqa: F401
-from .engine.tuner import RandomSearch  # noqa: F401
+from .engine.tuner import BayesianOptimization, RandomSearch  # noqa: F401

@@ -229,3 +229,91 @@ class RandomSearchOracle(Oracle):
         if trial.metrics.exists(obj.name):
             trial.score = trial.metrics.get_best_value(obj.name)
             trial.best_step = trial.metrics.get_best_step(obj.name)
+
+
+class BayesianOptimizationOracle(RandomSearchOracle):
+    """KerasTuner's ``BayesianOptimization`` oracle on this framework's Gaussian-process bandit
+    (``tuner/gp_bandit.py``, the model the local optimizer service uses too): the first trial
+    evaluates the defaults, the next ``num_initial_points - 1`` are random, after that every trial is
+    the random candidate with the largest expected improvement given the finished trials; running
+    trials count as observations at their predicted value, so parallel workers spread out."""
+
+    def __init__(self, objective, max_trials=None, num_initial_points=None, num_candidates=256,
+                 hyperparameters=None, allow_new_entries=True, tune_new_entries=True, seed=None):
+        super().__init__(objective, max_trials=max_trials, hyperparameters=hyperparameters,
+                         allow_new_entries=allow_new_entries, tune_new_entries=tune_new_entries, seed=seed)
+        self.num_initial_points = num_initial_points
+        self.num_candidates = int(num_candidates)
+
+    @staticmethod
+    def _entries(specs, values):
+        """A value dict in the optimizer service's parameter-list shape (what gp_bandit encodes)."""
+        out = []
+        for spec in specs:
+            name = spec["parameter"]
+            if name not in values:
+                continue
+            v = values[name]
+            if spec["type"] == "CATEGORICAL":
+                out.append({"parameter": name, "stringValue": str(v)})
+            elif spec["type"] == "INTEGER":
+                out.append({"parameter": name, "intValue": str(int(v))})
+            else:
+                out.append({"parameter": name, "floatValue": float(v)})
+        return out
+
+    def _neighbour(self, values):
+        """A point near ``values``: numeric hyperparameters take a Gaussian step of 10 % of their
+        (log-)range and are snapped to their step, the others mostly keep their value."""
+        import math
+        rng = random.Random(self._seed_state)
+        self._seed_state += 1
+        out = {}
+        for hp in self.hyperparameters.space:
+            v = values.get(hp.name, hp.default)
+            if isinstance(hp, (hp_module.Int, hp_module.Float)):
+                lo, hi = float(hp.min_value), float(hp.max_value)
+                log = getattr(hp, "sampling", None) == "log" and lo > 0
+                a, b = (math.log(lo), math.log(hi)) if log else (lo, hi)
+                x = rng.gauss(math.log(float(v)) if log else float(v), 0.1 * (b - a))
+                x = min(max(x, a), b)
+                x = math.exp(x) if log else x
+                step = getattr(hp, "step", None)
+                if isinstance(hp, hp_module.Int):
+                    step = step or 1
+                if step:
+                    x = lo + round((x - lo) / step) * step
+                x = min(max(x, lo), hi)
+                out[hp.name] = int(round(x)) if isinstance(hp, hp_module.Int) else x
+            elif isinstance(hp, hp_module.Fixed):
+                out[hp.name] = hp.value
+            else:
+                out[hp.name] = v if rng.random() < 0.75 else hp.random_sample(rng.randrange(1 << 30))
+        return out
+
+    def _populate_space(self, trial_id):
+        from .. import gp_bandit, utils
+        obj = self.objective[0] if isinstance(self.objective, list) else self.objective
+        specs = utils._convert_hyperparams_to_optimizer_params(self.hyperparameters)
+        done, running = [], []
+        for t in self.trials.values():
+            if t.status == trial_lib.TrialStatus.COMPLETED and t.score is not None:
+                done.append((self._entries(specs, t.hyperparameters.values), float(t.score)))
+            elif t.status == trial_lib.TrialStatus.INVALID:
+                done.append((self._entries(specs, t.hyperparameters.values), None))
+            elif t.status == trial_lib.TrialStatus.RUNNING:
+                running.append(self._entries(specs, t.hyperparameters.values))
+        n_init = self.num_initial_points or gp_bandit.min_initial_trials(gp_bandit.SpaceEncoder(specs).dims)
+        if len(done) < n_init:
+            return super()._populate_space(trial_id)
+        candidates = [self._random_values() for _ in range(self.num_candidates)]
+        ranked = sorted((d for d in done if d[1] is not None), key=lambda d: d[1],
+                        reverse=obj.direction == "max")
+        best_values = [t.hyperparameters.values for t in self.trials.values()
+                       if t.score is not None and any(t.score == r[1] for r in ranked[:3])]
+        for anchor in best_values[:3]:                   # exploit: neighbours of the best trials
+            candidates += [self._neighbour(anchor) for _ in range(self.num_candidates // 8)]
+        pick = gp_bandit.choose(specs, done, running, [self._entries(specs, c) for c in candidates],
+                                maximize=obj.direction == "max")
+        values = candidates[pick] if pick is not None else self._random_values()
+        return {"status": trial_lib.TrialStatus.RUNNING, "values": values}

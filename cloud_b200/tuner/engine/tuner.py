@@ -242,3 +242,18 @@ class RandomSearch(Tuner):
                                     tune_new_entries=tune_new_entries,
                                     allow_new_entries=allow_new_entries)
         super().__init__(oracle, hypermodel, **kwargs)
+
+
+class BayesianOptimization(Tuner):
+    """``kerastuner.tuners.BayesianOptimization``: Gaussian-process regression + expected improvement
+    over the declared search space (``oracle.BayesianOptimizationOracle``)."""
+
+    def __init__(self, hypermodel, objective, max_trials, num_initial_points=None, seed=None,
+                 hyperparameters=None, tune_new_entries=True, allow_new_entries=True, **kwargs):
+        from .oracle import BayesianOptimizationOracle
+        oracle = BayesianOptimizationOracle(objective=objective, max_trials=max_trials,
+                                            num_initial_points=num_initial_points, seed=seed,
+                                            hyperparameters=hyperparameters,
+                                            tune_new_entries=tune_new_entries,
+                                            allow_new_entries=allow_new_entries)
+        super().__init__(oracle, hypermodel, **kwargs)

@@ -215,3 +215,70 @@ def test_no_stopping_config_never_stops(svc):
     for k in range(4):
         _finish(svc, _suggest(svc, name, "f%d" % k), [0.9])
     assert _running(svc, name, [0.0, 0.0, 0.0], "hopeless") is False
+
+
+# -- the same Gaussian-process model behind KerasTuner's BayesianOptimization tuner --------------------
+def _drive(oracle, n):
+    """create_trial / update_trial / end_trial like Tuner.search does, scoring with a known function."""
+    best = -float("inf")
+    for _ in range(n):
+        trial = oracle.create_trial("tuner0")
+        v = trial.hyperparameters.values
+        score = -(math.log10(v["lr"]) + 3) ** 2 - ((v["units"] - 96) / 40) ** 2 - (0.0 if v["act"] == "relu" else 0.4) \
+            - (0.1 if v["wide"] else 0.0)
+        oracle.update_trial(trial.trial_id, {"score": score}, step=0)
+        oracle.end_trial(trial.trial_id, "COMPLETED")
+        best = max(best, score)
+    return best
+
+
+def _hp_space():
+    from cloud_b200.tuner import HyperParameters
+    hps = HyperParameters()
+    hps.Float("lr", 1e-5, 1e-1, sampling="log", default=1e-2)
+    hps.Int("units", 8, 128, step=8, default=32)
+    hps.Choice("act", ["relu", "tanh"])
+    hps.Boolean("wide", default=True)
+    return hps
+
+
+def test_bayesian_optimization_oracle_beats_random_search(tmp_path):
+    from cloud_b200.tuner import Objective
+    from cloud_b200.tuner.engine import oracle as oracle_module
+    gp, rnd = [], []
+    for seed in range(3):
+        for cls, out in ((oracle_module.BayesianOptimizationOracle, gp), (oracle_module.RandomSearchOracle, rnd)):
+            o = cls(Objective("score", "max"), max_trials=30, hyperparameters=_hp_space(), seed=seed + 1)
+            o._set_project_dir(str(tmp_path / "{}{}".format(cls.__name__, seed)), "p", overwrite=True)
+            out.append(_drive(o, 26))
+    assert statistics.mean(gp) > statistics.mean(rnd) and statistics.median(gp) > -0.15
+    # first trial = the declared defaults; values respect steps and choices
+    o = oracle_module.BayesianOptimizationOracle(Objective("score", "max"), max_trials=4,
+                                                 hyperparameters=_hp_space(), seed=7)
+    o._set_project_dir(str(tmp_path / "first"), "p", overwrite=True)
+    first = o.create_trial("t").hyperparameters.values
+    assert first == {"lr": 1e-2, "units": 32, "act": "relu", "wide": True}
+
+
+def test_bayesian_optimization_tuner_searches_a_real_model(tmp_path):
+    import cloud_b200 as tfc
+    from cloud_b200 import tuner as tuners
+    tfc.distribute.experimental_set_strategy(tfc.distribute.OneDeviceStrategy("/cpu:0"))
+    keras = tfc.keras
+    rng = np.random.RandomState(0)
+    centers = rng.randn(3, 10) * 3
+    y = rng.randint(0, 3, 192)
+    x = (centers[y] + rng.randn(192, 10)).astype("float32")
+
+    def build(hp):
+        m = keras.Sequential([keras.layers.Dense(hp.Int("units", 4, 32, step=4), activation="relu", input_shape=(10,)),
+                              keras.layers.Dense(3, activation="softmax")])
+        m.compile(keras.optimizers.Adam(hp.Float("lr", 1e-4, 1e-1, sampling="log")),
+                  "sparse_categorical_crossentropy", metrics=["accuracy"])
+        return m
+    t = tuners.BayesianOptimization(build, objective="val_accuracy", max_trials=5, num_initial_points=2, seed=0,
+                                    directory=str(tmp_path), project_name="bo")
+    t.search(x=x, y=y, epochs=2, validation_data=(x, y), verbose=0)
+    assert len(t.oracle.trials) == 5
+    best = t.get_best_models(1)[0]
+    assert best.evaluate(x, y, verbose=0)[1] >= max(tr.score for tr in t.oracle.trials.values()) - 0.2
