@@ -5,3 +5,4 @@ from .tuner import CloudOracle, CloudTuner, DistributingCloudTuner  # noqa: F401
 from .scheduler import TrialScheduler  # noqa: F401
 from .engine import HyperParameters, Objective  # noqa: F401
 from .engine.tuner import BayesianOptimization, RandomSearch  # noqa: F401
+from .engine.hyperband import Hyperband  # noqa: F401

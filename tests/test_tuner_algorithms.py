@@ -282,3 +282,100 @@ def test_bayesian_optimization_tuner_searches_a_real_model(tmp_path):
     assert len(t.oracle.trials) == 5
     best = t.get_best_models(1)[0]
     assert best.evaluate(x, y, verbose=0)[1] >= max(tr.score for tr in t.oracle.trials.values()) - 0.2
+
+
+# -- Hyperband ------------------------------------------------------------------------------------------
+def test_hyperband_schedule_promotes_the_best_and_waits_for_unfinished_rounds(tmp_path):
+    from cloud_b200.tuner import Objective
+    from cloud_b200.tuner.engine import hyperband, trial as trial_lib
+    o = hyperband.HyperbandOracle(Objective("score", "max"), max_epochs=9, factor=3, hyperparameters=_hp_space(), seed=3)
+    o._set_project_dir(str(tmp_path), "hb", overwrite=True)
+    assert o.num_brackets() == 3
+    assert [[o.round_size(b, r) for r in range(o.num_rounds(b))] for b in (2, 1, 0)] == [[9, 3, 1], [5, 2], [3]]
+    assert [[o.round_epochs(b, r) for r in range(o.num_rounds(b))] for b in (2, 1, 0)] == [[1, 3, 9], [3, 9], [9]]
+    assert o.total_trials() == 23
+
+    def finish(trial, score, status="COMPLETED"):
+        if status == "COMPLETED":
+            o.update_trial(trial.trial_id, {"score": score}, step=trial.hyperparameters.values["tuner/epochs"] - 1)
+        o.end_trial(trial.trial_id, status)
+
+    # bracket 2, round 0: nine fresh configurations on one epoch; two workers
+    first = [o.create_trial("w%d" % i) for i in range(2)]
+    assert first[0].hyperparameters.values["units"] == 32            # the defaults go first
+    finish(first[0], 0.10)
+    finish(first[1], 0.20)
+    rest = []
+    for i in range(7):
+        t = o.create_trial("w0")
+        assert t.hyperparameters.values["tuner/epochs"] == 1 and t.hyperparameters.values["tuner/round"] == 0
+        rest.append(t)
+        if i < 6:
+            finish(t, 0.30 + 0.01 * i)
+    # the round is handed out but its last trial still runs: a second worker has to wait
+    assert o.create_trial("w1").status == trial_lib.TrialStatus.IDLE
+    finish(rest[6], None, status="INVALID")                         # ... and then fails
+    promoted = [o.create_trial("w%d" % i) for i in range(3)]
+    parents = [t.hyperparameters.values["tuner/trial_id"] for t in promoted]
+    assert parents == [rest[5].trial_id, rest[4].trial_id, rest[3].trial_id]      # best three, best first
+    for t, parent in zip(promoted, rest[5:2:-1]):
+        v = t.hyperparameters.values
+        assert (v["tuner/epochs"], v["tuner/initial_epoch"], v["tuner/round"], v["tuner/bracket"]) == (3, 1, 1, 2)
+        assert {k: v[k] for k in ("lr", "units", "act", "wide")} == \
+            {k: parent.hyperparameters.values[k] for k in ("lr", "units", "act", "wide")}
+    for i, t in enumerate(promoted):
+        finish(t, 0.5 + 0.1 * i)
+    final = o.create_trial("w0")
+    assert final.hyperparameters.values["tuner/trial_id"] == promoted[2].trial_id
+    assert final.hyperparameters.values["tuner/epochs"] == 9 and final.hyperparameters.values["tuner/initial_epoch"] == 3
+    finish(final, 0.9)
+    # the remaining brackets run to the end, then the oracle stops
+    count = 13
+    while True:
+        t = o.create_trial("w0")
+        if t.status == trial_lib.TrialStatus.STOPPED:
+            break
+        finish(t, 0.1)
+        count += 1
+    assert count == o.total_trials()
+    assert o.get_best_trials(1)[0].trial_id == final.trial_id
+
+
+def test_hyperband_tuner_continues_training_from_the_parent_checkpoint(tmp_path):
+    import cloud_b200 as tfc
+    from cloud_b200 import tuner as tuners
+    tfc.distribute.experimental_set_strategy(tfc.distribute.OneDeviceStrategy("/cpu:0"))
+    keras = tfc.keras
+    rng = np.random.RandomState(0)
+    centers = rng.randn(3, 10) * 2
+    y = rng.randint(0, 3, 192)
+    x = (centers[y] + rng.randn(192, 10)).astype("float32")
+    histories = {}
+
+    class Record(keras.callbacks.Callback):
+        def on_epoch_end(self, epoch, logs=None):
+            histories.setdefault(id(self.model), []).append((epoch, logs["loss"]))
+
+    def build(hp):
+        m = keras.Sequential([keras.layers.Dense(hp.Int("units", 8, 32, step=8), activation="relu", input_shape=(10,)),
+                              keras.layers.Dense(3, activation="softmax")])
+        m.compile(keras.optimizers.SGD(hp.Choice("lr", [0.01, 0.03])), "sparse_categorical_crossentropy",
+                  metrics=["accuracy"])
+        return m
+    t = tuners.Hyperband(build, objective="loss", max_epochs=4, factor=3, seed=1, directory=str(tmp_path),
+                         project_name="hb")
+    assert t.oracle.total_trials() == 10
+    t.search(x=x, y=y, batch_size=32, verbose=0, callbacks=[Record()])
+    trials = list(t.oracle.trials.values())
+    assert len(trials) == 10
+    promoted = [tr for tr in trials if "tuner/trial_id" in tr.hyperparameters.values]
+    assert len(promoted) == 2 and all(tr.hyperparameters.values["tuner/initial_epoch"] == 2 for tr in promoted)
+    runs = sorted(histories.values(), key=lambda h: h[0][0])
+    fresh = [h for h in runs if h[0][0] == 0]
+    resumed = [h for h in runs if h[0][0] == 2]
+    assert len(fresh) == 8 and len(resumed) == 2
+    assert all([e for e, _l in h] == [2, 3] for h in resumed)           # two more epochs, not four
+    # a resumed run starts where its parent stopped, far below any first epoch
+    assert max(h[0][1] for h in resumed) < min(h[0][1] for h in fresh)
+    best = t.get_best_models(1)[0]
+    assert best.evaluate(x, y, verbose=0)[0] < min(h[0][1] for h in fresh)
