@@ -350,17 +350,19 @@ def test_hyperband_tuner_continues_training_from_the_parent_checkpoint(tmp_path)
     centers = rng.randn(3, 10) * 2
     y = rng.randint(0, 3, 192)
     x = (centers[y] + rng.randn(192, 10)).astype("float32")
-    histories = {}
+    histories, built = {}, []
 
     class Record(keras.callbacks.Callback):
         def on_epoch_end(self, epoch, logs=None):
-            histories.setdefault(id(self.model), []).append((epoch, logs["loss"]))
+            histories.setdefault(self.model._build_index, []).append((epoch, logs["loss"]))
 
     def build(hp):
         m = keras.Sequential([keras.layers.Dense(hp.Int("units", 8, 32, step=8), activation="relu", input_shape=(10,)),
                               keras.layers.Dense(3, activation="softmax")])
         m.compile(keras.optimizers.SGD(hp.Choice("lr", [0.01, 0.03])), "sparse_categorical_crossentropy",
                   metrics=["accuracy"])
+        m._build_index = len(built)                 # object ids can be reused once a model is freed
+        built.append(m._build_index)
         return m
     t = tuners.Hyperband(build, objective="loss", max_epochs=4, factor=3, seed=1, directory=str(tmp_path),
                          project_name="hb")
@@ -375,7 +377,12 @@ def test_hyperband_tuner_continues_training_from_the_parent_checkpoint(tmp_path)
     resumed = [h for h in runs if h[0][0] == 2]
     assert len(fresh) == 8 and len(resumed) == 2
     assert all([e for e, _l in h] == [2, 3] for h in resumed)           # two more epochs, not four
-    # a resumed run starts where its parent stopped, far below any first epoch
-    assert max(h[0][1] for h in resumed) < min(h[0][1] for h in fresh)
+    # a resumed run starts where its parent stopped: below the parent's own first epoch and close to
+    # its last one (models are built once for the search space, then once per trial, in trial order)
+    by_trial = {tr.trial_id: histories[built[i + 1]] for i, tr in enumerate(trials)}
+    for tr in promoted:
+        parent = by_trial[tr.hyperparameters.values["tuner/trial_id"]]
+        mine = by_trial[tr.trial_id]
+        assert mine[0][1] < parent[0][1] and mine[0][1] < parent[-1][1] + 0.05
     best = t.get_best_models(1)[0]
-    assert best.evaluate(x, y, verbose=0)[0] < min(h[0][1] for h in fresh)
+    assert best.evaluate(x, y, verbose=0)[0] < t.oracle.get_best_trials(1)[0].score + 0.05
