@@ -84,6 +84,13 @@ def test_model_search_inside_a_job(tmp_path):
     assert "Accuracy:" in res.stdout and os.path.exists(tmp_path / "ak" / "model.h5")
 
 
+def test_hyperband_and_bayesian_tuners_example(tmp_path):
+    res = _run(["keras_tuner_hyperband_example.py", "--samples", "384", "--max-epochs", "4", "--bayesian-trials", "3",
+                "--directory", str(tmp_path / "tuners")], EXAMPLES, tmp_path)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    assert "Hyperband ran 10 trials" in res.stdout and "Bayesian optimisation: best validation accuracy" in res.stdout
+
+
 # -- notebooks, run headless by cloud_b200.utils.notebook ----------------------------------------
 def _run_notebook(name, tmp_path, **env):
     return _run(["-m", "cloud_b200.utils.notebook", name], EXAMPLES, tmp_path, TFC_EXAMPLE_EPOCHS="2", **env)
