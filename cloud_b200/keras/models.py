@@ -319,6 +319,7 @@ class Model(nn.Module):
 
     def __init__(self, inputs=None, outputs=None, name=None, **kwargs):
         super().__init__()
+        self._weighted_targets = None
         self.name = name or L._auto_name(type(self).__name__)
         self.built = False
         self.stop_training = False
@@ -562,6 +563,7 @@ class Model(nn.Module):
         self._engine = None
         self._graph = None
         self._regularized_layers = None
+        self._weighted_targets = None
 
     def _build_with_batch(self, xb):
         """Run one forward on a single sample batch to create lazily-built weights."""
@@ -608,13 +610,22 @@ class Model(nn.Module):
     def _loss_and_metrics(self, out, y, global_batch, aux):
         inv = 1.0 / float(global_batch)
         fused = False
-        if isinstance(self.loss, losses_mod.SparseCategoricalCrossentropy) and out.dim() == 2:
+        weights = None
+        if self._weighted_targets is not None and self.training:
+            # fit(sample_weight= / class_weight=): the weights ride in the last column of y
+            weights = y[..., -1].float()
+            y = y[..., :-1]
+            if self._weighted_targets == "1d":
+                y = y.squeeze(-1)
+        if weights is None and isinstance(self.loss, losses_mod.SparseCategoricalCrossentropy) and out.dim() == 2:
             logits = self.loss.logits(out)
             if logits is not None:
                 loss = ops.softmax_cross_entropy(logits, y.reshape(-1), grad_scale=inv, stats=aux)
                 fused = True
         if not fused:
             per = self.loss.per_sample(y, out.float() if out.dtype != torch.float32 else out)
+            if weights is not None:
+                per = per * weights             # Keras: sum(w * loss) / batch size
             s = per.sum()
             with torch.no_grad():
                 aux[AUX_LOSS] += s.detach()
@@ -817,10 +828,7 @@ class Model(nn.Module):
             steps_per_epoch=None, validation_steps=None, validation_batch_size=None, **kwargs):
         if self.loss is None:
             raise RuntimeError("You must compile your model with a loss before calling fit().")
-        for name in ("class_weight", "sample_weight"):       # would change the loss: never ignore silently
-            if kwargs.get(name) is not None:
-                raise NotImplementedError("fit({}=...) is not supported; weight the loss in a custom "
-                                          "training loop (tfc.GradientTape) instead.".format(name))
+        weights = self._sample_weights(x, y, kwargs.get("sample_weight"), kwargs.get("class_weight"))
         unknown = set(kwargs) - {"class_weight", "sample_weight", "workers", "use_multiprocessing",
                                  "max_queue_size", "validation_freq"}
         if unknown:
@@ -830,6 +838,44 @@ class Model(nn.Module):
             if n_val:
                 validation_data = (x[-n_val:], y[-n_val:])
                 x, y = x[:-n_val], y[:-n_val]
+        if weights is not None:
+            y_arr = _np(y).astype(np.float32)
+            self._weighted_targets = "1d" if y_arr.ndim == 1 else "nd"
+            y = np.concatenate([y_arr.reshape(len(y_arr), -1), weights.reshape(-1, 1)], axis=1)
+        try:
+            return self._fit(x, y, batch_size, epochs, verbose, callbacks, validation_data, shuffle,
+                             initial_epoch, steps_per_epoch, validation_steps, validation_batch_size, kwargs)
+        finally:
+            self._weighted_targets = None
+
+    def _sample_weights(self, x, y, sample_weight, class_weight):
+        """Per-sample loss weights of ``fit(sample_weight=..., class_weight=...)`` as one float32
+        array (their product when both are given), or None.  Array inputs only."""
+        if sample_weight is None and class_weight is None:
+            return None
+        if isinstance(x, (Dataset, DistributedDataset)) or y is None:
+            raise NotImplementedError("sample_weight / class_weight need array inputs (x, y); with a "
+                                      "dataset, weight the loss in a custom training loop.")
+        n = len(y)
+        w = np.ones(n, dtype=np.float32)
+        if sample_weight is not None:
+            sw = _np(sample_weight).astype(np.float32).reshape(-1)
+            if len(sw) != n:
+                raise ValueError("sample_weight has {} entries for {} samples".format(len(sw), n))
+            w *= sw
+        if class_weight is not None:
+            labels = _np(y)
+            if labels.ndim > 1 and labels.shape[-1] > 1:
+                labels = labels.argmax(-1)              # one-hot targets
+            labels = labels.reshape(-1).astype(np.int64)
+            table = np.ones(int(max(labels.max(), max(class_weight)) + 1), dtype=np.float32)
+            for cls, value in class_weight.items():
+                table[int(cls)] = float(value)
+            w *= table[labels]
+        return w
+
+    def _fit(self, x, y, batch_size, epochs, verbose, callbacks, validation_data, shuffle, initial_epoch,
+             steps_per_epoch, validation_steps, validation_batch_size, kwargs):
         source = self._make_source(x, y, batch_size, shuffle, steps_per_epoch)
         first = next(iter(_peek(source)))
         eng = self._ensure_engine(first[0])

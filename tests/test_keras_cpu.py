@@ -472,8 +472,60 @@ def test_fit_keyword_contract():
     m = _mlp()
     hist = m.fit(x, y, batch_size=32, epochs=4, verbose=0, validation_data=(x, y), validation_freq=2)
     assert len(hist.history["loss"]) == 4 and len(hist.history["val_loss"]) == 2      # epochs 2 and 4
-    with pytest.raises(NotImplementedError, match="sample_weight"):
-        m.fit(x, y, sample_weight=np.ones(len(x)), verbose=0)
+    with pytest.raises(NotImplementedError, match="array inputs"):
+        m.fit(tfc.data.Dataset.from_tensor_slices((x, y)).batch(16), sample_weight=np.ones(len(x)), verbose=0)
     with pytest.raises(TypeError, match="unexpected keyword"):
         m.fit(x, y, epochz=3)
     m.fit(x, y, batch_size=32, epochs=1, verbose=0, workers=4, use_multiprocessing=False)   # accepted, meaningless here
+
+
+def test_sample_and_class_weights_scale_each_sample_loss():
+    x, y = _blobs(64)
+    # weight 0 for half of the samples == training on the other half with a batch twice as "large"
+    w = (np.arange(64) % 2).astype("float32")
+
+    def run(**fit_kwargs):
+        torch.manual_seed(5)
+        m = keras.Sequential([L.Dense(16, activation="relu", input_shape=(20,)), L.Dense(4, activation="softmax")])
+        m.compile(keras.optimizers.SGD(0.1), "sparse_categorical_crossentropy", metrics=["accuracy"])
+        hist = m.fit(x, y, batch_size=16, epochs=2, shuffle=False, verbose=0, **fit_kwargs)
+        return m.get_weights(), hist.history
+
+    weighted, hist_w = run(sample_weight=w)
+    # oracle: plain torch, the same SGD steps with sum(w * loss) / batch
+    torch.manual_seed(5)
+    ref = keras.Sequential([L.Dense(16, activation="relu", input_shape=(20,)), L.Dense(4, activation="softmax")])
+    ref(x[:1])
+    params = [p for p in ref.parameters()]
+    for _epoch in range(2):
+        for i in range(0, 64, 16):
+            out = ref(x[i:i + 16], training=True)
+            per = torch.nn.functional.nll_loss(torch.log(out.float()), torch.tensor(y[i:i + 16]), reduction="none")
+            loss = (per * torch.tensor(w[i:i + 16])).sum() / 16
+            grads = torch.autograd.grad(loss, params)
+            with torch.no_grad():
+                for p, g in zip(params, grads):
+                    p -= 0.1 * g
+    for a, b in zip(weighted, ref.get_weights()):
+        np.testing.assert_allclose(a, b, rtol=1e-4, atol=1e-5)
+    plain, hist_p = run()
+    assert not np.allclose(weighted[0], plain[0])
+    assert hist_w["loss"][0] < hist_p["loss"][0]                       # half of the terms are zeroed
+    # class weights are per-sample weights looked up from the labels; both kinds multiply
+    by_class, _ = run(class_weight={0: 2.0, 3: 0.0})
+    lookup = np.ones(4, dtype="float32")
+    lookup[0], lookup[3] = 2.0, 0.0
+    by_sample, _ = run(sample_weight=lookup[y])
+    for a, b in zip(by_class, by_sample):
+        np.testing.assert_allclose(a, b, rtol=1e-6)
+    both, _ = run(sample_weight=w, class_weight={0: 2.0, 3: 0.0})
+    product, _ = run(sample_weight=w * lookup[y])
+    for a, b in zip(both, product):
+        np.testing.assert_allclose(a, b, rtol=1e-6)
+    with pytest.raises(ValueError, match="sample_weight has"):
+        run(sample_weight=np.ones(3))
+    # the flag does not leak into later calls
+    m = _mlp()
+    m.fit(x, y, sample_weight=np.ones(64), epochs=1, verbose=0)
+    assert m._weighted_targets is None and np.isfinite(m.evaluate(x, y, verbose=0)[0])
+    m.fit(x, y, epochs=1, verbose=0)
