@@ -855,3 +855,11 @@ LAYER_CLASSES = {c.__name__: c for c in (
     AveragePooling2D, GlobalAveragePooling2D, GlobalMaxPooling2D, ZeroPadding2D,
     BatchNormalization, ImageNormalization, Add, Concatenate, Rescaling, RandomFlip, RandomRotation, RandomWidth,
     RandomHeight, RandomZoom)}
+
+
+# the layers of extra_layers.py live in this namespace too (`keras.layers.SeparableConv2D`, ...)
+from . import extra_layers as _extra  # noqa: E402
+for _cls in _extra.EXTRA_LAYERS:
+    globals()[_cls.__name__] = _cls
+    LAYER_CLASSES[_cls.__name__] = _cls
+del _cls

@@ -543,9 +543,18 @@ class Model(nn.Module):
             t = t.permute(0, 3, 1, 2)        # NHWC batch -> NCHW-logical channels_last view
         if t.dtype == torch.uint8:
             return t                          # an ImageNormalization layer consumes raw bytes
+        if not t.is_floating_point() and self._takes_token_ids():
+            return t                          # ids for an Embedding must not be rounded to bf16
         if t.is_floating_point() or t.dtype in (torch.int32, torch.int64, torch.int16, torch.int8):
             t = t.to(self._compute_dtype())
         return t
+
+    def _takes_token_ids(self) -> bool:
+        flag = getattr(self, "_token_ids", None)
+        if flag is None:
+            flag = any(type(m).__name__ == "Embedding" for m in self.modules())
+            object.__setattr__(self, "_token_ids", flag)
+        return flag
 
     # -- compile ------------------------------------------------------------------------------
     def compile(self, optimizer="rmsprop", loss=None, metrics=None, run_eagerly=False,
