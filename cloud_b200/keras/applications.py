@@ -6,7 +6,9 @@ Keras'; it is the model of the reference's flagship example
 (core/tests/examples/call_run_within_script_with_keras_fit.py:79-87) and of BASELINE.json's
 headline config.  BN+ReLU and BN+Add+ReLU are single fused layers (one memory pass each on the
 hand-written NHWC batch-norm kernels).  ``ResNet18`` is the basic-block variant used by the
-tuner benchmark (BASELINE.json config 4); weights are always random-init (no network here).
+tuner benchmark (BASELINE.json config 4).  ``ResNet101`` / ``ResNet152`` share ResNet50's blocks,
+``VGG16`` and ``MobileNet`` (depthwise-separable blocks) round off the zoo; parameter counts equal Keras'
+(tests/test_models_zoo.py).  Weights are always random-init (no network here).
 """
 from __future__ import annotations
 
@@ -63,18 +65,87 @@ def _head(x, include_top, pooling, classes, classifier_activation):
     return x
 
 
-def ResNet50(include_top=True, weights=None, input_tensor=None, input_shape=None, pooling=None,
-             classes=1000, classifier_activation="softmax", **kwargs):
+def _check_weights(weights):
     if weights not in (None,):
         raise ValueError("Pretrained weights cannot be downloaded on this box (no network); "
                          "pass weights=None and load a local file with load_weights().")
+
+
+def _resnet_v1(name, stack_blocks, include_top, weights, input_tensor, input_shape, pooling, classes,
+               classifier_activation):
+    _check_weights(weights)
     inp = input_tensor if input_tensor is not None else L.Input(shape=input_shape or (224, 224, 3))
     x = _stem(inp, True, 1.001e-5)
-    for stage, (filters, blocks, stride) in enumerate([(64, 3, 1), (128, 4, 2), (256, 6, 2), (512, 3, 2)], 2):
+    for stage, (filters, blocks, stride) in enumerate(zip((64, 128, 256, 512), stack_blocks, (1, 2, 2, 2)), 2):
         for b in range(blocks):
             x = _bottleneck(x, filters, stride if b == 0 else 1, b == 0, f"conv{stage}_block{b + 1}")
     x = _head(x, include_top, pooling, classes, classifier_activation)
-    return Model(inp, x, name="resnet50")
+    return Model(inp, x, name=name)
+
+
+def ResNet50(include_top=True, weights=None, input_tensor=None, input_shape=None, pooling=None,
+             classes=1000, classifier_activation="softmax", **kwargs):
+    return _resnet_v1("resnet50", (3, 4, 6, 3), include_top, weights, input_tensor, input_shape, pooling,
+                      classes, classifier_activation)
+
+
+def ResNet101(include_top=True, weights=None, input_tensor=None, input_shape=None, pooling=None,
+              classes=1000, classifier_activation="softmax", **kwargs):
+    """Keras ``ResNet101``: 44 707 176 parameters with the 1000-class head."""
+    return _resnet_v1("resnet101", (3, 4, 23, 3), include_top, weights, input_tensor, input_shape, pooling,
+                      classes, classifier_activation)
+
+
+def ResNet152(include_top=True, weights=None, input_tensor=None, input_shape=None, pooling=None,
+              classes=1000, classifier_activation="softmax", **kwargs):
+    """Keras ``ResNet152``: 60 419 944 parameters with the 1000-class head."""
+    return _resnet_v1("resnet152", (3, 8, 36, 3), include_top, weights, input_tensor, input_shape, pooling,
+                      classes, classifier_activation)
+
+
+def VGG16(include_top=True, weights=None, input_tensor=None, input_shape=None, pooling=None,
+          classes=1000, classifier_activation="softmax", **kwargs):
+    """Keras ``VGG16`` (layer names ``block1_conv1`` ... ``fc1``, ``fc2``, ``predictions``):
+    138 357 544 parameters at 224 x 224 with the top."""
+    _check_weights(weights)
+    inp = input_tensor if input_tensor is not None else L.Input(shape=input_shape or (224, 224, 3))
+    x = inp
+    for block, (filters, convs) in enumerate(((64, 2), (128, 2), (256, 3), (512, 3), (512, 3)), 1):
+        for c in range(convs):
+            x = L.Conv2D(filters, 3, padding="same", activation="relu", name=f"block{block}_conv{c + 1}")(x)
+        x = L.MaxPooling2D(2, strides=2, name=f"block{block}_pool")(x)
+    if include_top:
+        x = L.Flatten(name="flatten")(x)
+        x = L.Dense(4096, activation="relu", name="fc1")(x)
+        x = L.Dense(4096, activation="relu", name="fc2")(x)
+        x = L.Dense(classes, activation=classifier_activation, name="predictions")(x)
+    elif pooling == "avg":
+        x = L.GlobalAveragePooling2D()(x)
+    elif pooling == "max":
+        x = L.GlobalMaxPooling2D()(x)
+    return Model(inp, x, name="vgg16")
+
+
+def MobileNet(include_top=True, weights=None, input_tensor=None, input_shape=None, pooling=None,
+              classes=1000, alpha=1.0, classifier_activation="softmax", **kwargs):
+    """MobileNet v1 graph: a strided 3x3 stem, then thirteen depthwise-separable blocks
+    (depthwise 3x3 + BN + ReLU, pointwise 1x1 + BN + ReLU), global average pooling, classifier.
+    ``alpha`` scales every width.  4.2 M parameters at alpha = 1 with 1000 classes."""
+    _check_weights(weights)
+    inp = input_tensor if input_tensor is not None else L.Input(shape=input_shape or (224, 224, 3))
+
+    def width(c):
+        return max(8, int(c * alpha))
+    x = L.Conv2D(width(32), 3, strides=2, padding="same", use_bias=False, name="conv1")(inp)
+    x = L.BatchNormalization(activation="relu", name="conv1_bn")(x)
+    plan = [(64, 1), (128, 2), (128, 1), (256, 2), (256, 1), (512, 2)] + [(512, 1)] * 5 + [(1024, 2), (1024, 1)]
+    for i, (filters, stride) in enumerate(plan, 1):
+        x = L.DepthwiseConv2D(3, strides=stride, padding="same", use_bias=False, name=f"conv_dw_{i}")(x)
+        x = L.BatchNormalization(activation="relu", name=f"conv_dw_{i}_bn")(x)
+        x = L.Conv2D(width(filters), 1, use_bias=False, name=f"conv_pw_{i}")(x)
+        x = L.BatchNormalization(activation="relu", name=f"conv_pw_{i}_bn")(x)
+    x = _head(x, include_top, pooling, classes, classifier_activation)
+    return Model(inp, x, name="mobilenet")
 
 
 def ResNet18(include_top=True, weights=None, input_tensor=None, input_shape=None, pooling=None,
@@ -94,6 +165,8 @@ def ResNet18(include_top=True, weights=None, input_tensor=None, input_shape=None
 
 class resnet:  # tf.keras.applications.resnet.*
     ResNet50 = staticmethod(ResNet50)
+    ResNet101 = staticmethod(ResNet101)
+    ResNet152 = staticmethod(ResNet152)
 
     @staticmethod
     def preprocess_input(x, data_format=None):

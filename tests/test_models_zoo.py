@@ -50,3 +50,20 @@ def test_registry():
     m = models.compiled("linear_probe")
     x = np.array([[9.], [10.], [11.]], dtype="float32")
     assert m.evaluate(x, x / 2 + 6, verbose=0) == pytest.approx(25.0025, rel=1e-5)
+
+
+def test_more_applications_have_the_parameter_counts_keras_reports():
+    apps = tfc.keras.applications
+    x = np.random.rand(1, 32, 32, 3).astype("float32")
+    for build, params in ((apps.ResNet101, 44707176), (apps.ResNet152, 60419944)):
+        m = build(weights=None, input_shape=(32, 32, 3))
+        assert m.predict(x).shape == (1, 1000) and m.count_params() == params
+    vgg = apps.VGG16(weights=None, include_top=False, pooling="avg", input_shape=(32, 32, 3))
+    assert vgg.predict(x).shape == (1, 512) and vgg.count_params() == 14714688
+    mobile = apps.MobileNet(weights=None, input_shape=(32, 32, 3), classes=10, alpha=0.5)
+    assert mobile.predict(x).shape == (1, 10)
+    full = apps.MobileNet(weights=None, input_shape=(32, 32, 3))
+    full.predict(x)
+    assert 4.2e6 < full.count_params() < 4.3e6
+    with pytest.raises(ValueError, match="no network"):
+        apps.ResNet101(weights="imagenet")
