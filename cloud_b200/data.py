@@ -59,8 +59,45 @@ class Dataset:
     def range(n):
         return Dataset(("slices", np.arange(n)))
 
+    @staticmethod
+    def zip(datasets):
+        """Elements are tuples of the corresponding elements of ``datasets``; ends with the shortest."""
+        parts = tuple(datasets)
+
+        def gen():
+            yield from zip(*parts)
+        return Dataset(("generator", gen))
+
     def _with(self, op):
         return Dataset(self._source, self._ops + [op])
+
+    def concatenate(self, other):
+        first = self
+
+        def gen():
+            yield from first
+            yield from other
+        return Dataset(("generator", gen))
+
+    def enumerate(self, start=0):
+        base = self
+
+        def gen():
+            for i, e in enumerate(base, start):
+                yield (np.int64(i), e)
+        return Dataset(("generator", gen))
+
+    def filter(self, predicate):
+        return self._with(("filter", predicate))
+
+    def reduce(self, initial_state, reduce_func):
+        state = initial_state
+        for e in self:
+            state = reduce_func(state, e)
+        return state
+
+    def apply(self, transformation_func):
+        return transformation_func(self)
 
     # -- transformations ------------------------------------------------------------------------
     def map(self, fn, num_parallel_calls=None, deterministic=True, **_):
@@ -122,7 +159,7 @@ class Dataset:
                 n = min(n, op[1])
             elif op[0] == "skip":
                 n = max(n - op[1], 0)
-            elif op[0] == "unbatch":
+            elif op[0] in ("unbatch", "filter"):
                 return -2
         return n                        # map / cache / shuffle / prefetch keep the count
 
@@ -244,6 +281,12 @@ def _apply(it, op, rng, ds, idx):
                     yield e
             finally:
                 stop.set()
+        return gen()
+    if kind == "filter":
+        def gen():
+            for e in it:
+                if bool(op[1](*e) if isinstance(e, tuple) else op[1](e)):
+                    yield e
         return gen()
     if kind == "cache":
         key = ("_cache", idx)

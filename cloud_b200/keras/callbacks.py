@@ -92,7 +92,8 @@ class ProgbarLogger(Callback):
     def on_epoch_end(self, epoch, logs=None):
         if not self.verbose:
             return
-        steps = self.params.get("steps", "?")
+        # a dataset of unknown size (generator, filter) has been counted by the end of the epoch
+        steps = self.params.get("steps") or (getattr(self.model, "_fit_profile", None) or {}).get("steps") or "?"
         dt = time.time() - self._t0
         body = " - ".join(f"{k}: {v:.4f}" for k, v in (logs or {}).items())
         print(f"{steps}/{steps} - {dt:.0f}s - {body}", flush=True)

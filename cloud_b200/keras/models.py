@@ -197,10 +197,7 @@ class _IterSource:
     def __len__(self):
         if self.steps:
             return self.steps
-        try:
-            return len(self.ds)
-        except TypeError:
-            return None
+        return len(self.ds)            # TypeError when the dataset's size is unknown (generators, filters)
 
     def __iter__(self):
         infinite = False
@@ -895,7 +892,10 @@ class Model(nn.Module):
         if verbose and self._is_chief:
             cbs.append(cb_mod.ProgbarLogger(verbose))
         cbs.append(history)
-        n_steps = len(source) if hasattr(source, "__len__") else None
+        try:
+            n_steps = len(source)
+        except TypeError:                  # unknown until the first epoch has been counted
+            n_steps = None
         params = {"epochs": epochs, "steps": n_steps, "verbose": verbose}
         cbl = cb_mod.CallbackList(cbs, self, params)
         batch_logs = _needs_batch_logs(cbs)

@@ -147,3 +147,26 @@ def test_prefetch_overlaps_producer_and_consumer_and_forwards_errors():
     # two epochs over the same dataset object
     twice = data.Dataset.range(6).shuffle(6, seed=1).batch(2).prefetch(2)
     assert sorted(sum((b.tolist() for b in twice), [])) == sorted(sum((b.tolist() for b in twice), [])) == list(range(6))
+
+
+def test_zip_concatenate_enumerate_filter_reduce():
+    from cloud_b200 import data
+    a, b = data.Dataset.range(5), data.Dataset.from_tensor_slices(np.arange(10, 17))
+    assert [(int(x), int(y)) for x, y in data.Dataset.zip((a, b))] == [(0, 10), (1, 11), (2, 12), (3, 13), (4, 14)]
+    assert [int(v) for v in a.concatenate(b.take(2))] == [0, 1, 2, 3, 4, 10, 11]
+    assert [(int(i), int(v)) for i, v in b.enumerate(start=1).take(2)] == [(1, 10), (2, 11)]
+    evens = a.concatenate(b).filter(lambda v: v % 2 == 0)
+    assert [int(v) for v in evens] == [0, 2, 4, 10, 12, 14, 16] and evens.cardinality() == data.experimental.UNKNOWN_CARDINALITY
+    assert [t.tolist() for t in evens.batch(3)] == [[0, 2, 4], [10, 12, 14], [16]]
+    pairs = data.Dataset.from_tensor_slices((np.arange(6), np.arange(6) * 10)).filter(lambda x, y: y >= 30)
+    assert [(int(x), int(y)) for x, y in pairs] == [(3, 30), (4, 40), (5, 50)]
+    assert int(a.reduce(np.int64(0), lambda s, v: s + v)) == 10
+    assert [int(v) for v in a.apply(lambda ds: ds.skip(3))] == [3, 4]
+    # zipped features and labels feed fit like a dataset of pairs
+    tfc.distribute.experimental_set_strategy(tfc.distribute.OneDeviceStrategy("/cpu:0"))
+    x = data.Dataset.from_tensor_slices(np.random.rand(32, 4).astype("float32"))
+    y = data.Dataset.from_tensor_slices(np.random.randint(0, 2, 32))
+    model = tfc.keras.Sequential([tfc.keras.layers.Dense(2, activation="softmax", input_shape=(4,))])
+    model.compile("adam", "sparse_categorical_crossentropy")
+    hist = model.fit(data.Dataset.zip((x, y)).batch(8), epochs=2, verbose=0)
+    assert len(hist.history["loss"]) == 2
