@@ -193,6 +193,23 @@ class Adam(Optimizer):
                 "epsilon": self.epsilon}
 
 
+class AdamW(Adam):
+    """Adam with decoupled weight decay (``tf.keras.optimizers.AdamW``, ``torch.optim.AdamW``):
+    ``p <- p (1 - lr * weight_decay)`` before the Adam step; the same fused kernel, optimizer code 3."""
+
+    def __init__(self, learning_rate=0.001, weight_decay=0.004, beta_1=0.9, beta_2=0.999, epsilon=1e-7,
+                 **kwargs):
+        super().__init__(learning_rate, beta_1=beta_1, beta_2=beta_2, epsilon=epsilon, **kwargs)
+        self.weight_decay = float(weight_decay)
+
+    def spec(self):
+        return OptimizerSpec("adamw", lr=self.current_lr(), beta1=self.beta_1, beta2=self.beta_2,
+                             eps=self.epsilon, weight_decay=self.weight_decay)
+
+    def get_config(self):
+        return {**super().get_config(), "weight_decay": self.weight_decay}
+
+
 class SGD(Optimizer):
     def __init__(self, learning_rate=0.01, momentum=0.0, nesterov=False, **kwargs):
         super().__init__(learning_rate, **kwargs)
@@ -223,7 +240,7 @@ class RMSprop(Optimizer):
                 "epsilon": self.epsilon}
 
 
-_BY_NAME = {"adam": Adam, "sgd": SGD, "rmsprop": RMSprop}
+_BY_NAME = {"adam": Adam, "adamw": AdamW, "sgd": SGD, "rmsprop": RMSprop}
 
 
 def get(identifier):

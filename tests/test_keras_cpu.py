@@ -98,6 +98,8 @@ def test_callbacks_early_stopping_checkpoint_and_lr_schedule(tmp_path):
     ("sgd_momentum", lambda: keras.optimizers.SGD(0.05, momentum=0.9),
      lambda p: torch.optim.SGD(p, 0.05, momentum=0.9)),
     ("rmsprop", lambda: keras.optimizers.RMSprop(1e-2), None),
+    ("adamw", lambda: keras.optimizers.AdamW(1e-2, weight_decay=0.1),
+     lambda p: torch.optim.AdamW(p, 1e-2, eps=1e-7, weight_decay=0.1)),
 ])
 def test_optimizers_follow_their_reference_update_rule(name, make, ref):
     x, y = _blobs(128, d=6, classes=2)
