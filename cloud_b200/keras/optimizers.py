@@ -8,6 +8,8 @@ tuner/tests/integration/tuner_integration_test.py:75, ``SGD(0.002)`` cloud_fit c
 """
 from __future__ import annotations
 
+import math
+
 from ..parallel.engine import OptimizerSpec
 
 
@@ -48,10 +50,77 @@ class PiecewiseConstantDecay(LearningRateSchedule):
         return self.values[-1]
 
 
+    def get_config(self):
+        return {"boundaries": self.boundaries, "values": self.values}
+
+
+class CosineDecay(LearningRateSchedule):
+    """``initial * ((1 - alpha) * 0.5 * (1 + cos(pi * min(step, decay_steps) / decay_steps)) + alpha)``,
+    optionally after a linear warm-up from ``initial`` to ``warmup_target`` over ``warmup_steps``."""
+
+    def __init__(self, initial_learning_rate, decay_steps, alpha=0.0, name=None, warmup_target=None,
+                 warmup_steps=0):
+        self.initial_learning_rate = float(initial_learning_rate)
+        self.decay_steps, self.alpha = int(decay_steps), float(alpha)
+        self.warmup_target, self.warmup_steps = warmup_target, int(warmup_steps)
+
+    def __call__(self, step):
+        peak = self.initial_learning_rate
+        if self.warmup_target is not None and self.warmup_steps > 0:
+            if step < self.warmup_steps:
+                return peak + (self.warmup_target - peak) * step / self.warmup_steps
+            peak, step = float(self.warmup_target), step - self.warmup_steps
+        frac = min(step, self.decay_steps) / float(self.decay_steps)
+        return peak * ((1.0 - self.alpha) * 0.5 * (1.0 + math.cos(math.pi * frac)) + self.alpha)
+
+    def get_config(self):
+        return {"initial_learning_rate": self.initial_learning_rate, "decay_steps": self.decay_steps,
+                "alpha": self.alpha, "warmup_target": self.warmup_target, "warmup_steps": self.warmup_steps}
+
+
+class PolynomialDecay(LearningRateSchedule):
+    def __init__(self, initial_learning_rate, decay_steps, end_learning_rate=0.0001, power=1.0, cycle=False,
+                 name=None):
+        self.initial_learning_rate, self.end_learning_rate = float(initial_learning_rate), float(end_learning_rate)
+        self.decay_steps, self.power, self.cycle = int(decay_steps), float(power), cycle
+
+    def __call__(self, step):
+        steps = self.decay_steps
+        if self.cycle:
+            steps = steps * max(1.0, math.ceil(step / steps))
+        else:
+            step = min(step, steps)
+        return (self.initial_learning_rate - self.end_learning_rate) * (1 - step / steps) ** self.power \
+            + self.end_learning_rate
+
+    def get_config(self):
+        return {"initial_learning_rate": self.initial_learning_rate, "decay_steps": self.decay_steps,
+                "end_learning_rate": self.end_learning_rate, "power": self.power, "cycle": self.cycle}
+
+
+class InverseTimeDecay(LearningRateSchedule):
+    def __init__(self, initial_learning_rate, decay_steps, decay_rate, staircase=False, name=None):
+        self.initial_learning_rate = float(initial_learning_rate)
+        self.decay_steps, self.decay_rate, self.staircase = decay_steps, decay_rate, staircase
+
+    def __call__(self, step):
+        p = step / self.decay_steps
+        if self.staircase:
+            p = float(int(p))
+        return self.initial_learning_rate / (1.0 + self.decay_rate * p)
+
+    def get_config(self):
+        return {"initial_learning_rate": self.initial_learning_rate, "decay_steps": self.decay_steps,
+                "decay_rate": self.decay_rate, "staircase": self.staircase}
+
+
 class schedules:  # tf.keras.optimizers.schedules.*
     LearningRateSchedule = LearningRateSchedule
     ExponentialDecay = ExponentialDecay
     PiecewiseConstantDecay = PiecewiseConstantDecay
+    CosineDecay = CosineDecay
+    PolynomialDecay = PolynomialDecay
+    InverseTimeDecay = InverseTimeDecay
 
 
 class _HyperParameter(float):

@@ -531,3 +531,24 @@ def test_sample_and_class_weights_scale_each_sample_loss():
     m.fit(x, y, sample_weight=np.ones(64), epochs=1, verbose=0)
     assert m._weighted_targets is None and np.isfinite(m.evaluate(x, y, verbose=0)[0])
     m.fit(x, y, epochs=1, verbose=0)
+
+
+def test_more_learning_rate_schedules():
+    sch = keras.optimizers.schedules
+    cos = sch.CosineDecay(0.1, decay_steps=100, alpha=0.1)
+    assert cos(0) == pytest.approx(0.1) and cos(50) == pytest.approx(0.1 * (0.9 * 0.5 + 0.1)) and cos(100) == cos(500) == pytest.approx(0.01)
+    warm = sch.CosineDecay(0.0, decay_steps=10, warmup_target=1.0, warmup_steps=4)
+    assert [round(warm(s), 3) for s in (0, 2, 4, 9, 14)] == [0.0, 0.5, 1.0, 0.5, 0.0]
+    poly = sch.PolynomialDecay(1.0, decay_steps=10, end_learning_rate=0.1, power=2.0)
+    assert poly(0) == 1.0 and poly(5) == pytest.approx(0.9 * 0.25 + 0.1) and poly(50) == pytest.approx(0.1)
+    assert sch.PolynomialDecay(1.0, 10, 0.0, cycle=True)(15) == pytest.approx(0.25)
+    inv = sch.InverseTimeDecay(1.0, decay_steps=10, decay_rate=0.5, staircase=True)
+    assert inv(9) == 1.0 and inv(25) == pytest.approx(1 / 2.0)
+    # a schedule drives the optimizer during fit and survives serialisation
+    x, y = _blobs(64)
+    m = _mlp()
+    m.compile(keras.optimizers.SGD(sch.CosineDecay(0.5, decay_steps=8)), "sparse_categorical_crossentropy")
+    m.fit(x, y, batch_size=16, epochs=2, verbose=0)
+    assert m.optimizer.current_lr() == pytest.approx(0.0, abs=1e-9) and m.optimizer.iterations == 8
+    again = keras.optimizers.deserialize(keras.optimizers.serialize(m.optimizer))
+    assert isinstance(again._schedule, sch.CosineDecay) and again._schedule.decay_steps == 8
