@@ -10,6 +10,7 @@ import torch
 class Metric:
     name = "metric"
     from_fused_xent = False    # True: the fused cross-entropy kernel already counts it
+    ratio = False              # True: result = sum of numerators / sum of denominators (``batch_sums``)
 
     def __init__(self, name=None):
         if name:
@@ -80,6 +81,79 @@ class MeanSquaredError(Metric):
         return d.reshape(d.shape[0], -1).mean(-1).sum()
 
 
+class SparseTopKCategoricalAccuracy(Metric):
+    name = "sparse_top_k_categorical_accuracy"
+
+    def __init__(self, k=5, name=None):
+        self.k = int(k)
+        super().__init__(name)
+
+    def batch_sum(self, y_true, y_pred):
+        top = y_pred.topk(min(self.k, y_pred.shape[-1]), dim=-1).indices
+        return (top == y_true.reshape(-1, 1).to(top.device)).any(-1).sum().float()
+
+
+class TopKCategoricalAccuracy(SparseTopKCategoricalAccuracy):
+    name = "top_k_categorical_accuracy"
+
+    def batch_sum(self, y_true, y_pred):
+        return super().batch_sum(y_true.argmax(-1), y_pred)
+
+
+class _RatioMetric(Metric):
+    """Numerator and denominator are both sums over samples (and over replicas): precision = true
+    positives / predicted positives, recall = true positives / actual positives."""
+    ratio = True
+
+    def __init__(self, thresholds=0.5, class_id=None, name=None):
+        self.threshold = 0.5 if thresholds is None else float(thresholds)
+        self.class_id = class_id
+        super().__init__(name)
+
+    def _binary(self, y_true, y_pred):
+        """(predicted positive, actually positive) as float masks of equal shape."""
+        y_pred = y_pred.float()
+        if y_pred.dim() > 1 and y_pred.shape[-1] > 1:            # multi-class scores
+            if y_true.dim() == y_pred.dim() and y_true.shape[-1] == y_pred.shape[-1]:
+                actual = y_true.float()                          # one-hot / multi-label targets
+            else:
+                actual = torch.nn.functional.one_hot(y_true.reshape(-1).long(), y_pred.shape[-1]).float()
+            pred = (y_pred > self.threshold).float()
+            if self.class_id is not None:
+                pred, actual = pred[..., self.class_id], actual[..., self.class_id]
+            return pred, actual.to(pred.device)
+        return (y_pred.reshape(-1) > self.threshold).float(), y_true.float().reshape(-1).to(y_pred.device)
+
+    def reset_states(self):
+        self._sum, self._count = 0.0, 0.0
+
+    reset_state = reset_states
+
+    def update_state(self, y_true, y_pred, sample_weight=None):
+        num, den = self.batch_sums(torch.as_tensor(y_true), torch.as_tensor(y_pred).detach())
+        self._sum += float(num)
+        self._count += float(den)
+
+    def batch_sum(self, y_true, y_pred):
+        return self.batch_sums(y_true, y_pred)[0]
+
+
+class Precision(_RatioMetric):
+    name = "precision"
+
+    def batch_sums(self, y_true, y_pred):
+        pred, actual = self._binary(y_true, y_pred)
+        return (pred * actual).sum(), pred.sum()
+
+
+class Recall(_RatioMetric):
+    name = "recall"
+
+    def batch_sums(self, y_true, y_pred):
+        pred, actual = self._binary(y_true, y_pred)
+        return (pred * actual).sum(), actual.sum()
+
+
 class Mean(Metric):
     """Running mean of whatever is fed (``tf.keras.metrics.Mean``)."""
     name = "mean"
@@ -112,7 +186,10 @@ def get(identifier, loss=None, output_dim=None):
     table = {"sparse_categorical_accuracy": SparseCategoricalAccuracy,
              "categorical_accuracy": CategoricalAccuracy, "binary_accuracy": BinaryAccuracy,
              "mae": MeanAbsoluteError, "mean_absolute_error": MeanAbsoluteError,
-             "mse": MeanSquaredError, "mean_squared_error": MeanSquaredError}
+             "mse": MeanSquaredError, "mean_squared_error": MeanSquaredError,
+             "sparse_top_k_categorical_accuracy": SparseTopKCategoricalAccuracy,
+             "top_k_categorical_accuracy": TopKCategoricalAccuracy,
+             "precision": Precision, "recall": Recall}
     if key in table:
         return table[key]()
     raise ValueError(f"Unknown metric function: {identifier}")

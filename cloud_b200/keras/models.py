@@ -323,6 +323,7 @@ class Model(nn.Module):
         self.optimizer = None
         self.loss = None
         self._metrics: list = []
+        self._ratio_slots: dict = {}
         self._engine = None
         self._strategy = None
         self._graph = None
@@ -563,6 +564,8 @@ class Model(nn.Module):
         self.optimizer = opt_mod.get(optimizer)
         self.loss = losses_mod.get(loss) if loss is not None else None
         self._metrics = [metrics_mod.get(m, self.loss) for m in (metrics or [])]
+        ratio = [i for i, m in enumerate(self._metrics) if m.ratio]
+        self._ratio_slots = {i: AUX_METRIC0 + len(self._metrics) + k for k, i in enumerate(ratio)}
         self.run_eagerly = bool(run_eagerly)
         self._compiled_with = {"loss": loss, "metrics": list(metrics or [])}
         self._strategy = get_strategy()
@@ -649,7 +652,12 @@ class Model(nn.Module):
             for i, m in enumerate(self._metrics):
                 if fused and m.from_fused_xent:
                     continue
-                aux[AUX_METRIC0 + i] += m.batch_sum(y, out)
+                if m.ratio:                 # numerator in the metric's slot, denominator behind them all
+                    num, den = m.batch_sums(y, out)
+                    aux[AUX_METRIC0 + i] += num
+                    aux[self._ratio_slots[i]] += den
+                else:
+                    aux[AUX_METRIC0 + i] += m.batch_sum(y, out)
         return loss, fused
 
     @property
@@ -693,14 +701,18 @@ class Model(nn.Module):
         return total
 
     def _aux_len(self):
-        return AUX_METRIC0 + len(self._metrics)
+        return AUX_METRIC0 + len(self._metrics) + len(self._ratio_slots)
 
     def _logs_from_aux(self, acc, fused, prefix=""):
         cnt = max(float(acc[AUX_COUNT]), 1.0)
         logs = {prefix + "loss": float(acc[AUX_LOSS]) / cnt}
         for i, m in enumerate(self._metrics):
             v = acc[AUX_CORRECT] if (fused and m.from_fused_xent) else acc[AUX_METRIC0 + i]
-            logs[prefix + m.name] = float(v) / cnt
+            if m.ratio:
+                den = float(acc[self._ratio_slots[i]])
+                logs[prefix + m.name] = float(v) / den if den > 0 else 0.0
+            else:
+                logs[prefix + m.name] = float(v) / cnt
         return logs
 
     # -- one training step --------------------------------------------------------------------

@@ -552,3 +552,36 @@ def test_more_learning_rate_schedules():
     assert m.optimizer.current_lr() == pytest.approx(0.0, abs=1e-9) and m.optimizer.iterations == 8
     again = keras.optimizers.deserialize(keras.optimizers.serialize(m.optimizer))
     assert isinstance(again._schedule, sch.CosineDecay) and again._schedule.decay_steps == 8
+
+
+def test_precision_recall_and_top_k_metrics():
+    m = keras.metrics
+    y_true = np.array([1, 0, 1, 1, 0, 0])
+    scores = np.array([0.9, 0.8, 0.4, 0.7, 0.2, 0.1], dtype="float32")       # predicted positive: 0, 1, 3
+    p, r = m.Precision(), m.Recall()
+    p.update_state(y_true, scores), r.update_state(y_true, scores)
+    assert p.result() == pytest.approx(2 / 3) and r.result() == pytest.approx(2 / 3)
+    p.update_state(np.array([1, 1]), np.array([0.9, 0.1], dtype="float32"))
+    assert p.result() == pytest.approx(3 / 4)                                 # sums, not a mean of ratios
+    probs = np.array([[0.1, 0.7, 0.2], [0.6, 0.3, 0.1], [0.1, 0.3, 0.6]], dtype="float32")
+    labels = np.array([1, 1, 0])
+    per_class = m.Precision(class_id=1)
+    per_class.update_state(labels, probs)
+    assert per_class.result() == 1.0                                          # only sample 0 crosses 0.5 for class 1
+    top2 = m.SparseTopKCategoricalAccuracy(k=2)
+    top2.update_state(labels, probs)
+    assert top2.result() == pytest.approx(2 / 3)
+    assert m.TopKCategoricalAccuracy(k=1)(np.eye(3)[labels], probs) == pytest.approx(1 / 3)
+    # inside fit / evaluate: two metrics with denominators of their own next to plain ones
+    x, y = _blobs(128, classes=2)
+    model = keras.Sequential([L.Dense(8, activation="relu", input_shape=(20,)), L.Dense(1, activation="sigmoid")])
+    model.compile(keras.optimizers.Adam(1e-2), "binary_crossentropy",
+                  metrics=["accuracy", m.Precision(), "recall", "mae"])
+    hist = model.fit(x, y.astype("float32"), batch_size=32, epochs=6, verbose=0)
+    assert set(hist.history) == {"loss", "accuracy", "precision", "recall", "mae"}
+    logs = model.evaluate(x, y.astype("float32"), verbose=0, return_dict=True)
+    pred = model.predict(x).reshape(-1) > 0.5
+    tp = float((pred & (y == 1)).sum())
+    assert logs["precision"] == pytest.approx(tp / max(pred.sum(), 1), abs=1e-6)
+    assert logs["recall"] == pytest.approx(tp / (y == 1).sum(), abs=1e-6)
+    assert logs["accuracy"] == pytest.approx(float((pred == (y == 1)).mean()), abs=1e-6)
