@@ -24,8 +24,10 @@ def build(seed):
     m = keras.Sequential([layers.Dense(64, activation="relu", input_shape=(32,)),
                           layers.Dense(16, activation="relu"),
                           layers.Dense(4, activation="softmax")])
+    # CHECK_RATIO_METRIC: a metric whose denominator is a sum of its own (recall) next to accuracy
+    metrics = ["accuracy", "recall"] if os.environ.get("CHECK_RATIO_METRIC") == "1" else ["accuracy"]
     m.compile(optimizer=keras.optimizers.Adam(1e-2), loss="sparse_categorical_crossentropy",
-              metrics=["accuracy"], run_eagerly=bool(int(os.environ.get("CHECK_EAGER", "1"))))
+              metrics=metrics, run_eagerly=bool(int(os.environ.get("CHECK_EAGER", "1"))))
     return m
 
 
@@ -57,6 +59,9 @@ def main():
     assert worst < tol, f"rank {rank}: weights differ from the single-replica run by {worst}"
     assert abs(h.history["loss"][-1] - h_ref.history["loss"][-1]) < (5e-2 if use_gpu else 1e-5), \
         (h.history, h_ref.history)
+    if "recall" in h.history:       # numerators and denominators were summed over the replicas
+        assert abs(h.history["recall"][-1] - h_ref.history["recall"][-1]) < (5e-2 if use_gpu else 1e-6), \
+            (h.history["recall"], h_ref.history["recall"])
     # replicas agree exactly
     t = torch.tensor(np.concatenate([w.reshape(-1) for w in w_dist]))
     lst = [torch.zeros_like(t) for _ in range(world)]

@@ -23,7 +23,8 @@ def _torchrun(script, nproc, env_extra, port, timeout=240):
 
 @pytest.mark.parametrize("nproc,backend", [(2, "shm"), (3, "shm"), (2, "dist"), (3, "dist")])
 def test_mirrored_equals_single_replica_cpu(tmp_path, nproc, backend):
-    env = {"CHECK_DEVICE": "cpu", "CUDA_VISIBLE_DEVICES": "", "CHECK_OUT": str(tmp_path)}
+    env = {"CHECK_DEVICE": "cpu", "CUDA_VISIBLE_DEVICES": "", "CHECK_OUT": str(tmp_path),
+           "CHECK_RATIO_METRIC": "1"}
     if backend != "shm":                       # shm is what CPU ranks pick by themselves
         env["TFC_COMM_BACKEND"] = backend
     res = _torchrun(os.path.join(ROOT, "tests", "dist_train_check.py"), nproc, env,
