@@ -159,3 +159,39 @@ def test_trial_scheduler_shares_the_box_with_a_running_job(tmp_path):
         holder.wait()
     records = TrialScheduler(gpus_per_trial=1).run(_report_gpu, num_workers=4, log_dir=str(tmp_path / "logs2"))
     assert {tuple(r["gpus"]) for r in records} == {(0,), (1,)}          # the whole box again
+
+
+def _lease_worker(args):
+    root, worker, rounds = args
+    import os
+    import time
+    os.environ["TFC_JOB_ROOT"] = root
+    from cloud_b200.launch import leases as ls
+    events = []
+    for i in range(rounds):
+        owner = "w{}_{}".format(worker, i)
+        got = ls.acquire(owner, 1 + (worker % 2), 3, timeout=60, poll=0.01)
+        t0 = time.time()
+        time.sleep(0.03)
+        t1 = time.time()
+        ls.release(owner)
+        events.append((got, t0, t1))
+    return events
+
+
+def test_lease_table_survives_concurrent_processes(tmp_path):
+    """Six processes fight over three GPUs (some want two at once): no GPU is ever held twice at the
+    same time and everybody gets served (the table is one JSON file under flock)."""
+    import multiprocessing as mp
+    root = str(tmp_path / "jobs")
+    ctx = mp.get_context("spawn")
+    with ctx.Pool(6) as pool:
+        results = pool.map(_lease_worker, [(root, w, 4) for w in range(6)])
+    holds = [(g, t0, t1) for events in results for got, t0, t1 in events for g in got]
+    assert len(holds) == 4 * (3 * 1 + 3 * 2)
+    for gpu in range(3):
+        mine = sorted((t0, t1) for g, t0, t1 in holds if g == gpu)
+        assert mine, "GPU {} was never handed out".format(gpu)
+        for (a0, a1), (b0, _b1) in zip(mine, mine[1:]):
+            assert a1 <= b0 + 1e-3, "GPU {} was held twice at once".format(gpu)
+    assert leases.snapshot(3)["free"] == [0, 1, 2] and leases.snapshot(3)["queue"] == []
