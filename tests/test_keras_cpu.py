@@ -213,7 +213,7 @@ def test_steps_per_execution_groups_steps_without_changing_the_training():
 
 @pytest.mark.parametrize("shuffle", [False, True])
 def test_array_source_groups_partition_each_global_batch_across_replicas(shuffle):
-    from cloud_b200.keras.models import _ArraySource
+    from cloud_b200.keras.batch_sources import _ArraySource
     n, B, K, world = 100, 8, 3, 2
     x = torch.arange(n).float().view(n, 1)
     y = torch.arange(n)
