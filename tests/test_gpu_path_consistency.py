@@ -96,3 +96,30 @@ def test_runtime_entry_points_python_calls_are_exported():
         called |= set(re.findall(r"\.(cb2(?:rt|h5|mon)_[a-z0-9_]*[a-z0-9])\b", open(path).read()))
     assert len(called) > 20
     assert not (called - exported), sorted(called - exported)
+
+
+def test_every_module_of_the_package_imports():
+    """Import errors in modules that only a GPU run touches (ops/*, parallel/symm.py, bench helpers)
+    show up here."""
+    import importlib
+    import pkgutil
+    import cloud_b200
+    failed = {}
+    for info in pkgutil.walk_packages(cloud_b200.__path__, "cloud_b200."):
+        if info.name.endswith("__main__"):
+            continue
+        try:
+            importlib.import_module(info.name)
+        except Exception as e:  # noqa: BLE001
+            failed[info.name] = repr(e)
+    assert not failed, failed
+
+
+def test_bench_and_tool_scripts_compile():
+    import py_compile
+    for folder in ("bench", "tools", "examples"):
+        for name in sorted(os.listdir(os.path.join(ROOT, folder))):
+            if name.endswith(".py"):
+                py_compile.compile(os.path.join(ROOT, folder, name), doraise=True)
+    py_compile.compile(os.path.join(ROOT, "bench.py"), doraise=True)
+    py_compile.compile(os.path.join(ROOT, "__graft_entry__.py"), doraise=True)
