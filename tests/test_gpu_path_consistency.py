@@ -123,3 +123,36 @@ def test_bench_and_tool_scripts_compile():
                 py_compile.compile(os.path.join(ROOT, folder, name), doraise=True)
     py_compile.compile(os.path.join(ROOT, "bench.py"), doraise=True)
     py_compile.compile(os.path.join(ROOT, "__graft_entry__.py"), doraise=True)
+
+
+def test_no_name_is_used_that_is_defined_nowhere_in_its_module():
+    """A coarse undefined-name check (every name loaded in a module is imported, assigned, or a
+    parameter somewhere in that module): typos in branches only a GPU run reaches fail here."""
+    import builtins
+    known = set(dir(builtins)) | {"__file__", "__name__", "__doc__", "__path__"}
+    files = list(_python_sources()) + [os.path.join(ROOT, "bench.py"), os.path.join(ROOT, "__graft_entry__.py")]
+    files += [os.path.join(ROOT, "bench", f) for f in os.listdir(os.path.join(ROOT, "bench")) if f.endswith(".py")]
+    problems = {}
+    for path in files:
+        tree = ast.parse(open(path).read())
+        defined = set(known)
+        for n in ast.walk(tree):
+            if isinstance(n, (ast.FunctionDef, ast.ClassDef, ast.AsyncFunctionDef)):
+                defined.add(n.name)
+            elif isinstance(n, ast.Import):
+                defined.update((a.asname or a.name).split(".")[0] for a in n.names)
+            elif isinstance(n, ast.ImportFrom):
+                defined.update(a.asname or a.name for a in n.names)
+            elif isinstance(n, ast.Name) and isinstance(n.ctx, (ast.Store, ast.Del)):
+                defined.add(n.id)
+            elif isinstance(n, ast.arg):
+                defined.add(n.arg)
+            elif isinstance(n, ast.ExceptHandler) and n.name:
+                defined.add(n.name)
+            elif isinstance(n, (ast.Global, ast.Nonlocal)):
+                defined.update(n.names)
+        bad = sorted({(n.id, n.lineno) for n in ast.walk(tree)
+                      if isinstance(n, ast.Name) and isinstance(n.ctx, ast.Load) and n.id not in defined})
+        if bad:
+            problems[os.path.relpath(path, ROOT)] = bad
+    assert not problems, problems
