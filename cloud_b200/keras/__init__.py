@@ -23,6 +23,8 @@ class backend:
 
 
 class utils:
+    from .batch_sources import Sequence  # noqa: F401
+
     @staticmethod
     def to_categorical(y, num_classes=None, dtype="float32"):
         import numpy as np

@@ -283,3 +283,38 @@ class _Prefetcher:
 
 
 # ----------------------------------------------------------------------------------------------
+
+
+class Sequence:
+    """``tf.keras.utils.Sequence``: ``__len__`` batches per epoch, ``__getitem__(i)`` returns batch i
+    as ``(x, y)``, ``on_epoch_end`` runs after every pass (reshuffle there)."""
+
+    def __len__(self):
+        raise NotImplementedError
+
+    def __getitem__(self, index):
+        raise NotImplementedError
+
+    def on_epoch_end(self):
+        pass
+
+    def __iter__(self):
+        return iter(_SequenceAdapter(self))
+
+
+class _SequenceAdapter:
+    """Makes anything with ``__len__`` and ``__getitem__`` (a Sequence, also one that does not derive
+    from the class above) an iterable of global batches for ``_IterSource``."""
+
+    def __init__(self, seq):
+        self.seq = seq
+
+    def __len__(self):
+        return len(self.seq)
+
+    def __iter__(self):
+        for i in range(len(self.seq)):
+            yield self.seq[i]
+        hook = getattr(self.seq, "on_epoch_end", None)
+        if callable(hook):
+            hook()

@@ -38,7 +38,7 @@ AUX_LOSS, AUX_CORRECT, AUX_COUNT, AUX_METRIC0 = 0, 1, 2, 3
 
 
 from .batch_sources import (_ArraySource, _grouped, _heartbeat, _IterSource, _NG, _np,  # noqa: F401
-                            _Prefetcher)
+                            _Prefetcher, _SequenceAdapter)
 
 
 class _Forked(list):
@@ -566,6 +566,9 @@ class Model(nn.Module):
     def _make_source(self, x, y, batch_size, shuffle, steps, training=True):
         st = self.distribute_strategy
         world, rank = st.num_replicas_in_sync, st.replica_id
+        if y is None and hasattr(x, "__getitem__") and hasattr(x, "__len__") and not isinstance(
+                x, (np.ndarray, torch.Tensor, list, tuple, dict, Dataset, DistributedDataset)):
+            x = _SequenceAdapter(x)                      # a keras.utils.Sequence (or look-alike)
         if isinstance(x, (Dataset, DistributedDataset)) or (
                 not isinstance(x, (np.ndarray, torch.Tensor, list, tuple)) and hasattr(x, "__iter__")):
             if callable(getattr(x, "__next__", None)) and not hasattr(x, "__len__") \

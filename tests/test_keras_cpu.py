@@ -585,3 +585,35 @@ def test_precision_recall_and_top_k_metrics():
     assert logs["precision"] == pytest.approx(tp / max(pred.sum(), 1), abs=1e-6)
     assert logs["recall"] == pytest.approx(tp / (y == 1).sum(), abs=1e-6)
     assert logs["accuracy"] == pytest.approx(float((pred == (y == 1)).mean()), abs=1e-6)
+
+
+def test_keras_sequence_feeds_fit_evaluate_and_predict_sources():
+    class Batches(keras.utils.Sequence):
+        def __init__(self):
+            self.x, self.y = _blobs(96)
+            self.epochs_seen = 0
+
+        def __len__(self):
+            return 6
+
+        def __getitem__(self, i):
+            return self.x[i * 16:(i + 1) * 16], self.y[i * 16:(i + 1) * 16]
+
+        def on_epoch_end(self):
+            self.epochs_seen += 1
+
+    seq = Batches()
+    m = _mlp()
+    hist = m.fit(seq, epochs=3, verbose=0)
+    assert len(hist.history["loss"]) == 3 and seq.epochs_seen == 3
+    assert hist.history["accuracy"][-1] > 0.8
+    loss, acc = m.evaluate(seq, verbose=0)
+    assert acc > 0.8 and np.isfinite(loss)
+
+    class Duck:                                    # not derived from Sequence, same protocol
+        def __len__(self):
+            return 2
+
+        def __getitem__(self, i):
+            return seq[i]
+    assert len(m.fit(Duck(), epochs=1, verbose=0).history["loss"]) == 1
