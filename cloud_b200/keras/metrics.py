@@ -10,7 +10,7 @@ import torch
 class Metric:
     name = "metric"
     from_fused_xent = False    # True: the fused cross-entropy kernel already counts it
-    ratio = False              # True: result = sum of numerators / sum of denominators (``batch_sums``)
+    extra_slots = 0            # > 0: the metric is built from 1 + extra_slots sums (``batch_vector`` / ``reduce_vector``)
 
     def __init__(self, name=None):
         if name:
@@ -103,7 +103,7 @@ class TopKCategoricalAccuracy(SparseTopKCategoricalAccuracy):
 class _RatioMetric(Metric):
     """Numerator and denominator are both sums over samples (and over replicas): precision = true
     positives / predicted positives, recall = true positives / actual positives."""
-    ratio = True
+    extra_slots = 1
 
     def __init__(self, thresholds=0.5, class_id=None, name=None):
         self.threshold = 0.5 if thresholds is None else float(thresholds)
@@ -136,6 +136,62 @@ class _RatioMetric(Metric):
 
     def batch_sum(self, y_true, y_pred):
         return self.batch_sums(y_true, y_pred)[0]
+
+    def batch_vector(self, y_true, y_pred):
+        return torch.stack(self.batch_sums(y_true, y_pred))
+
+    @staticmethod
+    def reduce_vector(sums):
+        return sums[0] / sums[1] if sums[1] > 0 else 0.0
+
+
+class AUC(Metric):
+    """Area under the ROC curve (``tf.keras.metrics.AUC``, ``curve="ROC"``, trapezoidal summation) for
+    scores in [0, 1] and binary labels.  True and false positives are counted at ``num_thresholds``
+    thresholds - sums over samples and replicas like every other metric - and the curve is integrated
+    when the result is read.  At most 100 thresholds (the step's scalar vector has 256 entries)."""
+    name = "auc"
+
+    def __init__(self, num_thresholds=100, name=None, **kwargs):
+        self.num_thresholds = max(3, min(int(num_thresholds), 100))
+        self.extra_slots = 2 * self.num_thresholds + 1           # tp[T], fp[T], positives, negatives - 1
+        eps = 1e-7
+        inner = [(i + 1) / (self.num_thresholds - 1) for i in range(self.num_thresholds - 2)]
+        self._thresholds = torch.tensor([0.0 - eps] + inner + [1.0 + eps])
+        super().__init__(name)
+
+    def batch_vector(self, y_true, y_pred):
+        scores = y_pred.float().reshape(-1)
+        actual = y_true.float().reshape(-1).to(scores.device)
+        th = self._thresholds.to(scores.device)
+        above = (scores[None, :] > th[:, None]).float()          # [T, batch]
+        tp = above @ actual
+        fp = above @ (1.0 - actual)
+        return torch.cat([tp, fp, actual.sum()[None], (1.0 - actual).sum()[None]])
+
+    def reduce_vector(self, sums):
+        t = self.num_thresholds
+        tp, fp, pos, neg = sums[:t], sums[t:2 * t], sums[2 * t], sums[2 * t + 1]
+        if pos <= 0 or neg <= 0:
+            return 0.0
+        tpr = [v / pos for v in tp]
+        fpr = [v / neg for v in fp]
+        return float(sum((fpr[i] - fpr[i + 1]) * (tpr[i] + tpr[i + 1]) / 2.0 for i in range(t - 1)))
+
+    def reset_states(self):
+        self._vec = None
+
+    reset_state = reset_states
+
+    def update_state(self, y_true, y_pred, sample_weight=None):
+        vec = self.batch_vector(torch.as_tensor(y_true), torch.as_tensor(y_pred).detach()).double()
+        self._vec = vec if self._vec is None else self._vec + vec
+
+    def batch_sum(self, y_true, y_pred):
+        return self.batch_vector(y_true, y_pred)[0]
+
+    def result(self):
+        return 0.0 if self._vec is None else self.reduce_vector([float(v) for v in self._vec])
 
 
 class Precision(_RatioMetric):
@@ -189,7 +245,7 @@ def get(identifier, loss=None, output_dim=None):
              "mse": MeanSquaredError, "mean_squared_error": MeanSquaredError,
              "sparse_top_k_categorical_accuracy": SparseTopKCategoricalAccuracy,
              "top_k_categorical_accuracy": TopKCategoricalAccuracy,
-             "precision": Precision, "recall": Recall}
+             "precision": Precision, "recall": Recall, "auc": AUC}
     if key in table:
         return table[key]()
     raise ValueError(f"Unknown metric function: {identifier}")

@@ -301,8 +301,18 @@ class Model(nn.Module):
         self.optimizer = opt_mod.get(optimizer)
         self.loss = losses_mod.get(loss) if loss is not None else None
         self._metrics = [metrics_mod.get(m, self.loss) for m in (metrics or [])]
-        ratio = [i for i, m in enumerate(self._metrics) if m.ratio]
-        self._ratio_slots = {i: AUX_METRIC0 + len(self._metrics) + k for k, i in enumerate(ratio)}
+        # metrics that need more than one sum (precision: a denominator; AUC: counts per threshold)
+        # keep their first value in their own slot and the rest behind all metrics, so the slots of the
+        # common metrics never move
+        self._ratio_slots, cursor = {}, AUX_METRIC0 + len(self._metrics)
+        for i, m in enumerate(self._metrics):
+            if m.extra_slots:
+                self._ratio_slots[i] = (cursor, m.extra_slots)
+                cursor += m.extra_slots
+        from ..parallel.comm import AUX_FLOATS
+        if cursor > AUX_FLOATS:
+            raise ValueError("The metrics need {} scalars per step; {} fit in the step's scalar vector "
+                             "(fewer AUC thresholds?)".format(cursor, AUX_FLOATS))
         self.run_eagerly = bool(run_eagerly)
         self._compiled_with = {"loss": loss, "metrics": list(metrics or [])}
         self._strategy = get_strategy()
@@ -389,10 +399,11 @@ class Model(nn.Module):
             for i, m in enumerate(self._metrics):
                 if fused and m.from_fused_xent:
                     continue
-                if m.ratio:                 # numerator in the metric's slot, denominator behind them all
-                    num, den = m.batch_sums(y, out)
-                    aux[AUX_METRIC0 + i] += num
-                    aux[self._ratio_slots[i]] += den
+                if m.extra_slots:           # first value in the metric's slot, the others behind them all
+                    vec = m.batch_vector(y, out)
+                    start, n = self._ratio_slots[i]
+                    aux[AUX_METRIC0 + i] += vec[0]
+                    aux[start:start + n] += vec[1:]
                 else:
                     aux[AUX_METRIC0 + i] += m.batch_sum(y, out)
         return loss, fused
@@ -438,16 +449,16 @@ class Model(nn.Module):
         return total
 
     def _aux_len(self):
-        return AUX_METRIC0 + len(self._metrics) + len(self._ratio_slots)
+        return AUX_METRIC0 + len(self._metrics) + sum(n for _s, n in self._ratio_slots.values())
 
     def _logs_from_aux(self, acc, fused, prefix=""):
         cnt = max(float(acc[AUX_COUNT]), 1.0)
         logs = {prefix + "loss": float(acc[AUX_LOSS]) / cnt}
         for i, m in enumerate(self._metrics):
             v = acc[AUX_CORRECT] if (fused and m.from_fused_xent) else acc[AUX_METRIC0 + i]
-            if m.ratio:
-                den = float(acc[self._ratio_slots[i]])
-                logs[prefix + m.name] = float(v) / den if den > 0 else 0.0
+            if m.extra_slots:
+                start, n = self._ratio_slots[i]
+                logs[prefix + m.name] = m.reduce_vector([float(v)] + [float(t) for t in acc[start:start + n]])
             else:
                 logs[prefix + m.name] = float(v) / cnt
         return logs

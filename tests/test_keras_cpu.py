@@ -617,3 +617,31 @@ def test_keras_sequence_feeds_fit_evaluate_and_predict_sources():
         def __getitem__(self, i):
             return seq[i]
     assert len(m.fit(Duck(), epochs=1, verbose=0).history["loss"]) == 1
+
+
+def test_auc_metric_matches_a_rank_based_reference():
+    rng = np.random.RandomState(0)
+    y = rng.randint(0, 2, 400)
+    scores = np.clip(0.35 * y + rng.rand(400) * 0.65, 0, 1).astype("float32")
+    auc = keras.metrics.AUC(num_thresholds=100)
+    for i in range(0, 400, 100):                       # accumulated over batches
+        auc.update_state(y[i:i + 100], scores[i:i + 100])
+    pos, neg = scores[y == 1], scores[y == 0]
+    exact = float(((pos[:, None] > neg[None, :]).sum() + 0.5 * (pos[:, None] == neg[None, :]).sum()) / (len(pos) * len(neg)))
+    assert auc.result() == pytest.approx(exact, abs=5e-3)
+    perfect = keras.metrics.AUC()
+    perfect.update_state([0, 0, 1, 1], [0.1, 0.2, 0.8, 0.9])
+    assert perfect.result() == pytest.approx(1.0) and keras.metrics.AUC().result() == 0.0
+    # through fit / evaluate next to other metrics
+    x, yb = _blobs(128, classes=2)
+    model = keras.Sequential([L.Dense(8, activation="relu", input_shape=(20,)), L.Dense(1, activation="sigmoid")])
+    model.compile(keras.optimizers.Adam(1e-2), "binary_crossentropy", metrics=["accuracy", "auc", "precision"])
+    hist = model.fit(x, yb.astype("float32"), batch_size=32, epochs=5, verbose=0)
+    assert hist.history["auc"][-1] > 0.9
+    logs = model.evaluate(x, yb.astype("float32"), verbose=0, return_dict=True)
+    p = model.predict(x).reshape(-1)
+    pos, neg = p[yb == 1], p[yb == 0]
+    exact = float((pos[:, None] > neg[None, :]).mean())
+    assert logs["auc"] == pytest.approx(exact, abs=1e-2) and 0 <= logs["precision"] <= 1
+    with pytest.raises(ValueError, match="scalars per step"):
+        model.compile("adam", "binary_crossentropy", metrics=[keras.metrics.AUC(name="a"), keras.metrics.AUC(name="b")])
