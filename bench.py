@@ -7,31 +7,42 @@
 
 Metric and config are BASELINE.json's: "ResNet-50 bf16 MirroredStrategy 224x224 synthetic images"
 (model of core/tests/examples/call_run_within_script_with_keras_fit.py:79-109, all 25.6 M
-parameters trained, Adam, per-replica batch 64 as in that example -> weak scaling).  The step is
-the full training step: forward, fused cross-entropy, backward, fused all-reduce + Adam.
+parameters trained, Adam; per-replica batch 256 by default - weak scaling - and the reference
+example's batch of 64 as the extra ``small_batch`` row).  The step is the full training step:
+forward, fused cross-entropy, backward, fused all-reduce + Adam.
 
-Two numbers are measured, both through the public Keras-shaped API of cloud_b200:
-  * value : device-timed (CUDA events, barrier + synchronize on both sides, max over ranks) over K
-            steps on a device-resident synthetic batch,
-  * e2e   : ``model.fit`` over pinned host arrays: every step copies its uint8 images + labels
-            host->device and the running loss is read back device->host for a per-batch callback.
+One invocation produces, in ONE JSON line printed by rank 0:
+  * value      : device-timed (CUDA events, barrier + synchronize on both sides, max over ranks)
+                 over K steps on a device-resident synthetic batch, through the Keras-shaped API,
+  * e2e        : ``model.fit`` over pinned host arrays: every step copies its uint8 images + labels
+                 host->device and the running loss is read back device->host (median of the passes),
+  * baseline   : the same model / batch / steps / warm-up on stock PyTorch DDP + NCCL in the same
+                 process group (bench/torch_baseline.py) - ``vs_baseline`` is value / baseline value,
+  * small_batch: 64 images per GPU, with the exposed-communication time per step,
+  * allreduce  : (N >= 2) bus bandwidth of the fused all-reduce kernels vs NCCL at 1 KiB .. 1 GiB,
+  * checks     : (N >= 2) replicas bit-identical, fused all-reduce(+Adam) vs NCCL + reference
+                 update, data-parallel vs single-replica training,
+  * clocks     : NVML samples of this rank's GPU taken inside the timed region only.
 --impl reference runs the unmodified reference from baseline/_ref; it needs TensorFlow, which is
 not installable here, so it reports itself unavailable.
 """
 from __future__ import annotations
 
 import argparse
+import gc
 import json
 import os
-import subprocess
 import sys
+import threading
 import time
 
-sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "bench"))
 
 
 def reference_arm(args) -> int:
-    ref = os.path.join(os.path.dirname(os.path.abspath(__file__)), "baseline", "_ref")
+    ref = os.path.join(ROOT, "baseline", "_ref")
     why = None
     if not os.path.isdir(os.path.join(ref, "tensorflow_cloud")):
         why = "baseline/_ref is empty: the reference could not be installed offline"
@@ -49,53 +60,80 @@ def reference_arm(args) -> int:
     return 0
 
 
-class ClockSampler:
-    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
-             "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+class NvmlSampler:
+    """SM clock + throttle reasons of ONE GPU, sampled in-process (NVML) every ``period`` seconds
+    between start() and stop(): only the timed region is covered, however short it is."""
 
-    def __init__(self, path):
-        self.path, self.proc = path, None
+    REASONS = (("hw_slowdown", 0x8), ("sw_power_cap", 0x4), ("hw_thermal_slowdown", 0x40),
+               ("sw_thermal_slowdown", 0x20), ("hw_power_brake", 0x80))
+
+    def __init__(self, device, period=0.005):
+        self.period, self.handle, self.err = period, None, None
+        try:
+            import pynvml
+            import torch
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            try:
+                uuid = str(torch.cuda.get_device_properties(device).uuid)
+                self.handle = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid).encode())
+            except Exception:
+                vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+                idx = device.index or 0
+                if vis:
+                    idx = int(vis.split(",")[idx])
+                self.handle = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM)
+        except Exception as e:       # no NVML: say so in the record
+            self.err = f"{type(e).__name__}: {e}"
+
+    def _sample(self):
+        nv = self.nv
+        sm = nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM)
+        try:
+            bits = nv.nvmlDeviceGetCurrentClocksEventReasons(self.handle)
+        except Exception:
+            bits = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
+        try:
+            watts = nv.nvmlDeviceGetPowerUsage(self.handle) / 1000.0
+        except Exception:
+            watts = None
+        return sm, bits, watts
 
     def start(self):
-        try:
-            self.fh = open(self.path, "w")
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv",
-                                          "-lms", "100"], stdout=self.fh, stderr=subprocess.DEVNULL)
-        except OSError:
-            self.proc = None
+        if self.handle is None:
+            return
+        self.samples, self._stop = [], threading.Event()
+
+        def loop():
+            while not self._stop.is_set():
+                try:
+                    self.samples.append(self._sample())
+                except Exception:
+                    pass
+                self._stop.wait(self.period)
+        self.thread = threading.Thread(target=loop, daemon=True)
+        self.thread.start()
 
     def stop(self) -> dict:
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except subprocess.TimeoutExpired:
-            self.proc.kill()
-        self.fh.close()
-        sm, mx, reasons = [], [], set()
-        with open(self.path) as f:
-            for line in f.readlines()[1:]:
-                parts = [p.strip() for p in line.split(",")]
-                if len(parts) < 9:
-                    continue
-                try:
-                    sm.append(float(parts[1].split()[0]))
-                    mx.append(float(parts[2].split()[0]))
-                except ValueError:
-                    continue
-                for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
-                                      "sw_power_cap"), parts[5:9]):
-                    if val.lower().startswith("active"):
-                        reasons.add(name)
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        if self.handle is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [f"NVML unavailable: {self.err}"]}
+        self._stop.set()
+        self.thread.join(timeout=2)
+        sm = sorted(s[0] for s in self.samples)
+        bits = 0
+        for s in self.samples:
+            bits |= int(s[1])
+        watts = sorted(s[2] for s in self.samples if s[2] is not None)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_min_mhz": sm[0] if sm else None,
+                "sm_max_mhz": self.max_mhz, "reasons": [n for n, b in self.REASONS if bits & b],
+                "power_w": watts[len(watts) // 2] if watts else None, "samples": len(sm),
+                "source": "NVML in-process, timed region only"}
 
 
 def build_model(keras, classes):
     from cloud_b200.keras import layers
+    keras.backend.clear_session()
     inp = keras.Input(shape=(224, 224, 3))
     x = layers.ImageNormalization(name="normalize")(inp)      # uint8 NHWC -> bf16, on the device
     base = keras.applications.ResNet50(include_top=False, weights=None, input_tensor=x)
@@ -117,8 +155,15 @@ def main() -> int:
                     help="per-GPU batch (weak scaling); 256 fills a B200: ~20 GB of activations")
     ap.add_argument("--classes", type=int, default=1000)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-baseline", action="store_true", help="skip the in-run torch DDP+NCCL arm")
+    ap.add_argument("--baseline-variants", default=os.environ.get("TFC_BENCH_BASELINE", "eager,graph"),
+                    help="comma list of eager, graph, compile")
+    ap.add_argument("--no-small-batch", action="store_true")
+    ap.add_argument("--no-allreduce", action="store_true")
+    ap.add_argument("--no-checks", action="store_true")
+    ap.add_argument("--allreduce-max-mb", type=int, default=1024)
     ap.add_argument("--profile-e2e", action="store_true", help="cProfile of the timed fit() to stderr")
-    ap.add_argument("--e2e-passes", type=int, default=2, help="timed passes of the end-to-end arm (best one reported)")
+    ap.add_argument("--e2e-passes", type=int, default=3, help="timed passes of the end-to-end arm (median reported)")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
@@ -155,18 +200,11 @@ def main() -> int:
     strategy = tfc.distribute.MirroredStrategy() if world > 1 else tfc.distribute.OneDeviceStrategy("cuda:0")
     tfc.distribute.experimental_set_strategy(strategy)
     dev = strategy.device
+    t_start = time.perf_counter()
 
-    torch.manual_seed(1234)
-    np.random.seed(1234)
-    B = args.batch_per_gpu
-    model = build_model(keras, args.classes)
-
-    # ---- device-timed arm: device-resident synthetic batch ------------------------------------
-    x_dev = torch.randint(0, 256, (B, 224, 224, 3), dtype=torch.uint8, device=dev)
-    y_dev = torch.randint(0, args.classes, (B,), device=dev)
-    model._ensure_engine(x_dev)
-    model.train(True)
-    xi = model._to_internal(x_dev)
+    def note(msg):
+        if rank == 0:
+            print(f"[bench +{time.perf_counter() - t_start:6.1f}s] {msg}", file=sys.stderr, flush=True)
 
     def sync():
         torch.cuda.synchronize(dev)
@@ -174,36 +212,76 @@ def main() -> int:
             dist.barrier()
             torch.cuda.synchronize(dev)
 
-    for _ in range(int(os.environ.get("TFC_GRAPH_WARMUP", "3")) + 2):   # eager steps + graph capture
-        model._run_step(xi, y_dev)
-    sync()
-    for _ in range(args.warmup):
-        model._run_step(xi, y_dev)
-    sync()
-    sampler = ClockSampler(f"/tmp/bench_clocks_{os.getpid()}.csv") if rank == 0 else None
-    if sampler:
-        sampler.start()
-    launches0 = ops.kernel_launches()
-    replays0 = getattr(model, "_graph_replays", 0)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(args.steps):
-        red = model._run_step(xi, y_dev)
-    e1.record()
-    sync()
-    ms = e0.elapsed_time(e1) / args.steps
-    clocks = sampler.stop() if sampler else None
-    t = torch.tensor([ms], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
-    loss_now = float(red[0].item()) / max(float(red[2].item()), 1.0)
-    replays = getattr(model, "_graph_replays", 0) - replays0
-    per_step = (model._graph or {}).get("launches_per_step", 0) if model._graph else 0
-    gpu_launches = (ops.kernel_launches() - launches0) + replays * per_step
-    value = world * B / (ms * 1e-3)
+    def max_over_ranks(v):
+        t = torch.tensor([v], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
 
-    # ---- end-to-end arm: model.fit over pinned host arrays -------------------------------------
+    B = args.batch_per_gpu
+    sampler = NvmlSampler(dev)
+
+    # ---- comparison arm: stock PyTorch DDP + NCCL, same model / batch / steps / warm-up ----------
+    baseline = None
+    if not args.no_baseline:
+        try:
+            import torch_baseline
+            variants = tuple(v for v in args.baseline_variants.split(",") if v)
+            baseline = torch_baseline.run("resnet50", B, args.steps, args.warmup, args.classes, dev, world,
+                                          variants=variants, e2e=not args.no_e2e, sampler=NvmlSampler(dev))
+            note(f"baseline {baseline.get('best_variant')}: {baseline.get('value', 0):.0f} img/s")
+        except Exception as e:
+            baseline = {"impl": "torch_ddp_nccl", "failed": f"{type(e).__name__}: {str(e)[:300]}"}
+        gc.collect()
+        torch.cuda.empty_cache()
+
+    torch.manual_seed(1234)
+    np.random.seed(1234)
+
+    def device_timed(model, batch, steps, warmup, with_clocks=False):
+        """K graph-replayed training steps on a device-resident batch; returns (ms/step max over
+        ranks, launches inside the timed region, clocks, last reduced scalars)."""
+        x_dev = torch.randint(0, 256, (batch, 224, 224, 3), dtype=torch.uint8, device=dev)
+        y_dev = torch.randint(0, args.classes, (batch,), device=dev)
+        model._ensure_engine(x_dev)
+        model.train(True)
+        xi = model._to_internal(x_dev)
+        for _ in range(int(os.environ.get("TFC_GRAPH_WARMUP", "3")) + 2):   # eager steps + graph capture
+            model._run_step(xi, y_dev)
+        sync()
+        for _ in range(warmup):
+            model._run_step(xi, y_dev)
+        sync()
+        if with_clocks:
+            sampler.start()
+        launches0 = ops.kernel_launches()
+        replays0 = getattr(model, "_graph_replays", 0)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            red = model._run_step(xi, y_dev)
+        e1.record()
+        sync()
+        clocks = sampler.stop() if with_clocks else None
+        ms = max_over_ranks(e0.elapsed_time(e1) / steps)
+        replays = getattr(model, "_graph_replays", 0) - replays0
+        per_step = (model._graph or {}).get("launches_per_step", 0) if model._graph else 0
+        launches = (ops.kernel_launches() - launches0) + replays * per_step
+        return ms, int(launches), clocks, red
+
+    # ---- device-timed arm ------------------------------------------------------------------------
+    model = build_model(keras, args.classes)
+    ms, gpu_launches, clocks, red = device_timed(model, B, args.steps, args.warmup, with_clocks=True)
+    loss_now = float(red[0].item()) / max(float(red[2].item()), 1.0)
+    value = world * B / (ms * 1e-3)
+    note(f"cloud_b200: {value:.0f} img/s ({ms:.2f} ms/step)")
+    eng = model._engine
+    cfg_comm = {"comm_backend": eng.comm.backend,
+                "allreduce_algos": sorted({a for g in eng.groups for a in getattr(g, "bucket_algos", [g.algo])}),
+                "buckets": [len(g.buckets) for g in eng.groups],
+                "cuda_graph": bool(model._graph and model._graph.get("graph") is not None)}
+
+    # ---- end-to-end arm: model.fit over pinned host arrays ---------------------------------------
     e2e = None
     if not args.no_e2e:
         n_steps = args.steps
@@ -220,10 +298,6 @@ def main() -> int:
         model.fit(host_x[:warm], host_y[:warm], batch_size=B * world, epochs=1, shuffle=False,
                   verbose=0, callbacks=[ReadLoss()])
         sync()
-        # The timed pass is repeated and the faster pass reported (every pass is listed): the host
-        # side of this arm - a Python thread per rank launching a step and reading a loss back
-        # every ~20 ms - is at the mercy of whatever else runs on the box's CPUs, and one pass in
-        # ~10 was seen to run at half speed with the device idle (host_ms_per_step shows it).
         prof = None
         passes = []
         for rep in range(max(1, args.e2e_passes)):
@@ -244,35 +318,91 @@ def main() -> int:
                 buf = io.StringIO()
                 pstats.Stats(prof, stream=buf).sort_stats("cumulative").print_stats(35)
                 print(buf.getvalue()[:8000], file=sys.stderr)
-            tt = torch.tensor([dt_rep], device=dev, dtype=torch.float64)
-            if world > 1:
-                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            passes.append((float(tt.item()), {k: round(v / n_steps * 1e3, 3) for k, v in
-                                              getattr(model, "_fit_profile", {}).items() if k.endswith("_s")}))
-        dt, host_ms = min(passes, key=lambda p: p[0])
+            passes.append((max_over_ranks(dt_rep), {k: round(v / n_steps * 1e3, 3) for k, v in
+                                                    getattr(model, "_fit_profile", {}).items() if k.endswith("_s")}))
+        # the MEDIAN pass is the number (every pass is listed)
+        dt, host_ms = sorted(passes, key=lambda p: p[0])[len(passes) // 2]
         e2e = {"value": n_img / dt, "unit": "img/s", "ms_per_step": dt / n_steps * 1e3,
                "h2d_bytes_per_step": int(model._h2d_bytes // n_steps),
                "d2h_bytes_per_step": int(model._d2h_bytes // max(len(seen), 1)),
                "steps": n_steps, "losses_read": len(seen), "api": "keras.Model.fit",
-               "host_ms_per_step": host_ms,
+               "host_ms_per_step": host_ms, "reported": "median pass",
                "passes_ms_per_step": [round(p[0] / n_steps * 1e3, 3) for p in passes]}
+        del host_x, host_y
+        note(f"e2e: {e2e['value']:.0f} img/s")
+
+    # ---- small batch: the reference example's 64 images per GPU ---------------------------------
+    small = None
+    if not args.no_small_batch:
+        try:
+            del model
+            gc.collect()
+            torch.cuda.empty_cache()
+            sb = 64
+            m64 = build_model(keras, args.classes)
+            ms64, _l, _c, _r = device_timed(m64, sb, args.steps, args.warmup)
+            small = {"batch_per_gpu": sb, "value": world * sb / (ms64 * 1e-3), "unit": "img/s",
+                     "ms_per_step": ms64, "n_gpus": world}
+            if world > 1:
+                # the same step on this rank alone (no peers): what is left of the difference is
+                # communication the step could not hide
+                del m64
+                gc.collect()
+                torch.cuda.empty_cache()
+                single = tfc.distribute.OneDeviceStrategy(dev)
+                tfc.distribute.experimental_set_strategy(single)
+                m1 = build_model(keras, args.classes)
+                ms1, _l, _c, _r = device_timed(m1, sb, args.steps, args.warmup)
+                tfc.distribute.experimental_set_strategy(strategy)
+                small["single_replica_ms_per_step"] = ms1
+                small["exposed_comm_ms_per_step"] = max(0.0, ms64 - ms1)
+                small["efficiency_vs_1gpu"] = ms1 / ms64
+                del m1
+            else:
+                del m64
+            note(f"small batch: {small['value']:.0f} img/s")
+        except Exception as e:
+            small = {"failed": f"{type(e).__name__}: {str(e)[:300]}"}
+            tfc.distribute.experimental_set_strategy(strategy)
+        gc.collect()
+        torch.cuda.empty_cache()
+
+    # ---- the other half of the metric: all-reduce bus bandwidth, and correctness (N >= 2) -------
+    allreduce = checks = None
+    if world > 1 and not args.no_allreduce:
+        try:
+            allreduce = allreduce_rows(strategy.communicator, dev, world, args.allreduce_max_mb << 20)
+            note("allreduce rows done")
+        except Exception as e:
+            allreduce = [{"failed": f"{type(e).__name__}: {str(e)[:300]}"}]
+    if world > 1 and not args.no_checks:
+        try:
+            checks = run_checks(tfc, strategy, dev, world, rank)
+            note(f"checks: {checks}")
+        except Exception as e:
+            checks = {"failed": f"{type(e).__name__}: {str(e)[:300]}"}
 
     if rank == 0:
-        eng = model._engine
+        base_val = (baseline or {}).get("value")
         out = {
             "metric": "ResNet-50 training throughput (img/s), bf16, 224x224 synthetic, data-parallel",
             "value": value, "unit": "img/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": "cloud_b200",
+            "vs_baseline": (value / base_val) if base_val else None,
+            "dtype": "bf16", "data": "synthetic", "impl": "cloud_b200",
             "config": {"model": "ResNet-50 (Keras v1 graph, 25.6M params, all trainable)",
                        "global_batch": B * world, "batch_per_gpu": B, "image": "224x224x3 uint8",
                        "seq_len": None, "classes": args.classes, "optimizer": "Adam(1e-3)",
-                       "parallelism": f"dp{world}", "comm_backend": eng.comm.backend,
-                       "allreduce_algos": [g.algo for g in eng.groups],
-                       "cuda_graph": bool(model._graph and model._graph.get("graph") is not None),
+                       "parallelism": f"dp{world}", **cfg_comm,
                        "l2": f"per-step working set (activations ~{B * 0.08:.0f} GB) >> 126 MB L2; no explicit flush"},
-            "clocks": clocks, "e2e": e2e, "gpu_launches": int(gpu_launches),
-            "loss": loss_now,
+            "clocks": clocks, "e2e": e2e, "gpu_launches": int(gpu_launches), "loss": loss_now,
+            "baseline": None if baseline is None else dict(
+                baseline, ratio=(value / base_val) if base_val else None,
+                e2e_ratio=(e2e["value"] / baseline["e2e"]["value"])
+                if (e2e and baseline.get("e2e", {}).get("value")) else None,
+                note="stand-in for the reference's TF MirroredStrategy+NCCL run, which cannot be installed here"),
+            "small_batch": small, "allreduce": allreduce, "checks": checks,
+            "bench_wall_s": round(time.perf_counter() - t_start, 1),
         }
         sys.stdout.flush()
         os.dup2(real_stdout, 1)
@@ -282,6 +412,142 @@ def main() -> int:
         dist.barrier()
         dist.destroy_process_group()
     return 0
+
+
+def allreduce_rows(comm, dev, world, max_bytes):
+    """fp32 sum all-reduce of one gradient bucket at 1 KiB / 1 MiB / 64 MiB / 1 GiB: this
+    framework's kernel (best schedule; plain and fused with Adam) against NCCL on the same buffers.
+    busBW = algBW * 2(N-1)/N; CUDA events, max over ranks; the arena is walked in slots so that
+    consecutive iterations do not hit the same L2 lines where the size allows."""
+    import torch
+    import torch.distributed as dist
+    from cloud_b200 import ops
+    from cloud_b200.parallel import comm as C
+    from cloud_b200.ops.optim import make_hyper, optim_tick
+    sizes = [s for s in (1 << 10, 1 << 20, 64 << 20, 1 << 30) if s <= max_bytes]
+    cap = max(sizes)
+    gbuf, pbuf = comm.alloc_pair(cap, cap)
+    ctx = comm.make_ctx(gbuf, pbuf)
+    nccl_buf = torch.zeros(cap // 4, device=dev)
+    has_mc = bool(gbuf.mc_ptr and pbuf.mc_ptr)
+    hyper = make_hyper(dev, lr=1e-3)
+    # optimizer state for the fused variant (sharded for two-shot / NVLS, replicated for one-shot)
+    state = [torch.zeros(max(cap // 4 // world, (8 << 20) // 4), device=dev) for _ in range(3)]
+
+    def timed(fn, iters):
+        for i in range(5):
+            fn(i)
+        torch.cuda.synchronize(dev)
+        dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(iters):
+            fn(i)
+        e1.record()
+        torch.cuda.synchronize(dev)
+        t = torch.tensor([e0.elapsed_time(e1) / iters], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    rows = []
+    for size in sizes:
+        n = max(size // 4, 8 * world)
+        n = (n + 8 * world - 1) // (8 * world) * (8 * world)
+        nbytes = n * 4
+        slots = max(1, min(cap // nbytes, 8))
+        iters = 200 if nbytes <= (1 << 20) else (30 if nbytes <= (64 << 20) else 8)
+        k = 2 * (world - 1) / world / 1e9
+        ms = timed(lambda i: dist.all_reduce(nccl_buf[(i % slots) * n:(i % slots) * n + n]), iters)
+        row = {"bytes": nbytes, "nccl_us": ms * 1e3, "nccl_busbw_gbs": nbytes / (ms * 1e-3) * k}
+        algos = [("oneshot", C.ALGO_ONESHOT)] if nbytes <= (8 << 20) else []
+        algos.append(("twoshot", C.ALGO_TWOSHOT))
+        if has_mc:
+            algos.append(("nvls", C.ALGO_NVLS))
+        best = None
+        for name, algo in algos:
+            def ours(i, algo=algo):
+                comm.fused(ctx, algo=algo, opt=0, grad_dtype=torch.float32, param_dtype=torch.float32,
+                           off=(i % slots) * n, length=n, master=None, s1=None, s2=None, state_off=0,
+                           hyper=hyper, zero_grads=False)
+            ms = timed(ours, iters)
+            row[name + "_us"] = ms * 1e3
+            if best is None or ms < best[0]:
+                best = (ms, name, algo)
+        row["algo"] = best[1]
+        row["us"] = best[0] * 1e3
+        row["busbw_gbs"] = nbytes / (best[0] * 1e-3) * k
+        row["frac_of_900"] = row["busbw_gbs"] / 900.0
+        row["vs_nccl"] = row["busbw_gbs"] / row["nccl_busbw_gbs"]
+        # the same schedule fused with Adam + parameter publication + gradient zeroing
+        sharded = best[2] != C.ALGO_ONESHOT
+        n_state = n // world if sharded else n
+        if n_state <= state[0].numel():
+            def fused(i, algo=best[2]):
+                optim_tick(hyper)
+                comm.fused(ctx, algo=algo, opt=ops.OPT_CODES["adam"], grad_dtype=torch.float32,
+                           param_dtype=torch.float32, off=0, length=n, master=None, s1=state[1], s2=state[2],
+                           state_off=0, hyper=hyper, zero_grads=True)
+            ms = timed(fused, iters)
+            row["fused_adam_us"] = ms * 1e3
+            row["fused_adam_busbw_gbs"] = nbytes / (ms * 1e-3) * k
+        rows.append(row)
+    del gbuf, pbuf, ctx
+    return rows
+
+
+def run_checks(tfc, strategy, dev, world, rank):
+    """Multi-GPU correctness, on the code paths of bench/allreduce_sweep.py --check-only and
+    tests/dist_train_check.py: every schedule x dtype of the fused all-reduce (plain and with Adam)
+    against NCCL + a reference update, replicas bit-identical, a skewed-arrival stress, and the
+    README-style MLP trained data-parallel against the same global batches on one replica."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import allreduce_sweep as sweep
+    from cloud_b200.keras import layers
+    keras = tfc.keras
+    results = []
+    comm = strategy.communicator
+    ok = sweep.check(comm, dev, world, rank, results)
+    ok = sweep.stress(comm, dev, world, rank, results, iters=24) and ok
+    errs = [r["max_err"] for r in results if "max_err" in r]
+    same = all(r.get("replicas_identical", True) for r in results)
+
+    def build(seed, st):
+        torch.manual_seed(seed)
+        keras.backend.clear_session()
+        with st.scope():
+            m = keras.Sequential([layers.Dense(64, activation="relu", input_shape=(32,)),
+                                  layers.Dense(16, activation="relu"),
+                                  layers.Dense(4, activation="softmax")])
+            m.compile(optimizer=keras.optimizers.Adam(1e-2), loss="sparse_categorical_crossentropy",
+                      metrics=["accuracy"])
+        return m
+
+    rng = np.random.RandomState(0)
+    x = rng.rand(512, 32).astype("float32")
+    y = (x[:, :4].argmax(1)).astype("int64")
+    m = build(1 + rank, strategy)                  # different init per replica: the broadcast fixes it
+    with strategy.scope():
+        h = m.fit(x, y, batch_size=64, epochs=3, shuffle=False, verbose=0)
+    w_dist = [w.copy() for w in m.get_weights()]
+    single = tfc.distribute.OneDeviceStrategy(dev)
+    ref = build(1, single)
+    ref._strategy = single
+    with single.scope():
+        h_ref = ref.fit(x, y, batch_size=64, epochs=3, shuffle=False, verbose=0)
+    w_err = max(float(np.abs(a - b).max()) for a, b in zip(w_dist, ref.get_weights()))
+    loss_err = abs(h.history["loss"][-1] - h_ref.history["loss"][-1])
+    flat = torch.tensor(np.concatenate([w.reshape(-1) for w in w_dist]), device=dev)
+    gathered = [torch.zeros_like(flat) for _ in range(world)]
+    dist.all_gather(gathered, flat)
+    same_w = all(torch.equal(g, gathered[0]) for g in gathered[1:])
+    return {"collective_checks_ok": bool(ok), "n_collective_checks": len(results),
+            "failed": [r["check"] for r in results if not r.get("ok", True)],
+            "replicas_identical": bool(same and same_w),
+            "fused_vs_nccl_max_err": max(errs) if errs else None,
+            "dp_vs_single_replica_loss_err": loss_err, "dp_vs_single_replica_weight_err": w_err,
+            "dp_loss": h.history["loss"][-1], "single_loss": h_ref.history["loss"][-1]}
 
 
 if __name__ == "__main__":

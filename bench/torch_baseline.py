@@ -1,0 +1,210 @@
+"""The comparison arm of ``bench.py``: stock PyTorch on the identical model, nothing from cloud_b200.
+
+The reference's own TensorFlow ``MirroredStrategy`` + NCCL run (what
+``core/preprocess.py:137-149`` injects) cannot be installed on this box, so the measured stand-in
+is torchvision ResNet-50 under ``DistributedDataParallel`` over NCCL with everything a careful
+PyTorch user would switch on:
+
+* ``cudnn.benchmark`` (cuDNN autotuning), channels_last weights and activations,
+* the synthetic batch already bf16 + channels_last on the device (no per-step cast),
+* bf16 autocast, ``torch.optim.Adam(fused=True)``, ``gradient_as_bucket_view``,
+* variants: ``eager``, ``graph`` (the step in a CUDA graph - one rank; under DDP the capture is
+  attempted and, if NCCL refuses it, reported as such), ``compile`` (``torch.compile`` of the model).
+
+``run()`` returns the best variant and every variant's number.  Device-timed (CUDA events, barrier +
+synchronize on both sides, max over ranks), plus an end-to-end loop with the same per-step host
+traffic as ``bench.py``'s own e2e arm: pinned uint8 images copied host->device on a side stream one
+batch ahead, normalised on the device, the loss read back every step.
+"""
+from __future__ import annotations
+
+import time
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+
+def _build(name, classes):
+    import torchvision
+    if name == "resnet50":
+        m = torchvision.models.resnet50(num_classes=classes)
+        # torchvision builds "v1.5" (stride on the 3x3 convolution); Keras' ResNet50 - the
+        # reference's model - is v1 (stride on the first 1x1 convolution of the block): move the
+        # stride so both arms train the same graph (v1 has ~7 % fewer FLOPs)
+        for mod in m.modules():
+            if isinstance(mod, torchvision.models.resnet.Bottleneck) and mod.conv2.stride == (2, 2):
+                mod.conv2.stride = (1, 1)
+                mod.conv1.stride = (2, 2)
+        return m
+    if name == "resnet18":
+        return torchvision.models.resnet18(num_classes=classes)
+    if name == "mlp":
+        return nn.Sequential(nn.Linear(784, 512), nn.ReLU(), nn.Dropout(0.2), nn.Linear(512, 10))
+    raise ValueError(name)
+
+
+def _sync(dev, world):
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize(dev)
+
+
+def _max_over_ranks(v, dev, world):
+    t = torch.tensor([v], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def run(model_name: str, batch: int, steps: int, warmup: int, classes: int, dev, world: int,
+        variants=("eager", "graph"), e2e: bool = True, sampler=None) -> dict:
+    torch.backends.cudnn.benchmark = True
+    out = {"impl": "torch_ddp_nccl" if world > 1 else "torch", "model": model_name, "variants": {},
+           "settings": "cudnn.benchmark, channels_last, bf16 autocast, bf16 device-resident input, "
+                       "Adam(fused=True), DDP(gradient_as_bucket_view) over NCCL"}
+    image = model_name != "mlp"
+    best = None
+    for variant in variants:
+        torch.manual_seed(0)
+        model = _build(model_name, classes).to(dev)
+        if image:
+            model = model.to(memory_format=torch.channels_last)
+            x = torch.randn(batch, 3, 224, 224, device=dev).to(torch.bfloat16).contiguous(
+                memory_format=torch.channels_last)
+            y = torch.randint(0, classes, (batch,), device=dev)
+        else:
+            x = torch.randn(batch, 784, device=dev)
+            y = torch.randint(0, 10, (batch,), device=dev)
+        graph_mode = variant == "graph"
+        opt = torch.optim.Adam(model.parameters(), lr=1e-3, fused=True, capturable=graph_mode)
+        net = model
+        if variant == "compile":
+            net = torch.compile(model)
+        if world > 1:
+            net = torch.nn.parallel.DistributedDataParallel(net, device_ids=[dev.index],
+                                                            gradient_as_bucket_view=True)
+        loss_fn = nn.CrossEntropyLoss()
+
+        def step(xb=x, yb=y, net=net, opt=opt):
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                o = net(xb)
+                loss = loss_fn(o.float(), yb)
+            opt.zero_grad(set_to_none=True)
+            loss.backward()
+            opt.step()
+            return loss
+
+        graph = None
+        try:
+            if graph_mode:
+                s = torch.cuda.Stream(dev)
+                s.wait_stream(torch.cuda.current_stream(dev))
+                with torch.cuda.stream(s):
+                    for _ in range(11 if world > 1 else 3):
+                        step()
+                torch.cuda.current_stream(dev).wait_stream(s)
+                torch.cuda.synchronize(dev)
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph):
+                    static_loss = step()
+
+            def one():
+                if graph is not None:
+                    graph.replay()
+                    return static_loss
+                return step()
+
+            t_c0 = time.perf_counter()
+            for _ in range(max(warmup, 3)):
+                one()
+            _sync(dev, world)
+            warm_s = time.perf_counter() - t_c0
+            if sampler is not None:
+                sampler.start()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(steps):
+                one()
+            e1.record()
+            _sync(dev, world)
+            clocks = sampler.stop() if sampler is not None else None
+            ms = _max_over_ranks(e0.elapsed_time(e1) / steps, dev, world)
+            rec = {"ms_per_step": ms, "value": world * batch / (ms * 1e-3), "warmup_s": round(warm_s, 2),
+                   "clocks": clocks}
+        except Exception as e:                       # e.g. NCCL inside a capture, inductor unavailable
+            torch.cuda.synchronize(dev)
+            rec = {"failed": f"{type(e).__name__}: {str(e)[:200]}"}
+        # every rank must agree on whether this variant worked before anyone uses its number
+        okv = _max_over_ranks(0.0 if "value" in rec else 1.0, dev, world)
+        if okv > 0 and "value" in rec:
+            rec = {"failed": "failed on another rank"}
+        out["variants"][variant] = rec
+        if "value" in rec and (best is None or rec["value"] > out["variants"][best]["value"]):
+            best = variant
+
+        # end-to-end loop of the eager variant (the one every user can run)
+        if e2e and image and variant == "eager" and "value" in rec:
+            out["e2e"] = _e2e(step, batch, steps, max(warmup, 3), classes, dev, world)
+        del net, model, opt, graph
+        torch.cuda.empty_cache()
+    if best is not None:
+        out["best_variant"] = best
+        out["value"] = out["variants"][best]["value"]
+        out["ms_per_step"] = out["variants"][best]["ms_per_step"]
+        out["clocks"] = out["variants"][best].get("clocks")
+    out["unit"] = "img/s" if image else "samples/s"
+    out["n_gpus"] = world
+    out["batch_per_gpu"] = batch
+    return out
+
+
+def _e2e(step, batch, steps, warmup, classes, dev, world) -> dict:
+    """Host -> device every step from pinned memory (copy stream, one batch ahead), uint8 -> bf16
+    normalisation on the device, loss read back to the host every step."""
+    n = batch * (steps + warmup)
+    host_x = torch.randint(0, 256, (n, 224, 224, 3), dtype=torch.uint8).pin_memory()
+    host_y = torch.randint(0, classes, (n,), dtype=torch.int64).pin_memory()
+    copy_stream = torch.cuda.Stream(dev)
+    mean = torch.tensor([123.68, 116.78, 103.94], device=dev).view(1, 3, 1, 1)
+    h2d = d2h = 0
+
+    def fetch(i):
+        with torch.cuda.stream(copy_stream):
+            xb = host_x[i * batch:(i + 1) * batch].to(dev, non_blocking=True)
+            yb = host_y[i * batch:(i + 1) * batch].to(dev, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(copy_stream)
+        return xb, yb, ev
+
+    def consume(item):
+        xb, yb, ev = item
+        cur = torch.cuda.current_stream(dev)
+        cur.wait_event(ev)
+        xb.record_stream(cur)
+        yb.record_stream(cur)
+        xf = (xb.permute(0, 3, 1, 2).to(torch.bfloat16) - mean.to(torch.bfloat16)).contiguous(
+            memory_format=torch.channels_last)
+        return step(xf, yb)
+
+    nxt = fetch(0)
+    losses = []
+    for i in range(warmup):
+        cur, nxt = nxt, fetch(i + 1)
+        losses.append(float(consume(cur).item()))
+    _sync(dev, world)
+    t0 = time.perf_counter()
+    for i in range(warmup, warmup + steps):
+        cur = nxt
+        if i + 1 < warmup + steps:
+            nxt = fetch(i + 1)
+        loss = consume(cur)
+        losses.append(float(loss.item()))           # the device->host read of this step
+        h2d += batch * 224 * 224 * 3 + batch * 8
+        d2h += 4
+    _sync(dev, world)
+    dt = _max_over_ranks(time.perf_counter() - t0, dev, world)
+    return {"value": world * batch * steps / dt, "unit": "img/s", "ms_per_step": dt / steps * 1e3,
+            "h2d_bytes_per_step": h2d // steps, "d2h_bytes_per_step": d2h // steps,
+            "api": "torch loop (pinned uint8 H2D on a copy stream, loss.item() every step)"}

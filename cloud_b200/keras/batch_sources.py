@@ -112,6 +112,11 @@ class _ArraySource:
 
     def __len__(self):
         full = self.n // self.batch if self.drop_last else -(-self.n // self.batch)
+        rem = self.n - (full - 1) * self.batch if full else 0
+        if full and self.world > 1 and 0 < rem < self.world:
+            # a tail with fewer samples than replicas would leave some replica with an empty batch
+            # while the others wait for it in the gradient all-reduce: every replica drops that step
+            full -= 1
         return min(full, self.steps) if self.steps else full
 
     def __iter__(self):
@@ -144,9 +149,11 @@ class _ArraySource:
         for s in range(s, n_steps):
             lo = s * self.batch
             hi = min(self.n, lo + self.batch)
-            per = -(-(hi - lo) // self.world)
-            a = lo + self.rank * per
-            b = min(hi, a + per)
+            # tail batches are split as evenly as they go: replica r gets floor(rem / world) rows
+            # plus one of the rem % world left-over rows if r is among the first ones
+            q, extra = divmod(hi - lo, self.world)
+            a = lo + self.rank * q + min(self.rank, extra)
+            b = a + q + (1 if self.rank < extra else 0)
             if perm is not None:
                 idx = perm[a:b]
                 xb = self.x.index_select(0, idx)

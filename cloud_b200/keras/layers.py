@@ -186,7 +186,13 @@ class Layer(nn.Module):
     def get_weights(self):
         out = []
         for _s, attr, to_keras, _f in self._keras_weight_specs:
-            t = getattr(self, attr).detach().float().cpu()
+            src = getattr(self, attr)
+            acc = getattr(src, "_cb2_fp32", None)
+            # a parameter owned by a training engine answers with its fp32 master, not with the bf16
+            # rounding the kernels compute on: what is saved is what training continues from
+            t = acc.get() if acc is not None else None
+            if t is None:
+                t = src.detach().float().cpu()
             if to_keras is not None:
                 t = to_keras(t)
             out.append(np.ascontiguousarray(t.numpy()))
@@ -206,7 +212,11 @@ class Layer(nn.Module):
                 if tuple(t.shape) != tuple(dst.shape):
                     raise ValueError(f"Layer {self.name}: weight shape {tuple(t.shape)} is not "
                                      f"compatible with {tuple(dst.shape)}")
-                dst.copy_(t.to(dst.device, dst.dtype))
+                acc = getattr(dst, "_cb2_fp32", None)
+                if acc is not None:
+                    acc.set(t)                 # fp32 into the master, its rounding into the arena
+                else:
+                    dst.copy_(t.to(dst.device, dst.dtype))
 
     def count_params(self):
         return sum(int(getattr(self, attr).numel()) for _s, attr, *_ in self._keras_weight_specs)

@@ -316,8 +316,19 @@ class Model(nn.Module):
         self.run_eagerly = bool(run_eagerly)
         self._compiled_with = {"loss": loss, "metrics": list(metrics or [])}
         self._strategy = get_strategy()
+        old = getattr(self, "_engine", None)
+        if old is not None:
+            # a re-compile (freeze / unfreeze, new optimizer) builds a new engine with new arenas:
+            # the old one must stop reacting to gradients, and no CUDA graph recorded against its
+            # arenas - single-step or steps_per_execution - may ever be replayed again
+            old.remove_hooks()
+            for g in old.groups:
+                g.ctx = None
+                g.bufs = ()
+                g.grad_arena = g.param_arena = g.master = g.s1 = g.s2 = None
         self._engine = None
         self._graph = None
+        self._graph_k = None
         self._regularized_layers = None
         self._weighted_targets = None
 

@@ -76,6 +76,7 @@ class _Group:
     bufs: tuple = ()
     algo: int = 0
     sharded: bool = False
+    master_buf: object = None
 
 
 def _round_up(x: int, m: int) -> int:
@@ -122,6 +123,7 @@ class DPEngine:
         self._hook_handles = []
         self.allreduce_host_us: list = []      # drained by the front end into the metrics registry
         self._in_step = False
+        self._master_exact = set()
         self._fault = None
         fault = os.environ.get("TFC_FAULT")
         if fault and os.environ.get("TFC_RESTART_COUNT", "0") == "0":   # injected once, not again after a restart
@@ -199,6 +201,13 @@ class DPEngine:
         code = self.opt.code
         z = lambda: torch.zeros(n_state, dtype=torch.float32, device=self.device)  # noqa: E731
         g.master = z() if need_master else None
+        g.master_buf = None
+        if need_master and g.sharded:
+            # the fp32 master shards live in peer-mapped memory: a checkpoint written by the chief
+            # alone (Keras' ModelCheckpoint) reads every rank's shard over NVLink, no collective
+            from . import symm
+            g.master_buf = symm.SymmetricBuffer(n_state * 4, self.device, self.comm.xchg, want_multicast=False)
+            g.master = g.master_buf.view(torch.float32, n_state)
         g.s1 = z() if code != 0 else None
         g.s2 = z() if code in (1, 2, 3, 5) else None
 
@@ -266,6 +275,7 @@ class DPEngine:
                 # into the arena view `p.grad` and call this instead of returning a gradient
                 p._cb2_direct_grad = self.is_cuda
                 p._cb2_grad_written = hook
+                p._cb2_fp32 = self._fp32_accessor(gi, _name)
                 seen += 1
                 if seen == g.buckets[bi].n_params:
                     bi, seen = bi + 1, 0
@@ -284,6 +294,106 @@ class DPEngine:
         for h in self._hook_handles:
             h.remove()
         self._hook_handles = []
+        for g in self.groups:
+            for _n, p in g.params:
+                for attr in ("_cb2_fp32", "_cb2_grad_written", "_cb2_direct_grad"):
+                    if hasattr(p, attr):
+                        try:
+                            delattr(p, attr)
+                        except AttributeError:
+                            pass
+
+    # ------------------------------------------------------------------------------------------
+    # fp32 view of a parameter: checkpoints must hold the master values, not their bf16 rounding
+    # ------------------------------------------------------------------------------------------
+    def _fp32_accessor(self, gi: int, name: str):
+        ref = weakref.ref(self)
+
+        class _Acc:
+            def get(_self):
+                eng = ref()
+                return None if eng is None else eng.master_value(gi, name)
+
+            def set(_self, value):
+                eng = ref()
+                if eng is not None:
+                    eng.set_master_value(gi, name, value)
+        return _Acc()
+
+    def _param_slot(self, gi: int, name: str):
+        g = self.groups[gi]
+        for (n, p), off in zip(g.params, g.offsets):
+            if n == name:
+                return g, p, off
+        raise KeyError(name)
+
+    def _to_logical(self, p, flat: torch.Tensor) -> torch.Tensor:
+        """Arena order -> the parameter's logical shape (conv kernels are O,H,W,I in a CUDA arena)."""
+        if p.dim() == 4 and self.is_cuda:
+            return flat.view(p.shape[0], p.shape[2], p.shape[3], p.shape[1]).permute(0, 3, 1, 2)
+        return flat.view(p.shape)
+
+    def _to_arena_order(self, p, t: torch.Tensor) -> torch.Tensor:
+        t = t.reshape(p.shape)
+        if p.dim() == 4 and self.is_cuda:
+            t = t.permute(0, 2, 3, 1)
+        return t.contiguous().reshape(-1)
+
+    def _gather_state(self, g: _Group, local: torch.Tensor, buf, lo: int, hi: int) -> torch.Tensor:
+        """Elements [lo, hi) of a (possibly sharded) fp32 state vector, in arena order.  Sharded
+        state that lives in peer-mapped memory (``buf``) is read from the peers directly."""
+        if not g.sharded:
+            return local[lo:hi].detach().clone()
+        if buf is None:
+            raise RuntimeError("sharded state without a peer mapping cannot be read by one rank")
+        from .symm import _wrap
+        out = torch.empty(hi - lo, dtype=torch.float32, device=self.device)
+        for b in g.buckets:
+            shard = b.length // self.world
+            s_off = b.off // self.world
+            for r in range(self.world):
+                a, z = max(lo, b.off + r * shard), min(hi, b.off + (r + 1) * shard)
+                if a >= z:
+                    continue
+                src = buf.local.view(torch.float32) if r == self.rank else \
+                    _wrap(buf.peer_ptrs[r], buf.nbytes, self.device).view(torch.float32)
+                k = s_off + (a - (b.off + r * shard))
+                out[a - lo: z - lo].copy_(src[k: k + (z - a)])
+        return out
+
+    def master_value(self, gi: int, name: str) -> torch.Tensor:
+        """The fp32 value of a parameter in its logical shape (CPU tensor): the master copy when the
+        group has one, else the parameter itself.  No collective: safe to call on the chief alone."""
+        g, p, off = self._param_slot(gi, name)
+        n = p.numel()
+        if g.master is None:
+            return p.detach().float().cpu()
+        if self.is_cuda:
+            torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
+        flat = self._gather_state(g, g.master, g.master_buf, off, off + n)
+        return self._to_logical(p, flat).contiguous().cpu()
+
+    def set_master_value(self, gi: int, name: str, value: torch.Tensor) -> None:
+        """Overwrite a parameter with fp32 values: the master first (this rank's shard), then their
+        rounding into the arena.  Every rank calls this with the same values (load_weights)."""
+        g, p, off = self._param_slot(gi, name)
+        n = p.numel()
+        flat = self._to_arena_order(p, value.detach().to(self.device, torch.float32))
+        with torch.no_grad():
+            g.param_arena[off:off + n].copy_(flat.to(g.dtype))
+            if g.master is None:
+                return
+            if not g.sharded:
+                g.master[off:off + n].copy_(flat)
+            else:
+                for b in g.buckets:
+                    shard = b.length // self.world
+                    lo = b.off + self.rank * shard
+                    a, z = max(lo, off), min(lo + shard, off + n)
+                    if a < z:
+                        s_off = b.off // self.world
+                        g.master[s_off + (a - lo): s_off + (z - lo)].copy_(flat[a - off: z - off])
+            self._master_exact.add((gi, name))
 
     # ------------------------------------------------------------------------------------------
     def set_lr(self, lr: float) -> None:
@@ -380,7 +490,9 @@ class DPEngine:
     # ------------------------------------------------------------------------------------------
     def full_master_state(self) -> dict:
         """Gather the (possibly sharded) fp32 master + moments as full-size CPU tensors keyed by
-        parameter name: what checkpoints store, so a run can resume under any strategy."""
+        parameter name, each in the parameter's LOGICAL shape (a conv kernel is O,I,H,W whatever
+        order the arena of this device keeps it in): what checkpoints store, so a run can resume
+        under any strategy and on any device type."""
         import torch.distributed as dist
         out = {}
         for g in self.groups:
@@ -390,7 +502,7 @@ class DPEngine:
                     continue
                 if g.sharded:
                     parts = [torch.empty_like(t) for _ in range(self.world)]
-                    dist.all_gather(parts, t, group=self.comm.group)
+                    dist.all_gather(parts, t.contiguous(), group=self.comm.group)
                     buf = torch.empty(g.total, dtype=torch.float32, device=self.device)
                     for b in g.buckets:
                         shard = b.length // self.world
@@ -404,12 +516,14 @@ class DPEngine:
                 n = p.numel()
                 entry = {}
                 for key, buf in full.items():
-                    entry[key] = buf[off:off + n].detach().cpu().clone()
+                    entry[key] = self._to_logical(p, buf[off:off + n].detach()).contiguous().cpu().clone()
                 out[name] = entry
         out["__step__"] = float(self.hyper[5].item())
+        out["__layout__"] = "logical"
         return out
 
     def load_master_state(self, state: dict) -> None:
+        logical = state.get("__layout__") == "logical"
         for g in self.groups:
             for (name, p), off in zip(g.params, g.offsets):
                 entry = state.get(name)
@@ -419,7 +533,10 @@ class DPEngine:
                 for key, t in (("master", g.master), ("s1", g.s1), ("s2", g.s2)):
                     if t is None or key not in entry:
                         continue
-                    src = entry[key].to(self.device).reshape(-1)
+                    src = entry[key].to(self.device)
+                    # files written before the layout tag hold the arena order of the device that
+                    # wrote them (assumed to be this one's)
+                    src = self._to_arena_order(p, src) if logical and src.dim() == p.dim() else src.reshape(-1)
                     if not g.sharded:
                         t[off:off + n].copy_(src)
                         continue
@@ -438,9 +555,19 @@ class DPEngine:
             self.hyper[7] = 1.0 - self.opt.beta2 ** step if step > 0 else 1.0
 
     def params_changed(self) -> None:
-        """Call after parameters were overwritten from outside (load_weights/set_weights)."""
+        """Call after parameters were overwritten from outside (load_weights/set_weights).  Masters
+        that were just given exact fp32 values through ``set_master_value`` keep them; the others
+        are re-derived from the arena."""
+        exact = self._master_exact
+        self._master_exact = set()
+        keep = {}
+        for gi, name in exact:
+            keep[(gi, name)] = self.master_value(gi, name)
         for g in self.groups:
             self._refresh_master(g)
+        for (gi, name), v in keep.items():
+            self.set_master_value(gi, name, v)
+        self._master_exact = set()
 
     def kernel_launches(self) -> int:
         return comm_mod.launches() + ops.optim.launches()

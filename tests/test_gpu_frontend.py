@@ -108,3 +108,31 @@ def test_weight_penalty_on_gpu():
     assert hist.history["loss"][0] == pytest.approx(25.0025, rel=2e-2)
     w = model.get_weights()[0][0, 0]
     assert w == pytest.approx(0.5 + 0.002 * 99.99, rel=2e-2)
+
+
+def test_recompile_with_steps_per_execution_trains_the_live_weights(tmp_path):
+    """compile -> fit -> compile -> fit with a K-step CUDA graph: the second fit must not replay the
+    graph recorded against the first engine's arenas, and a save/load round trip
+    keeps the fp32 master values, not their bf16 rounding."""
+    _on("cuda:0")
+    x, y = _blobs(512)
+    model = _mlp()
+    for _round in range(2):
+        model.compile(optimizer=keras.optimizers.Adam(1e-2),
+                      loss=keras.losses.SparseCategoricalCrossentropy(from_logits=True),
+                      steps_per_execution=4)
+        before = [w.copy() for w in model.get_weights()]
+        h = model.fit(x, y, batch_size=32, epochs=2, shuffle=False, verbose=0)
+        after = model.get_weights()
+        assert all(not np.array_equal(a, b) for a, b in zip(before, after)), "weights did not move"
+        assert h.history["loss"][-1] < h.history["loss"][0]
+    # get_weights answers with fp32 masters: finer than bf16
+    w = model.get_weights()[0]
+    assert not np.array_equal(w, torch.from_numpy(w).to(torch.bfloat16).float().numpy())
+    path = str(tmp_path / "w.h5")
+    model.save_weights(path)
+    model.set_weights([np.zeros_like(v) for v in model.get_weights()])
+    model.load_weights(path)
+    for a, b in zip(model.get_weights(), [w] + model.get_weights()[1:]):
+        assert np.array_equal(a, b)
+    assert np.array_equal(model.get_weights()[0], w)
