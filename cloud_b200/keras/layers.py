@@ -453,6 +453,10 @@ class Conv2D(Layer):
         # Set by a directly following trainable BatchNormalization: a 1x1 convolution on the
         # tcgen05 GEMM then reduces the batch statistics in its epilogue (ops/conv.py).
         self.feeds_bn = False
+        # Set when that BatchNormalization is the ONLY consumer of this layer's output: a wide 1x1
+        # convolution then hands its operands on and the pair runs as the folded GEMMs of
+        # ops/convbn.py (the convolution output is never stored).
+        self.fold_candidate = False
 
     def build(self, input_shape):
         cin = int(input_shape[-1])
@@ -512,6 +516,14 @@ class Conv2D(Layer):
         w = self.kernel
         if w.dtype != x.dtype:
             x = x.to(w.dtype)
+        if (training and self.fold_candidate and (self.bias_absorbed_by_bn or self.bias is None)
+                and self.activation_name in (None, "linear") and torch.is_grad_enabled()
+                and ops.convbn_supported(x, w, self.strides, pad, self.dilation)):
+            return ops.DeferredConv(x, w, self, pad)
+        return self._plain_conv(x, training, pad)
+
+    def _plain_conv(self, x, training=True, pad=0):
+        w = self.kernel
         b = self.bias
         if b is not None and self.bias_absorbed_by_bn and training:
             b = None
@@ -674,6 +686,7 @@ class BatchNormalization(Layer):
         prev = first.layer
         if isinstance(prev, Conv2D) and prev.activation_name in (None, "linear") and self._trainable:
             prev.feeds_bn = True
+            prev.fold_candidate = True       # Model._init_functional clears it if the output has other consumers
             if prev.use_bias:
                 prev.bias_absorbed_by_bn = True
                 object.__setattr__(self, "_absorbed_conv", prev)   # not a submodule: no double registration
@@ -697,6 +710,19 @@ class BatchNormalization(Layer):
         train = bool(training) and self._trainable
         conv = self._absorbed_conv
         mean_bias = conv.bias if (conv is not None and train and conv.bias is not None) else None
+        if isinstance(x, ops.DeferredConv):
+            d = x
+            ok = (train and self.gamma.dtype == torch.float32 and ops.bn_available() and
+                  (residual is None or (isinstance(residual, torch.Tensor) and residual.dtype == torch.bfloat16
+                                        and residual.dim() == 4 and residual.shape[0] == d.x.shape[0]
+                                        and residual.shape[1] == d.w.shape[0]
+                                        and tuple(residual.shape[2:]) == tuple(d.x.shape[2:])
+                                        and residual.is_contiguous(memory_format=torch.channels_last))))
+            if ok:
+                return ops.conv1x1_bn(d.x, d.w, self.gamma, self.beta, self.moving_mean, self.moving_variance,
+                                      1.0 - self.momentum, self.epsilon, relu=relu, residual=residual,
+                                      mean_bias=mean_bias)
+            x = d.materialize()
         if x.is_cuda and x.dim() == 4 and x.dtype == torch.bfloat16 and ops.bn_available():
             return ops.batch_norm_nhwc(x, self.gamma, self.beta, self.moving_mean,
                                        self.moving_variance, train, 1.0 - self.momentum,

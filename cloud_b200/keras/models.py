@@ -102,6 +102,13 @@ class Model(nn.Module):
                 cons = consumers.get(id(t), [])
                 if len(cons) == 1 and isinstance(cons[0].layer, L.Conv2D) and cons[0].layer.is_stem_geometry():
                     t.layer.defer_to_stem = True
+        # a convolution whose output is read by anything but one BatchNormalization cannot hand its
+        # operands on instead of its output (ops/convbn.py)
+        for t in order:
+            if isinstance(t.layer, L.Conv2D) and getattr(t.layer, "fold_candidate", False):
+                cons = consumers.get(id(t), [])
+                if id(t) in outs or len(cons) != 1 or not isinstance(cons[0].layer, L.BatchNormalization):
+                    t.layer.fold_candidate = False
         # a batch-norm output with two consumers (the input of a residual block): in training its
         # two gradients are merged inside the batch-norm backward kernels (ops.bn_fork)
         self._fork_ids = {id(t) for t in order

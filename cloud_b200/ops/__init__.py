@@ -18,13 +18,14 @@ from .bn import batch_norm_nhwc, bn_available, fork as bn_fork  # noqa: F401,E40
 from .pool import max_pool_nhwc  # noqa: F401,E402
 from .conv import conv1x1, supported as conv1x1_supported, mode as conv1x1_mode  # noqa: F401,E402
 from .conv import stem_conv, stem_conv_s2d, stem_supported, conv_kxk, kxk_supported  # noqa: F401,E402
+from .convbn import conv1x1_bn, supported as convbn_supported, DeferredConv  # noqa: F401,E402
 
 
 def kernel_launches() -> int:
     """How many cloud_b200 kernels this process has launched (bench.py reports it)."""
     import importlib
     total = 0
-    for name in ("dense", "loss", "elementwise", "optim", "bn", "pool"):   # `dense` the module, not the op
+    for name in ("dense", "loss", "elementwise", "optim", "bn", "pool", "convbn"):   # `dense` the module, not the op
         total += importlib.import_module(f"{__name__}.{name}").launches()
     return total + importlib.import_module("cloud_b200.parallel.comm").launches()
 

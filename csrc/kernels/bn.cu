@@ -146,6 +146,39 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ sums, i
   bn_block_reduce_to_global(s, q, m, C, sums);
 }
 
+// g = (dy (+ dy2)) where the saved sign bit is set, else 0; sums[0:C] += sum_m g.  The masked
+// gradient of a BN + shortcut + ReLU output in the form the folded 1x1-convolution backward
+// (convbn_tcgen05.cu) takes it: as a GEMM operand, with its column sums already reduced.
+__global__ void __launch_bounds__(kBnThreads)
+bn_mask_grad_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dy2,
+                    const uint8_t* __restrict__ mask, __nv_bfloat16* __restrict__ g,
+                    float* __restrict__ sums, int M, int C) {
+  const BnMap m = bn_map(C);
+  float s[8], q[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
+  for (int row = m.row0; row < M; row += m.stride) {
+    const size_t i = static_cast<size_t>(row) * C + m.c8;
+    Vec8 v = unpack8_bf16(ld_stream_v4(dy + i));
+    if (dy2) {
+      const Vec8 w = unpack8_bf16(ld_stream_v4(dy2 + i));
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v.v[j] += w.v[j];
+    }
+    const uint32_t bits = mask ? mask[static_cast<size_t>(row) * (C >> 3) + (m.c8 >> 3)] : 0xffu;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (!((bits >> j) & 1u)) v.v[j] = 0.f;
+    }
+    const uint4 packed = pack8_bf16(v);
+    const Vec8 r = unpack8_bf16(packed);          // sums of what the GEMMs will read
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s[j] += r.v[j];
+    *reinterpret_cast<uint4*>(g + i) = packed;
+  }
+  bn_block_reduce_to_global(s, q, m, C, sums);
+}
+
 // One bit per channel: output > 0.  Saved by the forward pass of a BN + shortcut + ReLU so that the
 // backward kernels read one byte per 8 channels instead of the 16 bytes of the saved output.
 __device__ __forceinline__ uint8_t bn_sign_bits(const Vec8& v) {
@@ -461,6 +494,24 @@ using namespace cb2;
 extern "C" int cb2_bn_supported(int C) { return bn_shape_ok(C) ? 1 : 0; }
 
 extern "C" int cb2_bn_scratch_floats(int C) { return kBnCopies * 2 * C; }
+
+extern "C" int cb2_bn_stats(const void* x, float* sums, int M, int C, void* stream) {
+  int rc = bn_check(M, C, "bn_stats");
+  if (rc) return rc;
+  bn_stats_kernel<<<bn_grid(M, C), kBnThreads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const __nv_bfloat16*>(x), sums, M, C);
+  return check_cuda(cudaGetLastError(), "bn_stats launch");
+}
+
+extern "C" int cb2_bn_mask_grad(const void* dy, const void* dy2, const void* mask, void* g, float* sums,
+                                int M, int C, void* stream) {
+  int rc = bn_check(M, C, "bn_mask_grad");
+  if (rc) return rc;
+  bn_mask_grad_kernel<<<bn_grid(M, C, true), kBnThreads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const __nv_bfloat16*>(dy), reinterpret_cast<const __nv_bfloat16*>(dy2),
+      reinterpret_cast<const uint8_t*>(mask), reinterpret_cast<__nv_bfloat16*>(g), sums, M, C);
+  return check_cuda(cudaGetLastError(), "bn_mask_grad launch");
+}
 
 extern "C" int cb2_bn_forward_mask(const void* x, const void* residual, void* y, float* sums,
                                    const float* gamma, const float* beta, float* run_mean,

@@ -29,6 +29,7 @@
 #include <mutex>
 
 #include "common.cuh"
+#include "gemm_host.cuh"
 #include "../../include/cloud_b200_kernels.h"
 
 namespace cb2 {
@@ -80,16 +81,6 @@ struct GemmCfg {
   static constexpr int kSmemBytes =
       kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
-
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
-  uint64_t d = 0;
-  d |= static_cast<uint64_t>((saddr >> 4) & 0x3FFFu);
-  d |= static_cast<uint64_t>(lbo & 0x3FFFu) << 16;
-  d |= static_cast<uint64_t>(sbo & 0x3FFFu) << 32;
-  d |= 1ull << 46;  // descriptor version: Blackwell
-  d |= 2ull << 61;  // SWIZZLE_128B
-  return d;
-}
 
 // Work item -> (m tile, n tile, k-block range).  Consecutive items differ in n (default: CTAs that
 // run together share the A tile) or in m (m_fast: they share the B tile, and one CTA keeps the same
@@ -741,93 +732,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 // ---------------------------------------------------------------------------------------------
 // Host side
 // ---------------------------------------------------------------------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
-                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
-                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn get_encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    void* sym = nullptr;
-    cudaDriverEntryPointQueryResult qres;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) ==
-            cudaSuccess &&
-        qres == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(sym);
-  });
-  // The driver call wants a current context on the calling thread.  A thread that has only ever
-  // been handed device pointers (autograd's backward thread running the first backward of the
-  // process) has none yet: a runtime call binds the primary context (seen as error 201).
-  static thread_local bool bound = false;
-  if (!bound) {
-    cudaFree(nullptr);
-    bound = true;
-  }
-  return fn;
-}
-
-// 2-D tensor map over a row-major [outer, inner] view with row pitch `ld` elements.
-static int make_tmap(CUtensorMap* tm, const void* base, uint64_t inner, uint64_t outer, uint64_t ld,
-                     uint32_t box_inner, uint32_t box_outer, bool f32 = false) {
-  EncodeTiledFn fn = get_encode_fn();
-  if (!fn) {
-    set_last_error("cuTensorMapEncodeTiled entry point not available");
-    return CB2_ERR_CUDA;
-  }
-  cuuint64_t dims[2] = {inner, outer};
-  cuuint64_t strides[1] = {ld * (f32 ? 4 : 2)};
-  cuuint32_t box[2] = {box_inner, box_outer};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(tm, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
-                  const_cast<void*>(base), dims, strides,
-                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) {
-    set_last_error("cuTensorMapEncodeTiled failed (%d): inner=%llu outer=%llu ld=%llu box=%ux%u",
-                   static_cast<int>(r), (unsigned long long)inner, (unsigned long long)outer,
-                   (unsigned long long)ld, box_inner, box_outer);
-    return CB2_ERR_CUDA;
-  }
-  return 0;
-}
-
-// N-d bf16 / fp32 tensor map with explicit byte strides (dims[0] is the contiguous one).
-static int make_tmap_nd(CUtensorMap* tm, const void* base, int rank, const cuuint64_t* dims,
-                        const cuuint64_t* strides_bytes /*[rank-1]*/, const cuuint32_t* box,
-                        bool f32 = false) {
-  EncodeTiledFn fn = get_encode_fn();
-  if (!fn) {
-    set_last_error("cuTensorMapEncodeTiled entry point not available");
-    return CB2_ERR_CUDA;
-  }
-  cuuint32_t estr[5] = {1, 1, 1, 1, 1};
-  CUresult r = fn(tm, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank,
-                  const_cast<void*>(base), dims, strides_bytes, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) {
-    set_last_error("cuTensorMapEncodeTiled (rank %d) failed (%d)", rank, static_cast<int>(r));
-    return CB2_ERR_CUDA;
-  }
-  return 0;
-}
-
 struct DescOverride {
   bool on = false;
   uint32_t a_lbo, a_sbo, b_lbo, b_sbo, a_kadv, b_kadv;
 };
 static DescOverride g_desc_override;
-
-static int num_sms() {
-  static int cached[64] = {0};
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (dev < 0 || dev >= 64) dev = 0;
-  if (!cached[dev]) cudaDeviceGetAttribute(&cached[dev], cudaDevAttrMultiProcessorCount, dev);
-  return cached[dev];
-}
 
 template <int BN, bool A_MN, bool B_MN>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,

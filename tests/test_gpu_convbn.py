@@ -1,0 +1,169 @@
+"""GPU: the folded 1x1-convolution + batch-norm op (ops/convbn.py, csrc/kernels/convbn_*.cu)
+against a plain fp32 PyTorch reference of the same maths - the fused GEMM on its own (two K sources,
+scale / shift, shortcut, ReLU, sign bits in and out, column sums) and the whole layer forward and
+backward, on ragged row counts.  (Reference workload: conv*_block*_3_conv/_3_bn/_add/_out of
+ResNet-50, core/tests/examples/call_run_within_script_with_keras_fit.py:79-83.)"""
+import math
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from cloud_b200 import ops
+from cloud_b200.ops import convbn
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev():
+    return torch.device("cuda", 0)
+
+
+def _bits(t):
+    """[M, N] bool -> packed uint8 [M * N / 8], bit j of a byte = element 8i + j."""
+    b = t.reshape(-1, 8).to(torch.uint8)
+    w = (b * (2 ** torch.arange(8, device=t.device, dtype=torch.uint8))).sum(1).to(torch.uint8)
+    return w.contiguous()
+
+
+def _unbits(b, M, N):
+    w = b.view(-1, 1).to(torch.int32)
+    return ((w >> torch.arange(8, device=b.device, dtype=torch.int32)) & 1).bool().reshape(M, N)
+
+
+@pytest.mark.parametrize("M,N,K1,K2,b_mn", [(300, 256, 64, 0, False), (1000, 512, 128, 0, False),
+                                            (257, 64, 256, 64, True), (4099, 128, 512, 128, True),
+                                            (640, 192, 64, 0, False), (515, 320, 128, 0, True)])
+def test_fused_gemm_matches_fp32_reference(M, N, K1, K2, b_mn):
+    torch.manual_seed(M + N)
+    dev = _dev()
+    a = (torch.randn(M, K1, device=dev) * 0.5).to(torch.bfloat16)
+    b = (torch.randn(N, K1, device=dev) / math.sqrt(K1)).to(torch.bfloat16)
+    want = a.float() @ b.float().t()
+    a2 = b2 = None
+    if K2:
+        a2 = (torch.randn(M, K2, device=dev) * 0.5).to(torch.bfloat16)
+        b2 = (torch.randn(N, K2, device=dev) / math.sqrt(K2)).to(torch.bfloat16)
+        want = want + a2.float() @ b2.float().t()
+    scale = torch.rand(N, device=dev) + 0.5
+    shift = torch.randn(N, device=dev)
+    res = torch.randn(M, N, device=dev).to(torch.bfloat16)
+    keep = torch.rand(M, N, device=dev) > 0.3
+    want = want * scale + shift + res.float()
+    want = torch.where(keep, want, torch.zeros_like(want)).clamp_min(0)
+    out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+    mask_out = torch.zeros(M * N // 8, device=dev, dtype=torch.uint8)
+    stats = torch.zeros(8, 2, N, device=dev)
+    bs = b.t().contiguous() if b_mn else b
+    b2s = None if b2 is None else (b2.t().contiguous() if b_mn else b2)
+    convbn.fused_gemm(a, bs, out, b_mn=b_mn, a2=a2, b2=b2s, scale=scale, shift=shift, residual=res,
+                      relu=True, mask_in=_bits(keep), mask_out=mask_out, colstats=stats)
+    torch.cuda.synchronize()
+    err = (out.float() - want).abs().max().item()
+    assert err <= 2e-2 * max(1.0, want.abs().max().item()), err
+    # sign bits describe what was stored; column sums are those of the stored bf16 values
+    assert torch.equal(_unbits(mask_out, M, N), out > 0)
+    s = stats.sum(0)
+    assert torch.allclose(s[0], out.float().sum(0), rtol=1e-3, atol=1e-2 * math.sqrt(M))
+    assert torch.allclose(s[1], (out.float() ** 2).sum(0), rtol=1e-3, atol=1e-2 * M)
+
+
+def test_fused_gemm_plain_and_bias_only():
+    torch.manual_seed(5)
+    dev = _dev()
+    M, N, K = 777, 128, 192
+    a = torch.randn(M, K, device=dev).to(torch.bfloat16)
+    b = (torch.randn(N, K, device=dev) / math.sqrt(K)).to(torch.bfloat16)
+    out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+    convbn.fused_gemm(a, b, out)
+    want = a.float() @ b.float().t()
+    assert (out.float() - want).abs().max().item() <= 2e-2 * want.abs().max().item()
+    bias = torch.randn(N, device=dev)
+    convbn.fused_gemm(a, b, out, shift=bias)
+    assert (out.float() - (want + bias)).abs().max().item() <= 2e-2 * (want + bias).abs().max().item()
+
+
+def _layer(n, cin, cout, hw, relu, with_res, seed):
+    torch.manual_seed(seed)
+    dev = _dev()
+    x = (torch.randn(n, cin, hw, hw, device=dev).relu() * 0.7 + 0.05).to(torch.bfloat16) \
+        .contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    w = (torch.randn(cout, cin, 1, 1, device=dev) / math.sqrt(cin)).to(torch.bfloat16) \
+        .contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    gamma = (torch.rand(cout, device=dev) + 0.5).requires_grad_(True)
+    beta = (torch.randn(cout, device=dev) * 0.2).requires_grad_(True)
+    res = None
+    if with_res:
+        res = torch.randn(n, cout, hw, hw, device=dev).to(torch.bfloat16) \
+            .contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    return x, w, gamma, beta, res
+
+
+@pytest.mark.parametrize("n,cin,cout,hw,relu,with_res", [(3, 64, 256, 14, True, True), (2, 128, 512, 9, True, True),
+                                                          (5, 64, 128, 7, False, False), (2, 256, 1024, 7, True, False),
+                                                          (1, 512, 2048, 5, True, True)])
+def test_conv1x1_bn_forward_backward_matches_fp32_reference(n, cin, cout, hw, relu, with_res):
+    x, w, gamma, beta, res = _layer(n, cin, cout, hw, relu, with_res, seed=cin + hw)
+    eps, mom = 1.001e-5, 0.01
+    rm, rv = torch.zeros(cout, device=_dev()), torch.ones(cout, device=_dev())
+    z = ops.conv1x1_bn(x, w, gamma, beta, rm, rv, mom, eps, relu=relu, residual=res)
+    # fp32 oracle on the same bf16-rounded inputs
+    xr, wr = x.detach().float().requires_grad_(True), w.detach().float().requires_grad_(True)
+    gr, br = gamma.detach().clone().requires_grad_(True), beta.detach().clone().requires_grad_(True)
+    rr = None if res is None else res.detach().float().requires_grad_(True)
+    y = F.conv2d(xr, wr)
+    rm_ref, rv_ref = torch.zeros(cout, device=_dev()), torch.ones(cout, device=_dev())
+    zr = F.batch_norm(y, rm_ref, rv_ref, gr, br, True, mom, eps)
+    if rr is not None:
+        zr = zr + rr
+    if relu:
+        zr = torch.relu(zr)
+    assert z.shape == zr.shape
+    tol = 3e-2 * max(1.0, zr.abs().max().item())
+    assert (z.float() - zr).abs().max().item() <= tol
+    assert torch.allclose(rm, rm_ref, atol=1e-3, rtol=1e-2) and torch.allclose(rv, rv_ref, atol=1e-3, rtol=2e-2)
+    # backward: the same upstream gradient through both (masked by each side's own ReLU)
+    dz = torch.randn_like(zr).to(torch.bfloat16)
+    z.backward(dz)
+    zr.backward(dz.float())
+
+    def close(a, b, what, rel=4e-2):
+        scale_ = max(b.abs().max().item(), 1e-3)
+        err = (a.float() - b).abs().max().item()
+        assert err <= rel * scale_, f"{what}: max err {err} vs scale {scale_}"
+    close(x.grad, xr.grad, "dx")
+    close(w.grad, wr.grad, "dw")
+    close(gamma.grad, gr.grad, "dgamma")
+    close(beta.grad, br.grad, "dbeta")
+    if res is not None:
+        close(res.grad, rr.grad, "dres")
+
+
+def test_resnet_bottleneck_trains_the_same_with_and_without_folding(monkeypatch):
+    """Two steps of a small bottleneck stack through the Keras front end, folded vs unfolded."""
+    import cloud_b200 as tfc
+    keras = tfc.keras
+    L = keras.layers
+    from cloud_b200.keras.applications import _bottleneck
+    losses = {}
+    for fold in ("1", "0"):
+        monkeypatch.setenv("TFC_BN_FOLD", fold)
+        tfc.distribute.experimental_set_strategy(tfc.distribute.OneDeviceStrategy("cuda:0"))
+        keras.backend.clear_session()
+        torch.manual_seed(11)
+        inp = keras.Input(shape=(16, 16, 64))
+        x = _bottleneck(inp, 64, 1, True, "conv2_block1")
+        x = _bottleneck(x, 64, 1, False, "conv2_block2")
+        x = L.GlobalAveragePooling2D()(x)
+        out = L.Dense(10, activation="softmax")(x)
+        m = keras.Model(inp, out)
+        m.compile(optimizer=keras.optimizers.SGD(0.05), loss="sparse_categorical_crossentropy", run_eagerly=True)
+        rng = np.random.RandomState(0)
+        xs = rng.rand(32, 16, 16, 64).astype("float32")
+        ys = rng.randint(0, 10, 32)
+        h = m.fit(xs, ys, batch_size=16, epochs=3, shuffle=False, verbose=0)
+        losses[fold] = h.history["loss"]
+    assert all(np.isfinite(v) for v in losses["1"])
+    assert abs(losses["1"][0] - losses["0"][0]) < 0.05, losses
+    assert abs(losses["1"][-1] - losses["0"][-1]) < 0.15, losses
