@@ -12,12 +12,19 @@ import sys
 
 import torch
 
+os.environ.setdefault("TFC_BN_FOLD_MIN_MB", "0")
+
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from cloud_b200 import ops  # noqa: E402
 from cloud_b200.ops import bn as bn_ops  # noqa: E402
 
 
-def timed(fn, iters=10, warm=3):
+ITERS, WARM = 10, 3
+
+
+def timed(fn, iters=None, warm=None):
+    iters = iters or ITERS
+    warm = WARM if warm is None else warm
     for _ in range(warm):
         fn()
     torch.cuda.synchronize()
@@ -34,11 +41,18 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--out", default="gpurun_out/convbn_probe.json")
+    ap.add_argument("--iters", type=int, default=10)
+    ap.add_argument("--warm", type=int, default=3)
+    ap.add_argument("--only", default="", help="comma list of hw values")
     args = ap.parse_args()
+    global ITERS, WARM
+    ITERS, WARM = args.iters, args.warm
     dev = torch.device("cuda", 0)
     bn_ops.arm_scratch(dev)
     rows = []
     for hw, cin in ((56, 64), (28, 128), (14, 256), (7, 512)):
+        if args.only and str(hw) not in args.only.split(","):
+            continue
         cout = 4 * cin
         n = args.batch
         M = n * hw * hw

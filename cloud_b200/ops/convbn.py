@@ -55,7 +55,7 @@ def _k():
                                                 i, i, i, f, f, vp]
         lib.cb2_convbn_bwd_finalize.restype = i
         lib.cb2_convbn_bwd_finalize.argtypes = [vp, i, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, vp, i, vp, vp,
-                                                vp, vp, i, i, i, vp]
+                                                vp, i, i, i, vp]
         lib.cb2_bn_stats.restype = i
         lib.cb2_bn_stats.argtypes = [vp, vp, i, i, vp]
         lib.cb2_bn_mask_grad.restype = i
@@ -78,6 +78,12 @@ def supported(x: torch.Tensor, w: torch.Tensor, stride, padding, dilation) -> bo
     if padding not in (0, (0, 0), "valid"):
         return False
     cin, cout = x.shape[1], w.shape[0]
+    # it pays where the convolution output would not stay in the 126 MB L2 between the kernels that
+    # touch it; smaller outputs are cheaper through the separate batch-norm kernels (measured,
+    # bench/convbn_probe.py)
+    out_mb = x.shape[0] * x.shape[2] * x.shape[3] * cout * 2 / 1e6
+    if out_mb < float(os.environ.get("TFC_BN_FOLD_MIN_MB", "150")):
+        return False
     return (cin % 64 == 0 and 64 <= cin <= 1024 and cout % 64 == 0 and cout >= 2 * cin
             and x.is_contiguous(memory_format=torch.channels_last) and w.is_contiguous(
                 memory_format=torch.channels_last))
@@ -199,19 +205,18 @@ class _ConvBnFn(torch.autograd.Function):
             dbeta = torch.zeros(cout, dtype=torch.float32, device=dev)
         direct_w = getattr(wparam, "_cb2_direct_grad", False) and wparam.grad is not None
         dW = wparam.grad.view(cout, cin) if direct_w else torch.zeros((cout, cin), dtype=torch.bfloat16, device=dev)
-        Ws = torch.empty((cout, cin), dtype=torch.bfloat16, device=dev)
-        Qn = torch.empty((cin, cin), dtype=torch.bfloat16, device=dev)
-        nbias = torch.empty(cin, dtype=torch.float32, device=dev)
-        coef = torch.empty(2 * cout, dtype=torch.float32, device=dev)
+        Wst = torch.empty((2, cout, cin), dtype=torch.bfloat16, device=dev)
+        Ws, Wt = Wst[0], Wst[1]
+        nbias = _bn._scratch(cin, dev)                       # accumulated into: starts at zero
         rc = lib.cb2_convbn_bwd_finalize(P.data_ptr(), cin, gsums.data_ptr(), W2.data_ptr(), cin, U.data_ptr(),
                                          S.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gamma.data_ptr(),
                                          dgamma.data_ptr(), dbeta.data_ptr(), dW.data_ptr(), dW.stride(0),
-                                         Ws.data_ptr(), Qn.data_ptr(), nbias.data_ptr(), coef.data_ptr(),
-                                         cout, cin, M, _stream())
+                                         Ws.data_ptr(), Wt.data_ptr(), nbias.data_ptr(), cout, cin, M, _stream())
         _lib.check(rc, "convbn_bwd_finalize")
-        _launches += 4
+        _launches += 3
         dx = None
         if ctx.needs_input_grad[0]:
+            Qn = _dense.gemm(Wt, W2, a_mn=True, b_mn=True)    # -(W^T diag(t) W), [cin, cin]
             dxm = torch.empty((n, h, wd, cin), dtype=torch.bfloat16, device=dev)
             fused_gemm(G, Ws, dxm.view(M, cin), b_mn=True, a2=X, b2=Qn, shift=nbias)
             dx = dxm.permute(0, 3, 1, 2)

@@ -38,7 +38,7 @@ constexpr int kFAStage = FBM * FBK * 2;     // 16 KiB
 constexpr int kResSlot = FBM * 128;         // 128 rows x 64 bf16
 constexpr int kFStatCopies = 8;             // = kColStatCopies / kBnCopies
 constexpr int kMaxStages = 8;
-constexpr int kMaxRing = 4;
+constexpr int kMaxRing = 8;
 
 struct FusedArgs {
   int M, N;
@@ -228,6 +228,7 @@ convbn_gemm_kernel(const __grid_constant__ FusedMaps tm, const FusedArgs p) {
     const bool has_scale = p.scale != nullptr, has_shift = p.shift != nullptr;
     const bool affine = has_scale || has_shift;
     const bool relu = p.relu != 0;
+    const bool has_min = p.mask_in != nullptr, has_mout = p.mask_out != nullptr;
     const int words_per_row = p.N >> 5;
     int stage_buf = 0;
     int par_n0 = -1;
@@ -328,12 +329,19 @@ convbn_gemm_kernel(const __grid_constant__ FusedMaps tm, const FusedArgs p) {
                 f[0] += bf16_lo(r0); f[1] += bf16_hi(r0); f[2] += bf16_lo(r1); f[3] += bf16_hi(r1);
                 f[4] += bf16_lo(r2); f[5] += bf16_hi(r2); f[6] += bf16_lo(r3); f[7] += bf16_hi(r3);
               }
-              const uint32_t mb = mi >> (g * 8);
+              if (has_min) {
+                const uint32_t mb = mi >> (g * 8);
 #pragma unroll
-              for (int e = 0; e < 8; ++e) {
-                if (!((mb >> e) & 1u)) f[e] = 0.f;
-                if (relu) f[e] = fmaxf(f[e], 0.f);
-                mo |= (f[e] > 0.f ? 1u : 0u) << (g * 8 + e);
+                for (int e = 0; e < 8; ++e)
+                  if (!((mb >> e) & 1u)) f[e] = 0.f;
+              }
+              if (relu) {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
+              }
+              if (has_mout) {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) mo |= (f[e] > 0.f ? 1u : 0u) << (g * 8 + e);
               }
               st_shared_v4(rowp + (((h * 4 + g) ^ sw) << 4), pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]),
                            pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
@@ -430,6 +438,13 @@ static int launch_fused(const FusedMaps& maps, FusedArgs& args, cudaStream_t str
     return CB2_ERR_UNSUPPORTED;
   }
   args.stages = stages;
+  if (args.ring > 0) {
+    // the shortcut tiles are the largest read of an output-bound GEMM: whatever shared memory the
+    // operand pipeline leaves goes into their ring (bytes in flight = bandwidth x latency)
+    int ring = (232448 - Cfg::smem_bytes(stages, 0)) / kResSlot;
+    if (ring > kMaxRing) ring = kMaxRing;
+    if (ring > args.ring) args.ring = ring;
+  }
   const int tiles = args.m_tiles * args.n_tiles;
   const int grid = tiles < num_sms() ? tiles : num_sms();
   kern<<<grid, kFusedThreads, Cfg::smem_bytes(stages, args.ring), stream>>>(maps, args);
@@ -468,14 +483,14 @@ extern "C" int cb2_convbn_gemm(const void* A, int lda, const void* B, int ldb, i
   const int m_tiles = (M + FBM - 1) / FBM;
   int bn = block_n;
   if (bn == 0) {
-    // fewest waves x tile width; ties go to the wider tile (fewer operand re-reads)
+    // the widest tile (fewest operand re-reads, best MMA shape) that keeps the waves full
     const int sms = num_sms();
-    long best = -1;
-    for (int cand : {256, 128, 64}) {
-      if (cand > N && cand != 64) continue;
+    bn = 64;
+    for (int cand : {256, 128}) {
+      if (cand > N) continue;
       const long tiles = static_cast<long>(m_tiles) * ((N + cand - 1) / cand);
-      const long cost = ((tiles + sms - 1) / sms) * cand;
-      if (best < 0 || cost < best) { best = cost; bn = cand; }
+      const long waves = (tiles + sms - 1) / sms;
+      if (tiles * 100 >= waves * sms * 80) { bn = cand; break; }    // >= 80 % of the slots do work
     }
   }
   if (bn != 64 && bn != 128 && bn != 256) {

@@ -16,6 +16,11 @@ from cloud_b200.ops import convbn
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True)
+def _fold_everything(monkeypatch):
+    monkeypatch.setenv("TFC_BN_FOLD_MIN_MB", "0")       # the size threshold is a tuning knob, not a limit
+
+
 def _dev():
     return torch.device("cuda", 0)
 
