@@ -23,8 +23,14 @@ def main():
         unit = r.get("Metric Unit", "ns")
         scale = {"ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6}.get(unit, 1e-3)
         rows.append((r["Kernel Name"], val * scale))
-    n = len(rows) // args.steps
-    last = rows[-n:] if n else rows
+    # one step = from the last `optim_tick` launch (the first kernel of a step) to the end; without
+    # that marker, the last of `--steps` equal slices
+    ticks = [i for i, (name, _us) in enumerate(rows) if "optim_tick" in name]
+    if len(ticks) >= 2:
+        last = rows[ticks[-1]:]
+    else:
+        n = len(rows) // args.steps
+        last = rows[-n:] if n else rows
     agg = collections.defaultdict(lambda: [0.0, 0])
     for name, us in last:
         short = re.sub(r"<.*", "", name)[:70]

@@ -25,6 +25,8 @@ _CONV1X1_GEMM = ops.conv1x1_mode() != "0"
 # k x k weight gradients on the tcgen05 shifted-box kernel: correct but slower than cuDNN's sm_100
 # kernels on the 3x3 shapes of ResNet-50 (256 vs 110 us at 56x56x64, batch 256), so opt-in
 _CONV_KXK = os.environ.get("TFC_CONV_KXK_WGRAD", "0") == "1"
+# strided 1x1 convolutions as a subsample + a plain 1x1 convolution (ops.subsample); 0: leave the stride to cuDNN
+_STRIDED_1X1 = os.environ.get("TFC_STRIDED_1X1", "1") != "0"
 
 _NAME_COUNTS: dict[str, int] = {}
 
@@ -516,28 +518,34 @@ class Conv2D(Layer):
         w = self.kernel
         if w.dtype != x.dtype:
             x = x.to(w.dtype)
+        strides = self.strides
+        if (_STRIDED_1X1 and self.kernel_size == (1, 1) and strides[0] == strides[1] and strides[0] > 1
+                and pad in (0, (0, 0)) and x.is_cuda and x.dim() == 4 and self.dilation == (1, 1)):
+            x = ops.subsample(x, strides[0])        # a strided 1x1 convolution reads every s-th pixel
+            strides = (1, 1)
         if (training and self.fold_candidate and (self.bias_absorbed_by_bn or self.bias is None)
                 and self.activation_name in (None, "linear") and torch.is_grad_enabled()
-                and ops.convbn_supported(x, w, self.strides, pad, self.dilation)):
+                and ops.convbn_supported(x, w, strides, pad, self.dilation)):
             return ops.DeferredConv(x, w, self, pad)
-        return self._plain_conv(x, training, pad)
+        return self._plain_conv(x, training, pad, strides)
 
-    def _plain_conv(self, x, training=True, pad=0):
+    def _plain_conv(self, x, training=True, pad=0, strides=None):
+        strides = self.strides if strides is None else strides
         w = self.kernel
         b = self.bias
         if b is not None and self.bias_absorbed_by_bn and training:
             b = None
         if b is not None and b.dtype != x.dtype:
             b = b.to(x.dtype)
-        if _CONV1X1_GEMM and ops.stem_supported(x, w, self.strides, pad, self.dilation):
+        if _CONV1X1_GEMM and ops.stem_supported(x, w, strides, pad, self.dilation):
             y = ops.stem_conv(x, w, b)
-        elif _CONV1X1_GEMM and _CONV_KXK and ops.kxk_supported(x, w, self.strides, pad, self.dilation):
+        elif _CONV1X1_GEMM and _CONV_KXK and ops.kxk_supported(x, w, strides, pad, self.dilation):
             y = ops.conv_kxk(x, w, b)
-        elif _CONV1X1_GEMM and ops.conv1x1_supported(x, w, self.strides, pad, self.dilation):
+        elif _CONV1X1_GEMM and ops.conv1x1_supported(x, w, strides, pad, self.dilation):
             y = ops.conv1x1(x, w, b, bn_stats=bool(training) and self.feeds_bn and
                             self.activation_name in (None, "linear"))
         else:
-            y = F.conv2d(x, w, b, stride=self.strides, padding=pad, dilation=self.dilation)
+            y = F.conv2d(x, w, b, stride=strides, padding=pad, dilation=self.dilation)
         if self.activation_name == "relu":
             return torch.relu_(y)
         return y if self._activation_fn is None else self._activation_fn(y)

@@ -239,6 +239,9 @@ class _ForkFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, a, mailbox):
         ctx.mailbox = mailbox
+        # a handle nobody differentiates through must arrive as None in backward, not as a
+        # zero-filled tensor of the activation's size (in the default, non channels_last layout)
+        ctx.set_materialize_grads(False)
         return a.view_as(a), a.view_as(a)
 
     @staticmethod
@@ -257,4 +260,8 @@ def fork(a: torch.Tensor):
     mb = getattr(a, "_cb2_mailbox", None)
     if mb is None or not a.requires_grad:
         return a, a
-    return _ForkFn.apply(a, mb)
+    h1, h2 = _ForkFn.apply(a, mb)
+    # one dictionary behind both handles: work derived from the tensor (its stride-2 subsample, read
+    # by the two strided 1x1 convolutions of a stage's first block) is done once
+    h1._cb2_shared = h2._cb2_shared = {}
+    return h1, h2

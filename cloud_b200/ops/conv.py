@@ -20,6 +20,8 @@ reference leaves these to cuDNN / cuBLAS inside TensorFlow.
 """
 from __future__ import annotations
 
+import ctypes
+
 import torch
 import torch.nn.functional as F
 
@@ -262,3 +264,66 @@ class _ConvKxKFn(torch.autograd.Function):
 def conv_kxk(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None) -> torch.Tensor:
     """k x k / stride-1 / 'same' convolution of a channels_last bf16 tensor."""
     return _ConvKxKFn.apply(x, w, bias)
+
+
+# ----------------------------------------------------------------------------------------------
+# Strided 1x1 convolutions = a 1x1 convolution of every s-th pixel
+# ----------------------------------------------------------------------------------------------
+def _subsample_kernel(src, dst, b, h, w, c, s, backward):
+    lib = _dense._lib.kernels()
+    lib.cb2_subsample_nhwc.restype = ctypes.c_int
+    lib.cb2_subsample_nhwc.argtypes = [ctypes.c_void_p, ctypes.c_void_p] + [ctypes.c_int] * 6 + [ctypes.c_void_p]
+    rc = lib.cb2_subsample_nhwc(src.data_ptr(), dst.data_ptr(), b, h, w, c, s, int(backward), _dense._stream())
+    _dense._lib.check(rc, "subsample_nhwc")
+    _dense._launches += 1
+
+
+class _SubsampleFn(torch.autograd.Function):
+    """``x[:, :, ::s, ::s]`` as a dense channels_last tensor; backward writes the full-size gradient
+    in one pass (zeros between the sampled pixels), channels_last like everything around it."""
+
+    @staticmethod
+    def forward(ctx, x, s):
+        ctx.shape, ctx.s = tuple(x.shape), s
+        b, c, h, w = x.shape
+        fast = (x.is_cuda and x.dtype == torch.bfloat16 and c % 8 == 0
+                and x.is_contiguous(memory_format=torch.channels_last))
+        ctx.fast = fast
+        if not fast:
+            return x[:, :, ::s, ::s].contiguous(memory_format=torch.channels_last)
+        y = torch.empty((b, c, -(-h // s), -(-w // s)), dtype=x.dtype, device=x.device,
+                        memory_format=torch.channels_last)
+        _subsample_kernel(x, y, b, h, w, c, s, False)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        b, c, h, w = ctx.shape
+        s = ctx.s
+        dx = torch.empty(ctx.shape, dtype=g.dtype, device=g.device, memory_format=torch.channels_last)
+        if ctx.fast and g.dtype == torch.bfloat16:
+            if not g.is_contiguous(memory_format=torch.channels_last):
+                g = g.contiguous(memory_format=torch.channels_last)
+            _subsample_kernel(g, dx, b, h, w, c, s, True)
+        else:
+            dx.zero_()
+            dx[:, :, ::s, ::s].copy_(g)
+        return dx, None
+
+
+def subsample(x: torch.Tensor, s: int) -> torch.Tensor:
+    """Every ``s``-th pixel of a channels_last tensor, computed once per tensor: the two strided 1x1
+    convolutions at the head of a ResNet stage (``*_0_conv`` and ``*_1_conv``) then run as plain
+    GEMMs on a quarter of the rows, and their input gradients meet in ONE scatter instead of two
+    strided-dgrad kernels over the full-resolution tensor."""
+    shared = getattr(x, "_cb2_shared", None)
+    if shared is None:
+        shared = {}
+        try:
+            x._cb2_shared = shared
+        except AttributeError:
+            pass
+    key = ("sub", s)
+    if key not in shared:
+        shared[key] = _SubsampleFn.apply(x, s)
+    return shared[key]

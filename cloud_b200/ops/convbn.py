@@ -36,6 +36,7 @@ _dense = importlib.import_module(__package__ + ".dense")     # the module (ops.d
 
 _declared = False
 _launches = 0
+_colsums: dict = {}      # data_ptr of a masked gradient -> its column sums, for the next backward in line
 
 
 def launches() -> int:
@@ -182,10 +183,12 @@ class _ConvBnFn(torch.autograd.Function):
             dz = dz + dz2
             dz2 = None
         # g = masked gradient (+ second consumer's gradient), with its column sums
-        gsums = _bn._scratch(lib.cb2_bn_scratch_floats(cout), dev)
+        cached = _colsums.pop(dz.data_ptr(), None) if (mask is None and dz2 is None) else None
+        gsums = cached if cached is not None else _bn._scratch(lib.cb2_bn_scratch_floats(cout), dev)
         if mask is None and dz2 is None:
             G = _as_matrix(dz)
-            _lib.check(lib.cb2_bn_stats(G.data_ptr(), gsums.data_ptr(), M, cout, _stream()), "bn_stats")
+            if cached is None:
+                _lib.check(lib.cb2_bn_stats(G.data_ptr(), gsums.data_ptr(), M, cout, _stream()), "bn_stats")
         else:
             g4 = torch.empty_like(dz)
             G = _as_matrix(g4)
@@ -223,6 +226,10 @@ class _ConvBnFn(torch.autograd.Function):
         dres = None
         if ctx.has_res:
             dres = G.view(n, h, wd, cout).permute(0, 3, 1, 2)
+            # the shortcut may itself be a folded convolution (the first block of a stage): its
+            # backward needs the column sums of exactly this tensor - already reduced above
+            _colsums.clear()
+            _colsums[G.data_ptr()] = gsums
         dw = dg = db = None
         if direct_w:
             wparam._cb2_grad_written(wparam)
@@ -264,4 +271,4 @@ class DeferredConv:
         self.x, self.w, self.layer, self.pad = x, w, layer, pad
 
     def materialize(self):
-        return self.layer._plain_conv(self.x, True, self.pad)
+        return self.layer._plain_conv(self.x, True, self.pad, (1, 1))

@@ -2,6 +2,7 @@
 // ReLU-backward + bias-gradient, Philox dropout, uint8->bf16 input normalisation and the flat
 // multi-optimizer update.  All are single-pass, 16-byte vectorised where the layout allows, with
 // grids sized against the 148 SMs.
+#include <algorithm>
 #include <stdarg.h>
 #include <stdio.h>
 
@@ -460,6 +461,70 @@ extern "C" int cb2_u8_to_s2d_bf16(const uint8_t* in, void* out, int B, int H, in
       in, reinterpret_cast<__nv_bfloat16*>(out), B, H, W, mean3[0], mean3[1], mean3[2], inv_std3[0],
       inv_std3[1], inv_std3[2]);
   return check_cuda(cudaGetLastError(), "u8_to_s2d_bf16 launch");
+}
+
+// ---------------------------------------------------------------------------------------------
+// Every s-th pixel of an NHWC tensor (the input of a strided 1x1 convolution) and its adjoint.
+// 16-byte vectors; the adjoint writes the whole gradient in one pass (zeros where no pixel was read)
+// instead of a memset followed by a strided copy.
+// ---------------------------------------------------------------------------------------------
+namespace cb2 {
+__global__ void __launch_bounds__(256)
+subsample_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, int H, int W, int C8, int OH,
+                     int OW, int s, size_t total) {
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % C8);
+    size_t p = i / C8;
+    const int ow = static_cast<int>(p % OW);
+    p /= OW;
+    const int oh = static_cast<int>(p % OH);
+    const size_t b = p / OH;
+    y[i] = ld_stream_v4(x + ((b * H + static_cast<size_t>(oh) * s) * W + static_cast<size_t>(ow) * s) * C8 + c);
+  }
+}
+__global__ void __launch_bounds__(256)
+subsample_bwd_kernel(const uint4* __restrict__ g, uint4* __restrict__ dx, int H, int W, int C8, int OH,
+                     int OW, int s, size_t total) {
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % C8);
+    size_t p = i / C8;
+    const int w = static_cast<int>(p % W);
+    p /= W;
+    const int h = static_cast<int>(p % H);
+    const size_t b = p / H;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (h % s == 0 && w % s == 0)
+      v = ld_stream_v4(g + ((b * OH + h / s) * OW + w / s) * C8 + c);
+    dx[i] = v;
+  }
+}
+}  // namespace cb2
+
+extern "C" int cb2_subsample_nhwc(const void* x, void* y, int B, int H, int W, int C, int s, int backward,
+                                  void* stream) {
+  if (B <= 0 || H <= 0 || W <= 0 || C <= 0 || (C & 7) || s < 1 ||
+      (reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(y) & 15)) {
+    cb2::set_last_error("subsample_nhwc: need C %% 8 == 0 and 16-byte aligned tensors (B=%d H=%d W=%d C=%d s=%d)",
+                        B, H, W, C, s);
+    return CB2_ERR_ARG;
+  }
+  const int OH = (H + s - 1) / s, OW = (W + s - 1) / s, C8 = C / 8;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (!backward) {
+    const size_t total = static_cast<size_t>(B) * OH * OW * C8;
+    const int grid = static_cast<int>(std::min<size_t>((total + 255) / 256, 148 * 16));
+    cb2::subsample_fwd_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const uint4*>(x),
+                                                    reinterpret_cast<uint4*>(y), H, W, C8, OH, OW, s, total);
+  } else {
+    // x = the gradient of the subsampled tensor [B, OH, OW, C], y = the full gradient [B, H, W, C]
+    const size_t total = static_cast<size_t>(B) * H * W * C8;
+    const int grid = static_cast<int>(std::min<size_t>((total + 255) / 256, 148 * 16));
+    cb2::subsample_bwd_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const uint4*>(x),
+                                                    reinterpret_cast<uint4*>(y), H, W, C8, OH, OW, s, total);
+  }
+  return cb2::check_cuda(cudaGetLastError(), "subsample_nhwc launch");
 }
 
 extern "C" int cb2_optim_tick(float* hyper, void* stream) {

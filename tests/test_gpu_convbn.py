@@ -172,3 +172,34 @@ def test_resnet_bottleneck_trains_the_same_with_and_without_folding(monkeypatch)
     assert all(np.isfinite(v) for v in losses["1"])
     assert abs(losses["1"][0] - losses["0"][0]) < 0.05, losses
     assert abs(losses["1"][-1] - losses["0"][-1]) < 0.15, losses
+
+
+def test_strided_1x1_convolutions_share_one_subsample_and_match_cudnn():
+    """The head of a ResNet stage: two stride-2 1x1 convolutions of one tensor, run as GEMMs on a
+    shared subsample, against F.conv2d with the stride - values and all three gradients."""
+    import cloud_b200 as tfc
+    L = tfc.keras.layers
+    torch.manual_seed(2)
+    dev = _dev()
+    x = torch.randn(3, 64, 10, 10, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last) \
+        .requires_grad_(True)
+    a, b = L.Conv2D(128, 1, strides=2, use_bias=False), L.Conv2D(32, 1, strides=2, use_bias=False)
+    for layer in (a, b):
+        layer._maybe_build((None, 10, 10, 64))
+        layer.to(dev)
+        layer.kernel.data = layer.kernel.data.to(torch.bfloat16)
+    ya, yb = a.call(x, training=True), b.call(x, training=True)
+    assert ya.shape == (3, 128, 5, 5) and yb.shape == (3, 32, 5, 5)
+    assert len(x._cb2_shared) == 1                                   # one subsample for both
+    xr = x.detach().float().requires_grad_(True)
+    wa, wb = a.kernel.detach().float().requires_grad_(True), b.kernel.detach().float().requires_grad_(True)
+    ra, rb = F.conv2d(xr, wa, stride=2), F.conv2d(xr, wb, stride=2)
+    assert (ya.float() - ra).abs().max().item() < 3e-2 * ra.abs().max().item()
+    assert (yb.float() - rb).abs().max().item() < 3e-2 * rb.abs().max().item()
+    ga, gb = torch.randn_like(ra), torch.randn_like(rb)
+    (ya.float() * ga).sum().backward(retain_graph=True)
+    (yb.float() * gb).sum().backward()
+    ((ra * ga).sum() + (rb * gb).sum()).backward()
+    assert x.grad.is_contiguous(memory_format=torch.channels_last)
+    for got, want in ((x.grad, xr.grad), (a.kernel.grad, wa.grad), (b.kernel.grad, wb.grad)):
+        assert (got.float() - want).abs().max().item() < 4e-2 * want.abs().max().item()
