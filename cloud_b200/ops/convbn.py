@@ -183,7 +183,7 @@ class _ConvBnFn(torch.autograd.Function):
             dz = dz + dz2
             dz2 = None
         # g = masked gradient (+ second consumer's gradient), with its column sums
-        cached = _colsums.pop(dz.data_ptr(), None) if (mask is None and dz2 is None) else None
+        cached = _colsums.pop((dz.data_ptr(), M, cout), None) if (mask is None and dz2 is None) else None
         gsums = cached if cached is not None else _bn._scratch(lib.cb2_bn_scratch_floats(cout), dev)
         if mask is None and dz2 is None:
             G = _as_matrix(dz)
@@ -229,7 +229,7 @@ class _ConvBnFn(torch.autograd.Function):
             # the shortcut may itself be a folded convolution (the first block of a stage): its
             # backward needs the column sums of exactly this tensor - already reduced above
             _colsums.clear()
-            _colsums[G.data_ptr()] = gsums
+            _colsums[(G.data_ptr(), M, cout)] = gsums
         dw = dg = db = None
         if direct_w:
             wparam._cb2_grad_written(wparam)
