@@ -156,7 +156,7 @@ def main() -> int:
     ap.add_argument("--classes", type=int, default=1000)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-baseline", action="store_true", help="skip the in-run torch DDP+NCCL arm")
-    ap.add_argument("--baseline-variants", default=os.environ.get("TFC_BENCH_BASELINE", "eager,graph"),
+    ap.add_argument("--baseline-variants", default=os.environ.get("TFC_BENCH_BASELINE", "eager,graph,compile"),
                     help="comma list of eager, graph, compile")
     ap.add_argument("--no-small-batch", action="store_true")
     ap.add_argument("--no-allreduce", action="store_true")
@@ -196,6 +196,7 @@ def main() -> int:
 
     import cloud_b200 as tfc
     from cloud_b200 import ops
+    from cloud_b200.parallel.comm import ALGO_LABELS as C_LABELS
     keras = tfc.keras
     strategy = tfc.distribute.MirroredStrategy() if world > 1 else tfc.distribute.OneDeviceStrategy("cuda:0")
     tfc.distribute.experimental_set_strategy(strategy)
@@ -277,7 +278,8 @@ def main() -> int:
     note(f"cloud_b200: {value:.0f} img/s ({ms:.2f} ms/step)")
     eng = model._engine
     cfg_comm = {"comm_backend": eng.comm.backend,
-                "allreduce_algos": sorted({a for g in eng.groups for a in getattr(g, "bucket_algos", [g.algo])}),
+                "allreduce_algos": sorted({C_LABELS.get(a, str(a)) for g in eng.groups
+                                           for a in getattr(g, "bucket_algos", [g.algo])}),
                 "buckets": [len(g.buckets) for g in eng.groups],
                 "cuda_graph": bool(model._graph and model._graph.get("graph") is not None)}
 
@@ -463,6 +465,9 @@ def allreduce_rows(comm, dev, world, max_bytes):
         algos.append(("twoshot", C.ALGO_TWOSHOT))
         if has_mc:
             algos.append(("nvls", C.ALGO_NVLS))
+        for name, algo in (("ll1", C.ALGO_LL1), ("ll2", C.ALGO_LL2)):
+            if nbytes <= comm.ll_capacity(algo):
+                algos.append((name, algo))
         best = None
         for name, algo in algos:
             def ours(i, algo=algo):
@@ -479,7 +484,7 @@ def allreduce_rows(comm, dev, world, max_bytes):
         row["frac_of_900"] = row["busbw_gbs"] / 900.0
         row["vs_nccl"] = row["busbw_gbs"] / row["nccl_busbw_gbs"]
         # the same schedule fused with Adam + parameter publication + gradient zeroing
-        sharded = best[2] != C.ALGO_ONESHOT
+        sharded = best[2] in C.SHARDED_ALGOS
         n_state = n // world if sharded else n
         if n_state <= state[0].numel():
             def fused(i, algo=best[2]):
@@ -510,6 +515,7 @@ def run_checks(tfc, strategy, dev, world, rank):
     comm = strategy.communicator
     ok = sweep.check(comm, dev, world, rank, results)
     ok = sweep.stress(comm, dev, world, rank, results, iters=24) and ok
+    ok = sweep.stress_ll(comm, dev, world, rank, results, iters=48) and ok
     errs = [r["max_err"] for r in results if "max_err" in r]
     same = all(r.get("replicas_identical", True) for r in results)
 

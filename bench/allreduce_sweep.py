@@ -40,6 +40,9 @@ def check(comm, dev, world, rank, results):
         algos = [("oneshot", C.ALGO_ONESHOT), ("twoshot", C.ALGO_TWOSHOT)]
         if gbuf.mc_ptr and pbuf.mc_ptr:
             algos.append(("nvls", C.ALGO_NVLS))
+        for name, algo in (("ll1", C.ALGO_LL1), ("ll2", C.ALGO_LL2)):
+            if n * item <= comm.ll_capacity(algo):
+                algos.append((name, algo))
         hyper = make_hyper(dev, lr=1e-2, grad_scale=1.0 / world)
         for name, algo in algos:
             # ---- plain reduction -----------------------------------------------------------
@@ -68,7 +71,7 @@ def check(comm, dev, world, rank, results):
                             "grads_zeroed": zeroed, "replicas_identical": same, "ok": ok and same})
             ok_all &= ok and same
             # ---- fused Adam, 3 steps ---------------------------------------------------------
-            sharded = algo != C.ALGO_ONESHOT
+            sharded = algo in C.SHARDED_ALGOS
             n_state = n // world if sharded else n
             master = torch.zeros(n_state, device=dev)
             m = torch.zeros(n_state, device=dev)
@@ -127,6 +130,8 @@ def stress(comm, dev, world, rank, results, iters=48):
     ctx = comm.make_ctx(gbuf, pbuf)
     g_arena, p_arena = gbuf.view(torch.float32, n_max), pbuf.view(torch.float32, n_max)
     algos = [C.ALGO_ONESHOT, C.ALGO_TWOSHOT] + ([C.ALGO_NVLS] if gbuf.mc_ptr and pbuf.mc_ptr else [])
+    if comm.ll_capacity(C.ALGO_LL1) >= n_max * 4:
+        algos += [C.ALGO_LL1, C.ALGO_LL2, C.ALGO_LL1, C.ALGO_LL2]     # back to back: exercises the parities
     hyper = make_hyper(dev, lr=1e-2, grad_scale=1.0 / world)
     rng = random.Random(1234 + 17 * rank)            # different delays on every rank
     lens = [8 * world * k for k in (1, 33, 1027, 8209)]
@@ -148,6 +153,52 @@ def stress(comm, dev, world, rank, results, iters=48):
     dist.all_reduce(t)
     ok = t.item() == 0
     results.append({"check": f"stress/skewed_arrival/{iters}_calls", "bad_calls": int(t.item()), "ok": ok})
+    return ok
+
+
+def stress_ll(comm, dev, world, rank, results, iters=96):
+    """The flag-in-payload schedules have no barrier: consecutive calls are only kept apart by the
+    two receive parities.  ``iters`` LL calls are queued back to back with NO host synchronisation,
+    each rank stalling its stream by different random amounts in between, every call reducing into
+    its own region; all regions are checked at the end."""
+    import random
+    if not comm.ll_capacity(C.ALGO_LL1):
+        return True
+    regions, n = 16, 8 * world * 515
+    total = regions * n
+    gbuf, pbuf = comm.alloc_pair(total * 4, total * 4)
+    ctx = comm.make_ctx(gbuf, pbuf)
+    g_arena, p_arena = gbuf.view(torch.float32, total), pbuf.view(torch.float32, total)
+    hyper = make_hyper(dev, lr=1e-2, grad_scale=1.0)
+    rng = random.Random(99 + 31 * rank)
+    aux_out = torch.zeros(C.AUX_FLOATS, device=dev)
+    aux_seen = []
+    torch.cuda.synchronize()
+    dist.barrier()
+    for it in range(iters):
+        r = it % regions
+        g_arena[r * n:(r + 1) * n].fill_(float((rank + 1) * (it + 1)))
+        comm.aux[:3].fill_(float(rank + it))
+        if rng.random() < 0.5:
+            torch.cuda._sleep(int(rng.random() * 2e6))
+        comm.fused(ctx, algo=C.ALGO_LL1 if it % 3 else C.ALGO_LL2, opt=0, grad_dtype=torch.float32,
+                   param_dtype=torch.float32, off=r * n, length=n, master=None, s1=None, s2=None,
+                   state_off=0, hyper=hyper, zero_grads=True, aux_len=3, aux_out=aux_out)
+        aux_seen.append(aux_out[:3].clone())
+    torch.cuda.synchronize()
+    bad = 0
+    for it in range(iters - regions, iters):
+        r = it % regions
+        want = (it + 1) * world * (world + 1) / 2.0
+        bad += int((p_arena[r * n:(r + 1) * n] - want).abs().max().item() > 1e-4 * want)
+    for it, a in enumerate(aux_seen):
+        want = sum(p + it for p in range(world))
+        bad += int((a - want).abs().max().item() > 1e-3)
+    bad += int(g_arena.abs().max().item() != 0.0) + int(comm.aux[:3].abs().max().item() != 0.0)
+    t = torch.tensor([bad], device=dev, dtype=torch.float32)
+    dist.all_reduce(t)
+    ok = t.item() == 0
+    results.append({"check": f"stress/ll_back_to_back/{iters}_calls", "bad": int(t.item()), "ok": ok})
     return ok
 
 
@@ -195,6 +246,9 @@ def sweep(comm, dev, world, rank, max_bytes, results):
         algos.append(("twoshot", C.ALGO_TWOSHOT))
         if has_mc:
             algos.append(("nvls", C.ALGO_NVLS))
+        for name, algo in (("ll1", C.ALGO_LL1), ("ll2", C.ALGO_LL2)):
+            if nbytes <= comm.ll_capacity(algo):
+                algos.append((name, algo))
         for name, algo in algos:
             def ours(i, algo=algo):
                 off = (i % slots) * n
@@ -206,7 +260,7 @@ def sweep(comm, dev, world, rank, max_bytes, results):
             ms = time_fn(ours, iters, dev)
             row[name + "_us"] = ms * 1e3
             row[name + "_busbw_gbs"] = nbytes / (ms * 1e-3) * 2 * (world - 1) / world / 1e9
-        best = max((row.get(k + "_busbw_gbs", 0.0), k) for k in ("oneshot", "twoshot", "nvls"))
+        best = max((row.get(k + "_busbw_gbs", 0.0), k) for k in ("oneshot", "twoshot", "nvls", "ll1", "ll2"))
         row["best"] = best[1]
         row["best_vs_nccl"] = best[0] / row["nccl_busbw_gbs"] if row["nccl_busbw_gbs"] else None
         row["best_frac_of_900"] = best[0] / 900.0
@@ -234,6 +288,7 @@ def main():
     else:
         ok = check(comm, dev, world, rank, out["checks"])
         ok = stress(comm, dev, world, rank, out["checks"]) and ok
+        ok = stress_ll(comm, dev, world, rank, out["checks"]) and ok
         out["checks_ok"] = bool(ok)
         for c in out["checks"]:
             log(json.dumps(c))

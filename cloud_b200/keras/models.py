@@ -484,7 +484,7 @@ class Model(nn.Module):
     # -- one training step --------------------------------------------------------------------
     def _train_step(self, xb, yb, global_batch=None):
         eng = self._engine
-        eng.begin_step()
+        eng.begin_step(self._aux_len())
         with nvtx_range("forward"):
             out = self.call(xb, training=True)
         if global_batch is None:

@@ -34,6 +34,9 @@ class CommCtx(ctypes.Structure):
         ("mc_grad", ctypes.c_void_p),
         ("mc_param", ctypes.c_void_p),
         ("epochs", ctypes.c_void_p),
+        ("ll_ptrs", ctypes.c_void_p * 8),
+        ("ll_bytes", ctypes.c_size_t),
+        ("ll_state", ctypes.c_void_p),
     ]
 
 

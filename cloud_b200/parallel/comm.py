@@ -33,8 +33,13 @@ COMM_MAX_BLOCKS = 128
 AUX_FLOATS = 256
 PAD_BYTES = COMM_MAX_BLOCKS * MAX_RANKS * 4 + AUX_FLOATS * 4
 
-ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_NVLS = 0, 1, 2
-ALGO_NAMES = {"oneshot": ALGO_ONESHOT, "twoshot": ALGO_TWOSHOT, "nvls": ALGO_NVLS}
+ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_NVLS, ALGO_LL1, ALGO_LL2 = 0, 1, 2, 3, 4
+ALGO_NAMES = {"oneshot": ALGO_ONESHOT, "twoshot": ALGO_TWOSHOT, "nvls": ALGO_NVLS, "ll1": ALGO_LL1,
+              "ll2": ALGO_LL2}
+ALGO_LABELS = {v: k for k, v in ALGO_NAMES.items()}
+SHARDED_ALGOS = (ALGO_TWOSHOT, ALGO_NVLS, ALGO_LL2)       # optimizer state cut across the ranks
+# gradient bytes one LL slot can take: the largest LL1 bucket, and 1/world of the largest LL2 bucket
+LL_SLOT_PAYLOAD = int(os.environ.get("TFC_LL_SLOT_KB", "512")) << 10
 
 _launches = 0
 
@@ -68,6 +73,8 @@ class Communicator:
         self.epochs = None
         self.aux = None            # fp32 view of the aux scalars (local)
         self.multicast = False
+        self.ll = None
+        self.ll_state = None
         if device.type == "cuda" and backend in ("p2p", "local"):
             self._init_symm()
         if backend == "shm":
@@ -104,6 +111,24 @@ class Communicator:
                 return
         self.epochs = torch.zeros(COMM_MAX_BLOCKS, dtype=torch.int32, device=self.device)
         self.aux = self.pad.view(torch.float32, AUX_FLOATS, COMM_MAX_BLOCKS * MAX_RANKS * 4)
+        # receive buffers of the flag-in-payload (LL) schedules, shared by every context of this
+        # communicator, and their call counter
+        self.ll = None
+        self.ll_state = torch.zeros(2, dtype=torch.int32, device=self.device)
+        if self.world in (2, 4, 8) and os.environ.get("TFC_DISABLE_LL") != "1":
+            lib = _lib.kernels()
+            lib.cb2_comm_ll_bytes.restype = ctypes.c_size_t
+            lib.cb2_comm_ll_bytes.argtypes = [ctypes.c_int, ctypes.c_size_t]
+            nbytes = int(lib.cb2_comm_ll_bytes(self.world, LL_SLOT_PAYLOAD))
+            try:
+                self.ll = symm.SymmetricBuffer(nbytes, self.device, self.xchg, want_multicast=False)
+                ok = True
+            except (symm.SymmUnavailable, OSError):
+                ok = False
+            oks = [None] * self.world
+            dist.all_gather_object(oks, ok, group=self.group)
+            if not all(oks):
+                self.ll = None
 
     def _init_shm(self) -> None:
         from . import shm
@@ -173,7 +198,20 @@ class Communicator:
         ctx.mc_grad = grad_buf.mc_ptr or None
         ctx.mc_param = param_buf.mc_ptr or None
         ctx.epochs = self.epochs.data_ptr()
+        for i in range(MAX_RANKS):
+            ctx.ll_ptrs[i] = self.ll.peer_ptrs[i] if (self.ll is not None and i < self.world) else None
+        ctx.ll_bytes = self.ll.nbytes if self.ll is not None else 0
+        ctx.ll_state = self.ll_state.data_ptr() if self.ll_state is not None else None
         return ctx
+
+    def ll_capacity(self, algo: int) -> int:
+        """Largest bucket (bytes) the LL buffers take under ``algo`` (0: LL unavailable)."""
+        if self.ll is None:
+            return 0
+        # mirrors ll_slot_chunks() in csrc/kernels/comm.cu
+        aux = self.world * AUX_FLOATS * 8
+        chunks = (self.ll.nbytes // 2 - aux) // 16 // (4 * self.world)
+        return chunks * 16 if algo == ALGO_LL1 else chunks * 16 * self.world
 
     # -- kernels ------------------------------------------------------------------------------
     def fused(self, ctx: CommCtx, *, algo: int, opt: int, grad_dtype: torch.dtype,

@@ -58,6 +58,10 @@ class _Bucket:
     n_params: int
     ready: int = 0
     launched: bool = False
+    algo: int = 0            # collective schedule of this bucket (comm.ALGO_*)
+    sharded: bool = False    # optimizer state of this bucket cut across the ranks
+    s_off: int = 0           # where this bucket's part starts in this rank's state arrays
+    s_len: int = 0
 
 
 @dataclass
@@ -123,6 +127,8 @@ class DPEngine:
         self._hook_handles = []
         self.allreduce_host_us: list = []      # drained by the front end into the metrics registry
         self._in_step = False
+        self._aux_pending = 0
+        self._aux_done = 0
         self._master_exact = set()
         self._fault = None
         fault = os.environ.get("TFC_FAULT")
@@ -150,37 +156,65 @@ class DPEngine:
         align = 8 * self.world
         for g in self.groups:
             itemsize = torch.empty((), dtype=g.dtype).element_size()
-            bucket_cap = max(self.bucket_elems // itemsize, 1)
-            off, b_start, b_count = 0, 0, 0
-            for _name, p in g.params:
-                g.offsets.append(off)
-                off += _round_up(p.numel(), 8)
-                b_count += 1
-                if off - b_start >= bucket_cap:
-                    off = _round_up(off - b_start, align) + b_start
-                    g.buckets.append(_Bucket(b_start, off - b_start, b_count))
-                    b_start, b_count = off, 0
-            if b_count:
+            sizes = [_round_up(p.numel(), 8) for _n, p in g.params]
+            off = 0
+            for lo, hi in self._partition(sizes, itemsize):
+                b_start = off
+                for i in range(lo, hi):
+                    g.offsets.append(off)
+                    off += sizes[i]
                 off = _round_up(off - b_start, align) + b_start
-                g.buckets.append(_Bucket(b_start, off - b_start, b_count))
+                g.buckets.append(_Bucket(b_start, off - b_start, hi - lo))
             g.total = off
             self._alloc_group(g, itemsize)
             self._adopt_params(g)
         self.sync_from_root()
         self._install_hooks()
 
+    def _partition(self, sizes, itemsize):
+        """Cut the arena (parameters in the order their gradients become ready) into buckets.
+        The bucket that is ready LAST - the first layers of the model - cannot hide behind any
+        backward work, so it is kept small (``TFC_TAIL_BUCKET_MB``, 4); towards the front of the
+        arena, where all of backward is still to come, buckets double up to ``TFC_BUCKET_MB``."""
+        cap_max = max(self.bucket_elems // itemsize, 1)
+        tail = max(int(float(os.environ.get("TFC_TAIL_BUCKET_MB", "4")) * (1 << 20)) // itemsize, 1)
+        cap = min(tail, cap_max) if self.world > 1 else cap_max
+        out, hi = [], len(sizes)
+        while hi > 0:
+            lo, acc = hi, 0
+            while lo > 0 and acc < cap:
+                lo -= 1
+                acc += sizes[lo]
+            out.append((lo, hi))
+            hi = lo
+            cap = min(cap * 2, cap_max)
+        out.reverse()
+        return out
+
     def _pick_algo(self, g: _Group, nbytes: int) -> int:
+        """Schedule of one bucket by its size: flag-in-payload pushes while latency dominates
+        (one-shot up to ``TFC_LL1_MAX_KB``, two-shot up to ``TFC_LL2_MAX_KB``), the in-switch
+        reduction (or peer-load two-shot) once bandwidth does."""
         name = self.algo_name
         if self.world == 1:
             return comm_mod.ALGO_TWOSHOT            # "my shard" is everything: no peers, no barrier
         has_mc = bool(g.bufs and g.bufs[0].mc_ptr and g.bufs[1].mc_ptr)
+        big = comm_mod.ALGO_NVLS if has_mc else comm_mod.ALGO_TWOSHOT
+        cap1 = self.comm.ll_capacity(comm_mod.ALGO_LL1)
+        cap2 = self.comm.ll_capacity(comm_mod.ALGO_LL2)
         if name == "auto":
-            if nbytes <= (1 << 20):
+            if nbytes <= min(cap1, int(os.environ.get("TFC_LL1_MAX_KB", "64")) << 10):
+                return comm_mod.ALGO_LL1
+            if nbytes <= min(cap2, int(os.environ.get("TFC_LL2_MAX_KB", "4096")) << 10):
+                return comm_mod.ALGO_LL2
+            if nbytes <= (1 << 20) and not cap1:
                 return comm_mod.ALGO_ONESHOT
-            return comm_mod.ALGO_NVLS if has_mc else comm_mod.ALGO_TWOSHOT
+            return big
         algo = comm_mod.ALGO_NAMES[name]
         if algo == comm_mod.ALGO_NVLS and not has_mc:
             algo = comm_mod.ALGO_TWOSHOT
+        if (algo == comm_mod.ALGO_LL1 and nbytes > cap1) or (algo == comm_mod.ALGO_LL2 and nbytes > cap2):
+            algo = big
         return algo
 
     def _alloc_group(self, g: _Group, itemsize: int) -> None:
@@ -192,12 +226,20 @@ class DPEngine:
             g.grad_arena = gb.view(g.dtype, n)
             g.param_arena = pb.view(g.dtype, n)
             g.ctx = self.comm.make_ctx(gb, pb)
-            g.algo = self._pick_algo(g, n * itemsize)
-            g.sharded = g.algo != comm_mod.ALGO_ONESHOT and self.world > 1
+            for b in g.buckets:
+                b.algo = self._pick_algo(g, b.length * itemsize)
+                b.sharded = b.algo in comm_mod.SHARDED_ALGOS and self.world > 1
         else:
             g.grad_arena = self.comm.alloc_flat(n, g.dtype)        # in the shared segment on CPU ranks
             g.param_arena = torch.zeros(n, dtype=g.dtype, device=self.device)
-        n_state = n // self.world if g.sharded else n
+        n_state = 0
+        for b in g.buckets:
+            b.s_off = n_state
+            b.s_len = b.length // self.world if b.sharded else b.length
+            n_state += b.s_len
+        g.bucket_algos = [b.algo for b in g.buckets]
+        g.algo = g.buckets[0].algo if g.buckets else 0
+        g.sharded = any(b.sharded for b in g.buckets)
         code = self.opt.code
         z = lambda: torch.zeros(n_state, dtype=torch.float32, device=self.device)  # noqa: E731
         g.master = z() if need_master else None
@@ -234,10 +276,18 @@ class DPEngine:
 
     def _state_range(self, g: _Group, b: _Bucket):
         """(arena offset, length, state offset) of the part of bucket b this rank updates."""
-        if g.sharded:
+        if b.sharded:
             shard = b.length // self.world
-            return b.off + self.rank * shard, shard, b.off // self.world
-        return b.off, b.length, b.off
+            return b.off + self.rank * shard, shard, b.s_off
+        return b.off, b.length, b.s_off
+
+    def _pieces(self, b: _Bucket):
+        """[(rank or None, arena lo, arena hi, state lo)]: whose state arrays hold which part of
+        bucket b (None: every rank holds all of it)."""
+        if not b.sharded:
+            return [(None, b.off, b.off + b.length, b.s_off)]
+        shard = b.length // self.world
+        return [(r, b.off + r * shard, b.off + (r + 1) * shard, b.s_off) for r in range(self.world)]
 
     def _refresh_master(self, g: _Group) -> None:
         if g.master is None:
@@ -342,22 +392,20 @@ class DPEngine:
     def _gather_state(self, g: _Group, local: torch.Tensor, buf, lo: int, hi: int) -> torch.Tensor:
         """Elements [lo, hi) of a (possibly sharded) fp32 state vector, in arena order.  Sharded
         state that lives in peer-mapped memory (``buf``) is read from the peers directly."""
-        if not g.sharded:
-            return local[lo:hi].detach().clone()
-        if buf is None:
-            raise RuntimeError("sharded state without a peer mapping cannot be read by one rank")
         from .symm import _wrap
         out = torch.empty(hi - lo, dtype=torch.float32, device=self.device)
         for b in g.buckets:
-            shard = b.length // self.world
-            s_off = b.off // self.world
-            for r in range(self.world):
-                a, z = max(lo, b.off + r * shard), min(hi, b.off + (r + 1) * shard)
+            for r, a_lo, a_hi, s_lo in self._pieces(b):
+                a, z = max(lo, a_lo), min(hi, a_hi)
                 if a >= z:
                     continue
-                src = buf.local.view(torch.float32) if r == self.rank else \
-                    _wrap(buf.peer_ptrs[r], buf.nbytes, self.device).view(torch.float32)
-                k = s_off + (a - (b.off + r * shard))
+                if r is None or r == self.rank:
+                    src = local
+                elif buf is None:
+                    raise RuntimeError("sharded state without a peer mapping cannot be read by one rank")
+                else:
+                    src = _wrap(buf.peer_ptrs[r], buf.nbytes, self.device).view(torch.float32)
+                k = s_lo + (a - a_lo)
                 out[a - lo: z - lo].copy_(src[k: k + (z - a)])
         return out
 
@@ -383,17 +431,19 @@ class DPEngine:
             g.param_arena[off:off + n].copy_(flat.to(g.dtype))
             if g.master is None:
                 return
-            if not g.sharded:
-                g.master[off:off + n].copy_(flat)
-            else:
-                for b in g.buckets:
-                    shard = b.length // self.world
-                    lo = b.off + self.rank * shard
-                    a, z = max(lo, off), min(lo + shard, off + n)
-                    if a < z:
-                        s_off = b.off // self.world
-                        g.master[s_off + (a - lo): s_off + (z - lo)].copy_(flat[a - off: z - off])
+            self._scatter_state(g, g.master, flat, off, n)
             self._master_exact.add((gi, name))
+
+    def _scatter_state(self, g: _Group, dst: torch.Tensor, flat: torch.Tensor, off: int, n: int) -> None:
+        """Write arena range [off, off + n) of a full-size vector into the parts of the state array
+        ``dst`` this rank holds."""
+        for b in g.buckets:
+            for r, a_lo, a_hi, s_lo in self._pieces(b):
+                if r is not None and r != self.rank:
+                    continue
+                a, z = max(a_lo, off), min(a_hi, off + n)
+                if a < z:
+                    dst[s_lo + (a - a_lo): s_lo + (z - a_lo)].copy_(flat[a - off: z - off])
 
     # ------------------------------------------------------------------------------------------
     def set_lr(self, lr: float) -> None:
@@ -402,8 +452,12 @@ class DPEngine:
             self.opt.lr = float(lr)
             self.hyper[0:1].fill_(float(lr))
 
-    def begin_step(self) -> None:
-        """Call before backward: arms the bucket hooks and advances the step counter."""
+    def begin_step(self, n_aux: int = 0) -> None:
+        """Call before backward: arms the bucket hooks and advances the step counter.  ``n_aux``:
+        how many metric scalars of ``comm.aux`` the step wants summed over the replicas."""
+        self._aux_pending = n_aux if (self.is_cuda and self.groups and self.groups[0].ctx is not None
+                                      and os.environ.get("TFC_AUX_IN_BUCKET", "1") != "0") else 0
+        self._aux_done = 0
         for g in self.groups:
             for b in g.buckets:
                 b.ready, b.launched = 0, False
@@ -433,10 +487,16 @@ class DPEngine:
         code = self.opt.code
         if g.ctx is not None:
             _a, _n, s_off = self._state_range(g, b)
-            self.comm.fused(g.ctx, algo=g.algo, opt=code, grad_dtype=g.dtype, param_dtype=g.dtype,
+            # the step's metric scalars are final before backward starts: they ride in the first
+            # bucket kernel that is launched (no launch of their own, no extra barrier rounds)
+            n_aux, self._aux_pending = self._aux_pending, 0
+            self.comm.fused(g.ctx, algo=b.algo, opt=code, grad_dtype=g.dtype, param_dtype=g.dtype,
                             off=b.off, length=b.length, master=g.master, s1=g.s1, s2=g.s2,
                             state_off=s_off, hyper=self.hyper, zero_grads=True,
+                            aux_len=n_aux, aux_out=self.aux_out if n_aux else None,
                             stream=self.comm_stream)
+            if n_aux:
+                self._aux_done = n_aux
             return
         grad = g.grad_arena[b.off:b.off + b.length]
         if self.world > 1:
@@ -460,7 +520,7 @@ class DPEngine:
         self._in_step = False
         out = None
         if n_aux:
-            out = self._reduce_aux(n_aux)
+            out = self.aux_out[:n_aux] if self._aux_done == n_aux else self._reduce_aux(n_aux)
         if self.is_cuda:
             torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
         self.steps += 1
@@ -500,18 +560,16 @@ class DPEngine:
             for key, t in (("master", g.master), ("s1", g.s1), ("s2", g.s2)):
                 if t is None:
                     continue
+                parts = None
                 if g.sharded:
                     parts = [torch.empty_like(t) for _ in range(self.world)]
                     dist.all_gather(parts, t.contiguous(), group=self.comm.group)
-                    buf = torch.empty(g.total, dtype=torch.float32, device=self.device)
-                    for b in g.buckets:
-                        shard = b.length // self.world
-                        for r in range(self.world):
-                            s_off = b.off // self.world
-                            buf[b.off + r * shard: b.off + (r + 1) * shard] = parts[r][s_off:s_off + shard]
-                    full[key] = buf
-                else:
-                    full[key] = t
+                buf = torch.empty(g.total, dtype=torch.float32, device=self.device)
+                for b in g.buckets:
+                    for r, a_lo, a_hi, s_lo in self._pieces(b):
+                        src = t if r is None else parts[r]
+                        buf[a_lo:a_hi] = src[s_lo:s_lo + (a_hi - a_lo)]
+                full[key] = buf
             for (name, p), off in zip(g.params, g.offsets):
                 n = p.numel()
                 entry = {}
@@ -537,17 +595,7 @@ class DPEngine:
                     # files written before the layout tag hold the arena order of the device that
                     # wrote them (assumed to be this one's)
                     src = self._to_arena_order(p, src) if logical and src.dim() == p.dim() else src.reshape(-1)
-                    if not g.sharded:
-                        t[off:off + n].copy_(src)
-                        continue
-                    for b in g.buckets:
-                        shard = b.length // self.world
-                        lo = b.off + self.rank * shard
-                        hi = lo + shard
-                        a, z = max(lo, off), min(hi, off + n)
-                        if a < z:
-                            s_off = b.off // self.world
-                            t[s_off + (a - lo): s_off + (z - lo)].copy_(src[a - off: z - off])
+                    self._scatter_state(g, t, src, off, n)
         if "__step__" in state:
             step = float(state["__step__"])
             self.hyper[5] = step

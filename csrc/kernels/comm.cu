@@ -36,6 +36,30 @@ struct DevCtx {
   void* mc_grad;
   void* mc_param;
   uint32_t* epochs;
+  uint4* ll[CB2_MAX_RANKS];      // every rank's LL receive buffer (flag-in-payload protocol)
+  size_t ll_bytes;               // size of one such buffer
+  uint32_t* ll_state;            // local: [0] calls completed, [1] blocks of the running call done
+  unsigned long long timeout_ns; // how long a wait for a peer may last before the kernel traps
+};
+
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// A peer that does not show up is a dead or wedged process: after `timeout_ns` (minutes by default,
+// TFC_COMM_TIMEOUT_S) the kernel traps, which surfaces as a launch failure on this rank.  The wait
+// backs off (up to ~1 us between polls), so a long wait does not hammer NVLink or the peer's L2.
+struct SpinWait {
+  unsigned long long t0 = 0;
+  unsigned ns = 32;
+  __device__ __forceinline__ void pause(unsigned long long timeout_ns) {
+    if (t0 == 0) t0 = global_ns();
+    __nanosleep(ns);
+    if (ns < 1024) ns <<= 1;
+    else if (global_ns() - t0 > timeout_ns) __trap();
+  }
 };
 
 __device__ __forceinline__ float* aux_of(uint32_t* pad) {
@@ -51,10 +75,8 @@ __device__ __forceinline__ void peer_barrier(const DevCtx& c, uint32_t epoch) {
     __threadfence_system();
     st_release_sys(c.pad[peer] + blockIdx.x * CB2_MAX_RANKS + c.rank, epoch);
     const uint32_t* mine = c.pad[c.rank] + blockIdx.x * CB2_MAX_RANKS + peer;
-    const long long t0 = clock64();
-    while (static_cast<int32_t>(ld_acquire_sys(mine) - epoch) < 0) {
-      if (clock64() - t0 > kSpinTimeoutCycles) __trap();
-    }
+    SpinWait w;
+    while (static_cast<int32_t>(ld_acquire_sys(mine) - epoch) < 0) w.pause(c.timeout_ns);
   }
   __syncthreads();
 }
@@ -298,6 +320,262 @@ comm_fused_kernel(const DevCtx c, const FusedArgs a, const int opt) {
   if (threadIdx.x == 0) c.epochs[blockIdx.x] = base + 2;
 }
 
+// ---------------------------------------------------------------------------------------------
+// LL ("low latency") schedules: flag-in-payload pushes, no barrier at all.
+//
+// A 16-byte gradient chunk travels as two 16-byte stores {d0, e, d1, e}, {d2, e, d3, e}: every
+// 8-byte half carries the epoch e of the call, so the arrival of the data IS the signal - one
+// NVLink traversal instead of "barrier, then load across the link".  The receiver polls its own
+// memory.  Receive buffers alternate between two parities (e & 1): a rank can only be one call ahead
+// of its slowest peer (it needs that peer's data of call e to finish call e), so data of call e + 2
+// never lands on data of call e that has not been consumed.  Nobody reads a peer's gradient arena in
+// these schedules, hence no closing barrier either: gradients are zeroed as soon as they are read.
+//
+//   LL1 (one-shot)  every rank pushes its whole bucket to every peer, sums all W copies in rank
+//                   order (bitwise identical everywhere) and updates a replicated state.
+//                   One hop; wire bytes 2 (W-1) S per rank: for buckets up to ~64 KiB.
+//   LL2 (two-shot)  rank r owns shard r: peers push their part of it, r sums, updates its sharded
+//                   state and pushes the new parameters back the same way.  Two hops; wire bytes
+//                   4 (W-1)/W S per rank: for buckets up to a few MiB.
+//
+// Layout of a rank's LL buffer (uint4 units, n = chunk capacity of one slot):
+//   [parity][region: 0 = gradients, 1 = parameters][sender rank][2 * n]   then the aux scalars:
+//   [parity][sender][CB2_COMM_AUX_FLOATS] as 8-byte {value, e} pairs.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void ll_push(uint4* dst, const uint4& d, uint32_t e) {
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "r"(d.x), "r"(e), "r"(d.y), "r"(e)
+               : "memory");
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(dst + 1), "r"(d.z), "r"(e), "r"(d.w),
+               "r"(e)
+               : "memory");
+}
+__device__ __forceinline__ uint4 ll_poll(const uint4* src, uint32_t e, unsigned long long timeout_ns) {
+  uint4 a, b;
+  SpinWait w;
+  while (true) {
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w) : "l"(src) : "memory");
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w) : "l"(src + 1) : "memory");
+    if (a.y == e && a.w == e && b.y == e && b.w == e) break;
+    w.pause(timeout_ns);
+  }
+  return make_uint4(a.x, a.z, b.x, b.z);
+}
+
+__host__ __device__ inline size_t ll_slot_chunks(size_t ll_bytes, int world) {
+  // bytes = 2 parities * (2 regions * W slots * 2n uint4 + W * AUX 8-byte pairs)
+  const size_t aux = static_cast<size_t>(world) * CB2_COMM_AUX_FLOATS * 8;
+  const size_t per_parity = ll_bytes / 2;
+  if (per_parity <= aux) return 0;
+  return (per_parity - aux) / 16 / (2 * static_cast<size_t>(world) * 2);
+}
+
+struct LLView {
+  size_t n;            // chunk capacity of a slot
+  size_t parity_u4;    // uint4 per parity
+  __device__ __forceinline__ uint4* slot(uint4* base, uint32_t e, int region, int sender, int world) const {
+    return base + (e & 1) * parity_u4 + (static_cast<size_t>(region) * world + sender) * 2 * n;
+  }
+  __device__ __forceinline__ uint2* aux(uint4* base, uint32_t e, int sender, int world) const {
+    uint4* p = base + (e & 1) * parity_u4 + static_cast<size_t>(2) * world * 2 * n;
+    return reinterpret_cast<uint2*>(p) + static_cast<size_t>(sender) * CB2_COMM_AUX_FLOATS;
+  }
+};
+
+// aux scalars ride with the call: pushed to every peer as {value, e}, summed in rank order
+__device__ __forceinline__ void ll_aux(const DevCtx& c, const FusedArgs& a, const LLView& lv, uint32_t e,
+                                       int W, int R) {
+  if (blockIdx.x != 0 || static_cast<int>(threadIdx.x) >= a.aux_len) return;
+  float* mine = aux_of(c.pad[R]) + threadIdx.x;
+  const float v = *mine;
+  for (int p = 0; p < W; ++p) {
+    if (p == R) continue;
+    uint2* dst = lv.aux(c.ll[p], e, R, W) + threadIdx.x;
+    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(dst), "r"(__float_as_uint(v)), "r"(e)
+                 : "memory");
+  }
+  float s = 0.f;
+  for (int p = 0; p < W; ++p) {
+    if (p == R) { s += v; continue; }
+    const uint2* src = lv.aux(c.ll[R], e, p, W) + threadIdx.x;
+    uint32_t x, f;
+    SpinWait w;
+    while (true) {
+      asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(x), "=r"(f) : "l"(src) : "memory");
+      if (f == e) break;
+      w.pause(c.timeout_ns);
+    }
+    s += __uint_as_float(x);
+  }
+  a.aux_out[threadIdx.x] = s;
+  if (a.zero_grads) *mine = 0.f;
+}
+
+// the call counter advances when the last block of the grid is done (no block of this launch can
+// still read it then; the next launch on the stream sees the new value)
+__device__ __forceinline__ void ll_finish(const DevCtx& c, uint32_t e) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(c.ll_state + 1, 1u) == gridDim.x - 1) {
+      c.ll_state[1] = 0;
+      c.ll_state[0] = e;
+    }
+  }
+}
+
+template <typename T, int WT>
+__global__ void __launch_bounds__(512)
+comm_ll1_kernel(const DevCtx c, const FusedArgs a, const int opt) {
+  constexpr int N = 16 / sizeof(T);
+  constexpr int U = 4;
+  const int W = WT, R = c.rank;
+  const uint32_t e = *reinterpret_cast<volatile uint32_t*>(c.ll_state) + 1;
+  const Hyper h = load_hyper(a.hyper);
+  LLView lv;
+  lv.n = ll_slot_chunks(c.ll_bytes, W);
+  lv.parity_u4 = c.ll_bytes / 32;
+  const size_t nvec = a.len / N;
+  const size_t tid = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
+  const size_t nthreads = static_cast<size_t>(gridDim.x) * blockDim.x;
+  T* const my_grad = reinterpret_cast<T*>(c.grad[R]);
+  T* const my_param = reinterpret_cast<T*>(c.param[R]);
+  const uint4 zero = make_uint4(0, 0, 0, 0);
+
+  for (size_t v0 = tid; v0 < nvec; v0 += nthreads * U) {
+    uint4 own[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t v = v0 + static_cast<size_t>(u) * nthreads;
+      if (v < nvec) {
+        own[u] = ld_stream_v4(my_grad + a.off + v * N);
+#pragma unroll
+        for (int d = 1; d < WT; ++d) {
+          const int p = (R + d) % WT;
+          ll_push(lv.slot(c.ll[p], e, 0, R, W) + 2 * v, own[u], e);
+        }
+        if (a.zero_grads) st_stream_v4(my_grad + a.off + v * N, zero);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t v = v0 + static_cast<size_t>(u) * nthreads;
+      if (v >= nvec) continue;
+      VecN<N> g;
+#pragma unroll
+      for (int j = 0; j < N; ++j) g.v[j] = 0.f;
+#pragma unroll
+      for (int p = 0; p < WT; ++p) {          // rank order: the same sum on every replica
+        const uint4 raw = p == R ? own[u] : ll_poll(lv.slot(c.ll[R], e, 0, p, W) + 2 * v, e, c.timeout_ns);
+        const VecN<N> o = unpack16<T>(raw);
+#pragma unroll
+        for (int j = 0; j < N; ++j) g.v[j] += o.v[j];
+      }
+      const size_t i = a.off + v * N;
+      const size_t si = a.state_off + v * N;
+      VecN<N> pin;
+      if (opt != CB2_OPT_NONE) {
+        if (a.master) pin = load_state<N>(a.master + si);
+        else pin = unpack16<T>(ld_stream_v4(my_param + i));
+      }
+      const VecN<N> pn = updateN_dyn<N>(opt, pin, g, a.s1, a.s2, si, h);
+      if (opt != CB2_OPT_NONE && a.master) store_state<N>(a.master + si, pn);
+      st_stream_v4(my_param + i, pack16(pn));
+    }
+  }
+  ll_aux(c, a, lv, e, W, R);
+  ll_finish(c, e);
+}
+
+template <typename T, int WT>
+__global__ void __launch_bounds__(512)
+comm_ll2_kernel(const DevCtx c, const FusedArgs a, const int opt) {
+  constexpr int N = 16 / sizeof(T);
+  constexpr int U = 4;
+  const int W = WT, R = c.rank;
+  const uint32_t e = *reinterpret_cast<volatile uint32_t*>(c.ll_state) + 1;
+  const Hyper h = load_hyper(a.hyper);
+  LLView lv;
+  lv.n = ll_slot_chunks(c.ll_bytes, W);
+  lv.parity_u4 = c.ll_bytes / 32;
+  const size_t span = a.len / W;             // elements per shard
+  const size_t nvec = span / N;
+  const size_t tid = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
+  const size_t nthreads = static_cast<size_t>(gridDim.x) * blockDim.x;
+  T* const my_grad = reinterpret_cast<T*>(c.grad[R]);
+  T* const my_param = reinterpret_cast<T*>(c.param[R]);
+  const uint4 zero = make_uint4(0, 0, 0, 0);
+
+  for (size_t v0 = tid; v0 < nvec; v0 += nthreads * U) {
+    // 1. my part of every peer's shard goes to its owner; my own shard stays in registers
+    uint4 own[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t v = v0 + static_cast<size_t>(u) * nthreads;
+      if (v < nvec) {
+#pragma unroll
+        for (int d = 1; d < WT; ++d) {
+          const int p = (R + d) % WT;
+          T* src = my_grad + a.off + static_cast<size_t>(p) * span + v * N;
+          const uint4 w = ld_stream_v4(src);
+          ll_push(lv.slot(c.ll[p], e, 0, R, W) + 2 * v, w, e);
+          if (a.zero_grads) st_stream_v4(src, zero);
+        }
+        T* mine = my_grad + a.off + static_cast<size_t>(R) * span + v * N;
+        own[u] = ld_stream_v4(mine);
+        if (a.zero_grads) st_stream_v4(mine, zero);
+      }
+    }
+    // 2. sum my shard in rank order, update it, publish the new parameters
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t v = v0 + static_cast<size_t>(u) * nthreads;
+      if (v >= nvec) continue;
+      VecN<N> g;
+#pragma unroll
+      for (int j = 0; j < N; ++j) g.v[j] = 0.f;
+#pragma unroll
+      for (int p = 0; p < WT; ++p) {
+        const uint4 raw = p == R ? own[u] : ll_poll(lv.slot(c.ll[R], e, 0, p, W) + 2 * v, e, c.timeout_ns);
+        const VecN<N> o = unpack16<T>(raw);
+#pragma unroll
+        for (int j = 0; j < N; ++j) g.v[j] += o.v[j];
+      }
+      const size_t i = a.off + static_cast<size_t>(R) * span + v * N;
+      const size_t si = a.state_off + v * N;
+      VecN<N> pin;
+      if (opt != CB2_OPT_NONE) {
+        if (a.master) pin = load_state<N>(a.master + si);
+        else pin = unpack16<T>(ld_stream_v4(my_param + i));
+      }
+      const VecN<N> pn = updateN_dyn<N>(opt, pin, g, a.s1, a.s2, si, h);
+      if (opt != CB2_OPT_NONE && a.master) store_state<N>(a.master + si, pn);
+      const uint4 packed = pack16(pn);
+      st_stream_v4(my_param + i, packed);
+#pragma unroll
+      for (int d = 1; d < WT; ++d) {
+        const int p = (R + d) % WT;
+        ll_push(lv.slot(c.ll[p], e, 1, R, W) + 2 * v, packed, e);
+      }
+    }
+    // 3. the other shards' new parameters arrive the same way
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t v = v0 + static_cast<size_t>(u) * nthreads;
+      if (v >= nvec) continue;
+#pragma unroll
+      for (int d = 1; d < WT; ++d) {
+        const int p = (R + d) % WT;
+        const uint4 raw = ll_poll(lv.slot(c.ll[R], e, 1, p, W) + 2 * v, e, c.timeout_ns);
+        st_stream_v4(my_param + a.off + static_cast<size_t>(p) * span + v * N, raw);
+      }
+    }
+  }
+  ll_aux(c, a, lv, e, W, R);
+  ll_finish(c, e);
+}
+
 template <typename T>
 __global__ void __launch_bounds__(512)
 comm_broadcast_kernel(const DevCtx c, int root, size_t off, size_t len, int use_mc) {
@@ -345,7 +623,33 @@ static int to_dev_ctx(const cb2_comm_ctx* ctx, DevCtx* d) {
   d->mc_grad = ctx->mc_grad;
   d->mc_param = ctx->mc_param;
   d->epochs = ctx->epochs;
+  for (int i = 0; i < CB2_MAX_RANKS; ++i) d->ll[i] = reinterpret_cast<uint4*>(ctx->ll_ptrs[i]);
+  d->ll_bytes = ctx->ll_bytes;
+  d->ll_state = ctx->ll_state;
+  static const unsigned long long timeout_ns = [] {
+    const char* e = getenv("TFC_COMM_TIMEOUT_S");
+    const double sec = e ? atof(e) : 600.0;
+    return static_cast<unsigned long long>((sec > 0 ? sec : 600.0) * 1e9);
+  }();
+  d->timeout_ns = timeout_ns;
   return 0;
+}
+
+template <int ALGO, typename T>
+static int launch_ll(const DevCtx& d, const FusedArgs& a, int opt, int blocks, cudaStream_t st) {
+#define CB2_LL(WT)                                                                    \
+  if (ALGO == CB2_ALGO_LL1) comm_ll1_kernel<T, WT><<<blocks, 512, 0, st>>>(d, a, opt); \
+  else comm_ll2_kernel<T, WT><<<blocks, 512, 0, st>>>(d, a, opt);
+  switch (d.world) {
+    case 2: CB2_LL(2) break;
+    case 4: CB2_LL(4) break;
+    case 8: CB2_LL(8) break;
+    default:
+      set_last_error("comm_fused: the LL schedules are built for 2, 4 or 8 ranks (world=%d)", d.world);
+      return CB2_ERR_UNSUPPORTED;
+  }
+#undef CB2_LL
+  return check_cuda(cudaGetLastError(), "comm_fused (LL) launch");
 }
 
 template <int ALGO, int WT>
@@ -391,6 +695,13 @@ static int max_blocks_env() {
 
 using namespace cb2;
 
+extern "C" size_t cb2_comm_ll_bytes(int world, size_t slot_payload) {
+  const size_t chunks = (slot_payload + 15) / 16;
+  const size_t per_parity = 2 * static_cast<size_t>(world) * 2 * chunks * 16 +
+                            static_cast<size_t>(world) * CB2_COMM_AUX_FLOATS * 8;
+  return 2 * per_parity;
+}
+
 extern "C" int cb2_comm_fused(const cb2_comm_ctx* ctx, int algo, int opt, int grad_dtype,
                               int param_dtype, size_t off, size_t len, float* master, float* s1,
                               float* s2, size_t state_off, const float* hyper, int zero_grads,
@@ -415,7 +726,38 @@ extern "C" int cb2_comm_fused(const cb2_comm_ctx* ctx, int algo, int opt, int gr
     set_last_error("comm_fused: bf16 parameters need an fp32 master copy");
     return CB2_ERR_ARG;
   }
-  if (d.world == 1 && algo == CB2_ALGO_NVLS) algo = CB2_ALGO_TWOSHOT;
+  if (d.world == 1 && algo != CB2_ALGO_ONESHOT) algo = CB2_ALGO_TWOSHOT;
+  if (algo == CB2_ALGO_LL1 || algo == CB2_ALGO_LL2) {
+    if (grad_dtype != param_dtype) {
+      set_last_error("comm_fused: gradient and parameter arenas must have the same dtype");
+      return CB2_ERR_UNSUPPORTED;
+    }
+    const size_t cap = d.ll_state && d.ll[d.rank] ? ll_slot_chunks(d.ll_bytes, d.world) : 0;
+    const size_t esz = grad_dtype == CB2_DTYPE_F32 ? 4 : 2;
+    const size_t chunks = (algo == CB2_ALGO_LL1 ? len : len / d.world) * esz / 16;
+    if (chunks > cap) {
+      set_last_error("comm_fused: %zu bytes per slot exceed the LL buffer (%zu bytes per slot); use "
+                     "TWOSHOT/NVLS for this bucket", chunks * 16, cap * 16);
+      return CB2_ERR_UNSUPPORTED;
+    }
+    FusedArgs a;
+    a.off = off; a.len = len; a.state_off = state_off;
+    a.master = master; a.s1 = s1; a.s2 = s2; a.hyper = hyper;
+    a.zero_grads = zero_grads; a.aux_len = aux_len; a.aux_out = aux_out;
+    if (blocks <= 0) {
+      // latency bound: spread the chunks so that a thread has at most one batch of four
+      size_t want = (chunks + 4 * 512 - 1) / (4 * 512);
+      if (want > 64) want = 64;
+      if (want < 1) want = 1;
+      blocks = static_cast<int>(want);
+    }
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (algo == CB2_ALGO_LL1)
+      return grad_dtype == CB2_DTYPE_F32 ? launch_ll<CB2_ALGO_LL1, float>(d, a, opt, blocks, st)
+                                         : launch_ll<CB2_ALGO_LL1, __nv_bfloat16>(d, a, opt, blocks, st);
+    return grad_dtype == CB2_DTYPE_F32 ? launch_ll<CB2_ALGO_LL2, float>(d, a, opt, blocks, st)
+                                       : launch_ll<CB2_ALGO_LL2, __nv_bfloat16>(d, a, opt, blocks, st);
+  }
   if (blocks <= 0) {
     // enough 16-byte requests in flight to cover the ~2 us NVLink round trip at 900 GB/s, but
     // never more than the work: one 8-element vector per thread minimum

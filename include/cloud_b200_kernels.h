@@ -226,6 +226,8 @@ int cb2_optim_flat(int opt, float* master, const void* grad, int grad_dtype, flo
 #define CB2_ALGO_ONESHOT 0  /* every rank reduces everything (replicated state); latency bound */
 #define CB2_ALGO_TWOSHOT 1  /* reduce-scatter by peer loads -> update shard -> all-gather by peer stores */
 #define CB2_ALGO_NVLS 2     /* multimem.ld_reduce (in-switch sum) -> update shard -> multimem.st */
+#define CB2_ALGO_LL1 3      /* flag-in-payload pushes, no barrier: one-shot, replicated state (<= ~64 KiB) */
+#define CB2_ALGO_LL2 4      /* flag-in-payload pushes, no barrier: two-shot, sharded state (<= a few MiB) */
 
 typedef struct {
   int rank, world;
@@ -235,11 +237,18 @@ typedef struct {
   void* mc_grad;                    /* multicast mapping of the gradient arena (NVLS) or NULL */
   void* mc_param;                   /* multicast mapping of the parameter arena or NULL */
   uint32_t* epochs;                 /* local uint32[CB2_COMM_MAX_BLOCKS], zero-initialised */
+  void* ll_ptrs[CB2_MAX_RANKS];     /* this rank's mapping of every rank's LL receive buffer, or NULL */
+  size_t ll_bytes;                  /* size of one LL buffer (zero-initialised, symmetric); a bucket of
+                                       S bytes needs cb2_comm_ll_bytes(world, S) for LL1, S / world for LL2 */
+  uint32_t* ll_state;               /* local uint32[2], zero-initialised, shared by every context that
+                                       uses the same LL buffers */
 } cb2_comm_ctx;
+/* Bytes of LL buffer that let one slot hold `slot_payload` bytes of gradients. */
+size_t cb2_comm_ll_bytes(int world, size_t slot_payload);
 
 /* Reduce grad[off, off+len) over ranks, apply `opt` to the owned part, publish parameters.
- *   ONESHOT: state arrays cover the whole range, indexed [state_off + i].
- *   TWOSHOT/NVLS: this rank owns [off + rank*len/world, +len/world); state indexed
+ *   ONESHOT/LL1: state arrays cover the whole range, indexed [state_off + i].
+ *   TWOSHOT/NVLS/LL2: this rank owns [off + rank*len/world, +len/world); state indexed
  *                 [state_off + i] for i in the owned shard.
  * len must be a multiple of 8*world, off a multiple of 8.  aux_len fp32 scalars living in the
  * signal pad are sum-reduced one-shot into aux_out (loss / accuracy counters) by block 0. */
