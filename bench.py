@@ -436,18 +436,34 @@ def allreduce_rows(comm, dev, world, max_bytes):
     # optimizer state for the fused variant (sharded for two-shot / NVLS, replicated for one-shot)
     state = [torch.zeros(max(cap // 4 // world, (8 << 20) // 4), device=dev) for _ in range(3)]
 
-    def timed(fn, iters):
+    def timed(fn, iters, graph=False):
+        # latency-bound sizes are timed as a CUDA-graph replay of `iters` calls: the device time a
+        # training step sees (the step is a CUDA graph), not the host's Python launch rate
         for i in range(5):
             fn(i)
         torch.cuda.synchronize(dev)
         dist.barrier()
+        reps, run = 1, None
+        if graph:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                for i in range(iters):
+                    fn(i)
+            g.replay()
+            torch.cuda.synchronize(dev)
+            dist.barrier()
+            reps, run = 5, g.replay
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for i in range(iters):
-            fn(i)
+        for _ in range(reps):
+            if run is not None:
+                run()
+            else:
+                for i in range(iters):
+                    fn(i)
         e1.record()
         torch.cuda.synchronize(dev)
-        t = torch.tensor([e0.elapsed_time(e1) / iters], device=dev, dtype=torch.float64)
+        t = torch.tensor([e0.elapsed_time(e1) / (iters * reps)], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
@@ -457,10 +473,12 @@ def allreduce_rows(comm, dev, world, max_bytes):
         n = (n + 8 * world - 1) // (8 * world) * (8 * world)
         nbytes = n * 4
         slots = max(1, min(cap // nbytes, 8))
-        iters = 200 if nbytes <= (1 << 20) else (30 if nbytes <= (64 << 20) else 8)
+        use_graph = nbytes <= (4 << 20)
+        iters = 50 if use_graph else (30 if nbytes <= (64 << 20) else 8)
         k = 2 * (world - 1) / world / 1e9
-        ms = timed(lambda i: dist.all_reduce(nccl_buf[(i % slots) * n:(i % slots) * n + n]), iters)
-        row = {"bytes": nbytes, "nccl_us": ms * 1e3, "nccl_busbw_gbs": nbytes / (ms * 1e-3) * k}
+        ms = timed(lambda i: dist.all_reduce(nccl_buf[(i % slots) * n:(i % slots) * n + n]), iters, use_graph)
+        row = {"bytes": nbytes, "timing": "cuda graph replay" if use_graph else "eager launches",
+               "nccl_us": ms * 1e3, "nccl_busbw_gbs": nbytes / (ms * 1e-3) * k}
         algos = [("oneshot", C.ALGO_ONESHOT)] if nbytes <= (8 << 20) else []
         algos.append(("twoshot", C.ALGO_TWOSHOT))
         if has_mc:
@@ -474,7 +492,7 @@ def allreduce_rows(comm, dev, world, max_bytes):
                 comm.fused(ctx, algo=algo, opt=0, grad_dtype=torch.float32, param_dtype=torch.float32,
                            off=(i % slots) * n, length=n, master=None, s1=None, s2=None, state_off=0,
                            hyper=hyper, zero_grads=False)
-            ms = timed(ours, iters)
+            ms = timed(ours, iters, use_graph)
             row[name + "_us"] = ms * 1e3
             if best is None or ms < best[0]:
                 best = (ms, name, algo)
@@ -492,7 +510,7 @@ def allreduce_rows(comm, dev, world, max_bytes):
                 comm.fused(ctx, algo=algo, opt=ops.OPT_CODES["adam"], grad_dtype=torch.float32,
                            param_dtype=torch.float32, off=0, length=n, master=None, s1=state[1], s2=state[2],
                            state_off=0, hyper=hyper, zero_grads=True)
-            ms = timed(fused, iters)
+            ms = timed(fused, iters, use_graph)
             row["fused_adam_us"] = ms * 1e3
             row["fused_adam_busbw_gbs"] = nbytes / (ms * 1e-3) * k
         rows.append(row)

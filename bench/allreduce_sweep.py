@@ -202,16 +202,41 @@ def stress_ll(comm, dev, world, rank, results, iters=96):
     return ok
 
 
-def time_fn(fn, iters, dev):
+def time_fn(fn, iters, dev, graph=False):
+    """Device time per call (CUDA events, max over ranks).  With ``graph`` the ``iters`` calls are
+    captured into one CUDA graph and the replay is timed: for latency-bound sizes this removes the
+    host's launch rate (a Python + ctypes call costs more than the kernel) from the number - what a
+    training step sees, since the step is a CUDA graph too."""
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 1
+    if graph:
+        s = torch.cuda.Stream(dev)
+        s.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(s):
+            for i in range(3):
+                fn(i)
+        torch.cuda.current_stream(dev).wait_stream(s)
+        torch.cuda.synchronize()
+        dist.barrier()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for i in range(iters):
+                fn(i)
+        g.replay()
+        reps = 5
+        run = g.replay
+    else:
+        def run():
+            for i in range(iters):
+                fn(i)
     torch.cuda.synchronize()
     dist.barrier()
     e0.record()
-    for i in range(iters):
-        fn(i)
+    for _ in range(reps):
+        run()
     e1.record()
     torch.cuda.synchronize()
-    t = torch.tensor([e0.elapsed_time(e1) / iters], device=dev, dtype=torch.float64)
+    t = torch.tensor([e0.elapsed_time(e1) / (iters * reps)], device=dev, dtype=torch.float64)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return t.item()
 
@@ -237,9 +262,11 @@ def sweep(comm, dev, world, rank, max_bytes, results):
         def nccl(i):
             off = (i % slots) * n
             dist.all_reduce(nccl_buf[off:off + n])
+        use_graph = nbytes <= (4 << 20)
+        iters = min(iters, 50) if use_graph else iters
         for i in range(warm):
             nccl(i)
-        ms = time_fn(nccl, iters, dev)
+        ms = time_fn(nccl, iters, dev, graph=use_graph)
         row["nccl_us"] = ms * 1e3
         row["nccl_busbw_gbs"] = nbytes / (ms * 1e-3) * 2 * (world - 1) / world / 1e9
         algos = [("oneshot", C.ALGO_ONESHOT)] if nbytes <= (8 << 20) else []
@@ -257,7 +284,7 @@ def sweep(comm, dev, world, rank, max_bytes, results):
                            s2=None, state_off=0, hyper=hyper, zero_grads=False)
             for i in range(warm):
                 ours(i)
-            ms = time_fn(ours, iters, dev)
+            ms = time_fn(ours, iters, dev, graph=use_graph)
             row[name + "_us"] = ms * 1e3
             row[name + "_busbw_gbs"] = nbytes / (ms * 1e-3) * 2 * (world - 1) / world / 1e9
         best = max((row.get(k + "_busbw_gbs", 0.0), k) for k in ("oneshot", "twoshot", "nvls", "ll1", "ll2"))

@@ -199,7 +199,8 @@ class DPEngine:
         if self.world == 1:
             return comm_mod.ALGO_TWOSHOT            # "my shard" is everything: no peers, no barrier
         has_mc = bool(g.bufs and g.bufs[0].mc_ptr and g.bufs[1].mc_ptr)
-        big = comm_mod.ALGO_NVLS if has_mc else comm_mod.ALGO_TWOSHOT
+        # two ranks: peer loads beat the switch (measured: 1 GiB 639 vs 430 GB/s busBW); four and more: NVLS
+        big = comm_mod.ALGO_NVLS if (has_mc and self.world > 2) else comm_mod.ALGO_TWOSHOT
         cap1 = self.comm.ll_capacity(comm_mod.ALGO_LL1)
         cap2 = self.comm.ll_capacity(comm_mod.ALGO_LL2)
         if name == "auto":
