@@ -279,6 +279,11 @@ def Input(shape=None, batch_size=None, name=None, dtype="float32", **kwargs):
     return KerasTensor(full, layer=layer, inputs=(), dtype=dtype)
 
 
+# Set by Model._train_step while fit() trains with the fused cross-entropy: the softmax Dense layer
+# named here returns its logits only (see Dense.call).
+LOGITS_ONLY = {"on": False, "layer": None}
+
+
 class Dense(Layer):
     """``activation(x @ kernel + bias)`` on the tcgen05 GEMM with a fused epilogue (K1/K2/K3)."""
 
@@ -292,6 +297,7 @@ class Dense(Layer):
         self.kernel_initializer = kernel_initializer
         self.bias_initializer = bias_initializer
         self.last_logits = None
+        self._fused_dropout = None      # set by Model._mark_fusions: the Dropout layer right behind
 
     def build(self, input_shape):
         in_dim = int(input_shape[-1])
@@ -314,8 +320,26 @@ class Dense(Layer):
             # keep the logits: the fused cross-entropy consumes them (what Keras does with
             # `_keras_logits`), the probabilities are only materialised when somebody looks
             logits = ops.dense(x, self.kernel, self.bias, None)
+            if training and LOGITS_ONLY["on"] and LOGITS_ONLY["layer"] is self and torch.is_grad_enabled():
+                # inside fit()'s training step with the fused cross-entropy and metrics that come out
+                # of the same kernel: nobody reads the probabilities, so they are not computed
+                # (a view, not the tensor itself: an attribute pointing back at its owner would keep
+                # the tensor alive until the garbage collector runs - possibly in the middle of a
+                # CUDA-graph capture, where freeing device memory of an earlier step is an error)
+                out = logits.view_as(logits)
+                out._keras_logits = logits
+                return out
             out = _LazySoftmax.make(logits)
             return out
+        drop = self._fused_dropout
+        if (drop is not None and training and act == "relu" and drop.rate > 0.0 and torch.is_grad_enabled()
+                and x.is_cuda):
+            # Dense + ReLU + Dropout: the dropout is applied here and undone in this layer's backward
+            # (ReLU mask, dropout scale and bias gradient in one pass); the Dropout layer passes it on
+            y = ops.dense(x, self.kernel, self.bias, act, dropout=ops.dropout_plan(x.shape[0] * self.units,
+                                                                                   drop.rate, drop.seed))
+            y._cb2_dropped = drop
+            return y
         if act in (None, "linear", "relu"):
             return ops.dense(x, self.kernel, self.bias, act)
         y = ops.dense(x, self.kernel, self.bias, None)
@@ -383,6 +407,8 @@ class Dropout(Layer):
         self.seed = seed
 
     def call(self, x, training=False):
+        if training and getattr(x, "_cb2_dropped", None) is self:
+            return x                     # the Dense layer in front already applied this dropout
         return ops.dropout(x, self.rate, training=training, seed=self.seed)
 
     def get_config(self):

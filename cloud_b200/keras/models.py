@@ -374,11 +374,49 @@ class Model(nn.Module):
                     if not p.requires_grad and p.dim() >= 2 and p.dtype != cd:
                         fmt = torch.channels_last if p.dim() == 4 else torch.preserve_format
                         p.data = p.data.to(dtype=cd, memory_format=fmt)
+        self._mark_fusions()
         pending = getattr(self, "_pending_optimizer_state", None)
         if pending:
             self._engine.load_master_state(pending)
             self._pending_optimizer_state = None
         return self._engine
+
+    def _mark_fusions(self):
+        """Cross-layer fusions decided once the layers exist: Dense(relu) -> Dropout pairs (the
+        dropout moves into the Dense op), and a softmax output layer whose probabilities nobody reads
+        during fit() (fused cross-entropy + metrics computed by the same kernel)."""
+        chain = []        # (layer, its only consumer layer or None)
+        if getattr(self, "_seq", None):
+            seq = [l for l in self._seq if not isinstance(l, L.InputLayer)]
+            chain = list(zip(seq, seq[1:] + [None]))
+            last = seq[-1] if seq else None
+        elif self._nodes:
+            consumers: dict = {}
+            for t in self._nodes:
+                for i in t.inputs:
+                    consumers.setdefault(id(i), []).append(t)
+            outs = {id(o) for o in self._outputs}
+            for t in self._nodes:
+                cons = consumers.get(id(t), [])
+                nxt = cons[0].layer if (len(cons) == 1 and id(t) not in outs and len(cons[0].inputs) == 1) else None
+                chain.append((t.layer, nxt))
+            last = self._outputs[0].layer if len(self._outputs) == 1 else None
+        else:
+            last = None
+        uses: dict = {}
+        for layer, _n in chain:
+            uses[id(layer)] = uses.get(id(layer), 0) + 1
+        for layer, nxt in chain:
+            if isinstance(layer, L.Dense):
+                layer._fused_dropout = nxt if (isinstance(nxt, L.Dropout) and layer.activation_name == "relu"
+                                               and uses.get(id(layer)) == 1 and uses.get(id(nxt)) == 1) else None
+        ok = (isinstance(last, L.Dense) and last.activation_name == "softmax"
+              and isinstance(self.loss, losses_mod.SparseCategoricalCrossentropy) and not self.loss.from_logits
+              and all(m.from_fused_xent for m in self._metrics) and self._weighted_targets is None
+              and self.device.type == "cuda")
+        if os.environ.get("TFC_LOGITS_ONLY", "1") == "0":
+            ok = False
+        object.__setattr__(self, "_logits_only_layer", last if ok else None)
 
     # -- loss / metrics -----------------------------------------------------------------------
     def _loss_and_metrics(self, out, y, global_batch, aux):
@@ -394,7 +432,8 @@ class Model(nn.Module):
         if weights is None and isinstance(self.loss, losses_mod.SparseCategoricalCrossentropy) and out.dim() == 2:
             logits = self.loss.logits(out)
             if logits is not None:
-                loss = ops.softmax_cross_entropy(logits, y.reshape(-1), grad_scale=inv, stats=aux)
+                loss = ops.softmax_cross_entropy(logits, y.reshape(-1), grad_scale=inv, stats=aux, count=True,
+                                                 unit_grad=True)
                 fused = True
         if not fused:
             per = self.loss.per_sample(y, out.float() if out.dtype != torch.float32 else out)
@@ -413,7 +452,8 @@ class Model(nn.Module):
                 aux[AUX_LOSS] += penalty.detach() * n
             loss = loss + penalty * (n * inv)
         with torch.no_grad():
-            aux[AUX_COUNT] += float(out.shape[0])
+            if not fused:                     # the fused cross-entropy kernel counts its rows itself
+                aux[AUX_COUNT] += float(out.shape[0])
             for i, m in enumerate(self._metrics):
                 if fused and m.from_fused_xent:
                     continue
@@ -485,8 +525,14 @@ class Model(nn.Module):
     def _train_step(self, xb, yb, global_batch=None):
         eng = self._engine
         eng.begin_step(self._aux_len())
+        lo = getattr(self, "_logits_only_layer", None) if self._weighted_targets is None else None
         with nvtx_range("forward"):
-            out = self.call(xb, training=True)
+            if lo is not None:
+                L.LOGITS_ONLY["on"], L.LOGITS_ONLY["layer"] = True, lo
+            try:
+                out = self.call(xb, training=True)
+            finally:
+                L.LOGITS_ONLY["on"], L.LOGITS_ONLY["layer"] = False, None
         if global_batch is None:
             global_batch = out.shape[0] * eng.world
         with nvtx_range("loss"):

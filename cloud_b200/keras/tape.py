@@ -24,7 +24,7 @@ class GradientTape:
         from ..parallel import engine as engine_mod
         for eng in engine_mod.live_engines():
             if not eng.in_step:
-                eng.begin_step()
+                eng.begin_step(direct=False)     # autograd.grad returns gradients: nothing may bypass it
         return self
 
     def __exit__(self, *exc):

@@ -11,7 +11,7 @@ Reference parity: these are the ops the reference makes TensorFlow execute on th
 from ._lib import KernelsUnavailable, kernels, runtime, check  # noqa: F401
 from .dense import gemm, dense, dense_reference  # noqa: F401
 from .loss import softmax_cross_entropy, softmax_cross_entropy_reference  # noqa: F401
-from .elementwise import dropout, relu_bwd_bias_grad, normalize_u8_images, normalize_u8_images_s2d  # noqa: F401
+from .elementwise import dropout, dropout_plan, relu_bwd_bias_grad, normalize_u8_images, normalize_u8_images_s2d  # noqa: F401
 from .optim import FlatOptimizerState, optim_flat, optim_tick, OPT_CODES, make_hyper  # noqa: F401
 
 from .bn import batch_norm_nhwc, bn_available, fork as bn_fork  # noqa: F401,E402

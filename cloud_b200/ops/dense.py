@@ -10,6 +10,8 @@ README.md:71-75 (ops K1, K2, K3 of SURVEY.md section 2.5).
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.nn.functional as F
 
@@ -21,6 +23,8 @@ GEMM_ACCUM = 4
 GEMM_SOFTMAX = 8
 
 _launches = 0
+_DIRECT_W = os.environ.get("TFC_DENSE_DIRECT_W", "1") != "0"
+_DIRECT_B = os.environ.get("TFC_DENSE_DIRECT_B", "1") != "0"
 
 
 def launches() -> int:
@@ -177,20 +181,46 @@ def _pad_cols(t: torch.Tensor, mult: int = 8) -> torch.Tensor:
     return F.pad(t, (0, r))
 
 
+def _padded_empty(m: int, n: int, device, dtype=torch.bfloat16) -> torch.Tensor:
+    """An [m, n] view of an [m, ceil8(n)] buffer: its row pitch is a multiple of 16 bytes, so TMA
+    can load and store it - no pad / un-pad copies around a GEMM whose width is not a multiple of 8."""
+    n8 = (n + 7) // 8 * 8
+    buf = torch.empty((m, n8), dtype=dtype, device=device)
+    return buf if n8 == n else buf[:, :n]
+
+
+def _tma_ok(t: torch.Tensor) -> bool:
+    return t.dim() == 2 and t.stride(1) == 1 and t.stride(0) % 8 == 0 and t.data_ptr() % 16 == 0
+
+
 class _DenseFn(torch.autograd.Function):
+    """``act(x @ w.T + b)`` (+ inverted dropout after a ReLU).  Backward in three kernels: ReLU mask
+    (x dropout scale) + bias gradient in one pass, input gradient, and the weight gradient stored
+    straight into the engine's gradient arena when the parameter lives there."""
+
     @staticmethod
-    def forward(ctx, x, w, b, activation):
-        from .elementwise import relu_bwd_bias_grad  # noqa: F401  (backward dependency)
+    def forward(ctx, x, w, b, activation, drop):
         x2 = x.reshape(-1, x.shape[-1])
         if x2.dtype != torch.bfloat16:
             x2 = x2.to(torch.bfloat16)
-        x2 = _pad_cols(x2)
         wk = w if w.dtype == torch.bfloat16 else w.to(torch.bfloat16)
-        wk = _pad_cols(wk)
-        fused_softmax = activation == "softmax" and w.shape[0] <= 256
-        y = gemm(x2, wk, bias=b, relu=(activation == "relu"), softmax=fused_softmax)
+        if x2.shape[1] % 8 or not _tma_ok(x2):
+            x2 = _pad_cols(x2)           # zero-filled up to a multiple of 8 columns (a copy)
+        if wk.shape[1] % 8 or not _tma_ok(wk):
+            wk = _pad_cols(wk)
+        M, N = x2.shape[0], w.shape[0]
+        fused_softmax = activation == "softmax" and N <= 256
+        y = gemm(x2, wk, bias=b, relu=(activation == "relu"), softmax=fused_softmax,
+                 out=_padded_empty(M, N, x2.device))
         if activation == "softmax" and not fused_softmax:
             y = torch.softmax(y.float(), dim=-1).to(torch.bfloat16)  # row wider than one tile
+        ctx.drop_scale = 1.0
+        if drop is not None and activation == "relu":
+            from .elementwise import _dropout_apply, _step
+            p, seed, offset = drop
+            step = _step["tensor"] if (_step["tensor"] is not None and _step["tensor"].device == y.device) else None
+            y = _dropout_apply(y, p, seed, offset, step)
+            ctx.drop_scale = 1.0 / (1.0 - p)
         ctx.activation = activation
         ctx.x_shape = x.shape
         ctx.in_features = w.shape[1]
@@ -198,29 +228,43 @@ class _DenseFn(torch.autograd.Function):
         ctx.w_dtype = w.dtype
         ctx.b_dtype = b.dtype if b is not None else None
         ctx.x_dtype = x.dtype
+        ctx.wparam, ctx.bparam = w, b
         ctx.save_for_backward(x2, wk, y if activation in ("relu", "softmax") else None)
-        return y.reshape(*x.shape[:-1], w.shape[0])
+        return y.reshape(*x.shape[:-1], N)
 
     @staticmethod
     def backward(ctx, dy):
         from .elementwise import relu_bwd_bias_grad
         x2, wk, y = ctx.saved_tensors
         N = wk.shape[0]
+        w, b = ctx.wparam, ctx.bparam
         dy2 = dy.reshape(-1, N)
         if dy2.dtype != torch.bfloat16:
             dy2 = dy2.to(torch.bfloat16)
-        if not dy2.is_contiguous():
-            dy2 = dy2.contiguous()
+        if not _tma_ok(dy2):
+            padded = _padded_empty(dy2.shape[0], N, dy2.device)
+            padded.copy_(dy2)
+            dy2 = padded
+        need_db = ctx.has_bias and ctx.needs_input_grad[2]
+        # the bias gradient goes straight into the engine's fp32 gradient arena when it exposes one
+        direct_b = need_db and _DIRECT_B and getattr(b, "_cb2_direct_grad", False) and b.grad is not None \
+            and b.grad.dtype == torch.float32 and b.grad.is_contiguous()
+        db = None
         if ctx.activation == "softmax":
             yf = y.float()
-            dz = (yf * (dy2.float() - (dy2.float() * yf).sum(-1, keepdim=True))).to(torch.bfloat16)
-            db = dz.float().sum(0) if ctx.has_bias else None
+            dzf = yf * (dy2.float() - (dy2.float() * yf).sum(-1, keepdim=True))
+            dz = _padded_empty(dy2.shape[0], N, dy2.device)
+            dz.copy_(dzf)
+            if need_db:
+                db = dzf.sum(0)
+                if direct_b:
+                    b.grad.add_(db)
         else:
-            need_db = ctx.has_bias and ctx.needs_input_grad[2]
-            dz, db = relu_bwd_bias_grad(dy2, y if ctx.activation == "relu" else None,
-                                        want_db=need_db)
-        # pitch padded to a multiple of 8 for TMA; the logical width stays N (OOB rows/cols read 0)
-        dz = _pad_cols(dz)[:, :N]
+            dz, db = relu_bwd_bias_grad(dy2, y if ctx.activation == "relu" else None, want_db=need_db,
+                                        scale=ctx.drop_scale, db_out=b.grad if direct_b else None)
+        if direct_b:
+            b._cb2_grad_written(b)
+            db = None
         dx = dw = None
         if ctx.needs_input_grad[0]:
             # dX[M,K] = dZ[M,N] @ W[N,K] : B is stored [reduce=N, K] -> MN-major
@@ -228,31 +272,44 @@ class _DenseFn(torch.autograd.Function):
             dx = dx[:, :ctx.in_features].reshape(ctx.x_shape).to(ctx.x_dtype)
         if ctx.needs_input_grad[1]:
             # dW[N,K] = dZ^T[N,M] @ X[M,K] : both stored [reduce=M, *] -> MN-major
-            dw = gemm(dz, x2, a_mn=True, b_mn=True,
-                      out_dtype=torch.float32 if ctx.w_dtype == torch.float32 else torch.bfloat16)
-            dw = dw[:N, :ctx.in_features]
-            if dw.dtype != ctx.w_dtype:
-                dw = dw.to(ctx.w_dtype)
+            direct_w = (_DIRECT_W and getattr(w, "_cb2_direct_grad", False) and w.grad is not None
+                        and w.grad.dtype == torch.bfloat16 and w.grad.dim() == 2 and _tma_ok(w.grad)
+                        and x2.shape[1] == ctx.in_features and not getattr(w, "_cb2_grad_stored", False))
+            if direct_w:
+                # the arena is zero at this point of the step (the bucket kernel zeroes what it
+                # reduced), and this is the only writer of this parameter's gradient: a plain store
+                gemm(dz, x2, a_mn=True, b_mn=True, out=w.grad)
+                w._cb2_grad_written(w)
+            else:
+                dw = gemm(dz, x2, a_mn=True, b_mn=True,
+                          out_dtype=torch.float32 if ctx.w_dtype == torch.float32 else torch.bfloat16)
+                dw = dw[:N, :ctx.in_features]
+                if dw.dtype != ctx.w_dtype:
+                    dw = dw.to(ctx.w_dtype)
         if db is not None and ctx.b_dtype is not None and db.dtype != ctx.b_dtype:
             db = db.to(ctx.b_dtype)
-        return dx, dw, db, None
+        return dx, dw, db, None, None
 
 
 def dense(x: torch.Tensor, w: torch.Tensor, b: torch.Tensor | None = None,
-          activation: str | None = None) -> torch.Tensor:
+          activation: str | None = None, dropout: tuple | None = None) -> torch.Tensor:
     """``activation(x @ w.T + b)`` with ``w`` in torch layout ``[out, in]``.
 
     CUDA: bf16 tcgen05 GEMM with fused epilogue (output bf16).  CPU: PyTorch in the input dtype.
+    ``dropout = (rate, seed, offset)``: inverted dropout behind a ReLU, undone in backward by the
+    same pass that applies the ReLU mask and reduces the bias gradient.
     """
     if activation not in (None, "linear", "relu", "softmax"):
         raise ValueError(f"unsupported fused activation: {activation}")
     if activation == "linear":
         activation = None
     if x.is_cuda:
-        return _DenseFn.apply(x, w, b, activation)
+        return _DenseFn.apply(x, w, b, activation, dropout)
     y = F.linear(x, w.to(x.dtype), None if b is None else b.to(x.dtype))
     if activation == "relu":
         y = torch.relu(y)
     elif activation == "softmax":
         y = torch.softmax(y, dim=-1)
+    if dropout is not None:
+        y = F.dropout(y, dropout[0], training=True)
     return y

@@ -24,27 +24,45 @@ def _stream() -> int:
 
 
 def relu_bwd_bias_grad(dy: torch.Tensor, y: torch.Tensor | None, want_db: bool = True,
-                       db_dtype: torch.dtype = torch.float32):
-    """Returns ``(dz, db)`` with ``dz = dy * (y > 0)`` (``dz = dy`` if ``y`` is None) and
-    ``db = dz.sum(0)``; one pass over ``dy``."""
+                       db_dtype: torch.dtype = torch.float32, scale: float = 1.0,
+                       db_out: torch.Tensor | None = None):
+    """Returns ``(dz, db)`` with ``dz = scale * dy * (y > 0)`` (``dz = scale * dy`` if ``y`` is None)
+    and ``db = dz.sum(0)``; one pass over ``dy``.  ``db_out`` (fp32): the sums are ADDED into it
+    (a gradient arena) and ``db`` comes back as None.  Row pitches may be padded (unit inner stride)."""
     global _launches
     M, N = dy.shape
     if not dy.is_cuda:
         dz = dy if y is None else torch.where(y > 0, dy, torch.zeros_like(dy))
-        return dz, (dz.float().sum(0).to(db_dtype) if want_db else None)
-    if y is None and not want_db:
+        if scale != 1.0:
+            dz = dz * scale
+        db = dz.float().sum(0).to(db_dtype) if want_db else None
+        if db_out is not None and db is not None:
+            db_out.add_(db)
+            db = None
+        return dz, db
+    if y is None and not want_db and scale == 1.0:
         return dy, None
     if dy.dtype != torch.bfloat16:
         raise TypeError("relu_bwd_bias_grad expects bfloat16 gradients")
-    dz = torch.empty_like(dy) if y is not None else dy
-    db = torch.empty(N, dtype=db_dtype, device=dy.device) if want_db else None
-    rc = _lib.kernels().cb2_relu_bwd_bias_grad(
-        dy.data_ptr(), None if y is None else y.data_ptr(),
-        dz.data_ptr() if y is not None else None, None if db is None else db.data_ptr(),
-        0 if db_dtype == torch.float32 else 1, M, N, dy.stride(0), 0, _stream())
+    if dy.stride(1) != 1 or (y is not None and (y.stride(1) != 1 or y.stride(0) != dy.stride(0))):
+        dy = dy.contiguous()
+        y = None if y is None else y.contiguous()
+    write_dz = y is not None or scale != 1.0
+    dz = torch.empty_strided(dy.shape, dy.stride(), dtype=dy.dtype, device=dy.device) if write_dz else dy
+    db = None
+    if want_db:
+        db = db_out if db_out is not None else torch.empty(N, dtype=db_dtype, device=dy.device)
+    lib = _lib.kernels()
+    lib.cb2_relu_bwd_bias_grad_ex.restype = ctypes.c_int
+    lib.cb2_relu_bwd_bias_grad_ex.argtypes = [ctypes.c_void_p] * 4 + [ctypes.c_int] * 5 + [ctypes.c_float,
+                                                                                       ctypes.c_void_p]
+    rc = lib.cb2_relu_bwd_bias_grad_ex(
+        dy.data_ptr(), None if y is None else y.data_ptr(), dz.data_ptr() if write_dz else None,
+        None if db is None else db.data_ptr(), 0 if (db is None or db.dtype == torch.float32) else 1, M, N,
+        dy.stride(0), 1 if db_out is not None else 0, float(scale), _stream())
     _lib.check(rc, "relu_bwd_bias_grad")
     _launches += 1
-    return dz, db
+    return dz, (None if db_out is not None else db)
 
 
 _step = {"tensor": None}
@@ -89,6 +107,16 @@ def _dropout_apply(x, p, seed, offset, step=None):
 
 
 _dropout_counter = {"offset": 0}
+
+
+def dropout_plan(numel: int, p: float, seed: int | None = None) -> tuple:
+    """``(rate, seed, offset)`` for a dropout over ``numel`` elements, taking its stretch of the
+    Philox counter exactly like ``dropout`` would (for kernels that apply the mask themselves)."""
+    if seed is None:
+        seed = torch.initial_seed() & 0xFFFFFFFFFFFFFFFF
+    offset = _dropout_counter["offset"]
+    _dropout_counter["offset"] += (numel + 3) // 4
+    return float(p), int(seed), int(offset)
 
 
 def dropout(x: torch.Tensor, p: float, training: bool = True, seed: int | None = None,

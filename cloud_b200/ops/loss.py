@@ -9,6 +9,8 @@ Reference workload: ``loss='sparse_categorical_crossentropy'`` + ``metrics=['acc
 """
 from __future__ import annotations
 
+import ctypes
+
 import torch
 import torch.nn.functional as F
 
@@ -36,42 +38,52 @@ def softmax_cross_entropy_reference(logits, labels, grad_scale=None):
 
 class _XentFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, logits, labels, grad_scale, stats):
+    def forward(ctx, logits, labels, grad_scale, stats, add_count, unit_grad):
         global _launches
         B, C = logits.shape
-        if not logits.is_contiguous():
+        if logits.stride(1) != 1:
             logits = logits.contiguous()
-        dlogits = torch.empty_like(logits)
-        if stats is None:
-            stats = torch.zeros(2, dtype=torch.float32, device=logits.device)
-        before = stats[0].clone()
+        # same (possibly padded) row pitch as the logits: the gradient goes into the weight- and
+        # input-gradient GEMMs as it is
+        dlogits = torch.empty_strided(logits.shape, logits.stride(), dtype=logits.dtype, device=logits.device)
+        loss = torch.zeros((), dtype=torch.float32, device=logits.device)
         lib = _lib.kernels()
+        lib.cb2_softmax_xent_ex.restype = ctypes.c_int
+        lib.cb2_softmax_xent_ex.argtypes = [ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 4 + \
+            [ctypes.c_int] * 3 + [ctypes.c_float, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
         dt = 1 if logits.dtype == torch.bfloat16 else 0
-        rc = lib.cb2_softmax_xent(logits.data_ptr(), dt, labels.data_ptr(), dlogits.data_ptr(), None,
-                                  stats.data_ptr(), B, C, logits.stride(0), float(grad_scale),
-                                  torch.cuda.current_stream().cuda_stream)
+        rc = lib.cb2_softmax_xent_ex(logits.data_ptr(), dt, labels.data_ptr(), dlogits.data_ptr(), None,
+                                     None if stats is None else stats.data_ptr(), B, C, logits.stride(0),
+                                     float(grad_scale), loss.data_ptr(),
+                                     int(bool(add_count) and stats is not None),
+                                     torch.cuda.current_stream().cuda_stream)
         _lib.check(rc, "softmax_xent")
         _launches += 1
         ctx.save_for_backward(dlogits)
         ctx.grad_scale = grad_scale
+        ctx.unit_grad = bool(unit_grad)
         # mean loss over the *global* batch this call was scaled for
-        return (stats[0] - before) * grad_scale
+        return loss
 
     @staticmethod
     def backward(ctx, g):
         (dlogits,) = ctx.saved_tensors
-        # g is 1 in the training loop; honour it anyway (one tiny multiply if it is not 1)
-        return dlogits * g.to(dlogits.dtype), None, None, None
+        if ctx.unit_grad:        # the caller differentiates the loss itself: d loss / d loss = 1
+            return dlogits, None, None, None, None, None
+        return dlogits * g.to(dlogits.dtype), None, None, None, None, None
 
 
 def softmax_cross_entropy(logits: torch.Tensor, labels: torch.Tensor,
                           grad_scale: float | None = None,
-                          stats: torch.Tensor | None = None) -> torch.Tensor:
+                          stats: torch.Tensor | None = None, count: bool = False,
+                          unit_grad: bool = False) -> torch.Tensor:
     """Mean sparse softmax cross-entropy with fused backward.
 
     ``grad_scale`` defaults to ``1/batch`` (per-replica callers pass ``1/global_batch``).  If
     ``stats`` (fp32[>=2], device) is given, the summed loss and the number of correct arg-max
-    predictions are *accumulated* into ``stats[0]`` and ``stats[1]``.
+    predictions are *accumulated* into ``stats[0]`` and ``stats[1]`` (and, with ``count``, the number
+    of rows into ``stats[2]``).  ``unit_grad``: the caller promises to call ``backward()`` on this
+    loss (or on a sum it is a plain term of), so the stored gradient is returned without a multiply.
     """
     if logits.dim() != 2:
         logits = logits.reshape(-1, logits.shape[-1])
@@ -83,11 +95,13 @@ def softmax_cross_entropy(logits: torch.Tensor, labels: torch.Tensor,
             logits = logits.float()
         if labels.dtype != torch.int64:
             labels = labels.long()
-        return _XentFn.apply(logits, labels, float(grad_scale), stats)
+        return _XentFn.apply(logits, labels, float(grad_scale), stats, count, unit_grad)
     z = logits.float()
     loss_sum = F.cross_entropy(z, labels.long(), reduction="sum")
     if stats is not None:
         with torch.no_grad():
             stats[0] += loss_sum.detach()
             stats[1] += (z.argmax(-1) == labels).sum().float()
+            if count:
+                stats[2] += float(z.shape[0])
     return loss_sum * grad_scale

@@ -129,6 +129,8 @@ class DPEngine:
         self._in_step = False
         self._aux_pending = 0
         self._aux_done = 0
+        self._direct = communicator.device.type == "cuda"
+        self._written = set()
         self._master_exact = set()
         self._fault = None
         fault = os.environ.get("TFC_FAULT")
@@ -335,6 +337,12 @@ class DPEngine:
         def hook(_p):
             if not self._in_step:
                 return
+            # once per parameter and step: a kernel that wrote the gradient itself reports it here,
+            # and autograd's post-accumulate hook may still fire for the same parameter afterwards
+            key = id(_p)
+            if key in self._written:
+                return
+            self._written.add(key)
             b = self.groups[gi].buckets[bi]
             b.ready += 1
             if b.ready == b.n_params and not b.launched:
@@ -453,12 +461,22 @@ class DPEngine:
             self.opt.lr = float(lr)
             self.hyper[0:1].fill_(float(lr))
 
-    def begin_step(self, n_aux: int = 0) -> None:
+    def begin_step(self, n_aux: int = 0, direct: bool = True) -> None:
         """Call before backward: arms the bucket hooks and advances the step counter.  ``n_aux``:
-        how many metric scalars of ``comm.aux`` the step wants summed over the replicas."""
+        how many metric scalars of ``comm.aux`` the step wants summed over the replicas.
+        ``direct``: kernels may write gradients straight into the arena and report them through
+        ``_cb2_grad_written`` - true when the step ends in ``loss.backward()``; a GradientTape passes
+        False, because ``torch.autograd.grad`` hands gradients back instead of accumulating them."""
+        direct = bool(direct) and self.is_cuda
+        if direct != self._direct:
+            self._direct = direct
+            for g in self.groups:
+                for _n, p in g.params:
+                    p._cb2_direct_grad = direct
         self._aux_pending = n_aux if (self.is_cuda and self.groups and self.groups[0].ctx is not None
                                       and os.environ.get("TFC_AUX_IN_BUCKET", "1") != "0") else 0
         self._aux_done = 0
+        self._written = set()
         for g in self.groups:
             for b in g.buckets:
                 b.ready, b.launched = 0, False

@@ -50,7 +50,8 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 softmax_xent_kernel(const T* __restrict__ logits, const int64_t* __restrict__ labels,
                     T* __restrict__ dlogits, float* __restrict__ row_loss,
-                    float* __restrict__ stats, int B, int C, int ld, float grad_scale) {
+                    float* __restrict__ stats, int B, int C, int ld, float grad_scale,
+                    float* __restrict__ loss_out, int add_count) {
   const int warps_per_block = blockDim.x >> 5;
   const int lane = threadIdx.x & 31;
   float loss_acc = 0.f, hit_acc = 0.f;
@@ -99,11 +100,15 @@ softmax_xent_kernel(const T* __restrict__ logits, const int64_t* __restrict__ la
   __shared__ float sh[2][8];
   if (lane == 0) { sh[0][threadIdx.x >> 5] = loss_acc; sh[1][threadIdx.x >> 5] = hit_acc; }
   __syncthreads();
-  if (threadIdx.x == 0 && stats) {
+  if (threadIdx.x == 0) {
     float l = 0.f, h = 0.f;
     for (int w = 0; w < warps_per_block; ++w) { l += sh[0][w]; h += sh[1][w]; }
-    atomicAdd(stats + 0, l);
-    atomicAdd(stats + 1, h);
+    if (stats) {
+      atomicAdd(stats + 0, l);
+      atomicAdd(stats + 1, h);
+      if (add_count && blockIdx.x == 0) atomicAdd(stats + 2, static_cast<float>(B));
+    }
+    if (loss_out) atomicAdd(loss_out, l * grad_scale);     // this call's mean loss (zero on entry)
   }
 }
 
@@ -114,7 +119,7 @@ template <typename DB>
 __global__ void __launch_bounds__(256)
 relu_bwd_bias_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
                      __nv_bfloat16* __restrict__ dz, DB* __restrict__ db, int M, int N, int ld,
-                     int row_chunk, int accumulate) {
+                     int row_chunk, int accumulate, float scale) {
   const int col = blockIdx.x * 32 + (threadIdx.x & 31);
   const int r_lane = threadIdx.x >> 5;
   const int r0 = blockIdx.y * row_chunk;
@@ -123,7 +128,7 @@ relu_bwd_bias_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
   if (col < N) {
     for (int r = r0 + r_lane; r < r1; r += 8) {
       const size_t idx = static_cast<size_t>(r) * ld + col;
-      float g = __bfloat162float(dy[idx]);
+      float g = __bfloat162float(dy[idx]) * scale;
       if (y && !(__bfloat162float(y[idx]) > 0.f)) g = 0.f;
       if (dz) dz[idx] = __float2bfloat16(g);
       acc += g;
@@ -340,9 +345,9 @@ using namespace cb2;
 extern "C" const char* cb2_last_error(void) { return g_err; }
 extern "C" int cb2_version(void) { return 100; }
 
-extern "C" int cb2_softmax_xent(const void* logits, int dtype, const int64_t* labels, void* dlogits,
-                                float* row_loss, float* stats, int B, int C, int ld,
-                                float grad_scale, void* stream) {
+extern "C" int cb2_softmax_xent_ex(const void* logits, int dtype, const int64_t* labels, void* dlogits,
+                                   float* row_loss, float* stats, int B, int C, int ld, float grad_scale,
+                                   float* loss_out, int add_count, void* stream) {
   if (B <= 0 || C <= 0 || ld < C) {
     set_last_error("softmax_xent: bad shape B=%d C=%d ld=%d", B, C, ld);
     return CB2_ERR_ARG;
@@ -354,11 +359,11 @@ extern "C" int cb2_softmax_xent(const void* logits, int dtype, const int64_t* la
   if (dtype == CB2_DTYPE_F32)
     softmax_xent_kernel<float><<<blocks, 256, 0, st>>>(
         reinterpret_cast<const float*>(logits), labels, reinterpret_cast<float*>(dlogits), row_loss,
-        stats, B, C, ld, grad_scale);
+        stats, B, C, ld, grad_scale, loss_out, add_count);
   else if (dtype == CB2_DTYPE_BF16)
     softmax_xent_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>(
         reinterpret_cast<const __nv_bfloat16*>(logits), labels,
-        reinterpret_cast<__nv_bfloat16*>(dlogits), row_loss, stats, B, C, ld, grad_scale);
+        reinterpret_cast<__nv_bfloat16*>(dlogits), row_loss, stats, B, C, ld, grad_scale, loss_out, add_count);
   else {
     set_last_error("softmax_xent: unsupported dtype %d", dtype);
     return CB2_ERR_ARG;
@@ -366,9 +371,24 @@ extern "C" int cb2_softmax_xent(const void* logits, int dtype, const int64_t* la
   return check_cuda(cudaGetLastError(), "softmax_xent launch");
 }
 
+extern "C" int cb2_softmax_xent(const void* logits, int dtype, const int64_t* labels, void* dlogits,
+                                float* row_loss, float* stats, int B, int C, int ld, float grad_scale,
+                                void* stream) {
+  return cb2_softmax_xent_ex(logits, dtype, labels, dlogits, row_loss, stats, B, C, ld, grad_scale, nullptr,
+                             0, stream);
+}
+
+extern "C" int cb2_relu_bwd_bias_grad_ex(const void* dy, const void* y, void* dz, void* db, int db_dtype,
+                                         int M, int N, int ld, int accumulate, float scale, void* stream);
+
 extern "C" int cb2_relu_bwd_bias_grad(const void* dy, const void* y, void* dz, void* db,
                                       int db_dtype, int M, int N, int ld, int accumulate,
                                       void* stream) {
+  return cb2_relu_bwd_bias_grad_ex(dy, y, dz, db, db_dtype, M, N, ld, accumulate, 1.f, stream);
+}
+
+extern "C" int cb2_relu_bwd_bias_grad_ex(const void* dy, const void* y, void* dz, void* db, int db_dtype,
+                                         int M, int N, int ld, int accumulate, float scale, void* stream) {
   if (M <= 0 || N <= 0 || ld < N) {
     set_last_error("relu_bwd_bias_grad: bad shape M=%d N=%d ld=%d", M, N, ld);
     return CB2_ERR_ARG;
@@ -394,12 +414,12 @@ extern "C" int cb2_relu_bwd_bias_grad(const void* dy, const void* y, void* dz, v
     relu_bwd_bias_kernel<float><<<grid, 256, 0, st>>>(
         reinterpret_cast<const __nv_bfloat16*>(dy), reinterpret_cast<const __nv_bfloat16*>(y),
         reinterpret_cast<__nv_bfloat16*>(dz), reinterpret_cast<float*>(db), M, N, ld, row_chunk,
-        accumulate);
+        accumulate, scale);
   else
     relu_bwd_bias_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(
         reinterpret_cast<const __nv_bfloat16*>(dy), reinterpret_cast<const __nv_bfloat16*>(y),
         reinterpret_cast<__nv_bfloat16*>(dz), reinterpret_cast<__nv_bfloat16*>(db), M, N, ld,
-        row_chunk, 0);
+        row_chunk, 0, scale);
   return check_cuda(cudaGetLastError(), "relu_bwd_bias_grad launch");
 }
 

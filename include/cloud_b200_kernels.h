@@ -95,9 +95,20 @@ int cb2_softmax_xent(const void* logits, int dtype, const int64_t* labels, void*
                      float* row_loss, float* stats, int B, int C, int ld, float grad_scale,
                      void* stream);
 
+/* cb2_softmax_xent plus: loss_out (nullable, one float, zero on entry) += this call's summed loss x
+ * grad_scale; add_count != 0: stats[2] += B (the sample counter next to loss and hit count). */
+int cb2_softmax_xent_ex(const void* logits, int dtype, const int64_t* labels, void* dlogits,
+                        float* row_loss, float* stats, int B, int C, int ld, float grad_scale,
+                        float* loss_out, int add_count, void* stream);
+
 /* dz = dy * (y > 0) (nullable y => dz = dy), db[n] (+)= sum_m dz[m,n].  bf16 tensors. (K3) */
 int cb2_relu_bwd_bias_grad(const void* dy, const void* y, void* dz, void* db, int db_dtype, int M,
                            int N, int ld, int accumulate, void* stream);
+/* The same with dz = scale * dy * (y > 0): the backward of Dense + ReLU + Dropout in one pass, y
+ * being the DROPOUT output (zero where the unit was dropped or inactive) and scale = 1 / (1 - rate);
+ * dz nullable (bias gradient only). */
+int cb2_relu_bwd_bias_grad_ex(const void* dy, const void* y, void* dz, void* db, int db_dtype, int M,
+                              int N, int ld, int accumulate, float scale, void* stream);
 
 /* Philox dropout, mask recomputed from (seed, offset, *step_ptr) in backward:
  * y = x * keep / (1-p).  step_ptr (nullable) is a device float holding the training step, so a
