@@ -150,7 +150,7 @@ class File(Group):
             raise OSError(_err())
 
     def _add_dataset(self, path, arr):
-        arr = np.ascontiguousarray(arr)
+        arr = np.asarray(arr, order="C")        # (np.ascontiguousarray would turn a 0-d array into 1-d)
         if arr.dtype not in _NP_TO_DT:
             arr = arr.astype(np.float32)
         dims = (ctypes.c_uint64 * max(arr.ndim, 1))(*arr.shape)

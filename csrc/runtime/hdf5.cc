@@ -466,7 +466,22 @@ void parse_messages(const Reader& r, uint64_t a, uint64_t end, int* remaining, R
       case 0x0003: parse_datatype(r, body, &obj->dtype, &obj->elem_size); break;
       case 0x0008: {
         const int ver = r.at(body);
-        if (ver == 3) {
+        if (ver == 1 || ver == 2) {
+          // libhdf5 <= 1.6 (e.g. MATLAB R2008): version, dimensionality (= rank + 1), class, 5
+          // reserved bytes, data address, then `dimensionality` 32-bit sizes, the last one being the
+          // element size.  Only the contiguous class is read.
+          const int ndim = r.at(body + 1), cls = r.at(body + 2);
+          if (cls == 1 && ndim >= 1 && ndim <= 33) {
+            obj->data_addr = r.rd(body + 8, 8);
+            if (obj->data_addr != UNDEF) obj->data_addr += r.base;
+            uint64_t bytes = 1;
+            for (int i = 0; i < ndim; ++i) {
+              const uint64_t d = r.rd(body + 16 + 4 * i, 4);
+              bytes = (d != 0 && bytes > (1ull << 40) / d) ? (1ull << 40) : bytes * d;
+            }
+            obj->data_size = bytes;
+          }
+        } else if (ver == 3) {
           const int cls = r.at(body + 1);
           if (cls == 1) { obj->data_addr = r.rd(body + 2, 8); obj->data_size = r.rd(body + 10, 8);
                           if (obj->data_addr != UNDEF) obj->data_addr += r.base; }
@@ -644,8 +659,12 @@ void* cb2h5_reader_open(const char* filename) {
   r->base = r->rd(p, 8);
   if (r->base == UNDEF) r->base = 0;
   r->base += 0;
+  // End-of-file address: relative to the base address by the format specification, but files with a
+  // user block written by libhdf5 1.6/1.8 (e.g. MATLAB v7.3 files: 512-byte header, base = 512)
+  // store the absolute file size here - accept either reading, reject only a file that is shorter
+  // than both
   const uint64_t eof = r->rd(p + 16, 8);
-  if (eof != UNDEF && (eof > r->f.size() || r->base > r->f.size() - eof)) {
+  if (eof != UNDEF && eof > r->f.size()) {
     cb2rt::set_error("%s is truncated: the superblock says %llu bytes, the file has %zu", filename,
                      static_cast<unsigned long long>(eof + r->base), r->f.size());
     return nullptr;
