@@ -56,33 +56,98 @@ def worker(tuner_id, directory, study_id, max_trials, model_kind, epochs):
     return {"tuner": tuner_id, "trials": len(t.oracle.trials)}
 
 
+class _UtilSampler:
+    """Average SM utilisation of every GPU of the box while a run is in flight (NVML, 50 ms)."""
+
+    def __init__(self):
+        import threading
+        self.samples, self._stop, self.ok = [], threading.Event(), False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.handles = [pynvml.nvmlDeviceGetHandleByIndex(i) for i in range(pynvml.nvmlDeviceGetCount())]
+            self.ok = bool(self.handles)
+        except Exception:
+            pass
+        self.thread = threading.Thread(target=self._loop, daemon=True)
+
+    def _loop(self):
+        while not self._stop.is_set():
+            try:
+                self.samples.append([self.nv.nvmlDeviceGetUtilizationRates(h).gpu for h in self.handles])
+            except Exception:
+                pass
+            self._stop.wait(0.05)
+
+    def __enter__(self):
+        if self.ok:
+            self.thread.start()
+        return self
+
+    def __exit__(self, *exc):
+        self._stop.set()
+        if self.ok:
+            self.thread.join(timeout=2)
+
+    def per_gpu(self):
+        if not self.samples:
+            return None
+        n = len(self.samples)
+        return [round(sum(s[i] for s in self.samples) / n, 1) for i in range(len(self.samples[0]))]
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--trials", type=int, default=8)
     ap.add_argument("--model", default="mlp")
     ap.add_argument("--epochs", type=int, default=5)
     ap.add_argument("--skip-sequential", action="store_true")
+    ap.add_argument("--cold", action="store_true", help="one cold process per worker (no pre-warmed pool)")
     args = ap.parse_args()
-    from cloud_b200.tuner import TrialScheduler
+    from cloud_b200.tuner import TrialScheduler, WorkerPool
     root = tempfile.mkdtemp(prefix="tuner8_")
     os.environ["TFC_JOB_ROOT"] = os.path.join(root, "jobs")
-    out = {"bench": "tuner8", "model": args.model, "trials": args.trials}
+    out = {"bench": "tuner8", "model": args.model, "trials": args.trials, "epochs": args.epochs,
+           "workers": "cold processes" if args.cold else "pre-warmed pool"}
     sched = TrialScheduler()
     n = max(sched.num_gpus, 1)
-    t0 = time.perf_counter()
-    res = sched.run(worker, args=(os.path.join(root, "packed"), "packed", args.trials, args.model, args.epochs),
-                    num_workers=min(n, args.trials), study=("bench", "local", "CloudTuner_study_packed"))
-    out["packed_seconds"] = time.perf_counter() - t0
-    out["packed_workers"] = len(res)
-    out["packed_exit_codes"] = [r["exit_code"] for r in res]
-    if not args.skip_sequential:
-        seq = TrialScheduler(num_gpus=min(n, 1))
-        t0 = time.perf_counter()
-        res = seq.run(worker, args=(os.path.join(root, "seq"), "seq", args.trials, args.model, args.epochs),
-                      num_workers=1, study=("bench", "local", "CloudTuner_study_seq"))
-        out["sequential_seconds"] = time.perf_counter() - t0
-        out["sequential_exit_codes"] = [r["exit_code"] for r in res]
-        out["speedup"] = out["sequential_seconds"] / out["packed_seconds"]
+    workers = min(n, args.trials)
+    pool = None
+    if not args.cold:
+        pool = WorkerPool(num_workers=workers)
+        out["pool_start_seconds"] = pool.start_seconds           # paid once, all workers in parallel
+    try:
+        with _UtilSampler() as util:
+            t0 = time.perf_counter()
+            res = sched.run(worker, args=(os.path.join(root, "packed"), "packed", args.trials, args.model,
+                                          args.epochs),
+                            num_workers=workers, study=("bench", "local", "CloudTuner_study_packed"), pool=pool)
+            out["packed_seconds"] = time.perf_counter() - t0
+        out["packed_workers"] = len(res)
+        out["packed_exit_codes"] = [r["exit_code"] for r in res]
+        out["packed_gpu_util_percent"] = util.per_gpu()
+        if not args.skip_sequential:
+            # the same trials one after another on ONE worker (warm as well when the pool is used)
+            seq = TrialScheduler(num_gpus=min(n, 1))
+            seq_pool = None
+            if pool is not None:
+                class _One:                    # the first slot of the pool only
+                    slots, procs = pool.slots[:1], pool.procs
+                    submit = staticmethod(pool.submit)
+                seq_pool = _One()
+            t0 = time.perf_counter()
+            res = seq.run(worker, args=(os.path.join(root, "seq"), "seq", args.trials, args.model, args.epochs),
+                          num_workers=1, study=("bench", "local", "CloudTuner_study_seq"), pool=seq_pool)
+            out["sequential_seconds"] = time.perf_counter() - t0
+            out["sequential_exit_codes"] = [r["exit_code"] for r in res]
+            out["speedup"] = out["sequential_seconds"] / out["packed_seconds"]
+            if pool is not None:
+                out["speedup_incl_pool_start"] = (out["sequential_seconds"] + out["pool_start_seconds"]) / \
+                    (out["packed_seconds"] + out["pool_start_seconds"])
+    finally:
+        if pool is not None:
+            pool.close()
     print(json.dumps(out))
 
 

@@ -11,6 +11,18 @@ pending trial marked infeasible (``INVALID``) and its GPUs are handed to a repla
     sched = TrialScheduler(gpus_per_trial=1)
     results = sched.run(search_fn, num_workers=8)     # search_fn(tuner_id) builds a CloudTuner
                                                       # with a common study_id and calls .search()
+
+Starting a worker costs far more than a short trial (interpreter + ``import torch`` + CUDA context +
+loading the kernel library: seconds, against a 2 s MNIST trial), so workers can be kept warm:
+
+    with WorkerPool(num_workers=8) as pool:           # one pre-warmed process per GPU slot
+        sched.run(search_fn, num_workers=8, pool=pool)
+        sched.run(other_search, num_workers=8, pool=pool)      # no start-up this time
+
+A pool worker imports the framework, creates its CUDA context and loads the kernels once, then takes
+jobs from a spool directory until the pool is closed (or its parent dies).  A worker that crashes
+takes only its current job with it: the job reports a non-zero exit code (the scheduler marks the
+trial infeasible and frees the slot) and the slot gets a fresh worker on its next job.
 """
 from __future__ import annotations
 
@@ -36,6 +48,7 @@ class TrialScheduler:
         self.gpus_per_trial = max(int(gpus_per_trial), 1)
         self.max_restarts = max_restarts
         self.poll = poll
+        self._pool = None
 
     def slots(self, num_workers: int | None = None) -> list:
         """GPU id lists, one per concurrent worker; a GPU-less box gets CPU slots."""
@@ -48,10 +61,20 @@ class TrialScheduler:
 
     def run(self, target, args=(), kwargs=None, num_workers: int | None = None,
             study: tuple | None = None, env: dict | None = None, timeout: float | None = None,
-            log_dir: str | None = None) -> list:
+            log_dir: str | None = None, pool: "WorkerPool | None" = None) -> list:
         """Runs ``target(tuner_id, *args, **kwargs)`` in ``num_workers`` processes, at most one per
         GPU slot at a time.  ``study=(project_id, region, full_study_id)`` enables crash clean-up
         in the optimizer store.  Returns one record per worker."""
+        if pool is not None:
+            # the pool already holds its GPUs (and their leases) and its warm processes
+            slots = pool.slots
+            num_workers = num_workers or len(slots)
+            self._concurrent = min(num_workers, len(slots))
+            self._pool = pool
+            try:
+                return self._run(target, args, kwargs, num_workers, slots, study, env, timeout, log_dir)
+            finally:
+                self._pool = None
         slots = self.slots(num_workers)
         num_workers = num_workers or len(slots)
         self._concurrent = min(num_workers, len(slots))
@@ -108,7 +131,7 @@ class TrialScheduler:
                 job.update(proc=self._spawn(job, slots[slot], blob, log_dir, env),
                            started=time.time())
                 running.append(job)
-            time.sleep(self.poll)
+            time.sleep(min(self.poll, 0.02) if self._pool is not None else self.poll)
             for job in list(running):
                 rc = job["proc"].poll()
                 if rc is None:
@@ -132,6 +155,8 @@ class TrialScheduler:
         return done
 
     def _spawn(self, job, gpu_ids, blob, log_dir, env):
+        if self._pool is not None:
+            return self._pool.submit(job["slot"], blob, job["tuner_id"], log_dir)
         e = dict(os.environ)
         e.update(env or {})
         e["KERASTUNER_TUNER_ID"] = job["tuner_id"]
@@ -170,6 +195,236 @@ class TrialScheduler:
             pass
 
 
+def _worker_env(gpu_ids, slot, concurrent, env):
+    e = dict(os.environ)
+    e.update(env or {})
+    e["CUDA_VISIBLE_DEVICES"] = ",".join(str(g) for g in gpu_ids)
+    e["TFC_TRIAL_SLOT"] = str(slot)
+    share = str(max(1, (os.cpu_count() or 1) // max(1, concurrent)))
+    for k in ("OMP_NUM_THREADS", "MKL_NUM_THREADS"):
+        if k not in os.environ and k not in (env or {}):
+            e[k] = share
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        e.pop(k, None)
+    repo_root = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    e["PYTHONPATH"] = os.pathsep.join([repo_root, e.get("PYTHONPATH", "")])
+    return e
+
+
+class _PoolJob:
+    """What ``TrialScheduler._run`` needs from a process handle: ``poll()`` and ``kill()``."""
+
+    def __init__(self, pool, slot, path):
+        self.pool, self.slot, self.path = pool, slot, path
+
+    def poll(self):
+        done = self.path + ".done"
+        if os.path.exists(done):
+            try:
+                with open(done) as f:
+                    return int(json.load(f).get("exit_code", 1))
+            except (ValueError, OSError):
+                return None                    # still being written
+        proc = self.pool.procs[self.slot]
+        rc = proc.poll() if proc is not None else 1
+        if rc is not None:                     # the worker died under this job
+            self.pool.procs[self.slot] = None
+            return rc if rc != 0 else 1
+        return None
+
+    def kill(self):
+        proc = self.pool.procs[self.slot]
+        if proc is not None:
+            proc.kill()
+
+
+class WorkerPool:
+    """Pre-warmed trial workers, one per GPU slot, for any number of ``TrialScheduler.run`` calls.
+
+    ``start_seconds`` is what the warm-up cost (all workers start in parallel); ``close()`` - or
+    leaving the ``with`` block - stops them and returns the GPU leases."""
+
+    def __init__(self, num_workers: int | None = None, num_gpus: int | None = None, gpus_per_trial: int = 1,
+                 env: dict | None = None, log_dir: str | None = None, warm_timeout: float = 300.0):
+        sched = TrialScheduler(num_gpus=num_gpus, gpus_per_trial=gpus_per_trial)
+        self.slots = sched.slots(num_workers)
+        self.env = dict(env or {})
+        self.dir = log_dir or tempfile.mkdtemp(prefix="cb2_pool_")
+        os.makedirs(self.dir, exist_ok=True)
+        self._lease_owner = None
+        wanted = sum(len(s) for s in self.slots)
+        if wanted and os.environ.get("TFC_GPU_LEASES", "1") != "0":
+            from ..launch import leases
+            self._lease_owner = "trial_pool_{}_{}".format(os.getpid(), int(time.time() * 1000) % 100000)
+            free = len(leases.snapshot(sched.num_gpus)["free"])
+            n = min(len(self.slots), max(1, free // sched.gpus_per_trial))
+            got = leases.acquire(self._lease_owner, n * sched.gpus_per_trial, sched.num_gpus,
+                                 timeout=float(os.environ.get("TFC_QUEUE_TIMEOUT", "0") or 0) or None)
+            self.slots = [got[i * sched.gpus_per_trial:(i + 1) * sched.gpus_per_trial] for i in range(n)]
+        self.procs = [None] * len(self.slots)
+        self._seq = 0
+        t0 = time.time()
+        try:
+            for i in range(len(self.slots)):
+                self._start(i)
+            self._wait_ready(range(len(self.slots)), warm_timeout)
+        except BaseException:
+            self.close()
+            raise
+        self.start_seconds = time.time() - t0
+
+    def _slot_dir(self, i):
+        d = os.path.join(self.dir, "slot{}".format(i))
+        os.makedirs(d, exist_ok=True)
+        return d
+
+    def _start(self, i):
+        d = self._slot_dir(i)
+        for name in ("ready", "stop"):
+            try:
+                os.unlink(os.path.join(d, name))
+            except OSError:
+                pass
+        log = open(os.path.join(d, "worker.log"), "ab", buffering=0)
+        self.procs[i] = subprocess.Popen(
+            [sys.executable, "-m", "cloud_b200.tuner.scheduler", "--serve", d, str(os.getpid())],
+            env=_worker_env(self.slots[i], i, len(self.slots), self.env), stdout=log, stderr=subprocess.STDOUT)
+
+    def _wait_ready(self, which, timeout):
+        t0 = time.time()
+        for i in which:
+            flag = os.path.join(self._slot_dir(i), "ready")
+            while not os.path.exists(flag):
+                if self.procs[i].poll() is not None:
+                    raise RuntimeError("trial worker {} died while warming up (see {})".format(
+                        i, os.path.join(self._slot_dir(i), "worker.log")))
+                if time.time() - t0 > timeout:
+                    raise TimeoutError("trial workers did not get ready within {} s".format(timeout))
+                time.sleep(0.02)
+
+    def submit(self, slot, blob, tuner_id, log_dir=None):
+        if self.procs[slot] is None or self.procs[slot].poll() is not None:
+            self._start(slot)                  # replacement for a worker that died: a cold start
+            self._wait_ready([slot], 300.0)
+        self._seq += 1
+        path = os.path.join(self._slot_dir(slot), "job{:06d}".format(self._seq))
+        spec = {"blob": blob, "tuner_id": tuner_id,
+                "log": os.path.join(log_dir or self._slot_dir(slot), tuner_id + ".log")}
+        with open(path + ".tmp", "w") as f:
+            json.dump(spec, f)
+        os.rename(path + ".tmp", path + ".job")    # appears atomically
+        return _PoolJob(self, slot, path)
+
+    def close(self):
+        for i, proc in enumerate(self.procs):
+            if proc is None:
+                continue
+            try:
+                open(os.path.join(self._slot_dir(i), "stop"), "w").close()
+            except OSError:
+                pass
+        deadline = time.time() + 5
+        for proc in self.procs:
+            if proc is None:
+                continue
+            try:
+                proc.wait(timeout=max(0.1, deadline - time.time()))
+            except subprocess.TimeoutExpired:
+                proc.kill()
+        self.procs = [None] * len(self.procs)
+        if self._lease_owner:
+            from ..launch import leases
+            leases.release(self._lease_owner)
+            self._lease_owner = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+        return False
+
+
+def _serve_main(argv):
+    """Body of a pool worker: warm up once, then run the jobs that appear in the slot directory."""
+    import glob
+    d, parent = argv[0], int(argv[1])
+    t0 = time.time()
+    warm = {}
+    try:                                        # everything a trial would pay for on its first step
+        import torch
+        import cloud_b200  # noqa: F401
+        from cloud_b200 import keras as _keras  # noqa: F401
+        if torch.cuda.is_available():
+            torch.cuda.init()
+            torch.zeros(1, device="cuda").add_(1).item()
+            from cloud_b200.ops import _lib
+            _lib.kernels()
+            _lib.runtime()
+            warm["cuda"] = True
+    except Exception as e:                      # a broken environment shows up in the first job instead
+        warm["error"] = "{}: {}".format(type(e).__name__, e)
+    warm["seconds"] = time.time() - t0
+    with open(os.path.join(d, "ready.tmp"), "w") as f:
+        json.dump(warm, f)
+    os.rename(os.path.join(d, "ready.tmp"), os.path.join(d, "ready"))
+    while True:
+        if os.path.exists(os.path.join(d, "stop")):
+            return 0
+        try:
+            os.kill(parent, 0)                  # the pool's owner is gone: nobody will send jobs
+        except OSError:
+            return 0
+        jobs = sorted(glob.glob(os.path.join(d, "*.job")))
+        if not jobs:
+            time.sleep(0.01)
+            continue
+        job = jobs[0]
+        base = job[:-4]
+        with open(job) as f:
+            spec = json.load(f)
+        os.rename(job, base + ".running")
+        rc, result = 0, None
+        os.environ["KERASTUNER_TUNER_ID"] = spec["tuner_id"]
+        log = open(spec["log"], "ab", buffering=0)
+        out, err = os.dup(1), os.dup(2)
+        os.dup2(log.fileno(), 1)
+        os.dup2(log.fileno(), 2)
+        try:
+            with open(spec["blob"], "rb") as f:
+                target, args, kwargs = cloudpickle.loads(f.read())
+            result = target(spec["tuner_id"], *args, **kwargs)
+        except SystemExit as e:
+            rc = int(e.code or 0) if not isinstance(e.code, str) else 1
+        except BaseException:
+            import traceback
+            traceback.print_exc()
+            rc = 1
+        finally:
+            sys.stdout.flush()
+            sys.stderr.flush()
+            os.dup2(out, 1)
+            os.dup2(err, 2)
+            os.close(out)
+            os.close(err)
+            log.close()
+        try:                                    # leave the GPU as a fresh worker would find it
+            import gc
+            import torch
+            gc.collect()
+            if torch.cuda.is_available():
+                torch.cuda.empty_cache()
+        except Exception:
+            pass
+        try:
+            json.dumps(result)
+        except TypeError:
+            result = None
+        with open(base + ".done.tmp", "w") as f:
+            json.dump({"exit_code": rc, "result": result}, f)
+        os.rename(base + ".done.tmp", base + ".done")
+
+
 def _worker_main(argv):
     blob, tuner_id = argv
     with open(blob, "rb") as f:
@@ -184,4 +439,6 @@ def _worker_main(argv):
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "--serve":
+        sys.exit(_serve_main(sys.argv[2:]))
     sys.exit(_worker_main(sys.argv[1:]))
