@@ -829,13 +829,12 @@ class Model(nn.Module):
             prof = getattr(self, "_fit_profile", None)
             if prof and prof.get("steps"):
                 mon.observe(mon.DATA_WAIT, prof["wait_data_s"] / prof["steps"] * 1e6)
-            for us in eng.allreduce_host_us[-4096:]:
+            for us in eng.drain_allreduce_us()[-4096:]:
                 mon.observe(mon.ALLREDUCE_TIME, us)
-            del eng.allreduce_host_us[:]
             n_buckets = sum(len(g.buckets) for g in eng.groups)
             mon.increment(mon.BUCKET_LAUNCHES, steps * n_buckets)
-            if eng.world > 1:
-                nbytes = sum(g.total * (2 if g.dtype == torch.bfloat16 else 4) for g in eng.groups)
+            nbytes = sum(g.total * (2 if g.dtype == torch.bfloat16 else 4) for g in eng.groups)
+            if eng.world > 1 or eng.is_cuda:          # on one GPU: the bytes the fused kernel updates
                 mon.increment(mon.BYTES_REDUCED, steps * nbytes)
         except Exception:      # metrics must never break training
             pass

@@ -131,6 +131,8 @@ class DPEngine:
         self._aux_done = 0
         self._direct = communicator.device.type == "cuda"
         self._written = set()
+        self._bucket_events = []
+        self._time_buckets = communicator.device.type == "cuda" and os.environ.get("TFC_TIME_BUCKETS", "1") != "0"
         self._master_exact = set()
         self._fault = None
         fault = os.environ.get("TFC_FAULT")
@@ -509,11 +511,23 @@ class DPEngine:
             # the step's metric scalars are final before backward starts: they ride in the first
             # bucket kernel that is launched (no launch of their own, no extra barrier rounds)
             n_aux, self._aux_pending = self._aux_pending, 0
+            # device time of the bucket kernel for the metrics registry: a CUDA-event pair around it
+            # whenever the step runs eagerly (the steps before the CUDA graph is captured, and every
+            # step of a model that cannot be captured); inside a capture there is nothing to time
+            timed = self._time_buckets and not torch.cuda.is_current_stream_capturing()
+            if timed:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(self.comm_stream)
             self.comm.fused(g.ctx, algo=b.algo, opt=code, grad_dtype=g.dtype, param_dtype=g.dtype,
                             off=b.off, length=b.length, master=g.master, s1=g.s1, s2=g.s2,
                             state_off=s_off, hyper=self.hyper, zero_grads=True,
                             aux_len=n_aux, aux_out=self.aux_out if n_aux else None,
                             stream=self.comm_stream)
+            if timed:
+                e1.record(self.comm_stream)
+                self._bucket_events.append((e0, e1))
+                if len(self._bucket_events) > 4096:
+                    del self._bucket_events[:2048]
             if n_aux:
                 self._aux_done = n_aux
             return
@@ -635,6 +649,20 @@ class DPEngine:
         for (gi, name), v in keep.items():
             self.set_master_value(gi, name, v)
         self._master_exact = set()
+
+    def drain_allreduce_us(self) -> list:
+        """Times (us) of the fused all-reduce + optimizer calls since the last drain: device times
+        of the bucket kernels on GPU ranks (finished event pairs only - nothing is waited for),
+        host times of the synchronous shared-memory / gloo calls on CPU ranks."""
+        out, self.allreduce_host_us = self.allreduce_host_us, []
+        keep = []
+        for e0, e1 in self._bucket_events:
+            if e1.query():
+                out.append(e0.elapsed_time(e1) * 1e3)
+            else:
+                keep.append((e0, e1))
+        self._bucket_events = keep
+        return out
 
     def kernel_launches(self) -> int:
         return comm_mod.launches() + ops.optim.launches()

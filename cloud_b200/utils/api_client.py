@@ -7,16 +7,3 @@ from ..version import __version__
 
 def user_agent() -> str:
     return "cloud-b200/" + __version__
-
-
-class LocalRequest:
-    """A request envelope for the in-process services (job registry, local Vizier)."""
-
-    def __init__(self, method: str, body=None, headers=None):
-        self.method = method
-        self.body = body
-        self.headers = dict(headers or {})
-        self.headers["user-agent"] = user_agent()
-
-    def to_record(self) -> dict:
-        return {"method": self.method, "body": self.body, "headers": self.headers}

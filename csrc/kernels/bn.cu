@@ -689,10 +689,29 @@ extern "C" int cb2_bn_forward_static(const void* x, const void* residual, void* 
   }
   int rc = bn_check(M, C, "bn_forward_static");
   if (rc) return rc;
-  float* scratch = nullptr;
-  rc = bn_static_scratch_ptr(&scratch);
-  if (rc) return rc;
+  if (training != 0 && training != 1) {
+    // training == 2 of cb2_bn_forward means "the caller's scratch already holds the batch sums":
+    // there is no caller scratch here
+    set_last_error("bn_forward_static: training must be 0 (running statistics) or 1 (batch statistics), "
+                   "got %d", training);
+    return CB2_ERR_ARG;
+  }
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  float* scratch = nullptr;
+  if (training) {
+    // The array is per device and its address is looked up for the CURRENT device: a stream that
+    // belongs to another device would run the kernels there, on this device's address.
+    int cur = -1, sdev = -1;
+    CB2_CUDA_OK(cudaGetDevice(&cur));
+    if (st != nullptr && st != cudaStreamLegacy && st != cudaStreamPerThread &&
+        cudaStreamGetDevice(st, &sdev) == cudaSuccess && sdev != cur) {
+      set_last_error("bn_forward_static: the stream belongs to device %d but device %d is current; make "
+                     "the stream's device current before the call", sdev, cur);
+      return CB2_ERR_ARG;
+    }
+    rc = bn_static_scratch_ptr(&scratch);      // inference reads no scratch: no lookup then
+    if (rc) return rc;
+  }
   const int grid = bn_grid(M, C);
   if (training) {
     // the array still holds the previous call's partial sums: the part this call accumulates into

@@ -187,7 +187,9 @@ int cb2_bn_backward3(const void* dy, const void* dy2, const void* y, int y_is_ma
  * overlap on the GPU (different streams, or the same stream from racing host threads) corrupt
  * each other's statistics - serialise them.  The first call on each device looks up the array's
  * device address (cudaGetSymbolAddress, with that device current) and caches it; make that first
- * call before starting any stream capture. */
+ * call before starting any stream capture.  `training` is 0 (running statistics: the scratch is not
+ * touched at all) or 1 (batch statistics); 2 - caller-reduced sums - has no meaning without a caller
+ * scratch and is rejected.  `stream` must belong to the current device (checked). */
 int cb2_bn_static_scratch_max_channels(void);
 int cb2_bn_forward_static(const void* x, const void* residual /*nullable*/, void* y,
                           const float* gamma, const float* beta, float* run_mean, float* run_var,

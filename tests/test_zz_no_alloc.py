@@ -69,6 +69,17 @@ def _case(lib, N, C, HW, relu, with_res, seed):
                                (2e-2, 1e-4, 1e-4, 1e-3)):
         err = (g - w).abs()
         assert bool((err <= tol + tol * w.abs()).all()), f"{name}: max err {err.max().item():.4g}"
+    # and against plain fp32 PyTorch, not only against the sibling entry point
+    xf = x.float()
+    ref = torch.nn.functional.batch_norm(xf, None, None, gamma, beta, True, 0.0, 1e-5)
+    if res is not None:
+        ref = ref + res.float()
+    if relu:
+        ref = torch.relu(ref)
+    err = (got[0] - ref).abs()
+    assert bool((err <= 3e-2 + 2e-2 * ref.abs()).all()), f"vs fp32 oracle: max err {err.max().item():.4g}"
+    assert torch.allclose(got[1], 0.1 * xf.mean(0), atol=2e-3)                       # momentum 0.1 from zeros
+    assert torch.allclose(got[2], 0.9 + 0.1 * xf.var(0, unbiased=True), rtol=2e-2, atol=2e-3)
 
 
 def test_static_scratch_matches_caller_scratch_on_two_calls_in_a_row():
@@ -95,3 +106,25 @@ def test_static_scratch_rejects_sizes_beyond_its_limit():
     assert rc != 0
     msg = lib.cb2_last_error().decode()
     assert "2048" in msg and "scratch" in msg
+
+
+def test_static_entry_point_inference_mode_and_argument_checks():
+    """training = 0 applies the running statistics (the scratch is not involved); training = 2 - the
+    caller-reduced-sums mode of cb2_bn_forward - is refused because there is no caller scratch."""
+    lib = _abi()
+    dev = torch.device("cuda:0")
+    torch.manual_seed(4)
+    M, C = 300, 64
+    x = torch.randn(M, C, device=dev).to(torch.bfloat16)
+    gamma, beta = torch.rand(C, device=dev) + 0.5, torch.randn(C, device=dev)
+    rm, rv = torch.randn(C, device=dev) * 0.1, torch.rand(C, device=dev) + 0.5
+    y = torch.empty_like(x)
+    st = torch.cuda.current_stream().cuda_stream
+    args = (gamma.data_ptr(), beta.data_ptr(), rm.data_ptr(), rv.data_ptr(), None, None, None, M, C, 1e-5, 0.1, 0)
+    rc = lib.cb2_bn_forward_static(x.data_ptr(), None, y.data_ptr(), *args, 0, st)
+    assert rc == 0, lib.cb2_last_error().decode()
+    torch.cuda.synchronize()
+    ref = torch.nn.functional.batch_norm(x.float(), rm, rv, gamma, beta, False, 0.0, 1e-5)
+    assert (y.float() - ref).abs().max().item() < 3e-2 * max(1.0, ref.abs().max().item())
+    rc = lib.cb2_bn_forward_static(x.data_ptr(), None, y.data_ptr(), *args, 2, st)
+    assert rc != 0 and "training" in lib.cb2_last_error().decode()
