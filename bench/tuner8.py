@@ -16,10 +16,13 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 
 def worker(tuner_id, directory, study_id, max_trials, model_kind, epochs):
+    t_start = time.time()
+    marks = {}
     import numpy as np
     import cloud_b200 as tfc
     from cloud_b200.tuner import HyperParameters
     keras = tfc.keras
+    marks["import_s"] = time.time() - t_start
     tfc.distribute.experimental_set_strategy(tfc.distribute.OneDeviceStrategy("/gpu:0"))
     rng = np.random.RandomState(0)
     if model_kind == "mlp":
@@ -46,14 +49,17 @@ def worker(tuner_id, directory, study_id, max_trials, model_kind, epochs):
                       loss="sparse_categorical_crossentropy", metrics=["acc"])
             return m
         fit = dict(x=x, y=y, epochs=epochs, batch_size=128, verbose=0)
+    marks["data_s"] = time.time() - t_start
     hps = HyperParameters()
     hps.Float("learning_rate", 1e-4, 1e-2, sampling="log")
     hps.Int("num_layers", 2, 10)
     t = tfc.CloudTuner(build, project_id="bench", region="local", objective="acc", hyperparameters=hps,
                        max_trials=max_trials, study_id=study_id, directory=os.path.join(directory, tuner_id))
     t.tuner_id = tuner_id
+    marks["tuner_s"] = time.time() - t_start
     t.search(**fit)
-    return {"tuner": tuner_id, "trials": len(t.oracle.trials)}
+    marks["done_s"] = time.time() - t_start
+    return {"tuner": tuner_id, "trials": len(t.oracle.trials), "marks": {k: round(v, 3) for k, v in marks.items()}}
 
 
 class _UtilSampler:
@@ -125,6 +131,8 @@ def main():
                             num_workers=workers, study=("bench", "local", "CloudTuner_study_packed"), pool=pool)
             out["packed_seconds"] = time.perf_counter() - t0
         out["packed_workers"] = len(res)
+        out["packed_worker_marks"] = [(r.get("result") or {}).get("marks") for r in res]
+        out["packed_worker_seconds"] = [round(r["seconds"], 2) for r in res]
         out["packed_exit_codes"] = [r["exit_code"] for r in res]
         out["packed_gpu_util_percent"] = util.per_gpu()
         if not args.skip_sequential:

@@ -210,7 +210,7 @@ class DPEngine:
         if name == "auto":
             if nbytes <= min(cap1, int(os.environ.get("TFC_LL1_MAX_KB", "64")) << 10):
                 return comm_mod.ALGO_LL1
-            if nbytes <= min(cap2, int(os.environ.get("TFC_LL2_MAX_KB", "4096")) << 10):
+            if nbytes <= min(cap2, int(os.environ.get("TFC_LL2_MAX_KB", "2048")) << 10):
                 return comm_mod.ALGO_LL2
             if nbytes <= (1 << 20) and not cap1:
                 return comm_mod.ALGO_ONESHOT

@@ -149,6 +149,7 @@ class TrialScheduler:
                                         "restarts": job["restarts"] + 1})
                         continue
                 done.append({k: job[k] for k in ("index", "tuner_id", "slot", "exit_code", "seconds", "restarts")}
+                            | {"result": getattr(job["proc"], "result", None)}
                             | {"gpus": slots[job["slot"]],
                                "log": os.path.join(log_dir, job["tuner_id"] + ".log")})
         done.sort(key=lambda r: r["index"])
@@ -216,13 +217,16 @@ class _PoolJob:
 
     def __init__(self, pool, slot, path):
         self.pool, self.slot, self.path = pool, slot, path
+        self.result = None                     # what the target returned (JSON-able), once done
 
     def poll(self):
         done = self.path + ".done"
         if os.path.exists(done):
             try:
                 with open(done) as f:
-                    return int(json.load(f).get("exit_code", 1))
+                    rec = json.load(f)
+                self.result = rec.get("result")
+                return int(rec.get("exit_code", 1))
             except (ValueError, OSError):
                 return None                    # still being written
         proc = self.pool.procs[self.slot]

@@ -363,6 +363,36 @@ __device__ __forceinline__ uint4 ll_poll(const uint4* src, uint32_t e, unsigned 
   return make_uint4(a.x, a.z, b.x, b.z);
 }
 
+// One chunk from each of the WT-1 peers' slots: every load is issued before the first flag is
+// examined (independent requests overlap), and only the slots that were not complete are read again.
+template <int WT>
+__device__ __forceinline__ void ll_poll_all(uint4 (&out)[WT], const uint4* const (&src)[WT], int self,
+                                            uint32_t e, unsigned long long timeout_ns) {
+  uint4 a[WT], b[WT];
+  uint32_t pending = ((1u << WT) - 1u) & ~(1u << self);
+  SpinWait w;
+  while (true) {
+#pragma unroll
+    for (int p = 0; p < WT; ++p) {
+      if (pending & (1u << p)) {
+        asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(a[p].x), "=r"(a[p].y), "=r"(a[p].z), "=r"(a[p].w) : "l"(src[p]) : "memory");
+        asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(b[p].x), "=r"(b[p].y), "=r"(b[p].z), "=r"(b[p].w) : "l"(src[p] + 1) : "memory");
+      }
+    }
+#pragma unroll
+    for (int p = 0; p < WT; ++p) {
+      if ((pending & (1u << p)) && a[p].y == e && a[p].w == e && b[p].y == e && b[p].w == e) {
+        out[p] = make_uint4(a[p].x, a[p].z, b[p].x, b[p].z);
+        pending &= ~(1u << p);
+      }
+    }
+    if (!pending) break;
+    w.pause(timeout_ns);
+  }
+}
+
 __host__ __device__ inline size_t ll_slot_chunks(size_t ll_bytes, int world) {
   // bytes = 2 parities * (2 regions * W slots * 2n uint4 + W * AUX 8-byte pairs)
   const size_t aux = static_cast<size_t>(world) * CB2_COMM_AUX_FLOATS * 8;
@@ -426,10 +456,9 @@ __device__ __forceinline__ void ll_finish(const DevCtx& c, uint32_t e) {
 }
 
 template <typename T, int WT>
-__global__ void __launch_bounds__(512)
+__global__ void __launch_bounds__(256)
 comm_ll1_kernel(const DevCtx c, const FusedArgs a, const int opt) {
   constexpr int N = 16 / sizeof(T);
-  constexpr int U = 4;
   const int W = WT, R = c.rank;
   const uint32_t e = *reinterpret_cast<volatile uint32_t*>(c.ll_state) + 1;
   const Hyper h = load_hyper(a.hyper);
@@ -443,56 +472,47 @@ comm_ll1_kernel(const DevCtx c, const FusedArgs a, const int opt) {
   T* const my_param = reinterpret_cast<T*>(c.param[R]);
   const uint4 zero = make_uint4(0, 0, 0, 0);
 
-  for (size_t v0 = tid; v0 < nvec; v0 += nthreads * U) {
-    uint4 own[U];
+  for (size_t v = tid; v < nvec; v += nthreads) {
+    uint4 part[WT];
+    part[R] = ld_stream_v4(my_grad + a.off + v * N);
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const size_t v = v0 + static_cast<size_t>(u) * nthreads;
-      if (v < nvec) {
-        own[u] = ld_stream_v4(my_grad + a.off + v * N);
-#pragma unroll
-        for (int d = 1; d < WT; ++d) {
-          const int p = (R + d) % WT;
-          ll_push(lv.slot(c.ll[p], e, 0, R, W) + 2 * v, own[u], e);
-        }
-        if (a.zero_grads) st_stream_v4(my_grad + a.off + v * N, zero);
-      }
+    for (int d = 1; d < WT; ++d) {
+      const int p = (R + d) % WT;
+      ll_push(lv.slot(c.ll[p], e, 0, R, W) + 2 * v, part[R], e);
     }
+    if (a.zero_grads) st_stream_v4(my_grad + a.off + v * N, zero);
+    const uint4* src[WT];
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const size_t v = v0 + static_cast<size_t>(u) * nthreads;
-      if (v >= nvec) continue;
-      VecN<N> g;
+    for (int p = 0; p < WT; ++p) src[p] = lv.slot(c.ll[R], e, 0, p, W) + 2 * v;
+    ll_poll_all<WT>(part, src, R, e, c.timeout_ns);
+    VecN<N> g;
 #pragma unroll
-      for (int j = 0; j < N; ++j) g.v[j] = 0.f;
+    for (int j = 0; j < N; ++j) g.v[j] = 0.f;
 #pragma unroll
-      for (int p = 0; p < WT; ++p) {          // rank order: the same sum on every replica
-        const uint4 raw = p == R ? own[u] : ll_poll(lv.slot(c.ll[R], e, 0, p, W) + 2 * v, e, c.timeout_ns);
-        const VecN<N> o = unpack16<T>(raw);
+    for (int p = 0; p < WT; ++p) {            // rank order: the same sum on every replica
+      const VecN<N> o = unpack16<T>(part[p]);
 #pragma unroll
-        for (int j = 0; j < N; ++j) g.v[j] += o.v[j];
-      }
-      const size_t i = a.off + v * N;
-      const size_t si = a.state_off + v * N;
-      VecN<N> pin;
-      if (opt != CB2_OPT_NONE) {
-        if (a.master) pin = load_state<N>(a.master + si);
-        else pin = unpack16<T>(ld_stream_v4(my_param + i));
-      }
-      const VecN<N> pn = updateN_dyn<N>(opt, pin, g, a.s1, a.s2, si, h);
-      if (opt != CB2_OPT_NONE && a.master) store_state<N>(a.master + si, pn);
-      st_stream_v4(my_param + i, pack16(pn));
+      for (int j = 0; j < N; ++j) g.v[j] += o.v[j];
     }
+    const size_t i = a.off + v * N;
+    const size_t si = a.state_off + v * N;
+    VecN<N> pin;
+    if (opt != CB2_OPT_NONE) {
+      if (a.master) pin = load_state<N>(a.master + si);
+      else pin = unpack16<T>(ld_stream_v4(my_param + i));
+    }
+    const VecN<N> pn = updateN_dyn<N>(opt, pin, g, a.s1, a.s2, si, h);
+    if (opt != CB2_OPT_NONE && a.master) store_state<N>(a.master + si, pn);
+    st_stream_v4(my_param + i, pack16(pn));
   }
   ll_aux(c, a, lv, e, W, R);
   ll_finish(c, e);
 }
 
 template <typename T, int WT>
-__global__ void __launch_bounds__(512)
+__global__ void __launch_bounds__(256)
 comm_ll2_kernel(const DevCtx c, const FusedArgs a, const int opt) {
   constexpr int N = 16 / sizeof(T);
-  constexpr int U = 4;
   const int W = WT, R = c.rank;
   const uint32_t e = *reinterpret_cast<volatile uint32_t*>(c.ll_state) + 1;
   const Hyper h = load_hyper(a.hyper);
@@ -507,70 +527,61 @@ comm_ll2_kernel(const DevCtx c, const FusedArgs a, const int opt) {
   T* const my_param = reinterpret_cast<T*>(c.param[R]);
   const uint4 zero = make_uint4(0, 0, 0, 0);
 
-  for (size_t v0 = tid; v0 < nvec; v0 += nthreads * U) {
+  for (size_t v = tid; v < nvec; v += nthreads) {
     // 1. my part of every peer's shard goes to its owner; my own shard stays in registers
-    uint4 own[U];
+    uint4 mine[WT];
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const size_t v = v0 + static_cast<size_t>(u) * nthreads;
-      if (v < nvec) {
+    for (int p = 0; p < WT; ++p)
+      mine[p] = ld_stream_v4(my_grad + a.off + static_cast<size_t>(p) * span + v * N);
 #pragma unroll
-        for (int d = 1; d < WT; ++d) {
-          const int p = (R + d) % WT;
-          T* src = my_grad + a.off + static_cast<size_t>(p) * span + v * N;
-          const uint4 w = ld_stream_v4(src);
-          ll_push(lv.slot(c.ll[p], e, 0, R, W) + 2 * v, w, e);
-          if (a.zero_grads) st_stream_v4(src, zero);
-        }
-        T* mine = my_grad + a.off + static_cast<size_t>(R) * span + v * N;
-        own[u] = ld_stream_v4(mine);
-        if (a.zero_grads) st_stream_v4(mine, zero);
-      }
+    for (int d = 1; d < WT; ++d) {
+      const int p = (R + d) % WT;
+      ll_push(lv.slot(c.ll[p], e, 0, R, W) + 2 * v, mine[p], e);
+    }
+    if (a.zero_grads) {
+#pragma unroll
+      for (int p = 0; p < WT; ++p)
+        st_stream_v4(my_grad + a.off + static_cast<size_t>(p) * span + v * N, zero);
     }
     // 2. sum my shard in rank order, update it, publish the new parameters
+    uint4 part[WT];
+    part[R] = mine[R];
+    const uint4* src[WT];
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const size_t v = v0 + static_cast<size_t>(u) * nthreads;
-      if (v >= nvec) continue;
-      VecN<N> g;
+    for (int p = 0; p < WT; ++p) src[p] = lv.slot(c.ll[R], e, 0, p, W) + 2 * v;
+    ll_poll_all<WT>(part, src, R, e, c.timeout_ns);
+    VecN<N> g;
 #pragma unroll
-      for (int j = 0; j < N; ++j) g.v[j] = 0.f;
+    for (int j = 0; j < N; ++j) g.v[j] = 0.f;
 #pragma unroll
-      for (int p = 0; p < WT; ++p) {
-        const uint4 raw = p == R ? own[u] : ll_poll(lv.slot(c.ll[R], e, 0, p, W) + 2 * v, e, c.timeout_ns);
-        const VecN<N> o = unpack16<T>(raw);
+    for (int p = 0; p < WT; ++p) {
+      const VecN<N> o = unpack16<T>(part[p]);
 #pragma unroll
-        for (int j = 0; j < N; ++j) g.v[j] += o.v[j];
-      }
-      const size_t i = a.off + static_cast<size_t>(R) * span + v * N;
-      const size_t si = a.state_off + v * N;
-      VecN<N> pin;
-      if (opt != CB2_OPT_NONE) {
-        if (a.master) pin = load_state<N>(a.master + si);
-        else pin = unpack16<T>(ld_stream_v4(my_param + i));
-      }
-      const VecN<N> pn = updateN_dyn<N>(opt, pin, g, a.s1, a.s2, si, h);
-      if (opt != CB2_OPT_NONE && a.master) store_state<N>(a.master + si, pn);
-      const uint4 packed = pack16(pn);
-      st_stream_v4(my_param + i, packed);
+      for (int j = 0; j < N; ++j) g.v[j] += o.v[j];
+    }
+    const size_t i = a.off + static_cast<size_t>(R) * span + v * N;
+    const size_t si = a.state_off + v * N;
+    VecN<N> pin;
+    if (opt != CB2_OPT_NONE) {
+      if (a.master) pin = load_state<N>(a.master + si);
+      else pin = unpack16<T>(ld_stream_v4(my_param + i));
+    }
+    const VecN<N> pn = updateN_dyn<N>(opt, pin, g, a.s1, a.s2, si, h);
+    if (opt != CB2_OPT_NONE && a.master) store_state<N>(a.master + si, pn);
+    const uint4 packed = pack16(pn);
+    st_stream_v4(my_param + i, packed);
 #pragma unroll
-      for (int d = 1; d < WT; ++d) {
-        const int p = (R + d) % WT;
-        ll_push(lv.slot(c.ll[p], e, 1, R, W) + 2 * v, packed, e);
-      }
+    for (int d = 1; d < WT; ++d) {
+      const int p = (R + d) % WT;
+      ll_push(lv.slot(c.ll[p], e, 1, R, W) + 2 * v, packed, e);
     }
     // 3. the other shards' new parameters arrive the same way
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const size_t v = v0 + static_cast<size_t>(u) * nthreads;
-      if (v >= nvec) continue;
+    for (int p = 0; p < WT; ++p) src[p] = lv.slot(c.ll[R], e, 1, p, W) + 2 * v;
+    ll_poll_all<WT>(part, src, R, e, c.timeout_ns);
 #pragma unroll
-      for (int d = 1; d < WT; ++d) {
-        const int p = (R + d) % WT;
-        const uint4 raw = ll_poll(lv.slot(c.ll[R], e, 1, p, W) + 2 * v, e, c.timeout_ns);
-        st_stream_v4(my_param + a.off + static_cast<size_t>(p) * span + v * N, raw);
-      }
-    }
+    for (int p = 0; p < WT; ++p)
+      if (p != R) st_stream_v4(my_param + a.off + static_cast<size_t>(p) * span + v * N, part[p]);
   }
   ll_aux(c, a, lv, e, W, R);
   ll_finish(c, e);
@@ -638,8 +649,8 @@ static int to_dev_ctx(const cb2_comm_ctx* ctx, DevCtx* d) {
 template <int ALGO, typename T>
 static int launch_ll(const DevCtx& d, const FusedArgs& a, int opt, int blocks, cudaStream_t st) {
 #define CB2_LL(WT)                                                                    \
-  if (ALGO == CB2_ALGO_LL1) comm_ll1_kernel<T, WT><<<blocks, 512, 0, st>>>(d, a, opt); \
-  else comm_ll2_kernel<T, WT><<<blocks, 512, 0, st>>>(d, a, opt);
+  if (ALGO == CB2_ALGO_LL1) comm_ll1_kernel<T, WT><<<blocks, 256, 0, st>>>(d, a, opt); \
+  else comm_ll2_kernel<T, WT><<<blocks, 256, 0, st>>>(d, a, opt);
   switch (d.world) {
     case 2: CB2_LL(2) break;
     case 4: CB2_LL(4) break;
@@ -745,9 +756,10 @@ extern "C" int cb2_comm_fused(const cb2_comm_ctx* ctx, int algo, int opt, int gr
     a.master = master; a.s1 = s1; a.s2 = s2; a.hyper = hyper;
     a.zero_grads = zero_grads; a.aux_len = aux_len; a.aux_out = aux_out;
     if (blocks <= 0) {
-      // latency bound: spread the chunks so that a thread has at most one batch of four
-      size_t want = (chunks + 4 * 512 - 1) / (4 * 512);
-      if (want > 64) want = 64;
+      // latency bound: one chunk per thread as long as the grid stays resident (every block waits
+      // for peers, so all of them must be on the chip at once: 148 SMs, at least one 256-thread block each)
+      size_t want = (chunks + 255) / 256;
+      if (want > 128) want = 128;
       if (want < 1) want = 1;
       blocks = static_cast<int>(want);
     }
