@@ -48,6 +48,26 @@ for (n, c, hw) in ((256, 256, 56), (64, 1024, 14)):
     y = ops.batch_norm_nhwc(x, g, bt, rm, rv, True, 0.1, 1e-5, relu=True)
     y.backward(torch.ones_like(y))
 
+# folded 1x1 convolution + batch-norm (ops/convbn.py): the fused forward GEMM with scale / shift /
+# shortcut / ReLU / sign-bit epilogue and the dual-K input-gradient GEMM, ResNet-50 stage-2 shape
+import math  # noqa: E402
+os.environ.setdefault("TFC_BN_FOLD_MIN_MB", "0")
+for (n, cin, hw) in ((256, 64, 56), (256, 128, 28)):
+    cout = 4 * cin
+    xx = torch.randn(n, cin, hw, hw, device=dev).relu().to(torch.bfloat16).contiguous(
+        memory_format=torch.channels_last).requires_grad_(True)
+    ww = (torch.randn(cout, cin, 1, 1, device=dev) / math.sqrt(cin)).to(torch.bfloat16).contiguous(
+        memory_format=torch.channels_last).requires_grad_(True)
+    gg = torch.ones(cout, device=dev, requires_grad=True)
+    bb = torch.zeros(cout, device=dev, requires_grad=True)
+    rr = torch.randn(n, cout, hw, hw, device=dev).to(torch.bfloat16).contiguous(
+        memory_format=torch.channels_last).requires_grad_(True)
+    rm, rv = torch.zeros(cout, device=dev), torch.ones(cout, device=dev)
+    for _ in range(2):
+        zz = ops.conv1x1_bn(xx, ww, gg, bb, rm, rv, 0.01, 1e-5, relu=True, residual=rr)
+        zz.backward(torch.ones_like(zz))
+    del xx, ww, rr, zz
+
 # ResNet stem on the implicit GEMM (space-to-depth image through a 4-D tensor map), batch 256
 from cloud_b200.ops import conv as conv_ops  # noqa: E402
 img = torch.randint(0, 256, (256, 224, 224, 3), dtype=torch.uint8, device=dev)

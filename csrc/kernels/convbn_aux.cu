@@ -60,13 +60,23 @@ convbn_fwd_finalize_kernel(const float* __restrict__ gram, int ldg, const float*
 #pragma unroll
   for (int i = 0; i < JPL; ++i) u[i] = 0.f;
   const float* wrow = wsm + warp * K;
-#pragma unroll 2
-  for (int k = 0; k < K; ++k) {
-    const float wk = wrow[k];
-    const float* g = gram + static_cast<size_t>(k) * ldg + lane;
+  // eight Gram rows per step: their loads are all issued before the first FMA needs one (a warp
+  // here has nothing else to hide the L2 latency behind)
+  constexpr int KU = JPL <= 4 ? 8 : (JPL <= 8 ? 4 : 2);
+  for (int k0 = 0; k0 < K; k0 += KU) {
+    float gv[KU][JPL];
 #pragma unroll
-    for (int i = 0; i < JPL; ++i)
-      if (lane + 32 * i < K) u[i] = fmaf(wk, g[32 * i], u[i]);
+    for (int kk = 0; kk < KU; ++kk) {
+      const float* g = gram + static_cast<size_t>(k0 + kk) * ldg + lane;
+#pragma unroll
+      for (int i = 0; i < JPL; ++i) gv[kk][i] = (lane + 32 * i < K) ? __ldg(g + 32 * i) : 0.f;
+    }
+#pragma unroll
+    for (int kk = 0; kk < KU; ++kk) {
+      const float wk = wrow[k0 + kk];
+#pragma unroll
+      for (int i = 0; i < JPL; ++i) u[i] = fmaf(wk, gv[kk][i], u[i]);
+    }
   }
   float ms = 0.f, es = 0.f;
 #pragma unroll

@@ -444,6 +444,8 @@ static int launch_fused(const FusedMaps& maps, FusedArgs& args, cudaStream_t str
     int ring = (232448 - Cfg::smem_bytes(stages, 0)) / kResSlot;
     if (ring > kMaxRing) ring = kMaxRing;
     if (ring > args.ring) args.ring = ring;
+    static const int ring_env = [] { const char* e = getenv("TFC_CONVBN_RING"); return e ? atoi(e) : 0; }();
+    if (ring_env >= 1 && ring_env <= ring) args.ring = ring_env;      // tuning knob (bench/convbn_probe.py)
   }
   const int tiles = args.m_tiles * args.n_tiles;
   const int grid = tiles < num_sms() ? tiles : num_sms();
@@ -482,6 +484,8 @@ extern "C" int cb2_convbn_gemm(const void* A, int lda, const void* B, int ldb, i
   }
   const int m_tiles = (M + FBM - 1) / FBM;
   int bn = block_n;
+  static const int bn_env = [] { const char* e = getenv("TFC_CONVBN_BN"); return e ? atoi(e) : 0; }();
+  if (bn == 0 && (bn_env == 64 || bn_env == 128 || bn_env == 256) && bn_env <= N) bn = bn_env;
   if (bn == 0) {
     // the widest tile (fewest operand re-reads, best MMA shape) that keeps the waves full
     const int sms = num_sms();
