@@ -83,7 +83,7 @@ def supported(x: torch.Tensor, w: torch.Tensor, stride, padding, dilation) -> bo
     # touch it; smaller outputs are cheaper through the separate batch-norm kernels (measured,
     # bench/convbn_probe.py)
     out_mb = x.shape[0] * x.shape[2] * x.shape[3] * cout * 2 / 1e6
-    if out_mb < float(os.environ.get("TFC_BN_FOLD_MIN_MB", "150")):
+    if out_mb < float(os.environ.get("TFC_BN_FOLD_MIN_MB", "100")):
         return False
     return (cin % 64 == 0 and 64 <= cin <= 1024 and cout % 64 == 0 and cout >= 2 * cin
             and x.is_contiguous(memory_format=torch.channels_last) and w.is_contiguous(

@@ -157,15 +157,13 @@ bn_mask_grad_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
   float s[8], q[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
-  for (int row = m.row0; row < M; row += m.stride) {
-    const size_t i = static_cast<size_t>(row) * C + m.c8;
-    Vec8 v = unpack8_bf16(ld_stream_v4(dy + i));
+  auto one = [&](size_t i, const uint4& wa, const uint4& wb, uint32_t bits) {
+    Vec8 v = unpack8_bf16(wa);
     if (dy2) {
-      const Vec8 w = unpack8_bf16(ld_stream_v4(dy2 + i));
+      const Vec8 w = unpack8_bf16(wb);
 #pragma unroll
       for (int j = 0; j < 8; ++j) v.v[j] += w.v[j];
     }
-    const uint32_t bits = mask ? mask[static_cast<size_t>(row) * (C >> 3) + (m.c8 >> 3)] : 0xffu;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       if (!((bits >> j) & 1u)) v.v[j] = 0.f;
@@ -174,7 +172,29 @@ bn_mask_grad_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
     const Vec8 r = unpack8_bf16(packed);          // sums of what the GEMMs will read
 #pragma unroll
     for (int j = 0; j < 8; ++j) s[j] += r.v[j];
-    *reinterpret_cast<uint4*>(g + i) = packed;
+    st_stream_v4(g + i, packed);
+  };
+  const uint4 z4 = make_uint4(0, 0, 0, 0);
+  int row = m.row0;
+  // four rows (up to eight 16-byte loads) in flight per thread
+  for (; row + 3 * m.stride < M; row += 4 * m.stride) {
+    size_t i[4];
+    uint4 wa[4], wb[4];
+    uint32_t bits[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      i[u] = static_cast<size_t>(row + u * m.stride) * C + m.c8;
+      wa[u] = ld_stream_v4(dy + i[u]);
+      wb[u] = dy2 ? ld_stream_v4(dy2 + i[u]) : z4;
+      bits[u] = mask ? mask[static_cast<size_t>(row + u * m.stride) * (C >> 3) + (m.c8 >> 3)] : 0xffu;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) one(i[u], wa[u], wb[u], bits[u]);
+  }
+  for (; row < M; row += m.stride) {
+    const size_t i = static_cast<size_t>(row) * C + m.c8;
+    one(i, ld_stream_v4(dy + i), dy2 ? ld_stream_v4(dy2 + i) : z4,
+        mask ? mask[static_cast<size_t>(row) * (C >> 3) + (m.c8 >> 3)] : 0xffu);
   }
   bn_block_reduce_to_global(s, q, m, C, sums);
 }
