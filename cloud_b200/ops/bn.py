@@ -264,4 +264,7 @@ def fork(a: torch.Tensor):
     # one dictionary behind both handles: work derived from the tensor (its stride-2 subsample, read
     # by the two strided 1x1 convolutions of a stage's first block) is done once
     h1._cb2_shared = h2._cb2_shared = {}
+    # the consumers may talk to the producer (ops/convbn.py: the 1x1 convolution that reads one
+    # handle can deliver the producer's masked gradient itself)
+    h1._cb2_producer = h2._cb2_producer = mb
     return h1, h2

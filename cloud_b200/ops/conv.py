@@ -60,9 +60,10 @@ def mode() -> str:
 
 class _Conv1x1Fn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, w, bias, colstats, all_gemm):
+    def forward(ctx, x, w, bias, colstats, all_gemm, prod=None):
         n, cin, h, wd = x.shape
         cout = w.shape[0]
+        ctx.prod = prod
         ctx.save_for_backward(x, w)
         ctx.has_bias = bias is not None
         ctx.all_gemm = all_gemm
@@ -83,7 +84,20 @@ class _Conv1x1Fn(torch.autograd.Function):
             dy = dy.contiguous(memory_format=torch.channels_last)
         dy2 = _as_matrix(dy)
         dx = dw = db = None
-        if ctx.needs_input_grad[0] and not ctx.all_gemm:
+        g_next = ctx.prod.pop("g_next", None) if ctx.prod is not None else None
+        if ctx.needs_input_grad[0] and g_next is not None:
+            # x is one handle of a folded conv+BN(+shortcut)+ReLU output z whose other handle is the
+            # shortcut of the block this convolution belongs to.  dL/dz = dy W + g_next, and the
+            # producer wants it masked by its ReLU bits, with its column sums: all of that is the
+            # epilogue of this input-gradient GEMM (no separate pass over the largest tensor of the block)
+            convbn = importlib.import_module(__package__ + ".convbn")
+            G = torch.empty((n, h, wd, cin), dtype=torch.bfloat16, device=x.device)
+            gsums = _bn._scratch(16 * cin, x.device)
+            convbn.fused_gemm(dy2, w.reshape(cout, cin), G.view(m, cin), b_mn=True, residual=g_next,
+                              mask_in=ctx.prod["mask"], colstats=gsums)
+            ctx.prod["premasked"] = gsums
+            dx = G.permute(0, 3, 1, 2)
+        elif ctx.needs_input_grad[0] and not ctx.all_gemm:
             dx = torch.ops.aten.convolution_backward(
                 dy, x, w, None, (1, 1), (0, 0), (1, 1), False, (0, 0), 1, (True, False, False))[0]
         elif ctx.needs_input_grad[0]:
@@ -113,7 +127,7 @@ class _Conv1x1Fn(torch.autograd.Function):
                 w._cb2_grad_written(w)      # straight into the engine's arena: no autograd add
         if ctx.has_bias and ctx.needs_input_grad[2]:
             db = dy2.float().sum(0)
-        return dx, dw, db, None, None
+        return dx, dw, db, None, None, None
 
 
 def conv1x1(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None,
@@ -129,7 +143,16 @@ def conv1x1(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None,
         sums = _bn._scratch(16 * cout, x.device)
     if bias is not None and bias.dtype != torch.float32:
         bias = bias.float()
-    y = _Conv1x1Fn.apply(x, w, bias, sums, all_gemm)
+    # the input may be one handle of a forked, folded conv+BN output (ops/convbn.py): tell the
+    # producer that this convolution can deliver its masked gradient (see backward)
+    prod = getattr(x, "_cb2_producer", None)
+    if prod is not None and not ("mask" in prod and x.shape[1] % 64 == 0 and w.shape[0] % 64 == 0
+                                 and torch.is_grad_enabled()
+                                 and os.environ.get("TFC_BN_FOLD_FUSE_G", "1") != "0"):
+        prod = None
+    if prod is not None:
+        prod["dgrad_consumer"] = True
+    y = _Conv1x1Fn.apply(x, w, bias, sums, all_gemm, prod)
     if sums is not None:
         y._cb2_bn_sums = sums
     return y

@@ -39,6 +39,10 @@ _launches = 0
 _colsums: dict = {}      # data_ptr of a masked gradient -> its column sums, for the next backward in line
 
 
+def _fuse_g() -> bool:
+    return os.environ.get("TFC_BN_FOLD_FUSE_G", "1") != "0"
+
+
 def launches() -> int:
     return _launches
 
@@ -156,6 +160,13 @@ class _ConvBnFn(torch.autograd.Function):
         R = None if residual is None else _as_matrix(residual)
         fused_gemm(X, W2, z.view(M, cout), scale=scale, shift=shift, residual=R, relu=relu, mask_out=mask)
         _launches += 2
+        if mailbox is not None and mask is not None:
+            mailbox["mask"] = mask               # for a consumer that masks this layer's gradient itself
+        rp = getattr(residual, "_cb2_producer", None) if residual is not None else None
+        # the shortcut is one handle of a forked folded output whose other handle feeds a 1x1
+        # convolution that registered itself: that convolution's input-gradient GEMM will add this
+        # layer's shortcut gradient and apply the producer's ReLU mask in its epilogue
+        ctx.res_prod = rp if (rp is not None and rp.get("dgrad_consumer") and _fuse_g()) else None
         ctx.save_for_backward(x, w, gamma, mask, vec, U)
         ctx.params = (gamma, beta)
         ctx.wparam = w
@@ -183,9 +194,14 @@ class _ConvBnFn(torch.autograd.Function):
             dz = dz + dz2
             dz2 = None
         # g = masked gradient (+ second consumer's gradient), with its column sums
+        pre = ctx.mailbox.pop("premasked", None) if ctx.mailbox is not None else None
         cached = _colsums.pop((dz.data_ptr(), M, cout), None) if (mask is None and dz2 is None) else None
+        if pre is not None and dz2 is None:
+            cached = pre                         # dz already is the masked, summed gradient (see conv.py)
         gsums = cached if cached is not None else _bn._scratch(lib.cb2_bn_scratch_floats(cout), dev)
-        if mask is None and dz2 is None:
+        if pre is not None and dz2 is None:
+            G = _as_matrix(dz)
+        elif mask is None and dz2 is None:
             G = _as_matrix(dz)
             if cached is None:
                 _lib.check(lib.cb2_bn_stats(G.data_ptr(), gsums.data_ptr(), M, cout, _stream()), "bn_stats")
@@ -224,7 +240,9 @@ class _ConvBnFn(torch.autograd.Function):
             fused_gemm(G, Ws, dxm.view(M, cin), b_mn=True, a2=X, b2=Qn, shift=nbias)
             dx = dxm.permute(0, 3, 1, 2)
         dres = None
-        if ctx.has_res:
+        if ctx.has_res and ctx.res_prod is not None:
+            ctx.res_prod["g_next"] = G           # picked up by the 1x1 convolution on the other handle
+        elif ctx.has_res:
             dres = G.view(n, h, wd, cout).permute(0, 3, 1, 2)
             # the shortcut may itself be a folded convolution (the first block of a stage): its
             # backward needs the column sums of exactly this tensor - already reduced above

@@ -203,3 +203,39 @@ def test_strided_1x1_convolutions_share_one_subsample_and_match_cudnn():
     assert x.grad.is_contiguous(memory_format=torch.channels_last)
     for got, want in ((x.grad, xr.grad), (a.kernel.grad, wa.grad), (b.kernel.grad, wb.grad)):
         assert (got.float() - want).abs().max().item() < 4e-2 * want.abs().max().item()
+
+
+def test_masked_gradient_delivered_by_the_next_convolution_matches_the_separate_pass(monkeypatch):
+    """Identity blocks: the 1x1 convolution that reads a folded block output delivers dL/dz already
+    summed with the shortcut gradient and masked (its input-gradient GEMM's epilogue) instead of a
+    separate mask pass.  One SGD step with and without that fusion must move every weight alike."""
+    import cloud_b200 as tfc
+    keras = tfc.keras
+    L = keras.layers
+    from cloud_b200.keras.applications import _bottleneck
+    from cloud_b200.ops import convbn as cb
+    after = {}
+    for fuse in ("1", "0"):
+        monkeypatch.setenv("TFC_BN_FOLD_FUSE_G", fuse)
+        tfc.distribute.experimental_set_strategy(tfc.distribute.OneDeviceStrategy("cuda:0"))
+        keras.backend.clear_session()
+        torch.manual_seed(5)
+        inp = keras.Input(shape=(12, 12, 64))
+        x = _bottleneck(inp, 64, 1, True, "conv2_block1")
+        x = _bottleneck(x, 64, 1, False, "conv2_block2")
+        x = _bottleneck(x, 64, 1, False, "conv2_block3")
+        out = L.Dense(10, activation="softmax")(L.GlobalAveragePooling2D()(x))
+        m = keras.Model(inp, out)
+        m.compile(optimizer=keras.optimizers.SGD(0.1), loss="sparse_categorical_crossentropy", run_eagerly=True)
+        rng = np.random.RandomState(0)
+        xs, ys = rng.rand(16, 12, 12, 64).astype("float32"), rng.randint(0, 10, 16)
+        before = cb.launches()
+        m.train_on_batch(xs, ys)
+        after[fuse] = ([w.copy() for w in m.get_weights()], cb.launches() - before)
+    (w1, n1), (w0, n0) = after["1"], after["0"]
+    assert n1 > n0                                   # two more fused GEMMs took the place of the mask passes
+    for a, b in zip(w1, w0):
+        # same maths, different rounding points (the fused epilogue rounds the summed, masked
+        # gradient once): compare as vectors - zero-initialised shifts hold nothing but -lr * gradient
+        rel = np.linalg.norm((a - b).ravel()) / max(np.linalg.norm(b.ravel()), 1e-6)
+        assert rel <= 0.08, rel
