@@ -57,7 +57,9 @@ def _k():
                                         vp, vp, vp, i, vp]
         lib.cb2_convbn_fwd_finalize.restype = i
         lib.cb2_convbn_fwd_finalize.argtypes = [vp, i, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp,
-                                                i, i, i, f, f, vp]
+                                                i, i, i, f, f, i, vp]
+        lib.cb2_split_hilo_bf16.restype = i
+        lib.cb2_split_hilo_bf16.argtypes = [vp, vp, vp, ctypes.c_size_t, vp]
         lib.cb2_convbn_bwd_finalize.restype = i
         lib.cb2_convbn_bwd_finalize.argtypes = [vp, i, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, vp, i, vp, vp,
                                                 vp, i, i, i, vp]
@@ -149,11 +151,23 @@ class _ConvBnFn(torch.autograd.Function):
         scale, shift, mean, rstd = (vec[i * cout:(i + 1) * cout] for i in range(4))
         S = vec[4 * cout:]
         U = torch.empty((cout, cin), **f32)
+        u_ready = cin >= int(os.environ.get("TFC_CONVBN_U_GEMM_MIN_K", "256"))
+        if u_ready:
+            # U = W Gram is O(N K^2): from K = 256 on it goes through the tensor cores, Gram as the
+            # sum of two bf16 matrices (hi + lo keeps ~16 mantissa bits; the variance is a difference
+            # of two such products), accumulated in fp32
+            hl = torch.empty((2, cin, cin), dtype=torch.bfloat16, device=dev)
+            _lib.check(lib.cb2_split_hilo_bf16(gram.data_ptr(), hl[0].data_ptr(), hl[1].data_ptr(), cin * cin,
+                                               _stream()), "split_hilo")
+            _dense.gemm(W2, hl[0], out=U)                      # Gram is symmetric: [n, k] = [k, n]
+            _dense.gemm(W2, hl[1], out=U, accumulate=True)
+            _launches += 1
         rc = lib.cb2_convbn_fwd_finalize(gram.data_ptr(), cin, xsums.data_ptr(), W2.data_ptr(), cin,
                                          gamma.data_ptr(), beta.data_ptr(), run_mean.data_ptr(),
                                          run_var.data_ptr(), _ptr(mean_bias), scale.data_ptr(),
                                          shift.data_ptr(), mean.data_ptr(), rstd.data_ptr(), U.data_ptr(),
-                                         S.data_ptr(), cout, cin, M, float(eps), float(momentum), _stream())
+                                         S.data_ptr(), cout, cin, M, float(eps), float(momentum), int(u_ready),
+                                         _stream())
         _lib.check(rc, "convbn_fwd_finalize")
         z = torch.empty((n, h, wd, cout), dtype=torch.bfloat16, device=dev)
         mask = torch.empty(M * cout // 8, dtype=torch.uint8, device=dev) if relu else None

@@ -18,6 +18,7 @@
 // One warp per output channel; the only O(N K^2) work left on CUDA cores is U = W Gram.
 //
 // No counterpart in the reference (see convbn_tcgen05.cu).
+#include <algorithm>
 #include <type_traits>
 
 #include "common.cuh"
@@ -40,7 +41,7 @@ convbn_fwd_finalize_kernel(const float* __restrict__ gram, int ldg, const float*
                            float* __restrict__ scale, float* __restrict__ shift,
                            float* __restrict__ save_mean, float* __restrict__ save_rstd,
                            float* __restrict__ U, float* __restrict__ S_out, int N, int K, float M,
-                           float eps, float momentum) {
+                           float eps, float momentum, int u_ready) {
   extern __shared__ float sm[];
   float* Ssm = sm;                    // [K]
   float* wsm = sm + K;                // [kWPB][K]
@@ -63,7 +64,13 @@ convbn_fwd_finalize_kernel(const float* __restrict__ gram, int ldg, const float*
   // eight Gram rows per step: their loads are all issued before the first FMA needs one (a warp
   // here has nothing else to hide the L2 latency behind)
   constexpr int KU = JPL <= 4 ? 8 : (JPL <= 8 ? 4 : 2);
-  for (int k0 = 0; k0 < K; k0 += KU) {
+  if (u_ready) {
+    // U = W Gram came from the tensor cores (two bf16 GEMMs over a hi / lo split of Gram)
+#pragma unroll
+    for (int i = 0; i < JPL; ++i)
+      if (lane + 32 * i < K) u[i] = U[static_cast<size_t>(c) * K + lane + 32 * i];
+  }
+  for (int k0 = 0; k0 < (u_ready ? 0 : K); k0 += KU) {
     float gv[KU][JPL];
 #pragma unroll
     for (int kk = 0; kk < KU; ++kk) {
@@ -83,7 +90,7 @@ convbn_fwd_finalize_kernel(const float* __restrict__ gram, int ldg, const float*
   for (int i = 0; i < JPL; ++i) {
     const int j = lane + 32 * i;
     if (j < K) {
-      U[static_cast<size_t>(c) * K + j] = u[i];
+      if (!u_ready) U[static_cast<size_t>(c) * K + j] = u[i];
       ms = fmaf(wrow[j], Ssm[j], ms);
       es = fmaf(wrow[j], u[i], es);
     }
@@ -183,6 +190,27 @@ static int aux_shape_ok(int N, int K, const char* what) {
   return 0;
 }
 
+// fp32 -> two bf16 arrays with hi + lo = x to ~16 mantissa bits: the operand form in which an fp32
+// matrix goes through the bf16 tensor cores without losing what a variance needs
+__global__ void split_hilo_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ hi,
+                                  __nv_bfloat16* __restrict__ lo, size_t n) {
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const float v = x[i];
+    const __nv_bfloat16 h = __float2bfloat16(v);
+    hi[i] = h;
+    lo[i] = __float2bfloat16(v - __bfloat162float(h));
+  }
+}
+
+extern "C" int cb2_split_hilo_bf16(const float* x, void* hi, void* lo, size_t n, void* stream) {
+  if (n == 0) return 0;
+  const int blocks = static_cast<int>(std::min<size_t>((n + 255) / 256, 1184));
+  split_hilo_kernel<<<blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      x, reinterpret_cast<__nv_bfloat16*>(hi), reinterpret_cast<__nv_bfloat16*>(lo), n);
+  return check_cuda(cudaGetLastError(), "split_hilo launch");
+}
+
 template <typename F>
 static int dispatch_jpl(int K, F&& f) {
   const int per = (K + 31) / 32;
@@ -197,7 +225,7 @@ extern "C" int cb2_convbn_fwd_finalize(const float* gram, int ldg, const float* 
                                        int ldw, const float* gamma, const float* beta, float* run_mean,
                                        float* run_var, const float* mean_bias, float* scale, float* shift,
                                        float* save_mean, float* save_rstd, float* U, float* S, int N,
-                                       int K, int M, float eps, float momentum, void* stream) {
+                                       int K, int M, float eps, float momentum, int u_ready, void* stream) {
   int rc = aux_shape_ok(N, K, "convbn_fwd_finalize");
   if (rc) return rc;
   const size_t smem = static_cast<size_t>(kWPB + 1) * K * sizeof(float);
@@ -206,7 +234,7 @@ extern "C" int cb2_convbn_fwd_finalize(const float* gram, int ldg, const float* 
     constexpr int JPL = decltype(jpl)::value;
     convbn_fwd_finalize_kernel<JPL><<<N / kWPB, 32 * kWPB, smem, st>>>(
         gram, ldg, xsums, reinterpret_cast<const __nv_bfloat16*>(W), ldw, gamma, beta, run_mean, run_var,
-        mean_bias, scale, shift, save_mean, save_rstd, U, S, N, K, static_cast<float>(M), eps, momentum);
+        mean_bias, scale, shift, save_mean, save_rstd, U, S, N, K, static_cast<float>(M), eps, momentum, u_ready);
     return check_cuda(cudaGetLastError(), "convbn_fwd_finalize launch");
   });
 }
