@@ -169,6 +169,59 @@ int cb2_bn_backward3(const void* dy, const void* dy2, const void* y, int y_is_ma
                      const float* beta, float* sums, float* dbeta, float* dgamma, void* dx, void* dres,
                      int M, int C, int relu, void* stream);
 
+/* Column sums / sums of squares of a bf16 [M, C] matrix into `sums` (cb2_bn_scratch_floats(C) floats,
+ * accumulated: zero on entry) - the statistics pass of cb2_bn_forward on its own. */
+int cb2_bn_stats(const void* x, float* sums, int M, int C, void* stream);
+/* g = (dy (+ dy2, nullable)) where the sign bit saved by cb2_bn_forward_mask / cb2_convbn_gemm is set
+ * (mask nullable: all kept), else 0; sums[0:C] += column sums of g.  The masked gradient of a
+ * BN + shortcut + ReLU output as a GEMM operand, for the folded backward below. */
+int cb2_bn_mask_grad(const void* dy, const void* dy2, const void* mask, void* g, float* sums, int M, int C,
+                     void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * 1x1 convolution + batch normalisation (+ shortcut) (+ ReLU) folded into GEMMs: the convolution
+ * output y = X W^T (X bf16 [M, K], W bf16 [N, K]) is never stored.
+ *   forward : Gram = X^T X and column sums of X (cb2_gemm_bf16_ex, cb2_bn_stats) ->
+ *             cb2_convbn_fwd_finalize: mean_c = w_c . S / M, E[y_c^2] = w_c^T Gram w_c / M ->
+ *             scale / shift, saved mean / inv-std, running statistics, U = W Gram (u_ready != 0: U
+ *             was computed by the caller, e.g. on the tensor cores from cb2_split_hilo_bf16 halves) ->
+ *             cb2_convbn_gemm: z = relu(y * scale + shift + residual), one sign bit per element.
+ *   backward: g = masked upstream gradient (cb2_bn_mask_grad, or the epilogue of the GEMM that
+ *             produced it: mask_in + residual + colstats), P = g^T X ->
+ *             cb2_convbn_bwd_finalize: dgamma, dbeta, dW (added into a bf16 arena), Ws = s' W,
+ *             Wt = -t W, nbias (accumulated: zero on entry) -> Qn = Wt^T W (cb2_gemm_bf16) ->
+ *             cb2_convbn_gemm over two operand pairs: dX = g Ws + X Qn + nbias.
+ * cb2_convbn_gemm: C[M,N] = mask_in ? relu?((A B^T [+ A2 B2^T]) * scale + shift + residual) : 0, bf16,
+ * N / K1 / K2 multiples of 64; b_mn = 0: B stored [N, K], 1: stored [K, N]; scale / shift / residual /
+ * masks / colstats nullable; masks are bit arrays [M, N/32] words (bit set = element kept / positive);
+ * colstats = [cb2_convbn_stat_copies()][2][N] fp32 column sums / sums of squares of the stored values,
+ * accumulated.  block_n 0 = choose.
+ * Workload: conv*_block*_3_conv/_3_bn/_add/_out and *_0_conv/_0_bn of Keras' ResNet-50
+ * (core/tests/examples/call_run_within_script_with_keras_fit.py:79-83); no counterpart in the
+ * reference, which leaves these to cuDNN convolution, batch-norm, add and ReLU kernels.
+ * ------------------------------------------------------------------------------------------ */
+int cb2_convbn_stat_copies(void);
+int cb2_convbn_gemm(const void* A, int lda, const void* B, int ldb, int b_mn, const void* A2, int lda2,
+                    const void* B2, int ldb2, int K2, void* C, int ldc, int M, int N, int K1,
+                    const float* scale, const float* shift, const void* residual, int ldr, int relu,
+                    const void* mask_in, void* mask_out, float* colstats, int block_n, void* stream);
+int cb2_convbn_fwd_finalize(const float* gram, int ldg, const float* xsums, const void* W, int ldw,
+                            const float* gamma, const float* beta, float* run_mean, float* run_var,
+                            const float* mean_bias, float* scale, float* shift, float* save_mean,
+                            float* save_rstd, float* U, float* S, int N, int K, int M, float eps,
+                            float momentum, int u_ready, void* stream);
+int cb2_convbn_bwd_finalize(const float* P, int ldp, const float* gsums, const void* W, int ldw,
+                            const float* U, const float* S, const float* save_mean, const float* save_rstd,
+                            const float* gamma, float* dgamma, float* dbeta, void* dW, int lddw, void* Ws,
+                            void* Wt, float* nbias, int N, int K, int M, void* stream);
+/* hi[i] = bf16(x[i]), lo[i] = bf16(x[i] - hi[i]): an fp32 matrix as two bf16 GEMM operands. */
+int cb2_split_hilo_bf16(const float* x, void* hi, void* lo, size_t n, void* stream);
+/* Every s-th pixel of an NHWC bf16 tensor (backward = 0: y[B, ceil(H/s), ceil(W/s), C] <- x) and its
+ * adjoint (backward = 1: x is the gradient of the subsampled tensor, y the full-size gradient,
+ * written in one pass, zeros between the sampled pixels).  The input side of a strided 1x1
+ * convolution (conv*_block1_{0,1}_conv of ResNet-50), which then runs as a plain GEMM. */
+int cb2_subsample_nhwc(const void* x, void* y, int B, int H, int W, int C, int s, int backward, void* stream);
+
 /* cb2_bn_forward for callers that cannot allocate device memory.  (No counterpart in the
  * reference: it has no kernels and no C ABI; this entry exists for embedders of this library.)
  *
