@@ -12,7 +12,8 @@ import os
 import threading
 from pathlib import Path
 
-_LIB_DIR = Path(__file__).resolve().parent.parent / "_lib"
+# CLOUD_B200_LIB_DIR: load the two libraries from another directory (A/B runs of two builds on one box)
+_LIB_DIR = Path(os.environ.get("CLOUD_B200_LIB_DIR") or Path(__file__).resolve().parent.parent / "_lib")
 _lock = threading.Lock()
 _kernels = None
 _runtime = None

@@ -235,8 +235,10 @@ def stem_conv(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None
 
 
 # ----------------------------------------------------------------------------------------------
-# k x k / stride-1 / 'same' convolutions: cuDNN forward and input gradient, weight gradient on the
-# tcgen05 kernel (cb2_conv_wgrad: shifted pixel boxes through 4-D TMA maps)
+# k x k / stride-1 / 'same' convolutions: weight gradient on the tcgen05 kernel (cb2_conv_wgrad:
+# shifted pixel boxes through 4-D TMA maps); 3x3 forward and input gradient on the implicit-GEMM
+# kernel cb2_conv3x3 (halo strip loaded once per 64 channels, nine tap descriptors into it), other
+# kernel sizes and the shapes conv3x3_own() turns down on cuDNN
 # ----------------------------------------------------------------------------------------------
 def kxk_supported(x: torch.Tensor, w: torch.Tensor, stride, padding, dilation) -> bool:
     k = w.shape[2]
@@ -247,12 +249,58 @@ def kxk_supported(x: torch.Tensor, w: torch.Tensor, stride, padding, dilation) -
             and x.is_contiguous(memory_format=torch.channels_last))
 
 
+_CONV3 = os.environ.get("TFC_CONV3X3", "1")          # "0": cuDNN forward / input gradient for 3x3 too
+_CONV3_MIN_W = int(os.environ.get("TFC_CONV3X3_MIN_W", "14"))
+_conv3_declared = False
+
+
+def _conv3_lib():
+    global _conv3_declared
+    lib = _dense._lib.kernels()
+    if not _conv3_declared:
+        vp, i = ctypes.c_void_p, ctypes.c_int
+        lib.cb2_conv3x3.restype = i
+        lib.cb2_conv3x3.argtypes = [vp, vp, vp, i, i, i, i, i, i, vp, vp]
+        _conv3_declared = True
+    return lib
+
+
+def conv3x3_own(x: torch.Tensor, w: torch.Tensor) -> bool:
+    """Whether the 3x3 forward / input gradient of this layer run on ``cb2_conv3x3``
+    (csrc/kernels/conv3x3_tcgen05.cu).  The kernel computes on 128-row MMA tiles made of whole image
+    rows of W + 2 padded pixels: below 14 columns (the 7x7 stage of ResNet-50) more than half of every
+    tile would be padding, and with 64 output channels the MMAs are too short to keep the tensor
+    core busy (measured: bench/conv3_probe.py) - those shapes stay on cuDNN."""
+    if _CONV3 == "0" or w.shape[2] != 3 or not w.is_contiguous(memory_format=torch.channels_last):
+        return False
+    wd, cin, cout = x.shape[3], x.shape[1], w.shape[0]
+    if _CONV3 == "all":
+        return 6 <= wd <= 62
+    return _CONV3_MIN_W <= wd <= 62 and cin >= 128 and cout >= 128
+
+
+def _conv3_run(src, w, n_out, input_gradient, sums=None):
+    """src: channels_last [B, C, H, W] bf16 (NHWC in memory) -> channels_last [B, n_out, H, W]."""
+    b, _, h, wd = src.shape
+    cout, cin = w.shape[0], w.shape[1]
+    out = torch.empty((b, n_out, h, wd), device=src.device, dtype=torch.bfloat16,
+                      memory_format=torch.channels_last)
+    rc = _conv3_lib().cb2_conv3x3(src.data_ptr(), w.data_ptr(), out.data_ptr(), b, h, wd, cin, cout,
+                                  int(input_gradient), 0 if sums is None else sums.data_ptr(), _dense._stream())
+    _dense._lib.check(rc, "conv3x3")
+    _dense._launches += 1
+    return out
+
+
 class _ConvKxKFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, w, bias):
+    def forward(ctx, x, w, bias, sums=None):
         ctx.save_for_backward(x, w)
         ctx.has_bias = bias is not None
         k = w.shape[2]
+        ctx.own = bias is None and conv3x3_own(x, w)
+        if ctx.own:
+            return _conv3_run(x, w, w.shape[0], False, sums)
         return F.conv2d(x, w, None if bias is None else bias.to(x.dtype), padding=k // 2)
 
     @staticmethod
@@ -264,8 +312,11 @@ class _ConvKxKFn(torch.autograd.Function):
             dy = dy.contiguous(memory_format=torch.channels_last)
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
-            dx = torch.ops.aten.convolution_backward(
-                dy, x, w, None, (1, 1), (k // 2, k // 2), (1, 1), False, (0, 0), 1, (True, False, False))[0]
+            if ctx.own:
+                dx = _conv3_run(dy, w, cin, True)
+            else:
+                dx = torch.ops.aten.convolution_backward(
+                    dy, x, w, None, (1, 1), (k // 2, k // 2), (1, 1), False, (0, 0), 1, (True, False, False))[0]
         if ctx.needs_input_grad[1]:
             ws = _bn._scratch(k * k * cin * cout, x.device).view(k * k * cin, cout)   # zeroed per step
             rc = _dense._lib.kernels().cb2_conv_wgrad(x.data_ptr(), dy.data_ptr(), ws.data_ptr(), n, h, wd,
@@ -281,12 +332,22 @@ class _ConvKxKFn(torch.autograd.Function):
                 dw = g.to(torch.bfloat16)
         if ctx.has_bias and ctx.needs_input_grad[2]:
             db = dy.float().sum((0, 2, 3))
-        return dx, dw, db
+        return dx, dw, db, None
 
 
-def conv_kxk(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None) -> torch.Tensor:
-    """k x k / stride-1 / 'same' convolution of a channels_last bf16 tensor."""
-    return _ConvKxKFn.apply(x, w, bias)
+def conv_kxk(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None,
+             bn_stats: bool = False) -> torch.Tensor:
+    """k x k / stride-1 / 'same' convolution of a channels_last bf16 tensor.  3x3 layers that
+    ``conv3x3_own`` accepts run forward and input gradient on the implicit-GEMM kernel; with
+    ``bn_stats`` its epilogue also reduces the batch statistics of the result for the batch-norm
+    that follows (``_cb2_bn_sums``, as ``conv1x1`` does)."""
+    sums = None
+    if bn_stats and bias is None and conv3x3_own(x, w):
+        sums = _bn._scratch(16 * w.shape[0], x.device)
+    y = _ConvKxKFn.apply(x, w, bias, sums)
+    if sums is not None:
+        y._cb2_bn_sums = sums
+    return y
 
 
 # ----------------------------------------------------------------------------------------------

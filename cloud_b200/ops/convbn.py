@@ -124,6 +124,13 @@ def fused_gemm(a, b, out, *, b_mn=False, a2=None, b2=None, scale=None, shift=Non
                               K2, _ptr(out), out.stride(0), M, N, K1, _ptr(scale), _ptr(shift),
                               _ptr(residual), 0 if residual is None else residual.stride(0), int(relu),
                               _ptr(mask_in), _ptr(mask_out), _ptr(colstats), block_n, _stream())
+    if rc and os.environ.get("TFC_DEBUG_KERNEL_ARGS"):
+        import sys
+        print(f"[convbn_gemm failed] M={M} N={N} K1={K1} K2={K2} b_mn={b_mn} a={tuple(a.shape)}/{a.stride()} "
+              f"b={tuple(b.shape)}/{b.stride()} out={out.stride()} res={None if residual is None else residual.stride()} "
+              f"relu={relu} mask_in={mask_in is not None} mask_out={mask_out is not None} colstats={colstats is not None} "
+              f"ptrs a={_ptr(a):#x} b={_ptr(b):#x} out={_ptr(out):#x} res={_ptr(residual) or 0:#x} "
+              f"launches={_launches}", file=sys.stderr, flush=True)
     _lib.check(rc, "convbn_gemm")
     _launches += 1
     return out

@@ -45,6 +45,7 @@ struct FusedArgs {
   int kb1, kb2;                 // 64-wide k blocks of operand pair 1 / pair 2
   int m_tiles, n_tiles;
   int stages, ring;             // smem pipeline depth; residual ring slots (0: no residual)
+  int out_bufs;                 // staging buffers per epilogue warp (2, or 1 when the ring needs the room)
   uint32_t b_lbo, b_sbo, b_kadv;
   const float* scale;           // nullable [N]
   const float* shift;           // nullable [N]
@@ -66,12 +67,12 @@ struct FusedCfg {
   static constexpr int kNCW = kNC / kHF;                 // chunks per epilogue warp
   static constexpr int kBStage = BN * FBK * 2;
   static constexpr int kStage = kFAStage + kBStage;
-  static constexpr int kStaging = kEW * 2 * 4096;
+  static constexpr int staging(int out_bufs) { return kEW * out_bufs * 4096; }
   static constexpr int kParams = 8 * 2 * 128 * 4;        // per-warp scale / shift copies
   static constexpr int kBars = 512;
   static constexpr int kTmemCols = 2 * BN;
-  static constexpr int smem_bytes(int stages, int ring) {
-    return stages * kStage + kStaging + ring * kResSlot + kParams + kBars + 1024;
+  static constexpr int smem_bytes(int stages, int ring, int out_bufs = 2) {
+    return stages * kStage + staging(out_bufs) + ring * kResSlot + kParams + kBars + 1024;
   }
 };
 
@@ -88,18 +89,18 @@ convbn_gemm_kernel(const __grid_constant__ FusedMaps tm, const FusedArgs p) {
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem_a + S * kFAStage;
   uint8_t* smem_out = smem_b + S * Cfg::kBStage;
-  uint8_t* smem_res = smem_out + Cfg::kStaging;
+  uint8_t* smem_res = smem_out + Cfg::staging(p.out_bufs);
   uint8_t* smem_par = smem_res + R * kResSlot;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_par + Cfg::kParams);
   uint64_t* full_bar = bars;                               // [kMaxStages]
   uint64_t* empty_bar = bars + kMaxStages;                 // [kMaxStages]
   uint64_t* tfull_bar = bars + 2 * kMaxStages;             // [2]
   uint64_t* tempty_bar = bars + 2 * kMaxStages + 2;        // [2]
-  uint64_t* rfull_bar = bars + 2 * kMaxStages + 4;         // [kMaxRing]
-  uint64_t* rempty_bar = bars + 2 * kMaxStages + 4 + kMaxRing;   // [kMaxRing]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kMaxStages + 4 + 2 * kMaxRing);
+  uint64_t* rfull_bar = bars + 2 * kMaxStages + 4;         // [kMaxRing][2]: fills of a slot alternate
+  uint64_t* rempty_bar = bars + 2 * kMaxStages + 4 + 2 * kMaxRing;   // [kMaxRing]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kMaxStages + 4 + 3 * kMaxRing);
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);    // warp-uniform for ptxas
   const int lane = threadIdx.x & 31;
   const bool has_res = R > 0;
 
@@ -121,7 +122,8 @@ convbn_gemm_kernel(const __grid_constant__ FusedMaps tm, const FusedArgs p) {
       mbar_init(&tempty_bar[a], kEW);
     }
     for (int s = 0; s < kMaxRing; ++s) {
-      mbar_init(&rfull_bar[s], 1);
+      mbar_init(&rfull_bar[2 * s], 1);
+      mbar_init(&rfull_bar[2 * s + 1], 1);
       mbar_init(&rempty_bar[s], 4);
     }
     mbar_fence_init();
@@ -166,8 +168,8 @@ convbn_gemm_kernel(const __grid_constant__ FusedMaps tm, const FusedArgs p) {
     }
     __syncwarp();
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // ===================== MMA issuer (whole warp, one elected lane issues: common.cuh) ==========
+    {
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((B_MN ? 1u : 0u) << 16) |
                              (static_cast<uint32_t>(BN >> 3) << 17) |
                              (static_cast<uint32_t>(FBM >> 4) << 24);
@@ -176,21 +178,21 @@ convbn_gemm_kernel(const __grid_constant__ FusedMaps tm, const FusedArgs p) {
       int t = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
         const int acc = t & 1;
-        mbar_wait(&tempty_bar[acc], ((t >> 1) & 1) ^ 1);
+        mbar_wait_warp(&tempty_bar[acc], ((t >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BN;
         for (int kb = 0; kb < kbt; ++kb) {
-          mbar_wait(&full_bar[stage], phase);
+          mbar_wait_warp(&full_bar[stage], phase);
           tc_fence_after();
           const uint64_t adesc = make_smem_desc(smem_u32(smem_a + stage * kFAStage), 1, 1024 >> 4);
           const uint64_t bdesc =
               make_smem_desc(smem_u32(smem_b + stage * Cfg::kBStage), p.b_lbo, p.b_sbo);
 #pragma unroll
           for (int k = 0; k < FBK / 16; ++k)
-            umma_bf16(tmem_d, adesc + static_cast<uint64_t>(k * 2),
-                      bdesc + static_cast<uint64_t>(k * p.b_kadv), idesc, (kb | k) != 0);
-          umma_commit(&empty_bar[stage]);
-          if (kb == kbt - 1) umma_commit(&tfull_bar[acc]);
+            umma_bf16_warp(tmem_d, adesc + static_cast<uint64_t>(k * 2),
+                           bdesc + static_cast<uint64_t>(k * p.b_kadv), idesc, (kb | k) != 0);
+          umma_commit_warp(&empty_bar[stage]);
+          if (kb == kbt - 1) umma_commit_warp(&tfull_bar[acc]);
           if (++stage == S) { stage = 0; phase ^= 1; }
         }
       }
@@ -207,12 +209,14 @@ convbn_gemm_kernel(const __grid_constant__ FusedMaps tm, const FusedArgs p) {
           for (int hf = 0; hf < kHF; ++hf, ++seq) {
             const int c0 = n0 + (hf * kNCW + j) * 64;
             const int slot = seq % R;
-            mbar_wait(&rempty_bar[slot], ((seq / R) & 1) ^ 1);
+            const int use = seq / R;                         // n-th fill of this slot
+            uint64_t* rfull = &rfull_bar[2 * slot + (use & 1)];
+            mbar_wait(&rempty_bar[slot], (use & 1) ^ 1);
             if (c0 < p.N) {
-              mbar_expect_tx(&rfull_bar[slot], kResSlot);
-              tma_load_2d(&tm.r, &rfull_bar[slot], smem_res + slot * kResSlot, c0, m0);
+              mbar_expect_tx(rfull, kResSlot);
+              tma_load_2d(&tm.r, rfull, smem_res + slot * kResSlot, c0, m0);
             } else {
-              mbar_arrive(&rfull_bar[slot]);       // chunk past the last column: nothing to fetch
+              mbar_arrive(rfull);                  // chunk past the last column: nothing to fetch
             }
           }
       }
@@ -223,7 +227,7 @@ convbn_gemm_kernel(const __grid_constant__ FusedMaps tm, const FusedArgs p) {
     const int q = warp & 3;
     const int hf = (warp - 4) >> 2;
     const uint32_t sw = lane & 7;
-    const uint32_t stg = smem_u32(smem_out) + (warp - 4) * 8192;
+    const uint32_t stg = smem_u32(smem_out) + (warp - 4) * p.out_bufs * 4096;
     const uint32_t par = smem_u32(smem_par) + (warp - 4) * 1024;     // [0,512): scale, [512,1024): shift
     const bool has_scale = p.scale != nullptr, has_shift = p.shift != nullptr;
     const bool affine = has_scale || has_shift;
@@ -289,17 +293,29 @@ convbn_gemm_kernel(const __grid_constant__ FusedMaps tm, const FusedArgs p) {
 #pragma unroll
       for (int j = 0; j < kNCW; ++j) {
         const int c0 = cw0 + j * 64;
-        const int seq = (t * kNCW + j) * kHF + hf;            // position in the residual ring order
+        // Position in the residual ring order.  The ring is shared by the two column halves, and with
+        // an odd length the fills of one slot alternate between them - so a warp sees only every
+        // other fill of a slot.  A parity wait is only sound for a waiter that sees EVERY phase of its
+        // barrier (else "two phases ago" reads as "done": the warp would take a slot whose previous
+        // fill, a tile of the other half, is still in flight, and release it early).  Hence two "full"
+        // barriers per slot, used by alternate fills: every waiter of a barrier sees all its phases.
+        const int seq = (t * kNCW + j) * kHF + hf;
         const int slot = has_res ? seq % R : 0;
+        const int use = has_res ? seq / R : 0;
+        uint64_t* rfull = &rfull_bar[2 * slot + (use & 1)];
+        const uint32_t ring_phase = (use >> 1) & 1;
         if (c0 < p.N) {
           uint32_t v[2][32];
           tmem_ld_32x32(taddr + j * 64, v[0]);
           tmem_ld_32x32(taddr + j * 64 + 32, v[1]);
-          if (has_res) mbar_wait(&rfull_bar[slot], (seq / R) & 1);
+          if (has_res) mbar_wait(rfull, ring_phase);
           const uint32_t buf = stg + stage_buf * 4096;
           const uint32_t rowp = buf + lane * 128;
           const uint32_t resp = smem_u32(smem_res) + slot * kResSlot + (q * 32 + lane) * 128;
-          if (lane == 0) tma_store_wait_read<1>();          // the store that last read this buffer is done
+          if (lane == 0) {                                  // the store that last read this buffer is done
+            if (p.out_bufs == 2) tma_store_wait_read<1>();
+            else tma_store_wait_read<0>();
+          }
           __syncwarp();
           tmem_ld_wait_for(v[0]);
           reg_fence(v[1]);
@@ -381,10 +397,10 @@ convbn_gemm_kernel(const __grid_constant__ FusedMaps tm, const FusedArgs p) {
               }
             }
           }
-          stage_buf ^= 1;
+          stage_buf = (stage_buf + 1) & (p.out_bufs - 1);
         } else if (has_res) {
           // keep the ring in step for a chunk past the last column
-          mbar_wait(&rfull_bar[slot], (seq / R) & 1);
+          mbar_wait(rfull, ring_phase);
           __syncwarp();
           if (lane == 0) mbar_arrive(&rempty_bar[slot]);
         }
@@ -438,18 +454,25 @@ static int launch_fused(const FusedMaps& maps, FusedArgs& args, cudaStream_t str
     return CB2_ERR_UNSUPPORTED;
   }
   args.stages = stages;
+  args.out_bufs = 2;
   if (args.ring > 0) {
     // the shortcut tiles are the largest read of an output-bound GEMM: whatever shared memory the
     // operand pipeline leaves goes into their ring (bytes in flight = bandwidth x latency)
-    int ring = (232448 - Cfg::smem_bytes(stages, 0)) / kResSlot;
-    if (ring > kMaxRing) ring = kMaxRing;
-    if (ring > args.ring) args.ring = ring;
     static const int ring_env = [] { const char* e = getenv("TFC_CONVBN_RING"); return e ? atoi(e) : 0; }();
-    if (ring_env >= 1 && ring_env <= ring) args.ring = ring_env;      // tuning knob (bench/convbn_probe.py)
+    static const int bufs_env = [] { const char* e = getenv("TFC_CONVBN_OUT_BUFS"); return e ? atoi(e) : 0; }();
+    if (bufs_env == 1) args.out_bufs = 1;        // tuning knob: the second staging buffers go to the ring
+    int ring = (232448 - Cfg::smem_bytes(stages, 0, args.out_bufs)) / kResSlot;
+    if (ring > kMaxRing) ring = kMaxRing;
+    if (ring_env >= 1 && ring_env <= ring) ring = ring_env;           // tuning knob (bench/convbn_probe.py)
+    if (ring < 1) {
+      set_last_error("convbn_gemm: no room for the shortcut ring");
+      return CB2_ERR_UNSUPPORTED;
+    }
+    args.ring = ring;
   }
   const int tiles = args.m_tiles * args.n_tiles;
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  kern<<<grid, kFusedThreads, Cfg::smem_bytes(stages, args.ring), stream>>>(maps, args);
+  kern<<<grid, kFusedThreads, Cfg::smem_bytes(stages, args.ring, args.out_bufs), stream>>>(maps, args);
   return check_cuda(cudaGetLastError(), "convbn_gemm launch");
 }
 

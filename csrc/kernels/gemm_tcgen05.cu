@@ -348,7 +348,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
   uint64_t* wbar = bars + 2 * kStages + 5;      // conv == 4: resident weights loaded
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);    // warp-uniform for ptxas
   const int lane = threadIdx.x & 31;
 
   if (warp == 0 && lane == 0) {
@@ -481,8 +481,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
     __syncwarp();
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // ===================== MMA issuer (whole warp, one elected lane issues: common.cuh) ==========
+    {
       const uint32_t idesc = (1u << 4) /*D=f32*/ | (1u << 7) /*A=bf16*/ | (1u << 10) /*B=bf16*/ |
                              ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
                              (static_cast<uint32_t>(BN >> 3) << 17) |
@@ -491,7 +491,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       uint32_t phase = 0;
       int t = 0;
       if (kStemFwd && p.conv == 4) {
-        mbar_wait(wbar, 0);
+        mbar_wait_warp(wbar, 0);
         int base = 0, loaded = 0;    // load-sequence number of row oh of the tile / rows requested so far
         for (int R = tile_begin; R < tile_end; ++R, ++t) {
           const int oh = R % p.conv_oh;
@@ -499,12 +499,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           base = fresh ? loaded : base + 1;
           loaded += fresh ? 4 : 1;
           const int acc = t & 1;
-          mbar_wait(&tempty_bar[acc], ((t >> 1) & 1) ^ 1);
+          mbar_wait_warp(&tempty_bar[acc], ((t >> 1) & 1) ^ 1);
           tc_fence_after();
           const uint32_t tmem_d = tmem_base + acc * BN;
           for (int i = 0; i < 4; ++i) {
             const int sq = base + i, slot = sq % kStages;
-            mbar_wait(&full_bar[slot], (sq / kStages) & 1);     // rows seen by earlier tiles: already complete
+            mbar_wait_warp(&full_bar[slot], (sq / kStages) & 1);     // rows seen by earlier tiles: already complete
             tc_fence_after();
             const uint64_t adesc =
                 make_smem_desc(smem_u32(smem_a + slot * kAStageBytes), p.a_lbo, p.a_sbo);
@@ -512,27 +512,27 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 make_smem_desc(smem_u32(smem_b + i * Cfg::kBStageBytes), p.b_lbo, p.b_sbo);
 #pragma unroll
             for (int k = 0; k < BK / UMMA_K; ++k)
-              umma_bf16(tmem_d, adesc + static_cast<uint64_t>(k * p.a_kadv),
+              umma_bf16_warp(tmem_d, adesc + static_cast<uint64_t>(k * p.a_kadv),
                         bdesc + static_cast<uint64_t>(k * p.b_kadv), idesc, (i | k) != 0);
           }
           // this tile is the last user of row oh; the last tile of an image / of the range also
           // releases the three rows nobody else will read
-          umma_commit(&empty_bar[base % kStages]);
+          umma_commit_warp(&empty_bar[base % kStages]);
           if (R + 1 == tile_end || oh == p.conv_oh - 1)
-            for (int i = 1; i < 4; ++i) umma_commit(&empty_bar[(base + i) % kStages]);
-          umma_commit(&tfull_bar[acc]);
+            for (int i = 1; i < 4; ++i) umma_commit_warp(&empty_bar[(base + i) % kStages]);
+          umma_commit_warp(&tfull_bar[acc]);
         }
         tile_begin = tile_end;
       }
       for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++t) {
         const int acc = t & 1;
         const uint32_t acc_phase = (t >> 1) & 1;
-        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        mbar_wait_warp(&tempty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BN;
         const WorkItem it = decode_work<BN>(p, tile);
         for (int kb = it.kb0; kb < it.kb1; ++kb) {
-          mbar_wait(&full_bar[stage], phase);
+          mbar_wait_warp(&full_bar[stage], phase);
           tc_fence_after();
           const uint64_t adesc =
               make_smem_desc(smem_u32(smem_a + stage * kAStageBytes), p.a_lbo, p.a_sbo);
@@ -540,11 +540,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               make_smem_desc(smem_u32(smem_b + stage * Cfg::kBStageBytes), p.b_lbo, p.b_sbo);
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k) {
-            umma_bf16(tmem_d, adesc + static_cast<uint64_t>(k * p.a_kadv),
+            umma_bf16_warp(tmem_d, adesc + static_cast<uint64_t>(k * p.a_kadv),
                       bdesc + static_cast<uint64_t>(k * p.b_kadv), idesc, ((kb - it.kb0) | k) != 0);
           }
-          umma_commit(&empty_bar[stage]);  // smem slot reusable once these MMAs retire
-          if (kb == it.kb1 - 1) umma_commit(&tfull_bar[acc]);
+          umma_commit_warp(&empty_bar[stage]);  // smem slot reusable once these MMAs retire
+          if (kb == it.kb1 - 1) umma_commit_warp(&tfull_bar[acc]);
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       }
