@@ -251,6 +251,7 @@ def kxk_supported(x: torch.Tensor, w: torch.Tensor, stride, padding, dilation) -
 
 _CONV3 = os.environ.get("TFC_CONV3X3", "1")          # "0": cuDNN forward / input gradient for 3x3 too
 _CONV3_MIN_W = int(os.environ.get("TFC_CONV3X3_MIN_W", "14"))
+_CONV3_MIN_C = int(os.environ.get("TFC_CONV3X3_MIN_C", "64"))
 _conv3_declared = False
 
 
@@ -269,14 +270,15 @@ def conv3x3_own(x: torch.Tensor, w: torch.Tensor) -> bool:
     """Whether the 3x3 forward / input gradient of this layer run on ``cb2_conv3x3``
     (csrc/kernels/conv3x3_tcgen05.cu).  The kernel computes on 128-row MMA tiles made of whole image
     rows of W + 2 padded pixels: below 14 columns (the 7x7 stage of ResNet-50) more than half of every
-    tile would be padding, and with 64 output channels the MMAs are too short to keep the tensor
-    core busy (measured: bench/conv3_probe.py) - those shapes stay on cuDNN."""
+    tile would be padding (measured: bench/conv3_probe.py, 2x cuDNN's time) - those shapes stay on
+    cuDNN.  With 64 channels the MMAs are short (N = 64) and the forward pass is ~20 % behind cuDNN,
+    which the fused statistics (no separate pass over the 56 x 56 activation) more than pay back."""
     if _CONV3 == "0" or w.shape[2] != 3 or not w.is_contiguous(memory_format=torch.channels_last):
         return False
     wd, cin, cout = x.shape[3], x.shape[1], w.shape[0]
     if _CONV3 == "all":
         return 6 <= wd <= 62
-    return _CONV3_MIN_W <= wd <= 62 and cin >= 128 and cout >= 128
+    return _CONV3_MIN_W <= wd <= 62 and cin >= _CONV3_MIN_C and cout >= _CONV3_MIN_C
 
 
 def _conv3_run(src, w, n_out, input_gradient, sums=None):

@@ -80,6 +80,24 @@ int cb2_conv_stem_wgrad(const void* xs, const void* dy, float* dwt, int B, int O
  * No counterpart in the reference (cuDNN inside TensorFlow). */
 int cb2_conv_wgrad(const void* x, const void* dy, float* dwt, int B, int H, int W, int Cin, int Cout,
                    int ksize, int pad, int stride, void* stream);
+/* 3x3 / stride 1 / pad 1 convolution as an implicit GEMM (csrc/kernels/conv3x3_tcgen05.cu), bf16 NHWC:
+ *   input_gradient = 0: y[B,H,W,Cout] = conv(x[B,H,W,Cin], w[Cout,3,3,Cin])
+ *   input_gradient = 1: "x" is dy [B,H,W,Cout], "y" is dx [B,H,W,Cin], w the same tensor (taps mirrored,
+ *                       weight tiles read channel-transposed: no transposed copy)
+ * One TMA load per 64 input channels brings a strip of the zero-padded image (rows of W + 2 pixels) into
+ * shared memory; the nine taps are nine operand descriptors into that strip.  colstats (nullable) =
+ * [8][2][channels produced] fp32, accumulated: per-channel sums / sums of squares of the stored values
+ * over the real pixels - the batch statistics of a following batch-norm (cb2_bn_forward takes them).
+ * 6 <= W <= 62, Cin and Cout multiples of 64, dense 16-byte aligned tensors; cb2_conv3x3_supported says
+ * whether a geometry is accepted.  Workload: conv*_block*_2_conv of Keras' ResNet-50
+ * (core/tests/examples/call_run_within_script_with_keras_fit.py:79-83); no counterpart in the
+ * reference, which leaves it to cuDNN inside TensorFlow. */
+int cb2_conv3x3_supported(int H, int W, int Cin, int Cout);
+int cb2_conv3x3(const void* x, const void* w, void* y, int B, int H, int W, int Cin, int Cout,
+                int input_gradient, float* colstats, void* stream);
+/* Diagnostics / tuning only (bench/conv3_probe.py): descriptor base-offset mode, pipeline depths,
+ * staging buffers, traffic to skip (0 everywhere = defaults). */
+int cb2_conv3x3_debug(int base_off, int a_stages, int b_stages, int out_bufs, int skip);
 /* Diagnostics only (bench/gemm_epilogue_probe.py): bit mask of epilogue phases to skip. */
 int cb2_gemm_debug_epilogue(int bits);
 int cb2_gemm_debug_descriptors(int enable, unsigned a_lbo, unsigned a_sbo, unsigned b_lbo,
