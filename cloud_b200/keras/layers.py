@@ -565,7 +565,8 @@ class Conv2D(Layer):
             b = b.to(x.dtype)
         if _CONV1X1_GEMM and ops.stem_supported(x, w, strides, pad, self.dilation):
             y = ops.stem_conv(x, w, b)
-        elif _CONV1X1_GEMM and _CONV_KXK and ops.kxk_supported(x, w, strides, pad, self.dilation):
+        elif _CONV1X1_GEMM and ops.kxk_supported(x, w, strides, pad, self.dilation) and (
+                _CONV_KXK or (b is None and ops.conv3x3_own(x, w))):
             y = ops.conv_kxk(x, w, b, bn_stats=bool(training) and self.feeds_bn and
                              self.activation_name in (None, "linear"))
         elif _CONV1X1_GEMM and ops.conv1x1_supported(x, w, strides, pad, self.dilation):

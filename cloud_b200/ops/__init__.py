@@ -17,7 +17,7 @@ from .optim import FlatOptimizerState, optim_flat, optim_tick, OPT_CODES, make_h
 from .bn import batch_norm_nhwc, bn_available, fork as bn_fork  # noqa: F401,E402
 from .pool import max_pool_nhwc  # noqa: F401,E402
 from .conv import conv1x1, supported as conv1x1_supported, mode as conv1x1_mode  # noqa: F401,E402
-from .conv import stem_conv, stem_conv_s2d, stem_supported, conv_kxk, kxk_supported, subsample  # noqa: F401,E402
+from .conv import stem_conv, stem_conv_s2d, stem_supported, conv_kxk, kxk_supported, conv3x3_own, subsample  # noqa: F401,E402
 from .convbn import conv1x1_bn, supported as convbn_supported, DeferredConv  # noqa: F401,E402
 
 

@@ -249,6 +249,7 @@ def kxk_supported(x: torch.Tensor, w: torch.Tensor, stride, padding, dilation) -
             and x.is_contiguous(memory_format=torch.channels_last))
 
 
+_KXK_WGRAD = os.environ.get("TFC_CONV_KXK_WGRAD", "0") == "1"   # k x k weight gradients on cb2_conv_wgrad
 _CONV3 = os.environ.get("TFC_CONV3X3", "1")          # "0": cuDNN forward / input gradient for 3x3 too
 _CONV3_MIN_W = int(os.environ.get("TFC_CONV3X3_MIN_W", "14"))
 _CONV3_MIN_C = int(os.environ.get("TFC_CONV3X3_MIN_C", "64"))
@@ -319,7 +320,11 @@ class _ConvKxKFn(torch.autograd.Function):
             else:
                 dx = torch.ops.aten.convolution_backward(
                     dy, x, w, None, (1, 1), (k // 2, k // 2), (1, 1), False, (0, 0), 1, (True, False, False))[0]
-        if ctx.needs_input_grad[1]:
+        if ctx.needs_input_grad[1] and not _KXK_WGRAD:
+            # cuDNN's weight gradient (the shifted-box GEMM below is ~2x slower on these shapes: opt-in)
+            dw = torch.ops.aten.convolution_backward(
+                dy, x, w, None, (1, 1), (k // 2, k // 2), (1, 1), False, (0, 0), 1, (False, True, False))[1]
+        elif ctx.needs_input_grad[1]:
             ws = _bn._scratch(k * k * cin * cout, x.device).view(k * k * cin, cout)   # zeroed per step
             rc = _dense._lib.kernels().cb2_conv_wgrad(x.data_ptr(), dy.data_ptr(), ws.data_ptr(), n, h, wd,
                                                       cin, cout, k, k // 2, 1, _dense._stream())

@@ -94,6 +94,13 @@ __device__ __forceinline__ C3Unit c3_unit(const C3Args& p, int u) {
     const int x = u - p.full_units;
     tile = p.full_units + (x >> 1);
     half = x & 1;
+  } else {
+    // Whole waves are rotated by one CTA per wave.  A tile whose second sub-tile lies past the image
+    // costs half a tile, and such tiles come with a fixed period (28 x 28: every 4th); with 148 CTAs
+    // - a multiple of 4 - striding through them, a quarter of the CTAs would get nothing but the
+    // cheap tiles and the rest nothing but whole ones.
+    const int G = gridDim.x, wave = u / G;
+    if ((wave + 1) * G <= p.full_units) tile = wave * G + (u - wave * G + wave) % G;
   }
   const int mt = tile % p.m_tiles;
   C3Unit r;
@@ -466,7 +473,9 @@ extern "C" int cb2_conv3x3(const void* x, const void* w, void* y, int B, int H, 
   // (Rsub + 2) Wp + 2: the stage covers that), weight stages with what is left
   const int last_row = (a.Rsub + 2) * a.Wp + 2 + 128;
   a.a_stage = (last_row * 128 + 1023) & ~1023;
-  a.out_bufs = g_c3_out_bufs ? g_c3_out_bufs : 2;
+  // one staging buffer per sub-tile: the epilogue has slack (the kernel is MMA-bound), the weight
+  // pipeline does not - the 32 KiB buy two more stages
+  a.out_bufs = g_c3_out_bufs ? g_c3_out_bufs : 1;
   a.a_stages = g_c3_a_stages ? g_c3_a_stages : 2;
   if (a.a_stages > kC3MaxAStages) a.a_stages = kC3MaxAStages;
   const int fixed = 2 * a.out_bufs * 16384 + 512;
