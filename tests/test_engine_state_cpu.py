@@ -107,3 +107,34 @@ def test_recompile_drops_every_captured_graph_and_the_old_engine_hooks():
     m.fit(x, y, batch_size=4, epochs=1, verbose=0)
     assert m._engine is not old
     assert any(not np.array_equal(a, b) for a, b in zip(w0, m.get_weights()))   # the live weights train
+
+
+def test_conv3x3_routing_rules(monkeypatch):
+    """Which 3x3 layers go to the implicit-GEMM kernel is a pure function of shapes, layout and the
+    TFC_CONV3X3* switches (ops/conv.py::conv3x3_own) - checked here without a GPU."""
+    import torch
+    from cloud_b200.ops import conv as conv_mod
+
+    def xw(width, cin, cout, k=3, channels_last=True):
+        x = torch.zeros(1, cin, width, width, dtype=torch.bfloat16)
+        w = torch.zeros(cout, cin, k, k, dtype=torch.bfloat16)
+        if channels_last:
+            w = w.contiguous(memory_format=torch.channels_last)
+        return x, w
+
+    monkeypatch.setattr(conv_mod, "_CONV3", "1")
+    monkeypatch.setattr(conv_mod, "_CONV3_MIN_W", 14)
+    monkeypatch.setattr(conv_mod, "_CONV3_MIN_C", 64)
+    assert conv_mod.conv3x3_own(*xw(56, 64, 64))
+    assert conv_mod.conv3x3_own(*xw(28, 128, 128))
+    assert conv_mod.conv3x3_own(*xw(14, 256, 256))
+    assert not conv_mod.conv3x3_own(*xw(7, 512, 512))            # 7x7 stage: mostly padding, stays on cuDNN
+    assert not conv_mod.conv3x3_own(*xw(64, 64, 64))             # wider than one strip row allows
+    assert not conv_mod.conv3x3_own(*xw(28, 128, 128, k=5))      # only 3x3
+    assert not conv_mod.conv3x3_own(*xw(28, 128, 128, channels_last=False))   # weights must be [O, H, W, I]
+    monkeypatch.setattr(conv_mod, "_CONV3_MIN_C", 128)
+    assert not conv_mod.conv3x3_own(*xw(56, 64, 64))
+    monkeypatch.setattr(conv_mod, "_CONV3", "all")
+    assert conv_mod.conv3x3_own(*xw(7, 512, 512))
+    monkeypatch.setattr(conv_mod, "_CONV3", "0")
+    assert not conv_mod.conv3x3_own(*xw(28, 128, 128))
