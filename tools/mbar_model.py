@@ -1,0 +1,272 @@
+"""Exhaustive interleaving check of the mbarrier pipelines used by the tcgen05 kernels.
+
+compute-sanitizer's racecheck is not available on the GPU pool, and it does not understand mbarrier
+phase parity anyway.  The kernels here synchronise their warp roles with mbarriers that are waited on
+by PARITY (``mbarrier.try_wait.parity``): one bit, so "the phase I want is complete" and "the phase two
+before it is complete and nothing since" look the same.  A protocol is only sound if no waiter can
+ever be asked that ambiguous question.  This module states each pipeline as a handful of small
+sequential programs (producer, consumers) over a faithful model of the barrier, and explores EVERY
+interleaving - including asynchronous completions (TMA loads, tcgen05.commit arrivals) landing in any
+order - looking for
+
+* a wait that succeeds before the data it guards has landed (``early``),
+* a buffer overwritten while a reader that was granted it has not released it (``overwrite``),
+* an arrival on a barrier whose phase is already complete (``over-arrival``),
+* a state in which nobody can move before the programs are done (``deadlock``).
+
+It found nothing new - it was written AFTER the shortcut-ring race of the folded conv+BN GEMM
+ had been found the hard way - but it reproduces that race in 40 states from
+the protocol alone (``convbn_ring(two_full_barriers=False)``), passes the fixed protocol, and is the
+gate for any pipeline change: ``tests/test_mbar_protocols.py``.
+
+    python tools/mbar_model.py            # check every protocol listed in PROTOCOLS
+"""
+from __future__ import annotations
+
+import sys
+from collections import deque
+
+# ---------------------------------------------------------------------------------------------
+# Model.  A barrier = (completed phases, arrivals in the current phase); `expected` arrivals complete
+# a phase.  try_wait.parity(P) is true iff the current (incomplete) phase has parity != P.
+# Programs are tuples of ops; an op is a tuple:
+#   ("wait", bar, parity)             block until try_wait.parity(parity) holds
+#   ("arrive", bar)                   synchronous arrival
+#   ("async_arrive", bar)             arrival that happens some time later (tcgen05.commit)
+#   ("load", bar, buf, token)         async fill of `buf` with `token`; on landing arrives on `bar`
+#   ("read", buf, token)              the agent starts using `buf` and expects `token` in it
+#   ("release", buf)                  the agent is done with `buf`
+# ---------------------------------------------------------------------------------------------
+
+
+class Violation(Exception):
+    pass
+
+
+def check(programs: dict, expected: dict, max_states: int = 2_000_000) -> dict:
+    """Explore all interleavings.  ``programs``: name -> tuple of ops; ``expected``: barrier ->
+    arrival count.  Returns {"states": n} or raises Violation with a trace."""
+    names = sorted(programs)
+    bars = sorted(expected)
+    bidx = {b: i for i, b in enumerate(bars)}
+    bufs = sorted({op[2] for p in programs.values() for op in p if op[0] == "load"} |
+                  {op[1] for p in programs.values() for op in p if op[0] in ("read", "release")})
+    fidx = {b: i for i, b in enumerate(bufs)}
+
+    # state: (pcs, bar_state, buf_tokens, buf_readers, pending) - all tuples, hashable
+    init = (tuple(0 for _ in names),
+            tuple((0, 0) for _ in bars),
+            tuple(None for _ in bufs),
+            tuple(0 for _ in bufs),
+            frozenset())
+    seen = {init: None}
+    queue = deque([init])
+
+    def trace(state, last):
+        steps = [last]
+        while seen[state] is not None:
+            state, step = seen[state]
+            steps.append(step)
+        return list(reversed(steps))
+
+    def arrive(bar_state, b, state, what):
+        phases, got = bar_state[bidx[b]]
+        got += 1
+        if got > expected[b]:
+            raise Violation(("over-arrival", b, trace(state, what)))
+        if got == expected[b]:
+            phases, got = phases + 1, 0
+        bs = list(bar_state)
+        bs[bidx[b]] = (phases, got)
+        return tuple(bs)
+
+    while queue:
+        state = queue.popleft()
+        pcs, bar_state, tokens, readers, pending = state
+        moves = []
+        # asynchronous completions, any order
+        for ev in pending:
+            moves.append(("async", ev))
+        for ai, name in enumerate(names):
+            prog = programs[name]
+            if pcs[ai] >= len(prog):
+                continue
+            op = prog[pcs[ai]]
+            if op[0] == "wait":
+                phases, _ = bar_state[bidx[op[1]]]
+                if (phases & 1) == op[2]:
+                    continue                          # blocked
+            moves.append(("step", ai))
+        if not moves:
+            if any(pcs[ai] < len(programs[n]) for ai, n in enumerate(names)):
+                stuck = {n: programs[n][pcs[ai]] for ai, n in enumerate(names) if pcs[ai] < len(programs[n])}
+                raise Violation(("deadlock", stuck, trace(state, "stuck")))
+            continue
+        for mv in moves:
+            npcs, nbars, ntok, nrd, npend = list(pcs), bar_state, list(tokens), list(readers), set(pending)
+            if mv[0] == "async":
+                ev = mv[1]
+                npend.discard(ev)
+                if ev[0] == "land":
+                    _, b, buf, token, _uid = ev
+                    if nrd[fidx[buf]]:
+                        raise Violation(("overwrite", buf, trace(state, ev)))
+                    ntok[fidx[buf]] = token
+                    nbars = arrive(nbars, b, state, ev)
+                else:
+                    nbars = arrive(nbars, ev[1], state, ev)
+                what = ev
+            else:
+                ai = mv[1]
+                name = names[ai]
+                op = programs[name][pcs[ai]]
+                what = (name, op)
+                npcs[ai] += 1
+                if op[0] == "arrive":
+                    nbars = arrive(nbars, op[1], state, what)
+                elif op[0] == "async_arrive":
+                    npend.add(("commit", op[1], (name, pcs[ai])))
+                elif op[0] == "load":
+                    npend.add(("land", op[1], op[2], op[3], (name, pcs[ai])))
+                elif op[0] == "read":
+                    if ntok[fidx[op[1]]] != op[2]:
+                        raise Violation(("early", op[1], f"holds {ntok[fidx[op[1]]]}, wanted {op[2]}",
+                                         trace(state, what)))
+                    nrd[fidx[op[1]]] += 1
+                elif op[0] == "release":
+                    nrd[fidx[op[1]]] -= 1
+            nstate = (tuple(npcs), nbars, tuple(ntok), tuple(nrd), frozenset(npend))
+            if nstate not in seen:
+                seen[nstate] = (state, what)
+                if len(seen) > max_states:
+                    raise RuntimeError(f"more than {max_states} states: shorten the programs")
+                queue.append(nstate)
+    return {"states": len(seen)}
+
+
+# ---------------------------------------------------------------------------------------------
+# Protocols (each returns programs, expected)
+# ---------------------------------------------------------------------------------------------
+def convbn_ring(ring: int = 3, chunks: int = 8, two_full_barriers: bool = True):
+    """Shortcut ring of the folded conv+BN GEMM (convbn_tcgen05.cu): one producer fills slots in
+    sequence order, the two column halves of epilogue warps take alternate chunks.  With
+    ``two_full_barriers=False`` this is the protocol as first written (one "full" barrier per slot)."""
+    prod, cons = [], {0: [], 1: []}
+    expected = {}
+    for s in range(ring):
+        expected[f"rempty{s}"] = 1               # one agent stands for the four warps of a half
+        if two_full_barriers:
+            expected[f"rfull{s}a"] = expected[f"rfull{s}b"] = 1
+        else:
+            expected[f"rfull{s}"] = 1
+    for seq in range(chunks):
+        slot, use = seq % ring, seq // ring
+        if two_full_barriers:
+            full, parity = f"rfull{slot}{'ab'[use & 1]}", (use >> 1) & 1
+        else:
+            full, parity = f"rfull{slot}", use & 1
+        prod += [("wait", f"rempty{slot}", (use & 1) ^ 1), ("load", full, f"slot{slot}", seq)]
+        c = cons[seq % 2]
+        c += [("wait", full, parity), ("read", f"slot{slot}", seq), ("release", f"slot{slot}"),
+              ("arrive", f"rempty{slot}")]
+    return {"producer": tuple(prod), "half0": tuple(cons[0]), "half1": tuple(cons[1])}, expected
+
+
+def operand_pipeline(stages: int = 2, k_blocks: int = 5):
+    """TMA producer -> MMA issuer -> (commit) -> producer: the operand ring of every GEMM here."""
+    prod, mma = [], []
+    expected = {}
+    for s in range(stages):
+        expected[f"full{s}"] = expected[f"empty{s}"] = 1
+    for kb in range(k_blocks):
+        s, use = kb % stages, kb // stages
+        prod += [("wait", f"empty{s}", (use & 1) ^ 1), ("load", f"full{s}", f"stage{s}", kb)]
+        mma += [("wait", f"full{s}", use & 1), ("read", f"stage{s}", kb), ("release", f"stage{s}"),
+                ("async_arrive", f"empty{s}")]
+    return {"producer": tuple(prod), "mma": tuple(mma)}, expected
+
+
+def conv3x3_operands(a_stages: int = 2, b_stages: int = 3, strips: int = 2, taps: int = 3,
+                     second_issuer_idle: bool = False):
+    """conv3x3_tcgen05.cu: a strip producer and a weight producer, two MMA issuers (one per sub-tile)
+    that both consume every strip and every weight tile and both release them (count-2 "empty"
+    barriers, by tcgen05.commit - or by a plain arrival when the sub-tile has nothing to compute)."""
+    pa, pb, iss = [], [], {0: [], 1: []}
+    expected = {}
+    for s in range(a_stages):
+        expected[f"afull{s}"], expected[f"aempty{s}"] = 1, 2
+    for s in range(b_stages):
+        expected[f"bfull{s}"], expected[f"bempty{s}"] = 1, 2
+    bseq = 0
+    for cb in range(strips):
+        sa, ua = cb % a_stages, cb // a_stages
+        pa += [("wait", f"aempty{sa}", (ua & 1) ^ 1), ("load", f"afull{sa}", f"strip{sa}", ("a", cb))]
+        for i in (0, 1):
+            iss[i] += [("wait", f"afull{sa}", ua & 1), ("read", f"strip{sa}", ("a", cb))]
+        for _tap in range(taps):
+            sb, ub = bseq % b_stages, bseq // b_stages
+            pb += [("wait", f"bempty{sb}", (ub & 1) ^ 1), ("load", f"bfull{sb}", f"w{sb}", ("b", bseq))]
+            for i in (0, 1):
+                rel = "arrive" if (i == 1 and second_issuer_idle) else "async_arrive"
+                iss[i] += [("wait", f"bfull{sb}", ub & 1), ("read", f"w{sb}", ("b", bseq)), ("release", f"w{sb}"),
+                           (rel, f"bempty{sb}")]
+            bseq += 1
+        for i in (0, 1):
+            rel = "arrive" if (i == 1 and second_issuer_idle) else "async_arrive"
+            iss[i] += [("release", f"strip{sa}"), (rel, f"aempty{sa}")]
+    return {"strips": tuple(pa), "weights": tuple(pb), "issuer0": tuple(iss[0]), "issuer1": tuple(iss[1])}, expected
+
+
+def accumulator_handshake(tiles: int = 5, epilogue_warps: int = 2):
+    """MMA issuer <-> epilogue warps over two TMEM accumulator buffers (tfull by commit, tempty by one
+    arrival per epilogue warp).  The "buffer" is filled when the commit lands."""
+    mma, epi = [], {w: [] for w in range(epilogue_warps)}
+    expected = {}
+    for a in (0, 1):
+        expected[f"tfull{a}"], expected[f"tempty{a}"] = 1, epilogue_warps
+    for t in range(tiles):
+        a, use = t & 1, t >> 1
+        mma += [("wait", f"tempty{a}", (use & 1) ^ 1), ("load", f"tfull{a}", f"acc{a}", t)]
+        for w in range(epilogue_warps):
+            epi[w] += [("wait", f"tfull{a}", use & 1), ("read", f"acc{a}", t), ("release", f"acc{a}"),
+                       ("arrive", f"tempty{a}")]
+    progs = {"mma": tuple(mma)}
+    progs.update({f"epi{w}": tuple(p) for w, p in epi.items()})
+    return progs, expected
+
+
+PROTOCOLS = {
+    "convbn shortcut ring, 3 slots, two full barriers per slot (as built)": lambda: convbn_ring(3, 8, True),
+    "convbn shortcut ring, 4 slots": lambda: convbn_ring(4, 9, True),
+    "convbn shortcut ring, 1 slot": lambda: convbn_ring(1, 5, True),
+    "GEMM operand ring, 2 stages": lambda: operand_pipeline(2, 6),
+    "GEMM operand ring, 3 stages": lambda: operand_pipeline(3, 7),
+    "conv3x3 strips + weights, two issuers": lambda: conv3x3_operands(2, 3, 2, 3),
+    "conv3x3, second sub-tile idle (plain arrivals)": lambda: conv3x3_operands(2, 2, 2, 2, True),
+    "accumulator hand-over, two buffers": lambda: accumulator_handshake(5, 2),
+}
+
+
+def main() -> int:
+    bad = 0
+    for name, make in PROTOCOLS.items():
+        programs, expected = make()
+        try:
+            res = check(programs, expected)
+            print(f"ok    {name}: {res['states']} states")
+        except Violation as v:
+            bad += 1
+            print(f"FAIL  {name}: {v.args[0][0]} {v.args[0][1]}")
+    programs, expected = convbn_ring(3, 8, two_full_barriers=False)
+    try:
+        check(programs, expected)
+        print("the one-barrier-per-slot ring passed: the model lost its teeth")
+        bad += 1
+    except Violation as v:
+        kind, where = v.args[0][0], v.args[0][1]
+        print(f"ok    convbn shortcut ring as first written (one full barrier per slot) is caught: {kind} on {where}")
+    return 1 if bad else 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
