@@ -59,3 +59,12 @@ def test_a_consumer_that_skips_the_wait_is_caught_as_an_early_read():
     with pytest.raises(mm.Violation) as e:
         mm.check(broken, expected)
     assert e.value.args[0][0] == "early"
+
+
+def test_ll_allreduce_needs_two_receive_parities():
+    # flag-in-payload all-reduce of comm.cu: with one receive buffer a fast rank's store of call e + 1
+    # overwrites the cell a slow peer is still polling for call e
+    with pytest.raises(mm.Violation) as e:
+        mm.check(*mm.ll_allreduce(2, 4, parities=1))
+    assert e.value.args[0][0] == "lost"
+    mm.check(*mm.ll_allreduce(2, 6, parities=2))

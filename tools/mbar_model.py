@@ -14,6 +14,9 @@ order - looking for
 * an arrival on a barrier whose phase is already complete (``over-arrival``),
 * a state in which nobody can move before the programs are done (``deadlock``).
 
+The flag-in-payload ("LL") all-reduce between GPUs is modelled the same way (stores that land
+whenever, polls for a tag; ``lost`` = the awaited tag was overwritten before it was seen).
+
 It found nothing new - it was written AFTER the shortcut-ring race of the folded conv+BN GEMM
  had been found the hard way - but it reproduces that race in 40 states from
 the protocol alone (``convbn_ring(two_full_barriers=False)``), passes the fixed protocol, and is the
@@ -36,6 +39,10 @@ from collections import deque
 #   ("load", bar, buf, token)         async fill of `buf` with `token`; on landing arrives on `bar`
 #   ("read", buf, token)              the agent starts using `buf` and expects `token` in it
 #   ("release", buf)                  the agent is done with `buf`
+#   ("store", buf, token)             async write of `token` into `buf`, no barrier (a flag-in-payload
+#                                     store to a peer: lands whenever)
+#   ("poll", buf, token)              block until `buf` holds `token`; a LATER token there means the
+#                                     awaited one was overwritten before it was seen (``lost``)
 # ---------------------------------------------------------------------------------------------
 
 
@@ -50,7 +57,7 @@ def check(programs: dict, expected: dict, max_states: int = 2_000_000) -> dict:
     bars = sorted(expected)
     bidx = {b: i for i, b in enumerate(bars)}
     bufs = sorted({op[2] for p in programs.values() for op in p if op[0] == "load"} |
-                  {op[1] for p in programs.values() for op in p if op[0] in ("read", "release")})
+                  {op[1] for p in programs.values() for op in p if op[0] in ("read", "release", "store", "poll")})
     fidx = {b: i for i, b in enumerate(bufs)}
 
     # state: (pcs, bar_state, buf_tokens, buf_readers, pending) - all tuples, hashable
@@ -96,6 +103,13 @@ def check(programs: dict, expected: dict, max_states: int = 2_000_000) -> dict:
                 phases, _ = bar_state[bidx[op[1]]]
                 if (phases & 1) == op[2]:
                     continue                          # blocked
+            if op[0] == "poll":
+                have = tokens[fidx[op[1]]]
+                if have is not None and have > op[2]:
+                    raise Violation(("lost", op[1], f"holds {have}, still waiting for {op[2]}",
+                                     trace(state, (name, op))))
+                if have != op[2]:
+                    continue                          # blocked
             moves.append(("step", ai))
         if not moves:
             if any(pcs[ai] < len(programs[n]) for ai, n in enumerate(names)):
@@ -112,7 +126,8 @@ def check(programs: dict, expected: dict, max_states: int = 2_000_000) -> dict:
                     if nrd[fidx[buf]]:
                         raise Violation(("overwrite", buf, trace(state, ev)))
                     ntok[fidx[buf]] = token
-                    nbars = arrive(nbars, b, state, ev)
+                    if b is not None:
+                        nbars = arrive(nbars, b, state, ev)
                 else:
                     nbars = arrive(nbars, ev[1], state, ev)
                 what = ev
@@ -128,6 +143,8 @@ def check(programs: dict, expected: dict, max_states: int = 2_000_000) -> dict:
                     npend.add(("commit", op[1], (name, pcs[ai])))
                 elif op[0] == "load":
                     npend.add(("land", op[1], op[2], op[3], (name, pcs[ai])))
+                elif op[0] == "store":
+                    npend.add(("land", None, op[1], op[2], (name, pcs[ai])))
                 elif op[0] == "read":
                     if ntok[fidx[op[1]]] != op[2]:
                         raise Violation(("early", op[1], f"holds {ntok[fidx[op[1]]]}, wanted {op[2]}",
@@ -235,6 +252,26 @@ def accumulator_handshake(tiles: int = 5, epilogue_warps: int = 2):
     return progs, expected
 
 
+def ll_allreduce(ranks: int = 2, calls: int = 4, parities: int = 2):
+    """The flag-in-payload ("LL") all-reduce of comm.cu between kernels of successive calls: every
+    rank stores its chunk, tagged with the call number, into its cell of every peer's receive buffer
+    of parity call % parities, then polls its own cells for that tag.  Stores land whenever; a
+    rank's calls are stream-ordered.  Two parities are enough (a rank cannot start call e + 2 before
+    every peer has finished call e); one is not."""
+    progs = {}
+    for r in range(ranks):
+        p = []
+        for e in range(calls):
+            for q in range(ranks):
+                if q != r:
+                    p.append(("store", f"rx{q}_from{r}_p{e % parities}", e))
+            for q in range(ranks):
+                if q != r:
+                    p.append(("poll", f"rx{r}_from{q}_p{e % parities}", e))
+        progs[f"rank{r}"] = tuple(p)
+    return progs, {}
+
+
 PROTOCOLS = {
     "convbn shortcut ring, 3 slots, two full barriers per slot (as built)": lambda: convbn_ring(3, 8, True),
     "convbn shortcut ring, 4 slots": lambda: convbn_ring(4, 9, True),
@@ -244,6 +281,8 @@ PROTOCOLS = {
     "conv3x3 strips + weights, two issuers": lambda: conv3x3_operands(2, 3, 2, 3),
     "conv3x3, second sub-tile idle (plain arrivals)": lambda: conv3x3_operands(2, 2, 2, 2, True),
     "accumulator hand-over, two buffers": lambda: accumulator_handshake(5, 2),
+    "LL all-reduce, 2 ranks, two receive parities": lambda: ll_allreduce(2, 5, 2),
+    "LL all-reduce, 3 ranks, two receive parities": lambda: ll_allreduce(3, 3, 2),
 }
 
 
