@@ -661,7 +661,14 @@ class Model(nn.Module):
             steps_per_epoch=None, validation_steps=None, validation_batch_size=None, **kwargs):
         if self.loss is None:
             raise RuntimeError("You must compile your model with a loss before calling fit().")
-        weights = self._sample_weights(x, y, kwargs.get("sample_weight"), kwargs.get("class_weight"))
+        if isinstance(x, Dataset) and kwargs.get("sample_weight") is None:
+            # Keras: a dataset may yield (x, y, sample_weight) triples, and class_weight applies to the
+            # labels of every batch it yields
+            x, weighted = self._weighted_dataset(x, kwargs.get("class_weight"))
+            weights = None
+        else:
+            weighted = None
+            weights = self._sample_weights(x, y, kwargs.get("sample_weight"), kwargs.get("class_weight"))
         unknown = set(kwargs) - {"class_weight", "sample_weight", "workers", "use_multiprocessing",
                                  "max_queue_size", "validation_freq"}
         if unknown:
@@ -675,11 +682,50 @@ class Model(nn.Module):
             y_arr = _np(y).astype(np.float32)
             self._weighted_targets = "1d" if y_arr.ndim == 1 else "nd"
             y = np.concatenate([y_arr.reshape(len(y_arr), -1), weights.reshape(-1, 1)], axis=1)
+        elif weighted is not None:
+            self._weighted_targets = weighted
         try:
             return self._fit(x, y, batch_size, epochs, verbose, callbacks, validation_data, shuffle,
                              initial_epoch, steps_per_epoch, validation_steps, validation_batch_size, kwargs)
         finally:
             self._weighted_targets = None
+
+    @staticmethod
+    def _class_weight_table(class_weight, n_labels):
+        table = np.ones(int(max(n_labels, max(class_weight) + 1)), dtype=np.float32)
+        for cls, value in class_weight.items():
+            table[int(cls)] = float(value)
+        return table
+
+    def _weighted_dataset(self, ds, class_weight):
+        """A dataset whose elements are ``(x, y, sample_weight)`` and / or a ``class_weight`` table:
+        returns the dataset mapped to ``(x, y with the weight as a last column)`` - the encoding
+        ``_loss_and_metrics`` expects - and the target rank tag, or ``(ds, None)`` when there is
+        nothing to weight."""
+        first = next(iter(ds), None)
+        triple = isinstance(first, tuple) and len(first) == 3
+        if first is None or (not triple and class_weight is None):
+            return ds, None
+        if not isinstance(first, tuple) or len(first) < 2:
+            raise ValueError("class_weight needs a dataset of (x, y) or (x, y, sample_weight) elements")
+        y0 = _np(first[1])
+        batched = bool(getattr(ds, "batched", True))
+        label_rank = y0.ndim - (1 if batched else 0)
+        tag = "1d" if label_rank == 0 else "nd"
+
+        def fold(xb, yb, wb=None):
+            ya = _np(yb).astype(np.float32)
+            n = len(ya) if batched else 1
+            w = np.ones(n, dtype=np.float32) if wb is None else _np(wb).astype(np.float32).reshape(-1)
+            if class_weight is not None:
+                labels = ya.reshape(n, -1)
+                labels = labels.argmax(-1) if labels.shape[-1] > 1 else labels.reshape(-1)
+                labels = labels.astype(np.int64)
+                w = w * self._class_weight_table(class_weight, int(labels.max()) + 1)[labels]
+            ext = np.concatenate([ya.reshape(n, -1), w.reshape(n, 1)], axis=1)
+            return xb, (ext if batched else ext[0])
+
+        return ds.map(fold), tag
 
     def _sample_weights(self, x, y, sample_weight, class_weight):
         """Per-sample loss weights of ``fit(sample_weight=..., class_weight=...)`` as one float32
@@ -687,8 +733,9 @@ class Model(nn.Module):
         if sample_weight is None and class_weight is None:
             return None
         if isinstance(x, (Dataset, DistributedDataset)) or y is None:
-            raise NotImplementedError("sample_weight / class_weight need array inputs (x, y); with a "
-                                      "dataset, weight the loss in a custom training loop.")
+            raise NotImplementedError("sample_weight= needs array inputs (x, y): let the dataset yield "
+                                      "(x, y, sample_weight) elements instead; class_weight works with "
+                                      "a tfc.data.Dataset, not with a distributed dataset")
         n = len(y)
         w = np.ones(n, dtype=np.float32)
         if sample_weight is not None:
@@ -701,10 +748,7 @@ class Model(nn.Module):
             if labels.ndim > 1 and labels.shape[-1] > 1:
                 labels = labels.argmax(-1)              # one-hot targets
             labels = labels.reshape(-1).astype(np.int64)
-            table = np.ones(int(max(labels.max(), max(class_weight)) + 1), dtype=np.float32)
-            for cls, value in class_weight.items():
-                table[int(cls)] = float(value)
-            w *= table[labels]
+            w *= self._class_weight_table(class_weight, int(labels.max()) + 1)[labels]
         return w
 
     def _fit(self, x, y, batch_size, epochs, verbose, callbacks, validation_data, shuffle, initial_epoch,

@@ -481,6 +481,43 @@ def test_fit_keyword_contract():
     m.fit(x, y, batch_size=32, epochs=1, verbose=0, workers=4, use_multiprocessing=False)   # accepted, meaningless here
 
 
+def test_weights_from_a_dataset_match_weights_from_arrays():
+    """Keras: a dataset may yield (x, y, sample_weight); class_weight applies to every batch's labels."""
+    x, y = _blobs(64)
+    w = (1.0 + (np.arange(64) % 3)).astype("float32")
+    cw = {0: 2.0, 3: 0.5}
+
+    def run(data, **fit_kwargs):
+        torch.manual_seed(9)
+        m = keras.Sequential([L.Dense(16, activation="relu", input_shape=(20,)), L.Dense(4, activation="softmax")])
+        m.compile(keras.optimizers.SGD(0.1), "sparse_categorical_crossentropy", metrics=["accuracy"])
+        if isinstance(data, tuple):
+            m.fit(*data, batch_size=16, epochs=2, shuffle=False, verbose=0, **fit_kwargs)
+        else:
+            m.fit(data, epochs=2, verbose=0, **fit_kwargs)
+        assert m._weighted_targets is None                      # the flag does not outlive the call
+        return m.get_weights()
+
+    want = run((x, y), sample_weight=w)
+    got = run(tfc.data.Dataset.from_tensor_slices((x, y, w)).batch(16))
+    for a, b in zip(got, want):
+        np.testing.assert_allclose(a, b, rtol=1e-6, atol=1e-7)
+    want = run((x, y), class_weight=cw)
+    got = run(tfc.data.Dataset.from_tensor_slices((x, y)).batch(16), class_weight=cw)
+    for a, b in zip(got, want):
+        np.testing.assert_allclose(a, b, rtol=1e-6, atol=1e-7)
+    want = run((x, y), sample_weight=w, class_weight=cw)
+    got = run(tfc.data.Dataset.from_tensor_slices((x, y, w)).batch(16), class_weight=cw)
+    for a, b in zip(got, want):
+        np.testing.assert_allclose(a, b, rtol=1e-6, atol=1e-7)
+    # nothing to weight: the dataset goes through untouched (and the fused loss path stays available)
+    plain = run(tfc.data.Dataset.from_tensor_slices((x, y)).batch(16))
+    for a, b in zip(plain, run((x, y))):
+        np.testing.assert_allclose(a, b, rtol=1e-6, atol=1e-7)
+    with pytest.raises(NotImplementedError, match="sample_weight"):
+        run(tfc.data.Dataset.from_tensor_slices((x, y)).batch(16), sample_weight=w)
+
+
 def test_sample_and_class_weights_scale_each_sample_loss():
     x, y = _blobs(64)
     # weight 0 for half of the samples == training on the other half with a batch twice as "large"
