@@ -68,3 +68,12 @@ def test_ll_allreduce_needs_two_receive_parities():
         mm.check(*mm.ll_allreduce(2, 4, parities=1))
     assert e.value.args[0][0] == "lost"
     mm.check(*mm.ll_allreduce(2, 6, parities=2))
+
+
+def test_fused_allreduce_needs_its_closing_barrier():
+    # comm.cu, barrier-based schedules: without the second barrier a rank reads parameters a peer has
+    # not stored yet (and would zero gradients a peer has not read yet)
+    with pytest.raises(mm.Violation) as e:
+        mm.check(*mm.fused_allreduce(2, 2, closing_barrier=False))
+    assert e.value.args[0][0] == "stale"
+    mm.check(*mm.fused_allreduce(2, 3, closing_barrier=True))

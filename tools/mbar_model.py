@@ -14,8 +14,10 @@ order - looking for
 * an arrival on a barrier whose phase is already complete (``over-arrival``),
 * a state in which nobody can move before the programs are done (``deadlock``).
 
-The flag-in-payload ("LL") all-reduce between GPUs is modelled the same way (stores that land
-whenever, polls for a tag; ``lost`` = the awaited tag was overwritten before it was seen).
+The collectives between GPUs are modelled the same way: the flag-in-payload ("LL") all-reduce
+(stores that land whenever, polls for a tag; ``lost`` = the awaited tag was overwritten before it was
+seen) and the barrier-based fused all-reduce + optimizer over successive steps (monotonic epochs in
+the signal pads; ``stale`` = gradients or parameters read before or after the step they belong to).
 
 It found nothing new - it was written AFTER the shortcut-ring race of the folded conv+BN GEMM
  had been found the hard way - but it reproduces that race in 40 states from
@@ -43,6 +45,12 @@ from collections import deque
 #                                     store to a peer: lands whenever)
 #   ("poll", buf, token)              block until `buf` holds `token`; a LATER token there means the
 #                                     awaited one was overwritten before it was seen (``lost``)
+#   ("publish", buf, epoch)           async store of a monotonic epoch (same-address stores of one
+#                                     thread stay ordered: a landing never lowers the cell)
+#   ("poll_ge", buf, epoch)           block until the cell holds at least `epoch`
+#   ("set", buf, token)               synchronous write (local memory, or a peer store ordered before
+#                                     the next publish by a system fence + release)
+#   ("expect", buf, token)            synchronous read that must find `token` (``stale`` otherwise)
 # ---------------------------------------------------------------------------------------------
 
 
@@ -57,7 +65,8 @@ def check(programs: dict, expected: dict, max_states: int = 2_000_000) -> dict:
     bars = sorted(expected)
     bidx = {b: i for i, b in enumerate(bars)}
     bufs = sorted({op[2] for p in programs.values() for op in p if op[0] == "load"} |
-                  {op[1] for p in programs.values() for op in p if op[0] in ("read", "release", "store", "poll")})
+                  {op[1] for p in programs.values() for op in p
+                   if op[0] in ("read", "release", "store", "poll", "publish", "poll_ge", "set", "expect")})
     fidx = {b: i for i, b in enumerate(bufs)}
 
     # state: (pcs, bar_state, buf_tokens, buf_readers, pending) - all tuples, hashable
@@ -110,6 +119,10 @@ def check(programs: dict, expected: dict, max_states: int = 2_000_000) -> dict:
                                      trace(state, (name, op))))
                 if have != op[2]:
                     continue                          # blocked
+            if op[0] == "poll_ge":
+                have = tokens[fidx[op[1]]]
+                if have is None or have < op[2]:
+                    continue                          # blocked
             moves.append(("step", ai))
         if not moves:
             if any(pcs[ai] < len(programs[n]) for ai, n in enumerate(names)):
@@ -121,7 +134,11 @@ def check(programs: dict, expected: dict, max_states: int = 2_000_000) -> dict:
             if mv[0] == "async":
                 ev = mv[1]
                 npend.discard(ev)
-                if ev[0] == "land":
+                if ev[0] == "epoch":
+                    _, buf, token, _uid = ev
+                    have = ntok[fidx[buf]]
+                    ntok[fidx[buf]] = token if have is None else max(have, token)
+                elif ev[0] == "land":
                     _, b, buf, token, _uid = ev
                     if nrd[fidx[buf]]:
                         raise Violation(("overwrite", buf, trace(state, ev)))
@@ -145,6 +162,14 @@ def check(programs: dict, expected: dict, max_states: int = 2_000_000) -> dict:
                     npend.add(("land", op[1], op[2], op[3], (name, pcs[ai])))
                 elif op[0] == "store":
                     npend.add(("land", None, op[1], op[2], (name, pcs[ai])))
+                elif op[0] == "publish":
+                    npend.add(("epoch", op[1], op[2], (name, pcs[ai])))
+                elif op[0] == "set":
+                    ntok[fidx[op[1]]] = op[2]
+                elif op[0] == "expect":
+                    if ntok[fidx[op[1]]] != op[2]:
+                        raise Violation(("stale", op[1], f"holds {ntok[fidx[op[1]]]}, wanted {op[2]}",
+                                         trace(state, what)))
                 elif op[0] == "read":
                     if ntok[fidx[op[1]]] != op[2]:
                         raise Violation(("early", op[1], f"holds {ntok[fidx[op[1]]]}, wanted {op[2]}",
@@ -272,6 +297,42 @@ def ll_allreduce(ranks: int = 2, calls: int = 4, parities: int = 2):
     return progs, {}
 
 
+def fused_allreduce(ranks: int = 2, steps: int = 3, closing_barrier: bool = True):
+    """The barrier-based fused all-reduce + optimizer kernel of comm.cu (two-shot / NVLS) over
+    successive training steps: backward writes the local gradients; barrier 1 (epoch 2s + 1); every
+    rank reads its shard of EVERY rank's gradients and stores the new parameters of that shard into
+    every rank (ordered before its next publish); barrier 2 (epoch 2s + 2); the rank zeroes its
+    gradients; the next forward reads the parameters.  Without the closing barrier a fast rank zeroes
+    (and rewrites) gradients a slow peer has not read yet."""
+    progs = {}
+    for r in range(ranks):
+        p = []
+        for s in range(steps):
+            p.append(("set", f"grad{r}", s))
+            for q in range(ranks):
+                if q != r:
+                    p.append(("publish", f"pad{q}_from{r}", 2 * s + 1))
+            for q in range(ranks):
+                if q != r:
+                    p.append(("poll_ge", f"pad{r}_from{q}", 2 * s + 1))
+            for q in range(ranks):
+                p.append(("expect", f"grad{q}", s))
+            for q in range(ranks):
+                p.append(("set", f"param{q}_shard{r}", s))
+            if closing_barrier:
+                for q in range(ranks):
+                    if q != r:
+                        p.append(("publish", f"pad{q}_from{r}", 2 * s + 2))
+                for q in range(ranks):
+                    if q != r:
+                        p.append(("poll_ge", f"pad{r}_from{q}", 2 * s + 2))
+            p.append(("set", f"grad{r}", "zeroed"))
+            for q in range(ranks):
+                p.append(("expect", f"param{r}_shard{q}", s))
+        progs[f"rank{r}"] = tuple(p)
+    return progs, {}
+
+
 PROTOCOLS = {
     "convbn shortcut ring, 3 slots, two full barriers per slot (as built)": lambda: convbn_ring(3, 8, True),
     "convbn shortcut ring, 4 slots": lambda: convbn_ring(4, 9, True),
@@ -283,6 +344,8 @@ PROTOCOLS = {
     "accumulator hand-over, two buffers": lambda: accumulator_handshake(5, 2),
     "LL all-reduce, 2 ranks, two receive parities": lambda: ll_allreduce(2, 5, 2),
     "LL all-reduce, 3 ranks, two receive parities": lambda: ll_allreduce(3, 3, 2),
+    "fused all-reduce + optimizer, barrier before and after, 2 ranks": lambda: fused_allreduce(2, 3),
+    "fused all-reduce + optimizer, 3 ranks, one step": lambda: fused_allreduce(3, 1),
 }
 
 
