@@ -77,3 +77,12 @@ def test_fused_allreduce_needs_its_closing_barrier():
         mm.check(*mm.fused_allreduce(2, 2, closing_barrier=False))
     assert e.value.args[0][0] == "stale"
     mm.check(*mm.fused_allreduce(2, 3, closing_barrier=True))
+
+
+def test_stem_row_ring_needs_four_stages():
+    # a tile needs four input rows at once: with three stages the producer and the issuer wait on
+    # each other for ever
+    with pytest.raises(mm.Violation) as e:
+        mm.check(*mm.stem_row_ring(3, 1, 3))
+    assert e.value.args[0][0] == "deadlock"
+    mm.check(*mm.stem_row_ring(8, 2, 4))              # the kernel's depth

@@ -277,6 +277,40 @@ def accumulator_handshake(tiles: int = 5, epilogue_warps: int = 2):
     return progs, expected
 
 
+def stem_row_ring(stages: int = 5, images: int = 2, oh: int = 4):
+    """ResNet stem forward (gemm_tcgen05.cu, conv == 4): input rows stream through the A stages as a
+    ring.  Output row `o` of an image needs input rows o .. o + 3, of which only o + 3 is new unless
+    the tile starts an image; the issuer waits on all four (three of them for a phase it has already
+    seen), releases row o after the tile, and the three rows nobody else will read at the end of an
+    image."""
+    prod, mma = [], []
+    expected = {}
+    for s in range(stages):
+        expected[f"full{s}"] = expected[f"empty{s}"] = 1
+    seq = 0
+    base = loaded = 0
+    for b in range(images):
+        for o in range(oh):
+            fresh = o == 0
+            for h in range(o if fresh else o + 3, o + 4):
+                slot, use = seq % stages, seq // stages
+                prod += [("wait", f"empty{slot}", (use & 1) ^ 1), ("load", f"full{slot}", f"row{slot}", (b, h))]
+                seq += 1
+            base = loaded if fresh else base + 1
+            first_new = 0 if fresh else 3
+            loaded += 4 if fresh else 1
+            for i in range(4):
+                sq = base + i
+                slot = sq % stages
+                mma.append(("wait", f"full{slot}", (sq // stages) & 1))
+                mma.append(("read" if i >= first_new else "expect", f"row{slot}", (b, o + i)))
+            last = o == oh - 1
+            for i in range(4 if last else 1):
+                slot = (base + i) % stages
+                mma += [("release", f"row{slot}"), ("async_arrive", f"empty{slot}")]
+    return {"producer": tuple(prod), "mma": tuple(mma)}, expected
+
+
 def ll_allreduce(ranks: int = 2, calls: int = 4, parities: int = 2):
     """The flag-in-payload ("LL") all-reduce of comm.cu between kernels of successive calls: every
     rank stores its chunk, tagged with the call number, into its cell of every peer's receive buffer
@@ -342,6 +376,8 @@ PROTOCOLS = {
     "conv3x3 strips + weights, two issuers": lambda: conv3x3_operands(2, 3, 2, 3),
     "conv3x3, second sub-tile idle (plain arrivals)": lambda: conv3x3_operands(2, 2, 2, 2, True),
     "accumulator hand-over, two buffers": lambda: accumulator_handshake(5, 2),
+    "stem input-row ring, 5 stages": lambda: stem_row_ring(5, 2, 4),
+    "stem input-row ring, 4 stages (the minimum)": lambda: stem_row_ring(4, 2, 3),
     "LL all-reduce, 2 ranks, two receive parities": lambda: ll_allreduce(2, 5, 2),
     "LL all-reduce, 3 ranks, two receive parities": lambda: ll_allreduce(3, 3, 2),
     "fused all-reduce + optimizer, barrier before and after, 2 ranks": lambda: fused_allreduce(2, 3),
